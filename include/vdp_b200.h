@@ -1,0 +1,187 @@
+/*
+ * vdp_b200 -- C ABI of the B200 (sm_100a, float64) implementation of markovflow's VDP / CVI-DP
+ * site-update hot path.  Reference: AaltoML/vi-diffusion-processes (paths below are relative to it).
+ *
+ * The reference has no FFI of its own for this path; its only native seam is the set of TensorFlow
+ * custom ops it imports from banded_matrices (markovflow/block_tri_diag.py:22-31,
+ * markovflow/ssm_gaussian_transformations.py:23).  The entry points below are what a binding for
+ * this path replaces, op level first (one per banded op, block layout), then the fused level
+ * (one per Python function on the path).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host; the caller owns every buffer,
+ *     the library never allocates outputs;
+ *   - float64, row-major, reference tensor layout with a leading batch axis:
+ *       vectors   [B, n, D]      block diagonals [B, n, D, D]      block sub-diagonals [B, n-1, D, D]
+ *     (n = N + 1 grid points, N transitions, D = state dimension, 1..3);
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on it;
+ *   - return value: 0 = launched, negative = VDP_E_* (nothing launched);
+ *   - `status` (optional, may be NULL) is a device int64[2]: {code, flat grid index b*n+k of the first
+ *     block whose Cholesky pivot was not positive / not finite}; code 0 = clean.  Read it with
+ *     vdp_read_status (synchronises the stream).
+ */
+#ifndef VDP_B200_H
+#define VDP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VDP_OK 0
+#define VDP_E_BADARG (-1)   /* unsupported D, drift/D combination, null pointer, negative size */
+#define VDP_E_CUDA (-2)     /* a CUDA runtime call failed; see vdp_last_error() */
+#define VDP_E_WORKSPACE (-3) /* workspace too small */
+#define VDP_STATUS_NOT_PD 1
+
+/* drift plugin ids: markovflow/sde/sde.py classes; 7 and 8 are extensions (no 3-D SDE in the reference) */
+enum {
+    VDP_DRIFT_OU = 0,       /* params: decay                      sde.py:134-176 */
+    VDP_DRIFT_DW = 1,       /* params: scale, c                   sde.py:179-224 */
+    VDP_DRIFT_BENES = 2,    /* params: theta                      sde.py:227-268 */
+    VDP_DRIFT_SINE = 3,     /* params: theta                      sde.py:271-312 */
+    VDP_DRIFT_SQRT = 4,     /* params: theta                      sde.py:315-356 */
+    VDP_DRIFT_VDP = 5,      /* params: a, tau      (D = 2)        sde.py:433-518 */
+    VDP_DRIFT_MLP131 = 6,   /* params: w1[3], b1[3], w2[3], b2    sde.py:359-430 */
+    VDP_DRIFT_LORENZ63 = 7, /* params: sigma, rho, beta (D = 3)   extension */
+    VDP_DRIFT_OU_ND = 8     /* params: decay, full Jacobian       extension */
+};
+
+int vdp_version(void);
+const char* vdp_last_error(void);
+/* copies status[2] to the host after synchronising `stream`; returns status[0] */
+int64_t vdp_read_status(const int64_t* status, int64_t* out_host2, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * op level -- banded_matrices replacements in block layout
+ * ---------------------------------------------------------------------------------------------- */
+
+/* cholesky_band  (block_tri_diag.py:440  SymmetricBlockTriDiagonal.cholesky)
+ * Kd [B,n,D,D] symmetric, Ks [B,n-1,D,D] = K_{k+1,k} (NULL: block diagonal only) -> Ld, Ls */
+int vdp_btd_cholesky(const double* Kd, const double* Ks, double* Ld, double* Ls,
+                     int64_t B, int64_t n, int D, int64_t* status, void* stream);
+
+/* inverse_from_cholesky_band  (block_tri_diag.py:318-337 block_diagonal_of_inverse;
+ * ssm_gaussian_transformations.py:443-445): Sd = blocks Sigma_kk, Ss = Sigma_{k+1,k} (may be NULL) */
+int vdp_btd_inverse_band(const double* Ld, const double* Ls, double* Sd, double* Ss,
+                         int64_t B, int64_t n, int D, void* stream);
+
+/* solve_triang_mat  (block_tri_diag.py:339-351 LowerTriangularBlockTriDiagonal.solve)
+ * x = L^-1 rhs (transpose = 0) or L^-T rhs (transpose = 1); rhs, x: [B,n,D]; Ls may be NULL */
+int vdp_btd_solve(const double* Ld, const double* Ls, const double* rhs, double* x, int transpose,
+                  int64_t B, int64_t n, int D, void* stream);
+
+/* product_band_mat  (block_tri_diag.py:175-199 dense_mult): y = M x, M symmetric block-tridiagonal
+ * (symmetric = 1) or lower block-bidiagonal (symmetric = 0, optional transpose) */
+int vdp_btd_matvec(const double* Md, const double* Ms, const double* x, double* y, int symmetric,
+                   int transpose, int64_t B, int64_t n, int D, void* stream);
+
+/* abs_log_det  (block_tri_diag.py:353-366): out[b] = sum_k sum_i log |Ld[b,k,i,i]| */
+int vdp_btd_logdet(const double* Ld, double* out, int64_t B, int64_t n, int D, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * fused level
+ * ---------------------------------------------------------------------------------------------- */
+
+/* SDE.expected_drift / expected_gradient_drift  (sde.py:92-131, 501-518; gpflow mvnquad, H nodes/dim)
+ * m [count,D], S [count,D,D] -> Ef [count,D]; EJ [count,D,D] when the drift has a full Jacobian
+ * (VDP, LORENZ63, OU_ND), else [count,D] = E[d(sum_i f_i)/dx]  (either output may be NULL) */
+int vdp_gh_expect(int drift_id, const double* params_host, const double* m, const double* S, int H,
+                  double* Ef, double* EJ, int64_t count, int D, int64_t* status, void* stream);
+
+/* linearize_sde + LinearDrift.to_ssm  (sde_utils.py:119-179, drift.py:64-116) with the optional
+ * clip of variational_cvi_sde.py:417-430.  m,S are the linearisation path on grid points 1..N
+ * ([B,N,D],[B,N,D,D]); time_grid [N+1]; q_host [D,D]; outputs A [B,N,D,D], b [B,N,D], cholQ [B,N,D,D].
+ * clip = 1: A and b are clipped to [clip_lo, clip_hi] after the un-clipped values have been written to
+ * A_lin, b_lin (which may be NULL). */
+int vdp_linearize_to_ssm(int drift_id, const double* params_host, const double* q_host,
+                         const double* time_grid, const double* m, const double* S,
+                         double* A, double* b, double* cholQ, double* A_lin, double* b_lin,
+                         int clip, double clip_lo, double clip_hi,
+                         int64_t B, int64_t N, int D, int64_t* status, void* stream);
+
+/* ssm_to_naturals  (ssm_gaussian_transformations.py:182-253):
+ * A [B,N,D,D], b [B,N,D], cholQ [B,N,D,D], mu0 [B,D], cholP0 [B,D,D] -> th1 [B,N+1,D], thd, ths */
+int vdp_ssm_to_naturals(const double* A, const double* b, const double* cholQ, const double* mu0,
+                        const double* cholP0, double* th1, double* thd, double* ths,
+                        int64_t B, int64_t N, int D, void* stream);
+
+/* naturals_to_ssm_params  (ssm_gaussian_transformations.py:333-511).
+ * workspace: vdp_naturals_to_ssm_workspace(B,N,D) bytes */
+size_t vdp_naturals_to_ssm_workspace(int64_t B, int64_t N, int D);
+int vdp_naturals_to_ssm(const double* th1, const double* thd, const double* ths,
+                        double* A, double* b, double* cholQ, double* mu0, double* cholP0,
+                        void* workspace, size_t workspace_bytes,
+                        int64_t B, int64_t N, int D, int64_t* status, void* stream);
+
+/* StateSpaceModel.marginals  (state_space_model.py:231-262, 431-483; gauss_markov.py:107-117)
+ * -> m [B,N+1,D], Sd [B,N+1,D,D].  workspace: vdp_ssm_marginals_workspace(B,N,D) bytes */
+size_t vdp_ssm_marginals_workspace(int64_t B, int64_t N, int D);
+int vdp_ssm_marginals(const double* A, const double* b, const double* cholQ, const double* mu0,
+                      const double* cholP0, double* m, double* Sd,
+                      void* workspace, size_t workspace_bytes,
+                      int64_t B, int64_t N, int D, int64_t* status, void* stream);
+
+/* ssm_to_expectations / expectations_to_ssm_params  (ssm_gaussian_transformations.py:32-178) */
+int vdp_ssm_to_expectations(const double* A, const double* m, const double* Sd,
+                            double* e1, double* ed, double* es, int64_t B, int64_t N, int D, void* stream);
+int vdp_expectations_to_ssm(const double* e1, const double* ed, const double* es,
+                            double* A, double* b, double* cholQ, double* mu0, double* cholP0,
+                            int64_t B, int64_t N, int D, int64_t* status, void* stream);
+
+/* SDE_SSM_KL_with_grads_wrt_exp_params  (sde_utils.py:473-547), H = 20:
+ * q given by its transitions A [B,N,D,D] and marginals m, Sd; prior x0 ~ N(x0_mu_host, x0_cov_host);
+ * dt = float(grid[1]-grid[0]) (used in f_p), time_grid gives the per-step Q_p = delta_k q.
+ * -> kl [B], g1 [B,N+1,D], gd [B,N+1,D,D], gs [B,N,D,D] */
+int vdp_cvi_kl_and_grad(int drift_id, const double* params_host, const double* q_host, double dt,
+                        const double* time_grid, const double* x0_mu_host, const double* x0_cov_host,
+                        const double* A, const double* m, const double* Sd,
+                        double* kl, double* g1, double* gd, double* gs,
+                        int64_t B, int64_t N, int D, int64_t* status, void* stream);
+
+/* One CVI-DP site update = cvi_dp_trainer.py:71-77 once:
+ *   CVISitesSSM.update_data_sites      variational_cvi_sde.py:301-317
+ *   CVISitesSSM.update_girsanov_sites  variational_cvi_sde.py:279-299  (+ CVISitesSDE.grad_kl_wrt_exp_param :488-493)
+ *   CVISitesSSM.classic_elbo           variational_cvi_sde.py:339-352  (+ CVISitesSDE.KL_q_p :446-486)
+ * In/out: girsanov sites g1,gd,gs; data sites d1,d2; fx_mus,fx_covs (posterior marginals).
+ * Out: q as an SSM, elbo/ve/kl [B]. */
+typedef struct vdp_cvi_problem {
+    int64_t B, N, n_obs;
+    int32_t D, drift_id;
+    double drift_params[16];
+    double q[9];               /* spectral density, row-major D x D */
+    double dt;                 /* float(time_grid[1] - time_grid[0]) */
+    double x0_mu[3], x0_cov[9];/* prior on the initial state (Gaussian) */
+    double lik_chol[9];        /* Cholesky factor of the Gaussian likelihood covariance */
+    double lr_data, lr_girsanov;
+    const double* time_grid;   /* [N+1] */
+    const double *pA, *pb, *pcholQ, *pmu0, *pcholP0; /* linearised prior p: [B,N,D,D] [B,N,D] [B,N,D,D] [B,D] [B,D,D] */
+    double *g1, *gd, *gs;      /* girsanov sites   [B,N+1,D] [B,N+1,D,D] [B,N,D,D] */
+    double *d1, *d2;           /* data sites       [B,n_obs,D] [B,n_obs,D,D] */
+    const int64_t* obs_idx;    /* [B,n_obs] grid index of each observation */
+    const double* obs_y;       /* [B,n_obs,D] */
+    double *fx_mus, *fx_covs;  /* [B,N+1,D] [B,N+1,D,D] */
+    double *qA, *qb, *qcholQ, *qmu0, *qcholP0;       /* posterior q as an SSM (out) */
+    double *elbo, *ve, *kl;    /* [B] (out) */
+    void* workspace;
+    size_t workspace_bytes;    /* >= vdp_cvi_workspace(B,N,D,n_obs) */
+    int64_t* status;           /* device int64[2] or NULL */
+    int32_t flags;             /* VDP_FLAG_* */
+    int32_t reserved;
+} vdp_cvi_problem;
+
+#define VDP_FLAG_DEFAULT 0
+#define VDP_FLAG_SKIP_DATA_UPDATE 1   /* leave the data sites as they are */
+#define VDP_FLAG_SKIP_ELBO 2          /* do not evaluate classic_elbo */
+
+size_t vdp_cvi_workspace(int64_t B, int64_t N, int D, int64_t n_obs);
+int vdp_cvi_site_update(const vdp_cvi_problem* problem_host, void* stream);
+/* classic_elbo only (no site is modified); fills elbo/ve/kl, q* and fx_* */
+int vdp_cvi_elbo(const vdp_cvi_problem* problem_host, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VDP_B200_H */

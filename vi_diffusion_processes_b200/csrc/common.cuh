@@ -1,0 +1,99 @@
+// Shared host/device plumbing for the vdp_b200 library: error reporting, the device status word,
+// dispatch over the state dimension D and the drift id.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/vdp_b200.h"
+#include "drifts.cuh"
+#include "smallmat.cuh"
+
+namespace vdp {
+
+void set_error(const char* fmt, ...);
+
+#define VDP_CHECK_CUDA(expr)                                                                   \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess) {                                                               \
+            ::vdp::set_error("%s failed at %s:%d: %s", #expr, __FILE__, __LINE__,             \
+                             cudaGetErrorString(_e));                                          \
+            return VDP_E_CUDA;                                                                 \
+        }                                                                                      \
+    } while (0)
+
+#define VDP_CHECK_LAUNCH()  VDP_CHECK_CUDA(cudaGetLastError())
+
+#define VDP_REQUIRE(cond, msg)                                                                 \
+    do {                                                                                       \
+        if (!(cond)) {                                                                         \
+            ::vdp::set_error("bad argument: %s (%s)", msg, #cond);                            \
+            return VDP_E_BADARG;                                                               \
+        }                                                                                      \
+    } while (0)
+
+// first failing block wins; status[0] = code, status[1] = flat index
+__device__ __forceinline__ void report_not_pd(int64_t* status, int64_t flat_index) {
+    if (status != nullptr) {
+        if (atomicCAS(reinterpret_cast<unsigned long long*>(status), 0ULL,
+                      static_cast<unsigned long long>(VDP_STATUS_NOT_PD)) == 0ULL) {
+            status[1] = flat_index;
+        }
+    }
+}
+
+inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+inline unsigned grid_for(int64_t work, int block) { return (unsigned)((work + block - 1) / block); }
+
+// call f.template operator()<D>() for D in 1..3
+#define VDP_DISPATCH_D(D, ...)                                                                 \
+    switch (D) {                                                                               \
+        case 1: { constexpr int kD = 1; __VA_ARGS__; } break;                                  \
+        case 2: { constexpr int kD = 2; __VA_ARGS__; } break;                                  \
+        case 3: { constexpr int kD = 3; __VA_ARGS__; } break;                                  \
+        default: ::vdp::set_error("state dimension %d not supported (1..3)", D); return VDP_E_BADARG; \
+    }
+
+// instantiate `CALL` with kDrift for every (drift, D) pair that exists
+#define VDP_DRIFT_CASE(ID, ...)                                                                \
+    case ID: {                                                                                 \
+        constexpr int kDrift = ID;                                                             \
+        if constexpr (::vdp::DriftValid<ID, kD>::value) { __VA_ARGS__; }                       \
+        else { ::vdp::set_error("drift %d is not defined for D=%d", ID, kD); return VDP_E_BADARG; } \
+    } break;
+
+#define VDP_DISPATCH_DRIFT(id, ...)                                                            \
+    switch (id) {                                                                              \
+        VDP_DRIFT_CASE(::vdp::DRIFT_OU, __VA_ARGS__)                                           \
+        VDP_DRIFT_CASE(::vdp::DRIFT_DW, __VA_ARGS__)                                           \
+        VDP_DRIFT_CASE(::vdp::DRIFT_BENES, __VA_ARGS__)                                        \
+        VDP_DRIFT_CASE(::vdp::DRIFT_SINE, __VA_ARGS__)                                         \
+        VDP_DRIFT_CASE(::vdp::DRIFT_SQRT, __VA_ARGS__)                                         \
+        VDP_DRIFT_CASE(::vdp::DRIFT_VDP, __VA_ARGS__)                                          \
+        VDP_DRIFT_CASE(::vdp::DRIFT_MLP131, __VA_ARGS__)                                       \
+        VDP_DRIFT_CASE(::vdp::DRIFT_LORENZ63, __VA_ARGS__)                                     \
+        VDP_DRIFT_CASE(::vdp::DRIFT_OU_ND, __VA_ARGS__)                                        \
+        default: ::vdp::set_error("unknown drift id %d", id); return VDP_E_BADARG;             \
+    }
+
+inline DriftParams make_params(const double* host) {
+    DriftParams P;
+    for (int i = 0; i < VDP_MAX_DRIFT_PARAMS; ++i) P.p[i] = host ? host[i] : 0.0;
+    return P;
+}
+
+template <int D> struct HostMat { Mat<D> m; };
+template <int D> inline Mat<D> host_mat(const double* p) {
+    Mat<D> m;
+    for (int i = 0; i < D * D; ++i) m.a[i] = p[i];
+    return m;
+}
+template <int D> inline Vec<D> host_vec(const double* p) {
+    Vec<D> v;
+    for (int i = 0; i < D; ++i) v.v[i] = p[i];
+    return v;
+}
+
+}  // namespace vdp

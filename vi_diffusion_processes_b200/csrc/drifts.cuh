@@ -1,0 +1,135 @@
+// SDE drifts f(x) and their Jacobians as __device__ functors, selected at compile time.
+// Reference: markovflow/sde/sde.py (OU :152-163, double-well :200-211, Benes :244-255, sine :288-299,
+// sqrt :332-343, MLP 1-3-1 :394-416, Van der Pol :454-469).  The reference obtains Jacobians from a
+// GradientTape (:75-90, :484-499); every drift is a closed form so the analytic Jacobian is the same
+// function.  LORENZ63 and OU_ND are extensions (the reference has no 3-D SDE; BASELINE config 5).
+#pragma once
+#include "smallmat.cuh"
+
+namespace vdp {
+
+enum DriftId : int {
+    DRIFT_OU = 0, DRIFT_DW = 1, DRIFT_BENES = 2, DRIFT_SINE = 3, DRIFT_SQRT = 4,
+    DRIFT_VDP = 5, DRIFT_MLP131 = 6, DRIFT_LORENZ63 = 7, DRIFT_OU_ND = 8
+};
+
+constexpr int VDP_MAX_DRIFT_PARAMS = 16;
+struct DriftParams { double p[VDP_MAX_DRIFT_PARAMS]; };
+
+// f(x) and J_ij = d f_i / d x_j in one call (they share sub-expressions).
+template <int ID, int D> struct Drift;
+
+template <int D> struct Drift<DRIFT_OU, D> {
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<D>& x, Vec<D>& f, Mat<D>& J) {
+        J = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) { f(i) = -P.p[0] * x(i); J(i, i) = -P.p[0]; }
+    }
+};
+template <int D> struct Drift<DRIFT_OU_ND, D> : Drift<DRIFT_OU, D> {};
+
+template <int D> struct Drift<DRIFT_DW, D> {
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<D>& x, Vec<D>& f, Mat<D>& J) {
+        J = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            const double x2 = x(i) * x(i);
+            f(i) = P.p[0] * x(i) * (P.p[1] - x2);
+            J(i, i) = P.p[0] * (P.p[1] - 3.0 * x2);
+        }
+    }
+};
+template <int D> struct Drift<DRIFT_BENES, D> {
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<D>& x, Vec<D>& f, Mat<D>& J) {
+        J = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            const double t = tanh(x(i));
+            f(i) = P.p[0] * t;
+            J(i, i) = P.p[0] * (1.0 - t * t);
+        }
+    }
+};
+template <int D> struct Drift<DRIFT_SINE, D> {
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<D>& x, Vec<D>& f, Mat<D>& J) {
+        J = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            double s, c;
+            sincos(x(i) - P.p[0], &s, &c);
+            f(i) = s;
+            J(i, i) = c;
+        }
+    }
+};
+template <int D> struct Drift<DRIFT_SQRT, D> {
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<D>& x, Vec<D>& f, Mat<D>& J) {
+        J = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            const double r = sqrt(P.p[0] * fabs(x(i)));
+            const double sgn = (x(i) > 0.0) ? 1.0 : ((x(i) < 0.0) ? -1.0 : 0.0);
+            f(i) = r;
+            J(i, i) = 0.5 / r * P.p[0] * sgn;
+        }
+    }
+};
+// 1-3-1 relu MLP per coordinate; p = (w1[3], b1[3], w2[3], b2).  float64 (the reference's Keras layers
+// run in float32 and cast back, sde.py:411 -- documented deviation).
+template <int D> struct Drift<DRIFT_MLP131, D> {
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<D>& x, Vec<D>& f, Mat<D>& J) {
+        J = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            double acc = 0.0, g = 0.0;
+#pragma unroll
+            for (int h = 0; h < 3; ++h) {
+                const double pre = x(i) * P.p[h] + P.p[3 + h];
+                const bool on = pre > 0.0;
+                acc += (on ? pre : 0.0) * P.p[6 + h];
+                g += on ? (P.p[h] * P.p[6 + h]) : 0.0;
+            }
+            f(i) = acc + P.p[9];
+            J(i, i) = g;
+        }
+    }
+};
+// Van der Pol: f = tau [a (x1 - x1^3/3 - x2), x1 / a];  p = (a, tau).  D must be 2.
+template <> struct Drift<DRIFT_VDP, 2> {
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<2>& x, Vec<2>& f, Mat<2>& J) {
+        const double a = P.p[0], tau = P.p[1];
+        const double x1 = x(0), x2 = x(1);
+        f(0) = tau * (a * (x1 - (1.0 / 3.0) * (x1 * x1 * x1) - x2));
+        f(1) = tau * ((1.0 / a) * x1);
+        J(0, 0) = tau * a * (1.0 - x1 * x1);
+        J(0, 1) = -tau * a;
+        J(1, 0) = tau / a;
+        J(1, 1) = 0.0;
+    }
+};
+// Lorenz-63 (extension): f = [s (y - x), x (r - z) - y, x y - b z];  p = (sigma, rho, beta).  D must be 3.
+template <> struct Drift<DRIFT_LORENZ63, 3> {
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<3>& x, Vec<3>& f, Mat<3>& J) {
+        const double s = P.p[0], r = P.p[1], b = P.p[2];
+        const double X = x(0), Y = x(1), Z = x(2);
+        f(0) = s * (Y - X);
+        f(1) = X * (r - Z) - Y;
+        f(2) = X * Y - b * Z;
+        J(0, 0) = -s;    J(0, 1) = s;    J(0, 2) = 0.0;
+        J(1, 0) = r - Z; J(1, 1) = -1.0; J(1, 2) = -X;
+        J(2, 0) = Y;     J(2, 1) = X;    J(2, 2) = -b;
+    }
+};
+
+// Which (drift, D) pairs exist: the element-wise drifts for any D, VDP only D=2, LORENZ63 only D=3.
+template <int ID, int D> struct DriftValid { static constexpr bool value = true; };
+template <int D> struct DriftValid<DRIFT_VDP, D> { static constexpr bool value = (D == 2); };
+template <int D> struct DriftValid<DRIFT_LORENZ63, D> { static constexpr bool value = (D == 3); };
+
+// True when the reference's gradient_drift returns the full [D, D] Jacobian (batch_jacobian subclasses);
+// otherwise it returns d(sum_i f_i)/dx_j, a [D] vector (sde.py:86-90).
+__host__ __device__ inline bool drift_full_jacobian(int id) {
+    return id == DRIFT_VDP || id == DRIFT_LORENZ63 || id == DRIFT_OU_ND;
+}
+
+}  // namespace vdp

@@ -1,0 +1,307 @@
+// KL[q || p_SDE] along the Gaussian path and its reverse-mode gradient in expectation parameters.
+//
+// Reference: SDE_SSM_KL_with_grads_wrt_exp_params (sde_utils.py:473-547) -> expectations_to_ssm_params
+// (ssm_gaussian_transformations.py:93-178) -> SSM_KL_along_Gaussian_path (sde_utils.py:262-359) ->
+// mvnquad(H = 20); the gradient is what tf.GradientTape returns at sde_utils.py:545, i.e. the adjoint
+// of the DISCRETISED quadrature and of the D x D Choleskys (derivation: oracle/sde_np.py
+// sde_ssm_kl_and_grads, checked there against torch.autograd).
+//
+// Work decomposition: one group of G lanes per grid point i = (b, k).  The group evaluates transition
+// term k (if k < N): its quadrature, constants and adjoint.  A term touches nodes k ("left") and k+1
+// ("right"); the right part is handed to the neighbouring group through shared memory, the first
+// group of a block is a halo that only produces the right part for the block's first node.
+#pragma once
+#include "pointwise_kernels.cuh"
+#include "quad_core.cuh"
+
+namespace vdp {
+
+template <int D>
+struct KlNodePart {   // adjoint contributions of one transition term to one of its two nodes
+    Vec<D> gm;        // d term / d m        (before the -2 g_S m fold-in)
+    Mat<D> gS;        // d term / d S        (symmetric)
+};
+
+template <int D>
+struct KlTermOut {
+    double value;         // 0.5 (quad + C)
+    KlNodePart<D> left, right;
+    Mat<D> ges;           // d term / d eta_s[k]
+};
+
+// One transition term.  Inputs are the expectation parameters rebuilt from (A_q, m, S) exactly as
+// ssm_to_expectations does (ssm_gaussian_transformations.py:32-89).
+template <int DRIFT, int D, int H, int G>
+__device__ __forceinline__ void kl_term(const DriftParams& P, const Mat<D>& Qp, double dt, double pi_factor,
+                                        const Vec<D>& e1k, const Vec<D>& e1n, const Mat<D>& edk, const Mat<D>& edn,
+                                        const Mat<D>& esk, int lane, KlTermOut<D>& out, bool& ok) {
+    ExpToSsm<D> r;
+    exp_to_ssm_step(e1k, e1n, edk, edn, esk, r, ok);
+    const Mat<D> Qq = mmT(r.LQ, r.LQ);
+    const Mat<D> cQp = chol(Qp, ok);
+    const Mat<D> Qpinv = chol_inverse(cQp);
+    const Mat<D> Qpinv_s = sym(Qpinv);
+    // constants  C = -(logdet Qq - logdet Qp) - D + sum_i (Qp^-1)_ii (Qq)_ii   (sde_utils.py:317-330)
+    const Mat<D> cQq = chol(Qq, ok);
+    double tr = Qpinv(0, 0) * Qq(0, 0);
+#pragma unroll
+    for (int i = 1; i < D; ++i) tr += Qpinv(i, i) * Qq(i, i);
+    const double Cterm = -(logdet_from_chol(cQq) - logdet_from_chol(cQp)) - (double)D + tr;
+
+    // quadrature and its adjoint accumulators
+    double quad = 0.0;
+    Vec<D> gb = vec_zero<D>(), gmq = vec_zero<D>();
+    Mat<D> gA = mat_zero<D>(), LSb = mat_zero<D>();
+    constexpr int NP = NodeCount<H, D>::value;
+    for (int p = lane; p < NP; p += G) {
+        Vec<D> xi, f;
+        Mat<D> J;
+        double w;
+        gh_node<H, D>(p, xi, w);
+        w *= pi_factor;
+        const Vec<D> X = gh_point(r.LS, r.mk, xi);
+        Drift<DRIFT, D>::eval(P, X, f, J);
+        Vec<D> d;
+        const Vec<D> AX = mv(r.A, X);
+#pragma unroll
+        for (int i = 0; i < D; ++i) d(i) = (X(i) + dt * f(i)) - (AX(i) + r.b(i));
+        quad += w * dot(d, mv(Qpinv, d));
+        const Vec<D> rb = w * mv(Qpinv_s, d);
+        // Jd = (I + dt J) - A ;  Xb = Jd^T rb
+        Vec<D> Xb;
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            double s = 0.0;
+#pragma unroll
+            for (int j = 0; j < D; ++j) s += ((((i == j) ? 1.0 : 0.0) + dt * J(j, i)) - r.A(j, i)) * rb(j);
+            Xb(i) = s;
+        }
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            gb(i) -= rb(i);
+            gmq(i) += Xb(i);
+#pragma unroll
+            for (int j = 0; j < D; ++j) {
+                gA(i, j) -= rb(i) * X(j);
+                if (j <= i) LSb(i, j) += 1.4142135623730951 * (Xb(i) * xi(j));
+            }
+        }
+    }
+    quad = group_sum<G>(quad);
+    group_sum<G>(gb);
+    group_sum<G>(gmq);
+    group_sum<G>(gA);
+    group_sum<G>(LSb);
+
+    out.value = 0.5 * (quad + Cterm);
+    // ---- reverse through the pointwise algebra (same statement order as the oracle)
+    KlNodePart<D>& Lf = out.left;
+    KlNodePart<D>& Rt = out.right;
+    Lf.gm = gmq;
+    Lf.gS = chol_adjoint(r.LS, LSb);
+    Mat<D> diagQp = mat_zero<D>();
+#pragma unroll
+    for (int i = 0; i < D; ++i) diagQp(i, i) = Qpinv(i, i);
+    const Mat<D> gQc = sym(0.5 * (diagQp - chol_inverse(r.LQ)));
+    // b = m_{k+1} - A m_k
+    Rt.gm = gb;
+    gA = gA - outer(gb, r.mk);
+    Lf.gm = Lf.gm - Tmv(r.A, gb);
+    // Qc = S_{k+1} - A S_k A^T
+    Rt.gS = gQc;
+    gA = gA - 2.0 * mm(gQc, mm(r.A, r.Sk));
+    Lf.gS = Lf.gS - Tmm(r.A, mm(gQc, r.A));
+    // A = (S_k^-1 C)^T
+    const Mat<D> gC = chol_solve(r.LS, transpose(gA));
+    Lf.gS = Lf.gS + sym(-1.0 * mm(gC, r.A));
+    // C = eta_s^T - m_k m_{k+1}^T
+    out.ges = transpose(gC);
+    Lf.gm = Lf.gm - mv(gC, r.mn);
+    Rt.gm = Rt.gm - Tmv(gC, r.mk);
+}
+
+// shared-memory record handed from the group of node i to the group of node i+1
+template <int D>
+struct KlHandoff { double gm[D]; double gS[D * D]; };
+
+// Outputs per node i = (b,k): g1, gd (and gs for k < N) = d KL / d eta, plus the per-transition value
+// terms[i] (0 for k = N; KL_0 added at k = 0) for the deterministic reduction.
+// If `sites` update pointers are given (upd != 0) the girsanov site update of
+// variational_cvi_sde.py:286-296 is applied in place instead of writing the gradients:
+//   g1 += lr (scatter(d1) - dKL/deta1),  gd += lr (scatter(d2) - dKL/deta_d),  gs -= lr dKL/deta_s
+// where scatter(d.) has been pre-scattered into sc1/scd by the caller.
+template <int DRIFT, int D, int H, int G>
+__global__ void k_kl_grad(DriftParams P, Mat<D> q, double dt, double pi_factor,
+                          const double* __restrict__ time_grid, Vec<D> x0_mu, Mat<D> x0_cov,
+                          const double* __restrict__ Aq, const double* __restrict__ m,
+                          const double* __restrict__ Sd, double* __restrict__ terms, double* __restrict__ g1,
+                          double* __restrict__ gd, double* __restrict__ gs, int upd, double lr,
+                          const double* __restrict__ sc1, const double* __restrict__ scd, int64_t B, int64_t N,
+                          int64_t* status) {
+    extern __shared__ unsigned char smem_raw[];
+    KlHandoff<D>* hand = reinterpret_cast<KlHandoff<D>*>(smem_raw);
+    constexpr int DD = D * D;
+    const int groups = blockDim.x / G;          // groups per block, first one is the halo
+    const int gidx = threadIdx.x / G;
+    const int lane = threadIdx.x % G;
+    const int64_t n = N + 1;
+    const int64_t total = B * n;
+    const int64_t i = (int64_t)blockIdx.x * (groups - 1) + gidx - 1;   // flat node index of this group
+    const bool in_range = (i >= 0) && (i < total);
+    int64_t b = 0, k = 0;
+    if (in_range) { b = i / n; k = i % n; }
+    const bool has_term = in_range && (k < N);
+    bool ok = true;
+    KlTermOut<D> t;
+    Vec<D> mk = vec_zero<D>();
+    Mat<D> Sk = mat_eye<D>();
+    if (in_range) { mk = vec_load<D>(m + i * D); Sk = mat_load<D>(Sd + i * DD); }
+    if (has_term) {
+        const Vec<D> mn = vec_load<D>(m + (i + 1) * D);
+        const Mat<D> Sn = mat_load<D>(Sd + (i + 1) * DD);
+        const Mat<D> Ak = mat_load<D>(Aq + (b * N + k) * DD);
+        const Mat<D> edk = Sk + outer(mk, mk);
+        const Mat<D> edn = Sn + outer(mn, mn);
+        const Mat<D> esk = mm(Ak, Sk) + outer(mn, mk);
+        const double delta = time_grid[k + 1] - time_grid[k];
+        kl_term<DRIFT, D, H, G>(P, delta * q, dt, pi_factor, mk, mn, edk, edn, esk, lane, t, ok);
+        if (!ok && lane == 0) report_not_pd(status, i);
+        if (lane == 0) {
+#pragma unroll
+            for (int e = 0; e < D; ++e) hand[gidx].gm[e] = t.right.gm(e);
+#pragma unroll
+            for (int e = 0; e < DD; ++e) hand[gidx].gS[e] = t.right.gS.a[e];
+        }
+    }
+    __syncthreads();
+    if (!in_range || gidx == 0 || lane != 0) return;
+    // ---- node i: left part of term k + right part of term k-1 (+ KL_0 at k = 0)
+    Vec<D> gm = vec_zero<D>();
+    Mat<D> gS = mat_zero<D>();
+    double value = 0.0;
+    if (has_term) { gm = t.left.gm; gS = t.left.gS; value = t.value; }
+    if (k > 0) {
+#pragma unroll
+        for (int e = 0; e < D; ++e) gm(e) += hand[gidx - 1].gm[e];
+#pragma unroll
+        for (int e = 0; e < DD; ++e) gS.a[e] += hand[gidx - 1].gS[e];
+    } else {
+        // KL[q(x0) || p(x0)]  (sde_utils.py:536-541), q(x0) = N(m_0, S_0) through its Cholesky factor
+        bool ok0 = true;
+        const Mat<D> Lp = chol(x0_cov, ok0);
+        const Mat<D> Lq = chol(Sk, ok0);
+        const Mat<D> Ppinv = chol_inverse(Lp);
+        const Mat<D> Mq = trsm(Lp, Lq);
+        const Vec<D> diff = trsv(Lp, x0_mu - mk);
+        double fro = 0.0;
+#pragma unroll
+        for (int e = 0; e < DD; ++e) fro += Mq.a[e] * Mq.a[e];
+        value += 0.5 * (fro + dot(diff, diff) - (double)D + logdet_from_chol(Lp) - logdet_from_chol(Lq));
+        gm = gm + mv(Ppinv, mk - x0_mu);
+        gS = gS + 0.5 * (Ppinv - chol_inverse(Lq));
+    }
+    // S = eta_d - m m^T
+    gm = gm - 2.0 * mv(gS, mk);
+    terms[i] = value;
+    if (!upd) {
+        vec_store<D>(g1 + i * D, gm);
+        mat_store<D>(gd + i * DD, gS);
+        if (has_term) mat_store<D>(gs + (b * N + k) * DD, t.ges);
+    } else {
+        Vec<D> s1 = vec_zero<D>();
+        Mat<D> s2 = mat_zero<D>();
+        if (sc1) { s1 = vec_load<D>(sc1 + i * D); s2 = mat_load<D>(scd + i * DD); }
+        vec_store<D>(g1 + i * D, vec_load<D>(g1 + i * D) + lr * (s1 - gm));
+        mat_store<D>(gd + i * DD, mat_load<D>(gd + i * DD) + lr * (s2 - gS));
+        if (has_term) {
+            const int64_t tt = b * N + k;
+            mat_store<D>(gs + tt * DD, mat_load<D>(gs + tt * DD) - lr * t.ges);
+        }
+    }
+}
+
+// KL_q_p of classic_elbo (variational_cvi_sde.py:446-486): value only, with the reference's
+// element-wise square of the Cholesky factor (:452) standing in for Q_q.
+template <int DRIFT, int D, int H, int G>
+__global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
+                           const double* __restrict__ Aq, const double* __restrict__ bq,
+                           const double* __restrict__ cholQq, const double* __restrict__ m,
+                           const double* __restrict__ Sd, const double* __restrict__ qmu0,
+                           const double* __restrict__ qcholP0, const double* __restrict__ pmu0,
+                           const double* __restrict__ pcholP0, double* __restrict__ terms, int64_t B, int64_t N,
+                           int64_t* status) {
+    const int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / G;
+    const int lane = threadIdx.x % G;
+    const int64_t n = N + 1;
+    if (i >= B * n) return;
+    constexpr int DD = D * D;
+    const int64_t b = i / n, k = i % n;
+    if (k == N) { if (lane == 0) terms[i] = 0.0; return; }
+    const int64_t tt = b * N + k;
+    bool ok = true;
+    const Mat<D> Ak = mat_load<D>(Aq + tt * DD);
+    const Vec<D> bk = vec_load<D>(bq + tt * D);
+    const Mat<D> cq = mat_load<D>(cholQq + tt * DD);
+    Mat<D> Qq;
+#pragma unroll
+    for (int e = 0; e < DD; ++e) Qq.a[e] = cq.a[e] * cq.a[e];
+    const Mat<D> Qp = dt * q;
+    const Mat<D> cQp = chol(Qp, ok);
+    const Mat<D> Qpinv = chol_inverse(cQp);
+    const Mat<D> cQq = chol(Qq, ok);   // tf.linalg.logdet reads the lower triangle
+    double tr = Qpinv(0, 0) * Qq(0, 0);
+#pragma unroll
+    for (int e = 1; e < D; ++e) tr += Qpinv(e, e) * Qq(e, e);
+    const double Cterm = -(logdet_from_chol(cQq) - logdet_from_chol(cQp)) - (double)D + tr;
+    const Vec<D> mk = vec_load<D>(m + i * D);
+    const Mat<D> LS = chol(mat_load<D>(Sd + i * DD), ok);
+    double quad = 0.0;
+    constexpr int NP = NodeCount<H, D>::value;
+    for (int p = lane; p < NP; p += G) {
+        Vec<D> xi, f, d;
+        Mat<D> J;
+        double w;
+        gh_node<H, D>(p, xi, w);
+        w *= pi_factor;
+        const Vec<D> X = gh_point(LS, mk, xi);
+        Drift<DRIFT, D>::eval(P, X, f, J);
+        const Vec<D> AX = mv(Ak, X);
+#pragma unroll
+        for (int e = 0; e < D; ++e) d(e) = (X(e) + dt * f(e)) - (AX(e) + bk(e));
+        quad += w * dot(d, mv(Qpinv, d));
+    }
+    quad = group_sum<G>(quad);
+    if (lane == 0) {
+        double value = 0.5 * (quad + Cterm);
+        if (k == 0) {
+            // kl_0 (variational_cvi_sde.py:478-484): both covariances are rebuilt as chol chol^T
+            const Mat<D> cq0 = mat_load<D>(qcholP0 + b * DD), cp0 = mat_load<D>(pcholP0 + b * DD);
+            const Mat<D> Lq = chol(mmT(cq0, cq0), ok), Lp = chol(mmT(cp0, cp0), ok);
+            const Mat<D> Mq = trsm(Lp, Lq);
+            const Vec<D> diff = trsv(Lp, vec_load<D>(pmu0 + b * D) - vec_load<D>(qmu0 + b * D));
+            double fro = 0.0;
+#pragma unroll
+            for (int e = 0; e < DD; ++e) fro += Mq.a[e] * Mq.a[e];
+            value += 0.5 * (fro + dot(diff, diff) - (double)D + logdet_from_chol(Lp) - logdet_from_chol(Lq));
+        }
+        if (!ok) report_not_pd(status, i);
+        terms[i] = value;
+    }
+}
+
+// deterministic per-sequence sum of terms[b, 0..n) (+ optional extra[b]) : one block per sequence
+__global__ void k_reduce_terms(const double* __restrict__ terms, int64_t n, double* __restrict__ out) {
+    __shared__ double sh[256];
+    const int64_t b = blockIdx.x;
+    double acc = 0.0;
+    for (int64_t k = threadIdx.x; k < n; k += blockDim.x) acc += terms[b * n + k];
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = blockDim.x / 2; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[b] = sh[0];
+}
+
+}  // namespace vdp

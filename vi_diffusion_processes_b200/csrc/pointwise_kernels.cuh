@@ -1,0 +1,182 @@
+// Pointwise-in-time kernels: SSM <-> natural / expectation parameters, site assembly, data sites.
+// One thread per (sequence, grid point).
+#pragma once
+#include "common.cuh"
+
+namespace vdp {
+
+// ssm_to_naturals (ssm_gaussian_transformations.py:182-253) for grid point k of sequence b, optionally
+// summed with the girsanov sites: theta = nat(p) + g  (variational_cvi_sde.py:161-174; the data sites
+// are scattered on top by k_scatter_data, in the reference's left-to-right order).
+template <int D>
+__global__ void k_ssm_to_naturals(const double* __restrict__ A, const double* __restrict__ bo,
+                                  const double* __restrict__ cholQ, const double* __restrict__ mu0,
+                                  const double* __restrict__ cholP0, const double* __restrict__ g1,
+                                  const double* __restrict__ gd, const double* __restrict__ gs,
+                                  double* __restrict__ th1, double* __restrict__ thd, double* __restrict__ ths,
+                                  int64_t B, int64_t N) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t n = N + 1;
+    if (i >= B * n) return;
+    constexpr int DD = D * D;
+    const int64_t b = i / n, k = i % n;
+    const Mat<D> ck = (k == 0) ? mat_load<D>(cholP0 + b * DD) : mat_load<D>(cholQ + (b * N + k - 1) * DD);
+    const Vec<D> ok = (k == 0) ? vec_load<D>(mu0 + b * D) : vec_load<D>(bo + (b * N + k - 1) * D);
+    Vec<D> t1 = chol_solve(ck, ok);
+    Mat<D> td = chol_inverse(ck);
+    if (k < N) {
+        const Mat<D> Ak = mat_load<D>(A + (b * N + k) * DD);
+        const Mat<D> cn = mat_load<D>(cholQ + (b * N + k) * DD);
+        const Vec<D> tn = chol_solve(cn, vec_load<D>(bo + (b * N + k) * D));
+        const Mat<D> LinvA = trsm(cn, Ak);
+        Mat<D> ts = trsmT(cn, LinvA);
+        t1 = t1 - Tmv(Ak, tn);
+        td = td + Tmm(LinvA, LinvA);
+        if (gs) ts = ts + mat_load<D>(gs + (b * N + k) * DD);
+        mat_store<D>(ths + (b * N + k) * DD, ts);
+    }
+    td = -0.5 * td;
+    if (g1) t1 = t1 + vec_load<D>(g1 + i * D);
+    if (gd) td = td + mat_load<D>(gd + i * DD);
+    vec_store<D>(th1 + i * D, t1);
+    mat_store<D>(thd + i * DD, td);
+}
+
+// tf.scatter_nd of the data sites onto the grid, added to theta (duplicates accumulate)
+template <int D>
+__global__ void k_scatter_data(const double* __restrict__ d1, const double* __restrict__ d2,
+                               const int64_t* __restrict__ obs_idx, double* __restrict__ th1,
+                               double* __restrict__ thd, int64_t B, int64_t N, int64_t n_obs) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= B * n_obs) return;
+    constexpr int DD = D * D;
+    const int64_t b = i / n_obs;
+    const int64_t k = obs_idx[i];
+    if (k < 0 || k > N) return;
+    const int64_t node = b * (N + 1) + k;
+#pragma unroll
+    for (int e = 0; e < D; ++e) atomicAdd(th1 + node * D + e, d1[i * D + e]);
+#pragma unroll
+    for (int e = 0; e < DD; ++e) atomicAdd(thd + node * DD + e, d2[i * DD + e]);
+}
+
+// ssm_to_expectations (ssm_gaussian_transformations.py:32-89)
+template <int D>
+__global__ void k_ssm_to_expectations(const double* __restrict__ A, const double* __restrict__ m,
+                                      const double* __restrict__ Sd, double* __restrict__ e1,
+                                      double* __restrict__ ed, double* __restrict__ es, int64_t B, int64_t N) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t n = N + 1;
+    if (i >= B * n) return;
+    constexpr int DD = D * D;
+    const int64_t b = i / n, k = i % n;
+    const Vec<D> mk = vec_load<D>(m + i * D);
+    const Mat<D> Sk = mat_load<D>(Sd + i * DD);
+    vec_store<D>(e1 + i * D, mk);
+    mat_store<D>(ed + i * DD, Sk + outer(mk, mk));
+    if (k < N) {
+        const Mat<D> Ak = mat_load<D>(A + (b * N + k) * DD);
+        const Vec<D> mn = vec_load<D>(m + (i + 1) * D);
+        mat_store<D>(es + (b * N + k) * DD, mm(Ak, Sk) + outer(mn, mk));
+    }
+}
+
+// expectations_to_ssm_params (ssm_gaussian_transformations.py:93-178), one thread per transition
+// (thread k = N of each sequence writes nothing; thread 0 also writes mu0 / cholP0)
+template <int D>
+struct ExpToSsm {
+    Mat<D> Sk, Sn, Csub, LS, A, Qc, LQ;
+    Vec<D> mk, mn, b;
+};
+template <int D>
+__device__ __forceinline__ void exp_to_ssm_step(const Vec<D>& e1k, const Vec<D>& e1n, const Mat<D>& edk,
+                                                const Mat<D>& edn, const Mat<D>& esk, ExpToSsm<D>& r, bool& ok) {
+    r.mk = e1k;
+    r.mn = e1n;
+    r.Sk = edk - outer(e1k, e1k);
+    r.Sn = edn - outer(e1n, e1n);
+    r.Csub = transpose(esk) - outer(e1k, e1n);
+    r.LS = chol(r.Sk, ok);
+    r.A = transpose(chol_solve(r.LS, r.Csub));
+    r.b = e1n - mv(r.A, e1k);
+    r.Qc = r.Sn - mm(r.A, mmT(r.Sk, r.A));
+    r.LQ = chol(r.Qc, ok);
+}
+
+template <int D>
+__global__ void k_expectations_to_ssm(const double* __restrict__ e1, const double* __restrict__ ed,
+                                      const double* __restrict__ es, double* __restrict__ A,
+                                      double* __restrict__ bo, double* __restrict__ cholQ,
+                                      double* __restrict__ mu0, double* __restrict__ cholP0, int64_t B, int64_t N,
+                                      int64_t* status) {
+    const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (t >= B * N) return;
+    constexpr int DD = D * D;
+    const int64_t b = t / N, k = t % N;
+    const int64_t i = b * (N + 1) + k;
+    ExpToSsm<D> r;
+    bool ok = true;
+    exp_to_ssm_step(vec_load<D>(e1 + i * D), vec_load<D>(e1 + (i + 1) * D), mat_load<D>(ed + i * DD),
+                    mat_load<D>(ed + (i + 1) * DD), mat_load<D>(es + t * DD), r, ok);
+    if (!ok) report_not_pd(status, i);
+    mat_store<D>(A + t * DD, r.A);
+    vec_store<D>(bo + t * D, r.b);
+    mat_store<D>(cholQ + t * DD, r.LQ);
+    if (k == 0) {
+        vec_store<D>(mu0 + b * D, r.mk);
+        mat_store<D>(cholP0 + b * DD, r.LS);
+    }
+}
+
+// update_data_sites (variational_cvi_sde.py:301-314) for the Gaussian likelihood
+// (multivariate_gaussian.py:82-116, variational_cvi.py:448-462):
+//   dVE/dmu = Sigma^-1 (y - mu),  dVE/dS = -1/2 Sigma^-1,  grads wrt (mu, S + mu mu^T) = (g_mu - 2 g_S mu, g_S)
+template <int D>
+__global__ void k_data_site_update(const double* __restrict__ fx_mus, const int64_t* __restrict__ obs_idx,
+                                   const double* __restrict__ obs_y, Mat<D> lik_chol, double lr,
+                                   double* __restrict__ d1, double* __restrict__ d2, int64_t B, int64_t N,
+                                   int64_t n_obs) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= B * n_obs) return;
+    constexpr int DD = D * D;
+    const int64_t b = i / n_obs;
+    const int64_t k = obs_idx[i];
+    const Vec<D> mu = vec_load<D>(fx_mus + (b * (N + 1) + k) * D);
+    const Mat<D> inv = chol_inverse(lik_chol);
+    const Vec<D> gmu = mv(sym(inv), vec_load<D>(obs_y + i * D) - mu);
+    const Mat<D> gS = -0.5 * inv;
+    const Vec<D> g1 = gmu - 2.0 * mv(gS, mu);
+    const Vec<D> o1 = vec_load<D>(d1 + i * D);
+    const Mat<D> o2 = mat_load<D>(d2 + i * DD);
+    vec_store<D>(d1 + i * D, (1.0 - lr) * o1 + lr * g1);
+    mat_store<D>(d2 + i * DD, (1.0 - lr) * o2 + lr * gS);
+}
+
+// variational_expectation (variational_cvi_sde.py:319-337): one thread per sequence, fixed order
+template <int D>
+__global__ void k_variational_expectation(const double* __restrict__ fx_mus, const double* __restrict__ fx_covs,
+                                          const int64_t* __restrict__ obs_idx, const double* __restrict__ obs_y,
+                                          Mat<D> lik_chol, double* __restrict__ ve, int64_t B, int64_t N,
+                                          int64_t n_obs) {
+    const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    constexpr int DD = D * D;
+    const Mat<D> inv = chol_inverse(lik_chol);
+    double logdet = 0.0;
+#pragma unroll
+    for (int e = 0; e < D; ++e) logdet += log(fabs(lik_chol(e, e)));
+    double acc = 0.0;
+    for (int64_t j = 0; j < n_obs; ++j) {
+        const int64_t i = b * n_obs + j;
+        const int64_t node = b * (N + 1) + obs_idx[i];
+        const Vec<D> z = trsv(lik_chol, vec_load<D>(obs_y + i * D) - vec_load<D>(fx_mus + node * D));
+        const Mat<D> S = mat_load<D>(fx_covs + node * DD);
+        double tr = 0.0;
+#pragma unroll
+        for (int e = 0; e < DD; ++e) tr += inv.a[e] * S.a[e];
+        acc += -0.5 * tr + (-0.5 * dot(z, z) - logdet - 0.5 * D * 1.8378770664093453);
+    }
+    ve[b] = acc;
+}
+
+}  // namespace vdp

@@ -1,0 +1,117 @@
+// C ABI of libvdp_b200 (see include/vdp_b200.h).  Host-side launch logic only; kernels live in the
+// .cuh files next to this one.  Compiled for sm_100a.
+#include <stdarg.h>
+#include <string.h>
+
+#include <cmath>
+
+#include "btd_kernels.cuh"
+#include "common.cuh"
+#include "kl_kernels.cuh"
+#include "pointwise_kernels.cuh"
+#include "quad_core.cuh"
+
+namespace vdp {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+}
+
+constexpr int kSeqBlock = 32;   // threads per block for one-thread-per-sequence sweeps (spread over SMs)
+constexpr int kPtBlock = 128;   // threads per block for pointwise kernels
+
+static inline double pi_factor(int D) { return std::pow(M_PI, -D * 0.5); }
+
+// bump allocator over the caller's workspace
+struct Arena {
+    char* base;
+    size_t size, used;
+    Arena(void* p, size_t n) : base((char*)p), size(n), used(0) {}
+    double* take(size_t doubles) {
+        size_t bytes = (doubles * sizeof(double) + 255) & ~size_t(255);
+        if (used + bytes > size) return nullptr;
+        double* r = (double*)(base + used);
+        used += bytes;
+        return r;
+    }
+};
+static inline size_t padded(size_t doubles) { return (doubles * sizeof(double) + 255) & ~size_t(255); }
+
+}  // namespace vdp
+
+using namespace vdp;
+
+extern "C" {
+
+int vdp_version(void) { return 100; }
+const char* vdp_last_error(void) { return g_error; }
+
+int64_t vdp_read_status(const int64_t* status, int64_t* out_host2, void* stream) {
+    int64_t h[2] = {0, 0};
+    if (status) {
+        if (cudaStreamSynchronize(as_stream(stream)) != cudaSuccess) return VDP_E_CUDA;
+        if (cudaMemcpy(h, status, sizeof(h), cudaMemcpyDeviceToHost) != cudaSuccess) return VDP_E_CUDA;
+    }
+    if (out_host2) { out_host2[0] = h[0]; out_host2[1] = h[1]; }
+    return h[0];
+}
+
+// ---------------------------------------------------------------------------------------------------
+// op level
+// ---------------------------------------------------------------------------------------------------
+
+int vdp_btd_cholesky(const double* Kd, const double* Ks, double* Ld, double* Ls, int64_t B, int64_t n, int D,
+                     int64_t* status, void* stream) {
+    VDP_REQUIRE(Kd && Ld && B >= 0 && n >= 1, "Kd, Ld, B, n");
+    VDP_REQUIRE((Ks == nullptr) == (Ls == nullptr), "Ks and Ls must both be given or both be NULL");
+    if (B == 0) return VDP_OK;
+    VDP_DISPATCH_D(D, (k_chol_fwd<kD><<<grid_for(B, kSeqBlock), kSeqBlock, 0, as_stream(stream)>>>(
+                          Kd, Ks, 1.0, 1.0, Ld, Ls, B, n, status)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+int vdp_btd_inverse_band(const double* Ld, const double* Ls, double* Sd, double* Ss, int64_t B, int64_t n, int D,
+                         void* stream) {
+    VDP_REQUIRE(Ld && Sd && B >= 0 && n >= 1, "Ld, Sd, B, n");
+    if (B == 0) return VDP_OK;
+    VDP_DISPATCH_D(D, (k_invband_bwd<kD><<<grid_for(B, kSeqBlock), kSeqBlock, 0, as_stream(stream)>>>(
+                          Ld, Ls, Sd, Ls ? Ss : nullptr, B, n)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+int vdp_btd_solve(const double* Ld, const double* Ls, const double* rhs, double* x, int transpose, int64_t B,
+                  int64_t n, int D, void* stream) {
+    VDP_REQUIRE(Ld && rhs && x && B >= 0 && n >= 1, "Ld, rhs, x, B, n");
+    if (B == 0) return VDP_OK;
+    VDP_DISPATCH_D(D, (k_btd_solve<kD><<<grid_for(B, kSeqBlock), kSeqBlock, 0, as_stream(stream)>>>(
+                          Ld, Ls, rhs, x, transpose, B, n)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+int vdp_btd_matvec(const double* Md, const double* Ms, const double* x, double* y, int symmetric, int transpose,
+                   int64_t B, int64_t n, int D, void* stream) {
+    VDP_REQUIRE(Md && x && y && B >= 0 && n >= 1, "Md, x, y, B, n");
+    if (B == 0) return VDP_OK;
+    VDP_DISPATCH_D(D, (k_btd_matvec<kD><<<grid_for(B * n, kPtBlock), kPtBlock, 0, as_stream(stream)>>>(
+                          Md, Ms, x, y, symmetric, transpose, B, n)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+int vdp_btd_logdet(const double* Ld, double* out, int64_t B, int64_t n, int D, void* stream) {
+    VDP_REQUIRE(Ld && out && B >= 0 && n >= 1, "Ld, out, B, n");
+    if (B == 0) return VDP_OK;
+    VDP_DISPATCH_D(D, (k_btd_logdet<kD><<<grid_for(B, kSeqBlock), kSeqBlock, 0, as_stream(stream)>>>(Ld, out, B, n)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+}  // extern "C"
