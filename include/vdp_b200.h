@@ -134,12 +134,14 @@ int vdp_expectations_to_ssm(const double* e1, const double* ed, const double* es
 /* SDE_SSM_KL_with_grads_wrt_exp_params  (sde_utils.py:473-547), H = 20:
  * q given by its transitions A [B,N,D,D] and marginals m, Sd; prior x0 ~ N(x0_mu_host, x0_cov_host);
  * dt = float(grid[1]-grid[0]) (used in f_p), time_grid gives the per-step Q_p = delta_k q.
- * -> kl [B], g1 [B,N+1,D], gd [B,N+1,D,D], gs [B,N,D,D] */
+ * -> kl [B], g1 [B,N+1,D], gd [B,N+1,D,D], gs [B,N,D,D].  workspace: vdp_cvi_kl_workspace bytes */
 int vdp_cvi_kl_and_grad(int drift_id, const double* params_host, const double* q_host, double dt,
                         const double* time_grid, const double* x0_mu_host, const double* x0_cov_host,
                         const double* A, const double* m, const double* Sd,
                         double* kl, double* g1, double* gd, double* gs,
+                        void* workspace, size_t workspace_bytes,
                         int64_t B, int64_t N, int D, int64_t* status, void* stream);
+size_t vdp_cvi_kl_workspace(int64_t B, int64_t N, int D);
 
 /* One CVI-DP site update = cvi_dp_trainer.py:71-77 once:
  *   CVISitesSSM.update_data_sites      variational_cvi_sde.py:301-317

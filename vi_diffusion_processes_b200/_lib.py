@@ -1,0 +1,109 @@
+"""
+ctypes binding of libvdp_b200.so (C ABI declared in include/vdp_b200.h).
+
+There is NO fallback: if the shared library is missing or a call fails, an exception is raised.
+Build it with ``python -c "import __graft_entry__ as g; g.build()"`` or ``tools/build_lib.sh``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvdp_b200.so")
+
+c_dp = C.POINTER(C.c_double)
+c_i64p = C.POINTER(C.c_int64)
+i64 = C.c_int64
+vp = C.c_void_p
+
+
+class VdpError(RuntimeError):
+    pass
+
+
+class CviProblem(C.Structure):
+    """Mirror of ``struct vdp_cvi_problem`` (include/vdp_b200.h)."""
+    _fields_ = [
+        ("B", i64), ("N", i64), ("n_obs", i64),
+        ("D", C.c_int32), ("drift_id", C.c_int32),
+        ("drift_params", C.c_double * 16),
+        ("q", C.c_double * 9),
+        ("dt", C.c_double),
+        ("x0_mu", C.c_double * 3), ("x0_cov", C.c_double * 9),
+        ("lik_chol", C.c_double * 9),
+        ("lr_data", C.c_double), ("lr_girsanov", C.c_double),
+        ("time_grid", vp),
+        ("pA", vp), ("pb", vp), ("pcholQ", vp), ("pmu0", vp), ("pcholP0", vp),
+        ("g1", vp), ("gd", vp), ("gs", vp),
+        ("d1", vp), ("d2", vp),
+        ("obs_idx", vp), ("obs_y", vp),
+        ("fx_mus", vp), ("fx_covs", vp),
+        ("qA", vp), ("qb", vp), ("qcholQ", vp), ("qmu0", vp), ("qcholP0", vp),
+        ("elbo", vp), ("ve", vp), ("kl", vp),
+        ("workspace", vp), ("workspace_bytes", C.c_size_t),
+        ("status", vp),
+        ("flags", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+# name -> (restype, argtypes); every symbol include/vdp_b200.h declares
+SIGNATURES = {
+    "vdp_version": (C.c_int, []),
+    "vdp_last_error": (C.c_char_p, []),
+    "vdp_read_status": (i64, [vp, c_i64p, vp]),
+    "vdp_btd_cholesky": (C.c_int, [vp, vp, vp, vp, i64, i64, C.c_int, vp, vp]),
+    "vdp_btd_inverse_band": (C.c_int, [vp, vp, vp, vp, i64, i64, C.c_int, vp]),
+    "vdp_btd_solve": (C.c_int, [vp, vp, vp, vp, C.c_int, i64, i64, C.c_int, vp]),
+    "vdp_btd_matvec": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_int, i64, i64, C.c_int, vp]),
+    "vdp_btd_logdet": (C.c_int, [vp, vp, i64, i64, C.c_int, vp]),
+    "vdp_gh_expect": (C.c_int, [C.c_int, c_dp, vp, vp, C.c_int, vp, vp, i64, C.c_int, vp, vp]),
+    "vdp_linearize_to_ssm": (C.c_int, [C.c_int, c_dp, c_dp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_double,
+                                       C.c_double, i64, i64, C.c_int, vp, vp]),
+    "vdp_ssm_to_naturals": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, C.c_int, vp]),
+    "vdp_naturals_to_ssm_workspace": (C.c_size_t, [i64, i64, C.c_int]),
+    "vdp_naturals_to_ssm": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, i64, i64, C.c_int, vp, vp]),
+    "vdp_ssm_marginals_workspace": (C.c_size_t, [i64, i64, C.c_int]),
+    "vdp_ssm_marginals": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, i64, i64, C.c_int, vp, vp]),
+    "vdp_ssm_to_expectations": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i64, C.c_int, vp]),
+    "vdp_expectations_to_ssm": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, C.c_int, vp, vp]),
+    "vdp_cvi_kl_workspace": (C.c_size_t, [i64, i64, C.c_int]),
+    "vdp_cvi_kl_and_grad": (C.c_int, [C.c_int, c_dp, c_dp, C.c_double, vp, c_dp, c_dp, vp, vp, vp, vp, vp, vp, vp, vp,
+                                      C.c_size_t, i64, i64, C.c_int, vp, vp]),
+    "vdp_cvi_workspace": (C.c_size_t, [i64, i64, C.c_int, i64]),
+    "vdp_cvi_site_update": (C.c_int, [C.POINTER(CviProblem), vp]),
+    "vdp_cvi_elbo": (C.c_int, [C.POINTER(CviProblem), vp]),
+}
+
+_lib = None
+
+
+def load():
+    """Load the library once and attach signatures.  Raises VdpError if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise VdpError(f"{LIB_PATH} is missing: the CUDA library is not built and there is no CPU fallback. "
+                       f"Run tools/build_lib.sh (needs nvcc).")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = load().vdp_last_error().decode("utf-8", "replace")
+        raise VdpError(f"{what} failed with code {rc}: {msg}")
+
+
+def dvec(values, n):
+    """host double[n] from a sequence (zero padded)."""
+    arr = (C.c_double * n)()
+    for i, v in enumerate(values):
+        arr[i] = float(v)
+    return arr

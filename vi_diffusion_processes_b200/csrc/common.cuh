@@ -47,21 +47,46 @@ inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s
 
 inline unsigned grid_for(int64_t work, int block) { return (unsigned)((work + block - 1) / block); }
 
-// call f.template operator()<D>() for D in 1..3
+template <int V> struct IntTag { static constexpr int value = V; };
+
+// Run `body` with `constexpr int kD` = D for D in 1..3.  The body sits in a generic lambda so that
+// `if constexpr` on (drift, D) validity really discards the invalid instantiations; a `return x;`
+// inside the body leaves the lambda, and a non-zero value is propagated to the caller.
+#define VDP_D_CASE(V, ...)                                                                     \
+    case V: {                                                                                  \
+        auto _vdp_f = [&](auto _vdp_dt) -> int {                                               \
+            constexpr int kD = decltype(_vdp_dt)::value;                                       \
+            (void)kD;                                                                          \
+            __VA_ARGS__;                                                                       \
+            return VDP_OK;                                                                     \
+        };                                                                                     \
+        const int _vdp_rc = _vdp_f(::vdp::IntTag<V>{});                                        \
+        if (_vdp_rc) return _vdp_rc;                                                           \
+    } break;
+
 #define VDP_DISPATCH_D(D, ...)                                                                 \
     switch (D) {                                                                               \
-        case 1: { constexpr int kD = 1; __VA_ARGS__; } break;                                  \
-        case 2: { constexpr int kD = 2; __VA_ARGS__; } break;                                  \
-        case 3: { constexpr int kD = 3; __VA_ARGS__; } break;                                  \
+        VDP_D_CASE(1, __VA_ARGS__)                                                             \
+        VDP_D_CASE(2, __VA_ARGS__)                                                             \
+        VDP_D_CASE(3, __VA_ARGS__)                                                             \
         default: ::vdp::set_error("state dimension %d not supported (1..3)", D); return VDP_E_BADARG; \
     }
 
-// instantiate `CALL` with kDrift for every (drift, D) pair that exists
+// inside VDP_DISPATCH_D: run `body` with `constexpr int kDrift` for every (drift, D) pair that exists
 #define VDP_DRIFT_CASE(ID, ...)                                                                \
     case ID: {                                                                                 \
-        constexpr int kDrift = ID;                                                             \
-        if constexpr (::vdp::DriftValid<ID, kD>::value) { __VA_ARGS__; }                       \
-        else { ::vdp::set_error("drift %d is not defined for D=%d", ID, kD); return VDP_E_BADARG; } \
+        auto _vdp_g = [&](auto _vdp_it) -> int {                                               \
+            constexpr int kDrift = decltype(_vdp_it)::value;                                   \
+            if constexpr (::vdp::DriftValid<kDrift, kD>::value) {                              \
+                __VA_ARGS__;                                                                   \
+                return VDP_OK;                                                                 \
+            } else {                                                                           \
+                ::vdp::set_error("drift %d is not defined for D=%d", kDrift, kD);              \
+                return VDP_E_BADARG;                                                           \
+            }                                                                                  \
+        };                                                                                     \
+        const int _vdp_rc2 = _vdp_g(::vdp::IntTag<ID>{});                                      \
+        if (_vdp_rc2) return _vdp_rc2;                                                         \
     } break;
 
 #define VDP_DISPATCH_DRIFT(id, ...)                                                            \

@@ -115,3 +115,6 @@ int vdp_btd_logdet(const double* Ld, double* out, int64_t B, int64_t n, int D, v
 }
 
 }  // extern "C"
+
+#include "vdp_fused.inl"
+#include "vdp_cvi.inl"

@@ -1,0 +1,203 @@
+// CVI-DP entry points: KL + gradient, the fused site update and classic_elbo
+// (included at the end of vdp_abi.cu after vdp_fused.inl).
+
+namespace vdp {
+
+template <int D> struct KlLaunch {
+    static constexpr int G = QuadGroup<D>::value;
+    static constexpr int groups = (G == 1) ? 128 : 16;   // first group of a block is the halo
+    static constexpr int threads = groups * G;
+};
+
+template <int DRIFT, int D>
+static int launch_kl_grad(const DriftParams& P, const double* q_host, double dt, const double* time_grid,
+                          const double* x0_mu, const double* x0_cov, const double* Aq, const double* m,
+                          const double* Sd, double* terms, double* g1, double* gd, double* gs, int upd, double lr,
+                          const double* sc1, const double* scd, int64_t B, int64_t N, int64_t* status,
+                          cudaStream_t st) {
+    using KL = KlLaunch<D>;
+    const int64_t total = B * (N + 1);
+    const unsigned grid = (unsigned)((total + KL::groups - 2) / (KL::groups - 1));
+    const size_t smem = KL::groups * sizeof(KlHandoff<D>);
+    k_kl_grad<DRIFT, D, 20, KL::G><<<grid, KL::threads, smem, st>>>(
+        P, host_mat<D>(q_host), dt, pi_factor(D), time_grid, host_vec<D>(x0_mu), host_mat<D>(x0_cov), Aq, m, Sd,
+        terms, g1, gd, gs, upd, lr, sc1, scd, B, N, status);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+__global__ void k_elbo_combine(const double* __restrict__ ve, const double* __restrict__ kl,
+                               double* __restrict__ elbo, int64_t B) {
+    const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (b < B) elbo[b] = ve[b] - kl[b];
+}
+
+// workspace carve-up shared by site_update and elbo
+struct CviWs {
+    double *th1, *thd, *ths, *Ld, *Ls, *terms, *sc1, *scd;
+};
+static inline size_t cvi_ws_bytes(int64_t B, int64_t N, int D) {
+    const size_t n = (size_t)B * (N + 1), t = (size_t)B * N, DD = (size_t)D * D;
+    return padded(n * D) + padded(n * DD) + padded(t * DD) + padded(n * DD) + padded(t * DD) + padded(n) +
+           padded(n * D) + padded(n * DD);
+}
+static inline bool cvi_ws_take(void* ws, size_t bytes, int64_t B, int64_t N, int D, CviWs& w) {
+    if (!ws) return false;
+    Arena ar(ws, bytes);
+    const size_t n = (size_t)B * (N + 1), t = (size_t)B * N, DD = (size_t)D * D;
+    w.th1 = ar.take(n * D);
+    w.thd = ar.take(n * DD);
+    w.ths = ar.take(t * DD);
+    w.Ld = ar.take(n * DD);
+    w.Ls = ar.take(t * DD);
+    w.terms = ar.take(n);
+    w.sc1 = ar.take(n * D);
+    w.scd = ar.take(n * DD);
+    return w.scd != nullptr;
+}
+
+// (F): sites -> q as an SSM -> marginals.   variational_cvi_sde.py:161-192 + gauss_markov.py:107-117
+template <int D>
+static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t st) {
+    const int64_t B = p.B, N = p.N;
+    k_ssm_to_naturals<D><<<grid_for(B * (N + 1), kPtBlock), kPtBlock, 0, st>>>(
+        p.pA, p.pb, p.pcholQ, p.pmu0, p.pcholP0, p.g1, p.gd, p.gs, w.th1, w.thd, w.ths, B, N);
+    VDP_CHECK_LAUNCH();
+    if (p.n_obs > 0) {
+        k_scatter_data<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(p.d1, p.d2, p.obs_idx, w.th1, w.thd, B,
+                                                                            N, p.n_obs);
+        VDP_CHECK_LAUNCH();
+    }
+    int rc = run_nat2ssm<D>(w.th1, w.thd, w.ths, p.qA, p.qb, p.qcholQ, p.qmu0, p.qcholP0, w.Ld, w.Ls, B, N, p.status,
+                            st);
+    if (rc) return rc;
+    return run_marginals<D>(p.qA, p.qb, p.qcholQ, p.qmu0, p.qcholP0, p.fx_mus, p.fx_covs, w.Ld, w.Ls, B, N, p.status,
+                            st);
+}
+
+template <int DRIFT, int D>
+static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams& P, cudaStream_t st) {
+    const int64_t B = p.B, N = p.N;
+    constexpr int G = QuadGroup<D>::value;
+    k_variational_expectation<D><<<grid_for(B, kSeqBlock), kSeqBlock, 0, st>>>(
+        p.fx_mus, p.fx_covs, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.ve, B, N, p.n_obs);
+    VDP_CHECK_LAUNCH();
+    k_kl_value<DRIFT, D, 20, G><<<grid_for(B * (N + 1) * G, kPtBlock), kPtBlock, 0, st>>>(
+        P, host_mat<D>(p.q), p.dt, pi_factor(D), p.qA, p.qb, p.qcholQ, p.fx_mus, p.fx_covs, p.qmu0, p.qcholP0,
+        p.pmu0, p.pcholP0, w.terms, B, N, p.status);
+    VDP_CHECK_LAUNCH();
+    k_reduce_terms<<<(unsigned)B, 256, 0, st>>>(w.terms, N + 1, p.kl);
+    VDP_CHECK_LAUNCH();
+    k_elbo_combine<<<grid_for(B, kPtBlock), kPtBlock, 0, st>>>(p.ve, p.kl, p.elbo, B);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+template <int DRIFT, int D>
+static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t st) {
+    const int64_t B = p.B, N = p.N;
+    const DriftParams P = make_params(p.drift_params);
+    int rc;
+    // (A) update_data_sites  variational_cvi_sde.py:301-317
+    if (!(p.flags & VDP_FLAG_SKIP_DATA_UPDATE) && p.n_obs > 0) {
+        k_data_site_update<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
+            p.fx_mus, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.lr_data, p.d1, p.d2, B, N, p.n_obs);
+        VDP_CHECK_LAUNCH();
+    }
+    if ((rc = run_posterior<D>(p, w, st))) return rc;
+    // (B) update_girsanov_sites  variational_cvi_sde.py:279-299
+    const size_t n = (size_t)B * (N + 1);
+    VDP_CHECK_CUDA(cudaMemsetAsync(w.sc1, 0, n * D * sizeof(double), st));
+    VDP_CHECK_CUDA(cudaMemsetAsync(w.scd, 0, n * D * D * sizeof(double), st));
+    if (p.n_obs > 0) {
+        k_scatter_data<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(p.d1, p.d2, p.obs_idx, w.sc1, w.scd, B,
+                                                                            N, p.n_obs);
+        VDP_CHECK_LAUNCH();
+    }
+    if ((rc = launch_kl_grad<DRIFT, D>(P, p.q, p.dt, p.time_grid, p.x0_mu, p.x0_cov, p.qA, p.fx_mus, p.fx_covs,
+                                       w.terms, p.g1, p.gd, p.gs, 1, p.lr_girsanov, w.sc1, w.scd, B, N, p.status,
+                                       st)))
+        return rc;
+    if ((rc = run_posterior<D>(p, w, st))) return rc;
+    // (C) classic_elbo  variational_cvi_sde.py:339-352
+    if (!(p.flags & VDP_FLAG_SKIP_ELBO)) return run_elbo<DRIFT, D>(p, w, P, st);
+    return VDP_OK;
+}
+
+static int check_problem(const vdp_cvi_problem* p) {
+    VDP_REQUIRE(p != nullptr, "problem");
+    VDP_REQUIRE(p->B >= 0 && p->N >= 1 && p->n_obs >= 0, "B, N, n_obs");
+    VDP_REQUIRE(p->time_grid && p->pA && p->pb && p->pcholQ && p->pmu0 && p->pcholP0, "prior SSM pointers");
+    VDP_REQUIRE(p->g1 && p->gd && p->gs, "girsanov site pointers");
+    VDP_REQUIRE(p->n_obs == 0 || (p->d1 && p->d2 && p->obs_idx && p->obs_y), "data site pointers");
+    VDP_REQUIRE(p->fx_mus && p->fx_covs && p->qA && p->qb && p->qcholQ && p->qmu0 && p->qcholP0, "output pointers");
+    VDP_REQUIRE(p->elbo && p->ve && p->kl, "elbo pointers");
+    return VDP_OK;
+}
+
+}  // namespace vdp
+
+extern "C" {
+
+size_t vdp_cvi_kl_workspace(int64_t B, int64_t N, int D) { (void)D; return padded((size_t)B * (N + 1)); }
+
+int vdp_cvi_kl_and_grad(int drift_id, const double* params_host, const double* q_host, double dt,
+                        const double* time_grid, const double* x0_mu_host, const double* x0_cov_host,
+                        const double* A, const double* m, const double* Sd, double* kl, double* g1, double* gd,
+                        double* gs, void* workspace, size_t workspace_bytes, int64_t B, int64_t N, int D,
+                        int64_t* status, void* stream) {
+    VDP_REQUIRE(q_host && time_grid && x0_mu_host && x0_cov_host && A && m && Sd && kl && g1 && gd && gs,
+                "pointers");
+    VDP_REQUIRE(B >= 0 && N >= 1, "B, N");
+    if (B == 0) return VDP_OK;
+    Arena ar(workspace, workspace_bytes);
+    double* terms = workspace ? ar.take((size_t)B * (N + 1)) : nullptr;
+    if (!terms) { set_error("workspace too small"); return VDP_E_WORKSPACE; }
+    const DriftParams P = make_params(params_host);
+    cudaStream_t st = as_stream(stream);
+    VDP_DISPATCH_D(D, VDP_DISPATCH_DRIFT(drift_id, {
+        int rc = launch_kl_grad<kDrift, kD>(P, q_host, dt, time_grid, x0_mu_host, x0_cov_host, A, m, Sd, terms, g1,
+                                            gd, gs, 0, 0.0, nullptr, nullptr, B, N, status, st);
+        if (rc) return rc;
+    }));
+    k_reduce_terms<<<(unsigned)B, 256, 0, st>>>(terms, N + 1, kl);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+size_t vdp_cvi_workspace(int64_t B, int64_t N, int D, int64_t n_obs) { (void)n_obs; return cvi_ws_bytes(B, N, D); }
+
+int vdp_cvi_site_update(const vdp_cvi_problem* p, void* stream) {
+    int rc = check_problem(p);
+    if (rc) return rc;
+    if (p->B == 0) return VDP_OK;
+    CviWs w;
+    if (!cvi_ws_take(p->workspace, p->workspace_bytes, p->B, p->N, p->D, w)) {
+        set_error("workspace too small: need %zu bytes", cvi_ws_bytes(p->B, p->N, p->D));
+        return VDP_E_WORKSPACE;
+    }
+    VDP_DISPATCH_D(p->D, VDP_DISPATCH_DRIFT(p->drift_id, {
+        rc = run_site_update<kDrift, kD>(*p, w, as_stream(stream));
+        if (rc) return rc;
+    }));
+    return VDP_OK;
+}
+
+int vdp_cvi_elbo(const vdp_cvi_problem* p, void* stream) {
+    int rc = check_problem(p);
+    if (rc) return rc;
+    if (p->B == 0) return VDP_OK;
+    CviWs w;
+    if (!cvi_ws_take(p->workspace, p->workspace_bytes, p->B, p->N, p->D, w)) {
+        set_error("workspace too small: need %zu bytes", cvi_ws_bytes(p->B, p->N, p->D));
+        return VDP_E_WORKSPACE;
+    }
+    const DriftParams P = make_params(p->drift_params);
+    VDP_DISPATCH_D(p->D, VDP_DISPATCH_DRIFT(p->drift_id, {
+        if ((rc = run_posterior<kD>(*p, w, as_stream(stream)))) return rc;
+        if ((rc = run_elbo<kDrift, kD>(*p, w, P, as_stream(stream)))) return rc;
+    }));
+    return VDP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,152 @@
+"""
+Batched CVI-DP engine: device-resident state of B independent sequences and the fused site update.
+
+This is the object the reference-shaped model classes (``markovflow/models/variational_cvi_sde.py``
+mirror in :mod:`vi_diffusion_processes_b200.markovflow.models`) and ``bench.py`` drive.  One call of
+:meth:`CviEngine.site_update` = one iteration of the reference's hot loop
+(``docs/diffusion_processes/cvi_dp_trainer.py:71-77``): update_data_sites, update_girsanov_sites,
+classic_elbo -- executed by ``vdp_cvi_site_update`` on the GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib, ops
+from ._lib import CviProblem, check
+
+F64 = torch.float64
+
+
+class CviEngine:
+    """
+    State (all float64 CUDA tensors, reference layouts with a leading batch axis):
+      girsanov sites  g1 [B,N+1,D], gd [B,N+1,D,D], gs [B,N,D,D]     (variational_cvi_sde.py:135-151)
+      data sites      d1 [B,n_obs,D], d2 [B,n_obs,D,D]               (:97-104)
+      posterior       fx_mus [B,N+1,D], fx_covs [B,N+1,D,D]          (:110-115)
+      linearised prior p (A, b, cholQ, mu0, cholP0), and its un-clipped version p_lin (:408-432)
+    """
+
+    def __init__(self, drift_id, drift_params, q, time_grid, obs_idx, obs_y, lik_chol, x0_mu, x0_cov,
+                 device="cuda", stabilize_ssm=True, clip_state_transitions=(-1.0, 1.0),
+                 initial_mean=None, initial_cov=None):
+        self.device = torch.device(device)
+        self.drift_id = int(drift_id)
+        self.drift_params = [float(v) for v in np.asarray(drift_params).reshape(-1)]
+        self.q = np.atleast_2d(np.asarray(q, dtype=np.float64))
+        self.D = D = self.q.shape[0]
+        tg = np.asarray(time_grid, dtype=np.float64)
+        self.dt = float(tg[1] - tg[0])
+        self.time_grid = torch.as_tensor(tg, dtype=F64).to(self.device)
+        self.N = N = tg.shape[0] - 1
+        obs_idx = np.asarray(obs_idx, dtype=np.int64)
+        obs_y = np.asarray(obs_y, dtype=np.float64)
+        if obs_idx.ndim == 1:
+            obs_idx, obs_y = obs_idx[None], obs_y[None]
+        self.B = B = obs_idx.shape[0]
+        self.n_obs = n_obs = obs_idx.shape[1]
+        self.obs_idx = torch.as_tensor(obs_idx).to(self.device).contiguous()
+        self.obs_y = torch.as_tensor(obs_y.reshape(B, n_obs, D), dtype=F64).to(self.device).contiguous()
+        self.lik_chol = np.atleast_2d(np.asarray(lik_chol, dtype=np.float64))
+        self.x0_mu = np.asarray(x0_mu, dtype=np.float64).reshape(D)
+        self.x0_cov = np.atleast_2d(np.asarray(x0_cov, dtype=np.float64))
+        self.stabilize_ssm = stabilize_ssm
+        self.clip = tuple(float(c) for c in clip_state_transitions)
+        dev = self.device
+        z = lambda *s: torch.zeros(s, dtype=F64, device=dev)
+        self.g1 = z(B, N + 1, D)
+        self.gd = torch.full((B, N + 1, D, D), -1e-10, dtype=F64, device=dev)
+        self.gs = torch.full((B, N, D, D), -1e-10, dtype=F64, device=dev)
+        self.d1 = z(B, n_obs, D)
+        self.d2 = (torch.eye(D, dtype=F64, device=dev) * 1e-10).expand(B, n_obs, D, D).contiguous()
+        self.fx_mus = z(B, N + 1, D) if initial_mean is None else torch.as_tensor(
+            initial_mean, dtype=F64).to(dev).reshape(B, N + 1, D).contiguous()
+        self.fx_covs = (torch.eye(D, dtype=F64, device=dev).expand(B, N + 1, D, D).contiguous()
+                        if initial_cov is None else
+                        torch.as_tensor(initial_cov, dtype=F64).to(dev).reshape(B, N + 1, D, D).contiguous())
+        self.qA, self.qb, self.qcholQ = z(B, N, D, D), z(B, N, D), z(B, N, D, D)
+        self.qmu0, self.qcholP0 = z(B, D), z(B, D, D)
+        self.elbo, self.ve, self.kl = z(B), z(B), z(B)
+        self.status = ops.new_status(dev)
+        lib = _lib.load()
+        self._ws_bytes = lib.vdp_cvi_workspace(B, N, D, n_obs)
+        self._ws = torch.empty(self._ws_bytes, dtype=torch.uint8, device=dev)
+        # prior p: initial state from the prior on x0 (variational_cvi_sde.py:408-412, sde_utils.py:145-147)
+        self.pmu0 = torch.as_tensor(self.x0_mu, dtype=F64).to(dev).expand(B, D).contiguous()
+        self.pcholP0 = torch.as_tensor(np.linalg.cholesky(self.x0_cov), dtype=F64).to(dev).expand(B, D, D).contiguous()
+        self.set_linearized_prior()
+
+    # variational_cvi_sde.py:408-432
+    def set_linearized_prior(self):
+        m = self.fx_mus[:, 1:].contiguous()
+        S = self.fx_covs[:, 1:].contiguous()
+        clip = self.clip if self.stabilize_ssm else None
+        A, b, cholQ, A_lin, b_lin = ops.linearize_to_ssm(self.drift_id, self.drift_params, self.q, self.time_grid, m,
+                                                         S, clip=clip, status=self.status, want_unclipped=True)
+        self.pA, self.pb, self.pcholQ = A, b, cholQ
+        self.pA_lin, self.pb_lin = A_lin, b_lin
+
+    def _problem(self, lr_data, lr_girsanov, flags=0):
+        p = CviProblem()
+        p.B, p.N, p.n_obs, p.D, p.drift_id = self.B, self.N, self.n_obs, self.D, self.drift_id
+        for i, v in enumerate(self.drift_params[:16]):
+            p.drift_params[i] = v
+        for i, v in enumerate(self.q.reshape(-1)):
+            p.q[i] = v
+        p.dt = self.dt
+        for i, v in enumerate(self.x0_mu):
+            p.x0_mu[i] = v
+        for i, v in enumerate(self.x0_cov.reshape(-1)):
+            p.x0_cov[i] = v
+        for i, v in enumerate(self.lik_chol.reshape(-1)):
+            p.lik_chol[i] = v
+        p.lr_data, p.lr_girsanov = float(lr_data), float(lr_girsanov)
+        for name in ("time_grid", "pA", "pb", "pcholQ", "pmu0", "pcholP0", "g1", "gd", "gs", "d1", "d2", "obs_idx",
+                     "obs_y", "fx_mus", "fx_covs", "qA", "qb", "qcholQ", "qmu0", "qcholP0", "elbo", "ve", "kl",
+                     "status"):
+            t = getattr(self, name)
+            assert t.is_contiguous(), name
+            setattr(p, name, t.data_ptr())
+        p.workspace = self._ws.data_ptr()
+        p.workspace_bytes = self._ws_bytes
+        p.flags = flags
+        return p
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def site_update(self, lr_data, lr_girsanov, flags=0):
+        """cvi_dp_trainer.py:71-77 once.  Returns the ELBO tensor [B] (device)."""
+        p = self._problem(lr_data, lr_girsanov, flags)
+        check(_lib.load().vdp_cvi_site_update(C.byref(p), self._stream()), "vdp_cvi_site_update")
+        return self.elbo
+
+    def classic_elbo(self):
+        p = self._problem(0.0, 0.0)
+        check(_lib.load().vdp_cvi_elbo(C.byref(p), self._stream()), "vdp_cvi_elbo")
+        return self.elbo
+
+    def check_status(self):
+        code, idx = ops.read_status(self.status)
+        if code != 0:
+            raise _lib.VdpError(f"non positive-definite block at flat grid index {idx} (code {code})")
+
+    # sde_utils.py:550-568 applied as in cvi_dp_trainer.py:110-134
+    def _prior_naturals(self, A, b):
+        return ops.ssm_to_naturals(A, b, self.pcholQ, self.pmu0, self.pcholP0)
+
+    def relinearize(self):
+        cur = self._prior_naturals(self.pA, self.pb)
+        new = self._prior_naturals(self.pA_lin, self.pb_lin)
+        self.g1 = (self.g1 + cur[0] - new[0]).contiguous()
+        self.gd = (self.gd + cur[1] - new[1]).contiguous()
+        self.gs = (self.gs + cur[2] - new[2]).contiguous()
+        self.pA, self.pb = self.pA_lin, self.pb_lin
+        last = self._prior_naturals(self.pA, self.pb)
+        self.set_linearized_prior()
+        new = self._prior_naturals(self.pA, self.pb)
+        self.g1 = (self.g1 + last[0] - new[0]).contiguous()
+        self.gd = (self.gd + last[1] - new[1]).contiguous()
+        self.gs = (self.gs + last[2] - new[2]).contiguous()

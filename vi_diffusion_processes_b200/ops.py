@@ -1,0 +1,224 @@
+"""
+Thin torch-tensor front end of the C ABI: every function takes float64 CUDA tensors in the
+reference's layouts (leading batch axis), allocates the outputs with torch, and launches the CUDA
+kernels on torch's current stream.  No arithmetic happens in Python and nothing falls back to the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import CviProblem, check, dvec
+
+F64 = torch.float64
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _req(*tensors):
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise _lib.VdpError("vdp_b200 ops need CUDA tensors (there is no CPU path)")
+        if t.dtype not in (F64, torch.int64):
+            raise _lib.VdpError(f"expected float64/int64, got {t.dtype}")
+        if not t.is_contiguous():
+            raise _lib.VdpError("tensors must be contiguous")
+
+
+def new_status(device):
+    return torch.zeros(2, dtype=torch.int64, device=device)
+
+
+def read_status(status):
+    """(code, flat index) of the first non-positive-definite block seen since the word was zeroed."""
+    out = (C.c_int64 * 2)()
+    _lib.load().vdp_read_status(_p(status), out, _stream())
+    return int(out[0]), int(out[1])
+
+
+def _bnd(diag):
+    """[B, n, D, D] -> B, n, D (a missing batch axis is an error: callers add it)."""
+    assert diag.dim() == 4 and diag.shape[-1] == diag.shape[-2], diag.shape
+    return diag.shape[0], diag.shape[1], diag.shape[2]
+
+
+# ------------------------------------------------------------------ op level
+
+
+def btd_cholesky(Kd, Ks=None, status=None):
+    _req(Kd, Ks, status)
+    B, n, D = _bnd(Kd)
+    Ld = torch.empty_like(Kd)
+    Ls = None if Ks is None else torch.empty_like(Ks)
+    check(_lib.load().vdp_btd_cholesky(_p(Kd), _p(Ks), _p(Ld), _p(Ls), B, n, D, _p(status), _stream()),
+          "vdp_btd_cholesky")
+    return Ld, Ls
+
+
+def btd_inverse_band(Ld, Ls=None, want_sub=True):
+    _req(Ld, Ls)
+    B, n, D = _bnd(Ld)
+    Sd = torch.empty_like(Ld)
+    Ss = torch.empty_like(Ls) if (Ls is not None and want_sub) else None
+    check(_lib.load().vdp_btd_inverse_band(_p(Ld), _p(Ls), _p(Sd), _p(Ss), B, n, D, _stream()),
+          "vdp_btd_inverse_band")
+    return Sd, Ss
+
+
+def btd_solve(Ld, Ls, rhs, transpose=False):
+    _req(Ld, Ls, rhs)
+    B, n, D = _bnd(Ld)
+    x = torch.empty_like(rhs)
+    check(_lib.load().vdp_btd_solve(_p(Ld), _p(Ls), _p(rhs), _p(x), int(transpose), B, n, D, _stream()),
+          "vdp_btd_solve")
+    return x
+
+
+def btd_matvec(Md, Ms, x, symmetric, transpose=False):
+    _req(Md, Ms, x)
+    B, n, D = _bnd(Md)
+    y = torch.empty_like(x)
+    check(_lib.load().vdp_btd_matvec(_p(Md), _p(Ms), _p(x), _p(y), int(symmetric), int(transpose), B, n, D,
+                                     _stream()), "vdp_btd_matvec")
+    return y
+
+
+def btd_logdet(Ld):
+    _req(Ld)
+    B, n, D = _bnd(Ld)
+    out = torch.empty(B, dtype=F64, device=Ld.device)
+    check(_lib.load().vdp_btd_logdet(_p(Ld), _p(out), B, n, D, _stream()), "vdp_btd_logdet")
+    return out
+
+
+# ------------------------------------------------------------------ fused level
+
+
+def gh_expect(drift_id, params, m, S, H=10, full_jacobian=False, status=None):
+    """m [count, D], S [count, D, D] -> E[f] [count, D], E[grad f] ([count, D, D] or [count, D])."""
+    _req(m, S, status)
+    count, D = m.shape
+    Ef = torch.empty_like(m)
+    EJ = torch.empty((count, D, D) if full_jacobian else (count, D), dtype=F64, device=m.device)
+    check(_lib.load().vdp_gh_expect(int(drift_id), dvec(params, 16), _p(m), _p(S), int(H), _p(Ef), _p(EJ), count, D,
+                                    _p(status), _stream()), "vdp_gh_expect")
+    return Ef, EJ
+
+
+def linearize_to_ssm(drift_id, params, q, time_grid, m, S, clip=None, status=None, want_unclipped=False):
+    """m [B,N,D], S [B,N,D,D] on grid points 1..N -> A [B,N,D,D], b [B,N,D], cholQ [B,N,D,D]."""
+    _req(time_grid, m, S, status)
+    B, N, D = m.shape
+    A = torch.empty((B, N, D, D), dtype=F64, device=m.device)
+    b = torch.empty((B, N, D), dtype=F64, device=m.device)
+    cholQ = torch.empty_like(A)
+    A_lin = torch.empty_like(A) if want_unclipped else None
+    b_lin = torch.empty_like(b) if want_unclipped else None
+    lo, hi = (clip if clip is not None else (0.0, 0.0))
+    check(_lib.load().vdp_linearize_to_ssm(int(drift_id), dvec(params, 16), dvec(q.reshape(-1), D * D),
+                                           _p(time_grid), _p(m), _p(S), _p(A), _p(b), _p(cholQ), _p(A_lin), _p(b_lin),
+                                           int(clip is not None), float(lo), float(hi), B, N, D, _p(status),
+                                           _stream()), "vdp_linearize_to_ssm")
+    return (A, b, cholQ, A_lin, b_lin) if want_unclipped else (A, b, cholQ)
+
+
+def ssm_to_naturals(A, b, cholQ, mu0, cholP0):
+    _req(A, b, cholQ, mu0, cholP0)
+    B, N, D = b.shape
+    th1 = torch.empty((B, N + 1, D), dtype=F64, device=A.device)
+    thd = torch.empty((B, N + 1, D, D), dtype=F64, device=A.device)
+    ths = torch.empty((B, N, D, D), dtype=F64, device=A.device)
+    check(_lib.load().vdp_ssm_to_naturals(_p(A), _p(b), _p(cholQ), _p(mu0), _p(cholP0), _p(th1), _p(thd), _p(ths), B,
+                                          N, D, _stream()), "vdp_ssm_to_naturals")
+    return th1, thd, ths
+
+
+def _workspace(nbytes, device):
+    return torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+
+
+def naturals_to_ssm(th1, thd, ths, status=None):
+    _req(th1, thd, ths, status)
+    B, n, D = th1.shape
+    N = n - 1
+    dev = th1.device
+    A = torch.empty((B, N, D, D), dtype=F64, device=dev)
+    b = torch.empty((B, N, D), dtype=F64, device=dev)
+    cholQ = torch.empty_like(A)
+    mu0 = torch.empty((B, D), dtype=F64, device=dev)
+    cholP0 = torch.empty((B, D, D), dtype=F64, device=dev)
+    lib = _lib.load()
+    nbytes = lib.vdp_naturals_to_ssm_workspace(B, N, D)
+    ws = _workspace(nbytes, dev)
+    check(lib.vdp_naturals_to_ssm(_p(th1), _p(thd), _p(ths), _p(A), _p(b), _p(cholQ), _p(mu0), _p(cholP0), _p(ws),
+                                  nbytes, B, N, D, _p(status), _stream()), "vdp_naturals_to_ssm")
+    return A, b, cholP0, cholQ, mu0   # reference return order (ssm_gaussian_transformations.py:511)
+
+
+def ssm_marginals(A, b, cholQ, mu0, cholP0, status=None):
+    _req(A, b, cholQ, mu0, cholP0, status)
+    B, N, D = b.shape
+    dev = A.device
+    m = torch.empty((B, N + 1, D), dtype=F64, device=dev)
+    Sd = torch.empty((B, N + 1, D, D), dtype=F64, device=dev)
+    lib = _lib.load()
+    nbytes = lib.vdp_ssm_marginals_workspace(B, N, D)
+    ws = _workspace(nbytes, dev)
+    check(lib.vdp_ssm_marginals(_p(A), _p(b), _p(cholQ), _p(mu0), _p(cholP0), _p(m), _p(Sd), _p(ws), nbytes, B, N, D,
+                                _p(status), _stream()), "vdp_ssm_marginals")
+    return m, Sd
+
+
+def ssm_to_expectations(A, m, Sd):
+    _req(A, m, Sd)
+    B, n, D = m.shape
+    e1 = torch.empty_like(m)
+    ed = torch.empty_like(Sd)
+    es = torch.empty_like(A)
+    check(_lib.load().vdp_ssm_to_expectations(_p(A), _p(m), _p(Sd), _p(e1), _p(ed), _p(es), B, n - 1, D, _stream()),
+          "vdp_ssm_to_expectations")
+    return e1, ed, es
+
+
+def expectations_to_ssm(e1, ed, es, status=None):
+    _req(e1, ed, es, status)
+    B, n, D = e1.shape
+    N = n - 1
+    dev = e1.device
+    A = torch.empty((B, N, D, D), dtype=F64, device=dev)
+    b = torch.empty((B, N, D), dtype=F64, device=dev)
+    cholQ = torch.empty_like(A)
+    mu0 = torch.empty((B, D), dtype=F64, device=dev)
+    cholP0 = torch.empty((B, D, D), dtype=F64, device=dev)
+    check(_lib.load().vdp_expectations_to_ssm(_p(e1), _p(ed), _p(es), _p(A), _p(b), _p(cholQ), _p(mu0), _p(cholP0), B,
+                                              N, D, _p(status), _stream()), "vdp_expectations_to_ssm")
+    return A, b, cholP0, cholQ, mu0
+
+
+def cvi_kl_and_grad(drift_id, params, q, dt, time_grid, x0_mu, x0_cov, A, m, Sd, status=None):
+    _req(time_grid, A, m, Sd, status)
+    B, n, D = m.shape
+    N = n - 1
+    dev = m.device
+    kl = torch.empty(B, dtype=F64, device=dev)
+    g1 = torch.empty_like(m)
+    gd = torch.empty_like(Sd)
+    gs = torch.empty_like(A)
+    lib = _lib.load()
+    nbytes = lib.vdp_cvi_kl_workspace(B, N, D)
+    ws = _workspace(nbytes, dev)
+    check(lib.vdp_cvi_kl_and_grad(int(drift_id), dvec(params, 16), dvec(q.reshape(-1), D * D), float(dt),
+                                  _p(time_grid), dvec(x0_mu.reshape(-1), D), dvec(x0_cov.reshape(-1), D * D), _p(A),
+                                  _p(m), _p(Sd), _p(kl), _p(g1), _p(gd), _p(gs), _p(ws), nbytes, B, N, D, _p(status),
+                                  _stream()), "vdp_cvi_kl_and_grad")
+    return kl, (g1, gd, gs)
