@@ -1,0 +1,225 @@
+"""
+GPU parity tests: the CUDA path, called through the C ABI, against the NumPy oracle on the same inputs.
+Tolerance (north_star): 1e-9 relative on ELBO, site natural parameters and marginals; relative error
+here = max |cuda - oracle| / max |oracle| per tensor.
+"""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+from oracle import gauss_markov_np as G
+from oracle import models_np as M
+from oracle import scalar_d1
+from oracle import sde_np as S
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-9
+
+
+def rel(a, b, scale=None):
+    """max |a - b| / max |b|  (or / scale when the tensor is a cancellation result near zero)."""
+    a = a.detach().cpu().numpy() if hasattr(a, "detach") else np.asarray(a)
+    b = np.asarray(b)
+    assert a.shape == b.shape, (a.shape, b.shape)
+    den = np.abs(b).max() if scale is None else scale
+    return float(np.abs(a - b).max() / (den if den > 0 else 1.0))
+
+
+def dev(x):
+    return torch.as_tensor(np.ascontiguousarray(x), dtype=torch.float64).cuda()
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from vi_diffusion_processes_b200 import ops as o
+    return o
+
+
+def _spd(rng, B, n, D):
+    Ld = np.tril(rng.normal(size=(B, n, D, D))) * 0.3 + 2.0 * np.eye(D)
+    Ls = rng.normal(size=(B, n - 1, D, D)) * 0.5
+    Kd = Ld @ G.mT(Ld)
+    Kd[:, 1:] += Ls @ G.mT(Ls)
+    Ks = Ls @ G.mT(Ld[:, :-1])
+    return Kd, Ks
+
+
+@pytest.mark.parametrize("D", [1, 2, 3])
+@pytest.mark.parametrize("B,n", [(1, 1), (3, 2), (5, 64), (2, 1001)])
+def test_btd_ops(ops, D, B, n):
+    rng = np.random.default_rng(D * 100 + n)
+    Kd, Ks = _spd(rng, B, max(n, 2), D)
+    Kd, Ks = Kd[:, :n], Ks[:, :n - 1]
+    st = ops.new_status("cuda")
+    if n == 1:
+        Ld, _ = ops.btd_cholesky(dev(Kd), None, st)
+        assert rel(Ld, G.btd_cholesky(Kd, None)[0]) < TOL
+        return
+    Ld, Ls = ops.btd_cholesky(dev(Kd), dev(Ks), st)
+    oLd, oLs = G.btd_cholesky(Kd, Ks)
+    assert ops.read_status(st)[0] == 0
+    assert rel(Ld, oLd) < TOL and rel(Ls, oLs) < TOL
+    Sd, Ss = ops.btd_inverse_band(Ld, Ls)
+    oSd, oSs = G.btd_inverse_band(oLd, oLs)
+    assert rel(Sd, oSd) < TOL and rel(Ss, oSs) < TOL
+    rhs = rng.normal(size=(B, n, D))
+    for tr in (False, True):
+        assert rel(ops.btd_solve(Ld, Ls, dev(rhs), tr), G.btd_solve(oLd, oLs, rhs, tr)) < TOL
+        assert rel(ops.btd_matvec(Ld, Ls, dev(rhs), False, tr), G.btd_matvec(np.tril(oLd), oLs, rhs, False, tr)) < TOL
+    assert rel(ops.btd_matvec(dev(Kd), dev(Ks), dev(rhs), True), G.btd_matvec(Kd, Ks, rhs, True)) < TOL
+    assert rel(ops.btd_logdet(Ld), G.LowerTriangularBlockTriDiagonal(oLd, oLs).abs_log_det()) < TOL
+
+
+def test_cholesky_reports_non_pd(ops):
+    Kd = np.tile(np.eye(2), (1, 5, 1, 1))
+    Kd[0, 3] = -np.eye(2)
+    st = ops.new_status("cuda")
+    ops.btd_cholesky(dev(Kd), dev(np.zeros((1, 4, 2, 2))), st)
+    code, idx = ops.read_status(st)
+    assert code == 1 and idx == 3
+
+
+def _rand_ssm(rng, B, N, D):
+    A = np.eye(D) * 0.9 + 0.1 * rng.standard_normal((B, N, D, D))
+    b = 0.1 * rng.standard_normal((B, N, D))
+    R = rng.standard_normal((B, N, D, D))
+    cQ = np.linalg.cholesky(0.01 * np.eye(D) + 0.002 * R @ G.mT(R))
+    R0 = rng.standard_normal((B, D, D))
+    cP0 = np.linalg.cholesky(0.5 * np.eye(D) + 0.1 * R0 @ G.mT(R0))
+    mu0 = rng.standard_normal((B, D))
+    return G.StateSpaceModel(mu0, cP0, A, b, cQ)
+
+
+@pytest.mark.parametrize("D", [1, 2, 3])
+@pytest.mark.parametrize("B,N", [(1, 1), (4, 37), (2, 500)])
+def test_ssm_transforms(ops, D, B, N):
+    rng = np.random.default_rng(7 + D + N)
+    ssm = _rand_ssm(rng, B, N, D)
+    args = [dev(x) for x in (ssm.state_transitions, ssm.state_offsets, ssm.cholesky_process_covariances,
+                             ssm.initial_mean, ssm.cholesky_initial_covariance)]
+    th = ops.ssm_to_naturals(*args)
+    oth = G.ssm_to_naturals(ssm)
+    for a, b in zip(th, oth):
+        assert rel(a, b) < TOL
+    st = ops.new_status("cuda")
+    back = ops.naturals_to_ssm(*th, status=st)
+    oback = G.naturals_to_ssm_params(*oth)
+    assert ops.read_status(st)[0] == 0
+    for a, b in zip(back, oback):
+        assert rel(a, b) < TOL
+    m, Sd = ops.ssm_marginals(*args, status=st)
+    om, oS = ssm.marginals
+    assert rel(m, om) < TOL and rel(Sd, oS) < TOL
+    e = ops.ssm_to_expectations(args[0], m, Sd)
+    oe = G.ssm_to_expectations(ssm)
+    for a, b in zip(e, oe):
+        assert rel(a, b) < TOL
+    back = ops.expectations_to_ssm(*e, status=st)
+    oback = G.expectations_to_ssm_params(*oe)
+    for a, b in zip(back, oback):
+        assert rel(a, b) < 1e-8   # chol(S1 - A S0 A^T) amplifies the rounding of the marginals
+
+
+SDES = [S.OrnsteinUhlenbeckSDE(1.2), S.DoubleWellSDE(), S.BenesSDE(0.7), S.SineDiffusionSDE(0.3),
+        S.SqrtDiffusionSDE(1.1), S.MLPDrift(), S.VanderPolOscillatorSDE(1.3, 0.8, np.eye(2)),
+        S.Lorenz63SDE(q=np.eye(3)), S.OUNdSDE(0.5, np.eye(3))]
+IDS = [type(s).__name__ for s in SDES]
+
+
+@pytest.mark.parametrize("sde", SDES, ids=IDS)
+def test_gh_expect_and_linearize(ops, sde):
+    rng = np.random.default_rng(11)
+    D, n = sde.state_dim, 50
+    m = rng.normal(size=(n, D))
+    R = rng.normal(size=(n, D, D))
+    Sg = 0.05 * R @ G.mT(R) + 0.02 * np.eye(D)
+    Ef, EJ = ops.gh_expect(sde.drift_id, sde.params, dev(m), dev(Sg), H=10, full_jacobian=sde.full_jacobian)
+    assert rel(Ef, sde.expected_drift(m[None], Sg[None])[0]) < TOL
+    assert rel(EJ, sde.expected_gradient_drift(m[None], Sg[None])[0]) < TOL
+    grid = np.round(np.arange(n + 1) * 0.01, 2)
+    A, b, cQ = ops.linearize_to_ssm(sde.drift_id, sde.params, sde.q, dev(grid), dev(m[None]), dev(Sg[None]))
+    o = S.linearize_sde(sde, grid, S.Gaussian(m, Sg), S.Gaussian(np.zeros(D), np.eye(D)))
+    # b = (E[f] - A m) dt is a cancellation (exactly 0 for OU): compare at the scale of its operands
+    assert rel(A, o.state_transitions) < TOL
+    assert rel(b, o.state_offsets, scale=0.01 * np.abs(sde.expected_drift(m[None], Sg[None])).max()) < TOL
+    assert rel(cQ, o.cholesky_process_covariances) < TOL
+
+
+@pytest.mark.parametrize("sde", SDES, ids=IDS)
+def test_kl_and_grad(ops, sde):
+    rng = np.random.default_rng(13)
+    D = sde.state_dim
+    N = 40 if D < 3 else 6
+    ssm = _rand_ssm(rng, 1, N, D)
+    ssm1 = S.remove_batch_from_ssm(ssm)
+    grid = np.round(np.arange(N + 1) * 0.01, 2)
+    p0 = S.Gaussian(np.zeros(D) + 0.2, np.eye(D) * 0.7)
+    m, Sg = ssm.marginals
+    kl, g = ops.cvi_kl_and_grad(sde.drift_id, sde.params, sde.q, 0.01, dev(grid), p0.mu, p0.cov,
+                                dev(ssm.state_transitions), dev(m), dev(Sg))
+    okl, og = S.SDE_SSM_KL_with_grads_wrt_exp_params(ssm1, sde, 0.01, p0, grid)
+    assert abs(kl.item() - okl) < TOL * abs(okl)
+    for a, b in zip(g, og):
+        assert rel(a[0], b) < TOL
+
+
+def _d1_problem(rng, B, N, n_obs, dt):
+    grid = np.round(np.arange(N + 1) * dt, 6)
+    idx = np.sort(np.stack([rng.choice(N + 1, n_obs, replace=False) for _ in range(B)]), axis=1)
+    y = rng.normal(size=(B, n_obs)) * 0.3 + np.sign(rng.normal(size=(B, 1)))
+    return grid, idx, y
+
+
+@pytest.mark.parametrize("drift,params,B,N", [(S.DRIFT_DW, [4.0, 1.0], 3, 800), (S.DRIFT_OU, [1.2], 2, 1000),
+                                              (S.DRIFT_BENES, [1.0], 2, 300), (S.DRIFT_DW, [4.0, 1.0], 64, 2000)])
+def test_site_update_d1(drift, params, B, N):
+    from vi_diffusion_processes_b200.cvi import CviEngine
+    rng = np.random.default_rng(17)
+    grid, idx, y = _d1_problem(rng, B, N, 20, 0.005)
+    eng = CviEngine(drift, params, np.ones((1, 1)), grid, idx, y[..., None], [[0.1]], [1.0], [[1e-2]])
+    ref = scalar_d1.BatchedCVISitesSDE1D(drift, params, 1.0, grid, idx, y, 0.1, 1.0, 1e-2)
+    for it in range(3):
+        e = eng.site_update(0.5, 0.5)
+        r = ref.site_update(0.5, 0.5)
+        eng.check_status()
+        assert rel(e, r) < TOL
+        assert rel(eng.fx_mus[..., 0], ref.fx_mus) < TOL and rel(eng.fx_covs[..., 0, 0], ref.fx_covs) < TOL
+        # the sites are additive parts of q's natural parameters theta_q: a site tensor whose entries are
+        # tiny next to theta_q (OU prior: the exact answer is 0) is compared at 1e-3 of theta_q's scale
+        th = scalar_d1.ssm_to_naturals(ref.p["A"], ref.p["b"], ref.p["cQ"], ref.p["mu0"], ref.p["cP0"])
+        for got, want, t in ((eng.g1[..., 0], ref.g1, th[0]), (eng.gd[..., 0, 0], ref.gd, th[1]),
+                             (eng.gs[..., 0, 0], ref.gs, th[2])):
+            scale = max(np.abs(want).max(), 1e-3 * np.abs(t + want).max())
+            assert rel(got, want, scale=scale) < TOL
+        assert rel(eng.d1[..., 0], ref.d1) < TOL and rel(eng.d2[..., 0, 0], ref.d2) < TOL
+        if it == 1:
+            eng.relinearize()
+            ref.relinearize()
+
+
+def test_site_update_vdp_2d():
+    from vi_diffusion_processes_b200.cvi import CviEngine
+    rng = np.random.default_rng(19)
+    N, n_obs = 200, 16
+    grid = np.round(np.arange(N + 1) * 0.01, 2)
+    idx = np.sort(rng.choice(N + 1, n_obs, replace=False))
+    y = rng.normal(size=(n_obs, 2))
+    sde = S.VanderPolOscillatorSDE(1.0, 1.0, np.eye(2))
+    x0 = S.Gaussian(np.ones(2), 1e-2 * np.eye(2))
+    lik = M.MultivariateGaussian(0.1 * np.eye(2))
+    ref = M.CVISitesSDE(sde, grid, (grid[idx], y), lik, prior_initial_state=x0)
+    eng = CviEngine(sde.drift_id, sde.params, sde.q, grid, idx, y, 0.1 * np.eye(2), x0.mu, x0.cov)
+    for it in range(3):
+        e = eng.site_update(0.5, 0.5)
+        r = ref.site_update(0.5, 0.5)
+        eng.check_status()
+        assert abs(e.item() - r) < TOL * abs(r)
+        assert rel(eng.fx_mus[0], ref.fx_mus) < TOL and rel(eng.fx_covs[0], ref.fx_covs) < TOL
+        assert rel(eng.g1[0], ref.girsanov_sites.nat1) < TOL
+        assert rel(eng.gd[0], ref.girsanov_sites.nat2.block_diagonal) < TOL
+        assert rel(eng.gs[0], ref.girsanov_sites.nat2.block_sub_diagonal) < TOL
+        if it == 1:
+            eng.relinearize()
+            ref.relinearize()

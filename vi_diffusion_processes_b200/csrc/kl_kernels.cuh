@@ -131,7 +131,7 @@ struct KlHandoff { double gm[D]; double gS[D * D]; };
 //   g1 += lr (scatter(d1) - dKL/deta1),  gd += lr (scatter(d2) - dKL/deta_d),  gs -= lr dKL/deta_s
 // where scatter(d.) has been pre-scattered into sc1/scd by the caller.
 template <int DRIFT, int D, int H, int G>
-__global__ void k_kl_grad(DriftParams P, Mat<D> q, double dt, double pi_factor,
+__global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double dt, double pi_factor,
                           const double* __restrict__ time_grid, Vec<D> x0_mu, Mat<D> x0_cov,
                           const double* __restrict__ Aq, const double* __restrict__ m,
                           const double* __restrict__ Sd, double* __restrict__ terms, double* __restrict__ g1,

@@ -5,7 +5,7 @@ namespace vdp {
 
 template <int D> struct KlLaunch {
     static constexpr int G = QuadGroup<D>::value;
-    static constexpr int groups = (G == 1) ? 128 : 16;   // first group of a block is the halo
+    static constexpr int groups = (G == 1) ? 128 : 8;   // first group of a block is the halo
     static constexpr int threads = groups * G;
 };
 
