@@ -1,0 +1,327 @@
+#!/usr/bin/env python
+"""
+bench.py -- grid-steps/s of one CVI-DP site update (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--seqs B] [--grid N]
+
+Workload (config.workload "C4"): B independent double-well sequences (drift 4x(1-x^2), q = 1) on a dense
+grid of N = 10^4 steps, dt = 0.005, 50 noisy observations each, float64.  One "step" = one site update
+of every sequence = docs/diffusion_processes/cvi_dp_trainer.py:71-77 once (update_data_sites,
+update_girsanov_sites, classic_elbo).  Sequences are sharded over ranks with no collective on the data
+path; per-GPU work is fixed (B = 4096 per GPU) so scaling is "weak".  Timing state: sites after 3 warm
+updates.
+
+value  = grid steps of all ranks / max-over-ranks device time, state resident in HBM.
+e2e    = same metric with the site/posterior/prior state living in pinned HOST memory: every step copies
+         the inputs host->device, runs the update through the C ABI and copies the results back.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+DT = 0.005
+N_OBS = 50
+NOISE_STD = 0.1
+X0_MU, X0_COV = 1.0, 1e-2
+DW_PARAMS = [4.0, 1.0]
+LR = 0.5
+ALGO_BYTES_PER_STEP_D1 = 80  # 8 * (4D + 6D^2) for D = 1
+
+
+def make_problem(B, N, seed):
+    """Synthetic C4 inputs: Euler-Maruyama double-well paths (sde_utils.py:36-96 restated), 50 obs each."""
+    rng = np.random.default_rng(seed)
+    grid = np.round(np.arange(N + 1) * DT, 6)
+    x = np.empty((B, N + 1))
+    x[:, 0] = np.where(rng.random(B) < 0.5, -1.0, 1.0)
+    sq = np.sqrt(DT)
+    for k in range(N):
+        xk = x[:, k]
+        x[:, k + 1] = xk + DW_PARAMS[0] * xk * (DW_PARAMS[1] - xk * xk) * DT + sq * rng.standard_normal(B)
+    idx = np.sort(np.stack([rng.choice(N + 1, N_OBS, replace=False) for _ in range(B)]), axis=1)
+    y = np.take_along_axis(x, idx, axis=1) + NOISE_STD * rng.standard_normal((B, N_OBS))
+    return grid, idx, y
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [s.strip() for s in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(max(mx)) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        return json.load(open(path)).get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_oracle_steps_per_s(B, N, seed, updates=1):
+    """The oracle (NumPy port, oracle/scalar_d1.py) timed on the host on a bounded sample of the workload."""
+    from oracle import scalar_d1
+    from oracle.sde_np import DRIFT_DW
+    grid, idx, y = make_problem(B, N, seed)
+    ref = scalar_d1.BatchedCVISitesSDE1D(DRIFT_DW, DW_PARAMS, 1.0, grid, idx, y, NOISE_STD, X0_MU, X0_COV)
+    ref.site_update(LR, LR)  # warm (also moves the sites off their initial values)
+    t0 = time.perf_counter()
+    for _ in range(updates):
+        ref.site_update(LR, LR)
+    dt = time.perf_counter() - t0
+    return B * N * updates / dt, dt
+
+
+# algorithmic (compulsory) float64 values moved per grid step by each phase's kernels: (vectors, matrices)
+# read + written once; bytes = 8 * (v * D + M * D^2).  Stated per kernel in DESIGN.md section 4.
+PHASE_TRAFFIC = {
+    "data_sites": (0, 0),
+    "sites_to_nat": (2 + 1, 4 + 2),   # read b, g1 | A, cholQ, gd, gs ; write th1 | thd, ths
+    "chol_fwd": (0, 2 + 2),           # read thd, ths ; write Ld, Ls
+    "nat2ssm_bwd": (1 + 1, 4 + 2),    # read th1 | Ld, Ls, thd, ths ; write b | A, cholQ
+    "marg_fwd": (1 + 1, 2 + 2),       # read b | A, cholQ ; write m | Ld, Ls
+    "invband_bwd": (0, 2 + 1),        # read Ld, Ls ; write Sd
+    "kl_grad": (1 + 1 + 1 + 1 + 1, 2 + 2 + 1 + 2 + 1),  # read m, g1, sc1 | A, S, gd, gs, scd ; write g1 | gd, gs (+ memset sc)
+    "elbo": (2, 3),                   # read b, m | A, cholQ, S
+}
+LAUNCHES_PER_UPDATE = 1 + 2 * 6 + 2 + 4   # kernels of ours in one vdp_cvi_site_update
+
+
+def phase_bytes_per_step(name, D):
+    v, m = PHASE_TRAFFIC[name]
+    return 8 * (v * D + m * D * D)
+
+
+def run_ours(args):
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from oracle.sde_np import DRIFT_DW
+    from vi_diffusion_processes_b200 import _lib
+    from vi_diffusion_processes_b200.cvi import CviEngine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    B, N, D = args.seqs, args.grid, 1
+    grid, idx, y = make_problem(B, N, seed=4096 + rank)
+    eng = CviEngine(DRIFT_DW, DW_PARAMS, np.ones((1, 1)), grid, idx, y[..., None], [[NOISE_STD]], [X0_MU], [[X0_COV]],
+                    device=device)
+    lib = _lib.load()
+    for _ in range(3):                      # timing state: sites after 3 warm updates
+        eng.site_update(LR, LR)
+    eng.check_status()
+
+    # pinned host mirrors of the per-step inputs / outputs for the end-to-end leg
+    in_names = ["g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs", "pA", "pb"]
+    out_names = ["g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs", "elbo"]
+    host = {k: torch.empty_like(getattr(eng, k), device="cpu").pin_memory() for k in set(in_names + out_names)}
+    for k, h in host.items():
+        h.copy_(getattr(eng, k))
+    h2d = sum(host[k].numel() * 8 for k in in_names)
+    d2h = sum(host[k].numel() * 8 for k in out_names)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    def step_resident():
+        eng.site_update(LR, LR)
+
+    def step_e2e():
+        for k in in_names:
+            getattr(eng, k).copy_(host[k], non_blocking=True)
+        eng.site_update(LR, LR)
+        for k in out_names:
+            host[k].copy_(getattr(eng, k), non_blocking=True)
+        torch.cuda.current_stream().synchronize()   # the caller reads the ELBO of this step
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    lib.vdp_profile_enable(1)
+    ms_total = timed(step_resident, args.steps, args.warmup)
+    nph = len(_lib.PHASES)
+    ph_ms = (C.c_double * nph)()
+    ph_n = (C.c_int64 * nph)()
+    lib.vdp_profile_read(ph_ms, ph_n, nph)    # covers warm-up + timed steps: averages per launch below
+    lib.vdp_profile_enable(0)
+    clocks = sampler.stop() if rank == 0 else None
+    eng.check_status()
+    ms_e2e = timed(step_e2e, max(2, args.steps // 2), 1)
+    e2e_steps = max(2, args.steps // 2)
+
+    if rank != 0:
+        return
+    steps_total = B * N * world
+    value = steps_total * args.steps / (ms_total * 1e-3)
+    e2e_value = steps_total * e2e_steps / (ms_e2e * 1e-3)
+    phases = {nm: {"ms_per_launch": ph_ms[i] / max(1, ph_n[i]), "launches": int(ph_n[i]), "ms_total": ph_ms[i]}
+              for i, nm in enumerate(_lib.PHASES)}
+    dom = max(phases, key=lambda k: phases[k]["ms_total"])
+    peak, peak_src = measured_peaks()
+    dom_bytes = phase_bytes_per_step(dom, D) * B * N
+    achieved = dom_bytes / (phases[dom]["ms_per_launch"] * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "dominant_kernel_traffic.json")
+    if os.path.exists(tpath):
+        t = json.load(open(tpath))
+        if t.get("kernel_phase") == dom and t.get("B") == B and t.get("N") == N:
+            traffic = t.get("dram_bytes_per_launch")
+    cpu_B = 32
+    cpu_val, cpu_s = cpu_oracle_steps_per_s(cpu_B, N, seed=4096)
+    line = {
+        "metric": "grid-steps/sec per CVI-DP site update", "value": value, "unit": "grid-steps/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "C4: independent double-well sequences x dense grid, one CVI-DP site update per step",
+                   "sequences_per_gpu": B, "grid_steps": N, "state_dim": D, "dt": DT, "n_obs": N_OBS, "quad_H": 20,
+                   "parallelism": f"sequence-sharded x{world}, no data-path collective",
+                   "l2": "working set per step (~%.1f GB) exceeds the 126 MB L2" % (B * N * 8 * 30 / 1e9)},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": "grid-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e / e2e_steps},
+        "gpu_launches": LAUNCHES_PER_UPDATE * args.steps,
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": dom_bytes,
+                     "kernel_share_of_step": phases[dom]["ms_total"] / sum(p["ms_total"] for p in phases.values())},
+        "roofline_update": {"algorithmic_bytes_per_grid_step": ALGO_BYTES_PER_STEP_D1,
+                            "achieved": value * ALGO_BYTES_PER_STEP_D1 / world / 1e9, "peak": peak, "unit": "GB/s",
+                            "frac": value * ALGO_BYTES_PER_STEP_D1 / world / 1e9 / peak},
+        "phases": phases,
+        "cpu_baseline": {"value": cpu_val, "unit": "grid-steps/s", "cores": 1, "kind": "port",
+                         "sample": f"{cpu_B} sequences x {N} grid steps, 1 site update, NumPy oracle "
+                                   f"(oracle/scalar_d1.py), {cpu_s:.1f} s"},
+    }
+    print(json.dumps(line))
+
+
+def run_reference(args):
+    """The reference's CPU path = the oracle port (TensorFlow is not installable here)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    B = args.ref_seqs
+    times = []
+    from oracle import scalar_d1
+    from oracle.sde_np import DRIFT_DW
+    grid, idx, y = make_problem(B, args.grid, seed=4096)
+    ref = scalar_d1.BatchedCVISitesSDE1D(DRIFT_DW, DW_PARAMS, 1.0, grid, idx, y, NOISE_STD, X0_MU, X0_COV)
+    for _ in range(max(1, min(args.warmup, 1))):
+        ref.site_update(LR, LR)
+    steps = max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ref.site_update(LR, LR)
+    dt = time.perf_counter() - t0
+    value = B * args.grid * steps / dt
+    line = {
+        "impl": "reference", "metric": "grid-steps/sec per CVI-DP site update", "value": value,
+        "unit": "grid-steps/s", "n_gpus": args.gpus, "steps": steps, "warmup": 1, "ms_per_step": dt / steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "C4: independent double-well sequences x dense grid, one CVI-DP site update per step",
+                   "sequences": B, "grid_steps": args.grid, "state_dim": 1, "dt": DT, "n_obs": N_OBS, "quad_H": 20},
+        "cpu_baseline": {"value": value, "unit": "grid-steps/s", "cores": 1, "kind": "port",
+                         "sample": f"{B} sequences x {args.grid} grid steps x {steps} site updates (bounded sample)"},
+        "e2e": {"value": value, "unit": "grid-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--seqs", type=int, default=4096, help="sequences per GPU")
+    ap.add_argument("--grid", type=int, default=10000, help="grid steps per sequence")
+    ap.add_argument("--ref-seqs", type=int, default=32, help="sequences in the bounded CPU sample")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

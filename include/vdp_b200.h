@@ -183,6 +183,27 @@ int vdp_cvi_site_update(const vdp_cvi_problem* problem_host, void* stream);
 /* classic_elbo only (no site is modified); fills elbo/ve/kl, q* and fx_* */
 int vdp_cvi_elbo(const vdp_cvi_problem* problem_host, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * diagnostics: per-phase device time of the fused pipelines (CUDA events on the launching stream).
+ * vdp_profile_enable(1) starts recording (and clears earlier marks); vdp_profile_read synchronises on
+ * the last mark, returns accumulated milliseconds and number of spans per phase, and clears the marks.
+ * Not thread safe; meant for bench.py.
+ * ---------------------------------------------------------------------------------------------- */
+enum {
+    VDP_PHASE_DATA_SITES = 0,   /* k_data_site_update */
+    VDP_PHASE_SITES_TO_NAT = 1, /* k_ssm_to_naturals (+ k_scatter_data) */
+    VDP_PHASE_CHOL_FWD = 2,     /* k_chol_fwd */
+    VDP_PHASE_NAT2SSM_BWD = 3,  /* k_nat2ssm_bwd */
+    VDP_PHASE_MARG_FWD = 4,     /* k_marg_fwd */
+    VDP_PHASE_INVBAND_BWD = 5,  /* k_invband_bwd */
+    VDP_PHASE_KL_GRAD = 6,      /* memsets + k_scatter_data + k_kl_grad */
+    VDP_PHASE_ELBO = 7,         /* k_variational_expectation + k_kl_value + k_reduce_terms + k_elbo_combine */
+    VDP_PHASE_COUNT = 8,
+    VDP_PHASE_END = -1
+};
+int vdp_profile_enable(int on);
+int vdp_profile_read(double* ms_by_phase, int64_t* spans_by_phase, int n_phases);
+
 #ifdef __cplusplus
 }
 #endif

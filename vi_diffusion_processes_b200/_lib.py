@@ -73,7 +73,11 @@ SIGNATURES = {
     "vdp_cvi_workspace": (C.c_size_t, [i64, i64, C.c_int, i64]),
     "vdp_cvi_site_update": (C.c_int, [C.POINTER(CviProblem), vp]),
     "vdp_cvi_elbo": (C.c_int, [C.POINTER(CviProblem), vp]),
+    "vdp_profile_enable": (C.c_int, [C.c_int]),
+    "vdp_profile_read": (C.c_int, [c_dp, c_i64p, C.c_int]),
 }
+
+PHASES = ["data_sites", "sites_to_nat", "chol_fwd", "nat2ssm_bwd", "marg_fwd", "invband_bwd", "kl_grad", "elbo"]
 
 _lib = None
 

@@ -4,6 +4,7 @@
 #include <string.h>
 
 #include <cmath>
+#include <vector>
 
 #include "btd_kernels.cuh"
 #include "common.cuh"
@@ -42,6 +43,29 @@ struct Arena {
 };
 static inline size_t padded(size_t doubles) { return (doubles * sizeof(double) + 255) & ~size_t(255); }
 
+// ---- optional per-phase device timing (vdp_profile_*): CUDA events recorded on the launching stream at
+// phase boundaries of the fused pipelines; off by default, costs one cudaEventRecord per phase when on.
+struct Profiler {
+    bool on = false;
+    std::vector<cudaEvent_t> pool;
+    std::vector<int> phase;   // phase[i] = phase that starts at event i
+    size_t used = 0;
+};
+static Profiler g_prof;
+static inline void prof_mark(int phase, cudaStream_t st) {
+    if (!g_prof.on) return;
+    if (g_prof.used == g_prof.pool.size()) {
+        if (g_prof.pool.size() >= 65536) return;
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        g_prof.pool.push_back(e);
+        g_prof.phase.push_back(0);
+    }
+    g_prof.phase[g_prof.used] = phase;
+    cudaEventRecord(g_prof.pool[g_prof.used], st);
+    ++g_prof.used;
+}
+
 }  // namespace vdp
 
 using namespace vdp;
@@ -59,6 +83,28 @@ int64_t vdp_read_status(const int64_t* status, int64_t* out_host2, void* stream)
     }
     if (out_host2) { out_host2[0] = h[0]; out_host2[1] = h[1]; }
     return h[0];
+}
+
+int vdp_profile_enable(int on) {
+    g_prof.on = on != 0;
+    g_prof.used = 0;
+    return VDP_OK;
+}
+
+int vdp_profile_read(double* ms_by_phase, int64_t* spans_by_phase, int n_phases) {
+    for (int i = 0; i < n_phases; ++i) { ms_by_phase[i] = 0.0; spans_by_phase[i] = 0; }
+    if (g_prof.used == 0) return VDP_OK;
+    VDP_CHECK_CUDA(cudaEventSynchronize(g_prof.pool[g_prof.used - 1]));
+    for (size_t i = 0; i + 1 < g_prof.used; ++i) {
+        const int ph = g_prof.phase[i];
+        if (ph < 0 || ph >= n_phases) continue;   // VDP_PHASE_END marks close a span, they do not open one
+        float ms = 0.f;
+        VDP_CHECK_CUDA(cudaEventElapsedTime(&ms, g_prof.pool[i], g_prof.pool[i + 1]));
+        ms_by_phase[ph] += ms;
+        spans_by_phase[ph] += 1;
+    }
+    g_prof.used = 0;
+    return VDP_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------

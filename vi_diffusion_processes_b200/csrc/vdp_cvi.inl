@@ -60,6 +60,7 @@ static inline bool cvi_ws_take(void* ws, size_t bytes, int64_t B, int64_t N, int
 template <int D>
 static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t st) {
     const int64_t B = p.B, N = p.N;
+    prof_mark(VDP_PHASE_SITES_TO_NAT, st);
     k_ssm_to_naturals<D><<<grid_for(B * (N + 1), kPtBlock), kPtBlock, 0, st>>>(
         p.pA, p.pb, p.pcholQ, p.pmu0, p.pcholP0, p.g1, p.gd, p.gs, w.th1, w.thd, w.ths, B, N);
     VDP_CHECK_LAUNCH();
@@ -79,6 +80,7 @@ template <int DRIFT, int D>
 static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams& P, cudaStream_t st) {
     const int64_t B = p.B, N = p.N;
     constexpr int G = QuadGroup<D>::value;
+    prof_mark(VDP_PHASE_ELBO, st);
     k_variational_expectation<D><<<grid_for(B, kSeqBlock), kSeqBlock, 0, st>>>(
         p.fx_mus, p.fx_covs, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.ve, B, N, p.n_obs);
     VDP_CHECK_LAUNCH();
@@ -90,6 +92,7 @@ static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams&
     VDP_CHECK_LAUNCH();
     k_elbo_combine<<<grid_for(B, kPtBlock), kPtBlock, 0, st>>>(p.ve, p.kl, p.elbo, B);
     VDP_CHECK_LAUNCH();
+    prof_mark(VDP_PHASE_END, st);
     return VDP_OK;
 }
 
@@ -100,6 +103,7 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     int rc;
     // (A) update_data_sites  variational_cvi_sde.py:301-317
     if (!(p.flags & VDP_FLAG_SKIP_DATA_UPDATE) && p.n_obs > 0) {
+        prof_mark(VDP_PHASE_DATA_SITES, st);
         k_data_site_update<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
             p.fx_mus, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.lr_data, p.d1, p.d2, B, N, p.n_obs);
         VDP_CHECK_LAUNCH();
@@ -107,6 +111,7 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     if ((rc = run_posterior<D>(p, w, st))) return rc;
     // (B) update_girsanov_sites  variational_cvi_sde.py:279-299
     const size_t n = (size_t)B * (N + 1);
+    prof_mark(VDP_PHASE_KL_GRAD, st);
     VDP_CHECK_CUDA(cudaMemsetAsync(w.sc1, 0, n * D * sizeof(double), st));
     VDP_CHECK_CUDA(cudaMemsetAsync(w.scd, 0, n * D * D * sizeof(double), st));
     if (p.n_obs > 0) {

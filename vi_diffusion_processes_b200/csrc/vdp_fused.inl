@@ -19,8 +19,10 @@ template <int D>
 static int run_nat2ssm(const double* th1, const double* thd, const double* ths, double* A, double* b, double* cholQ,
                        double* mu0, double* cholP0, double* Ld, double* Ls, int64_t B, int64_t N, int64_t* status,
                        cudaStream_t st) {
+    prof_mark(VDP_PHASE_CHOL_FWD, st);
     int rc = launch_chol_nat<D>(thd, ths, Ld, Ls, B, N + 1, status, st);
     if (rc) return rc;
+    prof_mark(VDP_PHASE_NAT2SSM_BWD, st);
     k_nat2ssm_bwd<D><<<grid_for(B, kSeqBlock), kSeqBlock, 0, st>>>(Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0,
                                                                    B, N, status);
     VDP_CHECK_LAUNCH();
@@ -32,10 +34,13 @@ template <int D>
 static int run_marginals(const double* A, const double* b, const double* cholQ, const double* mu0,
                          const double* cholP0, double* m, double* Sd, double* Ld, double* Ls, int64_t B, int64_t N,
                          int64_t* status, cudaStream_t st) {
+    prof_mark(VDP_PHASE_MARG_FWD, st);
     k_marg_fwd<D><<<grid_for(B, kSeqBlock), kSeqBlock, 0, st>>>(A, b, cholQ, mu0, cholP0, m, Ld, Ls, B, N, status);
     VDP_CHECK_LAUNCH();
+    prof_mark(VDP_PHASE_INVBAND_BWD, st);
     k_invband_bwd<D><<<grid_for(B, kSeqBlock), kSeqBlock, 0, st>>>(Ld, Ls, Sd, nullptr, B, N + 1);
     VDP_CHECK_LAUNCH();
+    prof_mark(VDP_PHASE_END, st);
     return VDP_OK;
 }
 
