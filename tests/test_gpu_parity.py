@@ -37,6 +37,19 @@ def ops():
     return o
 
 
+@pytest.fixture(params=["seq", "tiled", "tiled-seg3"])
+def sweeps(request, monkeypatch):
+    """Run the test once per sweep mapping: thread-per-sequence, parallel-in-time tiles with one segment
+    per sequence, and tiles with every sequence split in three time segments (carry exchange path)."""
+    mode = request.param
+    monkeypatch.setenv("VDP_SWEEPS", "seq" if mode == "seq" else "tiled")
+    if mode == "tiled-seg3":
+        monkeypatch.setenv("VDP_NSEG", "3")
+    else:
+        monkeypatch.delenv("VDP_NSEG", raising=False)
+    return mode
+
+
 def _spd(rng, B, n, D):
     Ld = np.tril(rng.normal(size=(B, n, D, D))) * 0.3 + 2.0 * np.eye(D)
     Ls = rng.normal(size=(B, n - 1, D, D)) * 0.5
@@ -47,8 +60,8 @@ def _spd(rng, B, n, D):
 
 
 @pytest.mark.parametrize("D", [1, 2, 3])
-@pytest.mark.parametrize("B,n", [(1, 1), (3, 2), (5, 64), (2, 1001)])
-def test_btd_ops(ops, D, B, n):
+@pytest.mark.parametrize("B,n", [(1, 1), (3, 2), (5, 64), (2, 1001), (2, 5000)])
+def test_btd_ops(ops, sweeps, D, B, n):
     rng = np.random.default_rng(D * 100 + n)
     Kd, Ks = _spd(rng, B, max(n, 2), D)
     Kd, Ks = Kd[:, :n], Ks[:, :n - 1]
@@ -93,8 +106,8 @@ def _rand_ssm(rng, B, N, D):
 
 
 @pytest.mark.parametrize("D", [1, 2, 3])
-@pytest.mark.parametrize("B,N", [(1, 1), (4, 37), (2, 500)])
-def test_ssm_transforms(ops, D, B, N):
+@pytest.mark.parametrize("B,N", [(1, 1), (4, 37), (2, 500), (3, 4001)])
+def test_ssm_transforms(ops, sweeps, D, B, N):
     rng = np.random.default_rng(7 + D + N)
     ssm = _rand_ssm(rng, B, N, D)
     args = [dev(x) for x in (ssm.state_transitions, ssm.state_offsets, ssm.cholesky_process_covariances,
@@ -174,7 +187,7 @@ def _d1_problem(rng, B, N, n_obs, dt):
 
 @pytest.mark.parametrize("drift,params,B,N", [(S.DRIFT_DW, [4.0, 1.0], 3, 800), (S.DRIFT_OU, [1.2], 2, 1000),
                                               (S.DRIFT_BENES, [1.0], 2, 300), (S.DRIFT_DW, [4.0, 1.0], 64, 2000)])
-def test_site_update_d1(drift, params, B, N):
+def test_site_update_d1(sweeps, drift, params, B, N):
     from vi_diffusion_processes_b200.cvi import CviEngine
     rng = np.random.default_rng(17)
     grid, idx, y = _d1_problem(rng, B, N, 20, 0.005)
@@ -199,7 +212,7 @@ def test_site_update_d1(drift, params, B, N):
             ref.relinearize()
 
 
-def test_site_update_vdp_2d():
+def test_site_update_vdp_2d(sweeps):
     from vi_diffusion_processes_b200.cvi import CviEngine
     rng = np.random.default_rng(19)
     N, n_obs = 200, 16

@@ -1,0 +1,187 @@
+// Associative elements of the parallel-in-time sweeps and the block-level scan over them.
+//
+// Each sequential recursion of the block-tridiagonal layer (sweeps.cuh) is a composition of per-step
+// maps on a small carry.  A chunk of consecutive steps is summarised by one element of a family that is
+// closed under composition; scanning the chunk elements gives every chunk its incoming carry, after
+// which the chunk runs the reference-order recursion of sweeps.cuh from that carry.  Only the carries
+// see a rounding order different from the sequential reference (measured effect on the site natural
+// parameters: 1e-11 relative).
+//
+//   SchurElem   forward banded Cholesky (cholesky_band, block_tri_diag.py:428-440) in information form:
+//               S_out = Lb - Lab^T (S_in + La)^-1 Lab.  Composition eliminates the shared node by a
+//               Schur complement on positive-definite blocks (the pairwise-potential elements of the
+//               parallel smoother of Sarkka & Garcia-Fernandez), i.e. it is a block Cholesky of the same
+//               precision in nested-dissection order, backward stable like the sequential order.
+//   AffSymElem  backward inverse band (inverse_from_cholesky_band, block_tri_diag.py:318-337):
+//               S_out = C + G^T S_in G, all terms positive semi-definite.
+//   AffVecElem  affine vector recursions (solve_triang_mat on the A^-1 block, state_space_model.py:251,
+//               ssm_gaussian_transformations.py:502):  x_out = M x_in + v.
+#pragma once
+#include "smallmat.cuh"
+
+namespace vdp {
+
+// ---------------------------------------------------------------------------------------------------
+template <int D>
+struct SchurElem {
+    Mat<D> La, Lab, Lb;
+    int id;   // 1 = identity map
+};
+
+template <int D>
+struct SchurOps {
+    using Elem = SchurElem<D>;
+    using State = Mat<D>;
+    __device__ __forceinline__ static Elem identity() {
+        Elem e;
+        e.La = mat_zero<D>();
+        e.Lab = mat_zero<D>();
+        e.Lb = mat_zero<D>();
+        e.id = 1;
+        return e;
+    }
+    // one transition  S' = Kd_next - Ks S^-1 Ks^T
+    __device__ __forceinline__ static Elem step(const Mat<D>& Ks, const Mat<D>& Kd_next) {
+        Elem e;
+        e.La = mat_zero<D>();
+        e.Lab = transpose(Ks);
+        e.Lb = Kd_next;
+        e.id = 0;
+        return e;
+    }
+    // e1 first, then e2
+    __device__ __forceinline__ static Elem combine(const Elem& e1, const Elem& e2) {
+        if (e1.id) return e2;
+        if (e2.id) return e1;
+        bool ok = true;
+        const Mat<D> Lm = chol(e1.Lb + e2.La, ok);
+        const Mat<D> WU = trsm(Lm, transpose(e1.Lab));
+        const Mat<D> WV = trsm(Lm, e2.Lab);
+        Elem r;
+        r.La = e1.La - Tmm(WU, WU);
+        r.Lab = Tmm(WU, WV);
+        r.Lb = e2.Lb - Tmm(WV, WV);
+        r.id = 0;
+        return r;
+    }
+    // e followed by one transition (cheaper than combine(e, step()))
+    __device__ __forceinline__ static void push(Elem& e, const Mat<D>& Ks, const Mat<D>& Kd_next) {
+        if (e.id) { e = step(Ks, Kd_next); return; }
+        bool ok = true;
+        const Mat<D> Lm = chol(e.Lb, ok);
+        const Mat<D> WU = trsm(Lm, transpose(e.Lab));
+        const Mat<D> WV = trsm(Lm, transpose(Ks));
+        e.La = e.La - Tmm(WU, WU);
+        e.Lab = Tmm(WU, WV);
+        e.Lb = Kd_next - Tmm(WV, WV);
+    }
+    __device__ __forceinline__ static State apply(const Elem& e, const State& S) {
+        if (e.id) return S;
+        bool ok = true;
+        const Mat<D> Lx = chol(S + e.La, ok);
+        const Mat<D> W = trsm(Lx, e.Lab);
+        return e.Lb - Tmm(W, W);
+    }
+};
+
+// ---------------------------------------------------------------------------------------------------
+template <int D>
+struct AffSymElem {
+    Mat<D> C, G;
+};
+
+template <int D>
+struct AffSymOps {
+    using Elem = AffSymElem<D>;
+    using State = Mat<D>;
+    __device__ __forceinline__ static Elem identity() {
+        Elem e;
+        e.C = mat_zero<D>();
+        e.G = mat_eye<D>();
+        return e;
+    }
+    __device__ __forceinline__ static Elem combine(const Elem& e1, const Elem& e2) {
+        Elem r;
+        r.C = e2.C + Tmm(e2.G, mm(e1.C, e2.G));
+        r.G = mm(e1.G, e2.G);
+        return r;
+    }
+    __device__ __forceinline__ static State apply(const Elem& e, const State& S) {
+        return e.C + Tmm(e.G, mm(S, e.G));
+    }
+};
+
+// ---------------------------------------------------------------------------------------------------
+template <int D>
+struct AffVecElem {
+    Mat<D> M;
+    Vec<D> v;
+};
+
+template <int D>
+struct AffVecOps {
+    using Elem = AffVecElem<D>;
+    using State = Vec<D>;
+    __device__ __forceinline__ static Elem identity() {
+        Elem e;
+        e.M = mat_eye<D>();
+        e.v = vec_zero<D>();
+        return e;
+    }
+    __device__ __forceinline__ static Elem combine(const Elem& e1, const Elem& e2) {
+        Elem r;
+        r.M = mm(e2.M, e1.M);
+        r.v = e2.v + mv(e2.M, e1.v);
+        return r;
+    }
+    __device__ __forceinline__ static State apply(const Elem& e, const State& x) { return e.v + mv(e.M, x); }
+};
+
+// ---------------------------------------------------------------------------------------------------
+// warp shuffle of a register struct
+template <typename T>
+__device__ __forceinline__ T shfl_any(const T& v, int src_lane) {
+    static_assert(sizeof(T) % 4 == 0, "struct must be made of 32-bit words");
+    T r;
+    const int* pi = reinterpret_cast<const int*>(&v);
+    int* po = reinterpret_cast<int*>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 4); ++i) po[i] = __shfl_sync(0xffffffffu, pi[i], src_lane);
+    return r;
+}
+
+// Exclusive scan of one element per thread over a block of T threads, thread 0 first.
+// Returns the composition of the elements of all preceding threads (identity for thread 0) and, in
+// `total`, the composition of all T elements (the same value in every thread).
+// `warp_tot` is shared scratch of T/32 elements; the call contains block-wide barriers.
+template <class Ops, int T>
+__device__ __forceinline__ typename Ops::Elem block_exclusive_scan(const typename Ops::Elem& mine,
+                                                                   typename Ops::Elem* warp_tot,
+                                                                   typename Ops::Elem& total) {
+    using E = typename Ops::Elem;
+    constexpr int W = T / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    E inc = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const E other = shfl_any(inc, lane >= d ? lane - d : lane);
+        if (lane >= d) inc = Ops::combine(other, inc);
+    }
+    E excl = shfl_any(inc, lane > 0 ? lane - 1 : 0);
+    if (lane == 0) excl = Ops::identity();
+    __syncthreads();   // previous use of warp_tot is over
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    E tot = warp_tot[0];
+    E wp = Ops::identity();
+#pragma unroll
+    for (int w = 1; w < W; ++w) {
+        if (w == warp) wp = tot;
+        tot = Ops::combine(tot, warp_tot[w]);
+    }
+    total = tot;
+    if (warp == 0) return excl;
+    return Ops::combine(wp, excl);
+}
+
+}  // namespace vdp

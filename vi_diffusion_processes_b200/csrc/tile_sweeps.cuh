@@ -1,0 +1,499 @@
+// Parallel-in-time ("tiled") versions of the four sequential sweeps of the block-tridiagonal layer.
+//
+// Mapping: one CTA walks one SEGMENT of one sequence, tile by tile in sweep direction.  A tile is T
+// chunks of L consecutive grid steps; it is staged in shared memory with coalesced loads, thread c owns
+// chunk c.  Per tile: (A) every thread composes the associative element of its chunk (scan_elems.cuh),
+// (scan) a block-wide exclusive scan turns the elements and the tile's incoming carry into one carry
+// per chunk, (C) every thread runs the reference-order recursion of sweeps.cuh over its chunk, writing
+// into the staged tile, which is then stored with coalesced writes.  L is odd so that the chunk stride
+// in shared memory (L * D * D doubles) is conflict-free without padding.
+//
+// With one segment per sequence (many sequences, BASELINE config 4) the inputs are read from HBM once
+// and the sweep is a single launch.  With several segments per sequence (few long sequences, config 5,
+// and time-segment sharding over GPUs) the launch sequence is
+//     SUMMARY (segment elements)  ->  k_seg_scan (segment carries)  ->  FULL.
+//
+// Reference operations: see sweeps.cuh (same step functions; only the carries differ in rounding order).
+#pragma once
+#include "common.cuh"
+#include "scan_elems.cuh"
+#include "sweeps.cuh"
+
+namespace vdp {
+
+enum { SWEEP_FULL = 0, SWEEP_SUMMARY = 1, SWEEP_SUMMARY2 = 2 };
+
+template <int T>
+__device__ __forceinline__ void stage_in(double* __restrict__ s, const double* __restrict__ g, int64_t count,
+                                         double scale) {
+    for (int64_t i = threadIdx.x; i < count; i += T) s[i] = scale * g[i];
+}
+template <int T>
+__device__ __forceinline__ void stage_in(double* __restrict__ s, const double* __restrict__ g, int64_t count) {
+    for (int64_t i = threadIdx.x; i < count; i += T) s[i] = g[i];
+}
+template <int T>
+__device__ __forceinline__ void stage_out(double* __restrict__ g, const double* __restrict__ s, int64_t count) {
+    for (int64_t i = threadIdx.x; i < count; i += T) g[i] = s[i];
+}
+
+// two recursions scanned together
+template <class OpsA, class OpsB>
+struct PairOps {
+    struct Elem { typename OpsA::Elem a; typename OpsB::Elem b; };
+    struct State { typename OpsA::State a; typename OpsB::State b; };
+    __device__ __forceinline__ static Elem identity() {
+        Elem e;
+        e.a = OpsA::identity();
+        e.b = OpsB::identity();
+        return e;
+    }
+    __device__ __forceinline__ static Elem combine(const Elem& e1, const Elem& e2) {
+        Elem r;
+        r.a = OpsA::combine(e1.a, e2.a);
+        r.b = OpsB::combine(e1.b, e2.b);
+        return r;
+    }
+    __device__ __forceinline__ static State apply(const Elem& e, const State& s) {
+        State r;
+        r.a = OpsA::apply(e.a, s.a);
+        r.b = OpsB::apply(e.b, s.b);
+        return r;
+    }
+};
+
+// carries of the segments of every sequence: state at the start (forward) / top (reverse) of each segment
+template <class Ops>
+__global__ void k_seg_scan(const typename Ops::Elem* __restrict__ elems, const typename Ops::State* __restrict__ init,
+                           typename Ops::State* __restrict__ carry, int64_t B, int nseg, int reverse) {
+    const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    typename Ops::State st = init[b];
+    for (int i = 0; i < nseg; ++i) {
+        const int s = reverse ? nseg - 1 - i : i;
+        carry[b * nseg + s] = st;
+        st = Ops::apply(elems[b * nseg + s], st);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// forward Cholesky over one staged tile: sKd holds K_kk for nodes [0, cnt] of the tile (in: K, out: L_kk),
+// sKs holds K_{k+1,k} for transitions [0, cnt) (in: K, out: L_{k+1,k}).
+// Phase A: chunk element.
+template <int D, int L>
+__device__ __forceinline__ SchurElem<D> chol_tile_summary(const double* sKd, const double* sKs, int k0, int len) {
+    constexpr int DD = D * D;
+    SchurElem<D> e = SchurOps<D>::identity();
+    for (int t = 0; t < len; ++t)
+        SchurOps<D>::push(e, mat_load<D>(sKs + (k0 + t) * DD), mat_load<D>(sKd + (k0 + t + 1) * DD));
+    return e;
+}
+// Phase C: reference-order recursion from the chunk's carry S (the Schur complement at node k0).
+// `last_node` = local index of the sequence's final node if it is in this tile, else -1.
+template <int D, int L>
+__device__ __forceinline__ void chol_tile_recursion(double* sKd, double* sKs, int k0, int len, const Mat<D>& S,
+                                                    int last_node, int64_t flat_node0, int64_t* status) {
+    constexpr int DD = D * D;
+    if (len <= 0) return;
+    bool ok = true;
+    Mat<D> Lk = chol(S, ok);
+    if (!ok) { report_not_pd(status, flat_node0 + k0); ok = true; }
+    mat_store<D>(sKd + k0 * DD, Lk);
+    for (int t = 0; t < len; ++t) {
+        const Mat<D> Ksub = mat_load<D>(sKs + (k0 + t) * DD);
+        const Mat<D> Lsub = transpose(trsm(Lk, transpose(Ksub)));
+        mat_store<D>(sKs + (k0 + t) * DD, Lsub);
+        if (t < len - 1 || k0 + t + 1 == last_node) {
+            const Mat<D> Sn = mat_load<D>(sKd + (k0 + t + 1) * DD) - mmT(Lsub, Lsub);
+            Lk = chol(Sn, ok);
+            if (!ok) { report_not_pd(status, flat_node0 + k0 + t + 1); ok = true; }
+            mat_store<D>(sKd + (k0 + t + 1) * DD, Lk);
+        }
+    }
+}
+
+// cholesky_band of K = (scaleD * Xd, scaleS * Xs)    block_tri_diag.py:428-440
+template <int D, int T, int L, int MODE>
+__global__ void __launch_bounds__(T)
+k_chol_tiled(const double* __restrict__ Xd, const double* __restrict__ Xs, double scaleD, double scaleS,
+             double* __restrict__ Ld, double* __restrict__ Ls, int64_t B, int64_t N, int nseg, int64_t seg_len,
+             const Mat<D>* __restrict__ carry_in, Mat<D>* __restrict__ init_out,
+             SchurElem<D>* __restrict__ seg_elem, int64_t* status) {
+    constexpr int DD = D * D, TL = T * L;
+    extern __shared__ __align__(16) double smem[];
+    double* sKd = smem;
+    double* sKs = sKd + (TL + 1) * DD;
+    SchurElem<D>* wtot = reinterpret_cast<SchurElem<D>*>(sKs + TL * DD);
+    const int64_t b = blockIdx.x / nseg;
+    const int seg = (int)(blockIdx.x % nseg);
+    const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
+    const double* xd = Xd + b * (N + 1) * DD;
+    const double* xs = Xs + b * N * DD;
+    Mat<D> S_tile = mat_zero<D>();
+    if (MODE == SWEEP_FULL && seg > 0) S_tile = carry_in[b * nseg + seg];
+    SchurElem<D> seg_tot = SchurOps<D>::identity();
+    for (int64_t tk = t0; tk < t1; tk += TL) {
+        const int cnt = (int)min((int64_t)TL, t1 - tk);
+        __syncthreads();
+        stage_in<T>(sKd, xd + tk * DD, (int64_t)(cnt + 1) * DD, scaleD);
+        stage_in<T>(sKs, xs + tk * DD, (int64_t)cnt * DD, scaleS);
+        __syncthreads();
+        if (seg == 0 && tk == 0) {
+            S_tile = mat_load<D>(sKd);
+            if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = S_tile;
+        }
+        const int k0 = threadIdx.x * L;
+        const int len = min(L, cnt - k0);
+        const SchurElem<D> e = chol_tile_summary<D, L>(sKd, sKs, k0, len);
+        SchurElem<D> total;
+        const SchurElem<D> excl = block_exclusive_scan<SchurOps<D>, T>(e, wtot, total);
+        if (MODE != SWEEP_FULL) {
+            seg_tot = SchurOps<D>::combine(seg_tot, total);
+            continue;
+        }
+        const Mat<D> S = SchurOps<D>::apply(excl, S_tile);
+        S_tile = SchurOps<D>::apply(total, S_tile);
+        const int last_node = (tk + cnt == N) ? cnt : -1;
+        chol_tile_recursion<D, L>(sKd, sKs, k0, len, S, last_node, b * (N + 1) + tk, status);
+        __syncthreads();
+        stage_out<T>(Ld + (b * (N + 1) + tk) * DD, sKd, (int64_t)(cnt + (last_node >= 0 ? 1 : 0)) * DD);
+        stage_out<T>(Ls + (b * N + tk) * DD, sKs, (int64_t)cnt * DD);
+    }
+    if (MODE != SWEEP_FULL && threadIdx.x == 0) seg_elem[b * nseg + seg] = seg_tot;
+}
+
+template <int D, int T, int L>
+constexpr size_t chol_tiled_smem() {
+    return ((size_t)(T * L + 1) * D * D + (size_t)T * L * D * D) * sizeof(double) + (T / 32) * sizeof(SchurElem<D>);
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// StateSpaceModel.marginal_means (state_space_model.py:251) + _build_precision (:431-483) + cholesky_band:
+// forward sweep giving m [B,N+1,D] and the Cholesky factor (Ld, Ls) of the rebuilt precision.
+template <int D>
+using MargOps = PairOps<SchurOps<D>, AffVecOps<D>>;
+
+template <int D, int T, int L, int MODE>
+__global__ void __launch_bounds__(T)
+k_marg_tiled(const double* __restrict__ A, const double* __restrict__ bo, const double* __restrict__ cholQ,
+             const double* __restrict__ mu0, const double* __restrict__ cholP0, double* __restrict__ m,
+             double* __restrict__ Ld, double* __restrict__ Ls, int64_t B, int64_t N, int nseg, int64_t seg_len,
+             const typename MargOps<D>::State* __restrict__ carry_in,
+             typename MargOps<D>::State* __restrict__ init_out,
+             typename MargOps<D>::Elem* __restrict__ seg_elem, int64_t* status) {
+    constexpr int DD = D * D, TL = T * L;
+    using Ops = MargOps<D>;
+    extern __shared__ __align__(16) double smem[];
+    double* sC = smem;                        // chol factor of node i           (TL + 2)
+    double* sA = sC + (TL + 2) * DD;          // A of transition i               (TL + 1)
+    double* sKd = sA + (TL + 1) * DD;         // precision diagonal -> L_kk      (TL + 1)
+    double* sKs = sKd + (TL + 1) * DD;        // precision sub-diagonal -> L_sub (TL)
+    double* sb = sKs + TL * DD;               // offsets -> m_{k+1}              (TL)
+    typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(sb + TL * D);
+    const int64_t b = blockIdx.x / nseg;
+    const int seg = (int)(blockIdx.x % nseg);
+    const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
+    typename Ops::State st;
+    st.a = mat_zero<D>();
+    st.b = vec_zero<D>();
+    if (MODE == SWEEP_FULL && seg > 0) st = carry_in[b * nseg + seg];
+    typename Ops::Elem seg_tot = Ops::identity();
+    for (int64_t tk = t0; tk < t1; tk += TL) {
+        const int cnt = (int)min((int64_t)TL, t1 - tk);
+        const bool halo_has_next = tk + cnt < N;
+        __syncthreads();
+        // node factors: node k -> cholQ[k-1], node 0 -> cholP0
+        if (tk == 0) {
+            stage_in<T>(sC, cholP0 + b * DD, DD);
+            stage_in<T>(sC + DD, cholQ + b * N * DD, (int64_t)(cnt + (halo_has_next ? 1 : 0)) * DD);
+        } else {
+            stage_in<T>(sC, cholQ + (b * N + tk - 1) * DD, (int64_t)(cnt + 1 + (halo_has_next ? 1 : 0)) * DD);
+        }
+        stage_in<T>(sA, A + (b * N + tk) * DD, (int64_t)(cnt + (halo_has_next ? 1 : 0)) * DD);
+        stage_in<T>(sb, bo + (b * N + tk) * D, (int64_t)cnt * D);
+        __syncthreads();
+        // phase 0: precision blocks of nodes [0, cnt]
+        for (int i = threadIdx.x; i <= cnt; i += T) {
+            const bool has_next = (i < cnt) || halo_has_next;
+            Mat<D> Ak = mat_zero<D>(), cnext = mat_eye<D>(), diag, sub = mat_zero<D>();
+            if (has_next) { Ak = mat_load<D>(sA + i * DD); cnext = mat_load<D>(sC + (i + 1) * DD); }
+            precision_blocks(mat_load<D>(sC + i * DD), has_next, Ak, cnext, diag, sub);
+            mat_store<D>(sKd + i * DD, diag);
+            if (i < cnt) mat_store<D>(sKs + i * DD, sub);
+        }
+        __syncthreads();
+        if (seg == 0 && tk == 0) {
+            st.a = mat_load<D>(sKd);
+            st.b = vec_load<D>(mu0 + b * D);
+            if (threadIdx.x == 0) {
+                if (MODE == SWEEP_FULL) vec_store<D>(m + b * (N + 1) * D, st.b);
+                else init_out[b] = st;
+            }
+        }
+        const int k0 = threadIdx.x * L;
+        const int len = min(L, cnt - k0);
+        typename Ops::Elem e;
+        e.a = chol_tile_summary<D, L>(sKd, sKs, k0, len);
+        e.b = AffVecOps<D>::identity();
+        for (int t = 0; t < len; ++t) {
+            AffVecElem<D> s;
+            s.M = mat_load<D>(sA + (k0 + t) * DD);
+            s.v = vec_load<D>(sb + (k0 + t) * D);
+            e.b = AffVecOps<D>::combine(e.b, s);
+        }
+        typename Ops::Elem total;
+        const typename Ops::Elem excl = block_exclusive_scan<Ops, T>(e, wtot, total);
+        if (MODE != SWEEP_FULL) {
+            seg_tot = Ops::combine(seg_tot, total);
+            continue;
+        }
+        const typename Ops::State mine = Ops::apply(excl, st);
+        st = Ops::apply(total, st);
+        const int last_node = (tk + cnt == N) ? cnt : -1;
+        chol_tile_recursion<D, L>(sKd, sKs, k0, len, mine.a, last_node, b * (N + 1) + tk, status);
+        Vec<D> mk = mine.b;
+        for (int t = 0; t < len; ++t) {
+            mk = vec_load<D>(sb + (k0 + t) * D) + mv(mat_load<D>(sA + (k0 + t) * DD), mk);
+            vec_store<D>(sb + (k0 + t) * D, mk);
+        }
+        __syncthreads();
+        stage_out<T>(Ld + (b * (N + 1) + tk) * DD, sKd, (int64_t)(cnt + (last_node >= 0 ? 1 : 0)) * DD);
+        stage_out<T>(Ls + (b * N + tk) * DD, sKs, (int64_t)cnt * DD);
+        stage_out<T>(m + (b * (N + 1) + tk + 1) * D, sb, (int64_t)cnt * D);
+    }
+    if (MODE != SWEEP_FULL && threadIdx.x == 0) seg_elem[b * nseg + seg] = seg_tot;
+}
+
+template <int D, int T, int L>
+constexpr size_t marg_tiled_smem() {
+    return ((size_t)(T * L + 2) * D * D + 2 * (size_t)(T * L + 1) * D * D + (size_t)T * L * D * D + (size_t)T * L * D) *
+               sizeof(double) +
+           (T / 32) * sizeof(typename MargOps<D>::Elem);
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// Backward sweeps.  A segment's tiles are walked from its top; thread c owns the c-th chunk from the top
+// of the tile, local transitions [bot, top), processed downwards; its carry is the state at node `top`.
+struct BwdChunk { int top, bot, len; };
+template <int L>
+__device__ __forceinline__ BwdChunk bwd_chunk(int cnt) {
+    BwdChunk c;
+    c.top = cnt - (int)threadIdx.x * L;
+    c.bot = max(0, c.top - L);
+    c.len = c.top - c.bot;
+    return c;
+}
+
+// element of the inverse-band recursion over a chunk (top-down)
+template <int D>
+__device__ __forceinline__ AffSymElem<D> invband_tile_summary(const double* sLd, const double* sLs, const BwdChunk& ch) {
+    constexpr int DD = D * D;
+    AffSymElem<D> e = AffSymOps<D>::identity();
+    for (int k = ch.top - 1; k >= ch.bot; --k) {
+        const Mat<D> U = trsm(mat_load<D>(sLd + k * DD), mat_eye<D>());
+        AffSymElem<D> s;
+        s.G = mm(mat_load<D>(sLs + k * DD), U);
+        s.C = Tmm(U, U);
+        e = AffSymOps<D>::combine(e, s);
+    }
+    return e;
+}
+
+// inverse_from_cholesky_band (block_tri_diag.py:318-337): Sd [B,n,D,D] and optionally Ss [B,n-1,D,D]
+template <int D, int T, int L, int MODE>
+__global__ void __launch_bounds__(T)
+k_invband_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, double* __restrict__ Sd,
+                double* __restrict__ Ss, int64_t B, int64_t N, int nseg, int64_t seg_len,
+                const Mat<D>* __restrict__ carry_in, Mat<D>* __restrict__ init_out,
+                AffSymElem<D>* __restrict__ seg_elem) {
+    constexpr int DD = D * D, TL = T * L;
+    using Ops = AffSymOps<D>;
+    extern __shared__ __align__(16) double smem[];
+    double* sLd = smem;             // L_kk -> Sigma_kk       (TL)
+    double* sLs = sLd + TL * DD;    // L_sub -> Sigma_{k+1,k} (TL)
+    AffSymElem<D>* wtot = reinterpret_cast<AffSymElem<D>*>(sLs + TL * DD);
+    const int64_t b = blockIdx.x / nseg;
+    const int seg = (int)(blockIdx.x % nseg);
+    const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
+    Mat<D> S_tile;
+    if (t1 == N) {
+        S_tile = invband_last(mat_load<D>(Ld + (b * (N + 1) + N) * DD));
+        if (threadIdx.x == 0) {
+            if (MODE == SWEEP_FULL) mat_store<D>(Sd + (b * (N + 1) + N) * DD, S_tile);
+            else init_out[b] = S_tile;
+        }
+    } else {
+        S_tile = (MODE == SWEEP_FULL) ? carry_in[b * nseg + seg] : mat_zero<D>();
+    }
+    AffSymElem<D> seg_tot = Ops::identity();
+    for (int64_t hi = t1; hi > t0; hi -= TL) {
+        const int64_t lo = max(t0, hi - TL);
+        const int cnt = (int)(hi - lo);
+        __syncthreads();
+        stage_in<T>(sLd, Ld + (b * (N + 1) + lo) * DD, (int64_t)cnt * DD);
+        stage_in<T>(sLs, Ls + (b * N + lo) * DD, (int64_t)cnt * DD);
+        __syncthreads();
+        const BwdChunk ch = bwd_chunk<L>(cnt);
+        const AffSymElem<D> e = invband_tile_summary<D>(sLd, sLs, ch);
+        AffSymElem<D> total;
+        const AffSymElem<D> excl = block_exclusive_scan<Ops, T>(e, wtot, total);
+        if (MODE != SWEEP_FULL) {
+            seg_tot = Ops::combine(seg_tot, total);
+            continue;
+        }
+        Mat<D> S = Ops::apply(excl, S_tile);
+        S_tile = Ops::apply(total, S_tile);
+        for (int k = ch.top - 1; k >= ch.bot; --k) {
+            Mat<D> Ssub, Skk;
+            invband_step(mat_load<D>(sLd + k * DD), mat_load<D>(sLs + k * DD), S, Ssub, Skk);
+            S = Skk;
+            mat_store<D>(sLd + k * DD, Skk);
+            mat_store<D>(sLs + k * DD, Ssub);
+        }
+        __syncthreads();
+        stage_out<T>(Sd + (b * (N + 1) + lo) * DD, sLd, (int64_t)cnt * DD);
+        if (Ss) stage_out<T>(Ss + (b * N + lo) * DD, sLs, (int64_t)cnt * DD);
+    }
+    if (MODE != SWEEP_FULL && threadIdx.x == 0) seg_elem[b * nseg + seg] = seg_tot;
+}
+
+template <int D, int T, int L>
+constexpr size_t invband_tiled_smem() {
+    return 2 * (size_t)T * L * D * D * sizeof(double) + (T / 32) * sizeof(AffSymElem<D>);
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// naturals_to_ssm_params, backward half (ssm_gaussian_transformations.py:443-504): inverse band ->
+// A_k -> conditional precision -> covariance and its Cholesky factor -> (A^-T)-solve of theta1 -> offsets.
+// Two dependent recursions: Sigma (AffSym) and, through A_k(Sigma), the vector y (AffVec); the tile runs
+// scan / recursion for Sigma first, composes the y elements on the way, then scans and runs y.
+// Multi-segment launch order: SUMMARY (Sigma elements) -> k_seg_scan -> SUMMARY2 (y elements, needs the
+// Sigma carries) -> k_seg_scan -> FULL.
+template <int D, int T, int L, int MODE>
+__global__ void __launch_bounds__(T)
+k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, const double* __restrict__ th1,
+                const double* __restrict__ thd, const double* __restrict__ ths, double* __restrict__ A,
+                double* __restrict__ bo, double* __restrict__ cholQ, double* __restrict__ mu0,
+                double* __restrict__ cholP0, int64_t B, int64_t N, int nseg, int64_t seg_len,
+                const Mat<D>* __restrict__ carryS, const Vec<D>* __restrict__ carryY, Mat<D>* __restrict__ initS,
+                Vec<D>* __restrict__ initY, AffSymElem<D>* __restrict__ seg_elemS,
+                AffVecElem<D>* __restrict__ seg_elemY, int64_t* status) {
+    constexpr int DD = D * D, TL = T * L;
+    extern __shared__ __align__(16) double smem[];
+    double* sLd = smem;              // L_kk  -> chol of the conditional covariance of node k
+    double* sLs = sLd + TL * DD;     // L_sub -> A_k
+    double* sTd = sLs + TL * DD;     // theta_diag -> conditional covariance of node k
+    double* sTs = sTd + TL * DD;     // theta_sub
+    double* sT1 = sTs + TL * DD;     // theta_1 -> offset of node k
+    AffSymElem<D>* wtotS = reinterpret_cast<AffSymElem<D>*>(sT1 + TL * D);
+    AffVecElem<D>* wtotY = reinterpret_cast<AffVecElem<D>*>(wtotS);   // used after the Sigma scan is over
+    const int64_t b = blockIdx.x / nseg;
+    const int seg = (int)(blockIdx.x % nseg);
+    const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
+    const int64_t n = N + 1;
+    Mat<D> S_tile = mat_zero<D>();
+    Vec<D> y_tile = vec_zero<D>();
+    if (t1 == N) {
+        S_tile = invband_last(mat_load<D>(Ld + (b * n + N) * DD));
+        y_tile = vec_load<D>(th1 + (b * n + N) * D);
+        if (threadIdx.x == 0) {
+            if (MODE == SWEEP_SUMMARY) initS[b] = S_tile;
+            if (MODE == SWEEP_SUMMARY2) initY[b] = y_tile;
+            if (MODE == SWEEP_FULL) {   // outputs of the last node
+                bool ok = true;
+                Mat<D> cov, cc;
+                cov_from_precision(mirror_lower(-2.0 * mat_load<D>(thd + (b * n + N) * DD)), cov, cc, ok);
+                if (!ok) report_not_pd(status, b * n + N);
+                vec_store<D>(bo + (b * N + N - 1) * D, mv(cov, y_tile));
+                mat_store<D>(cholQ + (b * N + N - 1) * DD, cc);
+            }
+        }
+    } else {
+        if (MODE != SWEEP_SUMMARY) S_tile = carryS[b * nseg + seg];
+        if (MODE == SWEEP_FULL) y_tile = carryY[b * nseg + seg];
+    }
+    AffSymElem<D> seg_totS = AffSymOps<D>::identity();
+    AffVecElem<D> seg_totY = AffVecOps<D>::identity();
+    for (int64_t hi = t1; hi > t0; hi -= TL) {
+        const int64_t lo = max(t0, hi - TL);
+        const int cnt = (int)(hi - lo);
+        __syncthreads();
+        stage_in<T>(sLd, Ld + (b * n + lo) * DD, (int64_t)cnt * DD);
+        stage_in<T>(sLs, Ls + (b * N + lo) * DD, (int64_t)cnt * DD);
+        if (MODE != SWEEP_SUMMARY) {
+            stage_in<T>(sTd, thd + (b * n + lo) * DD, (int64_t)cnt * DD);
+            stage_in<T>(sTs, ths + (b * N + lo) * DD, (int64_t)cnt * DD);
+            stage_in<T>(sT1, th1 + (b * n + lo) * D, (int64_t)cnt * D);
+        }
+        __syncthreads();
+        const BwdChunk ch = bwd_chunk<L>(cnt);
+        const AffSymElem<D> eS = invband_tile_summary<D>(sLd, sLs, ch);
+        AffSymElem<D> totalS;
+        const AffSymElem<D> exclS = block_exclusive_scan<AffSymOps<D>, T>(eS, wtotS, totalS);
+        if (MODE == SWEEP_SUMMARY) {
+            seg_totS = AffSymOps<D>::combine(seg_totS, totalS);
+            continue;
+        }
+        Mat<D> S = AffSymOps<D>::apply(exclS, S_tile);
+        S_tile = AffSymOps<D>::apply(totalS, S_tile);
+        AffVecElem<D> eY = AffVecOps<D>::identity();
+        bool ok = true;
+        for (int k = ch.top - 1; k >= ch.bot; --k) {
+            Mat<D> Ssub, Skk;
+            invband_step(mat_load<D>(sLd + k * DD), mat_load<D>(sLs + k * DD), S, Ssub, Skk);
+            S = Skk;
+            const Mat<D> Ak = transition_from_cov(Skk, Ssub);
+            mat_store<D>(sLs + k * DD, Ak);
+            Mat<D> prec = -2.0 * mat_load<D>(sTd + k * DD);
+            prec = prec + Tmm(Ak, -1.0 * mat_load<D>(sTs + k * DD));
+            prec = mirror_lower(prec);
+            Mat<D> cov, cc;
+            cov_from_precision(prec, cov, cc, ok);
+            if (!ok) { report_not_pd(status, b * n + lo + k); ok = true; }
+            mat_store<D>(sTd + k * DD, cov);
+            mat_store<D>(sLd + k * DD, cc);
+            AffVecElem<D> s;
+            s.M = transpose(Ak);
+            s.v = vec_load<D>(sT1 + k * D);
+            eY = AffVecOps<D>::combine(eY, s);
+        }
+        AffVecElem<D> totalY;
+        const AffVecElem<D> exclY = block_exclusive_scan<AffVecOps<D>, T>(eY, wtotY, totalY);
+        if (MODE == SWEEP_SUMMARY2) {
+            seg_totY = AffVecOps<D>::combine(seg_totY, totalY);
+            continue;
+        }
+        Vec<D> y = AffVecOps<D>::apply(exclY, y_tile);
+        y_tile = AffVecOps<D>::apply(totalY, y_tile);
+        for (int k = ch.top - 1; k >= ch.bot; --k) {
+            y = vec_load<D>(sT1 + k * D) + Tmv(mat_load<D>(sLs + k * DD), y);
+            vec_store<D>(sT1 + k * D, mv(mat_load<D>(sTd + k * DD), y));
+        }
+        __syncthreads();
+        stage_out<T>(A + (b * N + lo) * DD, sLs, (int64_t)cnt * DD);
+        if (lo >= 1) {
+            stage_out<T>(bo + (b * N + lo - 1) * D, sT1, (int64_t)cnt * D);
+            stage_out<T>(cholQ + (b * N + lo - 1) * DD, sLd, (int64_t)cnt * DD);
+        } else {
+            stage_out<T>(mu0 + b * D, sT1, D);
+            stage_out<T>(cholP0 + b * DD, sLd, DD);
+            stage_out<T>(bo + b * N * D, sT1 + D, (int64_t)(cnt - 1) * D);
+            stage_out<T>(cholQ + b * N * DD, sLd + DD, (int64_t)(cnt - 1) * DD);
+        }
+    }
+    if (threadIdx.x == 0) {
+        if (MODE == SWEEP_SUMMARY) seg_elemS[b * nseg + seg] = seg_totS;
+        if (MODE == SWEEP_SUMMARY2) seg_elemY[b * nseg + seg] = seg_totY;
+    }
+}
+
+template <int D, int T, int L>
+constexpr size_t nat2ssm_tiled_smem() {
+    return (4 * (size_t)T * L * D * D + (size_t)T * L * D) * sizeof(double) +
+           (T / 32) * (sizeof(AffSymElem<D>) > sizeof(AffVecElem<D>) ? sizeof(AffSymElem<D>) : sizeof(AffVecElem<D>));
+}
+
+}  // namespace vdp

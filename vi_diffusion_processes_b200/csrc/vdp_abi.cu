@@ -3,7 +3,9 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "btd_kernels.cuh"
@@ -11,6 +13,7 @@
 #include "kl_kernels.cuh"
 #include "pointwise_kernels.cuh"
 #include "quad_core.cuh"
+#include "tile_sweeps.cuh"
 
 namespace vdp {
 
@@ -33,6 +36,13 @@ struct Arena {
     char* base;
     size_t size, used;
     Arena(void* p, size_t n) : base((char*)p), size(n), used(0) {}
+    void* take_bytes(size_t bytes) {
+        bytes = (bytes + 255) & ~size_t(255);
+        if (!base || used + bytes > size) return nullptr;
+        void* r = base + used;
+        used += bytes;
+        return r;
+    }
     double* take(size_t doubles) {
         size_t bytes = (doubles * sizeof(double) + 255) & ~size_t(255);
         if (used + bytes > size) return nullptr;
@@ -67,6 +77,8 @@ static inline void prof_mark(int phase, cudaStream_t st) {
 }
 
 }  // namespace vdp
+
+#include "vdp_sweeps.inl"
 
 using namespace vdp;
 
@@ -116,6 +128,11 @@ int vdp_btd_cholesky(const double* Kd, const double* Ks, double* Ld, double* Ls,
     VDP_REQUIRE(Kd && Ld && B >= 0 && n >= 1, "Kd, Ld, B, n");
     VDP_REQUIRE((Ks == nullptr) == (Ls == nullptr), "Ks and Ls must both be given or both be NULL");
     if (B == 0) return VDP_OK;
+    if (Ks && n >= 2 && use_tiled_sweeps(B, n - 1)) {
+        VDP_DISPATCH_D(D, { int rc = run_chol_tiled<kD>(Kd, Ks, 1.0, 1.0, Ld, Ls, B, n - 1, status,
+                                                        SegScratch(nullptr, 0), as_stream(stream)); if (rc) return rc; });
+        return VDP_OK;
+    }
     VDP_DISPATCH_D(D, (k_chol_fwd<kD><<<grid_for(B, kSeqBlock), kSeqBlock, 0, as_stream(stream)>>>(
                           Kd, Ks, 1.0, 1.0, Ld, Ls, B, n, status)));
     VDP_CHECK_LAUNCH();
@@ -126,6 +143,11 @@ int vdp_btd_inverse_band(const double* Ld, const double* Ls, double* Sd, double*
                          void* stream) {
     VDP_REQUIRE(Ld && Sd && B >= 0 && n >= 1, "Ld, Sd, B, n");
     if (B == 0) return VDP_OK;
+    if (Ls && n >= 2 && use_tiled_sweeps(B, n - 1)) {
+        VDP_DISPATCH_D(D, { int rc = run_invband_tiled<kD>(Ld, Ls, Sd, Ss, B, n - 1, SegScratch(nullptr, 0),
+                                                           as_stream(stream)); if (rc) return rc; });
+        return VDP_OK;
+    }
     VDP_DISPATCH_D(D, (k_invband_bwd<kD><<<grid_for(B, kSeqBlock), kSeqBlock, 0, as_stream(stream)>>>(
                           Ld, Ls, Sd, Ls ? Ss : nullptr, B, n)));
     VDP_CHECK_LAUNCH();

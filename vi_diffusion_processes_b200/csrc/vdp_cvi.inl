@@ -35,11 +35,12 @@ __global__ void k_elbo_combine(const double* __restrict__ ve, const double* __re
 // workspace carve-up shared by site_update and elbo
 struct CviWs {
     double *th1, *thd, *ths, *Ld, *Ls, *terms, *sc1, *scd;
+    void* seg;   // kSegScratchBytes of segment scratch for the tiled sweeps
 };
 static inline size_t cvi_ws_bytes(int64_t B, int64_t N, int D) {
     const size_t n = (size_t)B * (N + 1), t = (size_t)B * N, DD = (size_t)D * D;
     return padded(n * D) + padded(n * DD) + padded(t * DD) + padded(n * DD) + padded(t * DD) + padded(n) +
-           padded(n * D) + padded(n * DD);
+           padded(n * D) + padded(n * DD) + kSegScratchBytes;
 }
 static inline bool cvi_ws_take(void* ws, size_t bytes, int64_t B, int64_t N, int D, CviWs& w) {
     if (!ws) return false;
@@ -53,7 +54,8 @@ static inline bool cvi_ws_take(void* ws, size_t bytes, int64_t B, int64_t N, int
     w.terms = ar.take(n);
     w.sc1 = ar.take(n * D);
     w.scd = ar.take(n * DD);
-    return w.scd != nullptr;
+    w.seg = ar.take_bytes(kSegScratchBytes);
+    return w.seg != nullptr;
 }
 
 // (F): sites -> q as an SSM -> marginals.   variational_cvi_sde.py:161-192 + gauss_markov.py:107-117
@@ -69,11 +71,12 @@ static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t 
                                                                             N, p.n_obs);
         VDP_CHECK_LAUNCH();
     }
+    const SegScratch sc(w.seg, kSegScratchBytes);
     int rc = run_nat2ssm<D>(w.th1, w.thd, w.ths, p.qA, p.qb, p.qcholQ, p.qmu0, p.qcholP0, w.Ld, w.Ls, B, N, p.status,
-                            st);
+                            st, sc);
     if (rc) return rc;
     return run_marginals<D>(p.qA, p.qb, p.qcholQ, p.qmu0, p.qcholP0, p.fx_mus, p.fx_covs, w.Ld, w.Ls, B, N, p.status,
-                            st);
+                            st, sc);
 }
 
 template <int DRIFT, int D>

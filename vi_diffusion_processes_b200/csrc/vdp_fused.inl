@@ -18,9 +18,16 @@ static int launch_chol_nat(const double* thd, const double* ths, double* Ld, dou
 template <int D>
 static int run_nat2ssm(const double* th1, const double* thd, const double* ths, double* A, double* b, double* cholQ,
                        double* mu0, double* cholP0, double* Ld, double* Ls, int64_t B, int64_t N, int64_t* status,
-                       cudaStream_t st) {
+                       cudaStream_t st, SegScratch sc = SegScratch(nullptr, 0)) {
+    int rc;
+    if (use_tiled_sweeps(B, N)) {
+        prof_mark(VDP_PHASE_CHOL_FWD, st);
+        if ((rc = run_chol_tiled<D>(thd, ths, -2.0, -1.0, Ld, Ls, B, N, status, sc, st))) return rc;
+        prof_mark(VDP_PHASE_NAT2SSM_BWD, st);
+        return run_nat2ssm_bwd_tiled<D>(Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, status, sc, st);
+    }
     prof_mark(VDP_PHASE_CHOL_FWD, st);
-    int rc = launch_chol_nat<D>(thd, ths, Ld, Ls, B, N + 1, status, st);
+    rc = launch_chol_nat<D>(thd, ths, Ld, Ls, B, N + 1, status, st);
     if (rc) return rc;
     prof_mark(VDP_PHASE_NAT2SSM_BWD, st);
     k_nat2ssm_bwd<D><<<grid_for(B, kSeqBlock), kSeqBlock, 0, st>>>(Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0,
@@ -33,7 +40,16 @@ static int run_nat2ssm(const double* th1, const double* thd, const double* ths, 
 template <int D>
 static int run_marginals(const double* A, const double* b, const double* cholQ, const double* mu0,
                          const double* cholP0, double* m, double* Sd, double* Ld, double* Ls, int64_t B, int64_t N,
-                         int64_t* status, cudaStream_t st) {
+                         int64_t* status, cudaStream_t st, SegScratch sc = SegScratch(nullptr, 0)) {
+    if (use_tiled_sweeps(B, N)) {
+        int rc;
+        prof_mark(VDP_PHASE_MARG_FWD, st);
+        if ((rc = run_marg_fwd_tiled<D>(A, b, cholQ, mu0, cholP0, m, Ld, Ls, B, N, status, sc, st))) return rc;
+        prof_mark(VDP_PHASE_INVBAND_BWD, st);
+        if ((rc = run_invband_tiled<D>(Ld, Ls, Sd, nullptr, B, N, sc, st))) return rc;
+        prof_mark(VDP_PHASE_END, st);
+        return VDP_OK;
+    }
     prof_mark(VDP_PHASE_MARG_FWD, st);
     k_marg_fwd<D><<<grid_for(B, kSeqBlock), kSeqBlock, 0, st>>>(A, b, cholQ, mu0, cholP0, m, Ld, Ls, B, N, status);
     VDP_CHECK_LAUNCH();
@@ -97,7 +113,7 @@ int vdp_ssm_to_naturals(const double* A, const double* b, const double* cholQ, c
 }
 
 size_t vdp_naturals_to_ssm_workspace(int64_t B, int64_t N, int D) {
-    return padded((size_t)B * (N + 1) * D * D) + padded((size_t)B * N * D * D);
+    return padded((size_t)B * (N + 1) * D * D) + padded((size_t)B * N * D * D) + kSegScratchBytes;
 }
 
 int vdp_naturals_to_ssm(const double* th1, const double* thd, const double* ths, double* A, double* b,
@@ -109,8 +125,9 @@ int vdp_naturals_to_ssm(const double* th1, const double* thd, const double* ths,
     double* Ld = ar.take((size_t)B * (N + 1) * D * D);
     double* Ls = ar.take((size_t)B * N * D * D);
     if (!workspace || !Ld || !Ls) { set_error("workspace too small"); return VDP_E_WORKSPACE; }
+    SegScratch sc(ar.take_bytes(kSegScratchBytes), kSegScratchBytes);
     VDP_DISPATCH_D(D, { int rc = run_nat2ssm<kD>(th1, thd, ths, A, b, cholQ, mu0, cholP0, Ld, Ls, B, N, status,
-                                                 as_stream(stream)); if (rc) return rc; });
+                                                 as_stream(stream), sc); if (rc) return rc; });
     return VDP_OK;
 }
 
@@ -125,8 +142,9 @@ int vdp_ssm_marginals(const double* A, const double* b, const double* cholQ, con
     double* Ld = ar.take((size_t)B * (N + 1) * D * D);
     double* Ls = ar.take((size_t)B * N * D * D);
     if (!workspace || !Ld || !Ls) { set_error("workspace too small"); return VDP_E_WORKSPACE; }
+    SegScratch sc(ar.take_bytes(kSegScratchBytes), kSegScratchBytes);
     VDP_DISPATCH_D(D, { int rc = run_marginals<kD>(A, b, cholQ, mu0, cholP0, m, Sd, Ld, Ls, B, N, status,
-                                                   as_stream(stream)); if (rc) return rc; });
+                                                   as_stream(stream), sc); if (rc) return rc; });
     return VDP_OK;
 }
 

@@ -1,0 +1,220 @@
+// Host-side launch logic of the four time sweeps: choice between the thread-per-sequence kernels
+// (btd_kernels.cuh; many short sequences) and the parallel-in-time tiled kernels (tile_sweeps.cuh), and
+// the segment plan of the latter.  Included by vdp_abi.cu before vdp_fused.inl.
+
+namespace vdp {
+
+// tile shapes: T chunks of L steps; L odd (conflict-free chunk stride in shared memory)
+template <int D> struct TileCfg;
+template <> struct TileCfg<1> { static constexpr int T = 128, Lc = 17, Li = 17, Lm = 9, Ln = 9; };
+template <> struct TileCfg<2> { static constexpr int T = 64, Lc = 9, Li = 9, Lm = 5, Ln = 5; };
+template <> struct TileCfg<3> { static constexpr int T = 64, Lc = 5, Li = 5, Lm = 3, Ln = 3; };
+
+constexpr int64_t kTargetBlocks = 148 * 4;     // CTAs wanted in flight before sequences are split in time
+constexpr int64_t kMaxSegTotal = 4096;         // bound on B * nseg (sizes the segment scratch)
+constexpr size_t kSegScratchBytes = 8u << 20;  // part of every fused-level workspace
+
+struct SegScratch {
+    char* base;
+    size_t size, used;
+    SegScratch(void* p, size_t n) : base((char*)p), size(p ? n : 0), used(0) {}
+    template <class X> X* take(size_t count) {
+        const size_t bytes = (count * sizeof(X) + 255) & ~size_t(255);
+        if (used + bytes > size) return nullptr;
+        X* r = reinterpret_cast<X*>(base + used);
+        used += bytes;
+        return r;
+    }
+};
+
+struct SegPlan {
+    int nseg;
+    int64_t seg_len;
+};
+
+static inline int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return (e && *e) ? atoi(e) : dflt;
+}
+
+// VDP_SWEEPS = seq | tiled overrides the heuristic (tests run both paths)
+static inline bool use_tiled_sweeps(int64_t B, int64_t N) {
+    const char* e = getenv("VDP_SWEEPS");
+    if (e && !strcmp(e, "seq")) return false;
+    if (e && !strcmp(e, "tiled")) return N >= 1;
+    return N >= 512 || (B < 148 * 64 && N >= 32);
+}
+
+static inline SegPlan plan_segments(int64_t B, int64_t N, int tile_steps, bool have_scratch) {
+    int64_t want = 1;
+    const int forced = env_int("VDP_NSEG", 0);
+    if (forced > 0) {
+        want = forced;
+    } else if (B < kTargetBlocks) {
+        want = (kTargetBlocks + B - 1) / B;
+        want = std::min<int64_t>(want, std::max<int64_t>(1, N / tile_steps));   // >= one full tile per segment
+    }
+    want = std::min<int64_t>(want, std::max<int64_t>(1, kMaxSegTotal / std::max<int64_t>(B, 1)));
+    want = std::min<int64_t>(want, N);
+    if (!have_scratch) want = 1;
+    SegPlan p;
+    p.seg_len = (N + want - 1) / want;
+    p.nseg = (int)((N + p.seg_len - 1) / p.seg_len);
+    return p;
+}
+
+template <class K>
+static inline int allow_smem(K kernel, size_t bytes) {
+    if (bytes > 48 * 1024)
+        VDP_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return VDP_OK;
+}
+
+template <class Ops>
+static inline int launch_seg_scan(const typename Ops::Elem* el, const typename Ops::State* init,
+                                  typename Ops::State* carry, int64_t B, int nseg, int reverse, cudaStream_t st) {
+    k_seg_scan<Ops><<<grid_for(B, 32), 32, 0, st>>>(el, init, carry, B, nseg, reverse);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+// ---- cholesky_band ---------------------------------------------------------------------------------
+template <int D>
+static int run_chol_tiled(const double* Xd, const double* Xs, double scaleD, double scaleS, double* Ld, double* Ls,
+                          int64_t B, int64_t N, int64_t* status, SegScratch sc, cudaStream_t st) {
+    using C = TileCfg<D>;
+    constexpr size_t smem = chol_tiled_smem<D, C::T, C::Lc>();
+    const SegPlan pl = plan_segments(B, N, C::T * C::Lc, sc.size > 0);
+    const unsigned grid = (unsigned)(B * pl.nseg);
+    int rc;
+    if ((rc = allow_smem(k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL>, smem))) return rc;
+    if (pl.nseg == 1) {
+        k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL><<<grid, C::T, smem, st>>>(Xd, Xs, scaleD, scaleS, Ld, Ls, B, N, 1,
+                                                                           pl.seg_len, nullptr, nullptr, nullptr, status);
+        VDP_CHECK_LAUNCH();
+        return VDP_OK;
+    }
+    Mat<D>* carry = sc.take<Mat<D>>((size_t)B * pl.nseg);
+    Mat<D>* init = sc.take<Mat<D>>((size_t)B);
+    SchurElem<D>* el = sc.take<SchurElem<D>>((size_t)B * pl.nseg);
+    if (!el) { set_error("segment scratch too small"); return VDP_E_WORKSPACE; }
+    if ((rc = allow_smem(k_chol_tiled<D, C::T, C::Lc, SWEEP_SUMMARY>, smem))) return rc;
+    k_chol_tiled<D, C::T, C::Lc, SWEEP_SUMMARY><<<grid, C::T, smem, st>>>(Xd, Xs, scaleD, scaleS, Ld, Ls, B, N, pl.nseg,
+                                                                          pl.seg_len, nullptr, init, el, status);
+    VDP_CHECK_LAUNCH();
+    if ((rc = launch_seg_scan<SchurOps<D>>(el, init, carry, B, pl.nseg, 0, st))) return rc;
+    k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL><<<grid, C::T, smem, st>>>(Xd, Xs, scaleD, scaleS, Ld, Ls, B, N, pl.nseg,
+                                                                       pl.seg_len, carry, nullptr, nullptr, status);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+// ---- inverse_from_cholesky_band --------------------------------------------------------------------
+template <int D>
+static int run_invband_tiled(const double* Ld, const double* Ls, double* Sd, double* Ss, int64_t B, int64_t N,
+                             SegScratch sc, cudaStream_t st) {
+    using C = TileCfg<D>;
+    constexpr size_t smem = invband_tiled_smem<D, C::T, C::Li>();
+    const SegPlan pl = plan_segments(B, N, C::T * C::Li, sc.size > 0);
+    const unsigned grid = (unsigned)(B * pl.nseg);
+    int rc;
+    if ((rc = allow_smem(k_invband_tiled<D, C::T, C::Li, SWEEP_FULL>, smem))) return rc;
+    if (pl.nseg == 1) {
+        k_invband_tiled<D, C::T, C::Li, SWEEP_FULL><<<grid, C::T, smem, st>>>(Ld, Ls, Sd, Ss, B, N, 1, pl.seg_len,
+                                                                              nullptr, nullptr, nullptr);
+        VDP_CHECK_LAUNCH();
+        return VDP_OK;
+    }
+    Mat<D>* carry = sc.take<Mat<D>>((size_t)B * pl.nseg);
+    Mat<D>* init = sc.take<Mat<D>>((size_t)B);
+    AffSymElem<D>* el = sc.take<AffSymElem<D>>((size_t)B * pl.nseg);
+    if (!el) { set_error("segment scratch too small"); return VDP_E_WORKSPACE; }
+    if ((rc = allow_smem(k_invband_tiled<D, C::T, C::Li, SWEEP_SUMMARY>, smem))) return rc;
+    k_invband_tiled<D, C::T, C::Li, SWEEP_SUMMARY><<<grid, C::T, smem, st>>>(Ld, Ls, Sd, Ss, B, N, pl.nseg, pl.seg_len,
+                                                                             nullptr, init, el);
+    VDP_CHECK_LAUNCH();
+    if ((rc = launch_seg_scan<AffSymOps<D>>(el, init, carry, B, pl.nseg, 1, st))) return rc;
+    k_invband_tiled<D, C::T, C::Li, SWEEP_FULL><<<grid, C::T, smem, st>>>(Ld, Ls, Sd, Ss, B, N, pl.nseg, pl.seg_len,
+                                                                          carry, nullptr, nullptr);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+// ---- naturals_to_ssm_params, backward half ---------------------------------------------------------
+template <int D>
+static int run_nat2ssm_bwd_tiled(const double* Ld, const double* Ls, const double* th1, const double* thd,
+                                 const double* ths, double* A, double* b, double* cholQ, double* mu0, double* cholP0,
+                                 int64_t B, int64_t N, int64_t* status, SegScratch sc, cudaStream_t st) {
+    using C = TileCfg<D>;
+    constexpr size_t smem = nat2ssm_tiled_smem<D, C::T, C::Ln>();
+    const SegPlan pl = plan_segments(B, N, C::T * C::Ln, sc.size > 0);
+    const unsigned grid = (unsigned)(B * pl.nseg);
+    int rc;
+    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL>, smem))) return rc;
+    if (pl.nseg == 1) {
+        k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL><<<grid, C::T, smem, st>>>(
+            Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, 1, pl.seg_len, nullptr, nullptr, nullptr, nullptr,
+            nullptr, nullptr, status);
+        VDP_CHECK_LAUNCH();
+        return VDP_OK;
+    }
+    Mat<D>* carryS = sc.take<Mat<D>>((size_t)B * pl.nseg);
+    Vec<D>* carryY = sc.take<Vec<D>>((size_t)B * pl.nseg);
+    Mat<D>* initS = sc.take<Mat<D>>((size_t)B);
+    Vec<D>* initY = sc.take<Vec<D>>((size_t)B);
+    AffSymElem<D>* elS = sc.take<AffSymElem<D>>((size_t)B * pl.nseg);
+    AffVecElem<D>* elY = sc.take<AffVecElem<D>>((size_t)B * pl.nseg);
+    if (!elY) { set_error("segment scratch too small"); return VDP_E_WORKSPACE; }
+    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY>, smem))) return rc;
+    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2>, smem))) return rc;
+    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY><<<grid, C::T, smem, st>>>(
+        Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, pl.nseg, pl.seg_len, nullptr, nullptr, initS, initY, elS,
+        elY, status);
+    VDP_CHECK_LAUNCH();
+    if ((rc = launch_seg_scan<AffSymOps<D>>(elS, initS, carryS, B, pl.nseg, 1, st))) return rc;
+    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2><<<grid, C::T, smem, st>>>(
+        Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, pl.nseg, pl.seg_len, carryS, nullptr, initS, initY, elS,
+        elY, status);
+    VDP_CHECK_LAUNCH();
+    if ((rc = launch_seg_scan<AffVecOps<D>>(elY, initY, carryY, B, pl.nseg, 1, st))) return rc;
+    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL><<<grid, C::T, smem, st>>>(
+        Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, pl.nseg, pl.seg_len, carryS, carryY, nullptr, nullptr,
+        nullptr, nullptr, status);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+// ---- marginal means + Cholesky of the rebuilt precision --------------------------------------------
+template <int D>
+static int run_marg_fwd_tiled(const double* A, const double* b, const double* cholQ, const double* mu0,
+                              const double* cholP0, double* m, double* Ld, double* Ls, int64_t B, int64_t N,
+                              int64_t* status, SegScratch sc, cudaStream_t st) {
+    using C = TileCfg<D>;
+    using Ops = MargOps<D>;
+    constexpr size_t smem = marg_tiled_smem<D, C::T, C::Lm>();
+    const SegPlan pl = plan_segments(B, N, C::T * C::Lm, sc.size > 0);
+    const unsigned grid = (unsigned)(B * pl.nseg);
+    int rc;
+    if ((rc = allow_smem(k_marg_tiled<D, C::T, C::Lm, SWEEP_FULL>, smem))) return rc;
+    if (pl.nseg == 1) {
+        k_marg_tiled<D, C::T, C::Lm, SWEEP_FULL><<<grid, C::T, smem, st>>>(A, b, cholQ, mu0, cholP0, m, Ld, Ls, B, N, 1,
+                                                                           pl.seg_len, nullptr, nullptr, nullptr, status);
+        VDP_CHECK_LAUNCH();
+        return VDP_OK;
+    }
+    typename Ops::State* carry = sc.take<typename Ops::State>((size_t)B * pl.nseg);
+    typename Ops::State* init = sc.take<typename Ops::State>((size_t)B);
+    typename Ops::Elem* el = sc.take<typename Ops::Elem>((size_t)B * pl.nseg);
+    if (!el) { set_error("segment scratch too small"); return VDP_E_WORKSPACE; }
+    if ((rc = allow_smem(k_marg_tiled<D, C::T, C::Lm, SWEEP_SUMMARY>, smem))) return rc;
+    k_marg_tiled<D, C::T, C::Lm, SWEEP_SUMMARY><<<grid, C::T, smem, st>>>(A, b, cholQ, mu0, cholP0, m, Ld, Ls, B, N,
+                                                                          pl.nseg, pl.seg_len, nullptr, init, el, status);
+    VDP_CHECK_LAUNCH();
+    if ((rc = launch_seg_scan<Ops>(el, init, carry, B, pl.nseg, 0, st))) return rc;
+    k_marg_tiled<D, C::T, C::Lm, SWEEP_FULL><<<grid, C::T, smem, st>>>(A, b, cholQ, mu0, cholP0, m, Ld, Ls, B, N, pl.nseg,
+                                                                       pl.seg_len, carry, nullptr, nullptr, status);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+}  // namespace vdp
