@@ -84,6 +84,51 @@ struct SchurOps {
     }
 };
 
+// D = 1: the same maps with one reciprocal per composition instead of chol + two triangular solves
+template <>
+struct SchurOps<1> {
+    using Elem = SchurElem<1>;
+    using State = Mat<1>;
+    __device__ __forceinline__ static Elem identity() {
+        Elem e;
+        e.La.a[0] = 0.0; e.Lab.a[0] = 0.0; e.Lb.a[0] = 0.0;
+        e.id = 1;
+        return e;
+    }
+    __device__ __forceinline__ static Elem step(const Mat<1>& Ks, const Mat<1>& Kd_next) {
+        Elem e;
+        e.La.a[0] = 0.0; e.Lab = Ks; e.Lb = Kd_next;
+        e.id = 0;
+        return e;
+    }
+    __device__ __forceinline__ static Elem combine(const Elem& e1, const Elem& e2) {
+        if (e1.id) return e2;
+        if (e2.id) return e1;
+        const double r = 1.0 / (e1.Lb.a[0] + e2.La.a[0]);
+        const double ur = e1.Lab.a[0] * r, v = e2.Lab.a[0];
+        Elem o;
+        o.La.a[0] = e1.La.a[0] - ur * e1.Lab.a[0];
+        o.Lab.a[0] = ur * v;
+        o.Lb.a[0] = e2.Lb.a[0] - (v * r) * v;
+        o.id = 0;
+        return o;
+    }
+    __device__ __forceinline__ static void push(Elem& e, const Mat<1>& Ks, const Mat<1>& Kd_next) {
+        if (e.id) { e = step(Ks, Kd_next); return; }
+        const double r = 1.0 / e.Lb.a[0];
+        const double ur = e.Lab.a[0] * r, v = Ks.a[0];
+        e.La.a[0] = e.La.a[0] - ur * e.Lab.a[0];
+        e.Lab.a[0] = ur * v;
+        e.Lb.a[0] = Kd_next.a[0] - (v * r) * v;
+    }
+    __device__ __forceinline__ static State apply(const Elem& e, const State& S) {
+        if (e.id) return S;
+        State o;
+        o.a[0] = e.Lb.a[0] - (e.Lab.a[0] / (S.a[0] + e.La.a[0])) * e.Lab.a[0];
+        return o;
+    }
+};
+
 // ---------------------------------------------------------------------------------------------------
 template <int D>
 struct AffSymElem {

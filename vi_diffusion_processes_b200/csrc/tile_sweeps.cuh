@@ -23,14 +23,26 @@ namespace vdp {
 
 enum { SWEEP_FULL = 0, SWEEP_SUMMARY = 1, SWEEP_SUMMARY2 = 2 };
 
-template <int T>
-__device__ __forceinline__ void stage_in(double* __restrict__ s, const double* __restrict__ g, int64_t count,
-                                         double scale) {
-    for (int64_t i = threadIdx.x; i < count; i += T) s[i] = scale * g[i];
+// Tile staging: global -> shared with 8-byte cp.async (LDGSTS), so that every load of a tile is in flight
+// at once and no register staging limits the memory-level parallelism; any 8-byte alignment works.
+__device__ __forceinline__ void cp_async8(double* s, const double* g) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(s);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(sa), "l"(g));
 }
 template <int T>
 __device__ __forceinline__ void stage_in(double* __restrict__ s, const double* __restrict__ g, int64_t count) {
-    for (int64_t i = threadIdx.x; i < count; i += T) s[i] = g[i];
+    for (int64_t i = threadIdx.x; i < count; i += T) cp_async8(s + i, g + i);
+}
+// wait for this thread's copies (a __syncthreads() must follow before other threads' elements are read)
+__device__ __forceinline__ void stage_wait() {
+    asm volatile("cp.async.commit_group;\n" ::);
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+// scale the elements this thread staged itself (call between stage_wait and the barrier)
+template <int T>
+__device__ __forceinline__ void stage_scale(double* __restrict__ s, int64_t count, double scale) {
+    if (scale == 1.0) return;
+    for (int64_t i = threadIdx.x; i < count; i += T) s[i] = scale * s[i];
 }
 template <int T>
 __device__ __forceinline__ void stage_out(double* __restrict__ g, const double* __restrict__ s, int64_t count) {
@@ -135,8 +147,11 @@ k_chol_tiled(const double* __restrict__ Xd, const double* __restrict__ Xs, doubl
     for (int64_t tk = t0; tk < t1; tk += TL) {
         const int cnt = (int)min((int64_t)TL, t1 - tk);
         __syncthreads();
-        stage_in<T>(sKd, xd + tk * DD, (int64_t)(cnt + 1) * DD, scaleD);
-        stage_in<T>(sKs, xs + tk * DD, (int64_t)cnt * DD, scaleS);
+        stage_in<T>(sKd, xd + tk * DD, (int64_t)(cnt + 1) * DD);
+        stage_in<T>(sKs, xs + tk * DD, (int64_t)cnt * DD);
+        stage_wait();
+        stage_scale<T>(sKd, (int64_t)(cnt + 1) * DD, scaleD);
+        stage_scale<T>(sKs, (int64_t)cnt * DD, scaleS);
         __syncthreads();
         if (seg == 0 && tk == 0) {
             S_tile = mat_load<D>(sKd);
@@ -212,6 +227,7 @@ k_marg_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
         }
         stage_in<T>(sA, A + (b * N + tk) * DD, (int64_t)(cnt + (halo_has_next ? 1 : 0)) * DD);
         stage_in<T>(sb, bo + (b * N + tk) * D, (int64_t)cnt * D);
+        stage_wait();
         __syncthreads();
         // phase 0: precision blocks of nodes [0, cnt]
         for (int i = threadIdx.x; i <= cnt; i += T) {
@@ -334,6 +350,7 @@ k_invband_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, do
         __syncthreads();
         stage_in<T>(sLd, Ld + (b * (N + 1) + lo) * DD, (int64_t)cnt * DD);
         stage_in<T>(sLs, Ls + (b * N + lo) * DD, (int64_t)cnt * DD);
+        stage_wait();
         __syncthreads();
         const BwdChunk ch = bwd_chunk<L>(cnt);
         const AffSymElem<D> e = invband_tile_summary<D>(sLd, sLs, ch);
@@ -428,6 +445,7 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
             stage_in<T>(sTs, ths + (b * N + lo) * DD, (int64_t)cnt * DD);
             stage_in<T>(sT1, th1 + (b * n + lo) * D, (int64_t)cnt * D);
         }
+        stage_wait();
         __syncthreads();
         const BwdChunk ch = bwd_chunk<L>(cnt);
         const AffSymElem<D> eS = invband_tile_summary<D>(sLd, sLs, ch);
