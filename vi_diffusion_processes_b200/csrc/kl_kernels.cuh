@@ -29,12 +29,88 @@ struct KlTermOut {
     Mat<D> ges;           // d term / d eta_s[k]
 };
 
+// D = 1, one thread per transition: the same term with every block a scalar.  Per-step invariants are
+// hoisted out of the node loop, pi^(-1/2) and sqrt(2) are factored out of the sums, and each of the
+// three divisors (chol S_k, chol Q_c, chol Q_p) is inverted once (3 sqrt + 3 div + 1 log per step
+// instead of ~20 div/sqrt/log).  Results differ from the generic path in the last bits only.
+template <int DRIFT, int H>
+__device__ __forceinline__ void kl_term_scalar(const DriftParams& P, double Qp, double dt, double pi_factor,
+                                               double mk, double mn, double edk, double edn, double esk,
+                                               KlTermOut<1>& out, bool& ok) {
+    // expectations_to_ssm_params (ssm_gaussian_transformations.py:93-178)
+    const double Sk = edk - mk * mk;
+    const double Sn = edn - mn * mn;
+    const double Cs = esk - mk * mn;
+    if (!(Sk > 0.0)) ok = false;
+    const double LS = sqrt(Sk);
+    const double iLS = 1.0 / LS;
+    const double A = (Cs * iLS) * iLS;
+    const double b = mn - A * mk;
+    const double Qc = Sn - A * (Sk * A);
+    if (!(Qc > 0.0) || !(Qp > 0.0)) ok = false;
+    const double LQ = sqrt(Qc);
+    const double iLQ = 1.0 / LQ;
+    const double Qq = LQ * LQ;
+    const double cQp = sqrt(Qp);
+    const double iQp = 1.0 / cQp;
+    const double Qpinv = iQp * iQp;
+    // C = -(logdet Qq - logdet Qp) - 1 + Qp^-1 Qq   (sde_utils.py:317-330); chol(Qq) = LQ exactly
+    const double Cterm = -2.0 * log(LQ * iQp) - 1.0 + Qpinv * Qq;
+    const double sL = 1.4142135623730951 * LS;
+    double quad = 0.0, gb = 0.0, gmq = 0.0, gA = 0.0, lsb = 0.0;
+#pragma unroll
+    for (int p = 0; p < H; ++p) {
+        const double xi = gh_x<H>(p), w = gh_w<H>(p);
+        Vec<1> X, f;
+        Mat<1> J;
+        X(0) = fma(sL, xi, mk);
+        Drift<DRIFT, 1>::eval(P, X, f, J);
+        const double d = (X(0) + dt * f(0)) - (A * X(0) + b);
+        const double rb = w * (Qpinv * d);
+        quad = fma(rb, d, quad);
+        const double Xb = ((1.0 + dt * J(0, 0)) - A) * rb;
+        gb -= rb;
+        gmq += Xb;
+        gA = fma(-rb, X(0), gA);
+        lsb = fma(Xb, xi, lsb);
+    }
+    quad *= pi_factor;
+    gb *= pi_factor;
+    gmq *= pi_factor;
+    gA *= pi_factor;
+    lsb *= 1.4142135623730951 * pi_factor;
+    out.value = 0.5 * (quad + Cterm);
+    // reverse through the pointwise algebra
+    double Lgm = gmq;
+    double LgS = 0.5 * lsb * iLS;                 // adjoint of chol(S_k)
+    const double gQc = 0.5 * (Qpinv - iLQ * iLQ);
+    double Rgm = gb;                              // b = m_{k+1} - A m_k
+    gA -= gb * mk;
+    Lgm -= A * gb;
+    const double RgS = gQc;                       // Qc = S_{k+1} - A S_k A
+    gA -= 2.0 * (gQc * (A * Sk));
+    LgS -= A * (gQc * A);
+    const double gC = (gA * iLS) * iLS;           // A = C / S_k
+    LgS -= gC * A;
+    Lgm -= gC * mn;                               // C = eta_s - m_k m_{k+1}
+    Rgm -= gC * mk;
+    out.ges(0, 0) = gC;
+    out.left.gm(0) = Lgm;
+    out.left.gS(0, 0) = LgS;
+    out.right.gm(0) = Rgm;
+    out.right.gS(0, 0) = RgS;
+}
+
 // One transition term.  Inputs are the expectation parameters rebuilt from (A_q, m, S) exactly as
 // ssm_to_expectations does (ssm_gaussian_transformations.py:32-89).
 template <int DRIFT, int D, int H, int G>
 __device__ __forceinline__ void kl_term(const DriftParams& P, const Mat<D>& Qp, double dt, double pi_factor,
                                         const Vec<D>& e1k, const Vec<D>& e1n, const Mat<D>& edk, const Mat<D>& edn,
                                         const Mat<D>& esk, int lane, KlTermOut<D>& out, bool& ok) {
+    if constexpr (D == 1 && G == 1) {
+        kl_term_scalar<DRIFT, H>(P, Qp(0, 0), dt, pi_factor, e1k(0), e1n(0), edk(0, 0), edn(0, 0), esk(0, 0), out, ok);
+        return;
+    }
     ExpToSsm<D> r;
     exp_to_ssm_step(e1k, e1n, edk, edn, esk, r, ok);
     const Mat<D> Qq = mmT(r.LQ, r.LQ);
@@ -52,34 +128,6 @@ __device__ __forceinline__ void kl_term(const DriftParams& P, const Mat<D>& Qp, 
     double quad = 0.0;
     Vec<D> gb = vec_zero<D>(), gmq = vec_zero<D>();
     Mat<D> gA = mat_zero<D>(), LSb = mat_zero<D>();
-    if constexpr (D == 1 && G == 1) {
-        // scalar fast path: per-step invariants hoisted, pi^(-1/2) and sqrt(2) factored out of the sums
-        // (the sums differ from the generic path in the last bits only; ~20 instead of ~30 FP64 ops per node)
-        const double LS1 = r.LS(0, 0), A1 = r.A(0, 0), b1 = r.b(0), m1 = r.mk(0), qi = Qpinv(0, 0);
-        const double sL = 1.4142135623730951 * LS1;
-        double quad_ = 0.0, gb_ = 0.0, gmq_ = 0.0, gA_ = 0.0, lsb_ = 0.0;
-#pragma unroll
-        for (int p = 0; p < H; ++p) {
-            const double xi = gh_x<H>(p), w = gh_w<H>(p);
-            Vec<1> X, f;
-            Mat<1> J;
-            X(0) = fma(sL, xi, m1);
-            Drift<DRIFT, 1>::eval(P, X, f, J);
-            const double d = (X(0) + dt * f(0)) - (A1 * X(0) + b1);
-            const double rb = w * (qi * d);
-            quad_ = fma(rb, d, quad_);
-            const double Xb = ((1.0 + dt * J(0, 0)) - A1) * rb;
-            gb_ -= rb;
-            gmq_ += Xb;
-            gA_ = fma(-rb, X(0), gA_);
-            lsb_ = fma(Xb, xi, lsb_);
-        }
-        quad = pi_factor * quad_;
-        gb(0) = pi_factor * gb_;
-        gmq(0) = pi_factor * gmq_;
-        gA(0, 0) = pi_factor * gA_;
-        LSb(0, 0) = (1.4142135623730951 * pi_factor) * lsb_;
-    } else {
     constexpr int NP = NodeCount<H, D>::value;
     for (int p = lane; p < NP; p += G) {
         Vec<D> xi, f;
@@ -114,7 +162,6 @@ __device__ __forceinline__ void kl_term(const DriftParams& P, const Mat<D>& Qp, 
                 if (j <= i) LSb(i, j) += 1.4142135623730951 * (Xb(i) * xi(j));
             }
         }
-    }
     }
     quad = group_sum<G>(quad);
     group_sum<G>(gb);
@@ -275,15 +322,28 @@ __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
 #pragma unroll
     for (int e = 0; e < DD; ++e) Qq.a[e] = cq.a[e] * cq.a[e];
     const Mat<D> Qp = dt * q;
-    const Mat<D> cQp = chol(Qp, ok);
-    const Mat<D> Qpinv = chol_inverse(cQp);
-    const Mat<D> cQq = chol(Qq, ok);   // tf.linalg.logdet reads the lower triangle
-    double tr = Qpinv(0, 0) * Qq(0, 0);
-#pragma unroll
-    for (int e = 1; e < D; ++e) tr += Qpinv(e, e) * Qq(e, e);
-    const double Cterm = -(logdet_from_chol(cQq) - logdet_from_chol(cQp)) - (double)D + tr;
     const Vec<D> mk = vec_load<D>(m + i * D);
-    const Mat<D> LS = chol(mat_load<D>(Sd + i * DD), ok);
+    Mat<D> cQp, Qpinv, LS;
+    double Cterm;
+    if constexpr (D == 1 && G == 1) {
+        // scalar: one reciprocal, one log (chol(cq^2) = |cq| exactly)
+        const double Sk = Sd[i];
+        if (!(Qp(0, 0) > 0.0) || !(Sk > 0.0) || !(Qq(0, 0) > 0.0)) ok = false;
+        cQp(0, 0) = sqrt(Qp(0, 0));
+        const double iQp = 1.0 / cQp(0, 0);
+        Qpinv(0, 0) = iQp * iQp;
+        Cterm = -2.0 * log(fabs(cq(0, 0)) * iQp) - 1.0 + Qpinv(0, 0) * Qq(0, 0);
+        LS(0, 0) = sqrt(Sk);
+    } else {
+        cQp = chol(Qp, ok);
+        Qpinv = chol_inverse(cQp);
+        const Mat<D> cQq = chol(Qq, ok);   // tf.linalg.logdet reads the lower triangle
+        double tr = Qpinv(0, 0) * Qq(0, 0);
+#pragma unroll
+        for (int e = 1; e < D; ++e) tr += Qpinv(e, e) * Qq(e, e);
+        Cterm = -(logdet_from_chol(cQq) - logdet_from_chol(cQp)) - (double)D + tr;
+        LS = chol(mat_load<D>(Sd + i * DD), ok);
+    }
     double quad = 0.0;
     if constexpr (D == 1 && G == 1) {
         const double sL = 1.4142135623730951 * LS(0, 0), m1 = mk(0), A1 = Ak(0, 0), b1 = bk(0), qi = Qpinv(0, 0);
