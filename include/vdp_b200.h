@@ -184,6 +184,52 @@ int vdp_cvi_site_update(const vdp_cvi_problem* problem_host, void* stream);
 int vdp_cvi_elbo(const vdp_cvi_problem* problem_host, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * VDP: VariationalMarkovGP (markovflow/models/vi_sde.py:63-482), batched over B sequences.
+ *   vdp_vgp_forward_pass               forward_pass              vi_sde.py:171-204  -> m, S
+ *   vdp_vgp_update_lagrange            update_lagrange           vi_sde.py:289-347  (m, S) -> lam, psi
+ *                                      (+ _grad_E_sde :206-240, _jump_conditions :262-287)
+ *   vdp_vgp_update_param               update_param              vi_sde.py:377-414  (m, S, lam, psi) -> A, b
+ *   vdp_vgp_update_initial_statistics  update_initial_statistics vi_sde.py:242-260  -> q_mean, q_chol
+ *   vdp_vgp_elbo                       elbo                      vi_sde.py:436-455  (m, S current) -> elbo
+ *   vdp_vgp_sweep                      one iteration of VIMarkovGPTrainer.perform_inference
+ *                                      (docs/diffusion_processes/vi_markov_gp_trainer.py:62-73)
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct vdp_vgp_problem {
+    int64_t B, N, n_obs;
+    int32_t D, drift_id;
+    double drift_params[16];
+    double q[9];               /* spectral density, row-major D x D */
+    double dt;                 /* float(grid[1] - grid[0]) */
+    double x0_mu[3], x0_cov[9];/* prior on the initial state */
+    double lik_chol[9];        /* Cholesky factor of the Gaussian likelihood covariance */
+    double lr, x0_lr;          /* damping of update_param / update_initial_statistics */
+    const double* time_grid;   /* [N+1] */
+    double *A, *b;             /* variational drift  [B,N,D,D] [B,N,D]   (in/out) */
+    double *lam, *psi;         /* Lagrange multipliers [B,N,D] [B,N,D,D] (in/out) */
+    double *q_mean, *q_chol;   /* q(x0): [B,D] [B,D,D]                   (in/out) */
+    const int64_t* obs_idx;    /* [B,n_obs] */
+    const double* obs_y;       /* [B,n_obs,D] */
+    double *m, *S;             /* marginals [B,N+1,D] [B,N+1,D,D] */
+    double* elbo;              /* [B] */
+    void* workspace;
+    size_t workspace_bytes;    /* >= vdp_vgp_workspace(B,N,D,n_obs) */
+    int64_t* status;
+    int32_t flags;             /* VDP_VGP_* */
+    int32_t reserved;
+} vdp_vgp_problem;
+
+#define VDP_VGP_STABILIZE 1    /* stabilize_system=True (clips of vi_sde.py:184-197, 314-323, 393-397) */
+#define VDP_VGP_UPDATE_X0 2    /* vdp_vgp_sweep also runs update_initial_statistics */
+
+size_t vdp_vgp_workspace(int64_t B, int64_t N, int D, int64_t n_obs);
+int vdp_vgp_forward_pass(const vdp_vgp_problem* problem_host, void* stream);
+int vdp_vgp_update_lagrange(const vdp_vgp_problem* problem_host, void* stream);
+int vdp_vgp_update_param(const vdp_vgp_problem* problem_host, void* stream);
+int vdp_vgp_update_initial_statistics(const vdp_vgp_problem* problem_host, void* stream);
+int vdp_vgp_elbo(const vdp_vgp_problem* problem_host, void* stream);
+int vdp_vgp_sweep(const vdp_vgp_problem* problem_host, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * diagnostics: per-phase device time of the fused pipelines (CUDA events on the launching stream).
  * vdp_profile_enable(1) starts recording (and clears earlier marks); vdp_profile_read synchronises on
  * the last mark, returns accumulated milliseconds and number of spans per phase, and clears the marks.

@@ -33,10 +33,12 @@ def test_library_exports_every_declared_symbol():
     assert lib.vdp_version() >= 100
 
 
-def test_struct_layout_matches_header_field_order():
-    from vi_diffusion_processes_b200._lib import CviProblem
+@pytest.mark.parametrize("struct_name,cls_name", [("vdp_cvi_problem", "CviProblem"), ("vdp_vgp_problem", "VgpProblem")])
+def test_struct_layout_matches_header_field_order(struct_name, cls_name):
+    from vi_diffusion_processes_b200 import _lib
+    CviProblem = getattr(_lib, cls_name)
     src = open(HEADER).read()
-    body = src[src.index("typedef struct vdp_cvi_problem {"):src.index("} vdp_cvi_problem;")]
+    body = src[src.index("typedef struct %s {" % struct_name):src.index("} %s;" % struct_name)]
     body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
     names = []
     for stmt in body.split("{", 1)[1].split(";"):

@@ -236,3 +236,75 @@ def test_site_update_vdp_2d(sweeps):
         if it == 1:
             eng.relinearize()
             ref.relinearize()
+
+
+# ---------------------------------------------------------------------------------------------------
+# VDP (VariationalMarkovGP, vi_sde.py) against the oracle
+def _vgp_case(sde, N, n_obs, dt, seed, noise=0.1):
+    rng = np.random.default_rng(seed)
+    D = sde.state_dim
+    grid = np.round(np.arange(N + 1) * dt, 6)
+    idx = np.sort(rng.choice(np.arange(1, N + 1), n_obs, replace=False))
+    y = rng.normal(size=(n_obs, D)) * 0.5 + 0.5
+    lik = M.MultivariateGaussian(noise * np.eye(D))
+    x0 = S.Gaussian(np.full(D, 0.5), 0.3 * np.eye(D))
+    return grid, idx, y, lik, x0
+
+
+@pytest.mark.parametrize("sde,N,stab", [(S.DoubleWellSDE(), 600, False), (S.OrnsteinUhlenbeckSDE(0.8), 2500, False),
+                                        (S.BenesSDE(0.7), 300, True),
+                                        (S.VanderPolOscillatorSDE(1.0, 1.0, np.eye(2)), 250, False),
+                                        (S.Lorenz63SDE(q=np.eye(3)), 120, False)],
+                         ids=["dw", "ou", "benes-stab", "vdp2d", "lorenz3d"])
+def test_vgp_sweeps(sweeps, sde, N, stab):
+    from vi_diffusion_processes_b200.vgp import VgpEngine
+    D = sde.state_dim
+    dt = 0.01 if D < 3 else 0.002
+    grid, idx, y, lik, x0 = _vgp_case(sde, N, 12, dt, seed=23 + N)
+    ref = M.VariationalMarkovGP((grid[idx], y), sde, grid, lik, prior_initial_state=x0, stabilize_system=stab)
+    eng = VgpEngine(sde.drift_id, sde.params, sde.q, grid, idx, y, lik.chol_covariance, x0.mu, x0.cov,
+                    stabilize_system=stab)
+    for it in range(3):
+        # piecewise on the first iteration, fused afterwards
+        upd = it >= 1
+        if it == 0:
+            m, Sg = eng.forward_pass()
+            rm, rS = ref.forward_pass
+            assert rel(m[0], rm) < TOL and rel(Sg[0], rS) < TOL
+            eng.update_lagrange()
+            ref.update_lagrange(rm, rS)
+            assert rel(eng.lambda_lagrange[0], ref.lambda_lagrange) < TOL
+            assert rel(eng.psi_lagrange[0], ref.psi_lagrange) < TOL
+            eng.update_param(0.3)
+            ref.update_param(rm, rS, 0.3)
+            eng.forward_pass()
+            e = eng.elbo()
+            r = ref.elbo(*ref.forward_pass)
+        else:
+            e = eng.sweep(0.3, update_x0=upd, x0_lr=0.1)
+            r = ref.sweep(0.3, update_x0=upd, x0_lr=0.1)
+        eng.check_status()
+        assert rel(eng.A[0], ref.A) < TOL and rel(eng.b[0], ref.b) < TOL
+        assert rel(eng.q_initial_mean[0], ref.q_initial_mean) < TOL
+        assert rel(eng.q_initial_chol[0], ref.q_initial_chol) < TOL
+        assert abs(e.item() - r) < TOL * max(1.0, abs(r))
+
+
+def test_vgp_batched_matches_single():
+    """B sequences in one call == the same sequences one at a time (bitwise: no cross-sequence coupling)."""
+    from vi_diffusion_processes_b200.vgp import VgpEngine
+    sde = S.DoubleWellSDE()
+    rng = np.random.default_rng(5)
+    N, n_obs, B = 700, 10, 3
+    grid = np.round(np.arange(N + 1) * 0.01, 6)
+    idx = np.sort(np.stack([rng.choice(np.arange(1, N + 1), n_obs, replace=False) for _ in range(B)]), axis=1)
+    y = rng.normal(size=(B, n_obs, 1))
+    eng = VgpEngine(sde.drift_id, sde.params, sde.q, grid, idx, y, [[0.1]], [0.0], [[1.0]])
+    for _ in range(2):
+        eng.sweep(0.3)
+    for bi in range(B):
+        one = VgpEngine(sde.drift_id, sde.params, sde.q, grid, idx[bi], y[bi], [[0.1]], [0.0], [[1.0]])
+        for _ in range(2):
+            one.sweep(0.3)
+        assert torch.equal(one.A[0], eng.A[bi]) and torch.equal(one.m[0], eng.m[bi])
+        assert torch.equal(one.elbo_value[0], eng.elbo_value[bi])

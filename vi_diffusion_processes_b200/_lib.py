@@ -47,6 +47,33 @@ class CviProblem(C.Structure):
     ]
 
 
+class VgpProblem(C.Structure):
+    """Mirror of ``struct vdp_vgp_problem`` (include/vdp_b200.h)."""
+    _fields_ = [
+        ("B", i64), ("N", i64), ("n_obs", i64),
+        ("D", C.c_int32), ("drift_id", C.c_int32),
+        ("drift_params", C.c_double * 16),
+        ("q", C.c_double * 9),
+        ("dt", C.c_double),
+        ("x0_mu", C.c_double * 3), ("x0_cov", C.c_double * 9),
+        ("lik_chol", C.c_double * 9),
+        ("lr", C.c_double), ("x0_lr", C.c_double),
+        ("time_grid", vp),
+        ("A", vp), ("b", vp),
+        ("lam", vp), ("psi", vp),
+        ("q_mean", vp), ("q_chol", vp),
+        ("obs_idx", vp), ("obs_y", vp),
+        ("m", vp), ("S", vp),
+        ("elbo", vp),
+        ("workspace", vp), ("workspace_bytes", C.c_size_t),
+        ("status", vp),
+        ("flags", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+VGP_STABILIZE = 1
+VGP_UPDATE_X0 = 2
+
 # name -> (restype, argtypes); every symbol include/vdp_b200.h declares
 SIGNATURES = {
     "vdp_version": (C.c_int, []),
@@ -73,6 +100,13 @@ SIGNATURES = {
     "vdp_cvi_workspace": (C.c_size_t, [i64, i64, C.c_int, i64]),
     "vdp_cvi_site_update": (C.c_int, [C.POINTER(CviProblem), vp]),
     "vdp_cvi_elbo": (C.c_int, [C.POINTER(CviProblem), vp]),
+    "vdp_vgp_workspace": (C.c_size_t, [i64, i64, C.c_int, i64]),
+    "vdp_vgp_forward_pass": (C.c_int, [C.POINTER(VgpProblem), vp]),
+    "vdp_vgp_update_lagrange": (C.c_int, [C.POINTER(VgpProblem), vp]),
+    "vdp_vgp_update_param": (C.c_int, [C.POINTER(VgpProblem), vp]),
+    "vdp_vgp_update_initial_statistics": (C.c_int, [C.POINTER(VgpProblem), vp]),
+    "vdp_vgp_elbo": (C.c_int, [C.POINTER(VgpProblem), vp]),
+    "vdp_vgp_sweep": (C.c_int, [C.POINTER(VgpProblem), vp]),
     "vdp_profile_enable": (C.c_int, [C.c_int]),
     "vdp_profile_read": (C.c_int, [c_dp, c_i64p, C.c_int]),
 }

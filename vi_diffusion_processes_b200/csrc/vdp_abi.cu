@@ -14,6 +14,7 @@
 #include "pointwise_kernels.cuh"
 #include "quad_core.cuh"
 #include "tile_sweeps.cuh"
+#include "vgp_kernels.cuh"
 
 namespace vdp {
 
@@ -186,3 +187,4 @@ int vdp_btd_logdet(const double* Ld, double* out, int64_t B, int64_t n, int D, v
 
 #include "vdp_fused.inl"
 #include "vdp_cvi.inl"
+#include "vdp_vgp.inl"

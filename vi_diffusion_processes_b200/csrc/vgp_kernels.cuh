@@ -1,0 +1,349 @@
+// VDP (Archambeau et al. 2007) fixed-point sweep: markovflow/models/vi_sde.py (VariationalMarkovGP).
+//
+//   forward_pass      vi_sde.py:171-204   LinearDrift(-A, b).to_ssm (drift.py:64-116) -> marginals
+//   E_sde, its grads  vi_sde.py:206-240, 422-434 -> squared_drift_difference_along_Gaussian_path
+//                     (sde_utils.py:182-249), H = 20, reverse mode through the quadrature and chol(S)
+//   jump conditions   vi_sde.py:262-287   likelihood gradients at the observed grid points
+//   update_lagrange   vi_sde.py:289-347   backward Euler sweep for (lambda, psi)
+//   update_param      vi_sde.py:377-414   damped fixed point for (A, b), E[f], E[grad f] with H = 10
+//   update_initial_statistics :242-260, KL_initial_state :416-420, elbo :436-455
+//
+// Layouts: A [B,N,D,D], b [B,N,D], lambda [B,N,D], psi [B,N,D,D], m [B,N+1,D], S [B,N+1,D,D].
+#pragma once
+#include "kl_kernels.cuh"
+#include "tile_sweeps.cuh"
+
+namespace vdp {
+
+constexpr double kVgpClipMin = -5000.0, kVgpClipMax = 5000.0;   // vi_sde.py:59-60
+
+// tf.where(is_nan(x), 1e-8, x) then clip_by_value
+__device__ __forceinline__ double vgp_fix(double x, double lo, double hi) {
+    if (x != x) x = 1e-8;
+    return fmin(fmax(x, lo), hi);
+}
+template <int D> __device__ __forceinline__ Mat<D> vgp_fix(Mat<D> x, double lo, double hi) {
+#pragma unroll
+    for (int i = 0; i < D * D; ++i) x.a[i] = vgp_fix(x.a[i], lo, hi);
+    return x;
+}
+template <int D> __device__ __forceinline__ Vec<D> vgp_fix(Vec<D> x, double lo, double hi) {
+#pragma unroll
+    for (int i = 0; i < D; ++i) x.v[i] = vgp_fix(x.v[i], lo, hi);
+    return x;
+}
+
+// LinearDrift(-A, b).to_ssm (+ the stabilize_system clip of vi_sde.py:184-197); one thread per transition
+template <int D>
+__global__ void k_vgp_to_ssm(const double* __restrict__ A, const double* __restrict__ bv, Mat<D> q,
+                             const double* __restrict__ time_grid, int stabilize, double* __restrict__ sA,
+                             double* __restrict__ sb, double* __restrict__ scQ, int64_t B, int64_t N,
+                             int64_t* status) {
+    const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (t >= B * N) return;
+    constexpr int DD = D * D;
+    const int64_t k = t % N;
+    const double delta = time_grid[k + 1] - time_grid[k];
+    Mat<D> At = delta * (-1.0 * mat_load<D>(A + t * DD)) + mat_eye<D>();
+    Vec<D> bt = delta * vec_load<D>(bv + t * D);
+    bool ok = true;
+    const Mat<D> cQ = chol(delta * q, ok);
+    if (!ok) report_not_pd(status, t);
+    if (stabilize) { At = vgp_fix(At, -1.0, 1.0); bt = vgp_fix(bt, -1.0, 1.0); }
+    mat_store<D>(sA + t * DD, At);
+    vec_store<D>(sb + t * D, bt);
+    mat_store<D>(scQ + t * DD, cQ);
+}
+
+// E_sde terms and (optionally) gradients: one group of G lanes per transition (b, k), marginal of node k.
+//   term_k = 0.5 dt E_{N(m_k,S_k)} || (-A_k) x + b_k - f(x) ||^2_{q^-1}
+//   dEdm = d term / d m_k / dt, dEdS = d term / d S_k / dt       (vi_sde.py:206-225 divides by dt)
+template <int DRIFT, int D, int H, int G>
+__global__ void k_vgp_esde(DriftParams P, Mat<D> q, double dt, double pi_factor, const double* __restrict__ A,
+                           const double* __restrict__ bv, const double* __restrict__ m,
+                           const double* __restrict__ S, double* __restrict__ terms, double* __restrict__ dEdm,
+                           double* __restrict__ dEdS, int64_t B, int64_t N, int64_t* status) {
+    const int64_t t = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / G;
+    const int lane = threadIdx.x % G;
+    if (t >= B * N) return;
+    constexpr int DD = D * D;
+    const int64_t b = t / N, k = t % N;
+    const int64_t node = b * (N + 1) + k;
+    bool ok = true;
+    const Mat<D> Al = -1.0 * mat_load<D>(A + t * DD);
+    const Vec<D> bl = vec_load<D>(bv + t * D);
+    const Vec<D> mk = vec_load<D>(m + node * D);
+    const Mat<D> LS = chol(mat_load<D>(S + node * DD), ok);
+    const Mat<D> cq = chol(q, ok);
+    const Mat<D> sinv = chol_inverse(cq);
+    const Mat<D> sinv_s = sym(sinv);
+    double quad = 0.0;
+    Vec<D> gm = vec_zero<D>();
+    Mat<D> Lb = mat_zero<D>();
+    constexpr int NP = NodeCount<H, D>::value;
+    for (int p = lane; p < NP; p += G) {
+        Vec<D> xi, f;
+        Mat<D> J;
+        double w;
+        gh_node<H, D>(p, xi, w);
+        w *= pi_factor;
+        const Vec<D> X = gh_point(LS, mk, xi);
+        Drift<DRIFT, D>::eval(P, X, f, J);
+        const Vec<D> AX = mv(Al, X);
+        Vec<D> d;
+#pragma unroll
+        for (int i = 0; i < D; ++i) d(i) = (AX(i) + bl(i)) - f(i);
+        quad += w * dot(d, mv(sinv, d));
+        if (dEdm) {
+            const Vec<D> rb = (dt * w) * mv(sinv_s, d);
+#pragma unroll
+            for (int i = 0; i < D; ++i) {
+                double s = 0.0;
+#pragma unroll
+                for (int j = 0; j < D; ++j) s += (Al(j, i) - J(j, i)) * rb(j);
+                gm(i) += s;
+#pragma unroll
+                for (int j = 0; j <= i; ++j) Lb(i, j) += 1.4142135623730951 * (s * xi(j));
+            }
+        }
+    }
+    quad = group_sum<G>(quad);
+    if (dEdm) { group_sum<G>(gm); group_sum<G>(Lb); }
+    if (lane != 0) return;
+    if (!ok) report_not_pd(status, node);
+    terms[t] = 0.5 * dt * quad;
+    if (dEdm) {
+        const Mat<D> gS = chol_adjoint(LS, Lb);
+        const double idt = 1.0 / dt;
+        vec_store<D>(dEdm + t * D, idt * gm);
+        mat_store<D>(dEdS + t * DD, idt * gS);
+    }
+}
+
+// jump conditions: likelihood gradients scattered on the grid (buffers zeroed by the caller)
+template <int D>
+__global__ void k_vgp_jump(const double* __restrict__ m, const int64_t* __restrict__ obs_idx,
+                           const double* __restrict__ obs_y, Mat<D> lik_chol, double* __restrict__ dobs_m,
+                           double* __restrict__ dobs_S, int64_t B, int64_t N, int64_t n_obs) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= B * n_obs) return;
+    constexpr int DD = D * D;
+    const int64_t b = i / n_obs;
+    const int64_t k = obs_idx[i];
+    if (k < 0 || k > N) return;
+    const int64_t node = b * (N + 1) + k;
+    const Mat<D> inv = chol_inverse(lik_chol);
+    const Vec<D> gmu = mv(sym(inv), vec_load<D>(obs_y + i * D) - vec_load<D>(m + node * D));
+    const Mat<D> gS = -0.5 * inv;
+#pragma unroll
+    for (int e = 0; e < D; ++e) atomicAdd(dobs_m + node * D + e, gmu(e));
+#pragma unroll
+    for (int e = 0; e < DD; ++e) atomicAdd(dobs_S + node * DD + e, gS.a[e]);
+}
+
+// update_param: one group per transition (b, k), marginal of node k, H = 10
+template <int DRIFT, int D, int H, int G>
+__global__ void k_vgp_update_param(DriftParams P, Mat<D> q, double pi_factor, int stabilize, double lr,
+                                   const double* __restrict__ m, const double* __restrict__ S,
+                                   double* __restrict__ lam, double* __restrict__ psi, double* __restrict__ A,
+                                   double* __restrict__ bv, int64_t B, int64_t N, int64_t* status) {
+    const int64_t t = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / G;
+    const int lane = threadIdx.x % G;
+    if (t >= B * N) return;
+    constexpr int DD = D * D;
+    const int64_t b = t / N, k = t % N;
+    const int64_t node = b * (N + 1) + k;
+    bool ok = true;
+    Vec<D> ef;
+    Mat<D> ej;
+    const Vec<D> mk = vec_load<D>(m + node * D);
+    gh_expect_point<DRIFT, D, H, G>(P, mk, mat_load<D>(S + node * DD), lane, pi_factor, ef, ej, ok);
+    if (lane != 0) return;
+    if (!ok) report_not_pd(status, node);
+    Mat<D> ps = mat_load<D>(psi + t * DD);
+    Vec<D> la = vec_load<D>(lam + t * D);
+    if (stabilize) {
+        ps = vgp_fix(ps, kVgpClipMin, kVgpClipMax);
+        la = vgp_fix(la, kVgpClipMin, kVgpClipMax);
+        mat_store<D>(psi + t * DD, ps);
+        vec_store<D>(lam + t * D, la);
+    }
+    const Mat<D> At = (-1.0 * ej) + 2.0 * mm(q, ps);
+    const Vec<D> bt = (ef + mv(At, mk)) - mv(q, la);
+    mat_store<D>(A + t * DD, (1.0 - lr) * mat_load<D>(A + t * DD) + lr * At);
+    vec_store<D>(bv + t * D, (1.0 - lr) * vec_load<D>(bv + t * D) + lr * bt);
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// update_lagrange (vi_sde.py:337-347): for t = N-1 .. 1
+//     d_psi = psi_t A_t + psi_t A_t - dEdS_t ;  d_lam = A_t lam_t - dEdm_t
+//     psi_{t-1} = psi_t - dt d_psi - dObsS_t ;  lam_{t-1} = lam_t - dt d_lam - dObsm_t
+// with lam_{N-1} = 0, psi_{N-1} = 1e-10 I.  "Transition" j = t - 1 maps state j+1 to state j; the maps are
+// affine (lam: left-affine, psi: right-affine), scanned together.
+template <int D>
+struct RightAffElem { Mat<D> R, V; };
+template <int D>
+struct RightAffOps {
+    using Elem = RightAffElem<D>;
+    using State = Mat<D>;
+    __device__ __forceinline__ static Elem identity() {
+        Elem e;
+        e.R = mat_eye<D>();
+        e.V = mat_zero<D>();
+        return e;
+    }
+    __device__ __forceinline__ static Elem combine(const Elem& e1, const Elem& e2) {
+        Elem r;
+        r.R = mm(e1.R, e2.R);
+        r.V = mm(e1.V, e2.R) + e2.V;
+        return r;
+    }
+    __device__ __forceinline__ static State apply(const Elem& e, const State& X) { return mm(X, e.R) + e.V; }
+};
+template <int D>
+using LagrangeOps = PairOps<AffVecOps<D>, RightAffOps<D>>;
+
+template <int D, int T, int L, int MODE>
+__global__ void __launch_bounds__(T)
+k_vgp_lagrange_tiled(const double* __restrict__ A, const double* __restrict__ dEdm, const double* __restrict__ dEdS,
+                     const double* __restrict__ dobs_m, const double* __restrict__ dobs_S, double dt, int stabilize,
+                     double* __restrict__ lam, double* __restrict__ psi, int64_t B, int64_t N, int nseg,
+                     int64_t seg_len, const typename LagrangeOps<D>::State* __restrict__ carry_in,
+                     typename LagrangeOps<D>::State* __restrict__ init_out,
+                     typename LagrangeOps<D>::Elem* __restrict__ seg_elem) {
+    constexpr int DD = D * D, TL = T * L;
+    using Ops = LagrangeOps<D>;
+    extern __shared__ __align__(16) double smem[];
+    double* sA = smem;               // A_t                      index i <-> t = lo + 1 + i
+    double* sES = sA + TL * DD;      // dEdS_t  -> psi_{t-1}
+    double* sOS = sES + TL * DD;     // dObsS_t
+    double* sEm = sOS + TL * DD;     // dEdm_t  -> lam_{t-1}
+    double* sOm = sEm + TL * D;      // dObsm_t
+    typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(sOm + TL * D);
+    const int64_t b = blockIdx.x / nseg;
+    const int seg = (int)(blockIdx.x % nseg);
+    const int64_t NT = N - 1;        // transitions j = 0 .. N-2
+    const int64_t t0 = seg * seg_len, t1 = min(NT, t0 + seg_len);
+    typename Ops::State st;
+    st.a = vec_zero<D>();
+    st.b = 1e-10 * mat_eye<D>();
+    if (t1 == NT || NT <= 0) {
+        if (threadIdx.x == 0 && seg == nseg - 1) {
+            if (MODE == SWEEP_FULL) {
+                vec_store<D>(lam + (b * N + N - 1) * D, st.a);
+                mat_store<D>(psi + (b * N + N - 1) * DD, st.b);
+            } else {
+                init_out[b] = st;
+            }
+        }
+    } else if (MODE == SWEEP_FULL) {
+        st = carry_in[b * nseg + seg];
+    }
+    typename Ops::Elem seg_tot = Ops::identity();
+    for (int64_t hi = t1; hi > t0; hi -= TL) {
+        const int64_t lo = max(t0, hi - TL);
+        const int cnt = (int)(hi - lo);
+        __syncthreads();
+        // transition j uses the inputs of step t = j + 1
+        stage_in<T>(sA, A + (b * N + lo + 1) * DD, (int64_t)cnt * DD);
+        stage_in<T>(sES, dEdS + (b * N + lo + 1) * DD, (int64_t)cnt * DD);
+        stage_in<T>(sEm, dEdm + (b * N + lo + 1) * D, (int64_t)cnt * D);
+        stage_in<T>(sOS, dobs_S + (b * (N + 1) + lo + 1) * DD, (int64_t)cnt * DD);
+        stage_in<T>(sOm, dobs_m + (b * (N + 1) + lo + 1) * D, (int64_t)cnt * D);
+        stage_wait();
+        if (stabilize) {
+            for (int i = threadIdx.x; i < cnt * DD; i += T) {
+                sES[i] = vgp_fix(sES[i], kVgpClipMin, kVgpClipMax);
+                sOS[i] = vgp_fix(sOS[i], kVgpClipMin, kVgpClipMax);
+            }
+            for (int i = threadIdx.x; i < cnt * D; i += T) {
+                sEm[i] = vgp_fix(sEm[i], kVgpClipMin, kVgpClipMax);
+                sOm[i] = vgp_fix(sOm[i], kVgpClipMin, kVgpClipMax);
+            }
+        }
+        __syncthreads();
+        const BwdChunk ch = bwd_chunk<L>(cnt);
+        typename Ops::Elem e = Ops::identity();
+        for (int k = ch.top - 1; k >= ch.bot; --k) {
+            const Mat<D> At = mat_load<D>(sA + k * DD);
+            typename Ops::Elem s;
+            s.a.M = mat_eye<D>() - dt * At;
+            s.a.v = dt * vec_load<D>(sEm + k * D) - vec_load<D>(sOm + k * D);
+            s.b.R = mat_eye<D>() - (2.0 * dt) * At;
+            s.b.V = dt * mat_load<D>(sES + k * DD) - mat_load<D>(sOS + k * DD);
+            e = Ops::combine(e, s);
+        }
+        typename Ops::Elem total;
+        const typename Ops::Elem excl = block_exclusive_scan<Ops, T>(e, wtot, total);
+        if (MODE != SWEEP_FULL) {
+            seg_tot = Ops::combine(seg_tot, total);
+            continue;
+        }
+        typename Ops::State mine = Ops::apply(excl, st);
+        st = Ops::apply(total, st);
+        for (int k = ch.top - 1; k >= ch.bot; --k) {
+            const Mat<D> At = mat_load<D>(sA + k * DD);
+            const Mat<D> pa = mm(mine.b, At);
+            const Mat<D> dpsi = (pa + pa) - mat_load<D>(sES + k * DD);
+            const Vec<D> dlam = mv(At, mine.a) - vec_load<D>(sEm + k * D);
+            mine.b = (mine.b - dt * dpsi) - mat_load<D>(sOS + k * DD);
+            mine.a = (mine.a - dt * dlam) - vec_load<D>(sOm + k * D);
+            mat_store<D>(sES + k * DD, mine.b);
+            vec_store<D>(sEm + k * D, mine.a);
+        }
+        __syncthreads();
+        stage_out<T>(psi + (b * N + lo) * DD, sES, (int64_t)cnt * DD);
+        stage_out<T>(lam + (b * N + lo) * D, sEm, (int64_t)cnt * D);
+    }
+    if (MODE != SWEEP_FULL && threadIdx.x == 0) seg_elem[b * nseg + seg] = seg_tot;
+}
+
+template <int D, int T, int L>
+constexpr size_t lagrange_tiled_smem() {
+    return (3 * (size_t)T * L * D * D + 2 * (size_t)T * L * D) * sizeof(double) +
+           (T / 32) * sizeof(typename LagrangeOps<D>::Elem);
+}
+
+// update_initial_statistics (vi_sde.py:242-260), one thread per sequence
+template <int D>
+__global__ void k_vgp_update_initial(Vec<D> p_mu, Mat<D> p_cov, double lr, const double* __restrict__ lam,
+                                     const double* __restrict__ psi, double* __restrict__ q_mean,
+                                     double* __restrict__ q_chol, int64_t B, int64_t N, int64_t* status) {
+    const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    constexpr int DD = D * D;
+    bool ok = true;
+    const Mat<D> Lp = chol(p_cov, ok);
+    const Vec<D> qm = p_mu - mv(mmT(Lp, Lp), vec_load<D>(lam + b * N * D));
+    const Mat<D> pci = chol_inverse(Lp);
+    const Mat<D> prior_cov_inv = mmT(pci, pci);   // as written in the reference (:250-251)
+    const Mat<D> qc_new = lu_solve(prior_cov_inv + 2.0 * mat_load<D>(psi + b * N * DD), mat_eye<D>());
+    const Mat<D> qch = mat_load<D>(q_chol + b * DD);
+    const Mat<D> qc = (1.0 - lr) * mmT(qch, qch) + lr * qc_new;
+    vec_store<D>(q_mean + b * D, (1.0 - lr) * vec_load<D>(q_mean + b * D) + lr * qm);
+    mat_store<D>(q_chol + b * DD, chol(qc, ok));
+    if (!ok) report_not_pd(status, b * (N + 1));
+}
+
+// elbo = E_obs - E_sde - KL[q(x0) || p(x0)]  (vi_sde.py:436-455); ve and esde are per-sequence sums
+template <int D>
+__global__ void k_vgp_elbo_combine(const double* __restrict__ ve, const double* __restrict__ esde, Vec<D> p_mu,
+                                   Mat<D> p_cov, const double* __restrict__ q_mean,
+                                   const double* __restrict__ q_chol, double* __restrict__ elbo, int64_t B) {
+    const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    constexpr int DD = D * D;
+    bool ok = true;
+    const Mat<D> qch = mat_load<D>(q_chol + b * DD);
+    const Mat<D> Lp = chol(p_cov, ok), Lq = chol(mmT(qch, qch), ok);
+    const Mat<D> Mq = trsm(Lp, Lq);
+    const Vec<D> diff = trsv(Lp, p_mu - vec_load<D>(q_mean + b * D));
+    double fro = 0.0;
+#pragma unroll
+    for (int e = 0; e < DD; ++e) fro += Mq.a[e] * Mq.a[e];
+    const double kl0 = 0.5 * (fro + dot(diff, diff) - (double)D + logdet_from_chol(Lp) - logdet_from_chol(Lq));
+    elbo[b] = (ve[b] - esde[b]) - kl0;
+}
+
+}  // namespace vdp
