@@ -131,6 +131,22 @@ int vdp_expectations_to_ssm(const double* e1, const double* ed, const double* es
                             double* A, double* b, double* cholQ, double* mu0, double* cholP0,
                             int64_t B, int64_t N, int D, int64_t* status, void* stream);
 
+/* Vector-Jacobian product of expectations_to_ssm_params at (e1, ed, es): the chain-rule step of
+ * SSMNaturalGradient (ssm_natgrad.py:142-172, tape.gradient(ssm_params, etas, output_gradients=dL_dssm)).
+ * Cotangents gA [B,N,D,D], gb [B,N,D], gcholP0 [B,D,D], gcholQ [B,N,D,D] (lower triangles), gmu0 [B,D]. */
+int vdp_expectations_to_ssm_vjp(const double* e1, const double* ed, const double* es, const double* gA,
+                                const double* gb, const double* gcholP0, const double* gcholQ, const double* gmu0,
+                                double* g1, double* gd, double* gs, int64_t B, int64_t N, int D, int64_t* status,
+                                void* stream);
+
+/* SSMNaturalGradient._natgrad_step, momentum=False (ssm_natgrad.py:121-218): the SSM parameters are updated
+ * in place from the Euclidean gradients dL/d(A, b, chol_P0, chol_Q, mu0). */
+size_t vdp_ssm_natgrad_workspace(int64_t B, int64_t N, int D);
+int vdp_ssm_natgrad_step(double* A, double* b, double* cholP0, double* cholQ, double* mu0, const double* dL_dA,
+                         const double* dL_db, const double* dL_dcholP0, const double* dL_dcholQ,
+                         const double* dL_dmu0, double gamma, void* workspace, size_t workspace_bytes, int64_t B,
+                         int64_t N, int D, int64_t* status, void* stream);
+
 /* SDE_SSM_KL_with_grads_wrt_exp_params  (sde_utils.py:473-547), H = 20:
  * q given by its transitions A [B,N,D,D] and marginals m, Sd; prior x0 ~ N(x0_mu_host, x0_cov_host);
  * dt = float(grid[1]-grid[0]) (used in f_p), time_grid gives the per-step Q_p = delta_k q.
@@ -177,6 +193,8 @@ typedef struct vdp_cvi_problem {
 #define VDP_FLAG_DEFAULT 0
 #define VDP_FLAG_SKIP_DATA_UPDATE 1   /* leave the data sites as they are */
 #define VDP_FLAG_SKIP_ELBO 2          /* do not evaluate classic_elbo */
+#define VDP_FLAG_SKIP_GIRSANOV 4      /* update_data_sites only (variational_cvi_sde.py:301-317) */
+#define VDP_FLAG_POSTERIOR_SSM_ONLY 8 /* vdp_cvi_elbo: only rebuild q as an SSM from the sites (dist_q, :176-192) */
 
 size_t vdp_cvi_workspace(int64_t B, int64_t N, int D, int64_t n_obs);
 int vdp_cvi_site_update(const vdp_cvi_problem* problem_host, void* stream);
@@ -220,6 +238,22 @@ typedef struct vdp_vgp_problem {
 
 #define VDP_VGP_STABILIZE 1    /* stabilize_system=True (clips of vi_sde.py:184-197, 314-323, 393-397) */
 #define VDP_VGP_UPDATE_X0 2    /* vdp_vgp_sweep also runs update_initial_statistics */
+
+/* LinearDrift.to_ssm (markovflow/sde/drift.py:64-116): A_ssm = I + A delta_k, b_ssm = b delta_k,
+ * cholQ = chol(q delta_k).  A [B,N,D,D], b [B,N,D] -> same shapes. */
+int vdp_linear_drift_to_ssm(const double* A, const double* b, const double* q_host, const double* time_grid,
+                            double* ssm_A, double* ssm_b, double* ssm_cholQ, int64_t B, int64_t N, int D,
+                            int64_t* status, void* stream);
+
+/* squared_drift_difference_along_Gaussian_path (sde_utils.py:182-249), H = 20, linear drift (-A, b):
+ *   value[b] = 0.5 dt sum_k E_{N(m_k,S_k)} || -A_k x + b_k - f(x) ||^2_{q^-1},  k = 0..N-1,
+ * m [B,N+1,D], S [B,N+1,D,D] (the last grid point is not used); optional dEdm [B,N,D], dEdS [B,N,D,D]
+ * = gradients wrt (m_k, S_k) divided by dt (vi_sde.py:206-240). */
+size_t vdp_sq_drift_difference_workspace(int64_t B, int64_t N, int D);
+int vdp_sq_drift_difference(int drift_id, const double* params_host, const double* q_host, double dt,
+                            const double* A, const double* b, const double* m, const double* S, double* value,
+                            double* dEdm, double* dEdS, void* workspace, size_t workspace_bytes, int64_t B,
+                            int64_t N, int D, int64_t* status, void* stream);
 
 size_t vdp_vgp_workspace(int64_t B, int64_t N, int D, int64_t n_obs);
 int vdp_vgp_forward_pass(const vdp_vgp_problem* problem_host, void* stream);

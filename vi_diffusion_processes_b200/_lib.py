@@ -71,6 +71,7 @@ class VgpProblem(C.Structure):
     ]
 
 
+FLAG_SKIP_DATA_UPDATE, FLAG_SKIP_ELBO, FLAG_SKIP_GIRSANOV, FLAG_POSTERIOR_SSM_ONLY = 1, 2, 4, 8
 VGP_STABILIZE = 1
 VGP_UPDATE_X0 = 2
 
@@ -94,12 +95,19 @@ SIGNATURES = {
     "vdp_ssm_marginals": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, i64, i64, C.c_int, vp, vp]),
     "vdp_ssm_to_expectations": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i64, C.c_int, vp]),
     "vdp_expectations_to_ssm": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, C.c_int, vp, vp]),
+    "vdp_expectations_to_ssm_vjp": (C.c_int, [vp] * 11 + [i64, i64, C.c_int, vp, vp]),
+    "vdp_ssm_natgrad_workspace": (C.c_size_t, [i64, i64, C.c_int]),
+    "vdp_ssm_natgrad_step": (C.c_int, [vp] * 10 + [C.c_double, vp, C.c_size_t, i64, i64, C.c_int, vp, vp]),
     "vdp_cvi_kl_workspace": (C.c_size_t, [i64, i64, C.c_int]),
     "vdp_cvi_kl_and_grad": (C.c_int, [C.c_int, c_dp, c_dp, C.c_double, vp, c_dp, c_dp, vp, vp, vp, vp, vp, vp, vp, vp,
                                       C.c_size_t, i64, i64, C.c_int, vp, vp]),
     "vdp_cvi_workspace": (C.c_size_t, [i64, i64, C.c_int, i64]),
     "vdp_cvi_site_update": (C.c_int, [C.POINTER(CviProblem), vp]),
     "vdp_cvi_elbo": (C.c_int, [C.POINTER(CviProblem), vp]),
+    "vdp_linear_drift_to_ssm": (C.c_int, [vp, vp, c_dp, vp, vp, vp, vp, i64, i64, C.c_int, vp, vp]),
+    "vdp_sq_drift_difference_workspace": (C.c_size_t, [i64, i64, C.c_int]),
+    "vdp_sq_drift_difference": (C.c_int, [C.c_int, c_dp, c_dp, C.c_double, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t,
+                                          i64, i64, C.c_int, vp, vp]),
     "vdp_vgp_workspace": (C.c_size_t, [i64, i64, C.c_int, i64]),
     "vdp_vgp_forward_pass": (C.c_int, [C.POINTER(VgpProblem), vp]),
     "vdp_vgp_update_lagrange": (C.c_int, [C.POINTER(VgpProblem), vp]),

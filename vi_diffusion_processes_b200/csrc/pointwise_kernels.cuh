@@ -179,4 +179,102 @@ __global__ void k_variational_expectation(const double* __restrict__ fx_mus, con
     ve[b] = acc;
 }
 
+
+// Vector-Jacobian product of expectations_to_ssm_params (what tape.gradient(ssm_params, etas,
+// output_gradients=dL_dssm) returns in ssm_natgrad.py:168), pointwise in time.  Transition k touches nodes k
+// and k+1; thread i = (b, k) recomputes the two transitions next to its node and keeps the parts that land
+// on it, so no neighbour exchange is needed.
+template <int D>
+struct SsmCotangent { Mat<D> gA, gLQ; Vec<D> gb; };
+
+// adjoint of one transition: contributions to (m_k, S_k) ["left"], (m_{k+1}, S_{k+1}) ["right"] and eta_s[k]
+template <int D>
+__device__ __forceinline__ void exp_to_ssm_step_vjp(const ExpToSsm<D>& r, const SsmCotangent<D>& c, Vec<D>& Lgm,
+                                                    Mat<D>& LgS, Vec<D>& Rgm, Mat<D>& RgS, Mat<D>& ges) {
+    const Mat<D> gQc = chol_adjoint(r.LQ, tril(c.gLQ));
+    Mat<D> gA = c.gA;
+    // b = m_{k+1} - A m_k
+    Rgm = c.gb;
+    gA = gA - outer(c.gb, r.mk);
+    Lgm = -1.0 * Tmv(r.A, c.gb);
+    // Qc = S_{k+1} - A S_k A^T
+    RgS = gQc;
+    gA = gA - 2.0 * mm(gQc, mm(r.A, r.Sk));
+    LgS = -1.0 * Tmm(r.A, mm(gQc, r.A));
+    // A = (S_k^-1 C)^T
+    const Mat<D> gC = chol_solve(r.LS, transpose(gA));
+    LgS = LgS + sym(-1.0 * mm(gC, r.A));
+    // C = eta_s^T - m_k m_{k+1}^T
+    ges = transpose(gC);
+    Lgm = Lgm - mv(gC, r.mn);
+    Rgm = Rgm - Tmv(gC, r.mk);
+}
+
+// out = theta - gamma * dL/d eta when th* are given (natural-gradient step), else out = dL/d eta
+template <int D>
+__global__ void k_expectations_to_ssm_vjp(const double* __restrict__ e1, const double* __restrict__ ed,
+                                          const double* __restrict__ es, const double* __restrict__ gA,
+                                          const double* __restrict__ gb, const double* __restrict__ gcholP0,
+                                          const double* __restrict__ gcholQ, const double* __restrict__ gmu0,
+                                          const double* __restrict__ th1, const double* __restrict__ thd,
+                                          const double* __restrict__ ths, double gamma, double* __restrict__ o1,
+                                          double* __restrict__ od, double* __restrict__ os, int64_t B, int64_t N,
+                                          int64_t* status) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t n = N + 1;
+    if (i >= B * n) return;
+    constexpr int DD = D * D;
+    const int64_t b = i / n, k = i % n;
+    bool ok = true;
+    Vec<D> gm = vec_zero<D>();
+    Mat<D> gS = mat_zero<D>();
+    const Vec<D> mk = vec_load<D>(e1 + i * D);
+    const Mat<D> edk = mat_load<D>(ed + i * DD);
+    if (k < N) {   // transition k: left part and eta_s
+        const int64_t t = b * N + k;
+        ExpToSsm<D> r;
+        exp_to_ssm_step(mk, vec_load<D>(e1 + (i + 1) * D), edk, mat_load<D>(ed + (i + 1) * DD),
+                        mat_load<D>(es + t * DD), r, ok);
+        SsmCotangent<D> c;
+        c.gA = mat_load<D>(gA + t * DD);
+        c.gb = vec_load<D>(gb + t * D);
+        c.gLQ = mat_load<D>(gcholQ + t * DD);
+        Vec<D> Lgm, Rgm;
+        Mat<D> LgS, RgS, ges;
+        exp_to_ssm_step_vjp(r, c, Lgm, LgS, Rgm, RgS, ges);
+        gm = gm + Lgm;
+        gS = gS + LgS;
+        if (k == 0) {   // mu0 = eta1_0, cholP0 = chol(S_0)
+            gm = gm + vec_load<D>(gmu0 + b * D);
+            gS = gS + chol_adjoint(r.LS, tril(mat_load<D>(gcholP0 + b * DD)));
+        }
+        if (ths) ges = mat_load<D>(ths + t * DD) - gamma * ges;
+        mat_store<D>(os + t * DD, ges);
+    }
+    if (k > 0) {   // transition k-1: right part
+        const int64_t t = b * N + k - 1;
+        ExpToSsm<D> r;
+        exp_to_ssm_step(vec_load<D>(e1 + (i - 1) * D), mk, mat_load<D>(ed + (i - 1) * DD), edk,
+                        mat_load<D>(es + t * DD), r, ok);
+        SsmCotangent<D> c;
+        c.gA = mat_load<D>(gA + t * DD);
+        c.gb = vec_load<D>(gb + t * D);
+        c.gLQ = mat_load<D>(gcholQ + t * DD);
+        Vec<D> Lgm, Rgm;
+        Mat<D> LgS, RgS, ges;
+        exp_to_ssm_step_vjp(r, c, Lgm, LgS, Rgm, RgS, ges);
+        gm = gm + Rgm;
+        gS = gS + RgS;
+    }
+    if (!ok) report_not_pd(status, i);
+    // S = eta_d - m m^T
+    gm = gm - 2.0 * mv(sym(gS), mk);
+    if (th1) {
+        gm = vec_load<D>(th1 + i * D) - gamma * gm;
+        gS = mat_load<D>(thd + i * DD) - gamma * gS;
+    }
+    vec_store<D>(o1 + i * D, gm);
+    mat_store<D>(od + i * DD, gS);
+}
+
 }  // namespace vdp

@@ -74,7 +74,7 @@ static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t 
     const SegScratch sc(w.seg, kSegScratchBytes);
     int rc = run_nat2ssm<D>(w.th1, w.thd, w.ths, p.qA, p.qb, p.qcholQ, p.qmu0, p.qcholP0, w.Ld, w.Ls, B, N, p.status,
                             st, sc);
-    if (rc) return rc;
+    if (rc || (p.flags & VDP_FLAG_POSTERIOR_SSM_ONLY)) return rc;
     return run_marginals<D>(p.qA, p.qb, p.qcholQ, p.qmu0, p.qcholP0, p.fx_mus, p.fx_covs, w.Ld, w.Ls, B, N, p.status,
                             st, sc);
 }
@@ -112,6 +112,10 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
         VDP_CHECK_LAUNCH();
     }
     if ((rc = run_posterior<D>(p, w, st))) return rc;
+    if (p.flags & VDP_FLAG_SKIP_GIRSANOV) {
+        if (!(p.flags & VDP_FLAG_SKIP_ELBO)) return run_elbo<DRIFT, D>(p, w, P, st);
+        return VDP_OK;
+    }
     // (B) update_girsanov_sites  variational_cvi_sde.py:279-299
     const size_t n = (size_t)B * (N + 1);
     prof_mark(VDP_PHASE_KL_GRAD, st);
@@ -203,6 +207,7 @@ int vdp_cvi_elbo(const vdp_cvi_problem* p, void* stream) {
     const DriftParams P = make_params(p->drift_params);
     VDP_DISPATCH_D(p->D, VDP_DISPATCH_DRIFT(p->drift_id, {
         if ((rc = run_posterior<kD>(*p, w, as_stream(stream)))) return rc;
+        if (p->flags & VDP_FLAG_POSTERIOR_SSM_ONLY) return VDP_OK;
         if ((rc = run_elbo<kDrift, kD>(*p, w, P, as_stream(stream)))) return rc;
     }));
     return VDP_OK;

@@ -169,4 +169,66 @@ int vdp_expectations_to_ssm(const double* e1, const double* ed, const double* es
     return VDP_OK;
 }
 
+
+int vdp_expectations_to_ssm_vjp(const double* e1, const double* ed, const double* es, const double* gA,
+                                const double* gb, const double* gcholP0, const double* gcholQ, const double* gmu0,
+                                double* g1, double* gd, double* gs, int64_t B, int64_t N, int D, int64_t* status,
+                                void* stream) {
+    VDP_REQUIRE(e1 && ed && es && gA && gb && gcholP0 && gcholQ && gmu0 && g1 && gd && gs && B >= 0 && N >= 1,
+                "pointers, B, N");
+    if (B == 0) return VDP_OK;
+    VDP_DISPATCH_D(D, (k_expectations_to_ssm_vjp<kD><<<grid_for(B * (N + 1), kPtBlock), kPtBlock, 0, as_stream(stream)>>>(
+                          e1, ed, es, gA, gb, gcholP0, gcholQ, gmu0, nullptr, nullptr, nullptr, 0.0, g1, gd, gs, B, N,
+                          status)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+size_t vdp_ssm_natgrad_workspace(int64_t B, int64_t N, int D) {
+    const size_t n = (size_t)B * (N + 1), t = (size_t)B * N, DD = (size_t)D * D;
+    return 2 * (padded(n * D) + padded(n * DD) + padded(t * DD)) + padded(n * D) + padded(n * DD) + padded(n * DD) +
+           padded(t * DD) + kSegScratchBytes;
+}
+
+// SSMNaturalGradient._natgrad_step without momentum (ssm_natgrad.py:121-218):
+//   eta = ssm_to_expectations(ssm); dL/d eta = VJP of expectations_to_ssm_params at eta with dL/d(ssm params);
+//   theta = ssm_to_naturals(ssm); theta <- theta - gamma dL/d eta; ssm <- naturals_to_ssm_params(theta)
+int vdp_ssm_natgrad_step(double* A, double* b, double* cholP0, double* cholQ, double* mu0, const double* dL_dA,
+                         const double* dL_db, const double* dL_dcholP0, const double* dL_dcholQ,
+                         const double* dL_dmu0, double gamma, void* workspace, size_t workspace_bytes, int64_t B,
+                         int64_t N, int D, int64_t* status, void* stream) {
+    VDP_REQUIRE(A && b && cholP0 && cholQ && mu0 && dL_dA && dL_db && dL_dcholP0 && dL_dcholQ && dL_dmu0 && B >= 0 &&
+                    N >= 1, "pointers, B, N");
+    if (B == 0) return VDP_OK;
+    Arena ar(workspace, workspace_bytes);
+    const size_t n = (size_t)B * (N + 1), t = (size_t)B * N, DD = (size_t)D * D;
+    double* e1 = ar.take(n * D);
+    double* edd = ar.take(n * DD);
+    double* ess = ar.take(t * DD);
+    double* th1 = ar.take(n * D);
+    double* thd = ar.take(n * DD);
+    double* ths = ar.take(t * DD);
+    double* m = ar.take(n * D);
+    double* Sd = ar.take(n * DD);
+    double* Ld = ar.take(n * DD);
+    double* Ls = ar.take(t * DD);
+    void* seg = ar.take_bytes(kSegScratchBytes);
+    if (!workspace || !seg) { set_error("workspace too small"); return VDP_E_WORKSPACE; }
+    const SegScratch sc(seg, kSegScratchBytes);
+    cudaStream_t st = as_stream(stream);
+    VDP_DISPATCH_D(D, {
+        int rc = run_marginals<kD>(A, b, cholQ, mu0, cholP0, m, Sd, Ld, Ls, B, N, status, st, sc);
+        if (rc) return rc;
+        k_ssm_to_expectations<kD><<<grid_for(B * (N + 1), kPtBlock), kPtBlock, 0, st>>>(A, m, Sd, e1, edd, ess, B, N);
+        k_ssm_to_naturals<kD><<<grid_for(B * (N + 1), kPtBlock), kPtBlock, 0, st>>>(A, b, cholQ, mu0, cholP0, nullptr,
+                                                                                  nullptr, nullptr, th1, thd, ths, B, N);
+        k_expectations_to_ssm_vjp<kD><<<grid_for(B * (N + 1), kPtBlock), kPtBlock, 0, st>>>(
+            e1, edd, ess, dL_dA, dL_db, dL_dcholP0, dL_dcholQ, dL_dmu0, th1, thd, ths, gamma, th1, thd, ths, B, N, status);
+        VDP_CHECK_LAUNCH();
+        rc = run_nat2ssm<kD>(th1, thd, ths, A, b, cholQ, mu0, cholP0, Ld, Ls, B, N, status, st, sc);
+        if (rc) return rc;
+    });
+    return VDP_OK;
+}
+
 }  // extern "C"

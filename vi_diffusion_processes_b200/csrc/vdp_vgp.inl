@@ -54,7 +54,7 @@ static int check_vgp(const vdp_vgp_problem* p, VgpWs& w) {
 template <int D>
 static int vgp_forward(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st) {
     const int64_t B = p.B, N = p.N;
-    k_vgp_to_ssm<D><<<grid_for(B * N, kPtBlock), kPtBlock, 0, st>>>(p.A, p.b, host_mat<D>(p.q), p.time_grid,
+    k_vgp_to_ssm<D><<<grid_for(B * N, kPtBlock), kPtBlock, 0, st>>>(p.A, p.b, -1.0, host_mat<D>(p.q), p.time_grid,
                                                                     (p.flags & VDP_VGP_STABILIZE) ? 1 : 0, w.sA, w.sb,
                                                                     w.scQ, B, N, p.status);
     VDP_CHECK_LAUNCH();
@@ -180,6 +180,42 @@ static int vgp_elbo(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st) {
     }
 
 extern "C" {
+
+int vdp_linear_drift_to_ssm(const double* A, const double* b, const double* q_host, const double* time_grid,
+                            double* ssm_A, double* ssm_b, double* ssm_cholQ, int64_t B, int64_t N, int D,
+                            int64_t* status, void* stream) {
+    VDP_REQUIRE(A && b && q_host && time_grid && ssm_A && ssm_b && ssm_cholQ && B >= 0 && N >= 1, "pointers, B, N");
+    if (B == 0) return VDP_OK;
+    VDP_DISPATCH_D(D, (k_vgp_to_ssm<kD><<<grid_for(B * N, kPtBlock), kPtBlock, 0, as_stream(stream)>>>(
+                          A, b, 1.0, host_mat<kD>(q_host), time_grid, 0, ssm_A, ssm_b, ssm_cholQ, B, N, status)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+int vdp_sq_drift_difference(int drift_id, const double* params_host, const double* q_host, double dt,
+                            const double* A, const double* b, const double* m, const double* S, double* value,
+                            double* dEdm, double* dEdS, void* workspace, size_t workspace_bytes, int64_t B,
+                            int64_t N, int D, int64_t* status, void* stream) {
+    VDP_REQUIRE(q_host && A && b && m && S && value && B >= 0 && N >= 1, "pointers, B, N");
+    VDP_REQUIRE((dEdm == nullptr) == (dEdS == nullptr), "dEdm and dEdS must both be given or both be NULL");
+    if (B == 0) return VDP_OK;
+    Arena ar(workspace, workspace_bytes);
+    double* terms = workspace ? ar.take((size_t)B * N) : nullptr;
+    if (!terms) { set_error("workspace too small"); return VDP_E_WORKSPACE; }
+    const DriftParams P = make_params(params_host);
+    cudaStream_t st = as_stream(stream);
+    VDP_DISPATCH_D(D, VDP_DISPATCH_DRIFT(drift_id, {
+        constexpr int G = QuadGroup<kD>::value;
+        k_vgp_esde<kDrift, kD, 20, G><<<grid_for(B * N * G, kPtBlock), kPtBlock, 0, st>>>(
+            P, host_mat<kD>(q_host), dt, pi_factor(kD), A, b, m, S, terms, dEdm, dEdS, B, N, status);
+    }));
+    VDP_CHECK_LAUNCH();
+    k_reduce_terms<<<(unsigned)B, 256, 0, st>>>(terms, N, value);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+size_t vdp_sq_drift_difference_workspace(int64_t B, int64_t N, int D) { (void)D; return padded((size_t)B * N); }
 
 size_t vdp_vgp_workspace(int64_t B, int64_t N, int D, int64_t n_obs) { (void)n_obs; return vgp_ws_bytes(B, N, D); }
 

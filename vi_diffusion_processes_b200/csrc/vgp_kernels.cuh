@@ -33,9 +33,9 @@ template <int D> __device__ __forceinline__ Vec<D> vgp_fix(Vec<D> x, double lo, 
     return x;
 }
 
-// LinearDrift(-A, b).to_ssm (+ the stabilize_system clip of vi_sde.py:184-197); one thread per transition
+// LinearDrift(a_sign * A, b).to_ssm (+ the stabilize_system clip of vi_sde.py:184-197); one thread per transition
 template <int D>
-__global__ void k_vgp_to_ssm(const double* __restrict__ A, const double* __restrict__ bv, Mat<D> q,
+__global__ void k_vgp_to_ssm(const double* __restrict__ A, const double* __restrict__ bv, double a_sign, Mat<D> q,
                              const double* __restrict__ time_grid, int stabilize, double* __restrict__ sA,
                              double* __restrict__ sb, double* __restrict__ scQ, int64_t B, int64_t N,
                              int64_t* status) {
@@ -44,7 +44,7 @@ __global__ void k_vgp_to_ssm(const double* __restrict__ A, const double* __restr
     constexpr int DD = D * D;
     const int64_t k = t % N;
     const double delta = time_grid[k + 1] - time_grid[k];
-    Mat<D> At = delta * (-1.0 * mat_load<D>(A + t * DD)) + mat_eye<D>();
+    Mat<D> At = delta * (a_sign * mat_load<D>(A + t * DD)) + mat_eye<D>();
     Vec<D> bt = delta * vec_load<D>(bv + t * D);
     bool ok = true;
     const Mat<D> cQ = chol(delta * q, ok);

@@ -128,6 +128,12 @@ class CviEngine:
         check(_lib.load().vdp_cvi_elbo(C.byref(p), self._stream()), "vdp_cvi_elbo")
         return self.elbo
 
+    def posterior_ssm(self):
+        """dist_q (variational_cvi_sde.py:176-192): rebuild q as an SSM from the sites; marginals untouched."""
+        p = self._problem(0.0, 0.0, flags=_lib.FLAG_POSTERIOR_SSM_ONLY)
+        check(_lib.load().vdp_cvi_elbo(C.byref(p), self._stream()), "vdp_cvi_elbo")
+        return self.qA, self.qb, self.qcholQ, self.qmu0, self.qcholP0
+
     def check_status(self):
         code, idx = ops.read_status(self.status)
         if code != 0:

@@ -222,3 +222,52 @@ def cvi_kl_and_grad(drift_id, params, q, dt, time_grid, x0_mu, x0_cov, A, m, Sd,
                                   _p(m), _p(Sd), _p(kl), _p(g1), _p(gd), _p(gs), _p(ws), nbytes, B, N, D, _p(status),
                                   _stream()), "vdp_cvi_kl_and_grad")
     return kl, (g1, gd, gs)
+
+
+def linear_drift_to_ssm(A, b, q, time_grid, status=None):
+    """LinearDrift.to_ssm (drift.py:64-116): A [B,N,D,D], b [B,N,D] -> SSM transitions, offsets, chol Q."""
+    _req(A, b, time_grid, status)
+    B, N, D = b.shape
+    sA, sb, scQ = torch.empty_like(A), torch.empty_like(b), torch.empty_like(A)
+    check(_lib.load().vdp_linear_drift_to_ssm(_p(A), _p(b), dvec(q.reshape(-1), D * D), _p(time_grid), _p(sA), _p(sb),
+                                              _p(scQ), B, N, D, _p(status), _stream()), "vdp_linear_drift_to_ssm")
+    return sA, sb, scQ
+
+
+def sq_drift_difference(drift_id, params, q, dt, A, b, m, S, want_grads=False, status=None):
+    """sde_utils.py:182-249 with the linear drift (-A, b); m [B,N+1,D], S [B,N+1,D,D]."""
+    _req(A, b, m, S, status)
+    B, N, D = b.shape
+    lib = _lib.load()
+    value = torch.empty(B, dtype=F64, device=A.device)
+    dEdm = torch.empty_like(b) if want_grads else None
+    dEdS = torch.empty_like(A) if want_grads else None
+    nbytes = lib.vdp_sq_drift_difference_workspace(B, N, D)
+    ws = _workspace(nbytes, A.device)
+    check(lib.vdp_sq_drift_difference(int(drift_id), dvec(params, 16), dvec(q.reshape(-1), D * D), float(dt), _p(A),
+                                      _p(b), _p(m), _p(S), _p(value), _p(dEdm), _p(dEdS), _p(ws), nbytes, B, N, D,
+                                      _p(status), _stream()), "vdp_sq_drift_difference")
+    return (value, dEdm, dEdS) if want_grads else value
+
+
+def expectations_to_ssm_vjp(e1, ed, es, gA, gb, gcholP0, gcholQ, gmu0, status=None):
+    """VJP of expectations_to_ssm_params (ssm_natgrad.py:168) -> dL/d(eta1, eta_diag, eta_subdiag)."""
+    _req(e1, ed, es, gA, gb, gcholP0, gcholQ, gmu0, status)
+    B, n, D = e1.shape
+    g1, gd, gs = torch.empty_like(e1), torch.empty_like(ed), torch.empty_like(es)
+    check(_lib.load().vdp_expectations_to_ssm_vjp(_p(e1), _p(ed), _p(es), _p(gA), _p(gb), _p(gcholP0), _p(gcholQ),
+                                                  _p(gmu0), _p(g1), _p(gd), _p(gs), B, n - 1, D, _p(status),
+                                                  _stream()), "vdp_expectations_to_ssm_vjp")
+    return g1, gd, gs
+
+
+def ssm_natgrad_step(A, b, cholP0, cholQ, mu0, dL_dA, dL_db, dL_dcholP0, dL_dcholQ, dL_dmu0, gamma, status=None):
+    """In-place natural-gradient step on the SSM parameters (ssm_natgrad.py:121-218, momentum=False)."""
+    _req(A, b, cholP0, cholQ, mu0, dL_dA, dL_db, dL_dcholP0, dL_dcholQ, dL_dmu0, status)
+    B, N, D = b.shape
+    lib = _lib.load()
+    nbytes = lib.vdp_ssm_natgrad_workspace(B, N, D)
+    ws = _workspace(nbytes, A.device)
+    check(lib.vdp_ssm_natgrad_step(_p(A), _p(b), _p(cholP0), _p(cholQ), _p(mu0), _p(dL_dA), _p(dL_db), _p(dL_dcholP0),
+                                   _p(dL_dcholQ), _p(dL_dmu0), float(gamma), _p(ws), nbytes, B, N, D, _p(status),
+                                   _stream()), "vdp_ssm_natgrad_step")
