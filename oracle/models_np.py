@@ -381,32 +381,14 @@ def ssm_natgrad_step(ssm: StateSpaceModel, dL_dssm, gamma: float):
     """
     ssm_natgrad.py:121-218, plain step (momentum=False): theta <- theta - gamma dL/d eta with
     dL/d eta = J^T dL/d(ssm params), J the Jacobian of expectations_to_ssm_params at the current
-    expectation parameters.  ``dL_dssm`` = gradients with respect to (A, b, chol_P0, chol_Q, mu0).
-    The vector-Jacobian product is taken by central differences here (oracle use: tiny cases only).
+    expectation parameters (sde_np.expectations_to_ssm_params_vjp, checked against torch.autograd in
+    tests/test_oracle_ssm.py).  ``dL_dssm`` = gradients with respect to (A, b, chol_P0, chol_Q, mu0).
     """
-    etas = list(ssm_to_expectations(ssm))
-    thetas = list(ssm_to_naturals(ssm))
-
-    def f(e0, e1, e2):
-        return expectations_to_ssm_params(e0, e1, e2)
-
-    def inner(out):
-        return sum(np.sum(np.tril(o) * g) if o.ndim >= 2 and o.shape[-1] == o.shape[-2] and i in (2, 3)
-                   else np.sum(o * g) for i, (o, g) in enumerate(zip(out, dL_dssm)))
-
-    grads = []
-    for i in range(3):
-        g = np.zeros_like(etas[i])
-        it = np.nditer(etas[i], flags=["multi_index"])
-        for _ in it:
-            idx = it.multi_index
-            h = 1e-6 * max(1.0, abs(etas[i][idx]))
-            ep = [e.copy() for e in etas]
-            em = [e.copy() for e in etas]
-            ep[i][idx] += h
-            em[i][idx] -= h
-            g[idx] = (inner(f(*ep)) - inner(f(*em))) / (2 * h)
-        grads.append(g)
+    from .sde_np import expectations_to_ssm_params_vjp
+    etas = ssm_to_expectations(ssm)
+    thetas = ssm_to_naturals(ssm)
+    dL_dA, dL_db, dL_dP0, dL_dQ, dL_dmu0 = dL_dssm
+    grads = expectations_to_ssm_params_vjp(*etas, dL_dA, dL_db, dL_dP0, dL_dQ, dL_dmu0)
     new_thetas = [t - gamma * g for t, g in zip(thetas, grads)]
     As, offsets, chol_P0, chol_Q, mu0 = naturals_to_ssm_params(*new_thetas)
     return StateSpaceModel(mu0, chol_P0, As, offsets, chol_Q)

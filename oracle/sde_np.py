@@ -498,6 +498,44 @@ def cholesky_adjoint(L, Lbar):
     return 0.5 * (P + mT(P))
 
 
+def expectations_to_ssm_params_vjp(exp1, exp_diag, exp_sub_diag, g_A, g_b, g_cholP0, g_cholQ, g_mu0):
+    """
+    Vector-Jacobian product of expectations_to_ssm_params (ssm_gaussian_transformations.py:93-178) -- what
+    ``tape.gradient(ssm_params, etas, output_gradients=dL_dssm)`` returns at ssm_natgrad.py:168.  Same
+    statement-by-statement adjoint as in :func:`sde_ssm_kl_and_grads`; the gradient through a Cholesky is the
+    symmetrised one TensorFlow registers.  Cotangents of the Cholesky factors are lower triangular.
+    """
+    m = np.asarray(exp1, dtype=np.float64)
+    sym = lambda X: 0.5 * (X + mT(X))
+    mcol = m[..., None]
+    S = exp_diag - mcol @ mT(mcol)
+    Csub = mT(exp_sub_diag) - mcol[:-1] @ mT(mcol[1:])
+    LS = chol(S)
+    A = mT(chol_solve(LS[:-1], Csub))
+    Qc = S[1:] - A @ (S[:-1] @ mT(A))
+    LQ = chol(Qc)
+    g_m = np.zeros_like(m)
+    g_S = np.zeros_like(S)
+    g_A = np.array(g_A, dtype=np.float64)
+    g_b = np.asarray(g_b, dtype=np.float64)
+    g_Qc = cholesky_adjoint(LQ, np.tril(g_cholQ))
+    g_m[1:] += g_b
+    g_A += -g_b[..., None] @ mT(mcol[:-1])
+    g_m[:-1] += -(mT(A) @ g_b[..., None])[..., 0]
+    g_S[1:] += g_Qc
+    g_A += -2.0 * g_Qc @ A @ S[:-1]
+    g_S[:-1] += -mT(A) @ g_Qc @ A
+    g_C = chol_solve(LS[:-1], mT(g_A))
+    g_S[:-1] += sym(-g_C @ A)
+    g_m[0] += g_mu0
+    g_S[0] += cholesky_adjoint(LS[0], np.tril(g_cholP0))
+    g_eta_s = mT(g_C)
+    g_m[:-1] += -(g_C @ mcol[1:])[..., 0]
+    g_m[1:] += -(mT(g_C) @ mcol[:-1])[..., 0]
+    g_m += -2.0 * (g_S @ mcol)[..., 0]
+    return g_m, g_S, g_eta_s
+
+
 def gaussian_kl(mu_q, cov_q, mu_p, cov_p):
     """tfp kl_divergence(MultivariateNormalFullCovariance q, p) in closed form."""
     D = mu_q.shape[-1]

@@ -169,8 +169,10 @@ def test_sde_expectations_and_linearize(mf):
     want = S.squared_drift_difference_along_Gaussian_path(osde, S.LinearDrift(A, b), S.Gaussian(m[0], Sg[0]), 0.01)
     assert abs(val.item() - want) < TOL * abs(want)
     ssm = ld.to_ssm(np.ones((1, 1)), grid, np.zeros(1), np.eye(1))
-    ossm = S.LinearDrift(A, b).to_ssm(np.ones((1, 1)), grid, np.zeros(1), np.eye(1))
+    ossm = S.LinearDrift(A, b).to_ssm(q=np.ones((n, 1, 1)), transition_times=grid, initial_mean=np.zeros(1),
+                                      initial_chol_covariance=np.eye(1))
     assert rel(ssm.state_transitions, ossm.state_transitions) < TOL
+    assert rel(ssm.state_offsets, ossm.state_offsets) < TOL
     assert rel(ssm.cholesky_process_covariances, ossm.cholesky_process_covariances) < TOL
 
 
@@ -211,7 +213,7 @@ def test_cvi_sites_sde_reference_calls(mf):
             ref.relinearize()
             assert rel(model.dist_p.state_transitions, ref.dist_p.state_transitions) < TOL
     g = model.grad_kl_wrt_exp_param()
-    og = ref.grad_kl_wrt_exp_param()
+    _, og = ref.grad_kl_wrt_exp_param()
     for a, b in zip(g, og):
         assert rel(a, b) < 1e-8
 

@@ -109,3 +109,78 @@ def test_log_pdf_matches_dense():
     d = x.reshape(-1) - m
     expect = -0.5 * d @ P @ d + 0.5 * np.linalg.slogdet(P)[1] - 0.5 * d.size * np.log(2 * np.pi)
     np.testing.assert_allclose(ssm.log_pdf(x), expect, rtol=1e-9)
+
+
+def _exp_to_ssm_torch(e1, ed, es):
+    """expectations_to_ssm_params (ssm_gaussian_transformations.py:93-178) op by op in torch float64."""
+    import torch
+    el = e1[..., None]
+    mcov = ed - el @ el.transpose(-1, -2)
+    csub = es.transpose(-1, -2) - el[:-1] @ el[1:].transpose(-1, -2)
+    mch = torch.linalg.cholesky(mcov)
+    As = torch.cholesky_solve(csub, mch[:-1]).transpose(-1, -2)
+    b = (el[1:] - As @ el[:-1])[..., 0]
+    ccov = mcov[1:] - As @ (mcov[:-1] @ As.transpose(-1, -2))
+    return As, b, mch[0], torch.linalg.cholesky(ccov), el[0, :, 0]
+
+
+@pytest.mark.parametrize("D", [1, 2, 3])
+def test_expectations_to_ssm_vjp_matches_autograd(D):
+    """The chain-rule step of SSMNaturalGradient (ssm_natgrad.py:168): hand adjoint vs torch.autograd (torch's
+    Cholesky backward is the same symmetrised formula TensorFlow registers)."""
+    torch = pytest.importorskip("torch")
+    from oracle.sde_np import expectations_to_ssm_params_vjp
+    rng = np.random.default_rng(12 + D)
+    ssm = _ssm(rng, (), D, 6, stable=True)
+    e = [np.ascontiguousarray(x) for x in ssm_to_expectations(ssm)]
+    te = [torch.tensor(x, dtype=torch.float64, requires_grad=True) for x in e]
+    outs = _exp_to_ssm_torch(*te)
+    cot = [rng.normal(size=tuple(o.shape)) for o in outs]
+    cot[2], cot[3] = np.tril(cot[2]), np.tril(cot[3])
+    want = torch.autograd.grad(outs, te, grad_outputs=[torch.tensor(c) for c in cot])
+    got = expectations_to_ssm_params_vjp(*e, cot[0], cot[1], cot[2], cot[3], cot[4])
+    sym = lambda X: 0.5 * (X + np.swapaxes(X, -1, -2))
+    np.testing.assert_allclose(got[0], want[0].numpy(), rtol=1e-9, atol=1e-10)
+    np.testing.assert_allclose(sym(got[1]), sym(want[1].numpy()), rtol=1e-9, atol=1e-10)
+    np.testing.assert_allclose(got[2], want[2].numpy(), rtol=1e-9, atol=1e-10)
+
+
+def test_natgrad_step_with_unit_gamma_solves_a_conjugate_problem():
+    """Natural gradient with gamma = 1 on L = KL[q || p] jumps to q = p when the loss is expressed in the
+    expectation parameters linearly (conjugacy): here L = <eta(q), theta(q0) - theta(p)> has dL/d eta constant,
+    so one step from q0 with that gradient lands exactly on theta(p)."""
+    from oracle.models_np import ssm_natgrad_step
+    from oracle.sde_np import expectations_to_ssm_params_vjp
+    rng = np.random.default_rng(13)
+    q0 = _ssm(rng, (), 2, 5, stable=True)
+    p = _ssm(rng, (), 2, 5, stable=True)
+    tq, tp = ssm_to_naturals(q0), ssm_to_naturals(p)
+    g_eta = [a - b for a, b in zip(tq, tp)]          # desired dL/d eta
+    # find dL/d(ssm params) with J^T dL_dssm = g_eta by solving the small linear system column by column
+    e = ssm_to_expectations(q0)
+    shapes = [(5, 2, 2), (5, 2), (2, 2), (5, 2, 2), (2,)]
+    sizes = [int(np.prod(s)) for s in shapes]
+    cols = []
+    for i in range(sum(sizes)):
+        v = np.zeros(sum(sizes))
+        v[i] = 1.0
+        parts = [x.reshape(s) for x, s in zip(np.split(v, np.cumsum(sizes)[:-1]), shapes)]
+        if np.any(np.triu(parts[2], 1)) or np.any(np.triu(parts[3], 1)):
+            cols.append(None)
+            continue
+        g = expectations_to_ssm_params_vjp(*e, parts[0], parts[1], parts[2], parts[3], parts[4])
+        gd = np.tril(g[1]) + np.tril(g[1], -1)      # count the symmetric pair once (lower storage)
+        cols.append(np.concatenate([g[0].ravel(), gd.ravel(), g[2].ravel()]))
+    keep = [i for i, c in enumerate(cols) if c is not None]
+    J = np.stack([cols[i] for i in keep], axis=1)
+    gdl = np.tril(g_eta[1]) + np.tril(g_eta[1], -1)
+    rhs = np.concatenate([g_eta[0].ravel(), gdl.ravel(), g_eta[2].ravel()])
+    sol, *_ = np.linalg.lstsq(J, rhs, rcond=None)
+    np.testing.assert_allclose(J @ sol, rhs, atol=1e-8)
+    v = np.zeros(sum(sizes))
+    v[keep] = sol
+    dL = [x.reshape(s) for x, s in zip(np.split(v, np.cumsum(sizes)[:-1]), shapes)]
+    new = ssm_natgrad_step(q0, dL, 1.0)
+    np.testing.assert_allclose(new.state_transitions, p.state_transitions, atol=1e-6)
+    np.testing.assert_allclose(new.state_offsets, p.state_offsets, atol=1e-6)
+    np.testing.assert_allclose(new.cholesky_process_covariances, p.cholesky_process_covariances, atol=1e-6)
