@@ -112,8 +112,9 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def cpu_oracle_steps_per_s(B, N, seed, updates=1):
-    """The oracle (NumPy port, oracle/scalar_d1.py) timed on the host on a bounded sample of the workload."""
+def _oracle_worker(args):
+    """One host process: the NumPy oracle on its own sub-batch of sequences (fork-safe, no GPU touched)."""
+    B, N, seed, updates = args
     from oracle import scalar_d1
     from oracle.sde_np import DRIFT_DW
     grid, idx, y = make_problem(B, N, seed)
@@ -122,8 +123,23 @@ def cpu_oracle_steps_per_s(B, N, seed, updates=1):
     t0 = time.perf_counter()
     for _ in range(updates):
         ref.site_update(LR, LR)
-    dt = time.perf_counter() - t0
-    return B * N * updates / dt, dt
+    return time.perf_counter() - t0
+
+
+def cpu_oracle_steps_per_s(B_per_core, N, seed, updates=1, cores=None):
+    """The oracle (NumPy port, oracle/scalar_d1.py) timed on the host cores on a bounded sample of the workload:
+    one process per core, B_per_core sequences each (sequences are independent, like the GPU sharding).
+    Returns (grid-steps/s over all cores, wall seconds of the slowest worker, cores)."""
+    import multiprocessing as mp
+    cores = cores or len(os.sched_getaffinity(0))
+    jobs = [(B_per_core, N, seed + 1000 * c, updates) for c in range(cores)]
+    if cores == 1:
+        times = [_oracle_worker(jobs[0])]
+    else:
+        with mp.get_context("fork").Pool(cores) as pool:
+            times = pool.map(_oracle_worker, jobs)
+    dt = max(times)
+    return B_per_core * cores * N * updates / dt, dt, cores
 
 
 # algorithmic (compulsory) float64 values moved per grid step by each phase's kernels: (vectors, matrices)
@@ -230,6 +246,8 @@ def run_ours(args):
     e2e_steps = max(2, args.steps // 2)
 
     if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
         return
     steps_total = B * N * world
     value = steps_total * args.steps / (ms_total * 1e-3)
@@ -244,10 +262,10 @@ def run_ours(args):
     tpath = os.path.join(ROOT, "profiles", "dominant_kernel_traffic.json")
     if os.path.exists(tpath):
         t = json.load(open(tpath))
-        if t.get("kernel_phase") == dom and t.get("B") == B and t.get("N") == N:
-            traffic = t.get("dram_bytes_per_launch")
-    cpu_B = 32
-    cpu_val, cpu_s = cpu_oracle_steps_per_s(cpu_B, N, seed=4096)
+        if t.get("B") == B and t.get("N") == N:
+            traffic = t.get("dram_bytes_per_launch_by_phase", {}).get(dom)
+    cpu_B = 64
+    cpu_val, cpu_s, cpu_cores = cpu_oracle_steps_per_s(cpu_B, N, seed=4096, updates=2)
     line = {
         "metric": "grid-steps/sec per CVI-DP site update", "value": value, "unit": "grid-steps/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
@@ -268,40 +286,33 @@ def run_ours(args):
                             "achieved": value * ALGO_BYTES_PER_STEP_D1 / world / 1e9, "peak": peak, "unit": "GB/s",
                             "frac": value * ALGO_BYTES_PER_STEP_D1 / world / 1e9 / peak},
         "phases": phases,
-        "cpu_baseline": {"value": cpu_val, "unit": "grid-steps/s", "cores": 1, "kind": "port",
-                         "sample": f"{cpu_B} sequences x {N} grid steps, 1 site update, NumPy oracle "
-                                   f"(oracle/scalar_d1.py), {cpu_s:.1f} s"},
+        "cpu_baseline": {"value": cpu_val, "unit": "grid-steps/s", "cores": cpu_cores, "kind": "port",
+                         "sample": f"{cpu_cores} processes x {cpu_B} sequences x {N} grid steps x 2 site updates, "
+                                   f"NumPy oracle (oracle/scalar_d1.py), {cpu_s:.1f} s"},
     }
     print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def run_reference(args):
-    """The reference's CPU path = the oracle port (TensorFlow is not installable here)."""
+    """The reference's CPU path = the oracle port on all host cores (TensorFlow is not installable here)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    B = args.ref_seqs
-    times = []
-    from oracle import scalar_d1
-    from oracle.sde_np import DRIFT_DW
-    grid, idx, y = make_problem(B, args.grid, seed=4096)
-    ref = scalar_d1.BatchedCVISitesSDE1D(DRIFT_DW, DW_PARAMS, 1.0, grid, idx, y, NOISE_STD, X0_MU, X0_COV)
-    for _ in range(max(1, min(args.warmup, 1))):
-        ref.site_update(LR, LR)
     steps = max(1, min(args.steps, 3))
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        ref.site_update(LR, LR)
-    dt = time.perf_counter() - t0
-    value = B * args.grid * steps / dt
+    B = args.ref_seqs
+    value, dt, cores = cpu_oracle_steps_per_s(B, args.grid, seed=4096, updates=steps)
     line = {
         "impl": "reference", "metric": "grid-steps/sec per CVI-DP site update", "value": value,
         "unit": "grid-steps/s", "n_gpus": args.gpus, "steps": steps, "warmup": 1, "ms_per_step": dt / steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "C4: independent double-well sequences x dense grid, one CVI-DP site update per step",
-                   "sequences": B, "grid_steps": args.grid, "state_dim": 1, "dt": DT, "n_obs": N_OBS, "quad_H": 20},
-        "cpu_baseline": {"value": value, "unit": "grid-steps/s", "cores": 1, "kind": "port",
-                         "sample": f"{B} sequences x {args.grid} grid steps x {steps} site updates (bounded sample)"},
+                   "sequences": B * cores, "grid_steps": args.grid, "state_dim": 1, "dt": DT, "n_obs": N_OBS,
+                   "quad_H": 20},
+        "cpu_baseline": {"value": value, "unit": "grid-steps/s", "cores": cores, "kind": "port",
+                         "sample": f"{cores} processes x {B} sequences x {args.grid} grid steps x {steps} site updates "
+                                   f"(bounded sample of the 4096-sequence workload)"},
         "e2e": {"value": value, "unit": "grid-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -315,7 +326,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--seqs", type=int, default=4096, help="sequences per GPU")
     ap.add_argument("--grid", type=int, default=10000, help="grid steps per sequence")
-    ap.add_argument("--ref-seqs", type=int, default=32, help="sequences in the bounded CPU sample")
+    ap.add_argument("--ref-seqs", type=int, default=64, help="sequences per host core in the bounded CPU sample")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
