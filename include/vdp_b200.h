@@ -264,6 +264,54 @@ int vdp_vgp_elbo(const vdp_vgp_problem* problem_host, void* stream);
 int vdp_vgp_sweep(const vdp_vgp_problem* problem_host, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Time-segment sharding of one long sequence over ranks (BASELINE config 5).  Rank r owns the contiguous
+ * transitions [s_r, e_r) of the grid (N_local = e_r - s_r) and runs the tiled sweeps on them; ranks exchange
+ * one associative element per sweep ("total") and the natural initial state of the first / last rank
+ * ("init"), e.g. with an NCCL all-gather of vdp_dist_blob_bytes() bytes each.  Sequence per sweep:
+ *     vdp_dist_sweep_summary(p, total, init)            -> this rank's blobs (device memory)
+ *     all-gather -> all_totals [nranks x total_bytes], all_inits [nranks x init_bytes] (device memory)
+ *     vdp_dist_sweep_finish(p, all_totals, all_inits)   -> outputs of the local range
+ * VDP_SWEEP_NAT2SSM has two dependent recursions: summary(stage 0) -> gather -> summary(stage 1, with
+ * prev_totals / prev_inits = the gathered stage-0 blobs) -> gather -> finish (stage-1 blobs).
+ *
+ * Local arrays (one sequence, B = 1; D x D blocks row-major) and their halo slots:
+ *   VDP_SWEEP_CHOL     in[0] Kd [N_local+1]  (last block = first node of the next rank; on the last rank the
+ *                      final node), in[1] Ks [N_local]; scaleD / scaleS multiply them (-2 / -1 for naturals);
+ *                      out[0] Ld [N_local+1], out[1] Ls [N_local]
+ *   VDP_SWEEP_NAT2SSM  in[0] Ld, in[1] Ls, in[2] th1 [N_local(+1 on the last rank), D], in[3] thd, in[4] ths;
+ *                      out[0] A [N_local], out[1] b, out[2] cholQ: pointers to the slot of transition s_r, the
+ *                      slot BEFORE it must exist on ranks > 0 (it receives the output of node s_r);
+ *                      out[3] mu0, out[4] cholP0 (rank 0 only)
+ *   VDP_SWEEP_MARG     in[0] A [N_local+1] (last = first transition of the next rank, unused on the last
+ *                      rank), in[1] b [N_local], in[2] cholQ (slot -1 = factor of node s_r on ranks > 0, slot
+ *                      N_local = halo as for A), in[3] mu0, in[4] cholP0 (rank 0 only);
+ *                      out[0] m [N_local+1, D], out[1] Ld [N_local+1], out[2] Ls [N_local]
+ *   VDP_SWEEP_INVBAND  in[0] Ld, in[1] Ls; out[0] Sd [N_local (+1 on the last rank)], out[1] Ss or NULL
+ * ---------------------------------------------------------------------------------------------- */
+enum { VDP_SWEEP_CHOL = 0, VDP_SWEEP_NAT2SSM = 1, VDP_SWEEP_MARG = 2, VDP_SWEEP_INVBAND = 3 };
+
+typedef struct vdp_dist_sweep {
+    int32_t kind, stage;
+    int32_t rank, nranks;
+    int64_t N_local;
+    int32_t D, reserved;
+    double scaleD, scaleS;
+    const double* in[8];
+    double* out[8];
+    const void* prev_totals;   /* NAT2SSM stage 1: gathered stage-0 blobs */
+    const void* prev_inits;
+    void* workspace;           /* vdp_dist_workspace(D) bytes, the SAME buffer for all calls of one sweep */
+    size_t workspace_bytes;
+    int64_t* status;
+} vdp_dist_sweep;
+
+size_t vdp_dist_workspace(int D);
+int vdp_dist_blob_bytes(int kind, int stage, int D, size_t* total_bytes, size_t* init_bytes);
+int vdp_dist_sweep_summary(const vdp_dist_sweep* sweep_host, void* total_blob, void* init_blob, void* stream);
+int vdp_dist_sweep_finish(const vdp_dist_sweep* sweep_host, const void* all_totals, const void* all_inits,
+                          void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * diagnostics: per-phase device time of the fused pipelines (CUDA events on the launching stream).
  * vdp_profile_enable(1) starts recording (and clears earlier marks); vdp_profile_read synchronises on
  * the last mark, returns accumulated milliseconds and number of spans per phase, and clears the marks.

@@ -33,7 +33,8 @@ def test_library_exports_every_declared_symbol():
     assert lib.vdp_version() >= 100
 
 
-@pytest.mark.parametrize("struct_name,cls_name", [("vdp_cvi_problem", "CviProblem"), ("vdp_vgp_problem", "VgpProblem")])
+@pytest.mark.parametrize("struct_name,cls_name", [("vdp_cvi_problem", "CviProblem"), ("vdp_vgp_problem", "VgpProblem"),
+                                                  ("vdp_dist_sweep", "DistSweep")])
 def test_struct_layout_matches_header_field_order(struct_name, cls_name):
     from vi_diffusion_processes_b200 import _lib
     CviProblem = getattr(_lib, cls_name)

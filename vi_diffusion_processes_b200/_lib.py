@@ -71,6 +71,23 @@ class VgpProblem(C.Structure):
     ]
 
 
+class DistSweep(C.Structure):
+    """Mirror of ``struct vdp_dist_sweep`` (include/vdp_b200.h)."""
+    _fields_ = [
+        ("kind", C.c_int32), ("stage", C.c_int32),
+        ("rank", C.c_int32), ("nranks", C.c_int32),
+        ("N_local", i64),
+        ("D", C.c_int32), ("reserved", C.c_int32),
+        ("scaleD", C.c_double), ("scaleS", C.c_double),
+        ("in", vp * 8),
+        ("out", vp * 8),
+        ("prev_totals", vp), ("prev_inits", vp),
+        ("workspace", vp), ("workspace_bytes", C.c_size_t),
+        ("status", vp),
+    ]
+
+
+SWEEP_CHOL, SWEEP_NAT2SSM, SWEEP_MARG, SWEEP_INVBAND = 0, 1, 2, 3
 FLAG_SKIP_DATA_UPDATE, FLAG_SKIP_ELBO, FLAG_SKIP_GIRSANOV, FLAG_POSTERIOR_SSM_ONLY = 1, 2, 4, 8
 VGP_STABILIZE = 1
 VGP_UPDATE_X0 = 2
@@ -115,6 +132,10 @@ SIGNATURES = {
     "vdp_vgp_update_initial_statistics": (C.c_int, [C.POINTER(VgpProblem), vp]),
     "vdp_vgp_elbo": (C.c_int, [C.POINTER(VgpProblem), vp]),
     "vdp_vgp_sweep": (C.c_int, [C.POINTER(VgpProblem), vp]),
+    "vdp_dist_workspace": (C.c_size_t, [C.c_int]),
+    "vdp_dist_blob_bytes": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "vdp_dist_sweep_summary": (C.c_int, [C.POINTER(DistSweep), vp, vp, vp]),
+    "vdp_dist_sweep_finish": (C.c_int, [C.POINTER(DistSweep), vp, vp, vp]),
     "vdp_profile_enable": (C.c_int, [C.c_int]),
     "vdp_profile_read": (C.c_int, [c_dp, c_i64p, C.c_int]),
 }

@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(T)
 k_chol_tiled(const double* __restrict__ Xd, const double* __restrict__ Xs, double scaleD, double scaleS,
              double* __restrict__ Ld, double* __restrict__ Ls, int64_t B, int64_t N, int nseg, int64_t seg_len,
              const Mat<D>* __restrict__ carry_in, Mat<D>* __restrict__ init_out,
-             SchurElem<D>* __restrict__ seg_elem, int64_t* status) {
+             SchurElem<D>* __restrict__ seg_elem, int64_t* status, int first = 1) {
     constexpr int DD = D * D, TL = T * L;
     extern __shared__ __align__(16) double smem[];
     double* sKd = smem;
@@ -142,7 +142,7 @@ k_chol_tiled(const double* __restrict__ Xd, const double* __restrict__ Xs, doubl
     const double* xd = Xd + b * (N + 1) * DD;
     const double* xs = Xs + b * N * DD;
     Mat<D> S_tile = mat_zero<D>();
-    if (MODE == SWEEP_FULL && seg > 0) S_tile = carry_in[b * nseg + seg];
+    if (MODE == SWEEP_FULL && (seg > 0 || !first)) S_tile = carry_in[b * nseg + seg];
     SchurElem<D> seg_tot = SchurOps<D>::identity();
     for (int64_t tk = t0; tk < t1; tk += TL) {
         const int cnt = (int)min((int64_t)TL, t1 - tk);
@@ -153,7 +153,7 @@ k_chol_tiled(const double* __restrict__ Xd, const double* __restrict__ Xs, doubl
         stage_scale<T>(sKd, (int64_t)(cnt + 1) * DD, scaleD);
         stage_scale<T>(sKs, (int64_t)cnt * DD, scaleS);
         __syncthreads();
-        if (seg == 0 && tk == 0) {
+        if (seg == 0 && tk == 0 && first) {
             S_tile = mat_load<D>(sKd);
             if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = S_tile;
         }
@@ -196,7 +196,7 @@ k_marg_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
              double* __restrict__ Ld, double* __restrict__ Ls, int64_t B, int64_t N, int nseg, int64_t seg_len,
              const typename MargOps<D>::State* __restrict__ carry_in,
              typename MargOps<D>::State* __restrict__ init_out,
-             typename MargOps<D>::Elem* __restrict__ seg_elem, int64_t* status) {
+             typename MargOps<D>::Elem* __restrict__ seg_elem, int64_t* status, int first = 1, int last = 1) {
     constexpr int DD = D * D, TL = T * L;
     using Ops = MargOps<D>;
     extern __shared__ __align__(16) double smem[];
@@ -212,14 +212,16 @@ k_marg_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
     typename Ops::State st;
     st.a = mat_zero<D>();
     st.b = vec_zero<D>();
-    if (MODE == SWEEP_FULL && seg > 0) st = carry_in[b * nseg + seg];
+    if (MODE == SWEEP_FULL && (seg > 0 || !first)) st = carry_in[b * nseg + seg];
     typename Ops::Elem seg_tot = Ops::identity();
     for (int64_t tk = t0; tk < t1; tk += TL) {
         const int cnt = (int)min((int64_t)TL, t1 - tk);
-        const bool halo_has_next = tk + cnt < N;
+        // time-sharded ranks: the arrays carry one halo transition past N (from the next rank) and cholQ one
+        // before index 0 (the factor of this rank's first node)
+        const bool halo_has_next = (tk + cnt < N) || !last;
         __syncthreads();
         // node factors: node k -> cholQ[k-1], node 0 -> cholP0
-        if (tk == 0) {
+        if (tk == 0 && first) {
             stage_in<T>(sC, cholP0 + b * DD, DD);
             stage_in<T>(sC + DD, cholQ + b * N * DD, (int64_t)(cnt + (halo_has_next ? 1 : 0)) * DD);
         } else {
@@ -240,12 +242,12 @@ k_marg_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
         }
         __syncthreads();
         if (seg == 0 && tk == 0) {
-            st.a = mat_load<D>(sKd);
-            st.b = vec_load<D>(mu0 + b * D);
-            if (threadIdx.x == 0) {
-                if (MODE == SWEEP_FULL) vec_store<D>(m + b * (N + 1) * D, st.b);
-                else init_out[b] = st;
+            if (first) {
+                st.a = mat_load<D>(sKd);
+                st.b = vec_load<D>(mu0 + b * D);
+                if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = st;
             }
+            if (MODE == SWEEP_FULL && threadIdx.x == 0) vec_store<D>(m + b * (N + 1) * D, st.b);
         }
         const int k0 = threadIdx.x * L;
         const int len = min(L, cnt - k0);
@@ -323,7 +325,7 @@ __global__ void __launch_bounds__(T)
 k_invband_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, double* __restrict__ Sd,
                 double* __restrict__ Ss, int64_t B, int64_t N, int nseg, int64_t seg_len,
                 const Mat<D>* __restrict__ carry_in, Mat<D>* __restrict__ init_out,
-                AffSymElem<D>* __restrict__ seg_elem) {
+                AffSymElem<D>* __restrict__ seg_elem, int last = 1) {
     constexpr int DD = D * D, TL = T * L;
     using Ops = AffSymOps<D>;
     extern __shared__ __align__(16) double smem[];
@@ -334,7 +336,7 @@ k_invband_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, do
     const int seg = (int)(blockIdx.x % nseg);
     const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
     Mat<D> S_tile;
-    if (t1 == N) {
+    if (t1 == N && last) {
         S_tile = invband_last(mat_load<D>(Ld + (b * (N + 1) + N) * DD));
         if (threadIdx.x == 0) {
             if (MODE == SWEEP_FULL) mat_store<D>(Sd + (b * (N + 1) + N) * DD, S_tile);
@@ -397,7 +399,7 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
                 double* __restrict__ cholP0, int64_t B, int64_t N, int nseg, int64_t seg_len,
                 const Mat<D>* __restrict__ carryS, const Vec<D>* __restrict__ carryY, Mat<D>* __restrict__ initS,
                 Vec<D>* __restrict__ initY, AffSymElem<D>* __restrict__ seg_elemS,
-                AffVecElem<D>* __restrict__ seg_elemY, int64_t* status) {
+                AffVecElem<D>* __restrict__ seg_elemY, int64_t* status, int first = 1, int last = 1) {
     constexpr int DD = D * D, TL = T * L;
     extern __shared__ __align__(16) double smem[];
     double* sLd = smem;              // L_kk  -> chol of the conditional covariance of node k
@@ -413,7 +415,7 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
     const int64_t n = N + 1;
     Mat<D> S_tile = mat_zero<D>();
     Vec<D> y_tile = vec_zero<D>();
-    if (t1 == N) {
+    if (t1 == N && last) {
         S_tile = invband_last(mat_load<D>(Ld + (b * n + N) * DD));
         y_tile = vec_load<D>(th1 + (b * n + N) * D);
         if (threadIdx.x == 0) {
@@ -492,7 +494,7 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
         }
         __syncthreads();
         stage_out<T>(A + (b * N + lo) * DD, sLs, (int64_t)cnt * DD);
-        if (lo >= 1) {
+        if (lo >= 1 || !first) {   // time-sharded ranks own one slot before index 0 of bo / cholQ
             stage_out<T>(bo + (b * N + lo - 1) * D, sT1, (int64_t)cnt * D);
             stage_out<T>(cholQ + (b * N + lo - 1) * DD, sLd, (int64_t)cnt * DD);
         } else {

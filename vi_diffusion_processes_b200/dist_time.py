@@ -1,0 +1,248 @@
+"""
+Time-segment sharding of ONE long sequence over ranks (BASELINE config 5): the posterior rebuild
+(naturals -> state-space model -> marginals; variational_cvi_sde.py:176-192 + gauss_markov.py:107-117) with
+every rank holding a contiguous range of the grid.
+
+What crosses ranks per sweep is one associative element and one initial state (``vdp_dist_blob_bytes`` bytes,
+a few hundred) plus one-block halos of the inputs; the exchange is an all-gather over ``torch.distributed``
+(NCCL on GPUs; gloo in the CPU tests of the plumbing).  The sweeps themselves are the tiled CUDA kernels
+(``vdp_dist_sweep_summary`` / ``vdp_dist_sweep_finish``).
+
+The algorithm is written in lockstep over a list of rank states so that the same code runs
+  * distributed: the list holds this process's rank, ``Comm`` gathers over the process group;
+  * emulated: the list holds all R ranks of one process / one GPU (tests, no second GPU needed).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import torch
+
+from . import _lib
+from ._lib import DistSweep, check
+
+F64 = torch.float64
+
+
+def time_partition(N: int, nranks: int):
+    """Contiguous transition ranges [s_r, e_r) covering [0, N); the last rank also owns grid point N."""
+    base, extra = divmod(N, nranks)
+    out, s = [], 0
+    for r in range(nranks):
+        e = s + base + (1 if r < extra else 0)
+        out.append((s, e))
+        s = e
+    if any(e - s < 1 for s, e in out):
+        raise ValueError(f"cannot split {N} transitions over {nranks} ranks")
+    return out
+
+
+class Comm:
+    """All-gather of one small tensor per rank.  ``ranks`` = the ranks driven by this process."""
+
+    def __init__(self, nranks: int, local_ranks: List[int], group=None):
+        self.nranks, self.local_ranks, self.group = nranks, list(local_ranks), group
+        self.distributed = len(self.local_ranks) != nranks
+
+    @classmethod
+    def emulated(cls, nranks):
+        return cls(nranks, list(range(nranks)))
+
+    @classmethod
+    def from_process_group(cls, group=None):
+        import torch.distributed as dist
+        return cls(dist.get_world_size(group), [dist.get_rank(group)], group)
+
+    def all_gather(self, per_local: List[torch.Tensor]) -> List[torch.Tensor]:
+        """per_local[i] = the tensor of local rank i -> list over ALL ranks (same for every local rank)."""
+        if not self.distributed:
+            return list(per_local)
+        import torch.distributed as dist
+        t = per_local[0].contiguous()
+        out = [torch.empty_like(t) for _ in range(self.nranks)]
+        dist.all_gather(out, t, group=self.group)
+        return out
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+class _Rank:
+    """Per-rank scratch for the C calls."""
+
+    def __init__(self, rank, nranks, s, e, D, device):
+        self.rank, self.nranks, self.s, self.e, self.D = rank, nranks, s, e, D
+        self.N_local = e - s
+        self.first, self.last = rank == 0, rank == nranks - 1
+        self.device = device
+        lib = _lib.load()
+        self.ws = torch.empty(lib.vdp_dist_workspace(D), dtype=torch.uint8, device=device)
+        self.status = torch.zeros(2, dtype=torch.int64, device=device)
+
+    def sweep(self, kind, stage, ins, outs, scaleD=1.0, scaleS=1.0, prev=None):
+        p = DistSweep()
+        p.kind, p.stage, p.rank, p.nranks, p.N_local, p.D = kind, stage, self.rank, self.nranks, self.N_local, self.D
+        p.scaleD, p.scaleS = scaleD, scaleS
+        for i, t in enumerate(ins):
+            p.__getattribute__("in")[i] = _ptr(t)
+        for i, t in enumerate(outs):
+            p.out[i] = _ptr(t)
+        if prev is not None:
+            p.prev_totals, p.prev_inits = prev[0].data_ptr(), prev[1].data_ptr()
+        p.workspace, p.workspace_bytes = self.ws.data_ptr(), self.ws.numel()
+        p.status = self.status.data_ptr()
+        return p
+
+
+def _blob_bytes(kind, stage, D):
+    tb, ib = C.c_size_t(), C.c_size_t()
+    check(_lib.load().vdp_dist_blob_bytes(kind, stage, D, C.byref(tb), C.byref(ib)), "vdp_dist_blob_bytes")
+    return tb.value, ib.value
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _run_sweep(comm: Comm, ranks: List[_Rank], kind, problems_stage, D):
+    """summary -> all-gather -> [summary stage 1 -> all-gather] -> finish, in lockstep over the local ranks.
+    ``problems_stage(rank_state, stage, prev)`` builds the DistSweep of one rank."""
+    lib = _lib.load()
+    stages = 2 if kind == _lib.SWEEP_NAT2SSM else 1
+    prev = [None] * len(ranks)
+    gathered = None
+    for stage in range(stages):
+        tb, ib = _blob_bytes(kind, stage, D)
+        totals, inits = [], []
+        for i, rk in enumerate(ranks):
+            tot = torch.zeros(tb, dtype=torch.uint8, device=rk.device)
+            ini = torch.zeros(ib, dtype=torch.uint8, device=rk.device)
+            p = problems_stage(rk, stage, prev[i])
+            check(lib.vdp_dist_sweep_summary(C.byref(p), tot.data_ptr(), ini.data_ptr(), _stream()),
+                  "vdp_dist_sweep_summary")
+            totals.append(tot)
+            inits.append(ini)
+        all_t = torch.cat(comm.all_gather(totals)).contiguous()
+        all_i = torch.cat(comm.all_gather(inits)).contiguous()
+        gathered = (all_t, all_i)
+        prev = [gathered] * len(ranks)
+    for i, rk in enumerate(ranks):
+        p = problems_stage(rk, stages - 1, prev[i] if stages == 2 else None)
+        check(lib.vdp_dist_sweep_finish(C.byref(p), gathered[0].data_ptr(), gathered[1].data_ptr(), _stream()),
+              "vdp_dist_sweep_finish")
+
+
+class TimeShardedChain:
+    """
+    Posterior rebuild of one sequence of N transitions, state dimension D, sharded in time.
+
+    Per local rank r with range [s, e): ``th1`` [n_own, D], ``thd`` [n_own, D, D] for the owned grid points
+    (n_own = e - s, plus the final point N on the last rank), ``ths`` [e - s, D, D].
+    """
+
+    def __init__(self, N: int, D: int, comm: Comm, device="cuda"):
+        self.N, self.D, self.comm = N, D, comm
+        self.parts = time_partition(N, comm.nranks)
+        self.ranks = [_Rank(r, comm.nranks, *self.parts[r], D, torch.device(device)) for r in comm.local_ranks]
+
+    def owned_nodes(self, r):
+        s, e = self.parts[r]
+        return s, e + (1 if r == self.comm.nranks - 1 else 0)
+
+    # ---- halo helpers: element j of the result = what local rank j needs from its neighbour
+    def _from_next(self, firsts: List[torch.Tensor]):
+        """firsts[i] = the block local rank i offers to the rank before it -> block received from the next rank."""
+        allv = self.comm.all_gather(firsts)
+        return [allv[rk.rank + 1] if not rk.last else None for rk in self.ranks]
+
+    def _from_prev(self, lasts: List[torch.Tensor]):
+        allv = self.comm.all_gather(lasts)
+        return [allv[rk.rank - 1] if not rk.first else None for rk in self.ranks]
+
+    def naturals_to_ssm(self, th1: List[torch.Tensor], thd: List[torch.Tensor], ths: List[torch.Tensor]):
+        """naturals_to_ssm_params (ssm_gaussian_transformations.py:333-511), time-sharded.
+        Returns per local rank a dict: A [n,D,D], b [n,D], cholQ [n,D,D] for its transitions (n = e - s), the
+        node-s factor ``cholQ_prev`` (cholQ of transition s-1; None on rank 0) and mu0 / cholP0 on rank 0."""
+        D, dev = self.D, self.ranks[0].device
+        halo = self._from_next([t[:1].contiguous() for t in thd])
+        Kd, Ld, Ls = [], [], []
+        for rk, d_own, h in zip(self.ranks, thd, halo):
+            kd = d_own if rk.last else torch.cat([d_own, h])
+            assert kd.shape[0] == rk.N_local + 1
+            Kd.append(kd.contiguous())
+            Ld.append(torch.empty_like(Kd[-1]))
+            Ls.append(torch.empty((rk.N_local, D, D), dtype=F64, device=dev))
+        idx = {id(rk): i for i, rk in enumerate(self.ranks)}
+        _run_sweep(self.comm, self.ranks, _lib.SWEEP_CHOL,
+                   lambda rk, st, prev: rk.sweep(_lib.SWEEP_CHOL, 0, [Kd[idx[id(rk)]], ths[idx[id(rk)]]],
+                                                 [Ld[idx[id(rk)]], Ls[idx[id(rk)]]], -2.0, -1.0), D)
+        A, bbuf, qbuf, mu0, cP0 = [], [], [], [], []
+        for rk in self.ranks:
+            n = rk.N_local
+            A.append(torch.empty((n, D, D), dtype=F64, device=dev))
+            bbuf.append(torch.zeros((n + 1, D), dtype=F64, device=dev))       # slot j <-> transition s - 1 + j
+            qbuf.append(torch.zeros((n + 1, D, D), dtype=F64, device=dev))
+            mu0.append(torch.zeros(D, dtype=F64, device=dev))
+            cP0.append(torch.zeros((D, D), dtype=F64, device=dev))
+
+        def n2s(rk, stage, prev):
+            i = idx[id(rk)]
+            return rk.sweep(_lib.SWEEP_NAT2SSM, stage, [Ld[i], Ls[i], th1[i], thd[i], ths[i]],
+                            [A[i], bbuf[i][1:], qbuf[i][1:], mu0[i], cP0[i]], prev=prev)
+        _run_sweep(self.comm, self.ranks, _lib.SWEEP_NAT2SSM, n2s, D)
+        # transition e-1 (output of node e) lives in slot 0 of the next rank
+        nb = self._from_next([t[:1].contiguous() for t in bbuf])
+        nq = self._from_next([t[:1].contiguous() for t in qbuf])
+        out = []
+        for i, rk in enumerate(self.ranks):
+            if not rk.last:
+                bbuf[i][-1:] = nb[i]
+                qbuf[i][-1:] = nq[i]
+            out.append(dict(A=A[i], b=bbuf[i][1:], cholQ=qbuf[i][1:], cholQ_prev=None if rk.first else qbuf[i][:1],
+                            mu0=mu0[i] if rk.first else None, cholP0=cP0[i] if rk.first else None))
+        return out
+
+    def ssm_marginals(self, A: List[torch.Tensor], b: List[torch.Tensor], cholQ: List[torch.Tensor],
+                      mu0: List[Optional[torch.Tensor]], cholP0: List[Optional[torch.Tensor]]):
+        """StateSpaceModel.marginals (state_space_model.py:231-262), time-sharded.  Returns per local rank
+        (m [n_own, D], Sd [n_own, D, D]) for its owned grid points."""
+        D, dev = self.D, self.ranks[0].device
+        qprev = self._from_prev([t[-1:].contiguous() for t in cholQ])
+        anext = self._from_next([t[:1].contiguous() for t in A])
+        qnext = self._from_next([t[:1].contiguous() for t in cholQ])
+        Abuf, qbuf, m, Ld, Ls, Sd = [], [], [], [], [], []
+        zero = torch.zeros((1, D, D), dtype=F64, device=dev)
+        for i, rk in enumerate(self.ranks):
+            n = rk.N_local
+            Abuf.append(torch.cat([A[i], zero if rk.last else anext[i]]).contiguous())
+            qbuf.append(torch.cat([zero if rk.first else qprev[i], cholQ[i], zero if rk.last else qnext[i]]).contiguous())
+            m.append(torch.empty((n + 1, D), dtype=F64, device=dev))
+            Ld.append(torch.empty((n + 1, D, D), dtype=F64, device=dev))
+            Ls.append(torch.empty((n, D, D), dtype=F64, device=dev))
+            Sd.append(torch.empty((n + 1, D, D), dtype=F64, device=dev))
+        idx = {id(rk): i for i, rk in enumerate(self.ranks)}
+        dummy_v = torch.zeros(D, dtype=F64, device=dev)
+        dummy_m = torch.zeros((D, D), dtype=F64, device=dev)
+
+        def marg(rk, stage, prev):
+            i = idx[id(rk)]
+            return rk.sweep(_lib.SWEEP_MARG, 0,
+                            [Abuf[i], b[i].contiguous(), qbuf[i][1:], mu0[i] if rk.first else dummy_v,
+                             cholP0[i] if rk.first else dummy_m], [m[i], Ld[i], Ls[i]])
+        _run_sweep(self.comm, self.ranks, _lib.SWEEP_MARG, marg, D)
+        _run_sweep(self.comm, self.ranks, _lib.SWEEP_INVBAND,
+                   lambda rk, st, prev: rk.sweep(_lib.SWEEP_INVBAND, 0, [Ld[idx[id(rk)]], Ls[idx[id(rk)]]],
+                                                 [Sd[idx[id(rk)]], None]), D)
+        out = []
+        for i, rk in enumerate(self.ranks):
+            n_own = rk.N_local + (1 if rk.last else 0)
+            out.append((m[i][:n_own], Sd[i][:n_own]))
+        return out
+
+    def check_status(self):
+        for rk in self.ranks:
+            code = int(rk.status[0].item())
+            if code != 0:
+                raise _lib.VdpError(f"rank {rk.rank}: non positive-definite block at local index {int(rk.status[1])}")
