@@ -65,6 +65,19 @@ class Comm:
         return out
 
 
+def halo_from_next(comm: Comm, blocks: List[torch.Tensor]):
+    """blocks[i] = what local rank i offers to the rank before it -> what local rank i receives from the rank
+    after it (None on the last rank)."""
+    allv = comm.all_gather(blocks)
+    return [allv[r + 1] if r + 1 < comm.nranks else None for r in comm.local_ranks]
+
+
+def halo_from_prev(comm: Comm, blocks: List[torch.Tensor]):
+    """blocks[i] = what local rank i offers to the rank after it -> what it receives from the rank before it."""
+    allv = comm.all_gather(blocks)
+    return [allv[r - 1] if r > 0 else None for r in comm.local_ranks]
+
+
 def _ptr(t: Optional[torch.Tensor]):
     return None if t is None else t.data_ptr()
 
@@ -153,13 +166,10 @@ class TimeShardedChain:
 
     # ---- halo helpers: element j of the result = what local rank j needs from its neighbour
     def _from_next(self, firsts: List[torch.Tensor]):
-        """firsts[i] = the block local rank i offers to the rank before it -> block received from the next rank."""
-        allv = self.comm.all_gather(firsts)
-        return [allv[rk.rank + 1] if not rk.last else None for rk in self.ranks]
+        return halo_from_next(self.comm, firsts)
 
     def _from_prev(self, lasts: List[torch.Tensor]):
-        allv = self.comm.all_gather(lasts)
-        return [allv[rk.rank - 1] if not rk.first else None for rk in self.ranks]
+        return halo_from_prev(self.comm, lasts)
 
     def naturals_to_ssm(self, th1: List[torch.Tensor], thd: List[torch.Tensor], ths: List[torch.Tensor]):
         """naturals_to_ssm_params (ssm_gaussian_transformations.py:333-511), time-sharded.
