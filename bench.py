@@ -295,6 +295,43 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_vdp(args):
+    """Second line of SURVEY 8(d): one VDP fixed-point sweep (vi_markov_gp_trainer.py:62-73) on the C4 shape."""
+    import torch
+    from oracle.sde_np import DRIFT_DW
+    from vi_diffusion_processes_b200.vgp import VgpEngine
+    torch.cuda.set_device(0)
+    B, N = args.seqs, args.grid
+    grid, idx, y = make_problem(B, N, seed=4096)
+    idx = np.maximum(idx, 1)
+    eng = VgpEngine(DRIFT_DW, DW_PARAMS, np.ones((1, 1)), grid, idx, y[..., None], [[NOISE_STD]], [X0_MU], [[X0_COV]],
+                    stabilize_system=True)
+    eng.A += 2.0
+    eng.b += 2.0 * torch.as_tensor(np.sign(y[:, :1]), device="cuda").reshape(-1, 1, 1)
+    for _ in range(max(3, args.warmup)):
+        eng.sweep(0.01)
+    eng.check_status()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        eng.sweep(0.01)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    peak, peak_src = measured_peaks()
+    bytes_per_step = 8 * (2 + 2 + 2 + 2)   # read A, b, write A, b, lam, psi, m, S (D = 1)
+    print(json.dumps({"metric": "grid-steps/sec per VDP fixed-point sweep", "value": B * N / (ms * 1e-3),
+                      "unit": "grid-steps/s", "n_gpus": 1, "steps": args.steps, "warmup": max(3, args.warmup),
+                      "ms_per_step": ms, "higher_is_better": True, "dtype": "f64", "data": "synthetic",
+                      "config": {"workload": "C4 shape, VDP: forward pass, Lagrange sweep, parameter update, forward "
+                                             "pass, ELBO", "sequences_per_gpu": B, "grid_steps": N, "state_dim": 1},
+                      "roofline_update": {"algorithmic_bytes_per_grid_step": bytes_per_step,
+                                          "achieved": B * N * bytes_per_step / (ms * 1e-3) / 1e9, "peak": peak,
+                                          "unit": "GB/s", "frac": B * N * bytes_per_step / (ms * 1e-3) / 1e9 / peak,
+                                          "peak_source": peak_src}}))
+
+
 def run_reference(args):
     """The reference's CPU path = the oracle port on all host cores (TensorFlow is not installable here)."""
     rank = int(os.environ.get("RANK", "0"))
@@ -324,12 +361,16 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cvi", choices=["cvi", "vdp"],
+                    help="cvi = the BASELINE.json metric (default); vdp = the VDP sweep on the same shape (1 GPU)")
     ap.add_argument("--seqs", type=int, default=4096, help="sequences per GPU")
     ap.add_argument("--grid", type=int, default=10000, help="grid steps per sequence")
     ap.add_argument("--ref-seqs", type=int, default=64, help="sequences per host core in the bounded CPU sample")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "vdp":
+        run_vdp(args)
     else:
         run_ours(args)
 

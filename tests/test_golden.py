@@ -76,10 +76,17 @@ def test_cuda_reproduces_golden_cvi(path):
     assert relerr(eng.fx_covs[0].cpu().numpy(), g["cvi_S"]) < TOL
     assert relerr(eng.d1[0].cpu().numpy(), g["cvi_d1"]) < TOL
     # site tensors: at the scale of the posterior natural parameters they are added to (OU prior: exact sites are 0)
+    # the fixture records how far the float64 reference route itself is from its 80-bit evaluation on this data
+    # (site_floor_f64_vs_f80, e.g. 1.4e-9 for g1 on c2): no float64 implementation can be pinned tighter than that
     th = [t[0].cpu().numpy() for t in eng._prior_naturals(eng.pA, eng.pb)]
-    for got, want, t in ((eng.g1, g["cvi_g1"], th[0]), (eng.gd, g["cvi_gd"], th[1]), (eng.gs, g["cvi_gs"], th[2])):
+    for got, want, t, floor in ((eng.g1, g["cvi_g1"], th[0], g["site_floor_f64_vs_f80"][0]),
+                                (eng.gd, g["cvi_gd"], th[1], g["site_floor_f64_vs_f80"][1]),
+                                (eng.gs, g["cvi_gs"], th[2], g["site_floor_f64_vs_f80"][2])):
         scale = max(np.abs(want).max(), 1e-3 * np.abs(t + want).max())
-        assert relerr(got[0].cpu().numpy(), want, scale=scale) < TOL
+        floor = floor if floor < 1e-6 else 0.0   # OU prior: the exact sites are 0, a relative floor means nothing
+        assert relerr(got[0].cpu().numpy(), want, scale=scale) < max(TOL, 3.0 * floor)
+        # as a summand of q's natural parameters the site is right to 1e-11
+        assert relerr(got[0].cpu().numpy(), want, scale=np.abs(t + want).max()) < 1e-11
 
 
 @pytest.mark.gpu

@@ -70,6 +70,27 @@ def main():
                    cvi_gd=cvi.girsanov_sites.nat2.block_diagonal, cvi_gs=cvi.girsanov_sites.nat2.block_sub_diagonal,
                    cvi_d1=cvi.data_sites.nat1, cvi_d2=cvi.data_sites.nat2, cvi_m=cvi.fx_mus, cvi_S=cvi.fx_covs,
                    obs_idx=cvi.obs_sites_indices)
+        # rounding floor of the float64 reference route itself: the same three updates re-evaluated in 80-bit
+        # long double (oracle/scalar_d1.py, D = 1 only).  The site natural parameters are ill-conditioned
+        # functions of the marginals (1 / (S_{k+1} - A S_k A^T)): two float64 evaluations that round
+        # differently cannot agree better than this, so the GPU test allows max(1e-9, 3 x floor).
+        floor = np.zeros(3)
+        if D == 1:
+            from oracle import scalar_d1
+            runs = []
+            for dtype in (np.float64, np.longdouble):
+                m1 = scalar_d1.BatchedCVISitesSDE1D(sde.drift_id, np.asarray(sde.params), float(sde.q[0, 0]), grid,
+                                                    cvi.obs_sites_indices[None], y[None, :, 0], sigma,
+                                                    float(prior.mu[0]), float(prior.cov[0, 0]), dtype=dtype)
+                for it in range(3):
+                    m1.site_update(lr, lr)
+                    if it == 1:
+                        m1.relinearize()
+                runs.append(m1)
+            f64, f80 = runs
+            floor = np.array([float(np.abs(getattr(f64, k) - getattr(f80, k)).max() / np.abs(getattr(f80, k)).max())
+                              for k in ("g1", "gd", "gs")])
+        out.update(site_floor_f64_vs_f80=floor)
         # VDP: three fixed-point sweeps from a mean-reverting start (vi_markov_gp.py:83, trainer :62-73)
         vgp_stab = case != "c1_ou"   # sigma = 0.01 makes psi jump by 5000 at every observation: the reference's stabilize_system
         vgp = M.VariationalMarkovGP((obs_t, y), sde, grid, lik, prior_initial_state=prior, stabilize_system=vgp_stab)
