@@ -202,6 +202,29 @@ int vdp_cvi_site_update(const vdp_cvi_problem* problem_host, void* stream);
 int vdp_cvi_elbo(const vdp_cvi_problem* problem_host, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Host-buffer variant of vdp_cvi_site_update: the call a host program makes when its arrays live in HOST
+ * memory (what the reference's Python loop holds, cvi_dp_trainer.py:71-77).  Every array pointer of `problem`
+ * addresses host memory (pinned memory gives full PCIe speed; pageable memory works, slower); workspace,
+ * workspace_bytes and status of the struct are ignored.  The B sequences are cut into chunks of `chunk`
+ * sequences; chunk c is uploaded, updated and downloaded on stream c % slots, so with slots >= 3 the upload of
+ * one chunk, the kernels of the previous and the download of the one before overlap.  Results are identical to
+ * vdp_cvi_site_update on the whole batch (sequences are independent).  The call returns when all results are
+ * in the host buffers.
+ *   in/out (host): g1, gd, gs, d1, d2, fx_mus, fx_covs          in (host): time_grid, obs_idx, obs_y, prior
+ *   out (host, each optional = NULL): qA, qb, qcholQ, qmu0, qcholP0, elbo, ve, kl
+ * The linearised prior changes only at a re-linearisation (cvi_dp_trainer.py:110-134), so it can be kept on the
+ * device: upload it once with vdp_cvi_host_set_prior and pass pA = NULL in the site updates that follow.
+ * status_host2 (optional) receives the device status word; a reported grid index is relative to its chunk.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct vdp_cvi_host_ctx vdp_cvi_host_ctx;
+int vdp_cvi_host_create(vdp_cvi_host_ctx** ctx, int64_t chunk, int64_t N, int D, int64_t n_obs, int slots,
+                        int device);
+int vdp_cvi_host_set_prior(vdp_cvi_host_ctx* ctx, int64_t B, const double* pA, const double* pb,
+                           const double* pcholQ, const double* pmu0, const double* pcholP0);
+int vdp_cvi_host_site_update(vdp_cvi_host_ctx* ctx, const vdp_cvi_problem* problem, int64_t* status_host2);
+int vdp_cvi_host_destroy(vdp_cvi_host_ctx* ctx);
+
+/* ------------------------------------------------------------------------------------------------
  * VDP: VariationalMarkovGP (markovflow/models/vi_sde.py:63-482), batched over B sequences.
  *   vdp_vgp_forward_pass               forward_pass              vi_sde.py:171-204  -> m, S
  *   vdp_vgp_update_lagrange            update_lagrange           vi_sde.py:289-347  (m, S) -> lam, psi

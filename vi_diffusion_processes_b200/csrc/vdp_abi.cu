@@ -187,5 +187,6 @@ int vdp_btd_logdet(const double* Ld, double* out, int64_t B, int64_t n, int D, v
 
 #include "vdp_fused.inl"
 #include "vdp_cvi.inl"
+#include "vdp_host.inl"
 #include "vdp_vgp.inl"
 #include "vdp_dist.inl"

@@ -1,0 +1,219 @@
+// Host-buffer variant of the CVI-DP site update: every array of the problem lives in HOST memory (pinned
+// for full PCIe speed).  The B independent sequences are cut in chunks; chunk c runs on stream c % slots with
+// its own device slot:  H2D copies -> vdp_cvi_site_update -> D2H copies, all stream-ordered.  With >= 3 slots
+// the upload of chunk c+1, the kernels of chunk c and the download of chunk c-1 overlap (two copy engines +
+// SMs), so the call costs max(H2D, D2H, compute) instead of their sum.  Chunking over sequences is exact:
+// no kernel on the path mixes sequences.
+namespace vdp {
+
+struct HostSlot {
+    cudaStream_t st = nullptr;
+    double *pA, *pb, *pcholQ, *pmu0, *pcholP0, *g1, *gd, *gs, *d1, *d2, *obs_y, *fx_mus, *fx_covs;
+    double *qA, *qb, *qcholQ, *qmu0, *qcholP0, *elbo, *ve, *kl;
+    int64_t* obs_idx;
+    void* ws;
+};
+
+}  // namespace vdp
+
+struct vdp_cvi_host_ctx {
+    int64_t chunk, N, n_obs;
+    int D, device, nslots;
+    size_t ws_bytes;
+    char* pool = nullptr;            // one device allocation for all slots
+    double* time_grid = nullptr;     // [N+1]
+    int64_t* status = nullptr;       // device int64[2]
+    vdp::HostSlot slot[4];
+    // optional device-resident copy of the linearised prior of all B sequences (vdp_cvi_host_set_prior)
+    int64_t prior_B = 0;
+    char* prior_pool = nullptr;
+    double *rA = nullptr, *rb = nullptr, *rQ = nullptr, *rmu0 = nullptr, *rP0 = nullptr;
+};
+
+namespace vdp {
+
+struct HostSizes {
+    size_t vN1, mN1, vN, mN, v1, m1, vo, mo, io, s;
+    HostSizes(int64_t B, int64_t N, int D, int64_t n_obs) {
+        const size_t d = D, dd = (size_t)D * D, b = (size_t)B;
+        vN1 = padded(b * (N + 1) * d);  mN1 = padded(b * (N + 1) * dd);
+        vN = padded(b * N * d);         mN = padded(b * N * dd);
+        v1 = padded(b * d);             m1 = padded(b * dd);
+        vo = padded(b * n_obs * d + 1); mo = padded(b * n_obs * dd + 1);
+        io = padded(b * n_obs + 1);     s = padded(b);
+    }
+    size_t slot_bytes(size_t ws) const {
+        return (mN + vN + mN + v1 + m1)            // prior
+               + (vN1 + mN1 + mN) + (vo + mo)      // sites
+               + io + vo                           // observations
+               + (vN1 + mN1)                       // marginals
+               + (mN + vN + mN + v1 + m1)          // posterior SSM
+               + 3 * s + ((ws + 255) & ~size_t(255));
+    }
+};
+
+static inline cudaError_t h2d(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+    return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st) : cudaSuccess;
+}
+static inline cudaError_t d2h(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+    return (bytes && dst) ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
+}
+
+}  // namespace vdp
+
+extern "C" {
+
+int vdp_cvi_host_destroy(vdp_cvi_host_ctx* c) {
+    if (!c) return VDP_OK;
+    cudaSetDevice(c->device);
+    for (int i = 0; i < c->nslots; ++i)
+        if (c->slot[i].st) { cudaStreamSynchronize(c->slot[i].st); cudaStreamDestroy(c->slot[i].st); }
+    if (c->pool) cudaFree(c->pool);
+    if (c->prior_pool) cudaFree(c->prior_pool);
+    delete c;
+    return VDP_OK;
+}
+
+int vdp_cvi_host_create(vdp_cvi_host_ctx** out, int64_t chunk, int64_t N, int D, int64_t n_obs, int slots,
+                        int device) {
+    VDP_REQUIRE(out && chunk >= 1 && N >= 1 && D >= 1 && D <= 3 && n_obs >= 0, "out, chunk, N, D, n_obs");
+    VDP_REQUIRE(slots >= 1 && slots <= 4, "slots must be 1..4");
+    VDP_CHECK_CUDA(cudaSetDevice(device));
+    vdp_cvi_host_ctx* c = new vdp_cvi_host_ctx();
+    c->chunk = chunk; c->N = N; c->n_obs = n_obs; c->D = D; c->device = device; c->nslots = slots;
+    c->ws_bytes = vdp_cvi_workspace(chunk, N, D, n_obs);
+    const HostSizes z(chunk, N, D, n_obs);
+    const size_t per_slot = z.slot_bytes(c->ws_bytes);
+    const size_t total = per_slot * slots + padded(N + 1) + 256;
+    if (cudaMalloc((void**)&c->pool, total) != cudaSuccess) {
+        cudaGetLastError();
+        set_error("vdp_cvi_host_create: cannot allocate %zu device bytes", total);
+        delete c;
+        return VDP_E_CUDA;
+    }
+    Arena ar(c->pool, total);
+    c->time_grid = ar.take(N + 1);
+    c->status = (int64_t*)ar.take_bytes(256);
+    for (int i = 0; i < slots; ++i) {
+        HostSlot& s = c->slot[i];
+        const size_t d = D, dd = (size_t)D * D, b = (size_t)chunk;
+        s.pA = ar.take(b * N * dd); s.pb = ar.take(b * N * d); s.pcholQ = ar.take(b * N * dd);
+        s.pmu0 = ar.take(b * d); s.pcholP0 = ar.take(b * dd);
+        s.g1 = ar.take(b * (N + 1) * d); s.gd = ar.take(b * (N + 1) * dd); s.gs = ar.take(b * N * dd);
+        s.d1 = ar.take(b * n_obs * d + 1); s.d2 = ar.take(b * n_obs * dd + 1);
+        s.obs_idx = (int64_t*)ar.take(b * n_obs + 1); s.obs_y = ar.take(b * n_obs * d + 1);
+        s.fx_mus = ar.take(b * (N + 1) * d); s.fx_covs = ar.take(b * (N + 1) * dd);
+        s.qA = ar.take(b * N * dd); s.qb = ar.take(b * N * d); s.qcholQ = ar.take(b * N * dd);
+        s.qmu0 = ar.take(b * d); s.qcholP0 = ar.take(b * dd);
+        s.elbo = ar.take(b); s.ve = ar.take(b); s.kl = ar.take(b);
+        s.ws = ar.take_bytes(c->ws_bytes);
+        if (!s.ws || cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking) != cudaSuccess) {
+            set_error("vdp_cvi_host_create: slot %d setup failed", i);
+            vdp_cvi_host_destroy(c);
+            return VDP_E_CUDA;
+        }
+    }
+    *out = c;
+    return VDP_OK;
+}
+
+int vdp_cvi_host_set_prior(vdp_cvi_host_ctx* c, int64_t B, const double* pA, const double* pb, const double* pcholQ,
+                           const double* pmu0, const double* pcholP0) {
+    VDP_REQUIRE(c && B >= 1 && pA && pb && pcholQ && pmu0 && pcholP0, "ctx, B, prior pointers (host)");
+    VDP_CHECK_CUDA(cudaSetDevice(c->device));
+    if (c->prior_pool && c->prior_B != B) { cudaFree(c->prior_pool); c->prior_pool = nullptr; }
+    const size_t d = c->D, dd = (size_t)c->D * c->D, b = (size_t)B, N = (size_t)c->N;
+    const size_t total = 2 * padded(b * N * dd) + padded(b * N * d) + padded(b * d) + padded(b * dd);
+    if (!c->prior_pool && cudaMalloc((void**)&c->prior_pool, total) != cudaSuccess) {
+        cudaGetLastError();
+        set_error("vdp_cvi_host_set_prior: cannot allocate %zu device bytes", total);
+        return VDP_E_CUDA;
+    }
+    c->prior_B = B;
+    Arena ar(c->prior_pool, total);
+    c->rA = ar.take(b * N * dd); c->rb = ar.take(b * N * d); c->rQ = ar.take(b * N * dd);
+    c->rmu0 = ar.take(b * d); c->rP0 = ar.take(b * dd);
+    cudaStream_t st = c->slot[0].st;
+    VDP_CHECK_CUDA(h2d(c->rA, pA, b * N * dd * 8, st));
+    VDP_CHECK_CUDA(h2d(c->rb, pb, b * N * d * 8, st));
+    VDP_CHECK_CUDA(h2d(c->rQ, pcholQ, b * N * dd * 8, st));
+    VDP_CHECK_CUDA(h2d(c->rmu0, pmu0, b * d * 8, st));
+    VDP_CHECK_CUDA(h2d(c->rP0, pcholP0, b * dd * 8, st));
+    VDP_CHECK_CUDA(cudaStreamSynchronize(st));
+    return VDP_OK;
+}
+
+int vdp_cvi_host_site_update(vdp_cvi_host_ctx* c, const vdp_cvi_problem* hp, int64_t* status_host2) {
+    VDP_REQUIRE(c && hp, "ctx, problem");
+    VDP_REQUIRE(hp->N == c->N && hp->D == c->D && hp->n_obs == c->n_obs, "problem shape differs from the context");
+    VDP_REQUIRE(hp->time_grid && hp->g1 && hp->gd && hp->gs && hp->fx_mus && hp->fx_covs, "host state pointers");
+    VDP_REQUIRE(hp->n_obs == 0 || (hp->d1 && hp->d2 && hp->obs_idx && hp->obs_y), "host data-site pointers");
+    const bool resident = (hp->pA == nullptr);
+    if (resident) {
+        VDP_REQUIRE(c->prior_pool && c->prior_B == hp->B, "pA == NULL needs vdp_cvi_host_set_prior for the same B");
+    } else {
+        VDP_REQUIRE(hp->pb && hp->pcholQ && hp->pmu0 && hp->pcholP0, "host prior pointers");
+    }
+    VDP_CHECK_CUDA(cudaSetDevice(c->device));
+    const int64_t B = hp->B, N = c->N, no = c->n_obs;
+    const size_t d = c->D, dd = d * d, S = sizeof(double);
+    cudaStream_t s0 = c->slot[0].st;
+    VDP_CHECK_CUDA(cudaMemsetAsync(c->status, 0, 2 * sizeof(int64_t), s0));
+    VDP_CHECK_CUDA(h2d(c->time_grid, hp->time_grid, (N + 1) * S, s0));
+    VDP_CHECK_CUDA(cudaStreamSynchronize(s0));
+    int rc = VDP_OK;
+    int64_t ci = 0;
+    for (int64_t b0 = 0; b0 < B && rc == VDP_OK; b0 += c->chunk, ++ci) {
+        const size_t nb = (size_t)std::min<int64_t>(c->chunk, B - b0), o = (size_t)b0;
+        HostSlot& s = c->slot[ci % c->nslots];
+        cudaStream_t st = s.st;
+        vdp_cvi_problem p = *hp;
+        p.B = (int64_t)nb;
+        p.time_grid = c->time_grid;
+        cudaError_t e = cudaSuccess;
+        auto up = [&](void* dst, const void* src, size_t per_seq) {
+            if (e == cudaSuccess) e = h2d(dst, (const char*)src + o * per_seq, nb * per_seq, st);
+        };
+        auto down = [&](void* dst, const void* src, size_t per_seq) {
+            if (e == cudaSuccess && dst) e = d2h((char*)dst + o * per_seq, src, nb * per_seq, st);
+        };
+        if (resident) {
+            p.pA = c->rA + o * N * dd; p.pb = c->rb + o * N * d; p.pcholQ = c->rQ + o * N * dd;
+            p.pmu0 = c->rmu0 + o * d; p.pcholP0 = c->rP0 + o * dd;
+        } else {
+            up(s.pA, hp->pA, N * dd * S); up(s.pb, hp->pb, N * d * S); up(s.pcholQ, hp->pcholQ, N * dd * S);
+            up(s.pmu0, hp->pmu0, d * S); up(s.pcholP0, hp->pcholP0, dd * S);
+            p.pA = s.pA; p.pb = s.pb; p.pcholQ = s.pcholQ; p.pmu0 = s.pmu0; p.pcholP0 = s.pcholP0;
+        }
+        up(s.g1, hp->g1, (N + 1) * d * S); up(s.gd, hp->gd, (N + 1) * dd * S); up(s.gs, hp->gs, N * dd * S);
+        up(s.fx_mus, hp->fx_mus, (N + 1) * d * S); up(s.fx_covs, hp->fx_covs, (N + 1) * dd * S);
+        if (no > 0) {
+            up(s.d1, hp->d1, no * d * S); up(s.d2, hp->d2, no * dd * S);
+            up(s.obs_idx, hp->obs_idx, no * sizeof(int64_t)); up(s.obs_y, hp->obs_y, no * d * S);
+        }
+        if (e != cudaSuccess) { set_error("H2D copy: %s", cudaGetErrorString(e)); rc = VDP_E_CUDA; break; }
+        p.g1 = s.g1; p.gd = s.gd; p.gs = s.gs; p.d1 = s.d1; p.d2 = s.d2; p.obs_idx = s.obs_idx; p.obs_y = s.obs_y;
+        p.fx_mus = s.fx_mus; p.fx_covs = s.fx_covs;
+        p.qA = s.qA; p.qb = s.qb; p.qcholQ = s.qcholQ; p.qmu0 = s.qmu0; p.qcholP0 = s.qcholP0;
+        p.elbo = s.elbo; p.ve = s.ve; p.kl = s.kl;
+        p.workspace = s.ws; p.workspace_bytes = c->ws_bytes; p.status = c->status;
+        if ((rc = vdp_cvi_site_update(&p, st))) break;
+        down(hp->g1, s.g1, (N + 1) * d * S); down(hp->gd, s.gd, (N + 1) * dd * S); down(hp->gs, s.gs, N * dd * S);
+        down(hp->fx_mus, s.fx_mus, (N + 1) * d * S); down(hp->fx_covs, s.fx_covs, (N + 1) * dd * S);
+        if (no > 0) { down(hp->d1, s.d1, no * d * S); down(hp->d2, s.d2, no * dd * S); }
+        down(hp->qA, s.qA, N * dd * S); down(hp->qb, s.qb, N * d * S); down(hp->qcholQ, s.qcholQ, N * dd * S);
+        down(hp->qmu0, s.qmu0, d * S); down(hp->qcholP0, s.qcholP0, dd * S);
+        down(hp->elbo, s.elbo, S); down(hp->ve, s.ve, S); down(hp->kl, s.kl, S);
+        if (e != cudaSuccess) { set_error("D2H copy: %s", cudaGetErrorString(e)); rc = VDP_E_CUDA; }
+    }
+    for (int i = 0; i < c->nslots; ++i)
+        if (cudaStreamSynchronize(c->slot[i].st) != cudaSuccess && rc == VDP_OK) {
+            set_error("stream synchronize: %s", cudaGetErrorString(cudaGetLastError()));
+            rc = VDP_E_CUDA;
+        }
+    if (rc == VDP_OK && status_host2)
+        VDP_CHECK_CUDA(cudaMemcpy(status_host2, c->status, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost));
+    return rc;
+}
+
+}  // extern "C"

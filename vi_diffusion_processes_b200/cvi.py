@@ -156,3 +156,65 @@ class CviEngine:
         self.g1 = (self.g1 + last[0] - new[0]).contiguous()
         self.gd = (self.gd + last[1] - new[1]).contiguous()
         self.gs = (self.gs + last[2] - new[2]).contiguous()
+
+
+class CviHostEngine:
+    """
+    The same site update with the whole state in pinned HOST memory (``vdp_cvi_host_site_update``): what a host
+    program holding NumPy arrays calls.  Every call uploads the state (and the prior unless ``resident_prior``),
+    runs the update and downloads sites, marginals, posterior SSM and ELBO, chunked over sequences so that
+    copies and kernels overlap.  ``host`` maps the field names of ``vdp_cvi_problem`` to pinned CPU tensors.
+    """
+
+    STATE = ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs")
+    PRIOR = ("pA", "pb", "pcholQ", "pmu0", "pcholP0")
+    CONST = ("time_grid", "obs_idx", "obs_y")
+    OUT = ("qA", "qb", "qcholQ", "qmu0", "qcholP0", "elbo", "ve", "kl")
+
+    def __init__(self, eng: CviEngine, chunk=256, slots=3, resident_prior=False, want_posterior_ssm=True):
+        self._eng = eng
+        self.B, self.N, self.D, self.n_obs = eng.B, eng.N, eng.D, eng.n_obs
+        self.resident_prior = resident_prior
+        names = self.STATE + self.PRIOR + self.CONST + self.OUT
+        self.host = {k: getattr(eng, k).detach().to("cpu").contiguous().pin_memory() for k in names}
+        self.skip = set() if want_posterior_ssm else {"qA", "qb", "qcholQ", "qmu0", "qcholP0"}
+        self._ctx = C.c_void_p()
+        dev = eng.device.index if eng.device.index is not None else torch.cuda.current_device()
+        check(_lib.load().vdp_cvi_host_create(C.byref(self._ctx), min(chunk, self.B), self.N, self.D, self.n_obs,
+                                              slots, dev), "vdp_cvi_host_create")
+        if resident_prior:
+            self.set_prior()
+
+    def set_prior(self):
+        h = self.host
+        check(_lib.load().vdp_cvi_host_set_prior(self._ctx, self.B, *(h[k].data_ptr() for k in self.PRIOR)),
+              "vdp_cvi_host_set_prior")
+
+    def bytes_per_update(self):
+        """(host->device, device->host) bytes one site_update moves."""
+        h = self.host
+        nb = lambda names: sum(h[k].numel() * h[k].element_size() for k in names if k not in self.skip)
+        up = nb(self.STATE) + nb(self.CONST) + (0 if self.resident_prior else nb(self.PRIOR))
+        return up, nb(self.STATE) + nb(self.OUT)
+
+    def site_update(self, lr_data, lr_girsanov, flags=0):
+        p = self._eng._problem(lr_data, lr_girsanov, flags)
+        for k, t in self.host.items():
+            setattr(p, k, None if k in self.skip or (self.resident_prior and k in self.PRIOR) else t.data_ptr())
+        p.workspace, p.workspace_bytes, p.status = None, 0, None
+        st = (C.c_int64 * 2)()
+        check(_lib.load().vdp_cvi_host_site_update(self._ctx, C.byref(p), st), "vdp_cvi_host_site_update")
+        if st[0] != 0:
+            raise _lib.VdpError(f"non positive-definite block (code {st[0]}, chunk-local grid index {st[1]})")
+        return self.host["elbo"]
+
+    def close(self):
+        if self._ctx:
+            _lib.load().vdp_cvi_host_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
