@@ -352,6 +352,12 @@ enum {
     VDP_PHASE_COUNT = 8,
     VDP_PHASE_END = -1
 };
+/* Diagnostic: the library's float64 reciprocal / square root / division primitives (csrc/fastmath.cuh:
+ * hardware seed + Newton steps, no IEEE slow path), element-wise on device arrays of n positive normal numbers:
+ * rcp = 1/x, sq = sqrt(x), rsq = 1/sqrt(x), quo = y/x.  Used by the tests to bound their error in ulps. */
+int vdp_test_fastmath(const double* x, const double* y, double* rcp, double* sq, double* rsq, double* quo,
+                      int64_t n, void* stream);
+
 int vdp_profile_enable(int on);
 int vdp_profile_read(double* ms_by_phase, int64_t* spans_by_phase, int n_phases);
 

@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvdp_b200.so")
+LIB_PATH = os.environ.get("VDP_B200_LIB") or os.path.join(_HERE, "libvdp_b200.so")
 
 c_dp = C.POINTER(C.c_double)
 c_i64p = C.POINTER(C.c_int64)
@@ -140,6 +140,7 @@ SIGNATURES = {
     "vdp_dist_blob_bytes": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "vdp_dist_sweep_summary": (C.c_int, [C.POINTER(DistSweep), vp, vp, vp]),
     "vdp_dist_sweep_finish": (C.c_int, [C.POINTER(DistSweep), vp, vp, vp]),
+    "vdp_test_fastmath": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, vp]),
     "vdp_profile_enable": (C.c_int, [C.c_int]),
     "vdp_profile_read": (C.c_int, [c_dp, c_i64p, C.c_int]),
 }

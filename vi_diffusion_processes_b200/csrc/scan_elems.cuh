@@ -104,7 +104,7 @@ struct SchurOps<1> {
     __device__ __forceinline__ static Elem combine(const Elem& e1, const Elem& e2) {
         if (e1.id) return e2;
         if (e2.id) return e1;
-        const double r = 1.0 / (e1.Lb.a[0] + e2.La.a[0]);
+        const double r = rcp_fast(e1.Lb.a[0] + e2.La.a[0]);
         const double ur = e1.Lab.a[0] * r, v = e2.Lab.a[0];
         Elem o;
         o.La.a[0] = e1.La.a[0] - ur * e1.Lab.a[0];
@@ -115,7 +115,7 @@ struct SchurOps<1> {
     }
     __device__ __forceinline__ static void push(Elem& e, const Mat<1>& Ks, const Mat<1>& Kd_next) {
         if (e.id) { e = step(Ks, Kd_next); return; }
-        const double r = 1.0 / e.Lb.a[0];
+        const double r = rcp_fast(e.Lb.a[0]);
         const double ur = e.Lab.a[0] * r, v = Ks.a[0];
         e.La.a[0] = e.La.a[0] - ur * e.Lab.a[0];
         e.Lab.a[0] = ur * v;
@@ -124,7 +124,7 @@ struct SchurOps<1> {
     __device__ __forceinline__ static State apply(const Elem& e, const State& S) {
         if (e.id) return S;
         State o;
-        o.a[0] = e.Lb.a[0] - (e.Lab.a[0] / (S.a[0] + e.La.a[0])) * e.Lab.a[0];
+        o.a[0] = e.Lb.a[0] - div_fast(e.Lab.a[0], S.a[0] + e.La.a[0]) * e.Lab.a[0];
         return o;
     }
 };

@@ -7,6 +7,8 @@
 #include <cuda_runtime.h>
 #include <math.h>
 
+#include "fastmath.cuh"
+
 namespace vdp {
 
 template <int D>
@@ -229,14 +231,15 @@ template <int D> VDP_HD Mat<D> chol(const Mat<D>& X, bool& ok) {
 #pragma unroll
         for (int k = 0; k < j; ++k) d -= L(j, k) * L(j, k);
         if (!(d > 0.0)) ok = false;
-        const double ljj = sqrt(d);
+        double ljj, rjj;
+        sqrt_rsqrt_fast(d, ljj, rjj);
         L(j, j) = ljj;
 #pragma unroll
         for (int i = j + 1; i < D; ++i) {
             double s = X(i, j);
 #pragma unroll
             for (int k = 0; k < j; ++k) s -= L(i, k) * L(j, k);
-            L(i, j) = s / ljj;
+            L(i, j) = div_r(s, ljj, rjj);
         }
     }
     return L;
@@ -244,6 +247,9 @@ template <int D> VDP_HD Mat<D> chol(const Mat<D>& X, bool& ok) {
 // tf.linalg.triangular_solve(L, B, lower=True): X = L^-1 B
 template <int D> VDP_HD Mat<D> trsm(const Mat<D>& L, const Mat<D>& B) {
     Mat<D> X;
+    double rd[D];
+#pragma unroll
+    for (int i = 0; i < D; ++i) rd[i] = rcp_fast(L(i, i));
 #pragma unroll
     for (int c = 0; c < D; ++c)
 #pragma unroll
@@ -251,13 +257,16 @@ template <int D> VDP_HD Mat<D> trsm(const Mat<D>& L, const Mat<D>& B) {
             double acc = B(i, c);
 #pragma unroll
             for (int j = 0; j < i; ++j) acc -= L(i, j) * X(j, c);
-            X(i, c) = acc / L(i, i);
+            X(i, c) = div_r(acc, L(i, i), rd[i]);
         }
     return X;
 }
 // adjoint=True: X = L^-T B
 template <int D> VDP_HD Mat<D> trsmT(const Mat<D>& L, const Mat<D>& B) {
     Mat<D> X;
+    double rd[D];
+#pragma unroll
+    for (int i = 0; i < D; ++i) rd[i] = rcp_fast(L(i, i));
 #pragma unroll
     for (int c = 0; c < D; ++c)
 #pragma unroll
@@ -265,7 +274,7 @@ template <int D> VDP_HD Mat<D> trsmT(const Mat<D>& L, const Mat<D>& B) {
             double acc = B(i, c);
 #pragma unroll
             for (int j = i + 1; j < D; ++j) acc -= L(j, i) * X(j, c);
-            X(i, c) = acc / L(i, i);
+            X(i, c) = div_r(acc, L(i, i), rd[i]);
         }
     return X;
 }
@@ -276,7 +285,7 @@ template <int D> VDP_HD Vec<D> trsv(const Mat<D>& L, const Vec<D>& b) {
         double acc = b(i);
 #pragma unroll
         for (int j = 0; j < i; ++j) acc -= L(i, j) * x(j);
-        x(i) = acc / L(i, i);
+        x(i) = div_fast(acc, L(i, i));
     }
     return x;
 }
@@ -287,7 +296,7 @@ template <int D> VDP_HD Vec<D> trsvT(const Mat<D>& L, const Vec<D>& b) {
         double acc = b(i);
 #pragma unroll
         for (int j = i + 1; j < D; ++j) acc -= L(j, i) * x(j);
-        x(i) = acc / L(i, i);
+        x(i) = div_fast(acc, L(i, i));
     }
     return x;
 }
@@ -318,9 +327,10 @@ template <int D> VDP_HD Mat<D> lu_solve(Mat<D> A, Mat<D> B) {
             }
         }
         const double piv = A(k, k);
+        const double rpiv = rcp_fast(piv);
 #pragma unroll
         for (int i = k + 1; i < D; ++i) {
-            const double f = A(i, k) / piv;
+            const double f = div_r(A(i, k), piv, rpiv);
             A(i, k) = f;
 #pragma unroll
             for (int j = k + 1; j < D; ++j) A(i, j) -= f * A(k, j);
@@ -329,6 +339,9 @@ template <int D> VDP_HD Mat<D> lu_solve(Mat<D> A, Mat<D> B) {
         }
     }
     Mat<D> X;
+    double rd[D];
+#pragma unroll
+    for (int i = 0; i < D; ++i) rd[i] = rcp_fast(A(i, i));
 #pragma unroll
     for (int c = 0; c < D; ++c)
 #pragma unroll
@@ -336,7 +349,7 @@ template <int D> VDP_HD Mat<D> lu_solve(Mat<D> A, Mat<D> B) {
             double acc = B(i, c);
 #pragma unroll
             for (int j = i + 1; j < D; ++j) acc -= A(i, j) * X(j, c);
-            X(i, c) = acc / A(i, i);
+            X(i, c) = div_r(acc, A(i, i), rd[i]);
         }
     return X;
 }

@@ -107,6 +107,24 @@ __device__ __forceinline__ void chol_tile_recursion(double* sKd, double* sKs, in
                                                     int last_node, int64_t flat_node0, int64_t* status) {
     constexpr int DD = D * D;
     if (len <= 0) return;
+    if constexpr (D == 1) {
+        // scalar: one rsqrt seed gives the pivot and its reciprocal
+        double s = S.a[0], Lk, rL;
+        if (!(s > 0.0)) report_not_pd(status, flat_node0 + k0);
+        sqrt_rsqrt_fast(s, Lk, rL);
+        sKd[k0] = Lk;
+        for (int t = 0; t < len; ++t) {
+            const double Lsub = div_r(sKs[k0 + t], Lk, rL);
+            sKs[k0 + t] = Lsub;
+            if (t < len - 1 || k0 + t + 1 == last_node) {
+                s = sKd[k0 + t + 1] - Lsub * Lsub;
+                if (!(s > 0.0)) report_not_pd(status, flat_node0 + k0 + t + 1);
+                sqrt_rsqrt_fast(s, Lk, rL);
+                sKd[k0 + t + 1] = Lk;
+            }
+        }
+        return;
+    }
     bool ok = true;
     Mat<D> Lk = chol(S, ok);
     if (!ok) { report_not_pd(status, flat_node0 + k0); ok = true; }

@@ -120,6 +120,29 @@ int vdp_profile_read(double* ms_by_phase, int64_t* spans_by_phase, int n_phases)
     return VDP_OK;
 }
 
+// diagnostic: the fast float64 primitives of fastmath.cuh, element-wise (tests measure their error in ulps)
+__global__ void k_test_fastmath(const double* __restrict__ x, const double* __restrict__ y, double* __restrict__ rcp,
+                                double* __restrict__ sq, double* __restrict__ rsq, double* __restrict__ quo,
+                                int64_t n) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double s, rs;
+    sqrt_rsqrt_fast(x[i], s, rs);
+    rcp[i] = rcp_fast(x[i]);
+    sq[i] = s;
+    rsq[i] = rs;
+    quo[i] = div_fast(y[i], x[i]);
+}
+
+int vdp_test_fastmath(const double* x, const double* y, double* rcp, double* sq, double* rsq, double* quo, int64_t n,
+                      void* stream) {
+    VDP_REQUIRE(x && y && rcp && sq && rsq && quo && n >= 0, "pointers, n");
+    if (n == 0) return VDP_OK;
+    k_test_fastmath<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(x, y, rcp, sq, rsq, quo, n);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // op level
 // ---------------------------------------------------------------------------------------------------

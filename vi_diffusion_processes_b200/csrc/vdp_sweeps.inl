@@ -6,7 +6,23 @@ namespace vdp {
 
 // tile shapes: T chunks of L steps; L odd (conflict-free chunk stride in shared memory)
 template <int D> struct TileCfg;
-template <> struct TileCfg<1> { static constexpr int T = 128, Lc = 17, Li = 17, Lm = 9, Ln = 9; };
+// (the D = 1 shape can be overridden at build time for tuning runs: -DVDP_T1=.. -DVDP_LC1=.. ...)
+#ifndef VDP_T1
+#define VDP_T1 128
+#endif
+#ifndef VDP_LC1
+#define VDP_LC1 17
+#endif
+#ifndef VDP_LI1
+#define VDP_LI1 17
+#endif
+#ifndef VDP_LM1
+#define VDP_LM1 9
+#endif
+#ifndef VDP_LN1
+#define VDP_LN1 9
+#endif
+template <> struct TileCfg<1> { static constexpr int T = VDP_T1, Lc = VDP_LC1, Li = VDP_LI1, Lm = VDP_LM1, Ln = VDP_LN1; };
 template <> struct TileCfg<2> { static constexpr int T = 64, Lc = 9, Li = 9, Lm = 5, Ln = 5; };
 template <> struct TileCfg<3> { static constexpr int T = 64, Lc = 5, Li = 5, Lm = 3, Ln = 3; };
 
