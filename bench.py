@@ -193,8 +193,9 @@ def run_ours(args):
     # end-to-end leg: the whole state in pinned HOST memory, through vdp_cvi_host_site_update (C ABI with host
     # buffers): per step, upload state + prior + observations, update, download sites + marginals + ELBO
     from vi_diffusion_processes_b200.cvi import CviHostEngine
-    host_eng = CviHostEngine(eng, chunk=args.chunk, slots=3, want_posterior_ssm=False)
-    h2d, d2h = host_eng.bytes_per_update()
+    if not args.quick:
+        host_eng = CviHostEngine(eng, chunk=args.chunk, slots=3, want_posterior_ssm=False)
+        h2d, d2h = host_eng.bytes_per_update()
 
     def barrier():
         if world > 1:
@@ -234,6 +235,13 @@ def run_ours(args):
     lib.vdp_profile_enable(0)
     clocks = sampler.stop() if rank == 0 else None
     eng.check_status()
+    if args.quick:
+        if rank == 0:
+            print(json.dumps({"ms_per_step": ms_total / args.steps, "phases": {
+                nm: {"ms_per_launch": ph_ms[i] / max(1, ph_n[i])} for i, nm in enumerate(_lib.PHASES)}}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
     e2e_steps = max(2, args.steps // 2)
     ms_e2e = timed(step_e2e, e2e_steps, 1)
     host_eng.resident_prior = True          # variant: linearised prior uploaded once (it only changes at a
@@ -366,6 +374,7 @@ def main():
                     help="cvi = the BASELINE.json metric (default); vdp = the VDP sweep on the same shape (1 GPU)")
     ap.add_argument("--seqs", type=int, default=4096, help="sequences per GPU")
     ap.add_argument("--grid", type=int, default=10000, help="grid steps per sequence")
+    ap.add_argument("--quick", action="store_true", help="tuning runs: resident timing and phases only")
     ap.add_argument("--chunk", type=int, default=256, help="sequences per chunk of the host-buffer pipeline")
     ap.add_argument("--ref-seqs", type=int, default=64, help="sequences per host core in the bounded CPU sample")
     args = ap.parse_args()

@@ -34,8 +34,8 @@ template <int D> struct Drift<DRIFT_DW, D> {
 #pragma unroll
         for (int i = 0; i < D; ++i) {
             const double x2 = x(i) * x(i);
-            f(i) = P.p[0] * x(i) * (P.p[1] - x2);
-            J(i, i) = P.p[0] * (P.p[1] - 3.0 * x2);
+            f(i) = (P.p[0] * x(i)) * (P.p[1] - x2);
+            J(i, i) = P.p[0] * fma(-3.0, x2, P.p[1]);
         }
     }
 };

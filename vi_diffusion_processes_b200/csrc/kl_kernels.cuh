@@ -42,21 +42,22 @@ __device__ __forceinline__ void kl_term_scalar(const DriftParams& P, double Qp, 
     const double Sn = edn - mn * mn;
     const double Cs = esk - mk * mn;
     if (!(Sk > 0.0)) ok = false;
-    const double LS = sqrt(Sk);
-    const double iLS = 1.0 / LS;
+    double LS, iLS;
+    sqrt_rsqrt_fast(Sk, LS, iLS);
     const double A = (Cs * iLS) * iLS;
     const double b = mn - A * mk;
     const double Qc = Sn - A * (Sk * A);
     if (!(Qc > 0.0) || !(Qp > 0.0)) ok = false;
-    const double LQ = sqrt(Qc);
-    const double iLQ = 1.0 / LQ;
+    double LQ, iLQ, cQp, iQp;
+    sqrt_rsqrt_fast(Qc, LQ, iLQ);
     const double Qq = LQ * LQ;
-    const double cQp = sqrt(Qp);
-    const double iQp = 1.0 / cQp;
+    sqrt_rsqrt_fast(Qp, cQp, iQp);
     const double Qpinv = iQp * iQp;
     // C = -(logdet Qq - logdet Qp) - 1 + Qp^-1 Qq   (sde_utils.py:317-330); chol(Qq) = LQ exactly
     const double Cterm = -2.0 * log(LQ * iQp) - 1.0 + Qpinv * Qq;
     const double sL = 1.4142135623730951 * LS;
+    // d = x + dt f(x) - (A x + b) = (1 - A) x - b + dt f(x);  Q_p^-1 and pi^(-1/2) are factored out of the sums
+    const double omA = 1.0 - A, nb = -b;
     double quad = 0.0, gb = 0.0, gmq = 0.0, gA = 0.0, lsb = 0.0;
 #pragma unroll
     for (int p = 0; p < H; ++p) {
@@ -65,20 +66,21 @@ __device__ __forceinline__ void kl_term_scalar(const DriftParams& P, double Qp, 
         Mat<1> J;
         X(0) = fma(sL, xi, mk);
         Drift<DRIFT, 1>::eval(P, X, f, J);
-        const double d = (X(0) + dt * f(0)) - (A * X(0) + b);
-        const double rb = w * (Qpinv * d);
-        quad = fma(rb, d, quad);
-        const double Xb = ((1.0 + dt * J(0, 0)) - A) * rb;
-        gb -= rb;
+        const double d = fma(dt, f(0), fma(omA, X(0), nb));
+        const double wd = w * d;
+        quad = fma(wd, d, quad);
+        const double Xb = fma(dt, J(0, 0), omA) * wd;
+        gb -= wd;
         gmq += Xb;
-        gA = fma(-rb, X(0), gA);
+        gA = fma(-wd, X(0), gA);
         lsb = fma(Xb, xi, lsb);
     }
-    quad *= pi_factor;
-    gb *= pi_factor;
-    gmq *= pi_factor;
-    gA *= pi_factor;
-    lsb *= 1.4142135623730951 * pi_factor;
+    const double sc = pi_factor * Qpinv;
+    quad *= sc;
+    gb *= sc;
+    gmq *= sc;
+    gA *= sc;
+    lsb *= 1.4142135623730951 * sc;
     out.value = 0.5 * (quad + Cterm);
     // reverse through the pointwise algebra
     double Lgm = gmq;
@@ -329,11 +331,11 @@ __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
         // scalar: one reciprocal, one log (chol(cq^2) = |cq| exactly)
         const double Sk = Sd[i];
         if (!(Qp(0, 0) > 0.0) || !(Sk > 0.0) || !(Qq(0, 0) > 0.0)) ok = false;
-        cQp(0, 0) = sqrt(Qp(0, 0));
-        const double iQp = 1.0 / cQp(0, 0);
+        double iQp;
+        sqrt_rsqrt_fast(Qp(0, 0), cQp(0, 0), iQp);
         Qpinv(0, 0) = iQp * iQp;
         Cterm = -2.0 * log(fabs(cq(0, 0)) * iQp) - 1.0 + Qpinv(0, 0) * Qq(0, 0);
-        LS(0, 0) = sqrt(Sk);
+        LS(0, 0) = sqrt_fast(Sk);
     } else {
         cQp = chol(Qp, ok);
         Qpinv = chol_inverse(cQp);
@@ -346,7 +348,7 @@ __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
     }
     double quad = 0.0;
     if constexpr (D == 1 && G == 1) {
-        const double sL = 1.4142135623730951 * LS(0, 0), m1 = mk(0), A1 = Ak(0, 0), b1 = bk(0), qi = Qpinv(0, 0);
+        const double sL = 1.4142135623730951 * LS(0, 0), m1 = mk(0), omA = 1.0 - Ak(0, 0), nb = -bk(0);
         double quad_ = 0.0;
 #pragma unroll
         for (int p = 0; p < H; ++p) {
@@ -354,10 +356,10 @@ __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
             Mat<1> J;
             X(0) = fma(sL, gh_x<H>(p), m1);
             Drift<DRIFT, 1>::eval(P, X, f, J);
-            const double d = (X(0) + dt * f(0)) - (A1 * X(0) + b1);
-            quad_ = fma(gh_w<H>(p) * d, qi * d, quad_);
+            const double d = fma(dt, f(0), fma(omA, X(0), nb));   // x + dt f(x) - (A x + b)
+            quad_ = fma(gh_w<H>(p) * d, d, quad_);
         }
-        quad = pi_factor * quad_;
+        quad = (pi_factor * Qpinv(0, 0)) * quad_;
     } else {
     constexpr int NP = NodeCount<H, D>::value;
     for (int p = lane; p < NP; p += G) {

@@ -96,6 +96,24 @@ template <int D, int L>
 __device__ __forceinline__ SchurElem<D> chol_tile_summary(const double* sKd, const double* sKs, int k0, int len) {
     constexpr int DD = D * D;
     SchurElem<D> e = SchurOps<D>::identity();
+    if constexpr (D == 1) {
+        if (len == L) {   // full chunk: preloaded operands, unrolled; Lb carries the only serial dependency
+            double ks[L], kd[L];
+#pragma unroll
+            for (int t = 0; t < L; ++t) { ks[t] = sKs[k0 + t]; kd[t] = sKd[k0 + t + 1]; }
+            double La = 0.0, Lab = ks[0], Lb = kd[0];
+#pragma unroll
+            for (int t = 1; t < L; ++t) {
+                const double r = rcp_fast(Lb);
+                const double ur = Lab * r;
+                La = fma(-ur, Lab, La);
+                Lab = ur * ks[t];
+                Lb = fma(-(ks[t] * ks[t]), r, kd[t]);
+            }
+            e.La.a[0] = La; e.Lab.a[0] = Lab; e.Lb.a[0] = Lb; e.id = 0;
+            return e;
+        }
+    }
     for (int t = 0; t < len; ++t)
         SchurOps<D>::push(e, mat_load<D>(sKs + (k0 + t) * DD), mat_load<D>(sKd + (k0 + t + 1) * DD));
     return e;
@@ -108,20 +126,42 @@ __device__ __forceinline__ void chol_tile_recursion(double* sKd, double* sKs, in
     constexpr int DD = D * D;
     if (len <= 0) return;
     if constexpr (D == 1) {
-        // scalar: one rsqrt seed gives the pivot and its reciprocal
-        double s = S.a[0], Lk, rL;
-        if (!(s > 0.0)) report_not_pd(status, flat_node0 + k0);
-        sqrt_rsqrt_fast(s, Lk, rL);
-        sKd[k0] = Lk;
-        for (int t = 0; t < len; ++t) {
-            const double Lsub = div_r(sKs[k0 + t], Lk, rL);
-            sKs[k0 + t] = Lsub;
-            if (t < len - 1 || k0 + t + 1 == last_node) {
-                s = sKd[k0 + t + 1] - Lsub * Lsub;
-                if (!(s > 0.0)) report_not_pd(status, flat_node0 + k0 + t + 1);
+        // Scalar.  The only step-to-step dependency is the Schur complement S_{t+1} = Kd_{t+1} - Ks_t^2 / S_t
+        // (one reciprocal + one fma on the critical path); the factor entries L_t = sqrt(S_t) and
+        // L_{t+1,t} = Ks_t / L_t hang off it and overlap with the following steps.
+        if (len == L && last_node < 0) {   // full chunk: operands preloaded, loops unrolled
+            double ks[L], kd[L];
+#pragma unroll
+            for (int t = 0; t < L; ++t) { ks[t] = sKs[k0 + t]; kd[t] = (t < L - 1) ? sKd[k0 + t + 1] : 0.0; }
+            double s = S.a[0];   // (node k0 + L belongs to the next chunk: never read here, its owner rewrites it)
+            int bad = -1;
+#pragma unroll
+            for (int t = 0; t < L; ++t) {
+                if (!(s > 0.0) && bad < 0) bad = t;
+                const double r = rcp_fast(s);
+                double Lk, rL;
                 sqrt_rsqrt_fast(s, Lk, rL);
-                sKd[k0 + t + 1] = Lk;
+                sKd[k0 + t] = Lk;
+                sKs[k0 + t] = div_r(ks[t], Lk, rL);
+                if (t < L - 1) s = fma(-(ks[t] * ks[t]), r, kd[t]);
             }
+            if (bad >= 0) report_not_pd(status, flat_node0 + k0 + bad);
+            return;
+        }
+        double s = S.a[0];
+        for (int t = 0; t < len; ++t) {
+            if (!(s > 0.0)) report_not_pd(status, flat_node0 + k0 + t);
+            const double ks = sKs[k0 + t];
+            const double r = rcp_fast(s);
+            double Lk, rL;
+            sqrt_rsqrt_fast(s, Lk, rL);
+            sKd[k0 + t] = Lk;
+            sKs[k0 + t] = div_r(ks, Lk, rL);
+            if (t < len - 1 || k0 + len == last_node) s = fma(-(ks * ks), r, sKd[k0 + t + 1]);
+        }
+        if (k0 + len == last_node) {
+            if (!(s > 0.0)) report_not_pd(status, flat_node0 + last_node);
+            sKd[last_node] = sqrt_fast(s);
         }
         return;
     }
