@@ -142,6 +142,22 @@ def cpu_oracle_steps_per_s(B_per_core, N, seed, updates=1, cores=None):
     return B_per_core * cores * N * updates / dt, dt, cores
 
 
+def cpu_c_steps_per_s(B, N, seed, updates, threads):
+    """The C / OpenMP restatement of the oracle (oracle/cvi_d1.c) on `threads` host cores: B sequences x
+    `updates` site updates after one warm update.  Returns (grid-steps/s, seconds)."""
+    from oracle import c_port
+    from oracle.sde_np import DRIFT_DW
+    grid, idx, y = make_problem(B, N, seed)
+    ref = c_port.CBatchedCVISitesSDE1D(DRIFT_DW, DW_PARAMS, 1.0, grid, idx, y, NOISE_STD, X0_MU, X0_COV,
+                                       threads=threads)
+    ref.site_update(LR, LR)
+    t0 = time.perf_counter()
+    for _ in range(updates):
+        ref.site_update(LR, LR)
+    dt = time.perf_counter() - t0
+    return B * N * updates / dt, dt
+
+
 # algorithmic (compulsory) float64 values moved per grid step by each phase's kernels: (vectors, matrices)
 # read + written once; bytes = 8 * (v * D + M * D^2).  Stated per kernel in DESIGN.md section 4.
 PHASE_TRAFFIC = {
@@ -269,8 +285,11 @@ def run_ours(args):
         t = json.load(open(tpath))
         if t.get("B") == B and t.get("N") == N:
             traffic = t.get("dram_bytes_per_launch_by_phase", {}).get(dom)
-    cpu_B = 64
-    cpu_val, cpu_s, cpu_cores = cpu_oracle_steps_per_s(cpu_B, N, seed=4096, updates=2)
+    cpu_cores = len(os.sched_getaffinity(0))
+    cpu_B = 64 * cpu_cores
+    cpu_val, cpu_s = cpu_c_steps_per_s(cpu_B, N, seed=4096, updates=10, threads=cpu_cores)
+    cpu_1, cpu_1s = cpu_c_steps_per_s(16, N, seed=4096, updates=10, threads=1)
+    np_val, np_s, _ = cpu_oracle_steps_per_s(16, N, seed=4096, updates=1, cores=1)
     line = {
         "metric": "grid-steps/sec per CVI-DP site update", "value": value, "unit": "grid-steps/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
@@ -296,8 +315,12 @@ def run_ours(args):
                             "frac": value * ALGO_BYTES_PER_STEP_D1 / world / 1e9 / peak},
         "phases": phases,
         "cpu_baseline": {"value": cpu_val, "unit": "grid-steps/s", "cores": cpu_cores, "kind": "port",
-                         "sample": f"{cpu_cores} processes x {cpu_B} sequences x {N} grid steps x 2 site updates, "
-                                   f"NumPy oracle (oracle/scalar_d1.py), {cpu_s:.1f} s"},
+                         "sample": f"C/OpenMP restatement of the oracle (oracle/cvi_d1.c, gcc -O2), {cpu_cores} "
+                                   f"threads x 64 sequences x {N} grid steps x 10 site updates, {cpu_s:.1f} s",
+                         "single_thread": {"value": cpu_1, "sample": f"16 sequences x 10 updates, {cpu_1s:.1f} s"},
+                         "numpy_oracle_1_process": {"value": np_val,
+                                                    "sample": f"oracle/scalar_d1.py, 16 sequences x 1 update, "
+                                                              f"{np_s:.1f} s"}},
     }
     print(json.dumps(line))
     if world > 1:
@@ -342,23 +365,26 @@ def run_vdp(args):
 
 
 def run_reference(args):
-    """The reference's CPU path = the oracle port on all host cores (TensorFlow is not installable here)."""
+    """The reference's CPU path = the C/OpenMP port of the oracle on all host cores (TensorFlow is not installable
+    here; DESIGN.md)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps = max(1, min(args.steps, 3))
-    B = args.ref_seqs
-    value, dt, cores = cpu_oracle_steps_per_s(B, args.grid, seed=4096, updates=steps)
+    steps = max(1, args.steps)
+    cores = len(os.sched_getaffinity(0))
+    B = args.ref_seqs * cores
+    value, dt = cpu_c_steps_per_s(B, args.grid, seed=4096, updates=steps, threads=cores)
     line = {
         "impl": "reference", "metric": "grid-steps/sec per CVI-DP site update", "value": value,
         "unit": "grid-steps/s", "n_gpus": args.gpus, "steps": steps, "warmup": 1, "ms_per_step": dt / steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "C4: independent double-well sequences x dense grid, one CVI-DP site update per step",
-                   "sequences": B * cores, "grid_steps": args.grid, "state_dim": 1, "dt": DT, "n_obs": N_OBS,
+                   "sequences": B, "grid_steps": args.grid, "state_dim": 1, "dt": DT, "n_obs": N_OBS,
                    "quad_H": 20},
         "cpu_baseline": {"value": value, "unit": "grid-steps/s", "cores": cores, "kind": "port",
-                         "sample": f"{cores} processes x {B} sequences x {args.grid} grid steps x {steps} site updates "
-                                   f"(bounded sample of the 4096-sequence workload)"},
+                         "sample": f"C/OpenMP restatement of the oracle (oracle/cvi_d1.c), {cores} threads, {B} sequences "
+                                   f"x {args.grid} grid steps x {steps} site updates (bounded sample of the "
+                                   f"4096-sequence workload), {dt:.1f} s"},
         "e2e": {"value": value, "unit": "grid-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
