@@ -81,6 +81,20 @@ int vdp_btd_matvec(const double* Md, const double* Ms, const double* x, double* 
 /* abs_log_det  (block_tri_diag.py:353-366): out[b] = sum_k sum_i log |Ld[b,k,i,i]| */
 int vdp_btd_logdet(const double* Ld, double* out, int64_t B, int64_t n, int D, void* stream);
 
+/* Band storage of banded_matrices for callers that hold `.as_band` tensors (block_tri_diag.py:206-237,
+ * block_to_band / band_to_block): band [B, R, n*D] row-major with band[r, j] = M[j + r, j] (row 0 = main
+ * diagonal), R = 2 D with a sub-diagonal (Ms != NULL), else D.  band_to_block mirrors the upper triangles of
+ * the diagonal blocks when symmetric != 0 and zeroes them otherwise. */
+int vdp_btd_block_to_band(const double* Md, const double* Ms, double* band, int64_t B, int64_t n, int D,
+                          void* stream);
+int vdp_btd_band_to_block(const double* band, double* Md, double* Ms, int symmetric, int64_t B, int64_t n, int D,
+                          void* stream);
+/* The triangular band solve of naturals_to_ssm_params (ssm_gaussian_transformations.py:470-483):
+ * block diagonal of A_inv^-T P, A_inv = LowerTriangularBlockTriDiagonal(I, -As), P = (Kd, Ks) symmetric:
+ * out_k = Kd_k + As_k^T Ks_k (k < n-1), out_{n-1} = Kd_{n-1}.   As, Ks [B,n-1,D,D]; Kd, out [B,n,D,D]. */
+int vdp_btd_conditional_precisions(const double* As, const double* Kd, const double* Ks, double* out, int64_t B,
+                                   int64_t n, int D, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * fused level
  * ---------------------------------------------------------------------------------------------- */

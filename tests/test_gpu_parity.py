@@ -317,3 +317,75 @@ def test_vgp_batched_matches_single():
             one.sweep(0.1)
         assert torch.equal(one.A[0], eng.A[bi]) and torch.equal(one.m[0], eng.m[bi])
         assert torch.equal(one.elbo_value[0], eng.elbo_value[bi])
+
+
+# ---------------------------------------------------------------------------------------------------
+# band storage of banded_matrices and the triangular band solve of naturals_to_ssm_params
+@pytest.mark.parametrize("D", [1, 2, 3])
+@pytest.mark.parametrize("with_sub", [True, False])
+def test_band_pack_roundtrip_and_dense(ops, D, with_sub):
+    rng = np.random.default_rng(D)
+    B, n = 3, 7
+    Kd, Ks = _spd(rng, B, n, D)
+    band = ops.btd_block_to_band(dev(Kd), dev(Ks) if with_sub else None).cpu().numpy()
+    dense = G.btd_to_dense(Kd, Ks if with_sub else None, symmetric=True)
+    R = 2 * D if with_sub else D
+    assert band.shape == (B, R, n * D)
+    for r in range(R):        # band[r, j] = M[j + r, j]  (lower band, row 0 = main diagonal)
+        for j in range(n * D):
+            want = dense[:, j + r, j] if j + r < n * D else 0.0
+            if not with_sub and (j % D) + r >= D:
+                want = 0.0
+            assert np.all(band[:, r, j] == want)
+    Md, Ms = ops.btd_band_to_block(torch.as_tensor(band).cuda(), D, symmetric=True, with_sub=with_sub)
+    assert np.array_equal(Md.cpu().numpy(), G.symmetrise_from_lower(Kd))
+    if with_sub:
+        assert np.array_equal(Ms.cpu().numpy(), Ks)
+    Ml, _ = ops.btd_band_to_block(torch.as_tensor(band).cuda(), D, symmetric=False, with_sub=with_sub)
+    assert np.array_equal(Ml.cpu().numpy(), np.tril(Kd))
+
+
+@pytest.mark.parametrize("D", [1, 2, 3])
+def test_conditional_precisions_match_dense_solve(ops, D):
+    rng = np.random.default_rng(10 + D)
+    B, n = 2, 6
+    Kd, Ks = _spd(rng, B, n, D)
+    As = rng.normal(size=(B, n - 1, D, D)) * 0.4
+    got = ops.btd_conditional_precisions(dev(As), dev(Kd), dev(Ks)).cpu().numpy()
+    P = G.btd_to_dense(Kd, Ks, symmetric=True)
+    eye = np.broadcast_to(np.eye(D), (B, n, D, D))
+    Ainv = G.btd_to_dense(eye, -As, symmetric=False)
+    full = np.linalg.solve(np.swapaxes(Ainv, -1, -2), P)
+    for k in range(n):
+        blk = full[:, k * D:(k + 1) * D, k * D:(k + 1) * D]
+        assert rel(got[:, k], blk) < 1e-12
+
+
+@pytest.mark.parametrize("which", ["ou3", "lorenz"])
+def test_site_update_3d(sweeps, which):
+    """BASELINE config 5 shape (D = 3) at a size the oracle finishes in seconds (8000 nodes per transition)."""
+    from vi_diffusion_processes_b200.cvi import CviEngine
+    rng = np.random.default_rng(23)
+    N, n_obs = 40, 8
+    grid = np.round(np.arange(N + 1) * 0.01, 2)
+    idx = np.sort(rng.choice(N + 1, n_obs, replace=False))
+    if which == "ou3":
+        sde, y, mu0 = S.OUNdSDE(0.5, np.eye(3)), rng.normal(size=(n_obs, 3)) * 0.5, np.zeros(3)
+    else:
+        mu0 = np.array([1.0, 1.0, 20.0])
+        sde, y = S.Lorenz63SDE(q=np.eye(3)), rng.normal(size=(n_obs, 3)) * 0.3 + mu0
+    x0 = S.Gaussian(mu0, 0.5 * np.eye(3))
+    lik = M.MultivariateGaussian(0.1 * np.eye(3))
+    ref = M.CVISitesSDE(sde, grid, (grid[idx], y), lik, prior_initial_state=x0)
+    eng = CviEngine(sde.drift_id, sde.params, sde.q, grid, idx, y, 0.1 * np.eye(3), x0.mu, x0.cov)
+    for it in range(2):
+        e = eng.site_update(0.3, 0.3)
+        r = ref.site_update(0.3, 0.3)
+        eng.check_status()
+        assert abs(e.item() - r) < TOL * abs(r)
+        assert rel(eng.fx_mus[0], ref.fx_mus) < TOL and rel(eng.fx_covs[0], ref.fx_covs) < TOL
+        th = ref.dist_p_nat() if hasattr(ref, "dist_p_nat") else None
+        for got, want in ((eng.g1[0], ref.girsanov_sites.nat1), (eng.gd[0], ref.girsanov_sites.nat2.block_diagonal),
+                          (eng.gs[0], ref.girsanov_sites.nat2.block_sub_diagonal)):
+            scale = max(np.abs(want).max(), 1e-3 * np.abs(eng.fx_covs[0].cpu().numpy()).max() ** -1)
+            assert rel(got, want, scale=scale) < TOL

@@ -102,6 +102,9 @@ SIGNATURES = {
     "vdp_btd_solve": (C.c_int, [vp, vp, vp, vp, C.c_int, i64, i64, C.c_int, vp]),
     "vdp_btd_matvec": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_int, i64, i64, C.c_int, vp]),
     "vdp_btd_logdet": (C.c_int, [vp, vp, i64, i64, C.c_int, vp]),
+    "vdp_btd_block_to_band": (C.c_int, [vp, vp, vp, i64, i64, C.c_int, vp]),
+    "vdp_btd_band_to_block": (C.c_int, [vp, vp, vp, C.c_int, i64, i64, C.c_int, vp]),
+    "vdp_btd_conditional_precisions": (C.c_int, [vp, vp, vp, vp, i64, i64, C.c_int, vp]),
     "vdp_gh_expect": (C.c_int, [C.c_int, c_dp, vp, vp, C.c_int, vp, vp, i64, C.c_int, vp, vp]),
     "vdp_linearize_to_ssm": (C.c_int, [C.c_int, c_dp, c_dp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_double,
                                        C.c_double, i64, i64, C.c_int, vp, vp]),

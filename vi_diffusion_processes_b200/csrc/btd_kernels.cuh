@@ -230,3 +230,77 @@ __global__ void k_btd_logdet(const double* __restrict__ Ld, double* __restrict__
 }
 
 }  // namespace vdp
+
+namespace vdp {
+
+// Lower-band storage of banded_matrices (block_tri_diag.py:206-237 -> block_to_band): band[r, j] = M[j + r, j],
+// row 0 = main diagonal, R = 2 D rows when there is a sub-diagonal (lower bandwidth 2 D - 1), else D rows.
+// One thread per band entry (b, r, j), j = c D + i0.
+template <int D>
+__global__ void k_block_to_band(const double* __restrict__ Md, const double* __restrict__ Ms, double* __restrict__ band,
+                                int64_t B, int64_t n) {
+    constexpr int DD = D * D;
+    const int R = Ms ? 2 * D : D;
+    const int64_t cols = n * D;
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= B * R * cols) return;
+    const int64_t b = i / (R * cols), rem = i % (R * cols);
+    const int r = (int)(rem / cols);
+    const int64_t j = rem % cols, c = j / D;
+    const int i0 = (int)(j % D), row = i0 + r;
+    double v = 0.0;
+    if (row < D) v = Md[(b * n + c) * DD + row * D + i0];
+    else if (row < 2 * D && Ms && c < n - 1) v = Ms[(b * (n - 1) + c) * DD + (row - D) * D + i0];
+    band[i] = v;
+}
+
+// band_to_block: the block diagonal (upper triangles mirrored when symmetric, zero otherwise) and sub-diagonal
+template <int D>
+__global__ void k_band_to_block(const double* __restrict__ band, double* __restrict__ Md, double* __restrict__ Ms,
+                                int symmetric, int64_t B, int64_t n) {
+    constexpr int DD = D * D;
+    const int R = Ms ? 2 * D : D;
+    const int64_t cols = n * D;
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= B * n) return;
+    const int64_t b = i / n, c = i % n;
+    const double* bd = band + b * R * cols;
+#pragma unroll
+    for (int row = 0; row < D; ++row)
+#pragma unroll
+        for (int col = 0; col < D; ++col) {
+            double v = 0.0;
+            if (row >= col) v = bd[(row - col) * cols + c * D + col];
+            else if (symmetric) v = bd[(col - row) * cols + c * D + row];
+            Md[i * DD + row * D + col] = v;
+        }
+    if (Ms && c < n - 1) {
+#pragma unroll
+        for (int row = 0; row < D; ++row)
+#pragma unroll
+            for (int col = 0; col < D; ++col)
+                Ms[(b * (n - 1) + c) * DD + row * D + col] = bd[(D + row - col) * cols + c * D + col];
+    }
+}
+
+// Block diagonal of  A_inv^-T P  with A_inv = LowerTriangularBlockTriDiagonal(I, -As) and P the symmetric
+// block-tridiagonal (Kd, Ks): the solve_triang_band(..., transpose_left=True) of
+// ssm_gaussian_transformations.py:470-481 followed by band_to_block(...)[..., :D, :] -- the conditional
+// precisions  Kd_k + A_k^T Ks_k  (k < n-1),  Kd_{n-1}.
+template <int D>
+__global__ void k_conditional_precisions(const double* __restrict__ As, const double* __restrict__ Kd,
+                                         const double* __restrict__ Ks, double* __restrict__ out, int64_t B,
+                                         int64_t n) {
+    constexpr int DD = D * D;
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= B * n) return;
+    const int64_t b = i / n, c = i % n;
+    Mat<D> p = mat_load<D>(Kd + i * DD);
+    if (c < n - 1) {
+        const int64_t t = b * (n - 1) + c;
+        p = p + Tmm(mat_load<D>(As + t * DD), mat_load<D>(Ks + t * DD));
+    }
+    mat_store<D>(out + i * DD, p);
+}
+
+}  // namespace vdp

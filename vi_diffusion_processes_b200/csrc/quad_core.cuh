@@ -20,6 +20,16 @@ __constant__ double c_gh_w20[20] = VDP_GH_W_20;
 template <int H> __device__ __forceinline__ double gh_x(int i) { return H == 10 ? c_gh_x10[i] : c_gh_x20[i]; }
 template <int H> __device__ __forceinline__ double gh_w(int i) { return H == 10 ? c_gh_w10[i] : c_gh_w20[i]; }
 
+// The same tables in global memory for lookups whose index differs from lane to lane (D >= 2: the lanes of a
+// group hold different nodes).  A constant-bank read is serialised once per distinct address in the warp (up
+// to 20 replays per lookup here); a read-only global load of a 160-byte table is one or two L1 wavefronts.
+__device__ const double d_gh_x10[10] = VDP_GH_X_10;
+__device__ const double d_gh_w10[10] = VDP_GH_W_10;
+__device__ const double d_gh_x20[20] = VDP_GH_X_20;
+__device__ const double d_gh_w20[20] = VDP_GH_W_20;
+template <int H> __device__ __forceinline__ double gh_x_div(int i) { return __ldg(H == 10 ? &d_gh_x10[i] : &d_gh_x20[i]); }
+template <int H> __device__ __forceinline__ double gh_w_div(int i) { return __ldg(H == 10 ? &d_gh_w10[i] : &d_gh_w20[i]); }
+
 template <int H, int D> struct NodeCount { static constexpr int value = H * NodeCount<H, D - 1>::value; };
 template <int H> struct NodeCount<H, 0> { static constexpr int value = 1; };
 
@@ -30,10 +40,15 @@ __device__ __forceinline__ void gh_node(int p, Vec<D>& xi, double& w) {
     int r = p;
 #pragma unroll
     for (int d = D - 1; d >= 0; --d) { idx[d] = r % H; r /= H; }
-    w = gh_w<H>(idx[0]);
-    xi(0) = gh_x<H>(idx[0]);
+    if constexpr (D == 1) {   // every lane of the warp asks for the same entry: constant-bank broadcast
+        w = gh_w<H>(idx[0]);
+        xi(0) = gh_x<H>(idx[0]);
+    } else {
+        w = gh_w_div<H>(idx[0]);
+        xi(0) = gh_x_div<H>(idx[0]);
 #pragma unroll
-    for (int d = 1; d < D; ++d) { w *= gh_w<H>(idx[d]); xi(d) = gh_x<H>(idx[d]); }
+        for (int d = 1; d < D; ++d) { w *= gh_w_div<H>(idx[d]); xi(d) = gh_x_div<H>(idx[d]); }
+    }
 }
 
 // X = sqrt(2) * (L xi) + m

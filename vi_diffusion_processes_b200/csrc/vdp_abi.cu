@@ -206,6 +206,37 @@ int vdp_btd_logdet(const double* Ld, double* out, int64_t B, int64_t n, int D, v
     return VDP_OK;
 }
 
+int vdp_btd_block_to_band(const double* Md, const double* Ms, double* band, int64_t B, int64_t n, int D,
+                          void* stream) {
+    VDP_REQUIRE(Md && band && B >= 0 && n >= 1, "Md, band, B, n");
+    if (B == 0) return VDP_OK;
+    const int64_t total = B * (Ms ? 2 * D : D) * n * D;
+    VDP_DISPATCH_D(D, (k_block_to_band<kD><<<grid_for(total, kPtBlock), kPtBlock, 0, as_stream(stream)>>>(
+                          Md, Ms, band, B, n)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+int vdp_btd_band_to_block(const double* band, double* Md, double* Ms, int symmetric, int64_t B, int64_t n, int D,
+                          void* stream) {
+    VDP_REQUIRE(band && Md && B >= 0 && n >= 1, "band, Md, B, n");
+    if (B == 0) return VDP_OK;
+    VDP_DISPATCH_D(D, (k_band_to_block<kD><<<grid_for(B * n, kPtBlock), kPtBlock, 0, as_stream(stream)>>>(
+                          band, Md, Ms, symmetric, B, n)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+int vdp_btd_conditional_precisions(const double* As, const double* Kd, const double* Ks, double* out, int64_t B,
+                                   int64_t n, int D, void* stream) {
+    VDP_REQUIRE(Kd && out && B >= 0 && n >= 1 && (n == 1 || (As && Ks)), "As, Kd, Ks, out, B, n");
+    if (B == 0) return VDP_OK;
+    VDP_DISPATCH_D(D, (k_conditional_precisions<kD><<<grid_for(B * n, kPtBlock), kPtBlock, 0, as_stream(stream)>>>(
+                          As, Kd, Ks, out, B, n)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
 }  // extern "C"
 
 #include "vdp_fused.inl"

@@ -64,6 +64,12 @@ class BlockTriDiagonal:
             cols.append(ops.btd_matvec(d, s, e.reshape(B, n, D), self._symmetric, False).reshape(B, n * D))
         return unbatched(torch.stack(cols, dim=-1), had)
 
+    @property
+    def as_band(self) -> torch.Tensor:
+        """block_tri_diag.py:110-118, 206-237: lower-band storage [..., R, n*D], band[r, j] = M[j + r, j]."""
+        d, s, had = self._b()
+        return unbatched(ops.btd_block_to_band(d, s), had)
+
     def dense_mult(self, right: torch.Tensor, transpose_left: bool = False) -> torch.Tensor:
         """block_tri_diag.py:175-199: ``self @ right`` (or ``self^T @ right``), right [..., n, D]."""
         d, s, had = self._b()

@@ -101,6 +101,37 @@ def btd_logdet(Ld):
     return out
 
 
+def btd_block_to_band(Md, Ms=None):
+    """block_tri_diag.py:206-237 (`as_band`): [B,n,D,D] (+ [B,n-1,D,D]) -> [B, R, n*D], R = 2D or D."""
+    _req(Md, Ms)
+    B, n, D = _bnd(Md)
+    band = torch.empty((B, (2 * D if Ms is not None else D), n * D), dtype=F64, device=Md.device)
+    check(_lib.load().vdp_btd_block_to_band(_p(Md), _p(Ms), _p(band), B, n, D, _stream()), "vdp_btd_block_to_band")
+    return band
+
+
+def btd_band_to_block(band, D, symmetric, with_sub=True):
+    _req(band)
+    B, R, cols = band.shape
+    n = cols // D
+    assert R == (2 * D if with_sub else D) and cols == n * D, band.shape
+    Md = torch.empty((B, n, D, D), dtype=F64, device=band.device)
+    Ms = torch.empty((B, n - 1, D, D), dtype=F64, device=band.device) if with_sub else None
+    check(_lib.load().vdp_btd_band_to_block(_p(band), _p(Md), _p(Ms), int(symmetric), B, n, D, _stream()),
+          "vdp_btd_band_to_block")
+    return Md, Ms
+
+
+def btd_conditional_precisions(As, Kd, Ks):
+    """ssm_gaussian_transformations.py:470-483: block diagonal of A_inv^-T P."""
+    _req(As, Kd, Ks)
+    B, n, D = _bnd(Kd)
+    out = torch.empty_like(Kd)
+    check(_lib.load().vdp_btd_conditional_precisions(_p(As), _p(Kd), _p(Ks), _p(out), B, n, D, _stream()),
+          "vdp_btd_conditional_precisions")
+    return out
+
+
 # ------------------------------------------------------------------ fused level
 
 
