@@ -103,6 +103,81 @@ __device__ __forceinline__ void kl_term_scalar(const DriftParams& P, double Qp, 
     out.right.gS(0, 0) = RgS;
 }
 
+// D = 3 quadrature over the tensor-product nodes as nested loops: the lanes of the warp stride over the 400
+// (i0, i1) pairs, the inner loop runs over the last coordinate with a warp-uniform table index.  chol(S) is lower
+// triangular, so only X_2 changes in the inner loop; everything that depends on (X_0, X_1) alone -- the partial
+// residual c = X - (A X + b), the j = 0, 1 columns of the accumulators -- is hoisted per pair.  Same sums as the
+// flat loop of kl_term (other association of the partial sums), about half the float64 operations per node.
+template <int DRIFT, int H, bool GRAD>
+__device__ __forceinline__ void kl_quad_nested3(const DriftParams& P, const Mat<3>& LS, const Vec<3>& m,
+                                                const Mat<3>& A, const Vec<3>& b, const Mat<3>& Qs, double dt,
+                                                int lane, double& quad, Vec<3>& gb, Vec<3>& gmq, Mat<3>& gA,
+                                                Mat<3>& LSb) {
+    constexpr double R2 = 1.4142135623730951;
+    quad = 0.0;
+    gb = vec_zero<3>(); gmq = vec_zero<3>(); gA = mat_zero<3>(); LSb = mat_zero<3>();
+    const double s22 = R2 * LS(2, 2);
+    Mat<3> IA;   // I - A
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) IA(i, j) = ((i == j) ? 1.0 : 0.0) - A(i, j);
+    for (int o = lane; o < H * H; o += 32) {
+        const int i0 = o / H, i1 = o - i0 * H;
+        const double x0 = gh_x_div<H>(i0), x1 = gh_x_div<H>(i1);
+        const double w01 = gh_w_div<H>(i0) * gh_w_div<H>(i1);
+        const double X0 = R2 * (LS(0, 0) * x0) + m(0);
+        const double X1 = R2 * (LS(1, 0) * x0 + LS(1, 1) * x1) + m(1);
+        const double X2base = R2 * (LS(2, 0) * x0 + LS(2, 1) * x1) + m(2);
+        // c_i = (X_i [i < 2]) - (A_i0 X0 + A_i1 X1 + b_i)
+        const double c0 = X0 - (A(0, 0) * X0 + A(0, 1) * X1 + b(0));
+        const double c1 = X1 - (A(1, 0) * X0 + A(1, 1) * X1 + b(1));
+        const double c2 = -(A(2, 0) * X0 + A(2, 1) * X1 + b(2));
+        double q_o = 0.0, rb0 = 0.0, rb1 = 0.0, rb2 = 0.0, xb0 = 0.0, xb1 = 0.0, xb2 = 0.0;
+        double ra0 = 0.0, ra1 = 0.0, ra2 = 0.0, xs2 = 0.0;
+#pragma unroll 4
+        for (int i2 = 0; i2 < H; ++i2) {
+            const double x2 = gh_x<H>(i2), w2 = gh_w<H>(i2);
+            Vec<3> X, f;
+            Mat<3> J;
+            X(0) = X0; X(1) = X1; X(2) = fma(s22, x2, X2base);
+            Drift<DRIFT, 3>::eval(P, X, f, J);
+            const double d0 = fma(dt, f(0), fma(-A(0, 2), X(2), c0));
+            const double d1 = fma(dt, f(1), fma(-A(1, 2), X(2), c1));
+            const double d2 = fma(dt, f(2), fma(IA(2, 2), X(2), c2));
+            const double u0 = w2 * (Qs(0, 0) * d0 + Qs(0, 1) * d1 + Qs(0, 2) * d2);
+            const double u1 = w2 * (Qs(1, 0) * d0 + Qs(1, 1) * d1 + Qs(1, 2) * d2);
+            const double u2 = w2 * (Qs(2, 0) * d0 + Qs(2, 1) * d1 + Qs(2, 2) * d2);
+            q_o += d0 * u0 + d1 * u1 + d2 * u2;
+            if (GRAD) {
+                // Xb = ((I + dt J) - A)^T u
+                const double v0 = fma(dt, J(0, 0) * u0 + J(1, 0) * u1 + J(2, 0) * u2,
+                                      IA(0, 0) * u0 + IA(1, 0) * u1 + IA(2, 0) * u2);
+                const double v1 = fma(dt, J(0, 1) * u0 + J(1, 1) * u1 + J(2, 1) * u2,
+                                      IA(0, 1) * u0 + IA(1, 1) * u1 + IA(2, 1) * u2);
+                const double v2 = fma(dt, J(0, 2) * u0 + J(1, 2) * u1 + J(2, 2) * u2,
+                                      IA(0, 2) * u0 + IA(1, 2) * u1 + IA(2, 2) * u2);
+                rb0 += u0; rb1 += u1; rb2 += u2;
+                xb0 += v0; xb1 += v1; xb2 += v2;
+                ra0 = fma(u0, X(2), ra0); ra1 = fma(u1, X(2), ra1); ra2 = fma(u2, X(2), ra2);
+                xs2 = fma(v2, x2, xs2);
+            }
+        }
+        quad = fma(w01, q_o, quad);
+        if (GRAD) {
+            rb0 *= w01; rb1 *= w01; rb2 *= w01; xb0 *= w01; xb1 *= w01; xb2 *= w01;
+            gb(0) -= rb0; gb(1) -= rb1; gb(2) -= rb2;
+            gmq(0) += xb0; gmq(1) += xb1; gmq(2) += xb2;
+            gA(0, 0) -= rb0 * X0; gA(0, 1) -= rb0 * X1; gA(0, 2) -= w01 * ra0;
+            gA(1, 0) -= rb1 * X0; gA(1, 1) -= rb1 * X1; gA(1, 2) -= w01 * ra1;
+            gA(2, 0) -= rb2 * X0; gA(2, 1) -= rb2 * X1; gA(2, 2) -= w01 * ra2;
+            LSb(0, 0) += xb0 * x0;
+            LSb(1, 0) += xb1 * x0; LSb(1, 1) += xb1 * x1;
+            LSb(2, 0) += xb2 * x0; LSb(2, 1) += xb2 * x1; LSb(2, 2) += w01 * xs2;
+        }
+    }
+}
+
 // One transition term.  Inputs are the expectation parameters rebuilt from (A_q, m, S) exactly as
 // ssm_to_expectations does (ssm_gaussian_transformations.py:32-89).
 template <int DRIFT, int D, int H, int G>
@@ -131,7 +206,16 @@ __device__ __forceinline__ void kl_term(const DriftParams& P, const Mat<D>& Qp, 
     Vec<D> gb = vec_zero<D>(), gmq = vec_zero<D>();
     Mat<D> gA = mat_zero<D>(), LSb = mat_zero<D>();
     constexpr int NP = NodeCount<H, D>::value;
-    for (int p = lane; p < NP; p += G) {
+    constexpr bool kNested = (D == 3 && G == 32);
+    if constexpr (kNested) {
+        kl_quad_nested3<DRIFT, H, true>(P, r.LS, r.mk, r.A, r.b, Qpinv_s, dt, lane, quad, gb, gmq, gA, LSb);
+        quad *= pi_factor;
+#pragma unroll
+        for (int i = 0; i < D; ++i) { gb(i) *= pi_factor; gmq(i) *= pi_factor; }
+#pragma unroll
+        for (int e = 0; e < D * D; ++e) { gA.a[e] *= pi_factor; LSb.a[e] *= 1.4142135623730951 * pi_factor; }
+    }
+    for (int p = lane; p < (kNested ? 0 : NP); p += G) {
         Vec<D> xi, f;
         Mat<D> J;
         double w;
@@ -362,7 +446,14 @@ __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
         quad = (pi_factor * Qpinv(0, 0)) * quad_;
     } else {
     constexpr int NP = NodeCount<H, D>::value;
-    for (int p = lane; p < NP; p += G) {
+    constexpr bool kNested = (D == 3 && G == 32);
+    if constexpr (kNested) {
+        Vec<3> t1, t2;
+        Mat<3> t3, t4;
+        kl_quad_nested3<DRIFT, H, false>(P, LS, mk, Ak, bk, sym(Qpinv), dt, lane, quad, t1, t2, t3, t4);
+        quad *= pi_factor;
+    }
+    for (int p = lane; p < (kNested ? 0 : NP); p += G) {
         Vec<D> xi, f, d;
         Mat<D> J;
         double w;
