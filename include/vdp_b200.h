@@ -212,6 +212,17 @@ typedef struct vdp_cvi_problem {
 
 size_t vdp_cvi_workspace(int64_t B, int64_t N, int D, int64_t n_obs);
 int vdp_cvi_site_update(const vdp_cvi_problem* problem_host, void* stream);
+/* Sharded quadrature (one long sequence over several GPUs, BASELINE config 5, where the H^D-node quadrature is
+ * > 95 % of the update): every rank holds the whole chain and runs the cheap rebuilds on it, the quadrature and the
+ * girsanov site update only on its own range [node_begin, node_end) of the flat (sequence, grid point) index.
+ *   phase 0: update_data_sites, rebuild, KL gradient + site update of the range   -> g1, gd, gs (range only)
+ *            ... the caller exchanges the updated site ranges between ranks (broadcast / all-gather) ...
+ *   phase 1: rebuild, variational expectation (whole chain), KL value of the range -> ve [B], kl [B] = the
+ *            range's partial sum (KL_0 with the range holding grid point 0), elbo = ve - partial kl
+ *            ... the caller sums the partial kl over ranks: ELBO = ve - sum_r kl_r ...
+ * With the full range [0, B (N+1)) the two phases together equal vdp_cvi_site_update. */
+int vdp_cvi_site_update_sharded(const vdp_cvi_problem* problem_host, int phase, int64_t node_begin,
+                                int64_t node_end, void* stream);
 /* classic_elbo only (no site is modified); fills elbo/ve/kl, q* and fx_* */
 int vdp_cvi_elbo(const vdp_cvi_problem* problem_host, void* stream);
 

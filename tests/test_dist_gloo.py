@@ -109,3 +109,57 @@ def test_sequence_sharding_world_size_2():
     assert res[0][1] == res[1][1] == 11.0          # max over ranks
     assert res[0][2] != res[1][2]                  # different sequences per rank
     assert res[0][3] == res[1][3] == (4, 50)
+
+
+class _FakeEngine:
+    """Stands in for CviEngine in the exchange logic of dist_quad (CPU tensors, no kernels)."""
+
+    def __init__(self, N, D, rank):
+        self.B, self.N, self.D = 1, N, D
+        self.g1 = torch.full((1, N + 1, D), float(rank), dtype=torch.float64)
+        self.gd = torch.full((1, N + 1, D, D), float(rank), dtype=torch.float64)
+        self.gs = torch.full((1, N, D, D), float(rank), dtype=torch.float64)
+        self.kl = torch.tensor([1.0 + rank], dtype=torch.float64)
+        self.ve = torch.tensor([10.0], dtype=torch.float64)
+        self.elbo = torch.zeros(1, dtype=torch.float64)
+        self.calls = []
+
+    def site_update_sharded(self, phase, n0, n1, lr_data=0.0, lr_girsanov=0.0):
+        self.calls.append((phase, n0, n1))
+
+
+def _quad_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from vi_diffusion_processes_b200.dist_quad import ShardedQuadratureCvi
+        from vi_diffusion_processes_b200.dist_time import Comm
+        N, D = 13, 2
+        eng = _FakeEngine(N, D, rank)
+        sh = ShardedQuadratureCvi([eng], Comm.from_process_group())
+        elbo = sh.site_update(0.5, 0.5)
+        q.put((rank, elbo, eng.calls, eng.g1[0, :, 0].tolist(), eng.gs[0, :, 0, 0].tolist(), sh.parts))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_quadrature_exchange_world_size_2():
+    world = 2
+    port = _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_quad_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    parts = res[0][5]
+    (s0, e0), (s1, e1) = parts
+    for rank, elbo, calls, g1, gs, _ in res:
+        assert elbo == 10.0 - (1.0 + 2.0)                     # ve - sum of the ranks' partial KL
+        n0, n1 = (s0, e0) if rank == 0 else (s1, e1 + 1)      # the last rank owns the final grid point
+        assert calls == [(0, n0, n1), (1, n0, n1)]
+        assert g1 == [0.0] * e0 + [1.0] * (e1 + 1 - s1)       # every rank holds every rank's site range
+        assert gs == [0.0] * e0 + [1.0] * (e1 - s1)

@@ -123,6 +123,7 @@ SIGNATURES = {
                                       C.c_size_t, i64, i64, C.c_int, vp, vp]),
     "vdp_cvi_workspace": (C.c_size_t, [i64, i64, C.c_int, i64]),
     "vdp_cvi_site_update": (C.c_int, [C.POINTER(CviProblem), vp]),
+    "vdp_cvi_site_update_sharded": (C.c_int, [C.POINTER(CviProblem), C.c_int, i64, i64, vp]),
     "vdp_cvi_elbo": (C.c_int, [C.POINTER(CviProblem), vp]),
     "vdp_cvi_host_create": (C.c_int, [C.POINTER(vp), i64, i64, C.c_int, i64, C.c_int, C.c_int]),
     "vdp_cvi_host_set_prior": (C.c_int, [vp, i64, vp, vp, vp, vp, vp]),

@@ -299,7 +299,9 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
                           const double* __restrict__ Sd, double* __restrict__ terms, double* __restrict__ g1,
                           double* __restrict__ gd, double* __restrict__ gs, int upd, double lr,
                           const double* __restrict__ sc1, const double* __restrict__ scd, int64_t B, int64_t N,
-                          int64_t* status) {
+                          int64_t* status, int64_t node0 = 0, int64_t node1 = -1) {
+    // nodes [node0, node1) of the flat (b, k) index are processed (default: all); a rank of the sharded
+    // quadrature passes its own range, the halo group recomputes the term that straddles the range start
     extern __shared__ unsigned char smem_raw[];
     KlHandoff<D>* hand = reinterpret_cast<KlHandoff<D>*>(smem_raw);
     constexpr int DD = D * D;
@@ -307,8 +309,8 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
     const int gidx = threadIdx.x / G;
     const int lane = threadIdx.x % G;
     const int64_t n = N + 1;
-    const int64_t total = B * n;
-    const int64_t i = (int64_t)blockIdx.x * (groups - 1) + gidx - 1;   // flat node index of this group
+    const int64_t total = (node1 < 0) ? B * n : node1;
+    const int64_t i = node0 + (int64_t)blockIdx.x * (groups - 1) + gidx - 1;   // flat node index of this group
     const bool in_range = (i >= 0) && (i < total);
     int64_t b = 0, k = 0;
     if (in_range) { b = i / n; k = i % n; }
@@ -391,11 +393,11 @@ __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
                            const double* __restrict__ Sd, const double* __restrict__ qmu0,
                            const double* __restrict__ qcholP0, const double* __restrict__ pmu0,
                            const double* __restrict__ pcholP0, double* __restrict__ terms, int64_t B, int64_t N,
-                           int64_t* status) {
-    const int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / G;
+                           int64_t* status, int64_t node0 = 0, int64_t node1 = -1) {
+    const int64_t i = node0 + (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / G;
     const int lane = threadIdx.x % G;
     const int64_t n = N + 1;
-    if (i >= B * n) return;
+    if (i >= ((node1 < 0) ? B * n : node1)) return;
     constexpr int DD = D * D;
     const int64_t b = i / n, k = i % n;
     if (k == N) { if (lane == 0) terms[i] = 0.0; return; }

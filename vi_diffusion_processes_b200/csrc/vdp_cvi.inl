@@ -14,14 +14,15 @@ static int launch_kl_grad(const DriftParams& P, const double* q_host, double dt,
                           const double* x0_mu, const double* x0_cov, const double* Aq, const double* m,
                           const double* Sd, double* terms, double* g1, double* gd, double* gs, int upd, double lr,
                           const double* sc1, const double* scd, int64_t B, int64_t N, int64_t* status,
-                          cudaStream_t st) {
+                          cudaStream_t st, int64_t node0 = 0, int64_t node1 = -1) {
     using KL = KlLaunch<D>;
-    const int64_t total = B * (N + 1);
+    const int64_t total = ((node1 < 0) ? B * (N + 1) : node1) - node0;
+    if (total <= 0) return VDP_OK;
     const unsigned grid = (unsigned)((total + KL::groups - 2) / (KL::groups - 1));
     const size_t smem = KL::groups * sizeof(KlHandoff<D>);
     k_kl_grad<DRIFT, D, 20, KL::G><<<grid, KL::threads, smem, st>>>(
         P, host_mat<D>(q_host), dt, pi_factor(D), time_grid, host_vec<D>(x0_mu), host_mat<D>(x0_cov), Aq, m, Sd,
-        terms, g1, gd, gs, upd, lr, sc1, scd, B, N, status);
+        terms, g1, gd, gs, upd, lr, sc1, scd, B, N, status, node0, node1);
     VDP_CHECK_LAUNCH();
     return VDP_OK;
 }
@@ -80,17 +81,23 @@ static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t 
 }
 
 template <int DRIFT, int D>
-static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams& P, cudaStream_t st) {
+static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams& P, cudaStream_t st,
+                    int64_t node0 = 0, int64_t node1 = -1) {
     const int64_t B = p.B, N = p.N;
     constexpr int G = QuadGroup<D>::value;
     prof_mark(VDP_PHASE_ELBO, st);
+    const bool ranged = node1 >= 0;
+    const int64_t cnt = (ranged ? node1 : B * (N + 1)) - node0;
+    if (ranged) VDP_CHECK_CUDA(cudaMemsetAsync(w.terms, 0, (size_t)B * (N + 1) * sizeof(double), st));
     k_variational_expectation<D><<<grid_for(B, kSeqBlock), kSeqBlock, 0, st>>>(
         p.fx_mus, p.fx_covs, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.ve, B, N, p.n_obs);
     VDP_CHECK_LAUNCH();
-    k_kl_value<DRIFT, D, 20, G><<<grid_for(B * (N + 1) * G, kPtBlock), kPtBlock, 0, st>>>(
-        P, host_mat<D>(p.q), p.dt, pi_factor(D), p.qA, p.qb, p.qcholQ, p.fx_mus, p.fx_covs, p.qmu0, p.qcholP0,
-        p.pmu0, p.pcholP0, w.terms, B, N, p.status);
-    VDP_CHECK_LAUNCH();
+    if (cnt > 0) {
+        k_kl_value<DRIFT, D, 20, G><<<grid_for(cnt * G, kPtBlock), kPtBlock, 0, st>>>(
+            P, host_mat<D>(p.q), p.dt, pi_factor(D), p.qA, p.qb, p.qcholQ, p.fx_mus, p.fx_covs, p.qmu0, p.qcholP0,
+            p.pmu0, p.pcholP0, w.terms, B, N, p.status, node0, node1);
+        VDP_CHECK_LAUNCH();
+    }
     k_reduce_terms<<<(unsigned)B, 256, 0, st>>>(w.terms, N + 1, p.kl);
     VDP_CHECK_LAUNCH();
     k_elbo_combine<<<grid_for(B, kPtBlock), kPtBlock, 0, st>>>(p.ve, p.kl, p.elbo, B);
@@ -99,8 +106,11 @@ static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams&
     return VDP_OK;
 }
 
+// node0 / node1 >= 0: sharded quadrature (vdp_cvi_site_update_sharded): the rebuilds run on the whole chain, the
+// quadrature and the site update on the flat node range [node0, node1) only; stop_after_sites ends phase 0.
 template <int DRIFT, int D>
-static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t st) {
+static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t st, int64_t node0 = 0,
+                           int64_t node1 = -1, bool stop_after_sites = false) {
     const int64_t B = p.B, N = p.N;
     const DriftParams P = make_params(p.drift_params);
     int rc;
@@ -128,8 +138,9 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     }
     if ((rc = launch_kl_grad<DRIFT, D>(P, p.q, p.dt, p.time_grid, p.x0_mu, p.x0_cov, p.qA, p.fx_mus, p.fx_covs,
                                        w.terms, p.g1, p.gd, p.gs, 1, p.lr_girsanov, w.sc1, w.scd, B, N, p.status,
-                                       st)))
+                                       st, node0, node1)))
         return rc;
+    if (stop_after_sites) { prof_mark(VDP_PHASE_END, st); return VDP_OK; }
     if ((rc = run_posterior<D>(p, w, st))) return rc;
     // (C) classic_elbo  variational_cvi_sde.py:339-352
     if (!(p.flags & VDP_FLAG_SKIP_ELBO)) return run_elbo<DRIFT, D>(p, w, P, st);
@@ -190,6 +201,31 @@ int vdp_cvi_site_update(const vdp_cvi_problem* p, void* stream) {
     }
     VDP_DISPATCH_D(p->D, VDP_DISPATCH_DRIFT(p->drift_id, {
         rc = run_site_update<kDrift, kD>(*p, w, as_stream(stream));
+        if (rc) return rc;
+    }));
+    return VDP_OK;
+}
+
+int vdp_cvi_site_update_sharded(const vdp_cvi_problem* p, int phase, int64_t node_begin, int64_t node_end,
+                                void* stream) {
+    int rc = check_problem(p);
+    if (rc) return rc;
+    VDP_REQUIRE(phase == 0 || phase == 1, "phase must be 0 or 1");
+    VDP_REQUIRE(node_begin >= 0 && node_end >= node_begin && node_end <= p->B * (p->N + 1), "node range");
+    if (p->B == 0) return VDP_OK;
+    CviWs w;
+    if (!cvi_ws_take(p->workspace, p->workspace_bytes, p->B, p->N, p->D, w)) {
+        set_error("workspace too small: need %zu bytes", cvi_ws_bytes(p->B, p->N, p->D));
+        return VDP_E_WORKSPACE;
+    }
+    const DriftParams P = make_params(p->drift_params);
+    VDP_DISPATCH_D(p->D, VDP_DISPATCH_DRIFT(p->drift_id, {
+        if (phase == 0) {
+            rc = run_site_update<kDrift, kD>(*p, w, as_stream(stream), node_begin, node_end, true);
+        } else {
+            rc = run_posterior<kD>(*p, w, as_stream(stream));
+            if (!rc) rc = run_elbo<kDrift, kD>(*p, w, P, as_stream(stream), node_begin, node_end);
+        }
         if (rc) return rc;
     }));
     return VDP_OK;

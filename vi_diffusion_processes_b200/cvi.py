@@ -123,6 +123,12 @@ class CviEngine:
         check(_lib.load().vdp_cvi_site_update(C.byref(p), self._stream()), "vdp_cvi_site_update")
         return self.elbo
 
+    def site_update_sharded(self, phase, node_begin, node_end, lr_data=0.0, lr_girsanov=0.0):
+        """One phase of ``vdp_cvi_site_update_sharded`` on the flat node range [node_begin, node_end)."""
+        p = self._problem(lr_data, lr_girsanov)
+        check(_lib.load().vdp_cvi_site_update_sharded(C.byref(p), int(phase), int(node_begin), int(node_end),
+                                                      self._stream()), "vdp_cvi_site_update_sharded")
+
     def classic_elbo(self):
         p = self._problem(0.0, 0.0)
         check(_lib.load().vdp_cvi_elbo(C.byref(p), self._stream()), "vdp_cvi_elbo")
