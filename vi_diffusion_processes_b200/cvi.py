@@ -149,19 +149,25 @@ class CviEngine:
     def _prior_naturals(self, A, b):
         return ops.ssm_to_naturals(A, b, self.pcholQ, self.pmu0, self.pcholP0)
 
-    def relinearize(self):
-        cur = self._prior_naturals(self.pA, self.pb)
-        new = self._prior_naturals(self.pA_lin, self.pb_lin)
+    def _rebase_sites(self, cur, new):
         self.g1 = (self.g1 + cur[0] - new[0]).contiguous()
         self.gd = (self.gd + cur[1] - new[1]).contiguous()
         self.gs = (self.gs + cur[2] - new[2]).contiguous()
+
+    def to_linearized_prior(self):
+        """cvi_dp_trainer.py:110-113: re-base the sites from the (clipped) prior onto p_lin and adopt p_lin."""
+        self._rebase_sites(self._prior_naturals(self.pA, self.pb), self._prior_naturals(self.pA_lin, self.pb_lin))
         self.pA, self.pb = self.pA_lin, self.pb_lin
+
+    def relinearize_new(self):
+        """cvi_dp_trainer.py:128-134: linearise around the current posterior and re-base the sites onto it."""
         last = self._prior_naturals(self.pA, self.pb)
         self.set_linearized_prior()
-        new = self._prior_naturals(self.pA, self.pb)
-        self.g1 = (self.g1 + last[0] - new[0]).contiguous()
-        self.gd = (self.gd + last[1] - new[1]).contiguous()
-        self.gs = (self.gs + last[2] - new[2]).contiguous()
+        self._rebase_sites(last, self._prior_naturals(self.pA, self.pb))
+
+    def relinearize(self):
+        self.to_linearized_prior()
+        self.relinearize_new()
 
 
 class CviHostEngine:

@@ -150,5 +150,13 @@ class CVISitesSDE:
         """cvi_dp_trainer.py:110-134: tranform_girsanov_sites around set_linearized_prior."""
         self._eng.relinearize()
 
+    def transform_sites_to_linearized_prior(self):
+        """cvi_dp_trainer.py:110-113: ``tranform_girsanov_sites(sites, dist_p, dist_p_linearized)``; dist_p <- p_lin."""
+        self._eng.to_linearized_prior()
+
+    def relinearize_and_transform_sites(self):
+        """cvi_dp_trainer.py:128-134: ``set_linearized_prior`` + ``tranform_girsanov_sites(sites, p_last, dist_p)``."""
+        self._eng.relinearize_new()
+
     def loss(self):
         return -self.classic_elbo()

@@ -54,6 +54,9 @@ class VariationalMarkovGP:
     q_initial_mean = property(lambda s: s._get("q_initial_mean"), lambda s, v: s._set("q_initial_mean", v))
     q_initial_chol = property(lambda s: s._get("q_initial_chol"), lambda s, v: s._set("q_initial_chol", v))
 
+    m = property(lambda s: s._eng.m[0])     # marginals of the last forward pass
+    S = property(lambda s: s._eng.S[0])
+
     @property
     def forward_pass(self):
         """vi_sde.py:171-204 -> (m [N+1, D], S [N+1, D, D])"""

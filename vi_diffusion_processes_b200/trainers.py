@@ -1,0 +1,168 @@
+"""
+Mirrors of the reference's trainer loops around the hot path:
+
+* :class:`CVISitesTrainer`  -- ``docs/diffusion_processes/cvi_dp_trainer.py:18-160``: site updates until the ELBO
+  converges under a fixed linearised prior (learning-rate decay when it drops), then re-linearisation with the
+  girsanov sites re-based by ``tranform_girsanov_sites`` (``sde_utils.py:550-568``), until the outer ELBO converges;
+* :class:`VIMarkovGPTrainer` -- ``docs/diffusion_processes/vi_markov_gp_trainer.py:17-92``: the VDP fixed-point
+  iterations with learning-rate decay;
+* :func:`calculate_nlpd`, :func:`calculate_rmse` -- ``docs/diffusion_processes/exp_dp_utils.py:189-224``.
+
+Same constructor arguments, loop structure, break conditions and return values as the reference; logging, wandb and
+prior-parameter learning (``learn_prior_sde=True``; needs the adjoint of the linearisation, item 3 of 8f) are not
+part of this build.  The models are the ``markovflow`` mirrors of this package, i.e. every step runs through the
+C ABI on the GPU; the loop itself reads one ELBO scalar per iteration, as the reference does.
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+
+from .markovflow._util import as_np
+
+
+def _f(x) -> float:
+    return float(x.item()) if hasattr(x, "item") else float(x)
+
+
+def _test_indices(time_grid, test_t):
+    tg = as_np(time_grid).reshape(-1)
+    tt = as_np(test_t).reshape(-1)
+    return np.where(np.equal(tg[..., None], tt))[0]
+
+
+def calculate_nlpd(m, S, time_grid, test_data) -> float:
+    """exp_dp_utils.py:189-206: minus the mean Gaussian log predictive density at the test points.
+    m [N, D], S [N, D, D] (already passed through ``likelihood.predict_mean_and_var``)."""
+    m, S = torch.as_tensor(m), torch.as_tensor(S)
+    idx = torch.as_tensor(_test_indices(time_grid, test_data[0]), device=m.device)
+    y = torch.as_tensor(as_np(test_data[1]), dtype=m.dtype, device=m.device).reshape(idx.shape[0], -1)
+    mt, St = m.index_select(0, idx), S.index_select(0, idx)
+    L = torch.linalg.cholesky(St)
+    z = torch.linalg.solve_triangular(L, (y - mt)[..., None], upper=False)[..., 0]
+    D = mt.shape[-1]
+    logp = -0.5 * (z * z).sum(-1) - torch.log(torch.diagonal(L, dim1=-2, dim2=-1)).sum(-1) - 0.5 * D * math.log(2 * math.pi)
+    return float(-logp.mean().item())
+
+
+def calculate_rmse(m, time_grid, test_data) -> float:
+    """exp_dp_utils.py:209-224"""
+    m = torch.as_tensor(m)
+    idx = torch.as_tensor(_test_indices(time_grid, test_data[0]), device=m.device)
+    y = torch.as_tensor(as_np(test_data[1]), dtype=m.dtype, device=m.device).reshape(idx.shape[0], -1)
+    return float(torch.sqrt(torch.mean((m.index_select(0, idx) - y) ** 2)).item())
+
+
+class CVISitesTrainer:
+    """cvi_dp_trainer.py:18-160 (inference part)."""
+
+    def __init__(self, model, test_data, prior_sde=None, max_itr: int = 100, optim_tol: float = 1e-2,
+                 max_itr_sites_optim: int = 20, girsanov_sites_lr: float = 0.1, data_sites_lr: float = 0.1,
+                 learn_prior_sde: bool = False, **unused):
+        if learn_prior_sde:
+            raise NotImplementedError("prior-parameter learning is not part of this build (SURVEY 8f item 3)")
+        self.model, self.test_data, self.prior_sde = model, test_data, prior_sde
+        self.max_itr, self.optim_tol, self.max_itr_sites_optim = max_itr, optim_tol, max_itr_sites_optim
+        self.girsanov_sites_lr, self.data_sites_lr = girsanov_sites_lr, data_sites_lr
+
+    def _elbo(self) -> float:
+        return _f(self.model.classic_elbo())
+
+    def _marginals(self):
+        q = self.model.dist_q                     # cvi_dp_trainer.py:192-207: dist_q.marginals, rebuilt from the sites
+        q = q() if callable(q) else q
+        ms = q.marginals
+        return ms() if callable(ms) else ms
+
+    def model_nlpd(self) -> float:
+        m, S = self.model.likelihood.predict_mean_and_var(*self._marginals())
+        return calculate_nlpd(m, S, self.model.time_grid, self.test_data)
+
+    def model_rmse(self) -> float:
+        m, S = self.model.likelihood.predict_mean_and_var(*self._marginals())
+        return calculate_rmse(m, self.model.time_grid, self.test_data)
+
+    def _optimize_sites_under_stable_prior(self):
+        """cvi_dp_trainer.py:63-101"""
+        elbo, nlpd, rmse = [self._elbo()], [], []
+        while (len(elbo) - 1) < self.max_itr_sites_optim:
+            # update_data_sites; update_girsanov_sites; classic_elbo  == one fused vdp_cvi_site_update
+            elbo.append(_f(self.model.site_update(self.data_sites_lr, self.girsanov_sites_lr)))
+            nlpd.append(self.model_nlpd())
+            rmse.append(self.model_rmse())
+            if len(elbo) > 2 and elbo[-2] > elbo[-1]:
+                self.girsanov_sites_lr /= 10
+                self.data_sites_lr /= 10
+            if len(elbo) > 2 and abs(elbo[-2] - elbo[-1]) < self.optim_tol:
+                break
+        return elbo[1:], nlpd, rmse
+
+    def perform_inference(self):
+        """cvi_dp_trainer.py:103-136"""
+        elbo_vals, nlpd_vals, rmse_vals = [self._elbo()], [], []
+        for i in range(self.max_itr):
+            before = self._elbo()
+            e, n, r = self._optimize_sites_under_stable_prior()
+            self.model.transform_sites_to_linearized_prior()      # :110-113
+            after = self._elbo()
+            elbo_vals, nlpd_vals, rmse_vals = elbo_vals + e, nlpd_vals + n, rmse_vals + r
+            if abs(before - after) < self.optim_tol:
+                return elbo_vals[1:], nlpd_vals, rmse_vals
+            if i != self.max_itr - 1:                             # :128-134
+                self.model.relinearize_and_transform_sites()
+        return elbo_vals[1:], nlpd_vals, rmse_vals
+
+    def optimize(self):
+        """cvi_dp_trainer.py:138-190 without prior learning: one perform_inference."""
+        elbo, nlpd, rmse = [self._elbo()], [self.model_nlpd()], [self.model_rmse()]
+        e, n, r = self.perform_inference()
+        return elbo + e, nlpd + n, rmse + r, {}
+
+
+class VIMarkovGPTrainer:
+    """vi_markov_gp_trainer.py:17-92 (inference part)."""
+
+    def __init__(self, model, test_data, q_lr: float = 0.1, x0_lr: float = 0.1, max_itr: int = 100,
+                 lr_tol: float = 1e-2, optim_tol: float = 1e-2, warmup_x0_itr: int = 10,
+                 learn_prior_sde: bool = False, **unused):
+        if learn_prior_sde:
+            raise NotImplementedError("prior-parameter learning is not part of this build (SURVEY 8f item 3)")
+        self.model, self.test_data = model, test_data
+        self.q_lr, self.x0_lr, self.max_itr = q_lr, x0_lr, max_itr
+        self.lr_tol, self.optim_tol, self.warmup_x0_itr = lr_tol, optim_tol, warmup_x0_itr
+
+    def model_nlpd(self, m, S) -> float:
+        m, S = self.model.likelihood.predict_mean_and_var(m, S)
+        return calculate_nlpd(m, S, self.model.grid, self.test_data)
+
+    def model_rmse(self, m, S) -> float:
+        m, S = self.model.likelihood.predict_mean_and_var(m, S)
+        return calculate_rmse(m, self.model.grid, self.test_data)
+
+    def perform_inference(self):
+        """vi_markov_gp_trainer.py:50-92"""
+        elbo, nlpd, rmse = [_f(self.model.elbo())], [], []
+        q_lr, x0_lr = self.q_lr, self.x0_lr
+        for i in range(self.max_itr):
+            # forward_pass; update_lagrange; update_param; [update_initial_statistics]; forward_pass; elbo
+            e = self.model.sweep(q_lr, update_x0=i > self.warmup_x0_itr, x0_lr=x0_lr)
+            m, S = self.model.m, self.model.S
+            elbo.append(_f(e))
+            nlpd.append(self.model_nlpd(m, S))
+            rmse.append(self.model_rmse(m, S))
+            if elbo[-2] > elbo[-1] or abs(elbo[-2] - elbo[-1]) < self.lr_tol:
+                q_lr, x0_lr = q_lr / 10, x0_lr / 10
+            if abs(elbo[-2] - elbo[-1]) < self.optim_tol:
+                break
+        return elbo[1:], nlpd, rmse
+
+    def optimize(self):
+        """vi_markov_gp_trainer.py:94-130 without prior learning: 20 warm-up sweeps at lr 1e-6, then inference."""
+        for _ in range(20):
+            self.model.sweep(1e-6)
+        m, S = self.model.forward_pass
+        elbo, nlpd, rmse = [_f(self.model.elbo(m, S))], [self.model_nlpd(m, S)], [self.model_rmse(m, S)]
+        e, n, r = self.perform_inference()
+        return elbo + e, nlpd + n, rmse + r
