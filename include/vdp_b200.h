@@ -226,6 +226,14 @@ int vdp_cvi_site_update_sharded(const vdp_cvi_problem* problem_host, int phase, 
 /* classic_elbo only (no site is modified); fills elbo/ve/kl, q* and fx_* */
 int vdp_cvi_elbo(const vdp_cvi_problem* problem_host, void* stream);
 
+/* euler_maruyama (markovflow/sde/sde_utils.py:36-96), batched: x0 [B,D], time_grid [n] (device) -> out [B,n,D]
+ * with out[:,0] = x0 and the reference's time convention (clock starts at 0; returns [x0, first n-1 states]).
+ * noise: standard normals [B,n-1,D] used in place of the generator (NULL = Philox4x32-10 with `seed`,
+ * sub-sequence = sequence index).  Input generator for BASELINE configs 4 and 5. */
+int vdp_euler_maruyama(int drift_id, const double* params_host, const double* q_host, const double* x0,
+                       const double* time_grid, const double* noise, unsigned long long seed, double* out,
+                       int64_t B, int64_t n, int D, int64_t* status, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Host-buffer variant of vdp_cvi_site_update: the call a host program makes when its arrays live in HOST
  * memory (what the reference's Python loop holds, cvi_dp_trainer.py:71-77).  Every array pointer of `problem`

@@ -389,3 +389,50 @@ def test_site_update_3d(sweeps, which):
                           (eng.gs[0], ref.girsanov_sites.nat2.block_sub_diagonal)):
             scale = max(np.abs(want).max(), 1e-3 * np.abs(eng.fx_covs[0].cpu().numpy()).max() ** -1)
             assert rel(got, want, scale=scale) < TOL
+
+
+# ---------------------------------------------------------------------------------------------------
+# euler_maruyama (sde_utils.py:36-96)
+class _RecordingRng:
+    """np.random.Generator stand-in that records every standard_normal draw (to hand the same noise to CUDA)."""
+
+    def __init__(self, seed):
+        self.rng, self.draws = np.random.default_rng(seed), []
+
+    def standard_normal(self, shape):
+        z = self.rng.standard_normal(shape)
+        self.draws.append(z)
+        return z
+
+
+@pytest.mark.parametrize("sde", [S.DoubleWellSDE(q=0.7 * np.ones((1, 1))), S.OrnsteinUhlenbeckSDE(0.8, np.ones((1, 1))),
+                                 S.VanderPolOscillatorSDE(1.0, 2.0, np.array([[1.0, 0.2], [0.2, 0.5]])),
+                                 S.Lorenz63SDE(q=np.eye(3))])
+def test_euler_maruyama_given_noise(ops, sde):
+    D = sde.q.shape[0]
+    B, n = 5, 300
+    rec = _RecordingRng(9)
+    x0 = np.random.default_rng(1).normal(size=(B, D))
+    grid = np.arange(n) * 0.004
+    want = S.euler_maruyama(sde, x0, grid, rec)
+    noise = np.stack(rec.draws[:n - 1], axis=1)                       # [B, n-1, D]; the reference discards the last draw
+    got = ops.euler_maruyama(sde.drift_id, sde.params, sde.q, dev(x0), dev(grid), noise=dev(noise))
+    assert rel(got, want) < 1e-12
+
+
+def test_euler_maruyama_philox_statistics(ops):
+    """OU started in its stationary law stays in it: mean 0, variance q / (2 decay); paths reproducible by seed."""
+    B, n, decay = 8192, 400, 1.5
+    x0 = torch.randn((B, 1), dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(3))
+    x0 = x0 * (1.0 / (2 * decay)) ** 0.5
+    grid = dev(np.arange(n) * 0.01)
+    a = ops.euler_maruyama(S.DRIFT_OU, [decay], np.ones((1, 1)), x0, grid, seed=11)
+    b = ops.euler_maruyama(S.DRIFT_OU, [decay], np.ones((1, 1)), x0, grid, seed=11)
+    c = ops.euler_maruyama(S.DRIFT_OU, [decay], np.ones((1, 1)), x0, grid, seed=12)
+    assert torch.equal(a, b) and not torch.equal(a, c)
+    assert torch.equal(a[:, 0], x0)
+    last = a[:, -1, 0]
+    assert abs(last.mean().item()) < 0.03 and abs(last.var().item() - 1.0 / (2 * decay)) < 0.03
+    # a sequence's path does not depend on the batch it is simulated in
+    sub = ops.euler_maruyama(S.DRIFT_OU, [decay], np.ones((1, 1)), x0[:100].contiguous(), grid, seed=11)
+    assert torch.equal(sub, a[:100])

@@ -15,6 +15,7 @@
 #include "quad_core.cuh"
 #include "tile_sweeps.cuh"
 #include "vgp_kernels.cuh"
+#include "sim_kernels.cuh"
 
 namespace vdp {
 
@@ -240,6 +241,25 @@ int vdp_btd_conditional_precisions(const double* As, const double* Kd, const dou
 }  // extern "C"
 
 #include "vdp_fused.inl"
+
+extern "C" int vdp_euler_maruyama(int drift_id, const double* params_host, const double* q_host, const double* x0,
+                                  const double* time_grid, const double* noise, unsigned long long seed, double* out,
+                                  int64_t B, int64_t n, int D, int64_t* status, void* stream) {
+    VDP_REQUIRE(q_host && x0 && time_grid && out && B >= 0 && n >= 1, "pointers, B, n");
+    if (B == 0) return VDP_OK;
+    const DriftParams P = make_params(params_host);
+    VDP_DISPATCH_D(D, VDP_DISPATCH_DRIFT(drift_id, {
+        bool ok = true;
+        const Mat<kD> cq = chol(host_mat<kD>(q_host), ok);
+        if (!ok) { set_error("q is not positive definite"); return VDP_E_BADARG; }
+        k_euler_maruyama<kDrift, kD><<<grid_for(B, 64), 64, 0, as_stream(stream)>>>(P, cq, x0, time_grid, noise, seed,
+                                                                                 out, B, n);
+    }));
+    (void)status;
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
 #include "vdp_cvi.inl"
 #include "vdp_host.inl"
 #include "vdp_vgp.inl"

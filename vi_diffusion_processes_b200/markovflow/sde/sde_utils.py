@@ -31,18 +31,15 @@ def handle_tensor_shape(tensor, desired_dimensions=2):
     return t
 
 
-def euler_maruyama(sde: SDE, x0, time_grid, generator=None):
-    """sde_utils.py:36-96: x_{k+1} = x_k + f(x_k) dt + chol(q) sqrt(dt) eps; x0 [n_batch, D] -> [n_batch, N+1, D]."""
+def euler_maruyama(sde: SDE, x0, time_grid, seed: int = 0, noise=None):
+    """sde_utils.py:36-96 on the GPU (``vdp_euler_maruyama``): x0 [n_batch, D], time_grid [n] -> [n_batch, n, D],
+    first state = x0, the reference's clock convention (dt_0 = time_grid[0] - 0).  Randomness: Philox with ``seed``
+    (tf.random.normal in the reference), or the standard normals ``noise`` [n_batch, n-1, D]."""
     x = as_dev(x0)
-    tg = as_dev(time_grid).reshape(-1)
-    L = sde.diffusion(x, tg[0])
-    out = [x]
-    for k in range(tg.shape[0] - 1):
-        dt = tg[k + 1] - tg[k]
-        eps = torch.randn(x.shape, dtype=x.dtype, device=x.device, generator=generator)
-        x = x + sde.drift(x, tg[k]) * dt + torch.sqrt(dt) * (eps @ L.transpose(-1, -2))
-        out.append(x)
-    return torch.stack(out, dim=-2)
+    x = x.reshape(-1, x.shape[-1]).contiguous()
+    tg = as_dev(time_grid).reshape(-1).contiguous()
+    nz = None if noise is None else as_dev(noise).contiguous()
+    return ops.euler_maruyama(sde.drift_id, sde.params, sde.q, x, tg, noise=nz, seed=seed)
 
 
 def linearize_sde(sde: SDE, transition_times, linearization_path: Gaussian, initial_state: Gaussian) -> StateSpaceModel:

@@ -302,3 +302,18 @@ def ssm_natgrad_step(A, b, cholP0, cholQ, mu0, dL_dA, dL_db, dL_dcholP0, dL_dcho
     check(lib.vdp_ssm_natgrad_step(_p(A), _p(b), _p(cholP0), _p(cholQ), _p(mu0), _p(dL_dA), _p(dL_db), _p(dL_dcholP0),
                                    _p(dL_dcholQ), _p(dL_dmu0), float(gamma), _p(ws), nbytes, B, N, D, _p(status),
                                    _stream()), "vdp_ssm_natgrad_step")
+
+
+def euler_maruyama(drift_id, params, q, x0, time_grid, noise=None, seed=0):
+    """sde_utils.py:36-96, batched: x0 [B, D], time_grid [n] -> paths [B, n, D] (paths[:, 0] = x0).
+    ``noise`` [B, n-1, D] standard normals replaces the Philox generator (exact reproduction of a given draw)."""
+    _req(x0, time_grid, noise)
+    B, D = x0.shape
+    n = time_grid.shape[0]
+    out = torch.empty((B, n, D), dtype=F64, device=x0.device)
+    import numpy as np
+    qh = np.atleast_2d(np.asarray(q, dtype=np.float64))
+    check(_lib.load().vdp_euler_maruyama(int(drift_id), dvec(params, 16), dvec(qh.reshape(-1), D * D),
+                                         _p(x0), _p(time_grid), _p(noise), int(seed), _p(out), B, n, D, None,
+                                         _stream()), "vdp_euler_maruyama")
+    return out
