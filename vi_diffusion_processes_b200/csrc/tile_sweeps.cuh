@@ -449,7 +449,11 @@ constexpr size_t invband_tiled_smem() {
 // scan / recursion for Sigma first, composes the y elements on the way, then scans and runs y.
 // Multi-segment launch order: SUMMARY (Sigma elements) -> k_seg_scan -> SUMMARY2 (y elements, needs the
 // Sigma carries) -> k_seg_scan -> FULL.
-template <int D, int T, int L, int MODE>
+// FROML: the precision blocks the conditional precisions need, K_kk = -2 theta_d and K_{k+1,k} = -theta_s, are
+// rebuilt from the Cholesky factor already staged (K_kk = L_kk L_kk^T + L_{k,k-1} L_{k,k-1}^T,
+// K_{k+1,k} = L_{k+1,k} L_kk^T) instead of being read again: 16 of 64 B per grid step less traffic (D = 1) and
+// 3 instead of 5 staged arrays (twice the CTAs per SM).  Single-rank launches only (needs L_{k,k-1} below the range).
+template <int D, int T, int L, int MODE, bool FROML = false>
 __global__ void __launch_bounds__(T)
 k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, const double* __restrict__ th1,
                 const double* __restrict__ thd, const double* __restrict__ ths, double* __restrict__ A,
@@ -462,9 +466,9 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
     extern __shared__ __align__(16) double smem[];
     double* sLd = smem;              // L_kk  -> chol of the conditional covariance of node k
     double* sLs = sLd + TL * DD;     // L_sub -> A_k
-    double* sTd = sLs + TL * DD;     // theta_diag -> conditional covariance of node k
-    double* sTs = sTd + TL * DD;     // theta_sub
-    double* sT1 = sTs + TL * DD;     // theta_1 -> offset of node k
+    double* sTd = sLs + TL * DD;     // theta_diag -> conditional covariance of node k   (not FROML)
+    double* sTs = sTd + TL * DD;     // theta_sub                                         (not FROML)
+    double* sT1 = FROML ? sLs + TL * DD : sTs + TL * DD;     // theta_1 -> offset of node k
     AffSymElem<D>* wtotS = reinterpret_cast<AffSymElem<D>*>(sT1 + TL * D);
     AffVecElem<D>* wtotY = reinterpret_cast<AffVecElem<D>*>(wtotS);   // used after the Sigma scan is over
     const int64_t b = blockIdx.x / nseg;
@@ -481,8 +485,14 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
             if (MODE == SWEEP_SUMMARY2) initY[b] = y_tile;
             if (MODE == SWEEP_FULL) {   // outputs of the last node
                 bool ok = true;
-                Mat<D> cov, cc;
-                cov_from_precision(mirror_lower(-2.0 * mat_load<D>(thd + (b * n + N) * DD)), cov, cc, ok);
+                Mat<D> cov, cc, KN;
+                if (FROML) {
+                    const Mat<D> Ln = mat_load<D>(Ld + (b * n + N) * DD), Lm = mat_load<D>(Ls + (b * N + N - 1) * DD);
+                    KN = mmT(Ln, Ln) + mmT(Lm, Lm);
+                } else {
+                    KN = -2.0 * mat_load<D>(thd + (b * n + N) * DD);
+                }
+                cov_from_precision(mirror_lower(KN), cov, cc, ok);
                 if (!ok) report_not_pd(status, b * n + N);
                 vec_store<D>(bo + (b * N + N - 1) * D, mv(cov, y_tile));
                 mat_store<D>(cholQ + (b * N + N - 1) * DD, cc);
@@ -501,13 +511,21 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
         stage_in<T>(sLd, Ld + (b * n + lo) * DD, (int64_t)cnt * DD);
         stage_in<T>(sLs, Ls + (b * N + lo) * DD, (int64_t)cnt * DD);
         if (MODE != SWEEP_SUMMARY) {
-            stage_in<T>(sTd, thd + (b * n + lo) * DD, (int64_t)cnt * DD);
-            stage_in<T>(sTs, ths + (b * N + lo) * DD, (int64_t)cnt * DD);
+            if (!FROML) {
+                stage_in<T>(sTd, thd + (b * n + lo) * DD, (int64_t)cnt * DD);
+                stage_in<T>(sTs, ths + (b * N + lo) * DD, (int64_t)cnt * DD);
+            }
             stage_in<T>(sT1, th1 + (b * n + lo) * D, (int64_t)cnt * D);
         }
         stage_wait();
         __syncthreads();
         const BwdChunk ch = bwd_chunk<L>(cnt);
+        // FROML: L_{bot,bot-1}, the block below this thread's chunk (the neighbour overwrites it in its recursion)
+        Mat<D> Lbelow = mat_zero<D>();
+        if (FROML && MODE != SWEEP_SUMMARY && ch.len > 0) {
+            if (ch.bot >= 1) Lbelow = mat_load<D>(sLs + (ch.bot - 1) * DD);
+            else if (lo >= 1) Lbelow = mat_load<D>(Ls + (b * N + lo - 1) * DD);
+        }
         const AffSymElem<D> eS = invband_tile_summary<D>(sLd, sLs, ch);
         AffSymElem<D> totalS;
         const AffSymElem<D> exclS = block_exclusive_scan<AffSymOps<D>, T>(eS, wtotS, totalS);
@@ -521,17 +539,24 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
         bool ok = true;
         for (int k = ch.top - 1; k >= ch.bot; --k) {
             Mat<D> Ssub, Skk;
-            invband_step(mat_load<D>(sLd + k * DD), mat_load<D>(sLs + k * DD), S, Ssub, Skk);
+            const Mat<D> Lkk = mat_load<D>(sLd + k * DD), Lsub = mat_load<D>(sLs + k * DD);
+            invband_step(Lkk, Lsub, S, Ssub, Skk);
             S = Skk;
             const Mat<D> Ak = transition_from_cov(Skk, Ssub);
+            Mat<D> prec;
+            if (FROML) {
+                const Mat<D> Lkm1 = (k > ch.bot) ? mat_load<D>(sLs + (k - 1) * DD) : Lbelow;
+                prec = (mmT(Lkk, Lkk) + mmT(Lkm1, Lkm1)) + Tmm(Ak, mmT(Lsub, Lkk));
+            } else {
+                prec = -2.0 * mat_load<D>(sTd + k * DD);
+                prec = prec + Tmm(Ak, -1.0 * mat_load<D>(sTs + k * DD));
+            }
             mat_store<D>(sLs + k * DD, Ak);
-            Mat<D> prec = -2.0 * mat_load<D>(sTd + k * DD);
-            prec = prec + Tmm(Ak, -1.0 * mat_load<D>(sTs + k * DD));
             prec = mirror_lower(prec);
             Mat<D> cov, cc;
             cov_from_precision(prec, cov, cc, ok);
             if (!ok) { report_not_pd(status, b * n + lo + k); ok = true; }
-            mat_store<D>(sTd + k * DD, cov);
+            if (!FROML) mat_store<D>(sTd + k * DD, cov);
             mat_store<D>(sLd + k * DD, cc);
             AffVecElem<D> s;
             s.M = transpose(Ak);
@@ -548,7 +573,10 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
         y_tile = AffVecOps<D>::apply(totalY, y_tile);
         for (int k = ch.top - 1; k >= ch.bot; --k) {
             y = vec_load<D>(sT1 + k * D) + Tmv(mat_load<D>(sLs + k * DD), y);
-            vec_store<D>(sT1 + k * D, mv(mat_load<D>(sTd + k * DD), y));
+            Mat<D> cov;
+            if (FROML) { const Mat<D> cc = mat_load<D>(sLd + k * DD); cov = mmT(cc, cc); }
+            else cov = mat_load<D>(sTd + k * DD);
+            vec_store<D>(sT1 + k * D, mv(cov, y));
         }
         __syncthreads();
         stage_out<T>(A + (b * N + lo) * DD, sLs, (int64_t)cnt * DD);
@@ -568,9 +596,9 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
     }
 }
 
-template <int D, int T, int L>
+template <int D, int T, int L, bool FROML = false>
 constexpr size_t nat2ssm_tiled_smem() {
-    return (4 * (size_t)T * L * D * D + (size_t)T * L * D) * sizeof(double) +
+    return ((FROML ? 2 : 4) * (size_t)T * L * D * D + (size_t)T * L * D) * sizeof(double) +
            (T / 32) * (sizeof(AffSymElem<D>) > sizeof(AffVecElem<D>) ? sizeof(AffSymElem<D>) : sizeof(AffVecElem<D>));
 }
 

@@ -162,13 +162,13 @@ static int run_nat2ssm_bwd_tiled(const double* Ld, const double* Ls, const doubl
                                  const double* ths, double* A, double* b, double* cholQ, double* mu0, double* cholP0,
                                  int64_t B, int64_t N, int64_t* status, SegScratch sc, cudaStream_t st) {
     using C = TileCfg<D>;
-    constexpr size_t smem = nat2ssm_tiled_smem<D, C::T, C::Ln>();
+    constexpr size_t smem = nat2ssm_tiled_smem<D, C::T, C::Ln, true>();
     const SegPlan pl = plan_segments(B, N, C::T * C::Ln, sc.size > 0);
     const unsigned grid = (unsigned)(B * pl.nseg);
     int rc;
-    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL>, smem))) return rc;
+    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true>, smem))) return rc;
     if (pl.nseg == 1) {
-        k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL><<<grid, C::T, smem, st>>>(
+        k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true><<<grid, C::T, smem, st>>>(
             Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, 1, pl.seg_len, nullptr, nullptr, nullptr, nullptr,
             nullptr, nullptr, status);
         VDP_CHECK_LAUNCH();
@@ -181,19 +181,19 @@ static int run_nat2ssm_bwd_tiled(const double* Ld, const double* Ls, const doubl
     AffSymElem<D>* elS = sc.take<AffSymElem<D>>((size_t)B * pl.nseg);
     AffVecElem<D>* elY = sc.take<AffVecElem<D>>((size_t)B * pl.nseg);
     if (!elY) { set_error("segment scratch too small"); return VDP_E_WORKSPACE; }
-    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY>, smem))) return rc;
-    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2>, smem))) return rc;
-    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY><<<grid, C::T, smem, st>>>(
+    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY, true>, smem))) return rc;
+    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2, true>, smem))) return rc;
+    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY, true><<<grid, C::T, smem, st>>>(
         Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, pl.nseg, pl.seg_len, nullptr, nullptr, initS, initY, elS,
         elY, status);
     VDP_CHECK_LAUNCH();
     if ((rc = launch_seg_scan<AffSymOps<D>>(elS, initS, carryS, B, pl.nseg, 1, st))) return rc;
-    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2><<<grid, C::T, smem, st>>>(
+    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2, true><<<grid, C::T, smem, st>>>(
         Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, pl.nseg, pl.seg_len, carryS, nullptr, initS, initY, elS,
         elY, status);
     VDP_CHECK_LAUNCH();
     if ((rc = launch_seg_scan<AffVecOps<D>>(elY, initY, carryY, B, pl.nseg, 1, st))) return rc;
-    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL><<<grid, C::T, smem, st>>>(
+    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true><<<grid, C::T, smem, st>>>(
         Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, pl.nseg, pl.seg_len, carryS, carryY, nullptr, nullptr,
         nullptr, nullptr, status);
     VDP_CHECK_LAUNCH();
