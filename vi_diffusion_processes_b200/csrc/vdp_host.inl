@@ -186,7 +186,7 @@ int vdp_cvi_host_site_update(vdp_cvi_host_ctx* c, const vdp_cvi_problem* hp, int
             p.pA = s.pA; p.pb = s.pb; p.pcholQ = s.pcholQ; p.pmu0 = s.pmu0; p.pcholP0 = s.pcholP0;
         }
         up(s.g1, hp->g1, (N + 1) * d * S); up(s.gd, hp->gd, (N + 1) * dd * S); up(s.gs, hp->gs, N * dd * S);
-        up(s.fx_mus, hp->fx_mus, (N + 1) * d * S); up(s.fx_covs, hp->fx_covs, (N + 1) * dd * S);
+        up(s.fx_mus, hp->fx_mus, (N + 1) * d * S);   // fx_covs is an output only (the data-site update reads the means)
         if (no > 0) {
             up(s.d1, hp->d1, no * d * S); up(s.d2, hp->d2, no * dd * S);
             up(s.obs_idx, hp->obs_idx, no * sizeof(int64_t)); up(s.obs_y, hp->obs_y, no * d * S);

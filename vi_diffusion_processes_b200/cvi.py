@@ -206,7 +206,7 @@ class CviHostEngine:
         """(host->device, device->host) bytes one site_update moves."""
         h = self.host
         nb = lambda names: sum(h[k].numel() * h[k].element_size() for k in names if k not in self.skip)
-        up = nb(self.STATE) + nb(self.CONST) + (0 if self.resident_prior else nb(self.PRIOR))
+        up = nb([k for k in self.STATE if k != "fx_covs"]) + nb(self.CONST) + (0 if self.resident_prior else nb(self.PRIOR))
         return up, nb(self.STATE) + nb(self.OUT)
 
     def site_update(self, lr_data, lr_girsanov, flags=0):
