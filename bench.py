@@ -164,7 +164,7 @@ PHASE_TRAFFIC = {
     "data_sites": (0, 0),
     "sites_to_nat": (2 + 1, 4 + 2),   # read b, g1 | A, cholQ, gd, gs ; write th1 | thd, ths
     "chol_fwd": (0, 2 + 2),           # read thd, ths ; write Ld, Ls
-    "nat2ssm_bwd": (1 + 1, 4 + 2),    # read th1 | Ld, Ls, thd, ths ; write b | A, cholQ
+    "nat2ssm_bwd": (1 + 1, 2 + 2),    # read th1 | Ld, Ls ; write b | A, cholQ (K blocks rebuilt from L in the tile)
     "marg_fwd": (1 + 1, 2 + 2),       # read b | A, cholQ ; write m | Ld, Ls
     "invband_bwd": (0, 2 + 1),        # read Ld, Ls ; write Sd
     "kl_grad": (1 + 1 + 1 + 1 + 1, 2 + 2 + 1 + 2 + 1),  # read m, g1, sc1 | A, S, gd, gs, scd ; write g1 | gd, gs (+ memset sc)
