@@ -243,7 +243,8 @@ int vdp_euler_maruyama(int drift_id, const double* params_host, const double* q_
  * one chunk, the kernels of the previous and the download of the one before overlap.  Results are identical to
  * vdp_cvi_site_update on the whole batch (sequences are independent).  The call returns when all results are
  * in the host buffers.
- *   in/out (host): g1, gd, gs, d1, d2, fx_mus          in (host): time_grid, obs_idx, obs_y, prior
+ *   in/out (host): g1, gd, gs, d1, d2, fx_mus (of the input only the observed grid points are read and uploaded)
+ *   in (host): time_grid, obs_idx, obs_y, prior
  *   out (host): fx_covs;  out (host, each optional = NULL): qA, qb, qcholQ, qmu0, qcholP0, elbo, ve, kl
  * The linearised prior changes only at a re-linearisation (cvi_dp_trainer.py:110-134), so it can be kept on the
  * device: upload it once with vdp_cvi_host_set_prior and pass pA = NULL in the site updates that follow.

@@ -12,7 +12,21 @@ struct HostSlot {
     double *qA, *qb, *qcholQ, *qmu0, *qcholP0, *elbo, *ve, *kl;
     int64_t* obs_idx;
     void* ws;
+    // posterior means at the observed grid points: gathered on the host (pinned staging), scattered on the device
+    double *mu_obs_dev = nullptr, *mu_obs_host = nullptr;
+    cudaEvent_t staged = nullptr;
 };
+
+template <int D>
+__global__ void k_set_at_obs(const double* __restrict__ mu_obs, const int64_t* __restrict__ obs_idx,
+                             double* __restrict__ fx_mus, int64_t B, int64_t N, int64_t n_obs) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= B * n_obs) return;
+    const int64_t b = i / n_obs, k = obs_idx[i];
+    if (k < 0 || k > N) return;
+#pragma unroll
+    for (int e = 0; e < D; ++e) fx_mus[(b * (N + 1) + k) * D + e] = mu_obs[i * D + e];
+}
 
 }  // namespace vdp
 
@@ -45,7 +59,7 @@ struct HostSizes {
     size_t slot_bytes(size_t ws) const {
         return (mN + vN + mN + v1 + m1)            // prior
                + (vN1 + mN1 + mN) + (vo + mo)      // sites
-               + io + vo                           // observations
+               + io + 2 * vo                       // observations, gathered means
                + (vN1 + mN1)                       // marginals
                + (mN + vN + mN + v1 + m1)          // posterior SSM
                + 3 * s + ((ws + 255) & ~size_t(255));
@@ -67,7 +81,12 @@ int vdp_cvi_host_destroy(vdp_cvi_host_ctx* c) {
     if (!c) return VDP_OK;
     cudaSetDevice(c->device);
     for (int i = 0; i < c->nslots; ++i)
-        if (c->slot[i].st) { cudaStreamSynchronize(c->slot[i].st); cudaStreamDestroy(c->slot[i].st); }
+        if (c->slot[i].st) {
+            cudaStreamSynchronize(c->slot[i].st);
+            cudaStreamDestroy(c->slot[i].st);
+            if (c->slot[i].staged) cudaEventDestroy(c->slot[i].staged);
+            if (c->slot[i].mu_obs_host) cudaFreeHost(c->slot[i].mu_obs_host);
+        }
     if (c->pool) cudaFree(c->pool);
     if (c->prior_pool) cudaFree(c->prior_pool);
     delete c;
@@ -106,8 +125,12 @@ int vdp_cvi_host_create(vdp_cvi_host_ctx** out, int64_t chunk, int64_t N, int D,
         s.qA = ar.take(b * N * dd); s.qb = ar.take(b * N * d); s.qcholQ = ar.take(b * N * dd);
         s.qmu0 = ar.take(b * d); s.qcholP0 = ar.take(b * dd);
         s.elbo = ar.take(b); s.ve = ar.take(b); s.kl = ar.take(b);
+        s.mu_obs_dev = ar.take(b * n_obs * d + 1);
         s.ws = ar.take_bytes(c->ws_bytes);
-        if (!s.ws || cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking) != cudaSuccess) {
+        if (!s.ws || cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&s.staged, cudaEventDisableTiming) != cudaSuccess ||
+            cudaHostAlloc((void**)&s.mu_obs_host, (b * n_obs * d + 1) * sizeof(double), cudaHostAllocDefault) !=
+                cudaSuccess) {
             set_error("vdp_cvi_host_create: slot %d setup failed", i);
             vdp_cvi_host_destroy(c);
             return VDP_E_CUDA;
@@ -186,10 +209,29 @@ int vdp_cvi_host_site_update(vdp_cvi_host_ctx* c, const vdp_cvi_problem* hp, int
             p.pA = s.pA; p.pb = s.pb; p.pcholQ = s.pcholQ; p.pmu0 = s.pmu0; p.pcholP0 = s.pcholP0;
         }
         up(s.g1, hp->g1, (N + 1) * d * S); up(s.gd, hp->gd, (N + 1) * dd * S); up(s.gs, hp->gs, N * dd * S);
-        up(s.fx_mus, hp->fx_mus, (N + 1) * d * S);   // fx_covs is an output only (the data-site update reads the means)
+        // fx_covs is an output only, and of fx_mus the data-site update reads the observed grid points only:
+        // gather those on the host, upload n_obs values per sequence instead of N + 1
+        const bool need_mu = no > 0 && !(hp->flags & VDP_FLAG_SKIP_DATA_UPDATE);
         if (no > 0) {
             up(s.d1, hp->d1, no * d * S); up(s.d2, hp->d2, no * dd * S);
             up(s.obs_idx, hp->obs_idx, no * sizeof(int64_t)); up(s.obs_y, hp->obs_y, no * d * S);
+        }
+        if (need_mu && e == cudaSuccess) {
+            e = cudaEventSynchronize(s.staged);      // the previous upload from this staging buffer is over
+            for (size_t bb = 0; bb < nb; ++bb)
+                for (int64_t j = 0; j < no; ++j) {
+                    int64_t k = hp->obs_idx[(o + bb) * no + j];
+                    k = k < 0 ? 0 : (k > N ? N : k);
+                    for (size_t q = 0; q < d; ++q)
+                        s.mu_obs_host[(bb * no + j) * d + q] = hp->fx_mus[((o + bb) * (N + 1) + k) * d + q];
+                }
+            if (e == cudaSuccess) e = h2d(s.mu_obs_dev, s.mu_obs_host, nb * no * d * S, st);
+            if (e == cudaSuccess) e = cudaEventRecord(s.staged, st);
+            if (e == cudaSuccess) {
+                VDP_DISPATCH_D((int)d, (k_set_at_obs<kD><<<grid_for((int64_t)nb * no, kPtBlock), kPtBlock, 0, st>>>(
+                                          s.mu_obs_dev, s.obs_idx, s.fx_mus, (int64_t)nb, N, no)));
+                e = cudaGetLastError();
+            }
         }
         if (e != cudaSuccess) { set_error("H2D copy: %s", cudaGetErrorString(e)); rc = VDP_E_CUDA; break; }
         p.g1 = s.g1; p.gd = s.gd; p.gs = s.gs; p.d1 = s.d1; p.d2 = s.d2; p.obs_idx = s.obs_idx; p.obs_y = s.obs_y;

@@ -206,7 +206,9 @@ class CviHostEngine:
         """(host->device, device->host) bytes one site_update moves."""
         h = self.host
         nb = lambda names: sum(h[k].numel() * h[k].element_size() for k in names if k not in self.skip)
-        up = nb([k for k in self.STATE if k != "fx_covs"]) + nb(self.CONST) + (0 if self.resident_prior else nb(self.PRIOR))
+        mu_obs = self.B * self.n_obs * self.D * 8          # of fx_mus only the observed grid points are uploaded
+        up = (nb([k for k in self.STATE if k not in ("fx_covs", "fx_mus")]) + mu_obs + nb(self.CONST) +
+              (0 if self.resident_prior else nb(self.PRIOR)))
         return up, nb(self.STATE) + nb(self.OUT)
 
     def site_update(self, lr_data, lr_girsanov, flags=0):
