@@ -22,10 +22,10 @@ from __future__ import annotations
 
 import numpy as np
 
-from .gauss_markov_np import (BTDGaussian, StateSpaceModel, chol, chol_solve, expectations_to_ssm_params, mT,
+from .gauss_markov_np import (BTDGaussian, StateSpaceModel, btd_cholesky, btd_solve, chol, chol_solve, expectations_to_ssm_params, mT,
                               naturals_to_ssm_params, ssm_to_expectations, ssm_to_naturals, tri_solve)
 from .sde_np import (SDE, Gaussian, LinearDrift, SDE_SSM_KL_with_grads_wrt_exp_params, SSM_KL_along_Gaussian_path,
-                     gaussian_kl, grad_squared_drift_difference, linearize_sde, remove_batch_from_ssm,
+                     gaussian_kl, grad_squared_drift_difference, linearize_sde, mvnquad, remove_batch_from_ssm,
                      squared_drift_difference_along_Gaussian_path, ssm_to_btd_nat, tranform_girsanov_sites)
 
 
@@ -223,6 +223,103 @@ class CVISitesSDE:
         fx_mus, fx_covs = self.dist_q.marginals
         return self.variational_expectation(fx_mus, fx_covs) - self.KL_q_p()
 
+    # ---- :495-504
+    def grad_KL_wrt_prior_params(self):
+        """
+        d KL_q_p / d(prior_sde parameters), every entry of ``prior_sde.params``.  The tape of the reference watches
+        the drift's trainable variables only; dist_q, dist_p and f_q are constants on it (f_q is wrapped in
+        stop_gradient, :466), so the only dependence is through ``prior_sde.drift`` inside the H = 20 quadrature:
+            d/dp 1/2 sum_t E[d^T Q_p^-1 d] = sum_t E[d^T sym(Q_p^-1) dt df/dp],   d = x + dt f(x) - (A x + b).
+        """
+        dist_q = self.dist_q
+        m, S = dist_q.marginal_means[:-1], dist_q.marginal_covariances[:-1]
+        A, b = dist_q.state_transitions, dist_q.state_offsets
+        D, n = self.state_dim, A.shape[0]
+        Qp_inv = chol_solve(chol(self.dt * self.prior_sde.q), np.eye(D))
+        W = 0.5 * (Qp_inv + Qp_inv.T)
+        n_par = len(np.asarray(self.prior_sde.params))
+
+        def func(x):
+            x = x.reshape(-1, n, D)
+            d = x + self.dt * self.prior_sde.drift(x) - ((A[None] @ x[..., None])[..., 0] + b[None])
+            df, _ = self.prior_sde.param_grads(x)
+            return (self.dt * np.einsum("pni,ij,kpnj->pnk", d, W, df)).reshape(-1, n_par)
+
+        return np.sum(mvnquad(func, m, S, H=20, Din=D, Dout=(n_par,)), axis=0)
+
+    # ---- :506-518
+    def grad_VE_wrt_prior_params(self):
+        """
+        d(-VE)/d(prior_sde parameters) with the tape running through set_linearized_prior -> dist_q.marginals ->
+        variational_expectation.  As in the reference the call RE-LINEARISES the prior around the stored
+        (fx_mus, fx_covs) as a side effect and leaves fx_mus / fx_covs untouched.
+
+        Route of the restatement (forward mode in the parameters, reverse mode in the chain):
+          * dA_k/dp, db_k/dp of the linearised SSM: H = 10 expectations of dJ/dp, df/dp (sde_utils.py:156-166,
+            drift.py:102-108), zero where tf.clip_by_value saturates (:417-430);
+          * q has precision P and linear natural parameter h (prior naturals + sites); with L = -VE,
+            gbar_j = dL/dm_j, G_j = dL/dSigma_jj at the observed points:  dL = u^T dh - u^T dP m - tr(V dP),
+            u = P^-1 gbar,  V = P^-1 Gbar P^-1 (its block-tridiagonal band), both from block solves with the
+            Cholesky factor of P (one solve per observed point and state dimension);
+          * dP, dh from the differential of ssm_to_naturals (ssm_gaussian_transformations.py:182-253).
+        Checked against torch.autograd on a dense restatement and central differences
+        (tests/test_oracle_prior_grads.py).
+        """
+        self.set_linearized_prior()
+        sde, D = self.prior_sde, self.state_dim
+        n_par = len(np.asarray(sde.params))
+        path_m, path_S = self.fx_mus[1:], self.fx_covs[1:]
+        N = path_m.shape[0]
+        deltas = (self.time_grid[1:] - self.time_grid[:-1])[:, None, None]
+        E_dJ = mvnquad(lambda x: np.moveaxis(sde.param_grads(x)[1], 0, -1), path_m, path_S, H=10, Din=D,
+                       Dout=(D, D, n_par))
+        E_df = mvnquad(lambda x: np.moveaxis(sde.param_grads(x)[0], 0, -1), path_m, path_S, H=10, Din=D,
+                       Dout=(D, n_par))
+        dA = deltas[..., None] * E_dJ                                               # [N, D, D, P]
+        db = deltas[..., 0, :, None] * (E_df - np.einsum("nijp,nj->nip", E_dJ, path_m))  # [N, D, P]
+        if self.stabilize_ssm:
+            lo, hi = self.clip_state_transitions
+            A_lin, b_lin = self.dist_p_linearized.state_transitions, self.dist_p_linearized.state_offsets
+            dA = dA * ((A_lin >= lo) & (A_lin <= hi))[..., None]
+            db = db * ((b_lin >= lo) & (b_lin <= hi))[..., None]
+        # posterior q and the cotangents of L = -VE at the observed grid points
+        q_nat1, q_nat2 = self.full_sites()
+        Pd, Ps = -2.0 * q_nat2.block_diagonal, -q_nat2.block_sub_diagonal
+        Ld, Ls = btd_cholesky(Pd, Ps)
+        fx_mus, fx_covs = self.dist_q.marginals
+        idx = self.obs_sites_indices
+        g_mu, g_S = self.likelihood.variational_expectations_grads(fx_mus[idx], fx_covs[idx], self._observations)
+        g_mu, g_S = -g_mu, -0.5 * (g_S + mT(g_S))
+        n1 = N + 1
+        gbar = np.zeros((n1, D))
+        np.add.at(gbar, idx, g_mu)
+        solve = lambda rhs: btd_solve(Ld, Ls, btd_solve(Ld, Ls, rhs, transpose=False), transpose=True)
+        u = solve(gbar)
+        Vd, Vs = np.zeros((n1, D, D)), np.zeros((N, D, D))
+        for j, Gj in zip(idx, g_S):
+            Z = np.stack([solve(np.eye(n1 * D)[j * D + c].reshape(n1, D)) for c in range(D)], axis=-1)  # P^-1 E_j
+            Vd += Z @ Gj @ mT(Z)
+            Vs += Z[1:] @ Gj @ mT(Z[:-1])
+        # differential of the prior's naturals in (A_k, b_k)
+        A, b = self.dist_p.state_transitions, self.dist_p.state_offsets
+        cQ = self.dist_p.cholesky_process_covariances
+        W = chol_solve(cQ, np.broadcast_to(np.eye(D), cQ.shape))
+        grads = np.zeros(n_par)
+        m = fx_mus
+        for p in range(n_par):
+            dAp, dbp = dA[..., p], db[..., p]
+            dPd = np.zeros((n1, D, D))
+            dPd[:-1] = mT(dAp) @ W @ A + mT(A) @ W @ dAp
+            dPs = -W @ dAp
+            dh = np.zeros((n1, D))
+            dh[:-1] += -(mT(dAp) @ W @ b[..., None] + mT(A) @ W @ dbp[..., None])[..., 0]
+            dh[1:] += (W @ dbp[..., None])[..., 0]
+            dPm = (dPd @ m[..., None])[..., 0]
+            dPm[1:] += (dPs @ m[:-1, :, None])[..., 0]
+            dPm[:-1] += (mT(dPs) @ m[1:, :, None])[..., 0]
+            grads[p] = (np.sum(u * dh) - np.sum(u * dPm) - np.sum(Vd * dPd) - 2.0 * np.sum(Vs * dPs))
+        return grads
+
     # ---- cvi_dp_trainer.py:71-77 -- the unit the benchmark counts
     def site_update(self, data_lr: float, girsanov_lr: float):
         self.update_data_sites(data_lr)
@@ -365,6 +462,43 @@ class VariationalMarkovGP:
         E_obs = np.sum(self.likelihood.variational_expectations(m[self.obs_indices], S[self.obs_indices],
                                                                 self.observations))
         return float(E_obs - E_sde - self.KL_initial_state())
+
+    # ---- :457-470
+    def grad_prior_sde_params(self):
+        """
+        d E_sde / d(prior_sde parameters), every entry of ``prior_sde.params``, with (m, S) = forward_pass[1:]
+        held constant -- the reference pairs the marginals at grid points 1..N with A[0..N-1] here (:461-465),
+        unlike E_sde() itself, which uses grid points 0..N-1 (:428-430).
+            d/dp 1/2 dt sum_t E||r||^2_{q^-1} = -dt sum_t E[r^T sym(q^-1) df/dp],   r = -A x + b - f(x).
+        """
+        m, S = self.forward_pass
+        m, S = m[1:], S[1:]
+        D, n = self.state_dim, self.A.shape[0]
+        A, b = -1 * self.A, self.b
+        sig_inv = chol_solve(chol(self.prior_sde.q), np.eye(D))
+        W = 0.5 * (sig_inv + sig_inv.T)
+        n_par = len(np.asarray(self.prior_sde.params))
+
+        def func(x):
+            x = x.reshape(-1, n, D)
+            r = ((A[None] @ x[..., None])[..., 0] + b[None]) - self.prior_sde.drift(x)
+            df, _ = self.prior_sde.param_grads(x)
+            return (-np.einsum("pni,ij,kpnj->pnk", r, W, df)).reshape(-1, n_par)
+
+        return self.dt * np.sum(mvnquad(func, m, S, H=20, Din=D, Dout=(n_par,)), axis=0)
+
+    # ---- :472-482
+    def grad_initial_state(self):
+        """d KL[q(x0) || p(x0)] / d(prior loc, prior scale_tril), closed form of the tfp tape result."""
+        mu_p, cov_p = self.prior_initial_state.mu, self.prior_initial_state.cov
+        Lp = chol(cov_p)
+        P_inv = chol_solve(Lp, np.eye(self.state_dim))
+        Sq = self.q_initial_chol @ self.q_initial_chol.T
+        dm = self.q_initial_mean - mu_p
+        g_loc = -(P_inv @ dm)
+        g_cov = 0.5 * (P_inv - P_inv @ (Sq + np.outer(dm, dm)) @ P_inv)
+        g_tril = np.tril(2.0 * g_cov @ Lp)
+        return g_loc, g_tril
 
     # ---- vi_markov_gp_trainer.py:62-70 -- one fixed-point sweep
     def sweep(self, lr: float, update_x0: bool = False, x0_lr: float = 0.1):

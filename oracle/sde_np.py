@@ -96,6 +96,19 @@ class SDE:
     def jacobian(self, x):
         raise NotImplementedError
 
+    def with_params(self, params):
+        """A copy of this SDE with the parameter block replaced (used by the prior-learning restatement)."""
+        raise NotImplementedError
+
+    def param_grads(self, x):
+        """
+        (df/dp ``[P, ..., D]``, dJ/dp ``[P, ..., D, D]``) for every entry p of ``params``: what a tape watching
+        ``prior_sde.trainable_variables`` propagates through ``drift`` / ``gradient_drift``
+        (variational_cvi_sde.py:495-518, vi_sde.py:457-470).  Closed forms, checked against central
+        differences in tests/test_oracle_prior_grads.py.
+        """
+        raise NotImplementedError
+
     def diffusion(self, x, t=None):
         return np.ones_like(x[..., None]) * chol(self.q)
 
@@ -144,6 +157,12 @@ class OrnsteinUhlenbeckSDE(SDE):
     def jacobian(self, x):
         return _diag_jac(-self.decay * np.ones_like(x))
 
+    def with_params(self, params):
+        return type(self)(decay=params[0], q=self.q)
+
+    def param_grads(self, x):
+        return np.stack([-x]), np.stack([_diag_jac(-np.ones_like(x))])
+
 
 class DoubleWellSDE(SDE):
     """sde.py:179-224: f(x) = scale x (c - x^2)."""
@@ -164,6 +183,14 @@ class DoubleWellSDE(SDE):
     def jacobian(self, x):
         return _diag_jac(self.scale * (self.c - 3.0 * np.square(x)))
 
+    def with_params(self, params):
+        return type(self)(q=self.q, scale=params[0], c=params[1])
+
+    def param_grads(self, x):
+        x2 = np.square(x)
+        return (np.stack([x * (self.c - x2), self.scale * x]),
+                np.stack([_diag_jac(self.c - 3.0 * x2), _diag_jac(self.scale * np.ones_like(x))]))
+
 
 class BenesSDE(SDE):
     """sde.py:227-268: f(x) = theta tanh(x)."""
@@ -182,6 +209,13 @@ class BenesSDE(SDE):
 
     def jacobian(self, x):
         return _diag_jac(self.theta * (1.0 - np.square(np.tanh(x))))
+
+    def with_params(self, params):
+        return type(self)(theta=params[0], q=self.q)
+
+    def param_grads(self, x):
+        t = np.tanh(x)
+        return np.stack([t]), np.stack([_diag_jac(1.0 - np.square(t))])
 
 
 class SineDiffusionSDE(SDE):
@@ -202,6 +236,12 @@ class SineDiffusionSDE(SDE):
     def jacobian(self, x):
         return _diag_jac(np.cos(x - self.theta))
 
+    def with_params(self, params):
+        return type(self)(theta=params[0], q=self.q)
+
+    def param_grads(self, x):
+        return np.stack([-np.cos(x - self.theta)]), np.stack([_diag_jac(np.sin(x - self.theta))])
+
 
 class SqrtDiffusionSDE(SDE):
     """sde.py:315-356: f(x) = sqrt(theta |x|)."""
@@ -221,6 +261,13 @@ class SqrtDiffusionSDE(SDE):
     def jacobian(self, x):
         # d/dx sqrt(theta |x|) = theta sign(x) / (2 sqrt(theta |x|))   (tape: sqrt' * theta * sign)
         return _diag_jac(0.5 / np.sqrt(self.theta * np.abs(x)) * self.theta * np.sign(x))
+
+    def with_params(self, params):
+        return type(self)(theta=params[0], q=self.q)
+
+    def param_grads(self, x):
+        r = np.sqrt(self.theta * np.abs(x))
+        return np.stack([0.5 * np.abs(x) / r]), np.stack([_diag_jac(0.25 * np.sign(x) / r)])
 
 
 class MLPDrift(SDE):
@@ -253,6 +300,23 @@ class MLPDrift(SDE):
         act = (x[..., None] * w1 + b1) > 0.0
         return _diag_jac((act * (w1 * w2)).sum(-1))
 
+    def with_params(self, params):
+        return type(self)(q=self.q, weights=np.asarray(params, dtype=np.float64))
+
+    def param_grads(self, x):
+        w1, b1, w2 = self.weights[0:3], self.weights[3:6], self.weights[6:9]
+        pre = x[..., None] * w1 + b1
+        on = (pre > 0.0).astype(np.float64)          # relu'(0) = 0, as TensorFlow
+        df, dJ = [], []
+        for h in range(3):                           # d/dw1[h]
+            df.append(on[..., h] * x * w2[h]); dJ.append(on[..., h] * w2[h])
+        for h in range(3):                           # d/db1[h]
+            df.append(on[..., h] * w2[h]); dJ.append(np.zeros_like(x))
+        for h in range(3):                           # d/dw2[h]
+            df.append(np.maximum(pre[..., h], 0.0)); dJ.append(on[..., h] * w1[h])
+        df.append(np.ones_like(x)); dJ.append(np.zeros_like(x))   # d/db2
+        return np.stack(df), np.stack([_diag_jac(g) for g in dJ])
+
 
 class VanderPolOscillatorSDE(SDE):
     """sde.py:433-518: f = tau [a (x1 - x1^3/3 - x2), x1 / a]."""
@@ -279,6 +343,19 @@ class VanderPolOscillatorSDE(SDE):
         J[..., 0, 1] = -self.tau * self.a
         J[..., 1, 0] = self.tau / self.a
         return J
+
+    def with_params(self, params):
+        return type(self)(a=params[0], tau=params[1], q=self.q)
+
+    def param_grads(self, x):
+        a, tau = self.a, self.tau
+        x1, x2 = x[..., 0], x[..., 1]
+        g = x1 - (1 / 3) * np.power(x1, 3) - x2
+        df = np.stack([np.stack([tau * g, -tau * x1 / a ** 2], -1), np.stack([a * g, x1 / a], -1)])
+        dJ = np.zeros((2,) + x.shape + (2,))
+        dJ[0, ..., 0, 0] = tau * (1.0 - np.square(x1)); dJ[0, ..., 0, 1] = -tau; dJ[0, ..., 1, 0] = -tau / a ** 2
+        dJ[1, ..., 0, 0] = a * (1.0 - np.square(x1)); dJ[1, ..., 0, 1] = -a; dJ[1, ..., 1, 0] = 1.0 / a
+        return df, dJ
 
 
 class Lorenz63SDE(SDE):
@@ -314,6 +391,20 @@ class Lorenz63SDE(SDE):
         J[..., 2, 2] = -self.beta
         return J
 
+    def with_params(self, params):
+        return type(self)(sigma=params[0], rho=params[1], beta=params[2], q=self.q)
+
+    def param_grads(self, x):
+        X, Y, Z = x[..., 0], x[..., 1], x[..., 2]
+        zero = np.zeros_like(X)
+        df = np.stack([np.stack([Y - X, zero, zero], -1), np.stack([zero, X, zero], -1),
+                       np.stack([zero, zero, -Z], -1)])
+        dJ = np.zeros((3,) + x.shape + (3,))
+        dJ[0, ..., 0, 0] = -1.0; dJ[0, ..., 0, 1] = 1.0
+        dJ[1, ..., 1, 0] = 1.0
+        dJ[2, ..., 2, 2] = -1.0
+        return df, dJ
+
 
 class OUNdSDE(SDE):
     """EXTENSION: D-dimensional OU, f(x) = -decay x, with a full (diagonal) batch Jacobian."""
@@ -333,6 +424,12 @@ class OUNdSDE(SDE):
 
     def jacobian(self, x):
         return _diag_jac(-self.decay * np.ones_like(x))
+
+    def with_params(self, params):
+        return type(self)(decay=params[0], q=self.q)
+
+    def param_grads(self, x):
+        return np.stack([-x]), np.stack([_diag_jac(-np.ones_like(x))])
 
 
 # ----------------------------------------------------------------------------------------------
