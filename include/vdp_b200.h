@@ -226,6 +226,42 @@ int vdp_cvi_site_update_sharded(const vdp_cvi_problem* problem_host, int phase, 
 /* classic_elbo only (no site is modified); fills elbo/ve/kl, q* and fx_* */
 int vdp_cvi_elbo(const vdp_cvi_problem* problem_host, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Prior-parameter learning (cvi_dp_trainer.py:207-250, vi_markov_gp_trainer.py:163-201): gradients with respect
+ * to the drift parameters, i.e. what the reference's tape returns for prior_sde.trainable_variables.  Every entry
+ * of the drift's parameter block gets a gradient (the caller keeps the trainable ones); grads is [B, 16], entries
+ * beyond vdp_drift_num_params(drift_id) are set to 0.  Sums over the grid are reduced in a fixed order.
+ * ---------------------------------------------------------------------------------------------- */
+int vdp_drift_num_params(int drift_id);
+
+/* CVISitesSDE.grad_KL_wrt_prior_params (variational_cvi_sde.py:495-504): d KL_q_p / d params.  dist_q is rebuilt
+ * from the sites as KL_q_p does (:450-462): q*, fx_mus, fx_covs of the problem are outputs (pass scratch buffers
+ * for fx_* to leave the model's stored marginals alone, as the reference does); H = 20. */
+int vdp_cvi_grad_kl_prior_params(const vdp_cvi_problem* problem_host, double* grads, void* stream);
+
+/* CVISitesSDE.grad_VE_wrt_prior_params (variational_cvi_sde.py:506-518): d(-VE)/d params with the tape running
+ * through set_linearized_prior -> dist_q.marginals -> variational_expectation.  The caller has re-linearised the
+ * prior (vdp_linearize_to_ssm; pA, pb = the clipped SSM) around the stored posterior path path_m [B,N+1,D],
+ * path_S [B,N+1,D,D] (grid points 1..N are used, :412); clip / clip_lo / clip_hi = the stabilize_ssm window
+ * (:417-430; saturated entries pass no gradient).  q*, fx_mus, fx_covs of the problem are outputs (the marginals
+ * of dist_q under the new prior) and must not alias the path. */
+int vdp_cvi_grad_ve_prior_params(const vdp_cvi_problem* problem_host, const double* path_m, const double* path_S,
+                                 int clip, double clip_lo, double clip_hi, double* grads, void* stream);
+
+/* The quadrature both KL-type gradients share, H = 20:
+ *   grads[b, p] = out_scale sum_t E_{N(m_t, S_t)}[ r(x)^T W df/dp(x) ],   W = sym((q_scale q)^-1),
+ *   r(x) = c_x x + c_f f(x) - (a_sign A_t x + b_t),     A [B,N,D,D], b [B,N,D];
+ * the Gaussian of transition t of sequence b is read at m + (b * points_per_sequence + t) * D (same for S), so
+ * marginals [B,N+1,..] can be passed with or without an offset of one grid point.
+ *   VariationalMarkovGP.grad_prior_sde_params (vi_sde.py:457-470): c_x = 0, c_f = 1, a_sign = -1, q_scale = 1,
+ *   out_scale = dt, (m, S) = forward_pass[1:] (the reference pairs grid points 1..N with A[0..N-1] here). */
+size_t vdp_drift_param_grad_workspace(int64_t B, int64_t N, int D);
+int vdp_drift_param_grad(int drift_id, const double* params_host, const double* q_host, double q_scale, double c_x,
+                         double c_f, double a_sign, double out_scale, const double* A, const double* b,
+                         const double* m, const double* S, int64_t points_per_sequence, double* grads,
+                         void* workspace, size_t workspace_bytes, int64_t B, int64_t N, int D, int64_t* status,
+                         void* stream);
+
 /* euler_maruyama (markovflow/sde/sde_utils.py:36-96), batched: x0 [B,D], time_grid [n] (device) -> out [B,n,D]
  * with out[:,0] = x0 and the reference's time convention (clock starts at 0; returns [x0, first n-1 states]).
  * noise: standard normals [B,n-1,D] used in place of the generator (NULL = Philox4x32-10 with `seed`,

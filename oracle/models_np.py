@@ -297,7 +297,12 @@ class CVISitesSDE:
         u = solve(gbar)
         Vd, Vs = np.zeros((n1, D, D)), np.zeros((N, D, D))
         for j, Gj in zip(idx, g_S):
-            Z = np.stack([solve(np.eye(n1 * D)[j * D + c].reshape(n1, D)) for c in range(D)], axis=-1)  # P^-1 E_j
+            cols = []
+            for c in range(D):
+                rhs = np.zeros((n1, D))
+                rhs[j, c] = 1.0
+                cols.append(solve(rhs))
+            Z = np.stack(cols, axis=-1)                                   # P^-1 E_j, [n1, D, D]
             Vd += Z @ Gj @ mT(Z)
             Vs += Z[1:] @ Gj @ mT(Z[:-1])
         # differential of the prior's naturals in (A_k, b_k)

@@ -100,6 +100,27 @@ class SDE:
         """A copy of this SDE with the parameter block replaced (used by the prior-learning restatement)."""
         raise NotImplementedError
 
+    # the reference's tf.Variable(trainable=...) flags: ``trainable`` = positions in ``params`` (None = all)
+    trainable = None
+
+    @property
+    def trainable_indices(self):
+        n = len(np.asarray(self.params))
+        return list(range(n)) if self.trainable is None else list(self.trainable)
+
+    @property
+    def trainable_variables(self):
+        p = np.asarray(self.params, dtype=np.float64)
+        return [p[i] for i in self.trainable_indices]
+
+    def assign_trainable(self, values):
+        p = np.asarray(self.params, dtype=np.float64).copy()
+        for i, v in zip(self.trainable_indices, values):
+            p[i] = float(v)
+        keep = self.trainable
+        self.__dict__.update(self.with_params(p).__dict__)
+        self.trainable = keep
+
     def param_grads(self, x):
         """
         (df/dp ``[P, ..., D]``, dJ/dp ``[P, ..., D, D]``) for every entry p of ``params``: what a tape watching

@@ -125,6 +125,14 @@ SIGNATURES = {
     "vdp_cvi_site_update": (C.c_int, [C.POINTER(CviProblem), vp]),
     "vdp_cvi_site_update_sharded": (C.c_int, [C.POINTER(CviProblem), C.c_int, i64, i64, vp]),
     "vdp_cvi_elbo": (C.c_int, [C.POINTER(CviProblem), vp]),
+    "vdp_drift_num_params": (C.c_int, [C.c_int]),
+    "vdp_cvi_grad_kl_prior_params": (C.c_int, [C.POINTER(CviProblem), vp, vp]),
+    "vdp_cvi_grad_ve_prior_params": (C.c_int, [C.POINTER(CviProblem), vp, vp, C.c_int, C.c_double, C.c_double, vp,
+                                               vp]),
+    "vdp_drift_param_grad_workspace": (C.c_size_t, [i64, i64, C.c_int]),
+    "vdp_drift_param_grad": (C.c_int, [C.c_int, c_dp, c_dp, C.c_double, C.c_double, C.c_double, C.c_double,
+                                       C.c_double, vp, vp, vp, vp, i64, vp, vp, C.c_size_t, i64, i64, C.c_int, vp,
+                                       vp]),
     "vdp_euler_maruyama": (C.c_int, [C.c_int, c_dp, c_dp, vp, vp, vp, C.c_uint64, vp, i64, i64, C.c_int, vp, vp]),
     "vdp_cvi_host_create": (C.c_int, [C.POINTER(vp), i64, i64, C.c_int, i64, C.c_int, C.c_int]),
     "vdp_cvi_host_set_prior": (C.c_int, [vp, i64, vp, vp, vp, vp, vp]),

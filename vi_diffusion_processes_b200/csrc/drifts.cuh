@@ -121,6 +121,130 @@ template <> struct Drift<DRIFT_LORENZ63, 3> {
     }
 };
 
+// Derivatives of f and J with respect to every entry of the parameter block: what a tape watching
+// prior_sde.trainable_variables propagates through drift / gradient_drift (prior-parameter learning,
+// variational_cvi_sde.py:495-518, vi_sde.py:457-470).  df[p](i) = d f_i / d P.p[p], dJ[p](i, j) = d J_ij / d P.p[p].
+template <int ID, int D> struct DriftParamGrad;
+
+template <int D> struct DriftParamGrad<DRIFT_OU, D> {
+    static constexpr int NP = 1;
+    static __device__ __forceinline__ void eval(const DriftParams&, const Vec<D>& x, Vec<D>* df, Mat<D>* dJ) {
+        dJ[0] = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) { df[0](i) = -x(i); dJ[0](i, i) = -1.0; }
+    }
+};
+template <int D> struct DriftParamGrad<DRIFT_OU_ND, D> : DriftParamGrad<DRIFT_OU, D> {};
+
+template <int D> struct DriftParamGrad<DRIFT_DW, D> {
+    static constexpr int NP = 2;
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<D>& x, Vec<D>* df, Mat<D>* dJ) {
+        dJ[0] = mat_zero<D>();
+        dJ[1] = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            const double x2 = x(i) * x(i);
+            df[0](i) = x(i) * (P.p[1] - x2);
+            df[1](i) = P.p[0] * x(i);
+            dJ[0](i, i) = fma(-3.0, x2, P.p[1]);
+            dJ[1](i, i) = P.p[0];
+        }
+    }
+};
+template <int D> struct DriftParamGrad<DRIFT_BENES, D> {
+    static constexpr int NP = 1;
+    static __device__ __forceinline__ void eval(const DriftParams&, const Vec<D>& x, Vec<D>* df, Mat<D>* dJ) {
+        dJ[0] = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            const double t = tanh(x(i));
+            df[0](i) = t;
+            dJ[0](i, i) = 1.0 - t * t;
+        }
+    }
+};
+template <int D> struct DriftParamGrad<DRIFT_SINE, D> {
+    static constexpr int NP = 1;
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<D>& x, Vec<D>* df, Mat<D>* dJ) {
+        dJ[0] = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            double s, c;
+            sincos(x(i) - P.p[0], &s, &c);
+            df[0](i) = -c;
+            dJ[0](i, i) = s;
+        }
+    }
+};
+template <int D> struct DriftParamGrad<DRIFT_SQRT, D> {
+    static constexpr int NP = 1;
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<D>& x, Vec<D>* df, Mat<D>* dJ) {
+        dJ[0] = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            const double r = sqrt(P.p[0] * fabs(x(i)));
+            const double sgn = (x(i) > 0.0) ? 1.0 : ((x(i) < 0.0) ? -1.0 : 0.0);
+            df[0](i) = 0.5 * fabs(x(i)) / r;
+            dJ[0](i, i) = 0.25 * sgn / r;
+        }
+    }
+};
+// p = (w1[3], b1[3], w2[3], b2); relu'(0) = 0 as in TensorFlow
+template <int D> struct DriftParamGrad<DRIFT_MLP131, D> {
+    static constexpr int NP = 10;
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<D>& x, Vec<D>* df, Mat<D>* dJ) {
+#pragma unroll
+        for (int p = 0; p < NP; ++p) dJ[p] = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+#pragma unroll
+            for (int h = 0; h < 3; ++h) {
+                const double pre = x(i) * P.p[h] + P.p[3 + h];
+                const double on = (pre > 0.0) ? 1.0 : 0.0;
+                df[h](i) = on * x(i) * P.p[6 + h];
+                dJ[h](i, i) = on * P.p[6 + h];
+                df[3 + h](i) = on * P.p[6 + h];
+                df[6 + h](i) = on * pre;
+                dJ[6 + h](i, i) = on * P.p[h];
+            }
+            df[9](i) = 1.0;
+        }
+    }
+};
+template <> struct DriftParamGrad<DRIFT_VDP, 2> {
+    static constexpr int NP = 2;
+    static __device__ __forceinline__ void eval(const DriftParams& P, const Vec<2>& x, Vec<2>* df, Mat<2>* dJ) {
+        const double a = P.p[0], tau = P.p[1];
+        const double x1 = x(0), x2 = x(1);
+        const double g = x1 - (1.0 / 3.0) * (x1 * x1 * x1) - x2;
+        const double ia = 1.0 / a;
+        df[0](0) = tau * g;            df[0](1) = -tau * x1 * ia * ia;
+        df[1](0) = a * g;              df[1](1) = x1 * ia;
+        dJ[0](0, 0) = tau * (1.0 - x1 * x1); dJ[0](0, 1) = -tau; dJ[0](1, 0) = -tau * ia * ia; dJ[0](1, 1) = 0.0;
+        dJ[1](0, 0) = a * (1.0 - x1 * x1);   dJ[1](0, 1) = -a;   dJ[1](1, 0) = ia;             dJ[1](1, 1) = 0.0;
+    }
+};
+template <> struct DriftParamGrad<DRIFT_LORENZ63, 3> {
+    static constexpr int NP = 3;
+    static __device__ __forceinline__ void eval(const DriftParams&, const Vec<3>& x, Vec<3>* df, Mat<3>* dJ) {
+#pragma unroll
+        for (int p = 0; p < NP; ++p) { df[p] = vec_zero<3>(); dJ[p] = mat_zero<3>(); }
+        df[0](0) = x(1) - x(0); dJ[0](0, 0) = -1.0; dJ[0](0, 1) = 1.0;
+        df[1](1) = x(0);        dJ[1](1, 0) = 1.0;
+        df[2](2) = -x(2);       dJ[2](2, 2) = -1.0;
+    }
+};
+// number of entries of the parameter block a drift reads (0 for an unknown id)
+__host__ __device__ inline int drift_num_params(int id) {
+    switch (id) {
+        case DRIFT_OU: case DRIFT_OU_ND: case DRIFT_BENES: case DRIFT_SINE: case DRIFT_SQRT: return 1;
+        case DRIFT_DW: case DRIFT_VDP: return 2;
+        case DRIFT_LORENZ63: return 3;
+        case DRIFT_MLP131: return 10;
+        default: return 0;
+    }
+}
+
 // Which (drift, D) pairs exist: the element-wise drifts for any D, VDP only D=2, LORENZ63 only D=3.
 template <int ID, int D> struct DriftValid { static constexpr bool value = true; };
 template <int D> struct DriftValid<DRIFT_VDP, D> { static constexpr bool value = (D == 2); };

@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include "kl_kernels.cuh"
 #include "pointwise_kernels.cuh"
+#include "prior_grad_kernels.cuh"
 #include "quad_core.cuh"
 #include "tile_sweeps.cuh"
 #include "vgp_kernels.cuh"
@@ -261,6 +262,7 @@ extern "C" int vdp_euler_maruyama(int drift_id, const double* params_host, const
 }
 
 #include "vdp_cvi.inl"
+#include "vdp_prior.inl"
 #include "vdp_host.inl"
 #include "vdp_vgp.inl"
 #include "vdp_dist.inl"

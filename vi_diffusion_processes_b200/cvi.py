@@ -74,12 +74,18 @@ class CviEngine:
         self._ws_bytes = lib.vdp_cvi_workspace(B, N, D, n_obs)
         self._ws = torch.empty(self._ws_bytes, dtype=torch.uint8, device=dev)
         # prior p: initial state from the prior on x0 (variational_cvi_sde.py:408-412, sde_utils.py:145-147)
-        self.pmu0 = torch.as_tensor(self.x0_mu, dtype=F64).to(dev).expand(B, D).contiguous()
-        self.pcholP0 = torch.as_tensor(np.linalg.cholesky(self.x0_cov), dtype=F64).to(dev).expand(B, D, D).contiguous()
         self.set_linearized_prior()
 
     # variational_cvi_sde.py:408-432
+    def set_prior_initial_state(self, mu, cov):
+        """Assign the prior on x0 (cvi_dp_trainer.py:231-235); dist_p picks it up at the next linearisation."""
+        self.x0_mu = np.asarray(mu, dtype=np.float64).reshape(self.D)
+        self.x0_cov = np.atleast_2d(np.asarray(cov, dtype=np.float64))
+
     def set_linearized_prior(self):
+        dev, B, D = self.device, self.B, self.D
+        self.pmu0 = torch.as_tensor(self.x0_mu, dtype=F64).to(dev).expand(B, D).contiguous()
+        self.pcholP0 = torch.as_tensor(np.linalg.cholesky(self.x0_cov), dtype=F64).to(dev).expand(B, D, D).contiguous()
         m = self.fx_mus[:, 1:].contiguous()
         S = self.fx_covs[:, 1:].contiguous()
         clip = self.clip if self.stabilize_ssm else None
@@ -139,6 +145,50 @@ class CviEngine:
         p = self._problem(0.0, 0.0, flags=_lib.FLAG_POSTERIOR_SSM_ONLY)
         check(_lib.load().vdp_cvi_elbo(C.byref(p), self._stream()), "vdp_cvi_elbo")
         return self.qA, self.qb, self.qcholQ, self.qmu0, self.qcholP0
+
+    # ---- prior-parameter learning (cvi_dp_trainer.py:207-250)
+    def _scratch_marginals(self):
+        """Buffers for dist_q.marginals that must not overwrite the stored fx_mus / fx_covs (the reference keeps
+        self.fx_mus as of the last site update while classic_elbo / grad_* rebuild dist_q, :339-352, :495-518)."""
+        if getattr(self, "_tmp_mus", None) is None:
+            self._tmp_mus, self._tmp_covs = torch.empty_like(self.fx_mus), torch.empty_like(self.fx_covs)
+        return self._tmp_mus, self._tmp_covs
+
+    def _problem_with_scratch_marginals(self):
+        p = self._problem(0.0, 0.0)
+        tm, tS = self._scratch_marginals()
+        p.fx_mus, p.fx_covs = tm.data_ptr(), tS.data_ptr()
+        return p
+
+    def classic_elbo_keep_marginals(self):
+        """classic_elbo (variational_cvi_sde.py:339-352) with the stored fx_mus / fx_covs left as they are."""
+        p = self._problem_with_scratch_marginals()
+        check(_lib.load().vdp_cvi_elbo(C.byref(p), self._stream()), "vdp_cvi_elbo")
+        return self.elbo
+
+    def n_drift_params(self):
+        return ops.drift_num_params(self.drift_id)
+
+    def grad_kl_prior_params(self):
+        """CVISitesSDE.grad_KL_wrt_prior_params (variational_cvi_sde.py:495-504) -> [B, n_params]."""
+        p = self._problem_with_scratch_marginals()
+        g = torch.empty((self.B, 16), dtype=F64, device=self.device)
+        check(_lib.load().vdp_cvi_grad_kl_prior_params(C.byref(p), C.c_void_p(g.data_ptr()), self._stream()),
+              "vdp_cvi_grad_kl_prior_params")
+        return g[:, :self.n_drift_params()]
+
+    def grad_ve_prior_params(self):
+        """CVISitesSDE.grad_VE_wrt_prior_params (variational_cvi_sde.py:506-518) -> [B, n_params] = d(-VE)/dp.
+        Re-linearises the prior around the stored posterior path as a side effect, as the reference does (:512)."""
+        self.set_linearized_prior()
+        p = self._problem_with_scratch_marginals()
+        g = torch.empty((self.B, 16), dtype=F64, device=self.device)
+        clip = 1 if self.stabilize_ssm else 0
+        check(_lib.load().vdp_cvi_grad_ve_prior_params(C.byref(p), C.c_void_p(self.fx_mus.data_ptr()),
+                                                       C.c_void_p(self.fx_covs.data_ptr()), clip, self.clip[0],
+                                                       self.clip[1], C.c_void_p(g.data_ptr()), self._stream()),
+              "vdp_cvi_grad_ve_prior_params")
+        return g[:, :self.n_drift_params()]
 
     def check_status(self):
         code, idx = ops.read_status(self.status)

@@ -40,7 +40,7 @@ class CVISitesSDE:
         self.prior_sde = prior_sde
         if prior_initial_state is None:   # :434-444
             prior_initial_state = Gaussian(np.zeros(D), prior_sde.q * np.ones((D, D)))
-        self.prior_initial_state = prior_initial_state
+        self._prior_initial_state = prior_initial_state
         self.likelihood = likelihood
         tg = as_np(time_grid).reshape(-1)
         self.time_grid = tg
@@ -53,11 +53,21 @@ class CVISitesSDE:
             init_m, init_S = as_np(initial_posterior_path.mu), as_np(initial_posterior_path.cov)
         self.stabilize_ssm = stabilize_ssm
         self.clip_state_transitions = clip_state_transitions
-        self._eng = CviEngine(prior_sde.drift_id, prior_sde.params, prior_sde.q, tg, self.obs_sites_indices, obs_y,
+        self._engine = CviEngine(prior_sde.drift_id, prior_sde.params, prior_sde.q, tg, self.obs_sites_indices, obs_y,
                               likelihood.chol_covariance, as_np(prior_initial_state.mu), as_np(prior_initial_state.cov),
                               stabilize_ssm=stabilize_ssm, clip_state_transitions=clip_state_transitions,
                               initial_mean=None if init_m is None else init_m[None],
                               initial_cov=None if init_S is None else init_S[None])
+
+    @property
+    def prior_initial_state(self) -> Gaussian:
+        return self._prior_initial_state
+
+    @prior_initial_state.setter
+    def prior_initial_state(self, value: Gaussian):
+        """Assignable as in the reference (cvi_dp_trainer.py:231-235)."""
+        self._prior_initial_state = value
+        self._engine.set_prior_initial_state(as_np(value.mu), as_np(value.cov))
 
     # ---- state, in the reference's names
     @property
@@ -100,6 +110,12 @@ class CVISitesSDE:
         e = self._eng
         return StateSpaceModel(e.pmu0[0], e.pcholP0[0], e.pA_lin[0], e.pb_lin[0], e.pcholQ[0])
 
+    @property
+    def _eng(self) -> CviEngine:
+        """The engine with the drift parameters of ``prior_sde`` (prior learning changes them between calls)."""
+        self._engine.drift_params = [float(v) for v in self.prior_sde.params]
+        return self._engine
+
     def set_linearized_prior(self):
         """variational_cvi_sde.py:408-432"""
         self._eng.set_linearized_prior()
@@ -120,8 +136,20 @@ class CVISitesSDE:
         self._eng.site_update(0.0, lr, flags=_lib.FLAG_SKIP_DATA_UPDATE | _lib.FLAG_SKIP_ELBO)
 
     def classic_elbo(self):
-        """variational_cvi_sde.py:339-352"""
-        return self._eng.classic_elbo()[0]
+        """variational_cvi_sde.py:339-352.  dist_q is rebuilt from the sites; the stored ``fx_mus`` / ``fx_covs`` keep
+        the values of the last site update, as in the reference."""
+        return self._eng.classic_elbo_keep_marginals()[0]
+
+    # ---- prior-parameter learning (cvi_dp_trainer.py:207-250)
+    def grad_KL_wrt_prior_params(self):
+        """variational_cvi_sde.py:495-504 -> one gradient per ``prior_sde.trainable_variables`` entry."""
+        g = self._eng.grad_kl_prior_params()[0]
+        return [g[i] for i in self.prior_sde.trainable_indices]
+
+    def grad_VE_wrt_prior_params(self):
+        """variational_cvi_sde.py:506-518 (re-linearises the prior as a side effect, :512)."""
+        g = self._eng.grad_ve_prior_params()[0]
+        return [g[i] for i in self.prior_sde.trainable_indices]
 
     def site_update(self, data_lr: float, girsanov_lr: float):
         """The three calls above fused in one launch sequence; returns the ELBO."""
@@ -129,12 +157,12 @@ class CVISitesSDE:
 
     def variational_expectation(self):
         """variational_cvi_sde.py:319-337 (of the current posterior)"""
-        self._eng.classic_elbo()
+        self.classic_elbo()
         return self._eng.ve[0]
 
     def KL_q_p(self):
         """variational_cvi_sde.py:446-486"""
-        self._eng.classic_elbo()
+        self.classic_elbo()
         return self._eng.kl[0]
 
     def grad_kl_wrt_exp_param(self):

@@ -34,7 +34,7 @@ class VariationalMarkovGP:
         self.stabilize_system = stabilize_system
         self.obs_indices = np.where(np.equal(tg[..., None], self._time_points))[0]
         assert self.obs_indices.shape[0] == self.observations.shape[0], "every observation must sit on a grid point"
-        self._eng = VgpEngine(prior_sde.drift_id, prior_sde.params, prior_sde.q, tg, self.obs_indices,
+        self._engine = VgpEngine(prior_sde.drift_id, prior_sde.params, prior_sde.q, tg, self.obs_indices,
                               self.observations.reshape(-1, D), likelihood.chol_covariance,
                               as_np(prior_initial_state.mu), as_np(prior_initial_state.cov),
                               stabilize_system=stabilize_system)
@@ -80,6 +80,42 @@ class VariationalMarkovGP:
         if m is None:
             self._eng.forward_pass()
         return self._eng.elbo()[0]
+
+    # ---- prior-parameter learning (vi_markov_gp_trainer.py:163-235)
+    @property
+    def _eng(self) -> VgpEngine:
+        """The engine with the drift parameters of ``prior_sde`` (prior learning changes them between calls)."""
+        self._engine.drift_params = [float(v) for v in self.prior_sde.params]
+        return self._engine
+
+    def grad_prior_sde_params(self):
+        """vi_sde.py:457-470 -> one gradient of E_sde per ``prior_sde.trainable_variables`` entry."""
+        g = self._eng.grad_prior_sde_params()[0]
+        return [g[i] for i in self.prior_sde.trainable_indices]
+
+    def KL_initial_state(self):
+        """vi_sde.py:416-420: KL[q(x0) || p(x0)] (D x D algebra on the host side of the device tensors)."""
+        import torch
+        q0 = torch.distributions.MultivariateNormal(self.q_initial_mean, scale_tril=self.q_initial_chol)
+        p0 = torch.distributions.MultivariateNormal(as_dev(self.prior_initial_state.mu),
+                                                    covariance_matrix=as_dev(self.prior_initial_state.cov))
+        return torch.distributions.kl_divergence(q0, p0)
+
+    def grad_initial_state(self):
+        """vi_sde.py:472-482: d KL[q(x0) || p(x0)] / d(prior loc, prior scale_tril)."""
+        import torch
+        loc = as_dev(self.prior_initial_state.mu).clone().requires_grad_(True)
+        tril = torch.linalg.cholesky(as_dev(self.prior_initial_state.cov)).clone().requires_grad_(True)
+        q0 = torch.distributions.MultivariateNormal(self.q_initial_mean, scale_tril=self.q_initial_chol)
+        p0 = torch.distributions.MultivariateNormal(loc, scale_tril=torch.tril(tril))
+        g = torch.autograd.grad(torch.distributions.kl_divergence(q0, p0), [loc, tril])
+        return [g[0], torch.tril(g[1])]
+
+    def set_prior_initial_state(self, mu, cov):
+        """Assign p(x0) (vi_markov_gp_trainer.py:217-218)."""
+        self.prior_initial_state = Gaussian(as_np(mu), as_np(cov))
+        self._eng.x0_mu = as_np(mu).reshape(-1).astype(np.float64)
+        self._eng.x0_cov = np.atleast_2d(as_np(cov)).astype(np.float64)
 
     def sweep(self, lr: float, update_x0: bool = False, x0_lr: float = 0.1):
         """One iteration of VIMarkovGPTrainer.perform_inference (vi_markov_gp_trainer.py:62-73), fused."""

@@ -24,12 +24,32 @@ class SDE:
     drift_id = None
     full_jacobian = False   # True when gradient_drift returns the [.., D, D] Jacobian (batch_jacobian subclasses)
 
+    param_names = ()        # attributes behind ``params``, in the order of the kernels' parameter block
+
     def __init__(self, state_dim=1):
         self._state_dim = state_dim
+        if not hasattr(self, "_trainable"):
+            self._trainable = [False] * len(self.param_names)
 
     @property
     def state_dim(self) -> int:
         return self._state_dim
+
+    # ---- the reference's tf.Variable(trainable=...) parameters (sde.py:150, 197-198, 242, 286, 330, 451-452)
+    @property
+    def trainable_indices(self):
+        """Positions in ``params`` of the parameters the reference would list in ``trainable_variables``."""
+        return [i for i, t in enumerate(self._trainable) if t]
+
+    @property
+    def trainable_variables(self):
+        p = list(self.params)
+        return [p[i] for i in self.trainable_indices]
+
+    def assign_trainable(self, values):
+        """Write new values of the trainable parameters (what ``optimizer.apply_gradients`` does to the variables)."""
+        for i, v in zip(self.trainable_indices, values):
+            setattr(self, self.param_names[i], float(v))
 
     @property
     def params(self):
@@ -76,8 +96,11 @@ class OrnsteinUhlenbeckSDE(SDE):
 
     def __init__(self, decay: float = 1.0, q=np.ones((1, 1)), trainable: bool = False):
         self.q = _q(q)
+        self._trainable = [bool(trainable)]
         super().__init__(self.q.shape[0])
         self.decay = float(decay)
+
+    param_names = ("decay",)
 
     @property
     def params(self):
@@ -96,8 +119,11 @@ class DoubleWellSDE(SDE):
 
     def __init__(self, q=np.ones((1, 1)), scale_trainable: bool = False, c_trainable: bool = False, scale=4.0, c=1.0):
         self.q = _q(q)
+        self._trainable = [bool(scale_trainable), bool(c_trainable)]
         super().__init__(self.q.shape[0])
         self.scale, self.c = float(scale), float(c)
+
+    param_names = ("scale", "c")
 
     @property
     def params(self):
@@ -116,8 +142,11 @@ class BenesSDE(SDE):
 
     def __init__(self, theta: float = 1, q=np.ones((1, 1)), trainable=False):
         self.q = _q(q)
+        self._trainable = [bool(trainable)]
         super().__init__(self.q.shape[0])
         self.theta = float(theta)
+
+    param_names = ("theta",)
 
     @property
     def params(self):
@@ -136,8 +165,11 @@ class SineDiffusionSDE(SDE):
 
     def __init__(self, theta: float = 0, q=np.ones((1, 1)), trainable=False):
         self.q = _q(q)
+        self._trainable = [bool(trainable)]
         super().__init__(self.q.shape[0])
         self.theta = float(theta)
+
+    param_names = ("theta",)
 
     @property
     def params(self):
@@ -156,8 +188,11 @@ class SqrtDiffusionSDE(SDE):
 
     def __init__(self, theta: float = 1, q=np.ones((1, 1)), trainable=False):
         self.q = _q(q)
+        self._trainable = [bool(trainable)]
         super().__init__(self.q.shape[0])
         self.theta = float(theta)
+
+    param_names = ("theta",)
 
     @property
     def params(self):
@@ -181,6 +216,10 @@ class MLPDrift(SDE):
             weights = np.random.default_rng(seed).normal(size=10) * 0.5
         self.weights = [float(v) for v in np.asarray(weights).reshape(-1)]
         assert len(self.weights) == 10, "w1[3], b1[3], w2[3], b2"
+        self._trainable = [True] * 10     # Keras layers: every weight is a trainable variable (sde.py:373-377)
+
+    def assign_trainable(self, values):
+        self.weights = [float(v) for v in values]
 
     @property
     def params(self):
@@ -204,8 +243,11 @@ class VanderPolOscillatorSDE(SDE):
 
     def __init__(self, a: float = 1.0, tau: float = 1.0, q=np.eye(2), trainable=False):
         self.q = _q(q)
+        self._trainable = [bool(trainable), bool(trainable)]
         super().__init__(2)
         self.a, self.tau = float(a), float(tau)
+
+    param_names = ("a", "tau")
 
     @property
     def params(self):
@@ -227,8 +269,11 @@ class Lorenz63SDE(SDE):
     drift_id = DRIFT_LORENZ63
     full_jacobian = True
 
-    def __init__(self, sigma=10.0, rho=28.0, beta=8.0 / 3.0, q=np.eye(3)):
+    param_names = ("sigma", "rho", "beta")
+
+    def __init__(self, sigma=10.0, rho=28.0, beta=8.0 / 3.0, q=np.eye(3), trainable=False):
         self.q = _q(q)
+        self._trainable = [bool(trainable)] * 3
         super().__init__(3)
         self.sigma, self.rho, self.beta = float(sigma), float(rho), float(beta)
 
@@ -246,8 +291,11 @@ class OUNdSDE(SDE):
     drift_id = DRIFT_OU_ND
     full_jacobian = True
 
-    def __init__(self, decay=0.5, q=np.eye(3)):
+    param_names = ("decay",)
+
+    def __init__(self, decay=0.5, q=np.eye(3), trainable=False):
         self.q = _q(q)
+        self._trainable = [bool(trainable)]
         super().__init__(self.q.shape[0])
         self.decay = float(decay)
 

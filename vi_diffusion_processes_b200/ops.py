@@ -281,6 +281,35 @@ def sq_drift_difference(drift_id, params, q, dt, A, b, m, S, want_grads=False, s
     return (value, dEdm, dEdS) if want_grads else value
 
 
+def drift_num_params(drift_id):
+    return int(_lib.load().vdp_drift_num_params(int(drift_id)))
+
+
+def drift_param_grad(drift_id, params, q, q_scale, c_x, c_f, a_sign, out_scale, A, b, m, S, point_offset=0,
+                     status=None):
+    """
+    grads[b, p] = out_scale sum_t E_{N(m_t, S_t)}[r^T sym((q_scale q)^-1) df/dp],  r = c_x x + c_f f(x) - (a_sign A_t x
+    + b_t), H = 20 (``vdp_drift_param_grad``).  A [B,N,D,D], b [B,N,D]; m [B,P,D], S [B,P,D,D] with P >= N +
+    point_offset grid points per sequence, transition t reads grid point t + point_offset.  -> [B, n_params].
+    """
+    _req(A, b, m, S, status)
+    B, N, D = b.shape
+    pts = m.shape[1]
+    assert pts >= N + point_offset and S.shape[1] == pts
+    lib = _lib.load()
+    import numpy as np
+    qh = np.atleast_2d(np.asarray(q, dtype=np.float64))
+    grads = torch.empty((B, 16), dtype=F64, device=A.device)
+    nbytes = lib.vdp_drift_param_grad_workspace(B, N, D)
+    ws = _workspace(nbytes, A.device)
+    mp = C.c_void_p(m.data_ptr() + 8 * D * point_offset)
+    Sp = C.c_void_p(S.data_ptr() + 8 * D * D * point_offset)
+    check(lib.vdp_drift_param_grad(int(drift_id), dvec(params, 16), dvec(qh.reshape(-1), D * D), float(q_scale),
+                                   float(c_x), float(c_f), float(a_sign), float(out_scale), _p(A), _p(b), mp, Sp, pts,
+                                   _p(grads), _p(ws), nbytes, B, N, D, _p(status), _stream()), "vdp_drift_param_grad")
+    return grads[:, :drift_num_params(drift_id)]
+
+
 def expectations_to_ssm_vjp(e1, ed, es, gA, gb, gcholP0, gcholQ, gmu0, status=None):
     """VJP of expectations_to_ssm_params (ssm_natgrad.py:168) -> dL/d(eta1, eta_diag, eta_subdiag)."""
     _req(e1, ed, es, gA, gb, gcholP0, gcholQ, gmu0, status)

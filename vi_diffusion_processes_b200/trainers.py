@@ -8,10 +8,12 @@ Mirrors of the reference's trainer loops around the hot path (SURVEY section 8f,
   iterations with learning-rate decay;
 * :func:`calculate_nlpd`, :func:`calculate_rmse` -- ``docs/diffusion_processes/exp_dp_utils.py:189-224``.
 
-Same constructor arguments, loop structure, break conditions and return values as the reference; logging, wandb and
-prior-parameter learning (``learn_prior_sde=True``; needs the adjoint of the linearisation, item 3 of 8f) are not
-part of this build.  The models are the ``markovflow`` mirrors of this package, i.e. every step runs through the
-C ABI on the GPU; the loop itself reads one ELBO scalar per iteration, as the reference does.
+Same constructor arguments, loop structure, break conditions and return values as the reference, including
+prior-parameter learning (``learn_prior_sde=True``: ``optimize_prior_sde`` of ``cvi_dp_trainer.py:207-250`` and
+``vi_markov_gp_trainer.py:163-235`` with a host-side Adam on the few drift parameters, :class:`Adam` below); logging
+and wandb are not part of this build.  The models are the ``markovflow`` mirrors of this package, i.e. every step
+runs through the C ABI on the GPU; the loop itself reads one ELBO scalar (and, when learning, one gradient per
+drift parameter) per iteration, as the reference does.
 """
 from __future__ import annotations
 
@@ -55,17 +57,58 @@ def calculate_rmse(m, time_grid, test_data) -> float:
     return float(torch.sqrt(torch.mean((m.index_select(0, idx) - y) ** 2)).item())
 
 
+class Adam:
+    """tf.optimizers.Adam on a short list of float64 scalars (the drift parameters): beta1 = 0.9, beta2 = 0.999,
+    epsilon = 1e-7, lr_t = lr sqrt(1 - beta2^t) / (1 - beta1^t), theta -= lr_t m / (sqrt(v) + epsilon)."""
+
+    def __init__(self, learning_rate: float = 1e-2, beta_1: float = 0.9, beta_2: float = 0.999, epsilon: float = 1e-7):
+        self.lr, self.beta_1, self.beta_2, self.epsilon = learning_rate, beta_1, beta_2, epsilon
+        self.t, self.m, self.v = 0, None, None
+
+    def apply_gradients(self, grads, values):
+        g = np.asarray([_f(x) for x in grads], dtype=np.float64)
+        x = np.asarray([_f(v) for v in values], dtype=np.float64)
+        if self.m is None:
+            self.m, self.v = np.zeros_like(g), np.zeros_like(g)
+        self.t += 1
+        self.m = self.beta_1 * self.m + (1.0 - self.beta_1) * g
+        self.v = self.beta_2 * self.v + (1.0 - self.beta_2) * g * g
+        lr_t = self.lr * math.sqrt(1.0 - self.beta_2 ** self.t) / (1.0 - self.beta_1 ** self.t)
+        return x - lr_t * self.m / (np.sqrt(self.v) + self.epsilon)
+
+
+def _is_ou(sde) -> bool:
+    return type(sde).__name__ == "OrnsteinUhlenbeckSDE"
+
+
+def _is_mlp(sde) -> bool:
+    return type(sde).__name__ == "MLPDrift"
+
+
 class CVISitesTrainer:
-    """cvi_dp_trainer.py:18-160 (inference part)."""
+    """cvi_dp_trainer.py:18-250."""
 
     def __init__(self, model, test_data, prior_sde=None, max_itr: int = 100, optim_tol: float = 1e-2,
                  max_itr_sites_optim: int = 20, girsanov_sites_lr: float = 0.1, data_sites_lr: float = 0.1,
-                 learn_prior_sde: bool = False, **unused):
-        if learn_prior_sde:
-            raise NotImplementedError("prior-parameter learning is not part of this build (SURVEY 8f item 3)")
+                 learn_prior_sde: bool = False, prior_sde_lr: float = 1e-2, learning_max_itr: int = 100,
+                 learning_tol: float = 1e-2, **unused):
         self.model, self.test_data, self.prior_sde = model, test_data, prior_sde
         self.max_itr, self.optim_tol, self.max_itr_sites_optim = max_itr, optim_tol, max_itr_sites_optim
         self.girsanov_sites_lr, self.data_sites_lr = girsanov_sites_lr, data_sites_lr
+        self.learn_prior_sde, self.prior_sde_lr = learn_prior_sde, prior_sde_lr
+        self.learning_max_itr, self.learning_tol = learning_max_itr, learning_tol
+        self.prior_params = {}
+        self.n_prior_step = 0
+        if self.learn_prior_sde:
+            self.prior_sde_optim = Adam(learning_rate=self.prior_sde_lr)
+            self.store_prior_param_vals()
+
+    def store_prior_param_vals(self):
+        """cvi_dp_trainer.py:52-61"""
+        if _is_mlp(self.model.prior_sde):
+            return
+        for i, v in enumerate(self.model.prior_sde.trainable_variables):
+            self.prior_params.setdefault(str(i), []).append(float(v))
 
     def _elbo(self) -> float:
         return _f(self.model.classic_elbo())
@@ -114,24 +157,77 @@ class CVISitesTrainer:
                 self.model.relinearize_and_transform_sites()
         return elbo_vals[1:], nlpd_vals, rmse_vals
 
+    def optimize_prior_sde(self):
+        """cvi_dp_trainer.py:207-250: Adam steps on the drift parameters along d(KL - VE)/d params."""
+        from .markovflow.sde.sde_utils import Gaussian
+        model, sde = self.model, self.model.prior_sde
+        elbo, nlpd, rmse = [self._elbo()], [], []
+        for _ in range(self.learning_max_itr):
+            grads_kl = model.grad_KL_wrt_prior_params()
+            grads_ve = model.grad_VE_wrt_prior_params()
+            grads = [_f(a) + _f(b) for a, b in zip(grads_kl, grads_ve)]
+            sde.assign_trainable(self.prior_sde_optim.apply_gradients(grads, sde.trainable_variables))
+            elbo.append(self._elbo())
+            nlpd.append(self.model_nlpd())
+            rmse.append(self.model_rmse())
+            self.n_prior_step += 1
+            self.store_prior_param_vals()
+            if _is_ou(sde):   # :231-235: p(x0) follows the stationary variance
+                steady_cov = np.asarray(sde.q, dtype=np.float64) / (2.0 * sde.decay)
+                model.prior_initial_state = Gaussian(np.zeros((1,)), steady_cov * np.ones((1, 1)))
+            if elbo[-1] < elbo[-2]:
+                self.prior_sde_optim.lr = self.prior_sde_optim.lr / 2
+            if abs(elbo[-2] - elbo[-1]) < self.learning_tol:
+                break
+        return elbo[1:], nlpd, rmse
+
     def optimize(self):
-        """cvi_dp_trainer.py:138-190 without prior learning: one perform_inference."""
+        """cvi_dp_trainer.py:138-190"""
         elbo, nlpd, rmse = [self._elbo()], [self.model_nlpd()], [self.model_rmse()]
-        e, n, r = self.perform_inference()
-        return elbo + e, nlpd + n, rmse + r, {}
+        previous = []
+        for _ in range(self.max_itr):
+            e, n, r = self.perform_inference()
+            elbo, nlpd, rmse = elbo + e, nlpd + n, rmse + r
+            if not self.learn_prior_sde:
+                break
+            pe, pn, pr = self.optimize_prior_sde()
+            done = abs(elbo[-1] - pe[-1]) < self.optim_tol
+            elbo, nlpd, rmse = elbo + pe, nlpd + pn, rmse + pr
+            if done:
+                break
+            if len(previous) > 4 and (abs(previous[-1] - previous[-3]) < 1e-4 or abs(previous[-2] - previous[-4]) < 1e-4):
+                break   # the objective jumps between two values (:176-183)
+            previous.append(elbo[-1])
+        return elbo, nlpd, rmse, self.prior_params
 
 
 class VIMarkovGPTrainer:
-    """vi_markov_gp_trainer.py:17-92 (inference part)."""
+    """vi_markov_gp_trainer.py:17-235."""
 
     def __init__(self, model, test_data, q_lr: float = 0.1, x0_lr: float = 0.1, max_itr: int = 100,
                  lr_tol: float = 1e-2, optim_tol: float = 1e-2, warmup_x0_itr: int = 10,
-                 learn_prior_sde: bool = False, **unused):
-        if learn_prior_sde:
-            raise NotImplementedError("prior-parameter learning is not part of this build (SURVEY 8f item 3)")
+                 learn_prior_sde: bool = False, prior_sde_lr: float = 1e-2, learning_max_itr: int = 100,
+                 learning_tol: float = 1e-2, optimize_prior_initial_state: bool = False,
+                 prior_initial_state_lr: float = 0.1, **unused):
         self.model, self.test_data = model, test_data
         self.q_lr, self.x0_lr, self.max_itr = q_lr, x0_lr, max_itr
         self.lr_tol, self.optim_tol, self.warmup_x0_itr = lr_tol, optim_tol, warmup_x0_itr
+        self.learn_prior_sde, self.prior_sde_lr = learn_prior_sde, prior_sde_lr
+        self.learning_max_itr, self.learning_tol = learning_max_itr, learning_tol
+        self.optimize_prior_initial_state = optimize_prior_initial_state
+        self.prior_initial_state_lr = prior_initial_state_lr
+        self.prior_params = {}
+        self.n_prior_step = 0
+        if self.learn_prior_sde:
+            self.prior_sde_optim = Adam(learning_rate=self.prior_sde_lr)
+            self.store_prior_param_vals()
+
+    def store_prior_param_vals(self):
+        """vi_markov_gp_trainer.py:152-161"""
+        if _is_mlp(self.model.prior_sde):
+            return
+        for i, v in enumerate(self.model.prior_sde.trainable_variables):
+            self.prior_params.setdefault(i, []).append(float(v))
 
     def model_nlpd(self, m, S) -> float:
         m, S = self.model.likelihood.predict_mean_and_var(m, S)
@@ -158,11 +254,52 @@ class VIMarkovGPTrainer:
                 break
         return elbo[1:], nlpd, rmse
 
+    def optimize_prior_x0(self):
+        """vi_markov_gp_trainer.py:203-218 (the reference multiplies the new factor with itself, not its transpose)."""
+        model, sde = self.model, self.model.prior_sde
+        mu = torch.as_tensor(as_np(model.prior_initial_state.mu))
+        if _is_ou(sde):
+            tril = torch.as_tensor(np.asarray(sde.q, dtype=np.float64) / (2.0 * sde.decay))
+        else:
+            g = model.grad_initial_state()
+            tril0 = torch.linalg.cholesky(torch.as_tensor(as_np(model.prior_initial_state.cov)))
+            mu = mu - self.prior_initial_state_lr * g[0].cpu()
+            tril = tril0 - self.prior_initial_state_lr * g[1].cpu()
+        model.set_prior_initial_state(mu, tril @ tril)
+
+    def optimize_prior_sde(self):
+        """vi_markov_gp_trainer.py:163-201"""
+        model, sde = self.model, self.model.prior_sde
+        elbo, nlpd, rmse = [_f(model.elbo())], [], []
+        for _ in range(self.learning_max_itr):
+            grads = model.grad_prior_sde_params()
+            sde.assign_trainable(self.prior_sde_optim.apply_gradients(grads, sde.trainable_variables))
+            if self.optimize_prior_initial_state:
+                self.optimize_prior_x0()
+            m, S = model.forward_pass
+            elbo.append(_f(model.elbo(m, S)))
+            nlpd.append(self.model_nlpd(m, S))
+            rmse.append(self.model_rmse(m, S))
+            self.store_prior_param_vals()
+            self.n_prior_step += 1
+            if abs(elbo[-2] - elbo[-1]) < self.learning_tol:
+                break
+        return elbo[1:], nlpd, rmse
+
     def optimize(self):
-        """vi_markov_gp_trainer.py:94-130 without prior learning: 20 warm-up sweeps at lr 1e-6, then inference."""
+        """vi_markov_gp_trainer.py:94-135: 20 warm-up sweeps at lr 1e-6, then inference (and learning) rounds."""
         for _ in range(20):
             self.model.sweep(1e-6)
         m, S = self.model.forward_pass
         elbo, nlpd, rmse = [_f(self.model.elbo(m, S))], [self.model_nlpd(m, S)], [self.model_rmse(m, S)]
-        e, n, r = self.perform_inference()
-        return elbo + e, nlpd + n, rmse + r
+        for _ in range(self.max_itr):
+            e, n, r = self.perform_inference()
+            elbo, nlpd, rmse = elbo + e, nlpd + n, rmse + r
+            if not self.learn_prior_sde:
+                break
+            pe, pn, pr = self.optimize_prior_sde()
+            elbo, nlpd, rmse = elbo + pe, nlpd + pn, rmse + pr
+            # :131 as written: (len > 2 and |diff|) < optim_tol, i.e. a short list (False < tol) also stops
+            if (abs(pe[-2] - pe[-1]) if len(pe) > 2 else 0.0) < self.optim_tol:
+                break
+        return elbo, nlpd, rmse, self.prior_params

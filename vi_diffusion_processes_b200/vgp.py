@@ -123,6 +123,13 @@ class VgpEngine:
         self._call("vdp_vgp_sweep", self._problem(lr=lr, x0_lr=x0_lr, update_x0=update_x0))
         return self.elbo_value
 
+    # vi_sde.py:457-470
+    def grad_prior_sde_params(self):
+        """d E_sde / d(drift parameters) at (m, S) = forward_pass[1:] held constant -> [B, n_params]."""
+        m, S = self.forward_pass()
+        return ops.drift_param_grad(self.drift_id, self.drift_params, self.q, 1.0, 0.0, 1.0, -1.0, self.dt, self.A,
+                                    self.b, m, S, point_offset=1, status=self.status)
+
     def check_status(self):
         code, idx = ops.read_status(self.status)
         if code != 0:
