@@ -121,6 +121,55 @@ template <> struct Drift<DRIFT_LORENZ63, 3> {
     }
 };
 
+// D = 1 quadrature loops (kl_kernels.cuh): residual of one Euler step against a linear transition and its slope,
+//   d(x) = x + dt f(x) - (A x + b),     j(x) = d'(x) = 1 + dt f'(x) - A,
+// from per-transition constants prepared once outside the node loop.  The generic form calls the drift functor;
+// polynomial drifts collapse to a Horner form (DW: d = x (k1 - a x^2) - b, j = k1 - 3 a x^2 with a = dt s,
+// k1 = 1 + a c - A: 4 float64 instructions per node instead of 9).
+template <int ID> struct DriftStep1 {
+    struct K { double omA, nb, dt; };
+    static __device__ __forceinline__ K prepare(const DriftParams&, double dt, double A, double b) {
+        K k;
+        k.omA = 1.0 - A; k.nb = -b; k.dt = dt;
+        return k;
+    }
+    static __device__ __forceinline__ void eval(const DriftParams& P, const K& k, double X, double& d, double& j) {
+        Vec<1> x, f;
+        Mat<1> J;
+        x(0) = X;
+        Drift<ID, 1>::eval(P, x, f, J);
+        d = fma(k.dt, f(0), fma(k.omA, X, k.nb));
+        j = fma(k.dt, J(0, 0), k.omA);
+    }
+};
+template <> struct DriftStep1<DRIFT_DW> {
+    struct K { double k1, na, na3, nb; };
+    static __device__ __forceinline__ K prepare(const DriftParams& P, double dt, double A, double b) {
+        K k;
+        const double a = dt * P.p[0];
+        k.k1 = fma(a, P.p[1], 1.0 - A); k.na = -a; k.na3 = -3.0 * a; k.nb = -b;
+        return k;
+    }
+    static __device__ __forceinline__ void eval(const DriftParams&, const K& k, double X, double& d, double& j) {
+        const double x2 = X * X;
+        d = fma(X, fma(k.na, x2, k.k1), k.nb);
+        j = fma(k.na3, x2, k.k1);
+    }
+};
+template <> struct DriftStep1<DRIFT_OU> {
+    struct K { double k1, nb; };
+    static __device__ __forceinline__ K prepare(const DriftParams& P, double dt, double A, double b) {
+        K k;
+        k.k1 = fma(-dt, P.p[0], 1.0 - A); k.nb = -b;
+        return k;
+    }
+    static __device__ __forceinline__ void eval(const DriftParams&, const K& k, double X, double& d, double& j) {
+        d = fma(k.k1, X, k.nb);
+        j = k.k1;
+    }
+};
+template <> struct DriftStep1<DRIFT_OU_ND> : DriftStep1<DRIFT_OU> {};
+
 // Derivatives of f and J with respect to every entry of the parameter block: what a tape watching
 // prior_sde.trainable_variables propagates through drift / gradient_drift (prior-parameter learning,
 // variational_cvi_sde.py:495-518, vi_sde.py:457-470).  df[p](i) = d f_i / d P.p[p], dJ[p](i, j) = d J_ij / d P.p[p].

@@ -36,7 +36,7 @@ struct KlTermOut {
 template <int DRIFT, int H>
 __device__ __forceinline__ void kl_term_scalar(const DriftParams& P, double Qp, double dt, double pi_factor,
                                                double mk, double mn, double edk, double edn, double esk,
-                                               KlTermOut<1>& out, bool& ok) {
+                                               KlTermOut<1>& out, bool& ok, bool want_value = true) {
     // expectations_to_ssm_params (ssm_gaussian_transformations.py:93-178)
     const double Sk = edk - mk * mk;
     const double Sn = edn - mn * mn;
@@ -54,25 +54,25 @@ __device__ __forceinline__ void kl_term_scalar(const DriftParams& P, double Qp, 
     sqrt_rsqrt_fast(Qp, cQp, iQp);
     const double Qpinv = iQp * iQp;
     // C = -(logdet Qq - logdet Qp) - 1 + Qp^-1 Qq   (sde_utils.py:317-330); chol(Qq) = LQ exactly
-    const double Cterm = -2.0 * log(LQ * iQp) - 1.0 + Qpinv * Qq;
+    // (skipped when only the gradient is wanted: the fused site update takes the KL value from the refreshed
+    // posterior later, classic_elbo, and never reads this one)
+    const double Cterm = want_value ? -2.0 * log(LQ * iQp) - 1.0 + Qpinv * Qq : 0.0;
     const double sL = 1.4142135623730951 * LS;
-    // d = x + dt f(x) - (A x + b) = (1 - A) x - b + dt f(x);  Q_p^-1 and pi^(-1/2) are factored out of the sums
-    const double omA = 1.0 - A, nb = -b;
+    // d = x + dt f(x) - (A x + b) and its slope j (DriftStep1);  Q_p^-1 and pi^(-1/2) are factored out of the sums
+    const typename DriftStep1<DRIFT>::K kst = DriftStep1<DRIFT>::prepare(P, dt, A, b);
     double quad = 0.0, gb = 0.0, gmq = 0.0, gA = 0.0, lsb = 0.0;
 #pragma unroll
     for (int p = 0; p < H; ++p) {
         const double xi = gh_x<H>(p), w = gh_w<H>(p);
-        Vec<1> X, f;
-        Mat<1> J;
-        X(0) = fma(sL, xi, mk);
-        Drift<DRIFT, 1>::eval(P, X, f, J);
-        const double d = fma(dt, f(0), fma(omA, X(0), nb));
+        const double X = fma(sL, xi, mk);
+        double d, j;
+        DriftStep1<DRIFT>::eval(P, kst, X, d, j);
         const double wd = w * d;
         quad = fma(wd, d, quad);
-        const double Xb = fma(dt, J(0, 0), omA) * wd;
+        const double Xb = j * wd;
         gb -= wd;
         gmq += Xb;
-        gA = fma(-wd, X(0), gA);
+        gA = fma(-wd, X, gA);
         lsb = fma(Xb, xi, lsb);
     }
     const double sc = pi_factor * Qpinv;
@@ -183,9 +183,11 @@ __device__ __forceinline__ void kl_quad_nested3(const DriftParams& P, const Mat<
 template <int DRIFT, int D, int H, int G>
 __device__ __forceinline__ void kl_term(const DriftParams& P, const Mat<D>& Qp, double dt, double pi_factor,
                                         const Vec<D>& e1k, const Vec<D>& e1n, const Mat<D>& edk, const Mat<D>& edn,
-                                        const Mat<D>& esk, int lane, KlTermOut<D>& out, bool& ok) {
+                                        const Mat<D>& esk, int lane, KlTermOut<D>& out, bool& ok,
+                                        bool want_value = true) {
     if constexpr (D == 1 && G == 1) {
-        kl_term_scalar<DRIFT, H>(P, Qp(0, 0), dt, pi_factor, e1k(0), e1n(0), edk(0, 0), edn(0, 0), esk(0, 0), out, ok);
+        kl_term_scalar<DRIFT, H>(P, Qp(0, 0), dt, pi_factor, e1k(0), e1n(0), edk(0, 0), edn(0, 0), esk(0, 0), out, ok,
+                                 want_value);
         return;
     }
     ExpToSsm<D> r;
@@ -282,6 +284,14 @@ __device__ __forceinline__ void kl_term(const DriftParams& P, const Mat<D>& Qp, 
     Rt.gm = Rt.gm - Tmv(gC, r.mk);
 }
 
+// Optional epilogue of the girsanov site update: the natural parameters of the posterior that follows
+// (prior naturals + updated sites + scattered data sites), so that the rebuild after update_girsanov_sites
+// (variational_cvi_sde.py:299) starts from them without another pass over the sites.
+struct KlNaturalsOut {
+    const double *pA = nullptr, *pb = nullptr, *pcholQ = nullptr, *pmu0 = nullptr, *pcholP0 = nullptr;
+    double *th1 = nullptr, *thd = nullptr, *ths = nullptr;
+};
+
 // shared-memory record handed from the group of node i to the group of node i+1
 template <int D>
 struct KlHandoff { double gm[D]; double gS[D * D]; };
@@ -299,7 +309,7 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
                           const double* __restrict__ Sd, double* __restrict__ terms, double* __restrict__ g1,
                           double* __restrict__ gd, double* __restrict__ gs, int upd, double lr,
                           const double* __restrict__ sc1, const double* __restrict__ scd, int64_t B, int64_t N,
-                          int64_t* status, int64_t node0 = 0, int64_t node1 = -1) {
+                          int64_t* status, int64_t node0 = 0, int64_t node1 = -1, KlNaturalsOut nat = KlNaturalsOut()) {
     // nodes [node0, node1) of the flat (b, k) index are processed (default: all); a rank of the sharded
     // quadrature passes its own range, the halo group recomputes the term that straddles the range start
     extern __shared__ unsigned char smem_raw[];
@@ -328,7 +338,7 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
         const Mat<D> edn = Sn + outer(mn, mn);
         const Mat<D> esk = mm(Ak, Sk) + outer(mn, mk);
         const double delta = time_grid[k + 1] - time_grid[k];
-        kl_term<DRIFT, D, H, G>(P, delta * q, dt, pi_factor, mk, mn, edk, edn, esk, lane, t, ok);
+        kl_term<DRIFT, D, H, G>(P, delta * q, dt, pi_factor, mk, mn, edk, edn, esk, lane, t, ok, terms != nullptr);
         if (!ok && lane == 0) report_not_pd(status, i);
         if (lane == 0) {
 #pragma unroll
@@ -366,7 +376,7 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
     }
     // S = eta_d - m m^T
     gm = gm - 2.0 * mv(gS, mk);
-    terms[i] = value;
+    if (terms) terms[i] = value;
     if (!upd) {
         vec_store<D>(g1 + i * D, gm);
         mat_store<D>(gd + i * DD, gS);
@@ -375,11 +385,34 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
         Vec<D> s1 = vec_zero<D>();
         Mat<D> s2 = mat_zero<D>();
         if (sc1) { s1 = vec_load<D>(sc1 + i * D); s2 = mat_load<D>(scd + i * DD); }
-        vec_store<D>(g1 + i * D, vec_load<D>(g1 + i * D) + lr * (s1 - gm));
-        mat_store<D>(gd + i * DD, mat_load<D>(gd + i * DD) + lr * (s2 - gS));
+        const Vec<D> n1 = vec_load<D>(g1 + i * D) + lr * (s1 - gm);
+        const Mat<D> nd = mat_load<D>(gd + i * DD) + lr * (s2 - gS);
+        vec_store<D>(g1 + i * D, n1);
+        mat_store<D>(gd + i * DD, nd);
+        Mat<D> ns = mat_zero<D>();
+        const int64_t tt = b * N + k;
         if (has_term) {
-            const int64_t tt = b * N + k;
-            mat_store<D>(gs + tt * DD, mat_load<D>(gs + tt * DD) - lr * t.ges);
+            ns = mat_load<D>(gs + tt * DD) - lr * t.ges;
+            mat_store<D>(gs + tt * DD, ns);
+        }
+        if (nat.th1) {
+            // full_sites of the posterior that follows (variational_cvi_sde.py:161-174): naturals of the linearised
+            // prior (same statements as k_ssm_to_naturals) + the updated girsanov sites + the scattered data sites
+            const Mat<D> ck = (k == 0) ? mat_load<D>(nat.pcholP0 + b * DD) : mat_load<D>(nat.pcholQ + (tt - 1) * DD);
+            const Vec<D> ok0 = (k == 0) ? vec_load<D>(nat.pmu0 + b * D) : vec_load<D>(nat.pb + (tt - 1) * D);
+            Mat<D> Ak = mat_zero<D>(), cn = mat_eye<D>(), td, ts;
+            Vec<D> bn = vec_zero<D>(), t1;
+            if (has_term) {
+                Ak = mat_load<D>(nat.pA + tt * DD);
+                cn = mat_load<D>(nat.pcholQ + tt * DD);
+                bn = vec_load<D>(nat.pb + tt * D);
+            }
+            ssm_node_naturals<D>(ck, ok0, has_term, Ak, cn, bn, t1, td, ts);
+            if (has_term) mat_store<D>(nat.ths + tt * DD, ts + ns);
+            t1 = t1 + n1;
+            td = td + nd;
+            vec_store<D>(nat.th1 + i * D, t1 + s1);
+            mat_store<D>(nat.thd + i * DD, td + s2);
         }
     }
 }
@@ -434,15 +467,13 @@ __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
     }
     double quad = 0.0;
     if constexpr (D == 1 && G == 1) {
-        const double sL = 1.4142135623730951 * LS(0, 0), m1 = mk(0), omA = 1.0 - Ak(0, 0), nb = -bk(0);
+        const double sL = 1.4142135623730951 * LS(0, 0), m1 = mk(0);
+        const typename DriftStep1<DRIFT>::K kst = DriftStep1<DRIFT>::prepare(P, dt, Ak(0, 0), bk(0));
         double quad_ = 0.0;
 #pragma unroll
         for (int p = 0; p < H; ++p) {
-            Vec<1> X, f;
-            Mat<1> J;
-            X(0) = fma(sL, gh_x<H>(p), m1);
-            Drift<DRIFT, 1>::eval(P, X, f, J);
-            const double d = fma(dt, f(0), fma(omA, X(0), nb));   // x + dt f(x) - (A x + b)
+            double d, j;
+            DriftStep1<DRIFT>::eval(P, kst, fma(sL, gh_x<H>(p), m1), d, j);   // x + dt f(x) - (A x + b)
             quad_ = fma(gh_w<H>(p) * d, d, quad_);
         }
         quad = (pi_factor * Qpinv(0, 0)) * quad_;

@@ -5,6 +5,45 @@
 
 namespace vdp {
 
+// Natural parameters one node of a state-space model contributes (ssm_gaussian_transformations.py:182-253):
+//   t1 = C_k^-1 o_k - A_k^T Q_k^-1 b_k,   td = -1/2 (C_k^-1 + A_k^T Q_k^-1 A_k),   ts = Q_k^-1 A_k
+// with C_k = ck ck^T the covariance the node's own factor stands for (chol P0 for node 0, chol Q_{k-1} after),
+// o_k its offset (mu0 / b_{k-1}) and (A_k, cn = chol Q_k, bn = b_k) the transition that leaves the node (has_next).
+// D = 1 takes two reciprocals instead of the triangular-solve chain.
+template <int D>
+__device__ __forceinline__ void ssm_node_naturals(const Mat<D>& ck, const Vec<D>& ok, bool has_next, const Mat<D>& Ak,
+                                                  const Mat<D>& cn, const Vec<D>& bn, Vec<D>& t1, Mat<D>& td,
+                                                  Mat<D>& ts) {
+    if constexpr (D == 1) {
+        const double r = rcp_fast(ck.a[0]);
+        const double ir2 = r * r;
+        double v1 = ok.v[0] * ir2, vd = ir2;
+        ts.a[0] = 0.0;
+        if (has_next) {
+            const double rn = rcp_fast(cn.a[0]);
+            const double in2 = rn * rn;
+            const double la = Ak.a[0] * rn;
+            ts.a[0] = Ak.a[0] * in2;
+            v1 = fma(-Ak.a[0], bn.v[0] * in2, v1);
+            vd = fma(la, la, vd);
+        }
+        t1.v[0] = v1;
+        td.a[0] = -0.5 * vd;
+    } else {
+        t1 = chol_solve(ck, ok);
+        td = chol_inverse(ck);
+        ts = mat_zero<D>();
+        if (has_next) {
+            const Vec<D> tn = chol_solve(cn, bn);
+            const Mat<D> LinvA = trsm(cn, Ak);
+            ts = trsmT(cn, LinvA);
+            t1 = t1 - Tmv(Ak, tn);
+            td = td + Tmm(LinvA, LinvA);
+        }
+        td = -0.5 * td;
+    }
+}
+
 // ssm_to_naturals (ssm_gaussian_transformations.py:182-253) for grid point k of sequence b, optionally
 // summed with the girsanov sites: theta = nat(p) + g  (variational_cvi_sde.py:161-174; the data sites
 // are scattered on top by k_scatter_data, in the reference's left-to-right order).
@@ -22,20 +61,18 @@ __global__ void k_ssm_to_naturals(const double* __restrict__ A, const double* __
     const int64_t b = i / n, k = i % n;
     const Mat<D> ck = (k == 0) ? mat_load<D>(cholP0 + b * DD) : mat_load<D>(cholQ + (b * N + k - 1) * DD);
     const Vec<D> ok = (k == 0) ? vec_load<D>(mu0 + b * D) : vec_load<D>(bo + (b * N + k - 1) * D);
-    Vec<D> t1 = chol_solve(ck, ok);
-    Mat<D> td = chol_inverse(ck);
+    Mat<D> Ak = mat_zero<D>(), cn = mat_eye<D>(), td, ts;
+    Vec<D> bn = vec_zero<D>(), t1;
     if (k < N) {
-        const Mat<D> Ak = mat_load<D>(A + (b * N + k) * DD);
-        const Mat<D> cn = mat_load<D>(cholQ + (b * N + k) * DD);
-        const Vec<D> tn = chol_solve(cn, vec_load<D>(bo + (b * N + k) * D));
-        const Mat<D> LinvA = trsm(cn, Ak);
-        Mat<D> ts = trsmT(cn, LinvA);
-        t1 = t1 - Tmv(Ak, tn);
-        td = td + Tmm(LinvA, LinvA);
+        Ak = mat_load<D>(A + (b * N + k) * DD);
+        cn = mat_load<D>(cholQ + (b * N + k) * DD);
+        bn = vec_load<D>(bo + (b * N + k) * D);
+    }
+    ssm_node_naturals<D>(ck, ok, k < N, Ak, cn, bn, t1, td, ts);
+    if (k < N) {
         if (gs) ts = ts + mat_load<D>(gs + (b * N + k) * DD);
         mat_store<D>(ths + (b * N + k) * DD, ts);
     }
-    td = -0.5 * td;
     if (g1) t1 = t1 + vec_load<D>(g1 + i * D);
     if (gd) td = td + mat_load<D>(gd + i * DD);
     vec_store<D>(th1 + i * D, t1);

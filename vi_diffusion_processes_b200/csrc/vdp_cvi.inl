@@ -14,7 +14,8 @@ static int launch_kl_grad(const DriftParams& P, const double* q_host, double dt,
                           const double* x0_mu, const double* x0_cov, const double* Aq, const double* m,
                           const double* Sd, double* terms, double* g1, double* gd, double* gs, int upd, double lr,
                           const double* sc1, const double* scd, int64_t B, int64_t N, int64_t* status,
-                          cudaStream_t st, int64_t node0 = 0, int64_t node1 = -1) {
+                          cudaStream_t st, int64_t node0 = 0, int64_t node1 = -1,
+                          const KlNaturalsOut& nat = KlNaturalsOut()) {
     using KL = KlLaunch<D>;
     const int64_t total = ((node1 < 0) ? B * (N + 1) : node1) - node0;
     if (total <= 0) return VDP_OK;
@@ -22,7 +23,7 @@ static int launch_kl_grad(const DriftParams& P, const double* q_host, double dt,
     const size_t smem = KL::groups * sizeof(KlHandoff<D>);
     k_kl_grad<DRIFT, D, 20, KL::G><<<grid, KL::threads, smem, st>>>(
         P, host_mat<D>(q_host), dt, pi_factor(D), time_grid, host_vec<D>(x0_mu), host_mat<D>(x0_cov), Aq, m, Sd,
-        terms, g1, gd, gs, upd, lr, sc1, scd, B, N, status, node0, node1);
+        terms, g1, gd, gs, upd, lr, sc1, scd, B, N, status, node0, node1, nat);
     VDP_CHECK_LAUNCH();
     return VDP_OK;
 }
@@ -60,17 +61,20 @@ static inline bool cvi_ws_take(void* ws, size_t bytes, int64_t B, int64_t N, int
 }
 
 // (F): sites -> q as an SSM -> marginals.   variational_cvi_sde.py:161-192 + gauss_markov.py:107-117
+// naturals_ready: the site-update kernel has already written the natural parameters into the workspace
 template <int D>
-static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t st) {
+static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t st, bool naturals_ready = false) {
     const int64_t B = p.B, N = p.N;
-    prof_mark(VDP_PHASE_SITES_TO_NAT, st);
-    k_ssm_to_naturals<D><<<grid_for(B * (N + 1), kPtBlock), kPtBlock, 0, st>>>(
-        p.pA, p.pb, p.pcholQ, p.pmu0, p.pcholP0, p.g1, p.gd, p.gs, w.th1, w.thd, w.ths, B, N);
-    VDP_CHECK_LAUNCH();
-    if (p.n_obs > 0) {
-        k_scatter_data<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(p.d1, p.d2, p.obs_idx, w.th1, w.thd, B,
-                                                                            N, p.n_obs);
+    if (!naturals_ready) {
+        prof_mark(VDP_PHASE_SITES_TO_NAT, st);
+        k_ssm_to_naturals<D><<<grid_for(B * (N + 1), kPtBlock), kPtBlock, 0, st>>>(
+            p.pA, p.pb, p.pcholQ, p.pmu0, p.pcholP0, p.g1, p.gd, p.gs, w.th1, w.thd, w.ths, B, N);
         VDP_CHECK_LAUNCH();
+        if (p.n_obs > 0) {
+            k_scatter_data<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(p.d1, p.d2, p.obs_idx, w.th1,
+                                                                                w.thd, B, N, p.n_obs);
+            VDP_CHECK_LAUNCH();
+        }
     }
     const SegScratch sc(w.seg, kSegScratchBytes);
     int rc = run_nat2ssm<D>(w.th1, w.thd, w.ths, p.qA, p.qb, p.qcholQ, p.qmu0, p.qcholP0, w.Ld, w.Ls, B, N, p.status,
@@ -136,12 +140,20 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
                                                                             N, p.n_obs);
         VDP_CHECK_LAUNCH();
     }
+    // whole-chain update: the kernel also writes the naturals of the posterior that follows (no second pass over
+    // the sites); the sharded quadrature exchanges site ranges first and rebuilds from the sites
+    const bool fuse_nat = (node1 < 0) && !stop_after_sites && !env_int("VDP_NO_FUSED_NATURALS", 0);
+    KlNaturalsOut nat;
+    if (fuse_nat) {
+        nat.pA = p.pA; nat.pb = p.pb; nat.pcholQ = p.pcholQ; nat.pmu0 = p.pmu0; nat.pcholP0 = p.pcholP0;
+        nat.th1 = w.th1; nat.thd = w.thd; nat.ths = w.ths;
+    }
     if ((rc = launch_kl_grad<DRIFT, D>(P, p.q, p.dt, p.time_grid, p.x0_mu, p.x0_cov, p.qA, p.fx_mus, p.fx_covs,
-                                       w.terms, p.g1, p.gd, p.gs, 1, p.lr_girsanov, w.sc1, w.scd, B, N, p.status,
-                                       st, node0, node1)))
+                                       nullptr, p.g1, p.gd, p.gs, 1, p.lr_girsanov, w.sc1, w.scd, B, N, p.status,
+                                       st, node0, node1, nat)))
         return rc;
     if (stop_after_sites) { prof_mark(VDP_PHASE_END, st); return VDP_OK; }
-    if ((rc = run_posterior<D>(p, w, st))) return rc;
+    if ((rc = run_posterior<D>(p, w, st, fuse_nat))) return rc;
     // (C) classic_elbo  variational_cvi_sde.py:339-352
     if (!(p.flags & VDP_FLAG_SKIP_ELBO)) return run_elbo<DRIFT, D>(p, w, P, st);
     return VDP_OK;
