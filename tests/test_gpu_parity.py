@@ -436,3 +436,27 @@ def test_euler_maruyama_philox_statistics(ops):
     # a sequence's path does not depend on the batch it is simulated in
     sub = ops.euler_maruyama(S.DRIFT_OU, [decay], np.ones((1, 1)), x0[:100].contiguous(), grid, seed=11)
     assert torch.equal(sub, a[:100])
+
+
+def test_fused_naturals_equal_separate_pass(monkeypatch):
+    """The girsanov-update kernel emits the naturals of the posterior that follows; with VDP_NO_FUSED_NATURALS the
+    rebuild makes its own pass over the sites (k_ssm_to_naturals + scatter).  Same statements, same state."""
+    from oracle.sde_np import DRIFT_DW
+    from vi_diffusion_processes_b200.cvi import CviEngine
+    rng = np.random.default_rng(5)
+    N, B, n_obs = 700, 3, 9
+    grid = np.round(np.arange(N + 1) * 0.005, 3)
+    idx = np.sort(np.stack([rng.choice(N + 1, n_obs, replace=False) for _ in range(B)]), axis=1)
+    idx[0, 0], idx[1, -1] = 0, N                      # first and last grid point observed
+    y = rng.normal(size=(B, n_obs, 1)) * 0.3 + 1.0
+    mk = lambda: CviEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]])
+    a, c = mk(), mk()
+    for _ in range(3):
+        ea = a.site_update(0.5, 0.5).clone()
+    monkeypatch.setenv("VDP_NO_FUSED_NATURALS", "1")
+    for _ in range(3):
+        ec = c.site_update(0.5, 0.5).clone()
+    for name in ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs"):
+        ref = getattr(c, name)
+        assert (getattr(a, name) - ref).abs().max() <= 1e-12 * ref.abs().max(), name
+    assert (ea - ec).abs().max() <= 1e-12 * ec.abs().max()

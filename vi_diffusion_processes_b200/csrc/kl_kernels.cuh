@@ -292,6 +292,8 @@ struct KlNaturalsOut {
     double *th1 = nullptr, *thd = nullptr, *ths = nullptr;
 };
 
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // shared-memory record handed from the group of node i to the group of node i+1
 template <int D>
 struct KlHandoff { double gm[D]; double gS[D * D]; };
@@ -330,6 +332,20 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
     Vec<D> mk = vec_zero<D>();
     Mat<D> Sk = mat_eye<D>();
     if (in_range) { mk = vec_load<D>(m + i * D); Sk = mat_load<D>(Sd + i * DD); }
+    if (upd && in_range && lane == 0 && gidx != 0) {
+        // the site update at the end of the kernel reads the sites, the scattered data sites and (for the fused
+        // naturals) the prior: start those lines on their way now, the quadrature hides the latency
+        const int64_t tt = b * N + k;
+        prefetch_l2(g1 + i * D);
+        prefetch_l2(gd + i * DD);
+        if (k < N) prefetch_l2(gs + tt * DD);
+        if (sc1) { prefetch_l2(sc1 + i * D); prefetch_l2(scd + i * DD); }
+        if (nat.th1 && k < N) {
+            prefetch_l2(nat.pA + tt * DD);
+            prefetch_l2(nat.pb + tt * D);
+            prefetch_l2(nat.pcholQ + tt * DD);
+        }
+    }
     if (has_term) {
         const Vec<D> mn = vec_load<D>(m + (i + 1) * D);
         const Mat<D> Sn = mat_load<D>(Sd + (i + 1) * DD);

@@ -44,6 +44,13 @@ __device__ __forceinline__ void stage_scale(double* __restrict__ s, int64_t coun
     if (scale == 1.0) return;
     for (int64_t i = threadIdx.x; i < count; i += T) s[i] = scale * s[i];
 }
+// start the lines of [g, g + count) on their way to L2 (the next tile of this CTA: its cp.async loads then find them
+// there instead of in HBM); one 128-byte line per call
+template <int T>
+__device__ __forceinline__ void prefetch_range(const double* __restrict__ g, int64_t count) {
+    for (int64_t i = (int64_t)threadIdx.x * 16; i < count; i += (int64_t)T * 16)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(g + i));
+}
 template <int T>
 __device__ __forceinline__ void stage_out(double* __restrict__ g, const double* __restrict__ s, int64_t count) {
     for (int64_t i = threadIdx.x; i < count; i += T) g[i] = s[i];
@@ -211,6 +218,11 @@ k_chol_tiled(const double* __restrict__ Xd, const double* __restrict__ Xs, doubl
         stage_scale<T>(sKd, (int64_t)(cnt + 1) * DD, scaleD);
         stage_scale<T>(sKs, (int64_t)cnt * DD, scaleS);
         __syncthreads();
+        if (tk + TL < t1) {
+            const int64_t nxt = min((int64_t)TL, t1 - (tk + TL));
+            prefetch_range<T>(xd + (tk + TL + 1) * DD, nxt * DD);
+            prefetch_range<T>(xs + (tk + TL) * DD, nxt * DD);
+        }
         if (seg == 0 && tk == 0 && first) {
             S_tile = mat_load<D>(sKd);
             if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = S_tile;
@@ -412,6 +424,11 @@ k_invband_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, do
         stage_in<T>(sLs, Ls + (b * N + lo) * DD, (int64_t)cnt * DD);
         stage_wait();
         __syncthreads();
+        if (lo > t0) {
+            const int64_t nlo = max(t0, lo - TL);
+            prefetch_range<T>(Ld + (b * (N + 1) + nlo) * DD, (lo - nlo) * DD);
+            prefetch_range<T>(Ls + (b * N + nlo) * DD, (lo - nlo) * DD);
+        }
         const BwdChunk ch = bwd_chunk<L>(cnt);
         const AffSymElem<D> e = invband_tile_summary<D>(sLd, sLs, ch);
         AffSymElem<D> total;
@@ -519,6 +536,12 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
         }
         stage_wait();
         __syncthreads();
+        if (lo > t0) {
+            const int64_t nlo = max(t0, lo - TL);
+            prefetch_range<T>(Ld + (b * n + nlo) * DD, (lo - nlo) * DD);
+            prefetch_range<T>(Ls + (b * N + nlo) * DD, (lo - nlo) * DD);
+            if (MODE != SWEEP_SUMMARY) prefetch_range<T>(th1 + (b * n + nlo) * D, (lo - nlo) * D);
+        }
         const BwdChunk ch = bwd_chunk<L>(cnt);
         // FROML: L_{bot,bot-1}, the block below this thread's chunk (the neighbour overwrites it in its recursion)
         Mat<D> Lbelow = mat_zero<D>();
