@@ -460,3 +460,40 @@ def test_fused_naturals_equal_separate_pass(monkeypatch):
         ref = getattr(c, name)
         assert (getattr(a, name) - ref).abs().max() <= 1e-12 * ref.abs().max(), name
     assert (ea - ec).abs().max() <= 1e-12 * ec.abs().max()
+
+
+def test_cuda_graph_replay_equals_direct_calls():
+    """site_update_graphed / sweep_graphed (CUDA-graph replay for launch-bound single sequences) leave bitwise the
+    state of the direct calls, across a re-linearisation (buffers replaced -> re-capture) and a step-size change."""
+    from oracle.sde_np import DRIFT_DW
+    from vi_diffusion_processes_b200.cvi import CviEngine
+    from vi_diffusion_processes_b200.vgp import VgpEngine
+    rng = np.random.default_rng(8)
+    N, n_obs = 600, 12
+    grid = np.round(np.arange(N + 1) * 0.005, 3)
+    idx = np.sort(rng.choice(N + 1, n_obs, replace=False))[None]
+    y = rng.normal(size=(1, n_obs, 1)) * 0.3 + 1.0
+    mk = lambda: CviEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]])
+    a, b = mk(), mk()
+    for it in range(6):
+        lr = 0.5 if it < 4 else 0.25
+        ea = a.site_update(lr, lr).clone()
+        eb = b.site_update_graphed(lr, lr).clone()
+        assert torch.equal(ea, eb), it
+        if it == 2:
+            a.relinearize()
+            b.relinearize()
+    for name in ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs"):
+        assert torch.equal(getattr(a, name), getattr(b, name)), name
+    b.check_status()
+    mv = lambda: VgpEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]])
+    c, d = mv(), mv()
+    for e in (c, d):
+        e.A += 2.0
+        e.b += 2.0
+    for it in range(5):
+        ec = c.sweep(0.1, update_x0=it > 1).clone()
+        ed = d.sweep_graphed(0.1, update_x0=it > 1).clone()
+        assert torch.equal(ec, ed), it
+    for name in ("A", "b", "lambda_lagrange", "psi_lagrange", "q_initial_mean", "q_initial_chol", "m", "S"):
+        assert torch.equal(getattr(c, name), getattr(d, name)), name

@@ -129,6 +129,36 @@ class CviEngine:
         check(_lib.load().vdp_cvi_site_update(C.byref(p), self._stream()), "vdp_cvi_site_update")
         return self.elbo
 
+    _PTR_FIELDS = ("time_grid", "pA", "pb", "pcholQ", "pmu0", "pcholP0", "g1", "gd", "gs", "d1", "d2", "obs_idx", "obs_y",
+                   "fx_mus", "fx_covs", "qA", "qb", "qcholQ", "qmu0", "qcholP0", "elbo", "ve", "kl", "status")
+
+    def site_update_graphed(self, lr_data, lr_girsanov, flags=0):
+        """
+        The same update replayed from a CUDA graph: for one or a few short sequences (the reference's own configs:
+        N = 500..4000, B = 1) an update is ~20 launches of a few microseconds each, i.e. launch-bound; the graph
+        removes the per-launch host cost.  The graph is captured on first use and re-captured whenever a buffer of
+        the problem has been replaced (re-linearisation, site assignment) or the step sizes / drift parameters change.
+        """
+        key = (float(lr_data), float(lr_girsanov), int(flags), tuple(self.drift_params),
+               tuple(getattr(self, n).data_ptr() for n in self._PTR_FIELDS))
+        cache = getattr(self, "_graphs", None)
+        if cache is None:
+            cache = self._graphs = {}
+        g = cache.get(key)
+        if g is None:
+            if len(cache) >= 8:
+                cache.clear()
+            state = [getattr(self, n).clone() for n in ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs")]
+            self.site_update(lr_data, lr_girsanov, flags)          # warm-up outside the capture (attribute setup),
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.site_update(lr_data, lr_girsanov, flags)
+            for n, t in zip(("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs"), state):
+                getattr(self, n).copy_(t)                          # ... whose effect is undone: the replay below is
+            cache[key] = g                                         # the one update of this call
+        g.replay()
+        return self.elbo
+
     def site_update_sharded(self, phase, node_begin, node_end, lr_data=0.0, lr_girsanov=0.0):
         """One phase of ``vdp_cvi_site_update_sharded`` on the flat node range [node_begin, node_end)."""
         p = self._problem(lr_data, lr_girsanov)

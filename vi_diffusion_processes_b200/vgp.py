@@ -130,6 +130,32 @@ class VgpEngine:
         return ops.drift_param_grad(self.drift_id, self.drift_params, self.q, 1.0, 0.0, 1.0, -1.0, self.dt, self.A,
                                     self.b, m, S, point_offset=1, status=self.status)
 
+    def sweep_graphed(self, lr, update_x0=False, x0_lr=0.1):
+        """:meth:`sweep` replayed from a CUDA graph (launch-bound for single short sequences, see
+        ``CviEngine.site_update_graphed``); re-captured when a buffer, a step size or a drift parameter changes."""
+        names = ("time_grid", "A", "b", "lambda_lagrange", "psi_lagrange", "q_initial_mean", "q_initial_chol",
+                 "obs_idx", "obs_y", "m", "S", "elbo_value", "status")
+        key = (float(lr), bool(update_x0), float(x0_lr), tuple(self.drift_params), tuple(self.x0_mu.tolist()),
+               tuple(self.x0_cov.reshape(-1).tolist()), tuple(getattr(self, n).data_ptr() for n in names))
+        cache = getattr(self, "_graphs", None)
+        if cache is None:
+            cache = self._graphs = {}
+        g = cache.get(key)
+        if g is None:
+            if len(cache) >= 8:
+                cache.clear()
+            keep = ("A", "b", "lambda_lagrange", "psi_lagrange", "q_initial_mean", "q_initial_chol", "m", "S")
+            state = [getattr(self, n).clone() for n in keep]
+            self.sweep(lr, update_x0=update_x0, x0_lr=x0_lr)      # warm-up outside the capture, undone below
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.sweep(lr, update_x0=update_x0, x0_lr=x0_lr)
+            for n, t in zip(keep, state):
+                getattr(self, n).copy_(t)
+            cache[key] = g
+        g.replay()
+        return self.elbo_value
+
     def check_status(self):
         code, idx = ops.read_status(self.status)
         if code != 0:
