@@ -184,7 +184,7 @@ def run_ours(args):
     import ctypes as C
     import torch
     import torch.distributed as dist
-    from oracle.sde_np import DRIFT_DW
+    from vi_diffusion_processes_b200.markovflow.sde.sde import DRIFT_DW
     from vi_diffusion_processes_b200 import _lib
     from vi_diffusion_processes_b200.cvi import CviEngine
 
@@ -340,7 +340,7 @@ def run_ours(args):
 def run_vdp(args):
     """Second line of SURVEY 8(d): one VDP fixed-point sweep (vi_markov_gp_trainer.py:62-73) on the C4 shape."""
     import torch
-    from oracle.sde_np import DRIFT_DW
+    from vi_diffusion_processes_b200.markovflow.sde.sde import DRIFT_DW
     from vi_diffusion_processes_b200.vgp import VgpEngine
     torch.cuda.set_device(0)
     B, N = args.seqs, args.grid

@@ -3,7 +3,7 @@ import sys, time
 import numpy as np, torch
 sys.path.insert(0, ".")
 import bench
-from oracle.sde_np import DRIFT_DW
+DRIFT_DW = 1   # VDP_DRIFT_DW (include/vdp_b200.h)
 from vi_diffusion_processes_b200.cvi import CviEngine, CviHostEngine
 
 B, N = 4096, 10000

@@ -4,7 +4,7 @@ import numpy as np
 import torch
 sys.path.insert(0, ".")
 from bench import make_problem, DW_PARAMS, NOISE_STD, X0_MU, X0_COV, LR
-from oracle.sde_np import DRIFT_DW
+DRIFT_DW = 1   # VDP_DRIFT_DW (include/vdp_b200.h)
 from vi_diffusion_processes_b200.cvi import CviEngine
 
 B, N = 4096, 10000
