@@ -162,17 +162,21 @@ def cpu_c_steps_per_s(B, N, seed, updates, threads):
 # read + written once; bytes = 8 * (v * D + M * D^2).  Stated per kernel in DESIGN.md section 4.
 PHASE_TRAFFIC = {
     "data_sites": (0, 0),
-    "sites_to_nat": (2 + 1, 4 + 2),   # read b, g1 | A, cholQ, gd, gs ; write th1 | thd, ths
+    # consecutive updates carry the naturals of the previous update in the workspace and rewrite them at the observed
+    # grid points only (VDP_FLAG_NATURALS_CARRIED): O(n_obs) per sequence instead of a pass over the grid
+    "sites_to_nat": (0, 0),
     "chol_fwd": (0, 2 + 2),           # read thd, ths ; write Ld, Ls
     "nat2ssm_bwd": (1 + 1, 2 + 2),    # read th1 | Ld, Ls ; write b | A, cholQ (K blocks rebuilt from L in the tile)
     "marg_fwd": (1 + 1, 2 + 2),       # read b | A, cholQ ; write m | Ld, Ls
     "invband_bwd": (0, 2 + 1),        # read Ld, Ls ; write Sd
-    # read m, g1, sc1, prior b | A, S, gd, gs, scd, prior A, cholQ ; write g1, th1 | gd, gs, thd, ths (+ memset sc):
-    # the kernel also emits the naturals of the posterior that follows (no second k_ssm_to_naturals pass)
-    "kl_grad": (1 + 1 + 1 + 1 + 1 + 1 + 1, 2 + 2 + 1 + 2 + 1 + 2 + 2),
+    # read m, g1, sc1, prior b | A, S, gd, gs, scd, prior A, cholQ ; write g1, th1 | gd, gs, thd, ths: the kernel
+    # also emits the naturals of the posterior that follows (no second k_ssm_to_naturals pass); the dense copy of the
+    # data sites (sc) is carried between updates like the naturals (no memset)
+    "kl_grad": (1 + 1 + 1 + 1 + 1 + 1, 2 + 2 + 1 + 2 + 1 + 2 + 1),
     "elbo": (2, 3),                   # read b, m | A, cholQ, S
 }
-LAUNCHES_PER_UPDATE = 1 + 6 + 2 + 4 + 4   # kernels of ours in one vdp_cvi_site_update (second rebuild: 4 sweeps)
+LAUNCHES_PER_UPDATE = 1 + 5 + 1 + 4 + 4   # kernels of ours in one vdp_cvi_site_update in steady state (data sites,
+#                                           patch + 4 sweeps, kl_grad, 4 sweeps, VE + KL value + reduce + combine)
 
 
 def phase_bytes_per_step(name, D):
@@ -255,6 +259,13 @@ def run_ours(args):
     ph_n = (C.c_int64 * nph)()
     lib.vdp_profile_read(ph_ms, ph_n, nph)    # covers warm-up + timed steps: averages per launch below
     lib.vdp_profile_enable(0)
+    # the same update with the 20-point Gauss-Hermite loops instead of their closed form (polynomial drift), and with
+    # the naturals recomputed over the whole grid every update: reported beside the headline, not part of it
+    os.environ["VDP_GH_QUADRATURE"] = "1"
+    ms_gh = timed(step_resident, args.steps, 1)
+    os.environ["VDP_NO_CARRIED_NATURALS"] = "1"
+    ms_gh_full = timed(step_resident, args.steps, 1)
+    del os.environ["VDP_GH_QUADRATURE"], os.environ["VDP_NO_CARRIED_NATURALS"]
     # nvidia-smi samples every 100 ms: keep the same load running (untimed) until at least ~0.6 s have been sampled
     while time.perf_counter() - t_load < 0.6:
         step_resident()
@@ -263,7 +274,8 @@ def run_ours(args):
     eng.check_status()
     if args.quick:
         if rank == 0:
-            print(json.dumps({"ms_per_step": ms_total / args.steps, "phases": {
+            print(json.dumps({"ms_per_step": ms_total / args.steps, "ms_per_step_gh_loops": ms_gh / args.steps,
+                              "ms_per_step_gh_loops_no_carry": ms_gh_full / args.steps, "phases": {
                 nm: {"ms_per_launch": ph_ms[i] / max(1, ph_n[i])} for i, nm in enumerate(_lib.PHASES)}}))
         if world > 1:
             dist.destroy_process_group()
@@ -306,9 +318,16 @@ def run_ours(args):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "C4: independent double-well sequences x dense grid, one CVI-DP site update per step",
                    "sequences_per_gpu": B, "grid_steps": N, "state_dim": D, "dt": DT, "n_obs": N_OBS, "quad_H": 20,
+                   "quadrature": "double-well drift is a cubic: the 20-point Gauss-Hermite sums are taken in closed "
+                                 "form (central Gaussian moments, equal to rounding); variants has the loops",
                    "parallelism": f"sequence-sharded x{world}, no data-path collective",
                    "l2": "working set per step (~%.1f GB) exceeds the 126 MB L2" % (B * N * 8 * 30 / 1e9)},
         "clocks": clocks,
+        "variants": {"gh20_loops": {"ms_per_step": ms_gh / args.steps,
+                                    "value": steps_total * args.steps / (ms_gh * 1e-3)},
+                     "gh20_loops_naturals_recomputed_every_update": {
+                         "ms_per_step": ms_gh_full / args.steps,
+                         "value": steps_total * args.steps / (ms_gh_full * 1e-3)}},
         "e2e": {"value": e2e_value, "unit": "grid-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / e2e_steps, "api": "vdp_cvi_host_site_update (C ABI, pinned host buffers, "
                 "%d-sequence chunks on 3 streams)" % min(args.chunk, B)},

@@ -209,6 +209,14 @@ typedef struct vdp_cvi_problem {
 #define VDP_FLAG_SKIP_ELBO 2          /* do not evaluate classic_elbo */
 #define VDP_FLAG_SKIP_GIRSANOV 4      /* update_data_sites only (variational_cvi_sde.py:301-317) */
 #define VDP_FLAG_POSTERIOR_SSM_ONLY 8 /* vdp_cvi_elbo: only rebuild q as an SSM from the sites (dist_q, :176-192) */
+#define VDP_FLAG_NATURALS_CARRIED 16  /* vdp_cvi_site_update: the caller's promise that (1) the previous call that used
+                                         this workspace was a whole-chain vdp_cvi_site_update of this problem that ran
+                                         the girsanov update (no VDP_FLAG_SKIP_GIRSANOV) or itself carried, and (2)
+                                         prior, girsanov sites, data sites and observation indices are as that call
+                                         left them.  The natural parameters and the dense copy of the data sites it
+                                         left in the workspace are then rewritten at the observed grid points only
+                                         instead of over the whole grid (same resulting state; honoured for
+                                         n_obs <= 128, ignored otherwise) */
 
 size_t vdp_cvi_workspace(int64_t B, int64_t N, int D, int64_t n_obs);
 int vdp_cvi_site_update(const vdp_cvi_problem* problem_host, void* stream);

@@ -462,6 +462,104 @@ def test_fused_naturals_equal_separate_pass(monkeypatch):
     assert (ea - ec).abs().max() <= 1e-12 * ec.abs().max()
 
 
+def test_carried_naturals_equal_full_pass():
+    """Consecutive site updates patch the naturals left in the workspace at the observed grid points
+    (VDP_FLAG_NATURALS_CARRIED); an engine that recomputes them over the whole grid every time ends in bitwise the
+    same state -- across a re-linearisation, an in-place edit of the sites through torch, an ELBO call in between
+    and data-sites-only updates (carried, and not carried: that one leaves no dense data-site copy to carry on)."""
+    from vi_diffusion_processes_b200 import _lib
+    from vi_diffusion_processes_b200.markovflow.sde.sde import DRIFT_DW
+    from vi_diffusion_processes_b200.cvi import CviEngine
+    rng = np.random.default_rng(21)
+    N, B, n_obs = 900, 3, 11
+    grid = np.round(np.arange(N + 1) * 0.005, 3)
+    idx = np.sort(np.stack([rng.choice(N + 1, n_obs, replace=False) for _ in range(B)]), axis=1)
+    idx[0, 0], idx[1, -1] = 0, N
+    y = rng.normal(size=(B, n_obs, 1)) * 0.3 + 1.0
+    mk = lambda carry: CviEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]],
+                                 carry_naturals=carry)
+    a, c = mk(True), mk(False)
+    carried = []
+    for it in range(12):
+        for e in (a, c):
+            if it == 3:
+                e.relinearize()
+            if it == 5:
+                e.g1.mul_(0.999)
+            if it in (6, 9):
+                e.classic_elbo()
+        carried.append(a._nat_sig is not None and a._nat_sig == a._nat_signature())
+        flags = _lib.FLAG_SKIP_GIRSANOV if it in (7, 9) else 0
+        ea = a.site_update(0.4, 0.4, flags).clone()
+        ec = c.site_update(0.4, 0.4, flags).clone()
+        assert torch.equal(ea, ec), it
+    a.check_status()
+    assert carried == [False, True, True, False, True, False, False, True, True, False, False, True]
+    for name in ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs", "qA", "qb", "qcholQ"):
+        assert torch.equal(getattr(a, name), getattr(c, name)), name
+
+
+def test_carried_naturals_repeated_observation_points():
+    """Two observations on one grid point add up (tf.scatter_nd); the carried path sums them in entry order, the
+    scatter in arrival order: equal up to that rounding (amplified by the cancellation in the sites over 4 updates)."""
+    from vi_diffusion_processes_b200.markovflow.sde.sde import DRIFT_DW
+    from vi_diffusion_processes_b200.cvi import CviEngine
+    rng = np.random.default_rng(22)
+    N, B, n_obs = 400, 2, 8
+    grid = np.round(np.arange(N + 1) * 0.005, 3)
+    idx = np.sort(np.stack([rng.choice(N + 1, n_obs, replace=False) for _ in range(B)]), axis=1)
+    idx[0, 3] = idx[0, 4]
+    idx[1, 0] = idx[1, 1] = 0
+    y = rng.normal(size=(B, n_obs, 1)) * 0.3 + 1.0
+    mk = lambda carry: CviEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]],
+                                 carry_naturals=carry)
+    a, c = mk(True), mk(False)
+    for _ in range(4):
+        ea, ec = a.site_update(0.5, 0.5), c.site_update(0.5, 0.5)
+    a.check_status()
+    for name in ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs"):
+        ref = getattr(c, name)
+        assert (getattr(a, name) - ref).abs().max() <= 1e-10 * ref.abs().max(), name
+    assert (ea - ec).abs().max() <= 1e-10 * ec.abs().max()
+
+
+@pytest.mark.parametrize("drift,params,noise", [("dw", [4.0, 1.0], 0.1), ("dw", [2.5, 0.7], 1e-3), ("ou", [0.8], 0.05)])
+def test_closed_form_moments_equal_gauss_hermite(monkeypatch, drift, params, noise):
+    """For polynomial scalar drifts the 20-point Gauss-Hermite sums of the KL term and of its gradient are taken in
+    closed form (central Gaussian moments; the rule is exact for these integrands).  VDP_GH_QUADRATURE=1 runs the
+    quadrature loops: same sites, marginals and ELBO to rounding, also with a small observation noise (posterior
+    variances of 1e-6 next to the observations, where an expansion about zero instead of the mean would cancel)."""
+    from vi_diffusion_processes_b200.markovflow.sde import sde as sde_mod
+    from vi_diffusion_processes_b200.cvi import CviEngine
+    did = {"dw": sde_mod.DRIFT_DW, "ou": sde_mod.DRIFT_OU}[drift]
+    rng = np.random.default_rng(33)
+    N, B, n_obs = 800, 4, 10
+    grid = np.round(np.arange(N + 1) * 0.005, 3)
+    idx = np.sort(np.stack([rng.choice(N + 1, n_obs, replace=False) for _ in range(B)]), axis=1)
+    y = rng.normal(size=(B, n_obs, 1)) * 0.3 + np.array([1.0, -1.0, 0.2, 1.4])[:, None, None]
+    mk = lambda: CviEngine(did, params, np.ones((1, 1)), grid, idx, y, [[noise]], [1.0], [[1e-2]])
+    a, c = mk(), mk()
+    ea, ec = [], []
+    for it in range(4):
+        if it == 2:
+            a.relinearize()
+        ea.append(a.site_update(0.5, 0.5).clone())
+    monkeypatch.setenv("VDP_GH_QUADRATURE", "1")
+    for it in range(4):
+        if it == 2:
+            c.relinearize()
+        ec.append(c.site_update(0.5, 0.5).clone())
+    a.check_status()
+    c.check_status()
+    th = c._prior_naturals(c.pA, c.pb)
+    for name, prior in (("g1", th[0]), ("gd", th[1]), ("gs", th[2]), ("fx_mus", None), ("fx_covs", None)):
+        ref = getattr(c, name)
+        scale = ref.abs().max() if prior is None else (ref + prior).abs().max()
+        assert (getattr(a, name) - ref).abs().max() <= 1e-11 * scale, name
+    for x, r in zip(ea, ec):
+        assert (x - r).abs().max() <= 1e-11 * r.abs().max()
+
+
 def test_cuda_graph_replay_equals_direct_calls():
     """site_update_graphed / sweep_graphed (CUDA-graph replay for launch-bound single sequences) leave bitwise the
     state of the direct calls, across a re-linearisation (buffers replaced -> re-capture) and a step-size change."""

@@ -89,6 +89,7 @@ class DistSweep(C.Structure):
 
 SWEEP_CHOL, SWEEP_NAT2SSM, SWEEP_MARG, SWEEP_INVBAND = 0, 1, 2, 3
 FLAG_SKIP_DATA_UPDATE, FLAG_SKIP_ELBO, FLAG_SKIP_GIRSANOV, FLAG_POSTERIOR_SSM_ONLY = 1, 2, 4, 8
+FLAG_NATURALS_CARRIED = 16
 VGP_STABILIZE = 1
 VGP_UPDATE_X0 = 2
 

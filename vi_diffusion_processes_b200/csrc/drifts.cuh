@@ -126,7 +126,10 @@ template <> struct Drift<DRIFT_LORENZ63, 3> {
 // from per-transition constants prepared once outside the node loop.  The generic form calls the drift functor;
 // polynomial drifts collapse to a Horner form (DW: d = x (k1 - a x^2) - b, j = k1 - 3 a x^2 with a = dt s,
 // k1 = 1 + a c - A: 4 float64 instructions per node instead of 9).
+// kCubic: d is a polynomial of degree <= 3 in x; taylor() returns its coefficients about m,
+// d(m + e) = c0 + c1 e + c2 e^2 + c3 e^3, for the closed-form Gaussian expectations (CubicMoments).
 template <int ID> struct DriftStep1 {
+    static constexpr bool kCubic = false;
     struct K { double omA, nb, dt; };
     static __device__ __forceinline__ K prepare(const DriftParams&, double dt, double A, double b) {
         K k;
@@ -143,7 +146,16 @@ template <int ID> struct DriftStep1 {
     }
 };
 template <> struct DriftStep1<DRIFT_DW> {
+    static constexpr bool kCubic = true;
     struct K { double k1, na, na3, nb; };
+    static __device__ __forceinline__ void taylor(const K& k, double m, double& c0, double& c1, double& c2,
+                                                  double& c3) {
+        const double m2 = m * m;
+        c0 = fma(m, fma(k.na, m2, k.k1), k.nb);
+        c1 = fma(k.na3, m2, k.k1);
+        c2 = k.na3 * m;
+        c3 = k.na;
+    }
     static __device__ __forceinline__ K prepare(const DriftParams& P, double dt, double A, double b) {
         K k;
         const double a = dt * P.p[0];
@@ -157,7 +169,15 @@ template <> struct DriftStep1<DRIFT_DW> {
     }
 };
 template <> struct DriftStep1<DRIFT_OU> {
+    static constexpr bool kCubic = true;
     struct K { double k1, nb; };
+    static __device__ __forceinline__ void taylor(const K& k, double m, double& c0, double& c1, double& c2,
+                                                  double& c3) {
+        c0 = fma(k.k1, m, k.nb);
+        c1 = k.k1;
+        c2 = 0.0;
+        c3 = 0.0;
+    }
     static __device__ __forceinline__ K prepare(const DriftParams& P, double dt, double A, double b) {
         K k;
         k.k1 = fma(-dt, P.p[0], 1.0 - A); k.nb = -b;
@@ -169,6 +189,27 @@ template <> struct DriftStep1<DRIFT_OU> {
     }
 };
 template <> struct DriftStep1<DRIFT_OU_ND> : DriftStep1<DRIFT_OU> {};
+
+// Expectations over x = m + e, e ~ N(0, S), of a cubic d(x) = c0 + c1 e + c2 e^2 + c3 e^3, its slope j = d' and their
+// products, from the central moments E e^2 = S, E e^4 = 3 S^2, E e^6 = 15 S^3.  An H-point Gauss-Hermite rule
+// integrates polynomials up to degree 2H - 1 exactly, so for a polynomial drift these are the values the reference's
+// 20-point rule (sde_utils.py:317-330) returns, up to rounding; expanding about m keeps the cancellation of the
+// quadrature sums (d is the residual of a linearisation about m) and no more.
+struct CubicMoments {
+    double Ed, Ed2, Ede, Ejd, Ejde;   // E d, E d^2, E d e, E j d, E j d e
+    template <bool GRAD>
+    __device__ __forceinline__ void eval(double c0, double c1, double c2, double c3, double S) {
+        const double E4 = 3.0 * (S * S), E6 = 5.0 * (E4 * S);
+        const double c11 = c1 * c1, c02 = c0 * c2, c13 = c1 * c3, c22 = c2 * c2, c33 = c3 * c3;
+        Ed2 = fma(c0, c0, fma(fma(2.0, c02, c11), S, fma(fma(2.0, c13, c22), E4, c33 * E6)));
+        if constexpr (GRAD) {
+            Ed = fma(c2, S, c0);
+            Ede = fma(c1, S, c3 * E4);
+            Ejd = fma(c0, c1, fma(3.0 * fma(c1, c2, c0 * c3), S, 5.0 * ((c2 * c3) * E4)));
+            Ejde = fma(fma(2.0, c02, c11), S, fma(2.0 * fma(2.0, c13, c22), E4, 3.0 * (c33 * E6)));
+        }
+    }
+};
 
 // Derivatives of f and J with respect to every entry of the parameter block: what a tape watching
 // prior_sde.trainable_variables propagates through drift / gradient_drift (prior-parameter learning,

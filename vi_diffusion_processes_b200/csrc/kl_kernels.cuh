@@ -33,7 +33,7 @@ struct KlTermOut {
 // hoisted out of the node loop, pi^(-1/2) and sqrt(2) are factored out of the sums, and each of the
 // three divisors (chol S_k, chol Q_c, chol Q_p) is inverted once (3 sqrt + 3 div + 1 log per step
 // instead of ~20 div/sqrt/log).  Results differ from the generic path in the last bits only.
-template <int DRIFT, int H>
+template <int DRIFT, int H, bool CLOSED = false>
 __device__ __forceinline__ void kl_term_scalar(const DriftParams& P, double Qp, double dt, double pi_factor,
                                                double mk, double mn, double edk, double edn, double esk,
                                                KlTermOut<1>& out, bool& ok, bool want_value = true) {
@@ -61,6 +61,18 @@ __device__ __forceinline__ void kl_term_scalar(const DriftParams& P, double Qp, 
     // d = x + dt f(x) - (A x + b) and its slope j (DriftStep1);  Q_p^-1 and pi^(-1/2) are factored out of the sums
     const typename DriftStep1<DRIFT>::K kst = DriftStep1<DRIFT>::prepare(P, dt, A, b);
     double quad = 0.0, gb = 0.0, gmq = 0.0, gA = 0.0, lsb = 0.0;
+    if constexpr (CLOSED) {
+        // polynomial drift: the Gauss-Hermite sums in closed form (CubicMoments)
+        double c0, c1, c2, c3;
+        DriftStep1<DRIFT>::taylor(kst, mk, c0, c1, c2, c3);
+        CubicMoments cm;
+        cm.template eval<true>(c0, c1, c2, c3, Sk);
+        quad = Qpinv * cm.Ed2;
+        gb = -Qpinv * cm.Ed;
+        gmq = Qpinv * cm.Ejd;
+        gA = -Qpinv * fma(mk, cm.Ed, cm.Ede);
+        lsb = (Qpinv * cm.Ejde) * iLS;
+    } else {
 #pragma unroll
     for (int p = 0; p < H; ++p) {
         const double xi = gh_x<H>(p), w = gh_w<H>(p);
@@ -81,6 +93,7 @@ __device__ __forceinline__ void kl_term_scalar(const DriftParams& P, double Qp, 
     gmq *= sc;
     gA *= sc;
     lsb *= 1.4142135623730951 * sc;
+    }
     out.value = 0.5 * (quad + Cterm);
     // reverse through the pointwise algebra
     double Lgm = gmq;
@@ -180,13 +193,13 @@ __device__ __forceinline__ void kl_quad_nested3(const DriftParams& P, const Mat<
 
 // One transition term.  Inputs are the expectation parameters rebuilt from (A_q, m, S) exactly as
 // ssm_to_expectations does (ssm_gaussian_transformations.py:32-89).
-template <int DRIFT, int D, int H, int G>
+template <int DRIFT, int D, int H, int G, bool CLOSED = false>
 __device__ __forceinline__ void kl_term(const DriftParams& P, const Mat<D>& Qp, double dt, double pi_factor,
                                         const Vec<D>& e1k, const Vec<D>& e1n, const Mat<D>& edk, const Mat<D>& edn,
                                         const Mat<D>& esk, int lane, KlTermOut<D>& out, bool& ok,
                                         bool want_value = true) {
     if constexpr (D == 1 && G == 1) {
-        kl_term_scalar<DRIFT, H>(P, Qp(0, 0), dt, pi_factor, e1k(0), e1n(0), edk(0, 0), edn(0, 0), esk(0, 0), out, ok,
+        kl_term_scalar<DRIFT, H, CLOSED>(P, Qp(0, 0), dt, pi_factor, e1k(0), e1n(0), edk(0, 0), edn(0, 0), esk(0, 0), out, ok,
                                  want_value);
         return;
     }
@@ -304,7 +317,7 @@ struct KlHandoff { double gm[D]; double gS[D * D]; };
 // variational_cvi_sde.py:286-296 is applied in place instead of writing the gradients:
 //   g1 += lr (scatter(d1) - dKL/deta1),  gd += lr (scatter(d2) - dKL/deta_d),  gs -= lr dKL/deta_s
 // where scatter(d.) has been pre-scattered into sc1/scd by the caller.
-template <int DRIFT, int D, int H, int G>
+template <int DRIFT, int D, int H, int G, bool CLOSED = false>
 __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double dt, double pi_factor,
                           const double* __restrict__ time_grid, Vec<D> x0_mu, Mat<D> x0_cov,
                           const double* __restrict__ Aq, const double* __restrict__ m,
@@ -354,7 +367,7 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
         const Mat<D> edn = Sn + outer(mn, mn);
         const Mat<D> esk = mm(Ak, Sk) + outer(mn, mk);
         const double delta = time_grid[k + 1] - time_grid[k];
-        kl_term<DRIFT, D, H, G>(P, delta * q, dt, pi_factor, mk, mn, edk, edn, esk, lane, t, ok, terms != nullptr);
+        kl_term<DRIFT, D, H, G, CLOSED>(P, delta * q, dt, pi_factor, mk, mn, edk, edn, esk, lane, t, ok, terms != nullptr);
         if (!ok && lane == 0) report_not_pd(status, i);
         if (lane == 0) {
 #pragma unroll
@@ -435,7 +448,7 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
 
 // KL_q_p of classic_elbo (variational_cvi_sde.py:446-486): value only, with the reference's
 // element-wise square of the Cholesky factor (:452) standing in for Q_q.
-template <int DRIFT, int D, int H, int G>
+template <int DRIFT, int D, int H, int G, bool CLOSED = false>
 __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
                            const double* __restrict__ Aq, const double* __restrict__ bq,
                            const double* __restrict__ cholQq, const double* __restrict__ m,
@@ -485,6 +498,13 @@ __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
     if constexpr (D == 1 && G == 1) {
         const double sL = 1.4142135623730951 * LS(0, 0), m1 = mk(0);
         const typename DriftStep1<DRIFT>::K kst = DriftStep1<DRIFT>::prepare(P, dt, Ak(0, 0), bk(0));
+        if constexpr (CLOSED) {
+            double c0, c1, c2, c3;
+            DriftStep1<DRIFT>::taylor(kst, m1, c0, c1, c2, c3);
+            CubicMoments cm;
+            cm.template eval<false>(c0, c1, c2, c3, Sd[i]);
+            quad = Qpinv(0, 0) * cm.Ed2;
+        } else {
         double quad_ = 0.0;
 #pragma unroll
         for (int p = 0; p < H; ++p) {
@@ -493,6 +513,7 @@ __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
             quad_ = fma(gh_w<H>(p) * d, d, quad_);
         }
         quad = (pi_factor * Qpinv(0, 0)) * quad_;
+        }
     } else {
     constexpr int NP = NodeCount<H, D>::value;
     constexpr bool kNested = (D == 3 && G == 32);

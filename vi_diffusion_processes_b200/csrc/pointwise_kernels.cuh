@@ -97,6 +97,53 @@ __global__ void k_scatter_data(const double* __restrict__ d1, const double* __re
     for (int e = 0; e < DD; ++e) atomicAdd(thd + node * DD + e, d2[i * DD + e]);
 }
 
+// The naturals theta of the previous site update are still in the workspace (VDP_FLAG_NATURALS_CARRIED) and only the
+// data sites have changed since: rewrite theta_1 / theta_d at the observed grid points, in the statement order of the
+// site-update kernel's epilogue ((nat(p) + g) + sum of the data sites at the node), and likewise the dense copy of the
+// data sites (sc1 / scd, zero away from the observations) that kernel reads.  One thread per observation entry; of
+// several entries on one grid point the first does the work.
+template <int D>
+__global__ void k_patch_naturals(const double* __restrict__ A, const double* __restrict__ bo,
+                                 const double* __restrict__ cholQ, const double* __restrict__ mu0,
+                                 const double* __restrict__ cholP0, const double* __restrict__ g1,
+                                 const double* __restrict__ gd, const double* __restrict__ d1,
+                                 const double* __restrict__ d2, const int64_t* __restrict__ obs_idx,
+                                 double* __restrict__ th1, double* __restrict__ thd, double* __restrict__ sc1,
+                                 double* __restrict__ scd, int64_t B, int64_t N, int64_t n_obs) {
+    const int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (o >= B * n_obs) return;
+    constexpr int DD = D * D;
+    const int64_t b = o / n_obs, j = o - b * n_obs;
+    const int64_t k = obs_idx[o];
+    if (k < 0 || k > N) return;
+    const int64_t* row = obs_idx + b * n_obs;
+    Vec<D> s1 = vec_zero<D>();
+    Mat<D> s2 = mat_zero<D>();
+    for (int64_t jj = 0; jj < n_obs; ++jj) {
+        if (row[jj] != k) continue;
+        if (jj < j) return;
+        s1 = s1 + vec_load<D>(d1 + (b * n_obs + jj) * D);
+        s2 = s2 + mat_load<D>(d2 + (b * n_obs + jj) * DD);
+    }
+    const int64_t i = b * (N + 1) + k, tt = b * N + k;
+    const Mat<D> ck = (k == 0) ? mat_load<D>(cholP0 + b * DD) : mat_load<D>(cholQ + (tt - 1) * DD);
+    const Vec<D> ok = (k == 0) ? vec_load<D>(mu0 + b * D) : vec_load<D>(bo + (tt - 1) * D);
+    Mat<D> Ak = mat_zero<D>(), cn = mat_eye<D>(), td, ts;
+    Vec<D> bn = vec_zero<D>(), t1;
+    if (k < N) {
+        Ak = mat_load<D>(A + tt * DD);
+        cn = mat_load<D>(cholQ + tt * DD);
+        bn = vec_load<D>(bo + tt * D);
+    }
+    ssm_node_naturals<D>(ck, ok, k < N, Ak, cn, bn, t1, td, ts);
+    t1 = t1 + vec_load<D>(g1 + i * D);
+    td = td + mat_load<D>(gd + i * DD);
+    vec_store<D>(th1 + i * D, t1 + s1);
+    mat_store<D>(thd + i * DD, td + s2);
+    vec_store<D>(sc1 + i * D, s1);
+    mat_store<D>(scd + i * DD, s2);
+}
+
 // ssm_to_expectations (ssm_gaussian_transformations.py:32-89)
 template <int D>
 __global__ void k_ssm_to_expectations(const double* __restrict__ A, const double* __restrict__ m,

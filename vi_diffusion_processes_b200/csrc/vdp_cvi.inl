@@ -21,6 +21,17 @@ static int launch_kl_grad(const DriftParams& P, const double* q_host, double dt,
     if (total <= 0) return VDP_OK;
     const unsigned grid = (unsigned)((total + KL::groups - 2) / (KL::groups - 1));
     const size_t smem = KL::groups * sizeof(KlHandoff<D>);
+    // polynomial scalar drifts: the 20-point Gauss-Hermite sums are taken in closed form (CubicMoments, the same
+    // values up to rounding); VDP_GH_QUADRATURE=1 runs the quadrature loops instead
+    if constexpr (D == 1 && KL::G == 1 && DriftStep1<DRIFT>::kCubic) {
+        if (!env_int("VDP_GH_QUADRATURE", 0)) {
+            k_kl_grad<DRIFT, D, 20, KL::G, true><<<grid, KL::threads, smem, st>>>(
+                P, host_mat<D>(q_host), dt, pi_factor(D), time_grid, host_vec<D>(x0_mu), host_mat<D>(x0_cov), Aq, m,
+                Sd, terms, g1, gd, gs, upd, lr, sc1, scd, B, N, status, node0, node1, nat);
+            VDP_CHECK_LAUNCH();
+            return VDP_OK;
+        }
+    }
     k_kl_grad<DRIFT, D, 20, KL::G><<<grid, KL::threads, smem, st>>>(
         P, host_mat<D>(q_host), dt, pi_factor(D), time_grid, host_vec<D>(x0_mu), host_mat<D>(x0_cov), Aq, m, Sd,
         terms, g1, gd, gs, upd, lr, sc1, scd, B, N, status, node0, node1, nat);
@@ -96,7 +107,16 @@ static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams&
     k_variational_expectation<D><<<grid_for(B, kSeqBlock), kSeqBlock, 0, st>>>(
         p.fx_mus, p.fx_covs, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.ve, B, N, p.n_obs);
     VDP_CHECK_LAUNCH();
-    if (cnt > 0) {
+    bool closed = false;
+    if constexpr (D == 1 && G == 1 && DriftStep1<DRIFT>::kCubic) closed = !env_int("VDP_GH_QUADRATURE", 0);
+    if (cnt > 0 && closed) {
+        if constexpr (D == 1 && G == 1 && DriftStep1<DRIFT>::kCubic) {
+            k_kl_value<DRIFT, D, 20, G, true><<<grid_for(cnt * G, kPtBlock), kPtBlock, 0, st>>>(
+                P, host_mat<D>(p.q), p.dt, pi_factor(D), p.qA, p.qb, p.qcholQ, p.fx_mus, p.fx_covs, p.qmu0,
+                p.qcholP0, p.pmu0, p.pcholP0, w.terms, B, N, p.status, node0, node1);
+            VDP_CHECK_LAUNCH();
+        }
+    } else if (cnt > 0) {
         k_kl_value<DRIFT, D, 20, G><<<grid_for(cnt * G, kPtBlock), kPtBlock, 0, st>>>(
             P, host_mat<D>(p.q), p.dt, pi_factor(D), p.qA, p.qb, p.qcholQ, p.fx_mus, p.fx_covs, p.qmu0, p.qcholP0,
             p.pmu0, p.pcholP0, w.terms, B, N, p.status, node0, node1);
@@ -125,7 +145,17 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
             p.fx_mus, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.lr_data, p.d1, p.d2, B, N, p.n_obs);
         VDP_CHECK_LAUNCH();
     }
-    if ((rc = run_posterior<D>(p, w, st))) return rc;
+    // the naturals written by the previous update's girsanov kernel are still valid away from the observations
+    const bool carried = (p.flags & VDP_FLAG_NATURALS_CARRIED) && p.n_obs <= 128 && node1 < 0 &&
+                         !env_int("VDP_NO_CARRIED_NATURALS", 0);
+    if (carried && p.n_obs > 0) {
+        prof_mark(VDP_PHASE_SITES_TO_NAT, st);
+        k_patch_naturals<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
+            p.pA, p.pb, p.pcholQ, p.pmu0, p.pcholP0, p.g1, p.gd, p.d1, p.d2, p.obs_idx, w.th1, w.thd, w.sc1, w.scd, B, N,
+            p.n_obs);
+        VDP_CHECK_LAUNCH();
+    }
+    if ((rc = run_posterior<D>(p, w, st, carried))) return rc;
     if (p.flags & VDP_FLAG_SKIP_GIRSANOV) {
         if (!(p.flags & VDP_FLAG_SKIP_ELBO)) return run_elbo<DRIFT, D>(p, w, P, st);
         return VDP_OK;
@@ -133,12 +163,18 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     // (B) update_girsanov_sites  variational_cvi_sde.py:279-299
     const size_t n = (size_t)B * (N + 1);
     prof_mark(VDP_PHASE_KL_GRAD, st);
-    VDP_CHECK_CUDA(cudaMemsetAsync(w.sc1, 0, n * D * sizeof(double), st));
-    VDP_CHECK_CUDA(cudaMemsetAsync(w.scd, 0, n * D * D * sizeof(double), st));
-    if (p.n_obs > 0) {
-        k_scatter_data<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(p.d1, p.d2, p.obs_idx, w.sc1, w.scd, B,
-                                                                            N, p.n_obs);
-        VDP_CHECK_LAUNCH();
+    // data sites on the dense grid (variational_cvi_sde.py:286-288).  With carried naturals the dense copy is carried
+    // too: k_patch_naturals has rewritten its observed entries.  (A per-block gather of the observations into shared
+    // memory inside the kernel, which would save the dense reads, measured slower: the kernel is bound by the FP64
+    // pipe and instruction issue, and the gather's extra instructions cost more than the reads.)
+    if (!carried) {
+        VDP_CHECK_CUDA(cudaMemsetAsync(w.sc1, 0, n * D * sizeof(double), st));
+        VDP_CHECK_CUDA(cudaMemsetAsync(w.scd, 0, n * D * D * sizeof(double), st));
+        if (p.n_obs > 0) {
+            k_scatter_data<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(p.d1, p.d2, p.obs_idx, w.sc1, w.scd,
+                                                                                B, N, p.n_obs);
+            VDP_CHECK_LAUNCH();
+        }
     }
     // whole-chain update: the kernel also writes the naturals of the posterior that follows (no second pass over
     // the sites); the sharded quadrature exchanges site ranges first and rebuilds from the sites

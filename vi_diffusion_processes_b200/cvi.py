@@ -31,8 +31,10 @@ class CviEngine:
 
     def __init__(self, drift_id, drift_params, q, time_grid, obs_idx, obs_y, lik_chol, x0_mu, x0_cov,
                  device="cuda", stabilize_ssm=True, clip_state_transitions=(-1.0, 1.0),
-                 initial_mean=None, initial_cov=None):
+                 initial_mean=None, initial_cov=None, carry_naturals=True):
         self.device = torch.device(device)
+        self.carry_naturals = bool(carry_naturals)
+        self._nat_sig = None
         self.drift_id = int(drift_id)
         self.drift_params = [float(v) for v in np.asarray(drift_params).reshape(-1)]
         self.q = np.atleast_2d(np.asarray(q, dtype=np.float64))
@@ -118,15 +120,35 @@ class CviEngine:
         p.workspace = self._ws.data_ptr()
         p.workspace_bytes = self._ws_bytes
         p.flags = flags
+        self._nat_sig = None          # whatever is called with this problem may rewrite the workspace
         return p
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
-    def site_update(self, lr_data, lr_girsanov, flags=0):
-        """cvi_dp_trainer.py:71-77 once.  Returns the ELBO tensor [B] (device)."""
+    # what the natural parameters left in the workspace by a site update depend on (besides the update itself)
+    _NAT_FIELDS = ("pA", "pb", "pcholQ", "pmu0", "pcholP0", "g1", "gd", "gs", "d1", "d2", "obs_idx", "_ws")
+
+    def _nat_signature(self):
+        return tuple((t.data_ptr(), t._version) for t in (getattr(self, n) for n in self._NAT_FIELDS))
+
+    def site_update(self, lr_data, lr_girsanov, flags=0, carry=None):
+        """
+        cvi_dp_trainer.py:71-77 once.  Returns the ELBO tensor [B] (device).
+
+        Between two consecutive updates only the data sites change before the first posterior rebuild, so the
+        naturals the previous update left in the workspace are patched at the observed grid points instead of being
+        recomputed over the whole grid (``VDP_FLAG_NATURALS_CARRIED``).  The promise behind that flag is checked
+        here: no other library call on this engine in between, and none of the tensors the naturals are made of
+        replaced or modified in place through torch (storage pointer + version counter).
+        """
+        carry = self.carry_naturals if carry is None else carry
+        if carry and self._nat_sig is not None and self._nat_sig == self._nat_signature():
+            flags |= _lib.FLAG_NATURALS_CARRIED
         p = self._problem(lr_data, lr_girsanov, flags)
         check(_lib.load().vdp_cvi_site_update(C.byref(p), self._stream()), "vdp_cvi_site_update")
+        if carry and (not (flags & _lib.FLAG_SKIP_GIRSANOV) or (flags & _lib.FLAG_NATURALS_CARRIED)):
+            self._nat_sig = self._nat_signature()      # (a data-sites-only update leaves no dense data-site copy)
         return self.elbo
 
     _PTR_FIELDS = ("time_grid", "pA", "pb", "pcholQ", "pmu0", "pcholP0", "g1", "gd", "gs", "d1", "d2", "obs_idx", "obs_y",
@@ -149,14 +171,15 @@ class CviEngine:
             if len(cache) >= 8:
                 cache.clear()
             state = [getattr(self, n).clone() for n in ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs")]
-            self.site_update(lr_data, lr_girsanov, flags)          # warm-up outside the capture (attribute setup),
+            self.site_update(lr_data, lr_girsanov, flags, carry=False)   # warm-up outside the capture,
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                self.site_update(lr_data, lr_girsanov, flags)
+                self.site_update(lr_data, lr_girsanov, flags, carry=False)
             for n, t in zip(("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs"), state):
                 getattr(self, n).copy_(t)                          # ... whose effect is undone: the replay below is
             cache[key] = g                                         # the one update of this call
         g.replay()
+        self._nat_sig = None
         return self.elbo
 
     def site_update_sharded(self, phase, node_begin, node_end, lr_data=0.0, lr_girsanov=0.0):
