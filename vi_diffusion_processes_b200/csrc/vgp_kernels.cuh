@@ -58,7 +58,8 @@ __global__ void k_vgp_to_ssm(const double* __restrict__ A, const double* __restr
 // E_sde terms and (optionally) gradients: one group of G lanes per transition (b, k), marginal of node k.
 //   term_k = 0.5 dt E_{N(m_k,S_k)} || (-A_k) x + b_k - f(x) ||^2_{q^-1}
 //   dEdm = d term / d m_k / dt, dEdS = d term / d S_k / dt       (vi_sde.py:206-225 divides by dt)
-template <int DRIFT, int D, int H, int G>
+// CLOSED (polynomial scalar drifts): the Gauss-Hermite sums in closed form (CubicMoments, drifts.cuh)
+template <int DRIFT, int D, int H, int G, bool CLOSED = false>
 __global__ void k_vgp_esde(DriftParams P, Mat<D> q, double dt, double pi_factor, const double* __restrict__ A,
                            const double* __restrict__ bv, const double* __restrict__ m,
                            const double* __restrict__ S, double* __restrict__ terms, double* __restrict__ dEdm,
@@ -86,6 +87,20 @@ __global__ void k_vgp_esde(DriftParams P, Mat<D> q, double dt, double pi_factor,
         // one thread per transition: nodes unrolled (tables as immediates), q^-1 and pi^(-1/2) factored out
         const double sL = 1.4142135623730951 * LS(0, 0), m1 = mk(0), a1 = Al(0, 0), b1 = bl(0);
         double q_ = 0.0, g_ = 0.0, l_ = 0.0;
+        if constexpr (CLOSED) {
+            // d(x) = a1 x + b1 - f(x) = x - f(x) - ((1 - a1) x - b1): DriftStep1 with dt = -1
+            const typename DriftStep1<DRIFT>::K kst = DriftStep1<DRIFT>::prepare(P, -1.0, 1.0 - a1, -b1);
+            double c0, c1, c2, c3;
+            DriftStep1<DRIFT>::taylor(kst, m1, c0, c1, c2, c3);
+            const double Sk = LS(0, 0) * LS(0, 0);
+            CubicMoments cm;
+            if (dEdm) cm.template eval<true>(c0, c1, c2, c3, Sk); else cm.template eval<false>(c0, c1, c2, c3, Sk);
+            quad = sinv(0, 0) * cm.Ed2;
+            if (dEdm) {
+                gm(0) = (dt * sinv(0, 0)) * cm.Ejd;
+                Lb(0, 0) = (dt * sinv(0, 0)) * cm.Ejde / LS(0, 0);
+            }
+        } else {
         if (dEdm) {
 #pragma unroll
             for (int p = 0; p < H; ++p) {
@@ -115,6 +130,7 @@ __global__ void k_vgp_esde(DriftParams P, Mat<D> q, double dt, double pi_factor,
         quad = sc * q_;
         gm(0) = (dt * sc) * g_;
         Lb(0, 0) = (1.4142135623730951 * dt * sc) * l_;
+        }
     }
     for (int p = lane; p < (kScalar ? 0 : NP); p += G) {
         Vec<D> xi, f;
@@ -177,7 +193,7 @@ __global__ void k_vgp_jump(const double* __restrict__ m, const int64_t* __restri
 }
 
 // update_param: one group per transition (b, k), marginal of node k, H = 10
-template <int DRIFT, int D, int H, int G>
+template <int DRIFT, int D, int H, int G, bool CLOSED = false>
 __global__ void k_vgp_update_param(DriftParams P, Mat<D> q, double pi_factor, int stabilize, double lr,
                                    const double* __restrict__ m, const double* __restrict__ S,
                                    double* __restrict__ lam, double* __restrict__ psi, double* __restrict__ A,
@@ -192,7 +208,19 @@ __global__ void k_vgp_update_param(DriftParams P, Mat<D> q, double pi_factor, in
     Vec<D> ef;
     Mat<D> ej;
     const Vec<D> mk = vec_load<D>(m + node * D);
-    gh_expect_point<DRIFT, D, H, G>(P, mk, mat_load<D>(S + node * DD), lane, pi_factor, ef, ej, ok);
+    if constexpr (CLOSED) {
+        // E f = c0 + c2 S, E f' = c1 + 3 c3 S with f(m + e) = c0 + c1 e + c2 e^2 + c3 e^3 (DriftStep1 with dt = 1,
+        // A = 1, b = 0 is d = f)
+        const typename DriftStep1<DRIFT>::K kst = DriftStep1<DRIFT>::prepare(P, 1.0, 1.0, 0.0);
+        double c0, c1, c2, c3;
+        DriftStep1<DRIFT>::taylor(kst, mk(0), c0, c1, c2, c3);
+        const double Sk = S[node];
+        if (!(Sk > 0.0)) ok = false;
+        ef(0) = fma(c2, Sk, c0);
+        ej(0, 0) = fma(3.0 * c3, Sk, c1);
+    } else {
+        gh_expect_point<DRIFT, D, H, G>(P, mk, mat_load<D>(S + node * DD), lane, pi_factor, ef, ej, ok);
+    }
     if (lane != 0) return;
     if (!ok) report_not_pd(status, node);
     Mat<D> ps = mat_load<D>(psi + t * DD);
