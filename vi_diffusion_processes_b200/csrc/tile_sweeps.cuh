@@ -271,9 +271,9 @@ k_marg_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
     using Ops = MargOps<D>;
     extern __shared__ __align__(16) double smem[];
     double* sC = smem;                        // chol factor of node i           (TL + 2)
+    double* sKd = sC;                         // ... overwritten by: precision diagonal -> L_kk  (TL + 1)
     double* sA = sC + (TL + 2) * DD;          // A of transition i               (TL + 1)
-    double* sKd = sA + (TL + 1) * DD;         // precision diagonal -> L_kk      (TL + 1)
-    double* sKs = sKd + (TL + 1) * DD;        // precision sub-diagonal -> L_sub (TL)
+    double* sKs = sA + (TL + 1) * DD;         // precision sub-diagonal -> L_sub (TL)
     double* sb = sKs + TL * DD;               // offsets -> m_{k+1}              (TL)
     typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(sb + TL * D);
     const int64_t b = blockIdx.x / nseg;
@@ -301,14 +301,36 @@ k_marg_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
         stage_in<T>(sb, bo + (b * N + tk) * D, (int64_t)cnt * D);
         stage_wait();
         __syncthreads();
-        // phase 0: precision blocks of nodes [0, cnt]
-        for (int i = threadIdx.x; i <= cnt; i += T) {
-            const bool has_next = (i < cnt) || halo_has_next;
-            Mat<D> Ak = mat_zero<D>(), cnext = mat_eye<D>(), diag, sub = mat_zero<D>();
-            if (has_next) { Ak = mat_load<D>(sA + i * DD); cnext = mat_load<D>(sC + (i + 1) * DD); }
-            precision_blocks(mat_load<D>(sC + i * DD), has_next, Ak, cnext, diag, sub);
-            mat_store<D>(sKd + i * DD, diag);
-            if (i < cnt) mat_store<D>(sKs + i * DD, sub);
+        // phase 0: precision blocks of nodes [0, cnt], written over the staged node factors (sKd is sC: one staged
+        // array less, 6 instead of 4 CTAs per SM at D = 1).  Every thread walks its own chunk in order and holds the
+        // factor of the node after its chunk -- the first one of the next thread's chunk -- in registers; thread 0
+        // also does node cnt, whose factor nobody else overwrites.
+        const int k0 = threadIdx.x * L;
+        const int len = min(L, cnt - k0);
+        {
+            Mat<D> c_after = mat_eye<D>(), c_last = mat_eye<D>(), c_halo = mat_eye<D>(), A_halo = mat_zero<D>();
+            if (len > 0) c_after = mat_load<D>(sC + (k0 + len) * DD);
+            if (threadIdx.x == 0) {
+                c_last = mat_load<D>(sC + cnt * DD);
+                if (halo_has_next) { A_halo = mat_load<D>(sA + cnt * DD); c_halo = mat_load<D>(sC + (cnt + 1) * DD); }
+            }
+            __syncthreads();
+            Mat<D> ci = mat_eye<D>();
+            if (len > 0) ci = mat_load<D>(sC + k0 * DD);
+            for (int t = 0; t < len; ++t) {
+                const int i = k0 + t;
+                const Mat<D> cnext = (t == len - 1) ? c_after : mat_load<D>(sC + (i + 1) * DD);
+                Mat<D> diag, sub;
+                precision_blocks(ci, true, mat_load<D>(sA + i * DD), cnext, diag, sub);
+                mat_store<D>(sKd + i * DD, diag);
+                mat_store<D>(sKs + i * DD, sub);
+                ci = cnext;
+            }
+            if (threadIdx.x == 0) {
+                Mat<D> diag, sub = mat_zero<D>();
+                precision_blocks(c_last, halo_has_next, A_halo, c_halo, diag, sub);
+                mat_store<D>(sKd + cnt * DD, diag);
+            }
         }
         __syncthreads();
         if (seg == 0 && tk == 0) {
@@ -319,8 +341,6 @@ k_marg_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
             }
             if (MODE == SWEEP_FULL && threadIdx.x == 0) vec_store<D>(m + b * (N + 1) * D, st.b);
         }
-        const int k0 = threadIdx.x * L;
-        const int len = min(L, cnt - k0);
         typename Ops::Elem e;
         e.a = chol_tile_summary<D, L>(sKd, sKs, k0, len);
         e.b = AffVecOps<D>::identity();
@@ -355,7 +375,7 @@ k_marg_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
 
 template <int D, int T, int L>
 constexpr size_t marg_tiled_smem() {
-    return ((size_t)(T * L + 2) * D * D + 2 * (size_t)(T * L + 1) * D * D + (size_t)T * L * D * D + (size_t)T * L * D) *
+    return ((size_t)(T * L + 2) * D * D + (size_t)(T * L + 1) * D * D + (size_t)T * L * D * D + (size_t)T * L * D) *
                sizeof(double) +
            (T / 32) * sizeof(typename MargOps<D>::Elem);
 }
