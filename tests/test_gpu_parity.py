@@ -594,6 +594,39 @@ def test_vdp_closed_form_moments_equal_gauss_hermite(monkeypatch, drift, params)
         assert (x - r).abs().max() <= 1e-11 * r.abs().max()
 
 
+@pytest.mark.parametrize("drift,params,D,N,nseg", [("dw", [4.0, 1.0], 1, 3000, 0), ("dw", [4.0, 1.0], 1, 6000, 3),
+                                                  ("vdp", [1.0, 1.0], 2, 1500, 0), ("ou", [0.7], 1, 40, 0)])
+def test_marginals_from_first_factor(monkeypatch, drift, params, D, N, nseg):
+    """Posterior rebuild: the marginal covariances come from the Cholesky factor naturals_to_ssm started from (the
+    factor of the matrix the reference rebuilds from the state-space model and factorises a second time), the means
+    from the forward recursion alone.  VDP_REFACTOR_PRECISION=1 runs the second factorisation: same state to
+    rounding, also with the chain cut into segments."""
+    from vi_diffusion_processes_b200.markovflow.sde import sde as sde_mod
+    from vi_diffusion_processes_b200.cvi import CviEngine
+    did = {"dw": sde_mod.DRIFT_DW, "ou": sde_mod.DRIFT_OU, "vdp": sde_mod.DRIFT_VDP}[drift]
+    if nseg:
+        monkeypatch.setenv("VDP_NSEG", str(nseg))
+    rng = np.random.default_rng(52)
+    B, n_obs = 3, 12
+    grid = np.round(np.arange(N + 1) * 0.005, 3)
+    idx = np.sort(np.stack([rng.choice(N + 1, n_obs, replace=False) for _ in range(B)]), axis=1)
+    y = rng.normal(size=(B, n_obs, D)) * 0.3 + 1.0
+    mk = lambda: CviEngine(did, params, np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.ones(D), 1e-2 * np.eye(D))
+    a, c = mk(), mk()
+    ea = [a.site_update(0.5, 0.5).clone() for _ in range(3)]
+    monkeypatch.setenv("VDP_REFACTOR_PRECISION", "1")
+    ec = [c.site_update(0.5, 0.5).clone() for _ in range(3)]
+    a.check_status()
+    c.check_status()
+    th = c._prior_naturals(c.pA, c.pb)
+    for name, prior in (("g1", th[0]), ("gd", th[1]), ("gs", th[2]), ("fx_mus", None), ("fx_covs", None)):
+        ref = getattr(c, name)
+        scale = ref.abs().max() if prior is None else (ref + prior).abs().max()
+        assert (getattr(a, name) - ref).abs().max() <= 1e-11 * scale, name
+    for x, r in zip(ea, ec):
+        assert (x - r).abs().max() <= 1e-11 * r.abs().max()
+
+
 def test_cuda_graph_replay_equals_direct_calls():
     """site_update_graphed / sweep_graphed (CUDA-graph replay for launch-bound single sequences) leave bitwise the
     state of the direct calls, across a re-linearisation (buffers replaced -> re-capture) and a step-size change."""

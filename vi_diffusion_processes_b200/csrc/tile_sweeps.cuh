@@ -382,6 +382,73 @@ constexpr size_t marg_tiled_smem() {
 
 
 // ---------------------------------------------------------------------------------------------------
+// Marginal means alone, m_{k+1} = A_k m_k + b_k (state_space_model.py:251): the forward sweep of the posterior
+// rebuild when the Cholesky factor of the precision is already at hand (the one naturals_to_ssm was computed from is
+// the factor of the same matrix the reference rebuilds from the state-space model).
+template <int D, int T, int L, int MODE>
+__global__ void __launch_bounds__(T)
+k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const double* __restrict__ mu0,
+             double* __restrict__ m, int64_t B, int64_t N, int nseg, int64_t seg_len,
+             const Vec<D>* __restrict__ carry_in, Vec<D>* __restrict__ init_out,
+             AffVecElem<D>* __restrict__ seg_elem) {
+    constexpr int DD = D * D, TL = T * L;
+    using Ops = AffVecOps<D>;
+    extern __shared__ __align__(16) double smem[];
+    double* sA = smem;                        // A of transition i               (TL)
+    double* sb = sA + TL * DD;                // offsets -> m_{k+1}              (TL)
+    typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(sb + TL * D);
+    const int64_t b = blockIdx.x / nseg;
+    const int seg = (int)(blockIdx.x % nseg);
+    const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
+    Vec<D> st = vec_zero<D>();
+    if (MODE == SWEEP_FULL && seg > 0) st = carry_in[b * nseg + seg];
+    typename Ops::Elem seg_tot = Ops::identity();
+    for (int64_t tk = t0; tk < t1; tk += TL) {
+        const int cnt = (int)min((int64_t)TL, t1 - tk);
+        __syncthreads();
+        stage_in<T>(sA, A + (b * N + tk) * DD, (int64_t)cnt * DD);
+        stage_in<T>(sb, bo + (b * N + tk) * D, (int64_t)cnt * D);
+        stage_wait();
+        __syncthreads();
+        if (seg == 0 && tk == 0) {
+            st = vec_load<D>(mu0 + b * D);
+            if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = st;
+            if (MODE == SWEEP_FULL && threadIdx.x == 0) vec_store<D>(m + b * (N + 1) * D, st);
+        }
+        const int k0 = threadIdx.x * L;
+        const int len = min(L, cnt - k0);
+        typename Ops::Elem e = Ops::identity();
+        for (int t = 0; t < len; ++t) {
+            AffVecElem<D> s;
+            s.M = mat_load<D>(sA + (k0 + t) * DD);
+            s.v = vec_load<D>(sb + (k0 + t) * D);
+            e = Ops::combine(e, s);
+        }
+        typename Ops::Elem total;
+        const typename Ops::Elem excl = block_exclusive_scan<Ops, T>(e, wtot, total);
+        if (MODE != SWEEP_FULL) {
+            seg_tot = Ops::combine(seg_tot, total);
+            continue;
+        }
+        Vec<D> mk = Ops::apply(excl, st);
+        st = Ops::apply(total, st);
+        for (int t = 0; t < len; ++t) {
+            mk = vec_load<D>(sb + (k0 + t) * D) + mv(mat_load<D>(sA + (k0 + t) * DD), mk);
+            vec_store<D>(sb + (k0 + t) * D, mk);
+        }
+        __syncthreads();
+        stage_out<T>(m + (b * (N + 1) + tk + 1) * D, sb, (int64_t)cnt * D);
+    }
+    if (MODE != SWEEP_FULL && threadIdx.x == 0) seg_elem[b * nseg + seg] = seg_tot;
+}
+
+template <int D, int T, int L>
+constexpr size_t mean_tiled_smem() {
+    return ((size_t)T * L * D * D + (size_t)T * L * D) * sizeof(double) + (T / 32) * sizeof(AffVecElem<D>);
+}
+
+
+// ---------------------------------------------------------------------------------------------------
 // Backward sweeps.  A segment's tiles are walked from its top; thread c owns the c-th chunk from the top
 // of the tile, local transitions [bot, top), processed downwards; its carry is the state at node `top`.
 struct BwdChunk { int top, bot, len; };

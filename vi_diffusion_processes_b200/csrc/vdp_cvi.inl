@@ -91,6 +91,19 @@ static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t 
     int rc = run_nat2ssm<D>(w.th1, w.thd, w.ths, p.qA, p.qb, p.qcholQ, p.qmu0, p.qcholP0, w.Ld, w.Ls, B, N, p.status,
                             st, sc);
     if (rc || (p.flags & VDP_FLAG_POSTERIOR_SSM_ONLY)) return rc;
+    // marginals (gauss_markov.py:107-117): the reference rebuilds the precision from the state-space model and
+    // factorises it again; that matrix is the one naturals_to_ssm started from, whose factor (Ld, Ls) is still in the
+    // workspace, so the tiled route runs the mean recursion alone and takes the covariances from that factor
+    // (VDP_REFACTOR_PRECISION=1 keeps the second factorisation; equal to rounding,
+    // tests/test_gpu_parity.py::test_marginals_from_first_factor)
+    if (use_tiled_sweeps(B, N) && !env_int("VDP_REFACTOR_PRECISION", 0)) {
+        prof_mark(VDP_PHASE_MARG_FWD, st);
+        if ((rc = run_mean_fwd_tiled<D>(p.qA, p.qb, p.qmu0, p.fx_mus, B, N, sc, st))) return rc;
+        prof_mark(VDP_PHASE_INVBAND_BWD, st);
+        if ((rc = run_invband_tiled<D>(w.Ld, w.Ls, p.fx_covs, nullptr, B, N, sc, st))) return rc;
+        prof_mark(VDP_PHASE_END, st);
+        return VDP_OK;
+    }
     return run_marginals<D>(p.qA, p.qb, p.qcholQ, p.qmu0, p.qcholP0, p.fx_mus, p.fx_covs, w.Ld, w.Ls, B, N, p.status,
                             st, sc);
 }

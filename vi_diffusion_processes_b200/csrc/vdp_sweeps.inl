@@ -233,4 +233,37 @@ static int run_marg_fwd_tiled(const double* A, const double* b, const double* ch
     return VDP_OK;
 }
 
+// ---- marginal means alone (the posterior rebuild of the site update: the precision factor is already there) ----
+template <int D>
+static int run_mean_fwd_tiled(const double* A, const double* b, const double* mu0, double* m, int64_t B, int64_t N,
+                              SegScratch sc, cudaStream_t st) {
+    using C = TileCfg<D>;
+    using Ops = AffVecOps<D>;
+    constexpr int L = 2 * C::Lm;
+    constexpr size_t smem = mean_tiled_smem<D, C::T, L>();
+    const SegPlan pl = plan_segments(B, N, C::T * L, sc.size > 0);
+    const unsigned grid = (unsigned)(B * pl.nseg);
+    int rc;
+    if ((rc = allow_smem(k_mean_tiled<D, C::T, L, SWEEP_FULL>, smem))) return rc;
+    if (pl.nseg == 1) {
+        k_mean_tiled<D, C::T, L, SWEEP_FULL><<<grid, C::T, smem, st>>>(A, b, mu0, m, B, N, 1, pl.seg_len, nullptr, nullptr,
+                                                                     nullptr);
+        VDP_CHECK_LAUNCH();
+        return VDP_OK;
+    }
+    typename Ops::State* carry = sc.take<typename Ops::State>((size_t)B * pl.nseg);
+    typename Ops::State* init = sc.take<typename Ops::State>((size_t)B);
+    typename Ops::Elem* el = sc.take<typename Ops::Elem>((size_t)B * pl.nseg);
+    if (!el) { set_error("segment scratch too small"); return VDP_E_WORKSPACE; }
+    if ((rc = allow_smem(k_mean_tiled<D, C::T, L, SWEEP_SUMMARY>, smem))) return rc;
+    k_mean_tiled<D, C::T, L, SWEEP_SUMMARY><<<grid, C::T, smem, st>>>(A, b, mu0, m, B, N, pl.nseg, pl.seg_len, nullptr,
+                                                                    init, el);
+    VDP_CHECK_LAUNCH();
+    if ((rc = launch_seg_scan<Ops>(el, init, carry, B, pl.nseg, 0, st))) return rc;
+    k_mean_tiled<D, C::T, L, SWEEP_FULL><<<grid, C::T, smem, st>>>(A, b, mu0, m, B, N, pl.nseg, pl.seg_len, carry, nullptr,
+                                                                 nullptr);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
 }  // namespace vdp
