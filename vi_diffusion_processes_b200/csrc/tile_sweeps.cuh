@@ -557,7 +557,10 @@ constexpr size_t invband_tiled_smem() {
 // rebuilt from the Cholesky factor already staged (K_kk = L_kk L_kk^T + L_{k,k-1} L_{k,k-1}^T,
 // K_{k+1,k} = L_{k+1,k} L_kk^T) instead of being read again: 16 of 64 B per grid step less traffic (D = 1) and
 // 3 instead of 5 staged arrays (twice the CTAs per SM).  Single-rank launches only (needs L_{k,k-1} below the range).
-template <int D, int T, int L, int MODE, bool FROML = false>
+// COV: the diagonal blocks of the inverse band the Sigma recursion walks through are the marginal covariances of the
+// Gaussian the naturals describe; they are staged out as well (Sd [B, N+1, D, D]), which makes a separate
+// inverse-band sweep over the same factor unnecessary in the posterior rebuild.
+template <int D, int T, int L, int MODE, bool FROML = false, bool COV = false>
 __global__ void __launch_bounds__(T)
 k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, const double* __restrict__ th1,
                 const double* __restrict__ thd, const double* __restrict__ ths, double* __restrict__ A,
@@ -565,7 +568,8 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
                 double* __restrict__ cholP0, int64_t B, int64_t N, int nseg, int64_t seg_len,
                 const Mat<D>* __restrict__ carryS, const Vec<D>* __restrict__ carryY, Mat<D>* __restrict__ initS,
                 Vec<D>* __restrict__ initY, AffSymElem<D>* __restrict__ seg_elemS,
-                AffVecElem<D>* __restrict__ seg_elemY, int64_t* status, int first = 1, int last = 1) {
+                AffVecElem<D>* __restrict__ seg_elemY, int64_t* status, int first = 1, int last = 1,
+                double* __restrict__ Sd = nullptr) {
     constexpr int DD = D * D, TL = T * L;
     extern __shared__ __align__(16) double smem[];
     double* sLd = smem;              // L_kk  -> chol of the conditional covariance of node k
@@ -573,7 +577,8 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
     double* sTd = sLs + TL * DD;     // theta_diag -> conditional covariance of node k   (not FROML)
     double* sTs = sTd + TL * DD;     // theta_sub                                         (not FROML)
     double* sT1 = FROML ? sLs + TL * DD : sTs + TL * DD;     // theta_1 -> offset of node k
-    AffSymElem<D>* wtotS = reinterpret_cast<AffSymElem<D>*>(sT1 + TL * D);
+    double* sSd = sT1 + TL * D;      // marginal covariance of node k                     (COV)
+    AffSymElem<D>* wtotS = reinterpret_cast<AffSymElem<D>*>(sSd + (COV ? TL * DD : 0));
     AffVecElem<D>* wtotY = reinterpret_cast<AffVecElem<D>*>(wtotS);   // used after the Sigma scan is over
     const int64_t b = blockIdx.x / nseg;
     const int seg = (int)(blockIdx.x % nseg);
@@ -600,6 +605,7 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
                 if (!ok) report_not_pd(status, b * n + N);
                 vec_store<D>(bo + (b * N + N - 1) * D, mv(cov, y_tile));
                 mat_store<D>(cholQ + (b * N + N - 1) * DD, cc);
+                if (COV) mat_store<D>(Sd + (b * n + N) * DD, S_tile);
             }
         }
     } else {
@@ -652,6 +658,7 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
             const Mat<D> Lkk = mat_load<D>(sLd + k * DD), Lsub = mat_load<D>(sLs + k * DD);
             invband_step(Lkk, Lsub, S, Ssub, Skk);
             S = Skk;
+            if (COV && MODE == SWEEP_FULL) mat_store<D>(sSd + k * DD, Skk);
             const Mat<D> Ak = transition_from_cov(Skk, Ssub);
             Mat<D> prec;
             if (FROML) {
@@ -690,6 +697,7 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
         }
         __syncthreads();
         stage_out<T>(A + (b * N + lo) * DD, sLs, (int64_t)cnt * DD);
+        if (COV) stage_out<T>(Sd + (b * n + lo) * DD, sSd, (int64_t)cnt * DD);
         if (lo >= 1 || !first) {   // time-sharded ranks own one slot before index 0 of bo / cholQ
             stage_out<T>(bo + (b * N + lo - 1) * D, sT1, (int64_t)cnt * D);
             stage_out<T>(cholQ + (b * N + lo - 1) * DD, sLd, (int64_t)cnt * DD);
@@ -706,9 +714,9 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
     }
 }
 
-template <int D, int T, int L, bool FROML = false>
+template <int D, int T, int L, bool FROML = false, bool COV = false>
 constexpr size_t nat2ssm_tiled_smem() {
-    return ((FROML ? 2 : 4) * (size_t)T * L * D * D + (size_t)T * L * D) * sizeof(double) +
+    return (((FROML ? 2 : 4) + (COV ? 1 : 0)) * (size_t)T * L * D * D + (size_t)T * L * D) * sizeof(double) +
            (T / 32) * (sizeof(AffSymElem<D>) > sizeof(AffVecElem<D>) ? sizeof(AffSymElem<D>) : sizeof(AffVecElem<D>));
 }
 

@@ -88,19 +88,20 @@ static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t 
         }
     }
     const SegScratch sc(w.seg, kSegScratchBytes);
+    // marginals (gauss_markov.py:107-117): the reference rebuilds the precision from the state-space model,
+    // factorises it again and takes the diagonal of the inverse band.  That matrix is the one naturals_to_ssm started
+    // from, and naturals_to_ssm itself walks through the inverse band of its factor (ssm_gaussian_transformations.py:
+    // 443-504): on the tiled route the backward sweep writes those diagonal blocks out as the marginal covariances
+    // and the forward sweep that follows computes the means alone.  VDP_REFACTOR_PRECISION=1 keeps the second
+    // factorisation + inverse band (equal to rounding, tests/test_gpu_parity.py::test_marginals_from_first_factor).
+    const bool ssm_only = (p.flags & VDP_FLAG_POSTERIOR_SSM_ONLY) != 0;
+    const bool lite = use_tiled_sweeps(B, N) && !env_int("VDP_REFACTOR_PRECISION", 0);
     int rc = run_nat2ssm<D>(w.th1, w.thd, w.ths, p.qA, p.qb, p.qcholQ, p.qmu0, p.qcholP0, w.Ld, w.Ls, B, N, p.status,
-                            st, sc);
-    if (rc || (p.flags & VDP_FLAG_POSTERIOR_SSM_ONLY)) return rc;
-    // marginals (gauss_markov.py:107-117): the reference rebuilds the precision from the state-space model and
-    // factorises it again; that matrix is the one naturals_to_ssm started from, whose factor (Ld, Ls) is still in the
-    // workspace, so the tiled route runs the mean recursion alone and takes the covariances from that factor
-    // (VDP_REFACTOR_PRECISION=1 keeps the second factorisation; equal to rounding,
-    // tests/test_gpu_parity.py::test_marginals_from_first_factor)
-    if (use_tiled_sweeps(B, N) && !env_int("VDP_REFACTOR_PRECISION", 0)) {
+                            st, sc, (lite && !ssm_only) ? p.fx_covs : nullptr);
+    if (rc || ssm_only) return rc;
+    if (lite) {
         prof_mark(VDP_PHASE_MARG_FWD, st);
         if ((rc = run_mean_fwd_tiled<D>(p.qA, p.qb, p.qmu0, p.fx_mus, B, N, sc, st))) return rc;
-        prof_mark(VDP_PHASE_INVBAND_BWD, st);
-        if ((rc = run_invband_tiled<D>(w.Ld, w.Ls, p.fx_covs, nullptr, B, N, sc, st))) return rc;
         prof_mark(VDP_PHASE_END, st);
         return VDP_OK;
     }

@@ -18,13 +18,14 @@ static int launch_chol_nat(const double* thd, const double* ths, double* Ld, dou
 template <int D>
 static int run_nat2ssm(const double* th1, const double* thd, const double* ths, double* A, double* b, double* cholQ,
                        double* mu0, double* cholP0, double* Ld, double* Ls, int64_t B, int64_t N, int64_t* status,
-                       cudaStream_t st, SegScratch sc = SegScratch(nullptr, 0)) {
+                       cudaStream_t st, SegScratch sc = SegScratch(nullptr, 0), double* Sd_tiled = nullptr) {
     int rc;
     if (use_tiled_sweeps(B, N)) {
         prof_mark(VDP_PHASE_CHOL_FWD, st);
         if ((rc = run_chol_tiled<D>(thd, ths, -2.0, -1.0, Ld, Ls, B, N, status, sc, st))) return rc;
         prof_mark(VDP_PHASE_NAT2SSM_BWD, st);
-        return run_nat2ssm_bwd_tiled<D>(Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, status, sc, st);
+        // Sd_tiled (tiled route only): marginal covariances of the Gaussian the naturals describe, written on the way
+        return run_nat2ssm_bwd_tiled<D>(Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, status, sc, st, Sd_tiled);
     }
     prof_mark(VDP_PHASE_CHOL_FWD, st);
     rc = launch_chol_nat<D>(thd, ths, Ld, Ls, B, N + 1, status, st);

@@ -157,20 +157,22 @@ static int run_invband_tiled(const double* Ld, const double* Ls, double* Sd, dou
 }
 
 // ---- naturals_to_ssm_params, backward half ---------------------------------------------------------
-template <int D>
-static int run_nat2ssm_bwd_tiled(const double* Ld, const double* Ls, const double* th1, const double* thd,
-                                 const double* ths, double* A, double* b, double* cholQ, double* mu0, double* cholP0,
-                                 int64_t B, int64_t N, int64_t* status, SegScratch sc, cudaStream_t st) {
+template <int D, bool COV>
+static int run_nat2ssm_bwd_tiled_impl(const double* Ld, const double* Ls, const double* th1, const double* thd,
+                                      const double* ths, double* A, double* b, double* cholQ, double* mu0,
+                                      double* cholP0, int64_t B, int64_t N, int64_t* status, SegScratch sc,
+                                      cudaStream_t st, double* Sd) {
     using C = TileCfg<D>;
     constexpr size_t smem = nat2ssm_tiled_smem<D, C::T, C::Ln, true>();
+    constexpr size_t smem_full = nat2ssm_tiled_smem<D, C::T, C::Ln, true, COV>();
     const SegPlan pl = plan_segments(B, N, C::T * C::Ln, sc.size > 0);
     const unsigned grid = (unsigned)(B * pl.nseg);
     int rc;
-    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true>, smem))) return rc;
+    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true, COV>, smem_full))) return rc;
     if (pl.nseg == 1) {
-        k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true><<<grid, C::T, smem, st>>>(
+        k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true, COV><<<grid, C::T, smem_full, st>>>(
             Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, 1, pl.seg_len, nullptr, nullptr, nullptr, nullptr,
-            nullptr, nullptr, status);
+            nullptr, nullptr, status, 1, 1, Sd);
         VDP_CHECK_LAUNCH();
         return VDP_OK;
     }
@@ -193,12 +195,25 @@ static int run_nat2ssm_bwd_tiled(const double* Ld, const double* Ls, const doubl
         elY, status);
     VDP_CHECK_LAUNCH();
     if ((rc = launch_seg_scan<AffVecOps<D>>(elY, initY, carryY, B, pl.nseg, 1, st))) return rc;
-    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true><<<grid, C::T, smem, st>>>(
+    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true, COV><<<grid, C::T, smem_full, st>>>(
         Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, pl.nseg, pl.seg_len, carryS, carryY, nullptr, nullptr,
-        nullptr, nullptr, status);
+        nullptr, nullptr, status, 1, 1, Sd);
     VDP_CHECK_LAUNCH();
     return VDP_OK;
 }
+
+// Sd != NULL: also write the marginal covariances (the diagonal of the inverse band the sweep computes on its way)
+template <int D>
+static int run_nat2ssm_bwd_tiled(const double* Ld, const double* Ls, const double* th1, const double* thd,
+                                 const double* ths, double* A, double* b, double* cholQ, double* mu0, double* cholP0,
+                                 int64_t B, int64_t N, int64_t* status, SegScratch sc, cudaStream_t st,
+                                 double* Sd = nullptr) {
+    if (Sd) return run_nat2ssm_bwd_tiled_impl<D, true>(Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, status, sc,
+                                                       st, Sd);
+    return run_nat2ssm_bwd_tiled_impl<D, false>(Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, status, sc, st,
+                                                nullptr);
+}
+
 
 // ---- marginal means + Cholesky of the rebuilt precision --------------------------------------------
 template <int D>
