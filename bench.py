@@ -169,16 +169,18 @@ PHASE_TRAFFIC = {
     # read th1 | Ld, Ls ; write b | A, cholQ, Sd (K blocks rebuilt from L in the tile; the marginal covariances are
     # the diagonal of the inverse band the sweep walks through, so no separate inverse-band sweep)
     "nat2ssm_bwd": (1 + 1, 2 + 3),
-    "marg_fwd": (1 + 1, 1),           # means alone: read b | A ; write m
+    # means alone: read b | A ; write m.  The sweep of the second rebuild also reads S, cholQ and adds up the KL
+    # terms of classic_elbo (24 and 40 B per grid step: 32 on average over the two launches of an update)
+    "marg_fwd": (1 + 1, 1 + 1),
     "invband_bwd": (0, 2 + 1),        # (only with VDP_REFACTOR_PRECISION=1) read Ld, Ls ; write Sd
     # read m, g1, sc1, prior b | A, S, gd, gs, scd, prior A, cholQ ; write g1, th1 | gd, gs, thd, ths: the kernel
     # also emits the naturals of the posterior that follows (no second k_ssm_to_naturals pass); the dense copy of the
     # data sites (sc) is carried between updates like the naturals (no memset)
     "kl_grad": (1 + 1 + 1 + 1 + 1 + 1, 2 + 2 + 1 + 2 + 1 + 2 + 1),
-    "elbo": (2, 3),                   # read b, m | A, cholQ, S
+    "elbo": (0, 0),                   # variational expectations at the observations + sum of the KL partials
 }
-LAUNCHES_PER_UPDATE = 1 + 4 + 1 + 3 + 4   # kernels of ours in one vdp_cvi_site_update in steady state (data sites,
-#                                           patch + 3 sweeps, kl_grad, 3 sweeps, VE + KL value + reduce + combine)
+LAUNCHES_PER_UPDATE = 1 + 4 + 1 + 3 + 3   # kernels of ours in one vdp_cvi_site_update in steady state (data sites,
+#                                           patch + 3 sweeps, kl_grad, 3 sweeps, VE + reduce + combine)
 
 
 def phase_bytes_per_step(name, D):

@@ -627,6 +627,38 @@ def test_marginals_from_first_factor(monkeypatch, drift, params, D, N, nseg):
         assert (x - r).abs().max() <= 1e-11 * r.abs().max()
 
 
+@pytest.mark.parametrize("drift,params,N,nseg", [("dw", [4.0, 1.0], 3000, 0), ("dw", [4.0, 1.0], 7000, 3),
+                                                ("ou", [0.7], 2500, 0)])
+def test_kl_terms_summed_in_the_mean_sweep(monkeypatch, drift, params, N, nseg):
+    """Second rebuild of a site update, D = 1, polynomial drift: the mean sweep adds up the KL terms of classic_elbo on
+    its way (per thread, per CTA, per tile; k_reduce_terms adds the tiles).  VDP_SEPARATE_KL_VALUE=1 runs k_kl_value
+    over the grid instead: same ELBO and state up to the summation order."""
+    from vi_diffusion_processes_b200.markovflow.sde import sde as sde_mod
+    from vi_diffusion_processes_b200.cvi import CviEngine
+    did = {"dw": sde_mod.DRIFT_DW, "ou": sde_mod.DRIFT_OU}[drift]
+    if nseg:
+        monkeypatch.setenv("VDP_NSEG", str(nseg))
+    rng = np.random.default_rng(61)
+    B, n_obs = 3, 12
+    grid = np.round(np.arange(N + 1) * 0.005, 3)
+    idx = np.sort(np.stack([rng.choice(N + 1, n_obs, replace=False) for _ in range(B)]), axis=1)
+    y = rng.normal(size=(B, n_obs, 1)) * 0.3 + 1.0
+    mk = lambda: CviEngine(did, params, np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]])
+    a, c = mk(), mk()
+    ea = [a.site_update(0.5, 0.5).clone() for _ in range(3)]
+    monkeypatch.setenv("VDP_SEPARATE_KL_VALUE", "1")
+    ec = [c.site_update(0.5, 0.5).clone() for _ in range(3)]
+    a.check_status()
+    th = c._prior_naturals(c.pA, c.pb)
+    for name, prior in (("g1", th[0]), ("gd", th[1]), ("gs", th[2]), ("fx_mus", None), ("fx_covs", None)):
+        ref = getattr(c, name)
+        scale = ref.abs().max() if prior is None else (ref + prior).abs().max()
+        assert (getattr(a, name) - ref).abs().max() <= 1e-11 * scale, name
+    for x, r in zip(ea, ec):
+        assert (x - r).abs().max() <= 1e-12 * r.abs().max()
+    assert (a.kl - c.kl).abs().max() <= 1e-12 * c.kl.abs().max()
+
+
 def test_cuda_graph_replay_equals_direct_calls():
     """site_update_graphed / sweep_graphed (CUDA-graph replay for launch-bound single sequences) leave bitwise the
     state of the direct calls, across a re-linearisation (buffers replaced -> re-capture) and a step-size change."""

@@ -446,6 +446,41 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
     }
 }
 
+// D = 1, polynomial drift: the classic_elbo KL term of one transition from scalars (the statements of k_kl_value's
+// scalar path with the closed-form moments) and the KL of the initial state (variational_cvi_sde.py:478-484), for the
+// mean sweep that adds the terms up on its way (k_mean_tiled, tile_sweeps.cuh).
+template <int DRIFT>
+__device__ __forceinline__ double kl_value_scalar_closed(const DriftParams& P, double Qp, double dt, double Ak,
+                                                         double bk, double cq, double mk, double Sk, bool& ok) {
+    const double Qq = cq * cq;
+    if (!(Qp > 0.0) || !(Sk > 0.0) || !(Qq > 0.0)) ok = false;
+    double cQp, iQp;
+    sqrt_rsqrt_fast(Qp, cQp, iQp);
+    const double Qpinv = iQp * iQp;
+    const double Cterm = -2.0 * log(fabs(cq) * iQp) - 1.0 + Qpinv * Qq;
+    const typename DriftStep1<DRIFT>::K kst = DriftStep1<DRIFT>::prepare(P, dt, Ak, bk);
+    double c0, c1, c2, c3;
+    DriftStep1<DRIFT>::taylor(kst, mk, c0, c1, c2, c3);
+    CubicMoments cm;
+    cm.template eval<false>(c0, c1, c2, c3, Sk);
+    return 0.5 * (Qpinv * cm.Ed2 + Cterm);
+}
+
+template <int D>
+__device__ __forceinline__ double kl_initial_state(const double* __restrict__ qmu0, const double* __restrict__ qcholP0,
+                                                   const double* __restrict__ pmu0,
+                                                   const double* __restrict__ pcholP0, int64_t b, bool& ok) {
+    constexpr int DD = D * D;
+    const Mat<D> cq0 = mat_load<D>(qcholP0 + b * DD), cp0 = mat_load<D>(pcholP0 + b * DD);
+    const Mat<D> Lq = chol(mmT(cq0, cq0), ok), Lp = chol(mmT(cp0, cp0), ok);
+    const Mat<D> Mq = trsm(Lp, Lq);
+    const Vec<D> diff = trsv(Lp, vec_load<D>(pmu0 + b * D) - vec_load<D>(qmu0 + b * D));
+    double fro = 0.0;
+#pragma unroll
+    for (int e = 0; e < DD; ++e) fro += Mq.a[e] * Mq.a[e];
+    return 0.5 * (fro + dot(diff, diff) - (double)D + logdet_from_chol(Lp) - logdet_from_chol(Lq));
+}
+
 // KL_q_p of classic_elbo (variational_cvi_sde.py:446-486): value only, with the reference's
 // element-wise square of the Cholesky factor (:452) standing in for Q_q.
 template <int DRIFT, int D, int H, int G, bool CLOSED = false>

@@ -18,6 +18,7 @@
 #include "common.cuh"
 #include "scan_elems.cuh"
 #include "sweeps.cuh"
+#include "kl_kernels.cuh"
 
 namespace vdp {
 
@@ -385,18 +386,35 @@ constexpr size_t marg_tiled_smem() {
 // Marginal means alone, m_{k+1} = A_k m_k + b_k (state_space_model.py:251): the forward sweep of the posterior
 // rebuild when the Cholesky factor of the precision is already at hand (the one naturals_to_ssm was computed from is
 // the factor of the same matrix the reference rebuilds from the state-space model).
-template <int D, int T, int L, int MODE>
+// DRIFT >= 0 (D = 1, polynomial drift, FULL mode): the sweep also has everything the KL term of classic_elbo
+// (variational_cvi_sde.py:446-486) needs once S_k and chol Q_k are staged beside A_k and b_k, so it adds the terms up
+// on its way -- per thread over its chunk, then a fixed tree over the CTA -- into partials[b, seg, tile]; the
+// separate pass over A, b, m again (k_kl_value) and the per-grid-point terms array are not needed then.
+struct MeanKlArgs {
+    DriftParams P;
+    double Qp = 0.0, dt = 0.0;              // q dt, dt
+    const double *Sd = nullptr, *cholQ = nullptr, *qcholP0 = nullptr, *pmu0 = nullptr, *pcholP0 = nullptr;
+    double* partials = nullptr;             // [B, nseg, tiles_per_seg], zeroed by the caller
+    int64_t* status = nullptr;
+    int tiles_per_seg = 0;
+};
+
+template <int D, int T, int L, int MODE, int DRIFT = -1>
 __global__ void __launch_bounds__(T)
 k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const double* __restrict__ mu0,
              double* __restrict__ m, int64_t B, int64_t N, int nseg, int64_t seg_len,
              const Vec<D>* __restrict__ carry_in, Vec<D>* __restrict__ init_out,
-             AffVecElem<D>* __restrict__ seg_elem) {
+             AffVecElem<D>* __restrict__ seg_elem, MeanKlArgs kl = MeanKlArgs()) {
     constexpr int DD = D * D, TL = T * L;
+    constexpr bool KL = (DRIFT >= 0) && (MODE == SWEEP_FULL);
+    static_assert(DRIFT < 0 || D == 1, "the fused KL terms are scalar");
     using Ops = AffVecOps<D>;
     extern __shared__ __align__(16) double smem[];
     double* sA = smem;                        // A of transition i               (TL)
     double* sb = sA + TL * DD;                // offsets -> m_{k+1}              (TL)
-    typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(sb + TL * D);
+    double* sS = sb + TL * D;                 // S of node i                     (TL, KL only)
+    double* sQ = sS + (KL ? TL : 0);          // chol Q of transition i          (TL, KL only)
+    typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(sQ + (KL ? TL : 0));
     const int64_t b = blockIdx.x / nseg;
     const int seg = (int)(blockIdx.x % nseg);
     const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
@@ -408,6 +426,10 @@ k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
         __syncthreads();
         stage_in<T>(sA, A + (b * N + tk) * DD, (int64_t)cnt * DD);
         stage_in<T>(sb, bo + (b * N + tk) * D, (int64_t)cnt * D);
+        if (KL) {
+            stage_in<T>(sS, kl.Sd + (b * (N + 1) + tk), (int64_t)cnt);
+            stage_in<T>(sQ, kl.cholQ + (b * N + tk), (int64_t)cnt);
+        }
         stage_wait();
         __syncthreads();
         if (seg == 0 && tk == 0) {
@@ -432,19 +454,44 @@ k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
         }
         Vec<D> mk = Ops::apply(excl, st);
         st = Ops::apply(total, st);
+        double kl_acc = 0.0;
         for (int t = 0; t < len; ++t) {
-            mk = vec_load<D>(sb + (k0 + t) * D) + mv(mat_load<D>(sA + (k0 + t) * DD), mk);
+            const Vec<D> bk = vec_load<D>(sb + (k0 + t) * D);
+            const Mat<D> Ak = mat_load<D>(sA + (k0 + t) * DD);
+            if constexpr (KL) {
+                bool ok = true;
+                kl_acc += kl_value_scalar_closed<(DRIFT < 0 ? 0 : DRIFT)>(kl.P, kl.Qp, kl.dt, Ak.a[0], bk.v[0],
+                                                                          sQ[k0 + t], mk.v[0], sS[k0 + t], ok);
+                if (!ok) report_not_pd(kl.status, b * (N + 1) + tk + k0 + t);
+            }
+            mk = bk + mv(Ak, mk);
             vec_store<D>(sb + (k0 + t) * D, mk);
         }
         __syncthreads();
         stage_out<T>(m + (b * (N + 1) + tk + 1) * D, sb, (int64_t)cnt * D);
+        if constexpr (KL) {
+            if (seg == 0 && tk == 0 && threadIdx.x == 0) {
+                bool ok = true;
+                kl_acc += kl_initial_state<D>(mu0, kl.qcholP0, kl.pmu0, kl.pcholP0, b, ok);
+                if (!ok) report_not_pd(kl.status, b * (N + 1));
+            }
+            sS[threadIdx.x] = kl_acc;          // (the staged S values have been consumed: barrier above)
+            __syncthreads();
+            for (int s2 = T / 2; s2 > 0; s2 >>= 1) {
+                if ((int)threadIdx.x < s2) sS[threadIdx.x] += sS[threadIdx.x + s2];
+                __syncthreads();
+            }
+            if (threadIdx.x == 0)
+                kl.partials[((int64_t)b * nseg + seg) * kl.tiles_per_seg + (tk - t0) / TL] = sS[0];
+        }
     }
     if (MODE != SWEEP_FULL && threadIdx.x == 0) seg_elem[b * nseg + seg] = seg_tot;
 }
 
-template <int D, int T, int L>
+template <int D, int T, int L, bool KL = false>
 constexpr size_t mean_tiled_smem() {
-    return ((size_t)T * L * D * D + (size_t)T * L * D) * sizeof(double) + (T / 32) * sizeof(AffVecElem<D>);
+    return ((size_t)T * L * D * D + (size_t)T * L * D + (KL ? 2 * (size_t)T * L : 0)) * sizeof(double) +
+           (T / 32) * sizeof(AffVecElem<D>);
 }
 
 

@@ -73,9 +73,14 @@ static inline bool cvi_ws_take(void* ws, size_t bytes, int64_t B, int64_t N, int
 
 // (F): sites -> q as an SSM -> marginals.   variational_cvi_sde.py:161-192 + gauss_markov.py:107-117
 // naturals_ready: the site-update kernel has already written the natural parameters into the workspace
-template <int D>
-static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t st, bool naturals_ready = false) {
+// DRIFT >= 0 with kl_partials != NULL: classic_elbo follows on the whole chain; where the mean sweep can add up the KL
+// terms on its way (tiled route, D = 1, polynomial drift in closed form) it does, and *kl_partials is the number of
+// partial sums per sequence it left in w.terms (0: run_elbo makes its own pass).
+template <int D, int DRIFT = -1>
+static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t st, bool naturals_ready = false,
+                         int64_t* kl_partials = nullptr) {
     const int64_t B = p.B, N = p.N;
+    if (kl_partials) *kl_partials = 0;
     if (!naturals_ready) {
         prof_mark(VDP_PHASE_SITES_TO_NAT, st);
         k_ssm_to_naturals<D><<<grid_for(B * (N + 1), kPtBlock), kPtBlock, 0, st>>>(
@@ -101,6 +106,22 @@ static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t 
     if (rc || ssm_only) return rc;
     if (lite) {
         prof_mark(VDP_PHASE_MARG_FWD, st);
+        if constexpr (DRIFT >= 0 && D == 1) {
+            if constexpr (DriftStep1<(DRIFT < 0 ? 0 : DRIFT)>::kCubic) {
+                if (kl_partials && !env_int("VDP_GH_QUADRATURE", 0) && !env_int("VDP_SEPARATE_KL_VALUE", 0)) {
+                    MeanKlArgs ka;
+                    ka.P = make_params(p.drift_params);
+                    ka.Qp = p.dt * p.q[0];
+                    ka.dt = p.dt;
+                    ka.Sd = p.fx_covs; ka.cholQ = p.qcholQ; ka.qcholP0 = p.qcholP0; ka.pmu0 = p.pmu0;
+                    ka.pcholP0 = p.pcholP0; ka.partials = w.terms; ka.status = p.status;
+                    if ((rc = run_mean_fwd_tiled<D, DRIFT>(p.qA, p.qb, p.qmu0, p.fx_mus, B, N, sc, st, &ka, kl_partials)))
+                        return rc;
+                    prof_mark(VDP_PHASE_END, st);
+                    return VDP_OK;
+                }
+            }
+        }
         if ((rc = run_mean_fwd_tiled<D>(p.qA, p.qb, p.qmu0, p.fx_mus, B, N, sc, st))) return rc;
         prof_mark(VDP_PHASE_END, st);
         return VDP_OK;
@@ -111,7 +132,7 @@ static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t 
 
 template <int DRIFT, int D>
 static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams& P, cudaStream_t st,
-                    int64_t node0 = 0, int64_t node1 = -1) {
+                    int64_t node0 = 0, int64_t node1 = -1, int64_t kl_partials = 0) {
     const int64_t B = p.B, N = p.N;
     constexpr int G = QuadGroup<D>::value;
     prof_mark(VDP_PHASE_ELBO, st);
@@ -123,6 +144,15 @@ static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams&
     VDP_CHECK_LAUNCH();
     bool closed = false;
     if constexpr (D == 1 && G == 1 && DriftStep1<DRIFT>::kCubic) closed = !env_int("VDP_GH_QUADRATURE", 0);
+    if (kl_partials > 0) {
+        // the mean sweep of the rebuild has left kl_partials partial sums per sequence in w.terms
+        k_reduce_terms<<<(unsigned)B, 256, 0, st>>>(w.terms, kl_partials, p.kl);
+        VDP_CHECK_LAUNCH();
+        k_elbo_combine<<<grid_for(B, kPtBlock), kPtBlock, 0, st>>>(p.ve, p.kl, p.elbo, B);
+        VDP_CHECK_LAUNCH();
+        prof_mark(VDP_PHASE_END, st);
+        return VDP_OK;
+    }
     if (cnt > 0 && closed) {
         if constexpr (D == 1 && G == 1 && DriftStep1<DRIFT>::kCubic) {
             k_kl_value<DRIFT, D, 20, G, true><<<grid_for(cnt * G, kPtBlock), kPtBlock, 0, st>>>(
@@ -203,9 +233,11 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
                                        st, node0, node1, nat)))
         return rc;
     if (stop_after_sites) { prof_mark(VDP_PHASE_END, st); return VDP_OK; }
-    if ((rc = run_posterior<D>(p, w, st, fuse_nat))) return rc;
+    const bool want_elbo = !(p.flags & VDP_FLAG_SKIP_ELBO);
+    int64_t kl_partials = 0;
+    if ((rc = run_posterior<D, DRIFT>(p, w, st, fuse_nat, (want_elbo && node1 < 0) ? &kl_partials : nullptr))) return rc;
     // (C) classic_elbo  variational_cvi_sde.py:339-352
-    if (!(p.flags & VDP_FLAG_SKIP_ELBO)) return run_elbo<DRIFT, D>(p, w, P, st);
+    if (want_elbo) return run_elbo<DRIFT, D>(p, w, P, st, 0, -1, kl_partials);
     return VDP_OK;
 }
 

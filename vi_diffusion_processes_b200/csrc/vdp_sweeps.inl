@@ -249,20 +249,32 @@ static int run_marg_fwd_tiled(const double* A, const double* b, const double* ch
 }
 
 // ---- marginal means alone (the posterior rebuild of the site update: the precision factor is already there) ----
-template <int D>
+// DRIFT >= 0 (D = 1, polynomial drift): the sweep also adds up the KL terms of classic_elbo (MeanKlArgs); kl->partials
+// receives *n_partials sums per sequence, to be added by k_reduce_terms.
+template <int D, int DRIFT = -1>
 static int run_mean_fwd_tiled(const double* A, const double* b, const double* mu0, double* m, int64_t B, int64_t N,
-                              SegScratch sc, cudaStream_t st) {
+                              SegScratch sc, cudaStream_t st, const MeanKlArgs* kl = nullptr,
+                              int64_t* n_partials = nullptr) {
     using C = TileCfg<D>;
     using Ops = AffVecOps<D>;
-    constexpr int L = 2 * C::Lm;
+    constexpr bool KL = DRIFT >= 0;
+    constexpr int L = (D == 1) ? C::Lm : 2 * C::Lm;   // the same tile (and rounding order of the means) with and without KL
     constexpr size_t smem = mean_tiled_smem<D, C::T, L>();
+    constexpr size_t smem_full = mean_tiled_smem<D, C::T, L, KL>();
     const SegPlan pl = plan_segments(B, N, C::T * L, sc.size > 0);
     const unsigned grid = (unsigned)(B * pl.nseg);
+    MeanKlArgs ka;
+    if (KL) {
+        ka = *kl;
+        ka.tiles_per_seg = (int)((pl.seg_len + C::T * L - 1) / (C::T * L));
+        *n_partials = (int64_t)pl.nseg * ka.tiles_per_seg;
+        VDP_CHECK_CUDA(cudaMemsetAsync(ka.partials, 0, (size_t)B * *n_partials * sizeof(double), st));
+    }
     int rc;
-    if ((rc = allow_smem(k_mean_tiled<D, C::T, L, SWEEP_FULL>, smem))) return rc;
+    if ((rc = allow_smem(k_mean_tiled<D, C::T, L, SWEEP_FULL, DRIFT>, smem_full))) return rc;
     if (pl.nseg == 1) {
-        k_mean_tiled<D, C::T, L, SWEEP_FULL><<<grid, C::T, smem, st>>>(A, b, mu0, m, B, N, 1, pl.seg_len, nullptr, nullptr,
-                                                                     nullptr);
+        k_mean_tiled<D, C::T, L, SWEEP_FULL, DRIFT><<<grid, C::T, smem_full, st>>>(A, b, mu0, m, B, N, 1, pl.seg_len,
+                                                                                 nullptr, nullptr, nullptr, ka);
         VDP_CHECK_LAUNCH();
         return VDP_OK;
     }
@@ -275,8 +287,8 @@ static int run_mean_fwd_tiled(const double* A, const double* b, const double* mu
                                                                     init, el);
     VDP_CHECK_LAUNCH();
     if ((rc = launch_seg_scan<Ops>(el, init, carry, B, pl.nseg, 0, st))) return rc;
-    k_mean_tiled<D, C::T, L, SWEEP_FULL><<<grid, C::T, smem, st>>>(A, b, mu0, m, B, N, pl.nseg, pl.seg_len, carry, nullptr,
-                                                                 nullptr);
+    k_mean_tiled<D, C::T, L, SWEEP_FULL, DRIFT><<<grid, C::T, smem_full, st>>>(A, b, mu0, m, B, N, pl.nseg, pl.seg_len,
+                                                                             carry, nullptr, nullptr, ka);
     VDP_CHECK_LAUNCH();
     return VDP_OK;
 }
