@@ -449,15 +449,19 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
 // D = 1, polynomial drift: the classic_elbo KL term of one transition from scalars (the statements of k_kl_value's
 // scalar path with the closed-form moments) and the KL of the initial state (variational_cvi_sde.py:478-484), for the
 // mean sweep that adds the terms up on its way (k_mean_tiled, tile_sweeps.cuh).
+// The log-determinant part, -2 log(|chol Q_q| / chol Q_p), is left to the caller as the factor `ratio` of a running
+// product: one log per chunk of transitions instead of one per transition.
 template <int DRIFT>
 __device__ __forceinline__ double kl_value_scalar_closed(const DriftParams& P, double Qp, double dt, double Ak,
-                                                         double bk, double cq, double mk, double Sk, bool& ok) {
+                                                         double bk, double cq, double mk, double Sk, bool& ok,
+                                                         double& ratio) {
     const double Qq = cq * cq;
     if (!(Qp > 0.0) || !(Sk > 0.0) || !(Qq > 0.0)) ok = false;
     double cQp, iQp;
     sqrt_rsqrt_fast(Qp, cQp, iQp);
     const double Qpinv = iQp * iQp;
-    const double Cterm = -2.0 * log(fabs(cq) * iQp) - 1.0 + Qpinv * Qq;
+    ratio = fabs(cq) * iQp;
+    const double Cterm = -1.0 + Qpinv * Qq;
     const typename DriftStep1<DRIFT>::K kst = DriftStep1<DRIFT>::prepare(P, dt, Ak, bk);
     double c0, c1, c2, c3;
     DriftStep1<DRIFT>::taylor(kst, mk, c0, c1, c2, c3);

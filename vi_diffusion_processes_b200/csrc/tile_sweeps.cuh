@@ -432,6 +432,15 @@ k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
         }
         stage_wait();
         __syncthreads();
+        if (tk + TL < t1) {   // next tile on its way into L2
+            const int64_t nk = tk + TL, ncnt = min((int64_t)TL, t1 - nk);
+            prefetch_range<T>(A + (b * N + nk) * DD, ncnt * DD);
+            prefetch_range<T>(bo + (b * N + nk) * D, ncnt * D);
+            if (KL) {
+                prefetch_range<T>(kl.Sd + (b * (N + 1) + nk), ncnt);
+                prefetch_range<T>(kl.cholQ + (b * N + nk), ncnt);
+            }
+        }
         if (seg == 0 && tk == 0) {
             st = vec_load<D>(mu0 + b * D);
             if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = st;
@@ -454,19 +463,22 @@ k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
         }
         Vec<D> mk = Ops::apply(excl, st);
         st = Ops::apply(total, st);
-        double kl_acc = 0.0;
+        double kl_acc = 0.0, kl_ratio = 1.0;   // (L <= 9 ratios of O(1) each: the product stays far from the range ends)
         for (int t = 0; t < len; ++t) {
             const Vec<D> bk = vec_load<D>(sb + (k0 + t) * D);
             const Mat<D> Ak = mat_load<D>(sA + (k0 + t) * DD);
             if constexpr (KL) {
                 bool ok = true;
+                double r;
                 kl_acc += kl_value_scalar_closed<(DRIFT < 0 ? 0 : DRIFT)>(kl.P, kl.Qp, kl.dt, Ak.a[0], bk.v[0],
-                                                                          sQ[k0 + t], mk.v[0], sS[k0 + t], ok);
-                if (!ok) report_not_pd(kl.status, b * (N + 1) + tk + k0 + t);
+                                                                          sQ[k0 + t], mk.v[0], sS[k0 + t], ok, r);
+                kl_ratio *= r;
+                if (!ok) { report_not_pd(kl.status, b * (N + 1) + tk + k0 + t); kl_ratio = 1.0; }
             }
             mk = bk + mv(Ak, mk);
             vec_store<D>(sb + (k0 + t) * D, mk);
         }
+        if (KL && len > 0) kl_acc -= log(kl_ratio);      // sum of 0.5 (-2 log ratio_t)
         __syncthreads();
         stage_out<T>(m + (b * (N + 1) + tk + 1) * D, sb, (int64_t)cnt * D);
         if constexpr (KL) {
