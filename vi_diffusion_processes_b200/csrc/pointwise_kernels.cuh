@@ -236,13 +236,15 @@ __global__ void k_data_site_update(const double* __restrict__ fx_mus, const int6
     mat_store<D>(d2 + i * DD, (1.0 - lr) * o2 + lr * gS);
 }
 
-// variational_expectation (variational_cvi_sde.py:319-337): one thread per sequence, fixed order
+// variational_expectation (variational_cvi_sde.py:319-337): one warp per sequence, the lanes stride over the
+// observations and their partial sums are added in a fixed shuffle tree (deterministic)
 template <int D>
 __global__ void k_variational_expectation(const double* __restrict__ fx_mus, const double* __restrict__ fx_covs,
                                           const int64_t* __restrict__ obs_idx, const double* __restrict__ obs_y,
                                           Mat<D> lik_chol, double* __restrict__ ve, int64_t B, int64_t N,
                                           int64_t n_obs) {
-    const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t b = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / 32;
+    const int lane = threadIdx.x % 32;
     if (b >= B) return;
     constexpr int DD = D * D;
     const Mat<D> inv = chol_inverse(lik_chol);
@@ -250,7 +252,7 @@ __global__ void k_variational_expectation(const double* __restrict__ fx_mus, con
 #pragma unroll
     for (int e = 0; e < D; ++e) logdet += log(fabs(lik_chol(e, e)));
     double acc = 0.0;
-    for (int64_t j = 0; j < n_obs; ++j) {
+    for (int64_t j = lane; j < n_obs; j += 32) {
         const int64_t i = b * n_obs + j;
         const int64_t node = b * (N + 1) + obs_idx[i];
         const Vec<D> z = trsv(lik_chol, vec_load<D>(obs_y + i * D) - vec_load<D>(fx_mus + node * D));
@@ -260,7 +262,9 @@ __global__ void k_variational_expectation(const double* __restrict__ fx_mus, con
         for (int e = 0; e < DD; ++e) tr += inv.a[e] * S.a[e];
         acc += -0.5 * tr + (-0.5 * dot(z, z) - logdet - 0.5 * D * 1.8378770664093453);
     }
-    ve[b] = acc;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if (lane == 0) ve[b] = acc;
 }
 
 

@@ -170,7 +170,7 @@ static int vgp_elbo(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st) {
     k_reduce_terms<<<(unsigned)p.B, 256, 0, st>>>(w.terms, p.N, w.esde);
     VDP_CHECK_LAUNCH();
     if (p.n_obs > 0) {
-        k_variational_expectation<D><<<grid_for(p.B, kSeqBlock), kSeqBlock, 0, st>>>(
+        k_variational_expectation<D><<<grid_for(p.B * 32, kPtBlock), kPtBlock, 0, st>>>(
             p.m, p.S, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), w.ve, p.B, p.N, p.n_obs);
         VDP_CHECK_LAUNCH();
     } else {
