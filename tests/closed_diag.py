@@ -1,11 +1,11 @@
-"""Diagnostic: closed-form moments vs Gauss-Hermite loops vs the NumPy oracle, update by update (small noise)."""
+"""(test infrastructure, not collected by pytest) Diagnostic: closed-form moments vs Gauss-Hermite loops vs the NumPy oracle, update by update (small noise)."""
 import os
 import sys
 
 import numpy as np
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from oracle import models_np as M      # noqa: E402  (checker)
 from oracle import sde_np as S         # noqa: E402

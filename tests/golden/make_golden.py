@@ -8,7 +8,7 @@ image), so these vectors pin the ORACLE, not TensorFlow: they guard the oracle a
 and give the CUDA path fixed targets that do not depend on re-running the oracle (GPU test).  Run in the build
 container only (it reads /root/reference); the GPU box uses the committed files.
 
-    python tools/make_golden.py
+    python tests/golden/make_golden.py
 """
 import io
 import os
@@ -17,7 +17,7 @@ import zipfile
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from oracle import models_np as M  # noqa: E402
 from oracle import sde_np as S  # noqa: E402

@@ -1,5 +1,6 @@
 #!/usr/bin/env python
 """
+(test infrastructure, not collected by pytest: it runs the oracle as the checker and as the CPU baseline)
 BASELINE.md section 5 rows for configs C1-C3 (the golden fixtures made from the reference's shipped data files):
 per config, on cuda:0 -- max relative error of ELBO / marginals / sites against the fixture, device time of one
 CVI-DP site update and of one VDP sweep (CUDA events, sites after the 3 fixture updates), and the NumPy oracle's time

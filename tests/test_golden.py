@@ -1,5 +1,5 @@
 """
-Golden fixtures (tests/golden/*.npz, made by tools/make_golden.py from the data files the reference ships):
+Golden fixtures (tests/golden/*.npz, made by tests/golden/make_golden.py from the data files the reference ships):
   * CPU: the oracle still reproduces them (regression guard for the checker itself);
   * GPU: the CUDA path, through the C ABI, reproduces them to 1e-9 without running the oracle.
 """
@@ -35,7 +35,7 @@ def relerr(a, b, scale=None):
 
 
 def test_fixtures_exist():
-    assert len(GOLDEN) >= 3, "run tools/make_golden.py"
+    assert len(GOLDEN) >= 3, "run tests/golden/make_golden.py"
 
 
 @pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])

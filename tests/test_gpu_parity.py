@@ -531,7 +531,7 @@ def test_closed_form_moments_equal_gauss_hermite(monkeypatch, drift, params, noi
     variances of 1e-6 next to the observations, where an expansion about zero instead of the mean would cancel).
     With that noise the girsanov sites next to an observation are themselves ill-conditioned (the gradient with
     respect to the expectation parameters carries S^-1 ~ 1e6; the NumPy oracle and either variant differ by 1e-4
-    there, tools/exp/closed_diag.py, with the closed form the closer one), so the sites are compared on the scale of
+    there, tests/closed_diag.py, with the closed form the closer one), so the sites are compared on the scale of
     the total naturals, data sites included -- what the posterior is built from."""
     from vi_diffusion_processes_b200.markovflow.sde import sde as sde_mod
     from vi_diffusion_processes_b200.cvi import CviEngine
