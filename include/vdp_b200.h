@@ -138,6 +138,25 @@ int vdp_ssm_marginals(const double* A, const double* b, const double* cholQ, con
                       void* workspace, size_t workspace_bytes,
                       int64_t B, int64_t N, int D, int64_t* status, void* stream);
 
+/* Allocation-free variant of vdp_ssm_marginals.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same inputs, outputs and results as vdp_ssm_marginals, but the scratch (the Cholesky
+ * factor of the rebuilt precision and the segment carries) is a file-scope `static __device__` array of
+ * VDP_STATIC_SCRATCH_BYTES (16 MiB) inside the library; every GPU that loads the library holds it until exit.
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ *   Limit: 8 (2 N + 1) B D^2 <= VDP_STATIC_FACTOR_BYTES (8 MiB; each of the two factor arrays rounded up to
+ *   256 B), e.g. B (N + 1) <= 524 288 grid points at D = 1.  Larger problems return VDP_E_WORKSPACE
+ *   (vdp_last_error() names the limit); use vdp_ssm_marginals with a caller-owned workspace for those.
+ *   All calls on one GPU share the array: calls that overlap on the GPU (different streams, or several host
+ *   threads) RACE on it -- serialise them.  The array keeps the last call's contents; nothing in it has to start
+ *   at zero (every word a kernel reads is written earlier in the same call). */
+#define VDP_STATIC_FACTOR_BYTES ((size_t)8 << 20)
+#define VDP_STATIC_SCRATCH_BYTES ((size_t)16 << 20)
+size_t vdp_static_scratch_bytes(void);
+int vdp_ssm_marginals_static(const double* A, const double* b, const double* cholQ, const double* mu0,
+                             const double* cholP0, double* m, double* Sd,
+                             int64_t B, int64_t N, int D, int64_t* status, void* stream);
+
 /* ssm_to_expectations / expectations_to_ssm_params  (ssm_gaussian_transformations.py:32-178) */
 int vdp_ssm_to_expectations(const double* A, const double* m, const double* Sd,
                             double* e1, double* ed, double* es, int64_t B, int64_t N, int D, void* stream);

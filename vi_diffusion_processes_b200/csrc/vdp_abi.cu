@@ -266,3 +266,4 @@ extern "C" int vdp_euler_maruyama(int drift_id, const double* params_host, const
 #include "vdp_host.inl"
 #include "vdp_vgp.inl"
 #include "vdp_dist.inl"
+#include "vdp_noalloc.inl"
