@@ -596,7 +596,7 @@ __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
 }
 
 // deterministic per-sequence sum of terms[b, 0..n) (+ optional extra[b]) : one block per sequence
-__global__ void k_reduce_terms(const double* __restrict__ terms, int64_t n, double* __restrict__ out) {
+static __global__ void k_reduce_terms(const double* __restrict__ terms, int64_t n, double* __restrict__ out) {
     __shared__ double sh[256];
     const int64_t b = blockIdx.x;
     double acc = 0.0;

@@ -94,7 +94,7 @@ k_drift_param_grad(DriftParams P, Mat<D> W, double c_x, double c_f, double a_sig
 }
 
 // grads[b, p] = scale * sum over the blocks of sequence b (fixed order); entries p >= np are set to 0
-__global__ void k_reduce_partials(const double* __restrict__ partials, int64_t nbx, int np, double scale,
+static __global__ void k_reduce_partials(const double* __restrict__ partials, int64_t nbx, int np, double scale,
                                   double* __restrict__ grads) {
     __shared__ double sh[256];
     const int64_t b = blockIdx.x;

@@ -12,10 +12,10 @@
 
 namespace vdp {
 
-__constant__ double c_gh_x10[10] = VDP_GH_X_10;
-__constant__ double c_gh_w10[10] = VDP_GH_W_10;
-__constant__ double c_gh_x20[20] = VDP_GH_X_20;
-__constant__ double c_gh_w20[20] = VDP_GH_W_20;
+static __constant__ double c_gh_x10[10] = VDP_GH_X_10;
+static __constant__ double c_gh_w10[10] = VDP_GH_W_10;
+static __constant__ double c_gh_x20[20] = VDP_GH_X_20;
+static __constant__ double c_gh_w20[20] = VDP_GH_W_20;
 
 template <int H> __device__ __forceinline__ double gh_x(int i) { return H == 10 ? c_gh_x10[i] : c_gh_x20[i]; }
 template <int H> __device__ __forceinline__ double gh_w(int i) { return H == 10 ? c_gh_w10[i] : c_gh_w20[i]; }
@@ -23,10 +23,10 @@ template <int H> __device__ __forceinline__ double gh_w(int i) { return H == 10 
 // The same tables in global memory for lookups whose index differs from lane to lane (D >= 2: the lanes of a
 // group hold different nodes).  A constant-bank read is serialised once per distinct address in the warp (up
 // to 20 replays per lookup here); a read-only global load of a 160-byte table is one or two L1 wavefronts.
-__device__ const double d_gh_x10[10] = VDP_GH_X_10;
-__device__ const double d_gh_w10[10] = VDP_GH_W_10;
-__device__ const double d_gh_x20[20] = VDP_GH_X_20;
-__device__ const double d_gh_w20[20] = VDP_GH_W_20;
+static __device__ const double d_gh_x10[10] = VDP_GH_X_10;
+static __device__ const double d_gh_w10[10] = VDP_GH_W_10;
+static __device__ const double d_gh_x20[20] = VDP_GH_X_20;
+static __device__ const double d_gh_w20[20] = VDP_GH_W_20;
 template <int H> __device__ __forceinline__ double gh_x_div(int i) { return __ldg(H == 10 ? &d_gh_x10[i] : &d_gh_x20[i]); }
 template <int H> __device__ __forceinline__ double gh_w_div(int i) { return __ldg(H == 10 ? &d_gh_w10[i] : &d_gh_w20[i]); }
 

@@ -1,5 +1,22 @@
 // C ABI of libvdp_b200 (see include/vdp_b200.h).  Host-side launch logic only; kernels live in the
-// .cuh files next to this one.  Compiled for sm_100a.
+// .cuh files next to this one.  Compiled for sm_100a as several translation units (tu_*.cu), each of which defines
+// one VDP_EMIT_* macro and includes this file: the macro selects which extern "C" entry points (and hence which
+// kernel instantiations) the unit emits, so that the units build in parallel.
+#ifndef VDP_EMIT_CORE
+#define VDP_EMIT_CORE 0
+#endif
+#ifndef VDP_EMIT_CVI
+#define VDP_EMIT_CVI 0
+#endif
+#ifndef VDP_EMIT_PRIOR
+#define VDP_EMIT_PRIOR 0
+#endif
+#ifndef VDP_EMIT_VGP
+#define VDP_EMIT_VGP 0
+#endif
+#ifndef VDP_EMIT_DIST
+#define VDP_EMIT_DIST 0
+#endif
 #include <stdarg.h>
 #include <string.h>
 
@@ -20,7 +37,9 @@
 
 namespace vdp {
 
-static thread_local char g_error[512] = "";
+// library-wide state lives in the core translation unit (the library is compiled as several units, see tu_*.cu)
+#if VDP_EMIT_CORE
+thread_local char g_error[512] = "";
 
 void set_error(const char* fmt, ...) {
     va_list ap;
@@ -28,6 +47,9 @@ void set_error(const char* fmt, ...) {
     vsnprintf(g_error, sizeof(g_error), fmt, ap);
     va_end(ap);
 }
+#else
+extern thread_local char g_error[512];
+#endif
 
 constexpr int kSeqBlock = 32;   // threads per block for one-thread-per-sequence sweeps (spread over SMs)
 constexpr int kPtBlock = 128;   // threads per block for pointwise kernels
@@ -64,7 +86,11 @@ struct Profiler {
     std::vector<int> phase;   // phase[i] = phase that starts at event i
     size_t used = 0;
 };
-static Profiler g_prof;
+#if VDP_EMIT_CORE
+Profiler g_prof;
+#else
+extern Profiler g_prof;
+#endif
 static inline void prof_mark(int phase, cudaStream_t st) {
     if (!g_prof.on) return;
     if (g_prof.used == g_prof.pool.size()) {
@@ -85,6 +111,7 @@ static inline void prof_mark(int phase, cudaStream_t st) {
 
 using namespace vdp;
 
+#if VDP_EMIT_CORE
 extern "C" {
 
 int vdp_version(void) { return 100; }
@@ -240,9 +267,11 @@ int vdp_btd_conditional_precisions(const double* As, const double* Kd, const dou
 }
 
 }  // extern "C"
+#endif  // VDP_EMIT_CORE
 
 #include "vdp_fused.inl"
 
+#if VDP_EMIT_CORE
 extern "C" int vdp_euler_maruyama(int drift_id, const double* params_host, const double* q_host, const double* x0,
                                   const double* time_grid, const double* noise, unsigned long long seed, double* out,
                                   int64_t B, int64_t n, int D, int64_t* status, void* stream) {
@@ -260,10 +289,19 @@ extern "C" int vdp_euler_maruyama(int drift_id, const double* params_host, const
     VDP_CHECK_LAUNCH();
     return VDP_OK;
 }
+#endif  // VDP_EMIT_CORE
 
 #include "vdp_cvi.inl"
+#if VDP_EMIT_PRIOR
 #include "vdp_prior.inl"
+#endif
+#if VDP_EMIT_CVI
 #include "vdp_host.inl"
+#endif
+#if VDP_EMIT_VGP
 #include "vdp_vgp.inl"
+#endif
+#if VDP_EMIT_DIST
 #include "vdp_dist.inl"
 #include "vdp_noalloc.inl"
+#endif

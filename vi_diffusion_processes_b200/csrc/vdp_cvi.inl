@@ -1,5 +1,5 @@
 // CVI-DP entry points: KL + gradient, the fused site update and classic_elbo
-// (included at the end of vdp_abi.cu after vdp_fused.inl).
+// (included at the end of vdp_all.inl after vdp_fused.inl).
 
 namespace vdp {
 
@@ -39,7 +39,7 @@ static int launch_kl_grad(const DriftParams& P, const double* q_host, double dt,
     return VDP_OK;
 }
 
-__global__ void k_elbo_combine(const double* __restrict__ ve, const double* __restrict__ kl,
+static __global__ void k_elbo_combine(const double* __restrict__ ve, const double* __restrict__ kl,
                                double* __restrict__ elbo, int64_t B) {
     const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (b < B) elbo[b] = ve[b] - kl[b];
@@ -254,6 +254,7 @@ static int check_problem(const vdp_cvi_problem* p) {
 
 }  // namespace vdp
 
+#if VDP_EMIT_CVI
 extern "C" {
 
 size_t vdp_cvi_kl_workspace(int64_t B, int64_t N, int D) { (void)D; return padded((size_t)B * (N + 1)); }
@@ -344,3 +345,4 @@ int vdp_cvi_elbo(const vdp_cvi_problem* p, void* stream) {
 }
 
 }  // extern "C"
+#endif  // VDP_EMIT_CVI

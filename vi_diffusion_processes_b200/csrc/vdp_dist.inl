@@ -10,7 +10,7 @@
 //
 // The backward half of naturals_to_ssm_params has two dependent recursions (Sigma, then y through A(Sigma)):
 // stage 0 summarises Sigma, stage 1 (given the gathered stage-0 blobs) summarises y, finish needs both.
-// Included at the end of vdp_abi.cu.  B = 1 (one sequence); local arrays carry the halo slots documented in
+// Included at the end of vdp_all.inl.  B = 1 (one sequence); local arrays carry the halo slots documented in
 // include/vdp_b200.h.
 
 namespace vdp {

@@ -1,4 +1,4 @@
-// Fused-level entry points of the C ABI (included at the end of vdp_abi.cu; one translation unit so the
+// Fused-level entry points of the C ABI (included at the end of vdp_all.inl; one translation unit so the
 // constant-memory quadrature tables exist once).
 
 namespace vdp {
@@ -63,6 +63,7 @@ static int run_marginals(const double* A, const double* b, const double* cholQ, 
 
 }  // namespace vdp
 
+#if VDP_EMIT_CORE
 extern "C" {
 
 int vdp_gh_expect(int drift_id, const double* params_host, const double* m, const double* S, int H, double* Ef,
@@ -233,3 +234,4 @@ int vdp_ssm_natgrad_step(double* A, double* b, double* cholP0, double* cholQ, do
 }
 
 }  // extern "C"
+#endif  // VDP_EMIT_CORE

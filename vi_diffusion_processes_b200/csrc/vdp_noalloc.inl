@@ -1,4 +1,4 @@
-// Allocation-free variant of vdp_ssm_marginals (included at the end of vdp_abi.cu).
+// Allocation-free variant of vdp_ssm_marginals (included at the end of vdp_all.inl).
 //
 // No counterpart in the reference: added for callers that cannot call
 // cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch the sweeps need

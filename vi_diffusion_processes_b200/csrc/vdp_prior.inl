@@ -1,5 +1,5 @@
 // Prior-parameter learning entry points: gradients with respect to the drift parameters of
-// KL_q_p, of -VE through the re-linearised prior, and of E_sde.  Included at the end of vdp_abi.cu.
+// KL_q_p, of -VE through the re-linearised prior, and of E_sde.  Included at the end of vdp_all.inl.
 
 namespace vdp {
 

@@ -1,6 +1,6 @@
 // Host-side launch logic of the four time sweeps: choice between the thread-per-sequence kernels
 // (btd_kernels.cuh; many short sequences) and the parallel-in-time tiled kernels (tile_sweeps.cuh), and
-// the segment plan of the latter.  Included by vdp_abi.cu before vdp_fused.inl.
+// the segment plan of the latter.  Included by vdp_all.inl before vdp_fused.inl.
 
 namespace vdp {
 

@@ -1,5 +1,5 @@
 // VDP entry points (VariationalMarkovGP, vi_sde.py): forward pass, Lagrange sweep, parameter update,
-// initial-state update, ELBO and the fused trainer iteration.  Included at the end of vdp_abi.cu.
+// initial-state update, ELBO and the fused trainer iteration.  Included at the end of vdp_all.inl.
 
 namespace vdp {
 
