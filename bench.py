@@ -188,6 +188,31 @@ def phase_bytes_per_step(name, D):
     return 8 * (v * D + m * D * D)
 
 
+def parity_check(eng, grid, idx, y, n_updates, n_seq=4):
+    """First `n_seq` sequences of the resident engine against the C port of the oracle after the same `n_updates`
+    site updates (checker only: never inside a timed region)."""
+    from oracle import c_port
+    from oracle.sde_np import DRIFT_DW
+    n_seq = min(n_seq, idx.shape[0])
+    ref = c_port.CBatchedCVISitesSDE1D(DRIFT_DW, DW_PARAMS, 1.0, grid, idx[:n_seq], y[:n_seq], NOISE_STD, X0_MU, X0_COV,
+                                       threads=min(n_seq, len(os.sched_getaffinity(0))))
+    for _ in range(n_updates):
+        elbo = ref.site_update(LR, LR)
+
+    def rel(a, b):
+        a = a.detach().cpu().numpy()
+        return float(np.abs(a - b).max() / np.abs(b).max())
+    out = {"sequences": n_seq, "updates": n_updates, "checker": "oracle/cvi_d1.c",
+           "max_rel_elbo": rel(eng.elbo[:n_seq], elbo),
+           "max_rel_marginal_mean": rel(eng.fx_mus[:n_seq, :, 0], ref.fx_mus),
+           "max_rel_marginal_cov": rel(eng.fx_covs[:n_seq, :, 0, 0], ref.fx_covs),
+           "max_rel_sites_unscaled": {"g1": rel(eng.g1[:n_seq, :, 0], ref.g1), "gd": rel(eng.gd[:n_seq, :, 0, 0], ref.gd),
+                                      "gs": rel(eng.gs[:n_seq, :, 0, 0], ref.gs)},
+           "tolerance": 1e-9}
+    out["ok"] = bool(max(out["max_rel_elbo"], out["max_rel_marginal_mean"], out["max_rel_marginal_cov"]) < 1e-9)
+    return out
+
+
 def run_ours(args):
     import ctypes as C
     import torch
@@ -254,6 +279,12 @@ def run_ours(args):
         sampler.start()
     t_load = time.perf_counter()
     ms_total = timed(step_resident, args.steps, args.warmup)
+    # self-check of the state the timed updates produced (outside the timed region): the first 4 sequences after
+    # the same number of updates on the CPU checker (oracle/cvi_d1.c).  Sequences are independent, so a 4-sequence
+    # CPU run reproduces them.  Bar: 1e-9 relative on ELBO and marginals; a miss makes the run exit non-zero.
+    parity = None
+    if rank == 0 and not args.no_check:
+        parity = parity_check(eng, grid, idx, y, 3 + args.warmup + args.steps)
     # per-phase device times from a second pass with the library's phase timer on (it serialises the update on one
     # stream, so it is kept out of the timed region above)
     lib.vdp_profile_enable(1)
@@ -278,7 +309,7 @@ def run_ours(args):
     eng.check_status()
     if args.quick:
         if rank == 0:
-            print(json.dumps({"ms_per_step": ms_total / args.steps, "ms_per_step_gh_loops": ms_gh / args.steps,
+            print(json.dumps({"parity_check": parity, "ms_per_step": ms_total / args.steps, "ms_per_step_gh_loops": ms_gh / args.steps,
                               "ms_per_step_gh_loops_no_carry": ms_gh_full / args.steps, "phases": {
                 nm: {"ms_per_launch": ph_ms[i] / max(1, ph_n[i])} for i, nm in enumerate(_lib.PHASES)}}))
         if world > 1:
@@ -347,6 +378,7 @@ def run_ours(args):
                             "achieved": value * ALGO_BYTES_PER_STEP_D1 / world / 1e9, "peak": peak, "unit": "GB/s",
                             "frac": value * ALGO_BYTES_PER_STEP_D1 / world / 1e9 / peak},
         "phases": phases,
+        "parity_check": parity,
         "cpu_baseline": {"value": cpu_val, "unit": "grid-steps/s", "cores": cpu_cores, "kind": "port",
                          "sample": f"C/OpenMP restatement of the oracle (oracle/cvi_d1.c, gcc -O2), {cpu_cores} "
                                    f"threads x 64 sequences x {N} grid steps x 10 site updates, {cpu_s:.1f} s",
@@ -358,6 +390,8 @@ def run_ours(args):
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+    if parity is not None and not parity["ok"]:
+        raise SystemExit("bench.py: parity check against the CPU oracle failed: %s" % json.dumps(parity))
 
 
 def run_vdp(args):
@@ -434,6 +468,7 @@ def main():
     ap.add_argument("--seqs", type=int, default=4096, help="sequences per GPU")
     ap.add_argument("--grid", type=int, default=10000, help="grid steps per sequence")
     ap.add_argument("--quick", action="store_true", help="tuning runs: resident timing and phases only")
+    ap.add_argument("--no-check", action="store_true", help="skip the parity self-check against the CPU oracle")
     ap.add_argument("--chunk", type=int, default=256, help="sequences per chunk of the host-buffer pipeline")
     ap.add_argument("--ref-seqs", type=int, default=64, help="sequences per host core in the bounded CPU sample")
     args = ap.parse_args()

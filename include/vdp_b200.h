@@ -138,6 +138,31 @@ int vdp_ssm_marginals(const double* A, const double* b, const double* cholQ, con
                       void* workspace, size_t workspace_bytes,
                       int64_t B, int64_t N, int D, int64_t* status, void* stream);
 
+/* StateSpaceModel.kl_divergence  (state_space_model.py:528-593): kl[b] = KL(dist1 || dist2) of two state-space
+ * models with the same shapes, by the reference's route: marginals of dist1, precision of dist2 and its banded
+ * Cholesky factor, trace over the block tri-diagonal band, log-determinants from the models' Cholesky factors.
+ * workspace: vdp_ssm_kl_divergence_workspace(B,N,D) bytes */
+size_t vdp_ssm_kl_divergence_workspace(int64_t B, int64_t N, int D);
+int vdp_ssm_kl_divergence(const double* A1, const double* b1, const double* cholQ1, const double* mu01,
+                          const double* cholP01, const double* A2, const double* b2, const double* cholQ2,
+                          const double* mu02, const double* cholP02, double* kl,
+                          void* workspace, size_t workspace_bytes,
+                          int64_t B, int64_t N, int D, int64_t* status, void* stream);
+
+/* StateSpaceModel.log_pdf  (state_space_model.py:485-526): states [S,B,N+1,D] (S sample trajectories per
+ * sequence) -> out [S,B] = log p(x_0) + sum_k log p(x_{k+1} | x_k).  workspace: vdp_ssm_log_pdf_workspace bytes */
+size_t vdp_ssm_log_pdf_workspace(int64_t S, int64_t B, int64_t N);
+int vdp_ssm_log_pdf(const double* A, const double* b, const double* cholQ, const double* mu0, const double* cholP0,
+                    const double* states, double* out, void* workspace, size_t workspace_bytes,
+                    int64_t S, int64_t B, int64_t N, int D, void* stream);
+
+/* StateSpaceModel.sample  (state_space_model.py:298-324): out [S,B,N+1,D] = A_inv_block^-1 (offsets + chol eps),
+ * i.e. x_0 = mu0 + cholP0 eps_0, x_{k+1} = A_k x_k + b_k + cholQ_k eps_{k+1}.  eps: standard normals [S,B,N+1,D]
+ * used in place of the generator (NULL = Philox4x32-10 with `seed`, sub-sequence = s B + b). */
+int vdp_ssm_sample(const double* A, const double* b, const double* cholQ, const double* mu0, const double* cholP0,
+                   const double* eps, unsigned long long seed, double* out,
+                   int64_t S, int64_t B, int64_t N, int D, void* stream);
+
 /* Allocation-free variant of vdp_ssm_marginals.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  Same inputs, outputs and results as vdp_ssm_marginals, but the scratch (the Cholesky

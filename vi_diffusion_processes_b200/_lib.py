@@ -114,6 +114,11 @@ SIGNATURES = {
     "vdp_naturals_to_ssm": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, i64, i64, C.c_int, vp, vp]),
     "vdp_ssm_marginals_workspace": (C.c_size_t, [i64, i64, C.c_int]),
     "vdp_ssm_marginals": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, i64, i64, C.c_int, vp, vp]),
+    "vdp_ssm_kl_divergence_workspace": (C.c_size_t, [i64, i64, C.c_int]),
+    "vdp_ssm_kl_divergence": (C.c_int, [vp] * 11 + [vp, C.c_size_t, i64, i64, C.c_int, vp, vp]),
+    "vdp_ssm_log_pdf_workspace": (C.c_size_t, [i64, i64, i64]),
+    "vdp_ssm_log_pdf": (C.c_int, [vp] * 7 + [vp, C.c_size_t, i64, i64, i64, C.c_int, vp]),
+    "vdp_ssm_sample": (C.c_int, [vp] * 6 + [C.c_uint64, vp, i64, i64, i64, C.c_int, vp]),
     "vdp_static_scratch_bytes": (C.c_size_t, []),
     "vdp_ssm_marginals_static": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, i64, i64, C.c_int, vp, vp]),
     "vdp_ssm_to_expectations": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i64, C.c_int, vp]),

@@ -155,10 +155,9 @@ __global__ void k_linearize(DriftParams P, Mat<D> q, const double* __restrict__ 
     gh_expect_point<DRIFT, D, H, G>(P, mk, mat_load<D>(S + t * DD), lane, pi_factor, ef, ej, ok);
     if (lane != 0) return;
     if (!ok) report_not_pd(status, t);
-    if (!full_jac) {
-        // the reference's A for element-wise drifts is the [D] tape gradient; only D = 1 is usable there
-        // (sde_utils.py:162-164).  For D > 1 we keep the diagonal Jacobian it stands for.
-    }
+    // (element-wise drifts: the reference's A is the [D] tape gradient, only usable for D = 1, sde_utils.py:162-164;
+    // for D > 1 the diagonal Jacobian it stands for is kept)
+    (void)full_jac;
     Vec<D> bl = ef - mv(ej, mk);
     const double delta = time_grid[k + 1] - time_grid[k];
     // sde.diffusion = chol(q); q passed to to_ssm is chol_q @ chol_q (sde_utils.py:168-171)
@@ -168,6 +167,7 @@ __global__ void k_linearize(DriftParams P, Mat<D> q, const double* __restrict__ 
     Mat<D> At = delta * ej + mat_eye<D>();
     Vec<D> bt = delta * bl;
     const Mat<D> cQ = chol(delta * qq, okq);
+    if (!okq) report_not_pd(status, t);   // spectral density (or a grid step <= 0) that is not positive definite
     if (A_lin) mat_store<D>(A_lin + t * DD, At);
     if (b_lin) vec_store<D>(b_lin + t * D, bt);
     if (clip) {

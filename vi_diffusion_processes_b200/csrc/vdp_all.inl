@@ -304,4 +304,5 @@ extern "C" int vdp_euler_maruyama(int drift_id, const double* params_host, const
 #if VDP_EMIT_DIST
 #include "vdp_dist.inl"
 #include "vdp_noalloc.inl"
+#include "vdp_ssm_density.inl"
 #endif

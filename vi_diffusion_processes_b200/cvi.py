@@ -49,6 +49,8 @@ class CviEngine:
             obs_idx, obs_y = obs_idx[None], obs_y[None]
         self.B = B = obs_idx.shape[0]
         self.n_obs = n_obs = obs_idx.shape[1]
+        if obs_idx.size and (obs_idx.min() < 0 or obs_idx.max() > N):
+            raise _lib.VdpError(f"observation grid indices must lie in [0, {N}] (got {obs_idx.min()}..{obs_idx.max()})")
         self.obs_idx = torch.as_tensor(obs_idx).to(self.device).contiguous()
         self.obs_y = torch.as_tensor(obs_y.reshape(B, n_obs, D), dtype=F64).to(self.device).contiguous()
         self.lik_chol = np.atleast_2d(np.asarray(lik_chol, dtype=np.float64))
@@ -83,9 +85,11 @@ class CviEngine:
         """Assign the prior on x0 (cvi_dp_trainer.py:231-235); dist_p picks it up at the next linearisation."""
         self.x0_mu = np.asarray(mu, dtype=np.float64).reshape(self.D)
         self.x0_cov = np.atleast_2d(np.asarray(cov, dtype=np.float64))
+        self._graphs = {}             # captured graphs hold the old x0 prior by value
 
     def set_linearized_prior(self):
         dev, B, D = self.device, self.B, self.D
+        self._graphs = {}             # the caching allocator may hand the new prior the old addresses
         self.pmu0 = torch.as_tensor(self.x0_mu, dtype=F64).to(dev).expand(B, D).contiguous()
         self.pcholP0 = torch.as_tensor(np.linalg.cholesky(self.x0_cov), dtype=F64).to(dev).expand(B, D, D).contiguous()
         m = self.fx_mus[:, 1:].contiguous()
@@ -124,7 +128,12 @@ class CviEngine:
         return p
 
     def _stream(self):
-        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _run(self, name, *args):
+        """Call a library entry on this engine's device (the launches go to the CURRENT device) and stream."""
+        with torch.cuda.device(self.device):
+            check(getattr(_lib.load(), name)(*args, self._stream()), name)
 
     # what the natural parameters left in the workspace by a site update depend on (besides the update itself)
     _NAT_FIELDS = ("pA", "pb", "pcholQ", "pmu0", "pcholP0", "g1", "gd", "gs", "d1", "d2", "obs_idx", "_ws")
@@ -146,7 +155,7 @@ class CviEngine:
         if carry and self._nat_sig is not None and self._nat_sig == self._nat_signature():
             flags |= _lib.FLAG_NATURALS_CARRIED
         p = self._problem(lr_data, lr_girsanov, flags)
-        check(_lib.load().vdp_cvi_site_update(C.byref(p), self._stream()), "vdp_cvi_site_update")
+        self._run("vdp_cvi_site_update", C.byref(p))
         if carry and (not (flags & _lib.FLAG_SKIP_GIRSANOV) or (flags & _lib.FLAG_NATURALS_CARRIED)):
             self._nat_sig = self._nat_signature()      # (a data-sites-only update leaves no dense data-site copy)
         return self.elbo
@@ -161,7 +170,10 @@ class CviEngine:
         removes the per-launch host cost.  The graph is captured on first use and re-captured whenever a buffer of
         the problem has been replaced (re-linearisation, site assignment) or the step sizes / drift parameters change.
         """
-        key = (float(lr_data), float(lr_girsanov), int(flags), tuple(self.drift_params),
+        # everything a captured launch sequence holds by value or by address
+        key = (float(lr_data), float(lr_girsanov), int(flags), tuple(self.drift_params), tuple(self.x0_mu.tolist()),
+               tuple(self.x0_cov.reshape(-1).tolist()), tuple(self.q.reshape(-1).tolist()),
+               tuple(self.lik_chol.reshape(-1).tolist()), self.dt, self.clip, self.stabilize_ssm,
                tuple(getattr(self, n).data_ptr() for n in self._PTR_FIELDS))
         cache = getattr(self, "_graphs", None)
         if cache is None:
@@ -173,7 +185,7 @@ class CviEngine:
             state = [getattr(self, n).clone() for n in ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs")]
             self.site_update(lr_data, lr_girsanov, flags, carry=False)   # warm-up outside the capture,
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            with torch.cuda.device(self.device), torch.cuda.graph(g):
                 self.site_update(lr_data, lr_girsanov, flags, carry=False)
             for n, t in zip(("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs"), state):
                 getattr(self, n).copy_(t)                          # ... whose effect is undone: the replay below is
@@ -185,18 +197,17 @@ class CviEngine:
     def site_update_sharded(self, phase, node_begin, node_end, lr_data=0.0, lr_girsanov=0.0):
         """One phase of ``vdp_cvi_site_update_sharded`` on the flat node range [node_begin, node_end)."""
         p = self._problem(lr_data, lr_girsanov)
-        check(_lib.load().vdp_cvi_site_update_sharded(C.byref(p), int(phase), int(node_begin), int(node_end),
-                                                      self._stream()), "vdp_cvi_site_update_sharded")
+        self._run("vdp_cvi_site_update_sharded", C.byref(p), int(phase), int(node_begin), int(node_end))
 
     def classic_elbo(self):
         p = self._problem(0.0, 0.0)
-        check(_lib.load().vdp_cvi_elbo(C.byref(p), self._stream()), "vdp_cvi_elbo")
+        self._run("vdp_cvi_elbo", C.byref(p))
         return self.elbo
 
     def posterior_ssm(self):
         """dist_q (variational_cvi_sde.py:176-192): rebuild q as an SSM from the sites; marginals untouched."""
         p = self._problem(0.0, 0.0, flags=_lib.FLAG_POSTERIOR_SSM_ONLY)
-        check(_lib.load().vdp_cvi_elbo(C.byref(p), self._stream()), "vdp_cvi_elbo")
+        self._run("vdp_cvi_elbo", C.byref(p))
         return self.qA, self.qb, self.qcholQ, self.qmu0, self.qcholP0
 
     # ---- prior-parameter learning (cvi_dp_trainer.py:207-250)
@@ -216,7 +227,7 @@ class CviEngine:
     def classic_elbo_keep_marginals(self):
         """classic_elbo (variational_cvi_sde.py:339-352) with the stored fx_mus / fx_covs left as they are."""
         p = self._problem_with_scratch_marginals()
-        check(_lib.load().vdp_cvi_elbo(C.byref(p), self._stream()), "vdp_cvi_elbo")
+        self._run("vdp_cvi_elbo", C.byref(p))
         return self.elbo
 
     def n_drift_params(self):
@@ -226,8 +237,7 @@ class CviEngine:
         """CVISitesSDE.grad_KL_wrt_prior_params (variational_cvi_sde.py:495-504) -> [B, n_params]."""
         p = self._problem_with_scratch_marginals()
         g = torch.empty((self.B, 16), dtype=F64, device=self.device)
-        check(_lib.load().vdp_cvi_grad_kl_prior_params(C.byref(p), C.c_void_p(g.data_ptr()), self._stream()),
-              "vdp_cvi_grad_kl_prior_params")
+        self._run("vdp_cvi_grad_kl_prior_params", C.byref(p), C.c_void_p(g.data_ptr()))
         return g[:, :self.n_drift_params()]
 
     def grad_ve_prior_params(self):
@@ -237,10 +247,8 @@ class CviEngine:
         p = self._problem_with_scratch_marginals()
         g = torch.empty((self.B, 16), dtype=F64, device=self.device)
         clip = 1 if self.stabilize_ssm else 0
-        check(_lib.load().vdp_cvi_grad_ve_prior_params(C.byref(p), C.c_void_p(self.fx_mus.data_ptr()),
-                                                       C.c_void_p(self.fx_covs.data_ptr()), clip, self.clip[0],
-                                                       self.clip[1], C.c_void_p(g.data_ptr()), self._stream()),
-              "vdp_cvi_grad_ve_prior_params")
+        self._run("vdp_cvi_grad_ve_prior_params", C.byref(p), C.c_void_p(self.fx_mus.data_ptr()),
+                  C.c_void_p(self.fx_covs.data_ptr()), clip, self.clip[0], self.clip[1], C.c_void_p(g.data_ptr()))
         return g[:, :self.n_drift_params()]
 
     def check_status(self):

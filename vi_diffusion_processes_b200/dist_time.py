@@ -116,7 +116,7 @@ def _blob_bytes(kind, stage, D):
 
 
 def _stream():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)   # callers hold torch.cuda.device(self.device)
 
 
 def _run_sweep(comm: Comm, ranks: List[_Rank], kind, problems_stage, D):

@@ -188,3 +188,8 @@ class CVISitesSDE:
 
     def loss(self):
         return -self.classic_elbo()
+
+    def check_status(self):
+        """Raise if a kernel met a non positive-definite block since the model was built (the analogue of the
+        InvalidArgumentError TensorFlow's Cholesky raises); synchronises the stream."""
+        self._engine.check_status()

@@ -121,6 +121,10 @@ class VariationalMarkovGP:
         """One iteration of VIMarkovGPTrainer.perform_inference (vi_markov_gp_trainer.py:62-73), fused."""
         return self._eng.sweep(lr, update_x0=update_x0, x0_lr=x0_lr)[0]
 
+    def check_status(self):
+        """Raise if a kernel met a non positive-definite block (synchronises the stream)."""
+        self._engine.check_status()
+
     @property
     def dist_q_ssm(self) -> StateSpaceModel:
         """The SSM of the last forward pass (vi_sde.py:180-197)."""

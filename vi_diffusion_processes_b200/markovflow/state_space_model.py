@@ -130,6 +130,48 @@ class StateSpaceModel:
         c = self.concatenated_cholesky_process_covariance
         return -2.0 * torch.log(torch.abs(torch.diagonal(c, dim1=-2, dim2=-1))).sum(dim=(-1, -2))
 
+    # ---- densities (state_space_model.py:298-324, 485-593)
+    def _ssm(self):
+        A, b, cQ, mu0, cP0, had = self._b()
+        return (A.contiguous(), b.contiguous(), cQ.contiguous(), mu0.contiguous(), cP0.contiguous()), had
+
+    def kl_divergence(self, dist: "StateSpaceModel"):
+        """KL(self || dist) (state_space_model.py:528-593) -> tensor of shape batch_shape."""
+        assert self.event_shape == dist.event_shape and self.batch_shape == dist.batch_shape   # check_compatible
+        s1, had = self._ssm()
+        s2, _ = dist._ssm()
+        status = ops.new_status(s1[0].device)
+        kl = ops.ssm_kl_divergence(s1, s2, status=status)
+        code, idx = ops.read_status(status)
+        if code != 0:
+            raise ValueError(f"StateSpaceModel.kl_divergence: precision block {idx} is not positive definite")
+        return unbatched(kl, had)
+
+    def log_pdf(self, states):
+        """log p(states) (state_space_model.py:485-526); states: sample_shape + batch_shape + event_shape."""
+        s, had = self._ssm()
+        x = as_dev(states)
+        sample_shape = tuple(x.shape[:x.dim() - 2 - len(self.batch_shape)])
+        B = s[0].shape[0]
+        x = x.reshape((-1, B) + tuple(self.event_shape)).contiguous()
+        out = ops.ssm_log_pdf(*s, x)
+        return out.reshape(sample_shape + tuple(self.batch_shape))
+
+    def sample(self, sample_shape, seed: int = 0, eps=None):
+        """Sample trajectories (state_space_model.py:298-324) -> sample_shape + batch_shape + event_shape.
+        ``eps`` (same shape) replaces the device generator's standard normals."""
+        s, had = self._ssm()
+        shape = (sample_shape,) if isinstance(sample_shape, int) else tuple(sample_shape)
+        S = 1
+        for v in shape:
+            S *= int(v)
+        B = s[0].shape[0]
+        full = shape + tuple(self.batch_shape) + tuple(self.event_shape)
+        if S == 0:
+            return torch.empty(full, dtype=s[0].dtype, device=s[0].device)
+        e = None if eps is None else as_dev(eps).reshape((S, B) + tuple(self.event_shape)).contiguous()
+        return ops.ssm_sample(*s, S, eps=e, seed=seed).reshape(full)
+
     def create_non_trainable_copy(self) -> "StateSpaceModel":
         return StateSpaceModel(self._mu_0.clone(), self._chol_P_0.clone(), self._A_s.clone(), self._b_s.clone(),
                                self._chol_Q_s.clone())

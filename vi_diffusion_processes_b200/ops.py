@@ -19,6 +19,23 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def _on_tensor_device(fn):
+    """Run `fn` with the device of its first CUDA tensor argument current: the library launches on the CURRENT
+    device, so an op on tensors of cuda:1 while cuda:0 is current would otherwise run on the wrong GPU."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(*args, **kwargs):
+        for a in list(args) + list(kwargs.values()):
+            if isinstance(a, torch.Tensor) and a.is_cuda:
+                if a.device.index == torch.cuda.current_device():
+                    break
+                with torch.cuda.device(a.device):
+                    return fn(*args, **kwargs)
+        return fn(*args, **kwargs)
+    return wrapped
+
+
 def _p(t):
     return None if t is None else C.c_void_p(t.data_ptr())
 
@@ -210,6 +227,48 @@ def ssm_marginals(A, b, cholQ, mu0, cholP0, status=None):
     return m, Sd
 
 
+def ssm_kl_divergence(ssm1, ssm2, status=None):
+    """StateSpaceModel.kl_divergence (state_space_model.py:528-593); ssm = (A, b, cholQ, mu0, cholP0) -> [B]."""
+    _req(*ssm1, *ssm2, status)
+    B, N, D = ssm1[0].shape[0], ssm1[0].shape[1], ssm1[0].shape[-1]
+    lib = _lib.load()
+    nbytes = lib.vdp_ssm_kl_divergence_workspace(B, N, D)
+    ws = _workspace(nbytes, ssm1[0].device)
+    kl = torch.empty(B, dtype=F64, device=ssm1[0].device)
+    check(lib.vdp_ssm_kl_divergence(*[_p(t) for t in ssm1], *[_p(t) for t in ssm2], _p(kl), _p(ws), nbytes, B, N, D,
+                                    _p(status), _stream()), "vdp_ssm_kl_divergence")
+    return kl
+
+
+def ssm_log_pdf(A, b, cholQ, mu0, cholP0, states):
+    """StateSpaceModel.log_pdf (state_space_model.py:485-526); states [S, B, N+1, D] -> [S, B]."""
+    _req(A, b, cholQ, mu0, cholP0, states)
+    B, N, D = A.shape[0], A.shape[1], A.shape[-1]
+    S = states.shape[0]
+    assert states.shape == (S, B, N + 1, D), states.shape
+    lib = _lib.load()
+    nbytes = lib.vdp_ssm_log_pdf_workspace(S, B, N)
+    ws = _workspace(nbytes, A.device)
+    out = torch.empty((S, B), dtype=F64, device=A.device)
+    check(lib.vdp_ssm_log_pdf(_p(A), _p(b), _p(cholQ), _p(mu0), _p(cholP0), _p(states), _p(out), _p(ws), nbytes, S, B,
+                              N, D, _stream()), "vdp_ssm_log_pdf")
+    return out
+
+
+def ssm_sample(A, b, cholQ, mu0, cholP0, num_samples, eps=None, seed=0):
+    """StateSpaceModel.sample (state_space_model.py:298-324) -> [S, B, N+1, D]; eps [S, B, N+1, D] standard normals
+    to use instead of the device generator (Philox, `seed`)."""
+    _req(A, b, cholQ, mu0, cholP0, eps)
+    B, N, D = A.shape[0], A.shape[1], A.shape[-1]
+    S = int(num_samples)
+    if eps is not None:
+        assert eps.shape == (S, B, N + 1, D), eps.shape
+    out = torch.empty((S, B, N + 1, D), dtype=F64, device=A.device)
+    check(_lib.load().vdp_ssm_sample(_p(A), _p(b), _p(cholQ), _p(mu0), _p(cholP0), _p(eps), int(seed), _p(out), S, B,
+                                     N, D, _stream()), "vdp_ssm_sample")
+    return out
+
+
 def ssm_to_expectations(A, m, Sd):
     _req(A, m, Sd)
     B, n, D = m.shape
@@ -346,3 +405,11 @@ def euler_maruyama(drift_id, params, q, x0, time_grid, noise=None, seed=0):
                                          _p(x0), _p(time_grid), _p(noise), int(seed), _p(out), B, n, D, None,
                                          _stream()), "vdp_euler_maruyama")
     return out
+
+
+# every public op runs on the device of its tensors (see _on_tensor_device)
+for _name, _fn in list(globals().items()):
+    if callable(_fn) and not _name.startswith("_") and getattr(_fn, "__module__", None) == __name__ \
+            and _name not in ("new_status", "drift_num_params"):
+        globals()[_name] = _on_tensor_device(_fn)
+del _name, _fn

@@ -111,7 +111,16 @@ class CVISitesTrainer:
             self.prior_params.setdefault(str(i), []).append(float(v))
 
     def _elbo(self) -> float:
-        return _f(self.model.classic_elbo())
+        e = _f(self.model.classic_elbo())
+        self._check()
+        return e
+
+    def _check(self):
+        """Raise on a non positive-definite block (the reference fails inside tf.linalg.cholesky / cholesky_band;
+        here the kernels report through the device status word, read where the ELBO has just been synchronised)."""
+        check = getattr(self.model, "check_status", None)
+        if check is not None:
+            check()
 
     def _marginals(self):
         q = self.model.dist_q                     # cvi_dp_trainer.py:192-207: dist_q.marginals, rebuilt from the sites
@@ -133,6 +142,7 @@ class CVISitesTrainer:
         while (len(elbo) - 1) < self.max_itr_sites_optim:
             # update_data_sites; update_girsanov_sites; classic_elbo  == one fused vdp_cvi_site_update
             elbo.append(_f(self.model.site_update(self.data_sites_lr, self.girsanov_sites_lr)))
+            self._check()
             nlpd.append(self.model_nlpd())
             rmse.append(self.model_rmse())
             if len(elbo) > 2 and elbo[-2] > elbo[-1]:
@@ -229,6 +239,11 @@ class VIMarkovGPTrainer:
         for i, v in enumerate(self.model.prior_sde.trainable_variables):
             self.prior_params.setdefault(i, []).append(float(v))
 
+    def _check(self):
+        check = getattr(self.model, "check_status", None)
+        if check is not None:
+            check()
+
     def model_nlpd(self, m, S) -> float:
         m, S = self.model.likelihood.predict_mean_and_var(m, S)
         return calculate_nlpd(m, S, self.model.grid, self.test_data)
@@ -246,6 +261,7 @@ class VIMarkovGPTrainer:
             e = self.model.sweep(q_lr, update_x0=i > self.warmup_x0_itr, x0_lr=x0_lr)
             m, S = self.model.m, self.model.S
             elbo.append(_f(e))
+            self._check()
             nlpd.append(self.model_nlpd(m, S))
             rmse.append(self.model_rmse(m, S))
             if elbo[-2] > elbo[-1] or abs(elbo[-2] - elbo[-1]) < self.lr_tol:
@@ -278,6 +294,7 @@ class VIMarkovGPTrainer:
                 self.optimize_prior_x0()
             m, S = model.forward_pass
             elbo.append(_f(model.elbo(m, S)))
+            self._check()
             nlpd.append(self.model_nlpd(m, S))
             rmse.append(self.model_rmse(m, S))
             self.store_prior_param_vals()

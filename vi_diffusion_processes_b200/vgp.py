@@ -43,6 +43,8 @@ class VgpEngine:
             obs_idx, obs_y = obs_idx[None], obs_y[None]
         self.B = B = obs_idx.shape[0]
         self.n_obs = n_obs = obs_idx.shape[1]
+        if obs_idx.size and (obs_idx.min() < 0 or obs_idx.max() > N):
+            raise _lib.VdpError(f"observation grid indices must lie in [0, {N}] (got {obs_idx.min()}..{obs_idx.max()})")
         self.obs_idx = torch.as_tensor(obs_idx).to(dev).contiguous()
         self.obs_y = torch.as_tensor(obs_y.reshape(B, n_obs, D), dtype=F64).to(dev).contiguous()
         self.lik_chol = np.atleast_2d(np.asarray(lik_chol, dtype=np.float64))
@@ -93,8 +95,9 @@ class VgpEngine:
         return p
 
     def _call(self, name, p):
-        stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        check(getattr(_lib.load(), name)(C.byref(p), stream), name)
+        with torch.cuda.device(self.device):   # the launches go to the current device
+            stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+            check(getattr(_lib.load(), name)(C.byref(p), stream), name)
 
     # vi_sde.py:171-204
     def forward_pass(self):
@@ -136,7 +139,8 @@ class VgpEngine:
         names = ("time_grid", "A", "b", "lambda_lagrange", "psi_lagrange", "q_initial_mean", "q_initial_chol",
                  "obs_idx", "obs_y", "m", "S", "elbo_value", "status")
         key = (float(lr), bool(update_x0), float(x0_lr), tuple(self.drift_params), tuple(self.x0_mu.tolist()),
-               tuple(self.x0_cov.reshape(-1).tolist()), tuple(getattr(self, n).data_ptr() for n in names))
+               tuple(self.x0_cov.reshape(-1).tolist()), tuple(self.q.reshape(-1).tolist()),
+               tuple(self.lik_chol.reshape(-1).tolist()), self.dt, self.stabilize_system, tuple(getattr(self, n).data_ptr() for n in names))
         cache = getattr(self, "_graphs", None)
         if cache is None:
             cache = self._graphs = {}
@@ -148,7 +152,7 @@ class VgpEngine:
             state = [getattr(self, n).clone() for n in keep]
             self.sweep(lr, update_x0=update_x0, x0_lr=x0_lr)      # warm-up outside the capture, undone below
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            with torch.cuda.device(self.device), torch.cuda.graph(g):
                 self.sweep(lr, update_x0=update_x0, x0_lr=x0_lr)
             for n, t in zip(keep, state):
                 getattr(self, n).copy_(t)
