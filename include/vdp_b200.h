@@ -262,8 +262,23 @@ typedef struct vdp_cvi_problem {
                                          instead of over the whole grid (same resulting state; honoured for
                                          n_obs <= 128, ignored otherwise) */
 
+#define VDP_FLAG_SITES_IN_NATURALS 32  /* vdp_cvi_site_update, honoured only together with VDP_FLAG_NATURALS_CARRIED: the
+                                         girsanov sites are held implicitly in the natural parameters theta = nat(p)
+                                         + g + scatter(data sites) the workspace carries.  The girsanov update
+                                         (variational_cvi_sde.py:290-296) then moves theta by lr (scatter - dKL/deta)
+                                         and g1 / gd / gs are NEITHER READ NOR WRITTEN by the call (no pass over the
+                                         sites and the prior: 88 instead of 136 bytes per grid step, D = 1).  Call
+                                         vdp_cvi_materialize_sites before reading g1 / gd / gs, and before any call
+                                         on this problem that does not carry the naturals.  A re-basing of the sites
+                                         onto a new linearised prior (tranform_girsanov_sites, sde_utils.py:550-568:
+                                         g + nat(p_old) - nat(p_new)) leaves theta unchanged. */
+
 size_t vdp_cvi_workspace(int64_t B, int64_t N, int D, int64_t n_obs);
 int vdp_cvi_site_update(const vdp_cvi_problem* problem_host, void* stream);
+/* g1, gd, gs <- theta - nat(p) - scatter(data sites) from the natural parameters and the dense data-site copy the
+ * last vdp_cvi_site_update left in the workspace (see VDP_FLAG_SITES_IN_NATURALS; full_sites of
+ * variational_cvi_sde.py:161-174 read backwards).  p = the prior of the problem. */
+int vdp_cvi_materialize_sites(const vdp_cvi_problem* problem_host, void* stream);
 /* Sharded quadrature (one long sequence over several GPUs, BASELINE config 5, where the H^D-node quadrature is
  * > 95 % of the update): every rank holds the whole chain and runs the cheap rebuilds on it, the quadrature and the
  * girsanov site update only on its own range [node_begin, node_end) of the flat (sequence, grid point) index.

@@ -26,7 +26,8 @@ def test_sharded_quadrature_d1_equals_single_gpu_and_oracle(R):
     grid = np.round(np.arange(N + 1) * 0.005, 6)
     idx = np.sort(rng.choice(N + 1, n_obs, replace=False))[None]
     y = rng.normal(size=(1, n_obs)) * 0.3 + 1.0
-    mk = lambda: CviEngine(S.DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y[..., None], [[0.1]], [1.0], [[1e-2]])
+    mk = lambda: CviEngine(S.DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y[..., None], [[0.1]], [1.0], [[1e-2]],
+                           lazy_sites=False)   # bitwise comparisons below: sites written by every update
     single = mk()
     ref = scalar_d1.BatchedCVISitesSDE1D(S.DRIFT_DW, [4.0, 1.0], 1.0, grid, idx, y, 0.1, 1.0, 1e-2)
     sh = ShardedQuadratureCvi(_engines(R, mk), Comm.emulated(R))
@@ -53,7 +54,7 @@ def test_sharded_quadrature_3d():
     sde = S.OUNdSDE(0.5, np.eye(3))
     x0 = S.Gaussian(np.zeros(3), 0.5 * np.eye(3))
     ref = M.CVISitesSDE(sde, grid, (grid[idx], y), M.MultivariateGaussian(0.1 * np.eye(3)), prior_initial_state=x0)
-    mk = lambda: CviEngine(sde.drift_id, sde.params, sde.q, grid, idx, y, 0.1 * np.eye(3), x0.mu, x0.cov)
+    mk = lambda: CviEngine(sde.drift_id, sde.params, sde.q, grid, idx, y, 0.1 * np.eye(3), x0.mu, x0.cov, lazy_sites=False)
     single = mk()
     sh = ShardedQuadratureCvi(_engines(4, mk), Comm.emulated(4))
     for it in range(2):

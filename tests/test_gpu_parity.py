@@ -449,7 +449,8 @@ def test_fused_naturals_equal_separate_pass(monkeypatch):
     idx = np.sort(np.stack([rng.choice(N + 1, n_obs, replace=False) for _ in range(B)]), axis=1)
     idx[0, 0], idx[1, -1] = 0, N                      # first and last grid point observed
     y = rng.normal(size=(B, n_obs, 1)) * 0.3 + 1.0
-    mk = lambda: CviEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]])
+    mk = lambda: CviEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]],
+                           lazy_sites=False)
     a, c = mk(), mk()
     for _ in range(3):
         ea = a.site_update(0.5, 0.5).clone()
@@ -476,12 +477,14 @@ def test_carried_naturals_equal_full_pass():
     idx = np.sort(np.stack([rng.choice(N + 1, n_obs, replace=False) for _ in range(B)]), axis=1)
     idx[0, 0], idx[1, -1] = 0, N
     y = rng.normal(size=(B, n_obs, 1)) * 0.3 + 1.0
-    mk = lambda carry: CviEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]],
-                                 carry_naturals=carry)
-    a, c = mk(True), mk(False)
-    carried = []
+    mk = lambda carry, lazy=False: CviEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0],
+                                             [[1e-2]], carry_naturals=carry, lazy_sites=lazy)
+    # a: carried naturals, sites written every update; c: nothing carried; z: carried + sites held in theta between
+    # updates (VDP_FLAG_SITES_IN_NATURALS, the engine's default): same state up to the rounding of theta + delta
+    a, c, z = mk(True), mk(False), mk(True, True)
+    carried, lazy = [], []
     for it in range(12):
-        for e in (a, c):
+        for e in (a, c, z):
             if it == 3:
                 e.relinearize()
             if it == 5:
@@ -492,11 +495,22 @@ def test_carried_naturals_equal_full_pass():
         flags = _lib.FLAG_SKIP_GIRSANOV if it in (7, 9) else 0
         ea = a.site_update(0.4, 0.4, flags).clone()
         ec = c.site_update(0.4, 0.4, flags).clone()
+        ez = z.site_update(0.4, 0.4, flags).clone()
+        lazy.append(z._sites_stale)
         assert torch.equal(ea, ec), it
+        assert rel(ez, ec.cpu().numpy()) < 1e-11, it
     a.check_status()
+    z.check_status()
     assert carried == [False, True, True, False, True, False, False, True, True, False, False, True]
+    assert lazy == [False, True, True, False, True, False, False, False, True, False, False, True]
     for name in ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs", "qA", "qb", "qcholQ"):
         assert torch.equal(getattr(a, name), getattr(c, name)), name
+        scale = None
+        if name in ("g1", "gd", "gs"):   # a site is a summand of theta: right to 1e-11 at that scale
+            th = dict(zip(("g1", "gd", "gs"), c._prior_naturals(c.pA, c.pb)))[name]
+            scale = float((th + getattr(c, name)).abs().max())
+        assert rel(getattr(z, name), getattr(c, name).cpu().numpy(), scale=scale) < 1e-11, name
+    assert not z._sites_stale            # reading the sites brought them up to date
 
 
 def test_carried_naturals_repeated_observation_points():
@@ -670,7 +684,8 @@ def test_cuda_graph_replay_equals_direct_calls():
     grid = np.round(np.arange(N + 1) * 0.005, 3)
     idx = np.sort(rng.choice(N + 1, n_obs, replace=False))[None]
     y = rng.normal(size=(1, n_obs, 1)) * 0.3 + 1.0
-    mk = lambda: CviEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]])
+    mk = lambda: CviEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]],
+                           lazy_sites=False)   # (a replay writes the sites every update: bitwise comparison)
     a, b = mk(), mk()
     for it in range(6):
         lr = 0.5 if it < 4 else 0.25

@@ -49,7 +49,7 @@ def test_graph_replay_follows_a_changed_prior_initial_state():
     """site_update_graphed after set_prior_initial_state must use the new p(x0) in the KL_0 gradient (the captured
     launch holds x0_mu / x0_cov by value): replay == direct call, bitwise."""
     rng = np.random.default_rng(9)
-    a, b = _engine(np.random.default_rng(9)), _engine(np.random.default_rng(9))
+    a, b = _engine(np.random.default_rng(9), lazy_sites=False), _engine(np.random.default_rng(9), lazy_sites=False)
     for it in range(5):
         if it == 2:
             for e in (a, b):
@@ -60,7 +60,7 @@ def test_graph_replay_follows_a_changed_prior_initial_state():
     for name in ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs"):
         assert torch.equal(getattr(a, name), getattr(b, name)), name
     # and the change is not a no-op: an engine that keeps the old prior differs
-    c = _engine(np.random.default_rng(9))
+    c = _engine(np.random.default_rng(9), lazy_sites=False)
     for it in range(5):
         ec = c.site_update(0.5, 0.5)
     assert not torch.equal(ec, ea)

@@ -90,6 +90,7 @@ class DistSweep(C.Structure):
 SWEEP_CHOL, SWEEP_NAT2SSM, SWEEP_MARG, SWEEP_INVBAND = 0, 1, 2, 3
 FLAG_SKIP_DATA_UPDATE, FLAG_SKIP_ELBO, FLAG_SKIP_GIRSANOV, FLAG_POSTERIOR_SSM_ONLY = 1, 2, 4, 8
 FLAG_NATURALS_CARRIED = 16
+FLAG_SITES_IN_NATURALS = 32
 VGP_STABILIZE = 1
 VGP_UPDATE_X0 = 2
 
@@ -131,6 +132,7 @@ SIGNATURES = {
                                       C.c_size_t, i64, i64, C.c_int, vp, vp]),
     "vdp_cvi_workspace": (C.c_size_t, [i64, i64, C.c_int, i64]),
     "vdp_cvi_site_update": (C.c_int, [C.POINTER(CviProblem), vp]),
+    "vdp_cvi_materialize_sites": (C.c_int, [C.POINTER(CviProblem), vp]),
     "vdp_cvi_site_update_sharded": (C.c_int, [C.POINTER(CviProblem), C.c_int, i64, i64, vp]),
     "vdp_cvi_elbo": (C.c_int, [C.POINTER(CviProblem), vp]),
     "vdp_drift_num_params": (C.c_int, [C.c_int]),

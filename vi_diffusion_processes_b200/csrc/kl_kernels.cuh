@@ -349,11 +349,17 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
         // the site update at the end of the kernel reads the sites, the scattered data sites and (for the fused
         // naturals) the prior: start those lines on their way now, the quadrature hides the latency
         const int64_t tt = b * N + k;
-        prefetch_l2(g1 + i * D);
-        prefetch_l2(gd + i * DD);
-        if (k < N) prefetch_l2(gs + tt * DD);
+        if (upd == 2) {   // sites held in theta
+            prefetch_l2(nat.th1 + i * D);
+            prefetch_l2(nat.thd + i * DD);
+            if (k < N) prefetch_l2(nat.ths + tt * DD);
+        } else {
+            prefetch_l2(g1 + i * D);
+            prefetch_l2(gd + i * DD);
+            if (k < N) prefetch_l2(gs + tt * DD);
+        }
         if (sc1) { prefetch_l2(sc1 + i * D); prefetch_l2(scd + i * DD); }
-        if (nat.th1 && k < N) {
+        if (nat.pA && k < N) {
             prefetch_l2(nat.pA + tt * DD);
             prefetch_l2(nat.pb + tt * D);
             prefetch_l2(nat.pcholQ + tt * DD);
@@ -410,6 +416,19 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
         vec_store<D>(g1 + i * D, gm);
         mat_store<D>(gd + i * DD, gS);
         if (has_term) mat_store<D>(gs + (b * N + k) * DD, t.ges);
+    } else if (upd == 2) {
+        // VDP_FLAG_SITES_IN_NATURALS: the sites live in theta = nat(p) + g + scatter(data sites); the update
+        // g += lr (scatter - dKL/deta) (variational_cvi_sde.py:290-292) moves theta by the same amount.  No read of
+        // the prior or of g, no write of g: 88 instead of 136 bytes per grid step (D = 1).
+        Vec<D> s1 = vec_zero<D>();
+        Mat<D> s2 = mat_zero<D>();
+        if (sc1) { s1 = vec_load<D>(sc1 + i * D); s2 = mat_load<D>(scd + i * DD); }
+        vec_store<D>(nat.th1 + i * D, vec_load<D>(nat.th1 + i * D) + lr * (s1 - gm));
+        mat_store<D>(nat.thd + i * DD, mat_load<D>(nat.thd + i * DD) + lr * (s2 - gS));
+        if (has_term) {
+            const int64_t tt = b * N + k;
+            mat_store<D>(nat.ths + tt * DD, mat_load<D>(nat.ths + tt * DD) - lr * t.ges);
+        }
     } else {
         Vec<D> s1 = vec_zero<D>();
         Mat<D> s2 = mat_zero<D>();

@@ -144,6 +144,67 @@ __global__ void k_patch_naturals(const double* __restrict__ A, const double* __r
     mat_store<D>(scd + i * DD, s2);
 }
 
+// The same patch when the girsanov sites are held implicitly in theta (VDP_FLAG_SITES_IN_NATURALS: theta is the
+// state, g = theta - nat(p) - scatter(data sites) is formed on request): theta changes by the change of the data
+// sites at the observed grid points, whose previous sum is the dense copy's current entry.
+template <int D>
+__global__ void k_patch_naturals_delta(const double* __restrict__ d1, const double* __restrict__ d2,
+                                       const int64_t* __restrict__ obs_idx, double* __restrict__ th1,
+                                       double* __restrict__ thd, double* __restrict__ sc1, double* __restrict__ scd,
+                                       int64_t B, int64_t N, int64_t n_obs) {
+    const int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (o >= B * n_obs) return;
+    constexpr int DD = D * D;
+    const int64_t b = o / n_obs, j = o - b * n_obs;
+    const int64_t k = obs_idx[o];
+    if (k < 0 || k > N) return;
+    const int64_t* row = obs_idx + b * n_obs;
+    Vec<D> s1 = vec_zero<D>();
+    Mat<D> s2 = mat_zero<D>();
+    for (int64_t jj = 0; jj < n_obs; ++jj) {
+        if (row[jj] != k) continue;
+        if (jj < j) return;
+        s1 = s1 + vec_load<D>(d1 + (b * n_obs + jj) * D);
+        s2 = s2 + mat_load<D>(d2 + (b * n_obs + jj) * DD);
+    }
+    const int64_t i = b * (N + 1) + k;
+    vec_store<D>(th1 + i * D, vec_load<D>(th1 + i * D) + (s1 - vec_load<D>(sc1 + i * D)));
+    mat_store<D>(thd + i * DD, mat_load<D>(thd + i * DD) + (s2 - mat_load<D>(scd + i * DD)));
+    vec_store<D>(sc1 + i * D, s1);
+    mat_store<D>(scd + i * DD, s2);
+}
+
+// girsanov sites from the natural parameters they are part of (variational_cvi_sde.py:161-174 read backwards):
+//   g = theta - nat(p) - scatter(data sites),   sub-diagonal: g_s = theta_s - nat_s(p)
+// sc1 / scd = the dense copy of the data sites (zero away from the observations).
+template <int D>
+__global__ void k_sites_from_naturals(const double* __restrict__ A, const double* __restrict__ bo,
+                                      const double* __restrict__ cholQ, const double* __restrict__ mu0,
+                                      const double* __restrict__ cholP0, const double* __restrict__ th1,
+                                      const double* __restrict__ thd, const double* __restrict__ ths,
+                                      const double* __restrict__ sc1, const double* __restrict__ scd,
+                                      double* __restrict__ g1, double* __restrict__ gd, double* __restrict__ gs,
+                                      int64_t B, int64_t N) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t n = N + 1;
+    if (i >= B * n) return;
+    constexpr int DD = D * D;
+    const int64_t b = i / n, k = i % n;
+    const Mat<D> ck = (k == 0) ? mat_load<D>(cholP0 + b * DD) : mat_load<D>(cholQ + (b * N + k - 1) * DD);
+    const Vec<D> ok = (k == 0) ? vec_load<D>(mu0 + b * D) : vec_load<D>(bo + (b * N + k - 1) * D);
+    Mat<D> Ak = mat_zero<D>(), cn = mat_eye<D>(), td, ts;
+    Vec<D> bn = vec_zero<D>(), t1;
+    if (k < N) {
+        Ak = mat_load<D>(A + (b * N + k) * DD);
+        cn = mat_load<D>(cholQ + (b * N + k) * DD);
+        bn = vec_load<D>(bo + (b * N + k) * D);
+    }
+    ssm_node_naturals<D>(ck, ok, k < N, Ak, cn, bn, t1, td, ts);
+    if (k < N) mat_store<D>(gs + (b * N + k) * DD, mat_load<D>(ths + (b * N + k) * DD) - ts);
+    vec_store<D>(g1 + i * D, (vec_load<D>(th1 + i * D) - vec_load<D>(sc1 + i * D)) - t1);
+    mat_store<D>(gd + i * DD, (mat_load<D>(thd + i * DD) - mat_load<D>(scd + i * DD)) - td);
+}
+
 // ssm_to_expectations (ssm_gaussian_transformations.py:32-89)
 template <int D>
 __global__ void k_ssm_to_expectations(const double* __restrict__ A, const double* __restrict__ m,

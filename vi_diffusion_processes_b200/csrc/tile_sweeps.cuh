@@ -663,7 +663,7 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
                 cov_from_precision(mirror_lower(KN), cov, cc, ok);
                 if (!ok) report_not_pd(status, b * n + N);
                 vec_store<D>(bo + (b * N + N - 1) * D, mv(cov, y_tile));
-                mat_store<D>(cholQ + (b * N + N - 1) * DD, cc);
+                if (cholQ) mat_store<D>(cholQ + (b * N + N - 1) * DD, cc);
                 if (COV) mat_store<D>(Sd + (b * n + N) * DD, S_tile);
             }
         }
@@ -757,14 +757,16 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
         __syncthreads();
         stage_out<T>(A + (b * N + lo) * DD, sLs, (int64_t)cnt * DD);
         if (COV) stage_out<T>(Sd + (b * n + lo) * DD, sSd, (int64_t)cnt * DD);
+        // (cholQ == NULL: the caller has no use for the process-noise factors, e.g. the rebuild between the data-site
+        // and the girsanov-site update, whose consumer reads A, the means and the marginal covariances only)
         if (lo >= 1 || !first) {   // time-sharded ranks own one slot before index 0 of bo / cholQ
             stage_out<T>(bo + (b * N + lo - 1) * D, sT1, (int64_t)cnt * D);
-            stage_out<T>(cholQ + (b * N + lo - 1) * DD, sLd, (int64_t)cnt * DD);
+            if (cholQ) stage_out<T>(cholQ + (b * N + lo - 1) * DD, sLd, (int64_t)cnt * DD);
         } else {
             stage_out<T>(mu0 + b * D, sT1, D);
             stage_out<T>(cholP0 + b * DD, sLd, DD);
             stage_out<T>(bo + b * N * D, sT1 + D, (int64_t)(cnt - 1) * D);
-            stage_out<T>(cholQ + b * N * DD, sLd + DD, (int64_t)(cnt - 1) * DD);
+            if (cholQ) stage_out<T>(cholQ + b * N * DD, sLd + DD, (int64_t)(cnt - 1) * DD);
         }
     }
     if (threadIdx.x == 0) {

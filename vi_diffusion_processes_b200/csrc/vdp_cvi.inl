@@ -76,9 +76,10 @@ static inline bool cvi_ws_take(void* ws, size_t bytes, int64_t B, int64_t N, int
 // DRIFT >= 0 with kl_partials != NULL: classic_elbo follows on the whole chain; where the mean sweep can add up the KL
 // terms on its way (tiled route, D = 1, polynomial drift in closed form) it does, and *kl_partials is the number of
 // partial sums per sequence it left in w.terms (0: run_elbo makes its own pass).
+// skip_cholQ (tiled route only): the caller does not read the process-noise factors of this rebuild
 template <int D, int DRIFT = -1>
 static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t st, bool naturals_ready = false,
-                         int64_t* kl_partials = nullptr) {
+                         int64_t* kl_partials = nullptr, bool skip_cholQ = false) {
     const int64_t B = p.B, N = p.N;
     if (kl_partials) *kl_partials = 0;
     if (!naturals_ready) {
@@ -101,8 +102,9 @@ static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t 
     // factorisation + inverse band (equal to rounding, tests/test_gpu_parity.py::test_marginals_from_first_factor).
     const bool ssm_only = (p.flags & VDP_FLAG_POSTERIOR_SSM_ONLY) != 0;
     const bool lite = use_tiled_sweeps(B, N) && !env_int("VDP_REFACTOR_PRECISION", 0);
-    int rc = run_nat2ssm<D>(w.th1, w.thd, w.ths, p.qA, p.qb, p.qcholQ, p.qmu0, p.qcholP0, w.Ld, w.Ls, B, N, p.status,
-                            st, sc, (lite && !ssm_only) ? p.fx_covs : nullptr);
+    int rc = run_nat2ssm<D>(w.th1, w.thd, w.ths, p.qA, p.qb, (skip_cholQ && lite && !ssm_only) ? nullptr : p.qcholQ,
+                            p.qmu0, p.qcholP0, w.Ld, w.Ls, B, N, p.status, st, sc,
+                            (lite && !ssm_only) ? p.fx_covs : nullptr);
     if (rc || ssm_only) return rc;
     if (lite) {
         prof_mark(VDP_PHASE_MARG_FWD, st);
@@ -192,14 +194,24 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     // the naturals written by the previous update's girsanov kernel are still valid away from the observations
     const bool carried = (p.flags & VDP_FLAG_NATURALS_CARRIED) && p.n_obs <= 128 && node1 < 0 &&
                          !env_int("VDP_NO_CARRIED_NATURALS", 0);
+    // sites held in theta (VDP_FLAG_SITES_IN_NATURALS, only together with carried naturals): the girsanov update moves
+    // theta itself, g1 / gd / gs are neither read nor written (vdp_cvi_materialize_sites forms them on request)
+    const bool lazy = carried && (p.flags & VDP_FLAG_SITES_IN_NATURALS) && !stop_after_sites &&
+                      !(p.flags & VDP_FLAG_SKIP_GIRSANOV);
     if (carried && p.n_obs > 0) {
         prof_mark(VDP_PHASE_SITES_TO_NAT, st);
-        k_patch_naturals<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
-            p.pA, p.pb, p.pcholQ, p.pmu0, p.pcholP0, p.g1, p.gd, p.d1, p.d2, p.obs_idx, w.th1, w.thd, w.sc1, w.scd, B, N,
-            p.n_obs);
+        if (lazy)
+            k_patch_naturals_delta<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
+                p.d1, p.d2, p.obs_idx, w.th1, w.thd, w.sc1, w.scd, B, N, p.n_obs);
+        else
+            k_patch_naturals<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
+                p.pA, p.pb, p.pcholQ, p.pmu0, p.pcholP0, p.g1, p.gd, p.d1, p.d2, p.obs_idx, w.th1, w.thd, w.sc1, w.scd,
+                B, N, p.n_obs);
         VDP_CHECK_LAUNCH();
     }
-    if ((rc = run_posterior<D>(p, w, st, carried))) return rc;
+    // the rebuild between the two site updates feeds k_kl_grad (A, means, marginal covariances): no chol Q needed
+    const bool girsanov_follows = !(p.flags & VDP_FLAG_SKIP_GIRSANOV);
+    if ((rc = run_posterior<D>(p, w, st, carried, nullptr, girsanov_follows))) return rc;
     if (p.flags & VDP_FLAG_SKIP_GIRSANOV) {
         if (!(p.flags & VDP_FLAG_SKIP_ELBO)) return run_elbo<DRIFT, D>(p, w, P, st);
         return VDP_OK;
@@ -222,15 +234,15 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     }
     // whole-chain update: the kernel also writes the naturals of the posterior that follows (no second pass over
     // the sites); the sharded quadrature exchanges site ranges first and rebuilds from the sites
-    const bool fuse_nat = (node1 < 0) && !stop_after_sites && !env_int("VDP_NO_FUSED_NATURALS", 0);
+    const bool fuse_nat = lazy || ((node1 < 0) && !stop_after_sites && !env_int("VDP_NO_FUSED_NATURALS", 0));
     KlNaturalsOut nat;
     if (fuse_nat) {
-        nat.pA = p.pA; nat.pb = p.pb; nat.pcholQ = p.pcholQ; nat.pmu0 = p.pmu0; nat.pcholP0 = p.pcholP0;
+        if (!lazy) { nat.pA = p.pA; nat.pb = p.pb; nat.pcholQ = p.pcholQ; nat.pmu0 = p.pmu0; nat.pcholP0 = p.pcholP0; }
         nat.th1 = w.th1; nat.thd = w.thd; nat.ths = w.ths;
     }
     if ((rc = launch_kl_grad<DRIFT, D>(P, p.q, p.dt, p.time_grid, p.x0_mu, p.x0_cov, p.qA, p.fx_mus, p.fx_covs,
-                                       nullptr, p.g1, p.gd, p.gs, 1, p.lr_girsanov, w.sc1, w.scd, B, N, p.status,
-                                       st, node0, node1, nat)))
+                                       nullptr, p.g1, p.gd, p.gs, lazy ? 2 : 1, p.lr_girsanov, w.sc1, w.scd, B, N,
+                                       p.status, st, node0, node1, nat)))
         return rc;
     if (stop_after_sites) { prof_mark(VDP_PHASE_END, st); return VDP_OK; }
     const bool want_elbo = !(p.flags & VDP_FLAG_SKIP_ELBO);
@@ -298,6 +310,23 @@ int vdp_cvi_site_update(const vdp_cvi_problem* p, void* stream) {
         rc = run_site_update<kDrift, kD>(*p, w, as_stream(stream));
         if (rc) return rc;
     }));
+    return VDP_OK;
+}
+
+int vdp_cvi_materialize_sites(const vdp_cvi_problem* p, void* stream) {
+    int rc = check_problem(p);
+    if (rc) return rc;
+    if (p->B == 0) return VDP_OK;
+    CviWs w;
+    if (!cvi_ws_take(p->workspace, p->workspace_bytes, p->B, p->N, p->D, w)) {
+        set_error("workspace too small: need %zu bytes", cvi_ws_bytes(p->B, p->N, p->D));
+        return VDP_E_WORKSPACE;
+    }
+    VDP_DISPATCH_D(p->D, (k_sites_from_naturals<kD><<<grid_for(p->B * (p->N + 1), kPtBlock), kPtBlock, 0,
+                                                     as_stream(stream)>>>(
+                              p->pA, p->pb, p->pcholQ, p->pmu0, p->pcholP0, w.th1, w.thd, w.ths, w.sc1, w.scd, p->g1,
+                              p->gd, p->gs, p->B, p->N)));
+    VDP_CHECK_LAUNCH();
     return VDP_OK;
 }
 

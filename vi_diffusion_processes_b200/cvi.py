@@ -20,6 +20,12 @@ from ._lib import CviProblem, check
 F64 = torch.float64
 
 
+def _env_on(name):
+    import os
+    v = os.environ.get(name, "")
+    return bool(v) and v != "0"
+
+
 class CviEngine:
     """
     State (all float64 CUDA tensors, reference layouts with a leading batch axis):
@@ -31,9 +37,13 @@ class CviEngine:
 
     def __init__(self, drift_id, drift_params, q, time_grid, obs_idx, obs_y, lik_chol, x0_mu, x0_cov,
                  device="cuda", stabilize_ssm=True, clip_state_transitions=(-1.0, 1.0),
-                 initial_mean=None, initial_cov=None, carry_naturals=True):
+                 initial_mean=None, initial_cov=None, carry_naturals=True, lazy_sites=True):
         self.device = torch.device(device)
         self.carry_naturals = bool(carry_naturals)
+        # consecutive carried updates keep the girsanov sites implicitly in theta (VDP_FLAG_SITES_IN_NATURALS) and
+        # form g1 / gd / gs when somebody reads them (the g1 / gd / gs properties below)
+        self.lazy_sites = bool(lazy_sites) and self.carry_naturals
+        self._sites_stale = False
         self._nat_sig = None
         self.drift_id = int(drift_id)
         self.drift_params = [float(v) for v in np.asarray(drift_params).reshape(-1)]
@@ -60,9 +70,9 @@ class CviEngine:
         self.clip = tuple(float(c) for c in clip_state_transitions)
         dev = self.device
         z = lambda *s: torch.zeros(s, dtype=F64, device=dev)
-        self.g1 = z(B, N + 1, D)
-        self.gd = torch.full((B, N + 1, D, D), -1e-10, dtype=F64, device=dev)
-        self.gs = torch.full((B, N, D, D), -1e-10, dtype=F64, device=dev)
+        self._g1 = z(B, N + 1, D)
+        self._gd = torch.full((B, N + 1, D, D), -1e-10, dtype=F64, device=dev)
+        self._gs = torch.full((B, N, D, D), -1e-10, dtype=F64, device=dev)
         self.d1 = z(B, n_obs, D)
         self.d2 = (torch.eye(D, dtype=F64, device=dev) * 1e-10).expand(B, n_obs, D, D).contiguous()
         self.fx_mus = z(B, N + 1, D) if initial_mean is None else torch.as_tensor(
@@ -80,6 +90,26 @@ class CviEngine:
         # prior p: initial state from the prior on x0 (variational_cvi_sde.py:408-412, sde_utils.py:145-147)
         self.set_linearized_prior()
 
+    # ---- girsanov sites: plain tensors that are brought up to date on access when the last updates kept them in theta
+    def _sync_sites(self):
+        if self._sites_stale:
+            self._sites_stale = False
+            p = self._problem(0.0, 0.0, keep_carry=True)
+            self._run("vdp_cvi_materialize_sites", C.byref(p))
+
+    def _get_site(self, name):
+        self._sync_sites()
+        return getattr(self, name)
+
+    def _set_site(self, name, value):
+        self._sync_sites()
+        setattr(self, name, value)
+        self._nat_sig = None
+
+    g1 = property(lambda s: s._get_site("_g1"), lambda s, v: s._set_site("_g1", v))
+    gd = property(lambda s: s._get_site("_gd"), lambda s, v: s._set_site("_gd", v))
+    gs = property(lambda s: s._get_site("_gs"), lambda s, v: s._set_site("_gs", v))
+
     # variational_cvi_sde.py:408-432
     def set_prior_initial_state(self, mu, cov):
         """Assign the prior on x0 (cvi_dp_trainer.py:231-235); dist_p picks it up at the next linearisation."""
@@ -89,6 +119,7 @@ class CviEngine:
 
     def set_linearized_prior(self):
         dev, B, D = self.device, self.B, self.D
+        self._sync_sites()            # implicit sites are relative to the prior that is about to be replaced
         self._graphs = {}             # the caching allocator may hand the new prior the old addresses
         self.pmu0 = torch.as_tensor(self.x0_mu, dtype=F64).to(dev).expand(B, D).contiguous()
         self.pcholP0 = torch.as_tensor(np.linalg.cholesky(self.x0_cov), dtype=F64).to(dev).expand(B, D, D).contiguous()
@@ -100,7 +131,11 @@ class CviEngine:
         self.pA, self.pb, self.pcholQ = A, b, cholQ
         self.pA_lin, self.pb_lin = A_lin, b_lin
 
-    def _problem(self, lr_data, lr_girsanov, flags=0):
+    _RAW = {"g1": "_g1", "gd": "_gd", "gs": "_gs"}
+
+    def _problem(self, lr_data, lr_girsanov, flags=0, keep_carry=False):
+        if not keep_carry:
+            self._sync_sites()        # every entry but the lazy site update / the materialisation reads g1, gd, gs
         p = CviProblem()
         p.B, p.N, p.n_obs, p.D, p.drift_id = self.B, self.N, self.n_obs, self.D, self.drift_id
         for i, v in enumerate(self.drift_params[:16]):
@@ -118,13 +153,14 @@ class CviEngine:
         for name in ("time_grid", "pA", "pb", "pcholQ", "pmu0", "pcholP0", "g1", "gd", "gs", "d1", "d2", "obs_idx",
                      "obs_y", "fx_mus", "fx_covs", "qA", "qb", "qcholQ", "qmu0", "qcholP0", "elbo", "ve", "kl",
                      "status"):
-            t = getattr(self, name)
+            t = getattr(self, self._RAW.get(name, name))
             assert t.is_contiguous(), name
             setattr(p, name, t.data_ptr())
         p.workspace = self._ws.data_ptr()
         p.workspace_bytes = self._ws_bytes
         p.flags = flags
-        self._nat_sig = None          # whatever is called with this problem may rewrite the workspace
+        if not keep_carry:
+            self._nat_sig = None      # whatever is called with this problem may rewrite the workspace
         return p
 
     def _stream(self):
@@ -136,7 +172,7 @@ class CviEngine:
             check(getattr(_lib.load(), name)(*args, self._stream()), name)
 
     # what the natural parameters left in the workspace by a site update depend on (besides the update itself)
-    _NAT_FIELDS = ("pA", "pb", "pcholQ", "pmu0", "pcholP0", "g1", "gd", "gs", "d1", "d2", "obs_idx", "_ws")
+    _NAT_FIELDS = ("pA", "pb", "pcholQ", "pmu0", "pcholP0", "_g1", "_gd", "_gs", "d1", "d2", "obs_idx", "_ws")
 
     def _nat_signature(self):
         return tuple((t.data_ptr(), t._version) for t in (getattr(self, n) for n in self._NAT_FIELDS))
@@ -152,15 +188,25 @@ class CviEngine:
         replaced or modified in place through torch (storage pointer + version counter).
         """
         carry = self.carry_naturals if carry is None else carry
+        lazy = False
         if carry and self._nat_sig is not None and self._nat_sig == self._nat_signature():
             flags |= _lib.FLAG_NATURALS_CARRIED
-        p = self._problem(lr_data, lr_girsanov, flags)
+            # the library honours the lazy sites under these conditions (vdp_cvi.inl run_site_update)
+            lazy = (self.lazy_sites and self.n_obs <= 128 and not (flags & _lib.FLAG_SKIP_GIRSANOV)
+                    and not _env_on("VDP_NO_CARRIED_NATURALS") and not _env_on("VDP_NO_FUSED_NATURALS"))
+            if lazy:
+                flags |= _lib.FLAG_SITES_IN_NATURALS
+        p = self._problem(lr_data, lr_girsanov, flags, keep_carry=lazy)
         self._run("vdp_cvi_site_update", C.byref(p))
+        if lazy:
+            self._sites_stale = True
         if carry and (not (flags & _lib.FLAG_SKIP_GIRSANOV) or (flags & _lib.FLAG_NATURALS_CARRIED)):
             self._nat_sig = self._nat_signature()      # (a data-sites-only update leaves no dense data-site copy)
+        else:
+            self._nat_sig = None
         return self.elbo
 
-    _PTR_FIELDS = ("time_grid", "pA", "pb", "pcholQ", "pmu0", "pcholP0", "g1", "gd", "gs", "d1", "d2", "obs_idx", "obs_y",
+    _PTR_FIELDS = ("time_grid", "pA", "pb", "pcholQ", "pmu0", "pcholP0", "_g1", "_gd", "_gs", "d1", "d2", "obs_idx", "obs_y",
                    "fx_mus", "fx_covs", "qA", "qb", "qcholQ", "qmu0", "qcholP0", "elbo", "ve", "kl", "status")
 
     def site_update_graphed(self, lr_data, lr_girsanov, flags=0):
