@@ -19,6 +19,7 @@
 #include "scan_elems.cuh"
 #include "sweeps.cuh"
 #include "kl_kernels.cuh"
+#include "tma_tile.cuh"
 
 namespace vdp {
 
@@ -97,18 +98,32 @@ __global__ void k_seg_scan(const typename Ops::Elem* __restrict__ elems, const t
 }
 
 // ---------------------------------------------------------------------------------------------------
-// forward Cholesky over one staged tile: sKd holds K_kk for nodes [0, cnt] of the tile (in: K, out: L_kk),
-// sKs holds K_{k+1,k} for transitions [0, cnt) (in: K, out: L_{k+1,k}).
+// forward Cholesky over one staged tile: sKd holds X_kk for nodes [0, cnt] of the tile (in: X, out: L_kk),
+// sKs holds X_{k+1,k} for transitions [0, cnt) (in: X, out: L_{k+1,k}); the factorised matrix is
+// K = (scaleD X_d, scaleS X_s) (SCALED; the scales are applied as the operands are read, -2 / -1 for naturals).
+template <int D, bool SCALED>
+__device__ __forceinline__ Mat<D> tile_block(const double* p, double scale) {
+    Mat<D> m = mat_load<D>(p);
+    if (SCALED) {
+#pragma unroll
+        for (int e = 0; e < D * D; ++e) m.a[e] *= scale;
+    }
+    return m;
+}
 // Phase A: chunk element.
-template <int D, int L>
-__device__ __forceinline__ SchurElem<D> chol_tile_summary(const double* sKd, const double* sKs, int k0, int len) {
+template <int D, int L, bool SCALED = false>
+__device__ __forceinline__ SchurElem<D> chol_tile_summary(const double* sKd, const double* sKs, int k0, int len,
+                                                          double scaleD = 1.0, double scaleS = 1.0) {
     constexpr int DD = D * D;
     SchurElem<D> e = SchurOps<D>::identity();
     if constexpr (D == 1) {
         if (len == L) {   // full chunk: preloaded operands, unrolled; Lb carries the only serial dependency
             double ks[L], kd[L];
 #pragma unroll
-            for (int t = 0; t < L; ++t) { ks[t] = sKs[k0 + t]; kd[t] = sKd[k0 + t + 1]; }
+            for (int t = 0; t < L; ++t) {
+                ks[t] = SCALED ? scaleS * sKs[k0 + t] : sKs[k0 + t];
+                kd[t] = SCALED ? scaleD * sKd[k0 + t + 1] : sKd[k0 + t + 1];
+            }
             double La = 0.0, Lab = ks[0], Lb = kd[0];
 #pragma unroll
             for (int t = 1; t < L; ++t) {
@@ -123,14 +138,16 @@ __device__ __forceinline__ SchurElem<D> chol_tile_summary(const double* sKd, con
         }
     }
     for (int t = 0; t < len; ++t)
-        SchurOps<D>::push(e, mat_load<D>(sKs + (k0 + t) * DD), mat_load<D>(sKd + (k0 + t + 1) * DD));
+        SchurOps<D>::push(e, tile_block<D, SCALED>(sKs + (k0 + t) * DD, scaleS),
+                          tile_block<D, SCALED>(sKd + (k0 + t + 1) * DD, scaleD));
     return e;
 }
 // Phase C: reference-order recursion from the chunk's carry S (the Schur complement at node k0).
 // `last_node` = local index of the sequence's final node if it is in this tile, else -1.
-template <int D, int L>
+template <int D, int L, bool SCALED = false>
 __device__ __forceinline__ void chol_tile_recursion(double* sKd, double* sKs, int k0, int len, const Mat<D>& S,
-                                                    int last_node, int64_t flat_node0, int64_t* status) {
+                                                    int last_node, int64_t flat_node0, int64_t* status,
+                                                    double scaleD = 1.0, double scaleS = 1.0) {
     constexpr int DD = D * D;
     if (len <= 0) return;
     if constexpr (D == 1) {
@@ -140,7 +157,10 @@ __device__ __forceinline__ void chol_tile_recursion(double* sKd, double* sKs, in
         if (len == L && last_node < 0) {   // full chunk: operands preloaded, loops unrolled
             double ks[L], kd[L];
 #pragma unroll
-            for (int t = 0; t < L; ++t) { ks[t] = sKs[k0 + t]; kd[t] = (t < L - 1) ? sKd[k0 + t + 1] : 0.0; }
+            for (int t = 0; t < L; ++t) {
+                ks[t] = SCALED ? scaleS * sKs[k0 + t] : sKs[k0 + t];
+                kd[t] = (t < L - 1) ? (SCALED ? scaleD * sKd[k0 + t + 1] : sKd[k0 + t + 1]) : 0.0;
+            }
             double s = S.a[0];   // (node k0 + L belongs to the next chunk: never read here, its owner rewrites it)
             int bad = -1;
 #pragma unroll
@@ -159,13 +179,14 @@ __device__ __forceinline__ void chol_tile_recursion(double* sKd, double* sKs, in
         double s = S.a[0];
         for (int t = 0; t < len; ++t) {
             if (!(s > 0.0)) report_not_pd(status, flat_node0 + k0 + t);
-            const double ks = sKs[k0 + t];
+            const double ks = SCALED ? scaleS * sKs[k0 + t] : sKs[k0 + t];
             const double r = rcp_fast(s);
             double Lk, rL;
             sqrt_rsqrt_fast(s, Lk, rL);
             sKd[k0 + t] = Lk;
             sKs[k0 + t] = div_r(ks, Lk, rL);
-            if (t < len - 1 || k0 + len == last_node) s = fma(-(ks * ks), r, sKd[k0 + t + 1]);
+            if (t < len - 1 || k0 + len == last_node)
+                s = fma(-(ks * ks), r, SCALED ? scaleD * sKd[k0 + t + 1] : sKd[k0 + t + 1]);
         }
         if (k0 + len == last_node) {
             if (!(s > 0.0)) report_not_pd(status, flat_node0 + last_node);
@@ -178,11 +199,11 @@ __device__ __forceinline__ void chol_tile_recursion(double* sKd, double* sKs, in
     if (!ok) { report_not_pd(status, flat_node0 + k0); ok = true; }
     mat_store<D>(sKd + k0 * DD, Lk);
     for (int t = 0; t < len; ++t) {
-        const Mat<D> Ksub = mat_load<D>(sKs + (k0 + t) * DD);
+        const Mat<D> Ksub = tile_block<D, SCALED>(sKs + (k0 + t) * DD, scaleS);
         const Mat<D> Lsub = transpose(trsm(Lk, transpose(Ksub)));
         mat_store<D>(sKs + (k0 + t) * DD, Lsub);
         if (t < len - 1 || k0 + t + 1 == last_node) {
-            const Mat<D> Sn = mat_load<D>(sKd + (k0 + t + 1) * DD) - mmT(Lsub, Lsub);
+            const Mat<D> Sn = tile_block<D, SCALED>(sKd + (k0 + t + 1) * DD, scaleD) - mmT(Lsub, Lsub);
             Lk = chol(Sn, ok);
             if (!ok) { report_not_pd(status, flat_node0 + k0 + t + 1); ok = true; }
             mat_store<D>(sKd + (k0 + t + 1) * DD, Lk);
@@ -190,47 +211,85 @@ __device__ __forceinline__ void chol_tile_recursion(double* sKd, double* sKs, in
     }
 }
 
+// shared-memory layout of a sweep kernel with NSTAGE staged tiles: [mbarriers][stage 0 arrays][stage 1 arrays]...
+template <int NSTAGE>
+struct TileRing {
+    uint64_t* bar;
+    __device__ __forceinline__ void init(double* smem) {
+        bar = reinterpret_cast<uint64_t*>(smem);
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int s = 0; s < NSTAGE; ++s) mbar_init(bar + s, 1);
+            mbar_fence_init();
+        }
+        __syncthreads();
+    }
+    // all threads: tile `ti` (the ti-th this CTA staged) has landed in its stage
+    __device__ __forceinline__ void wait(int ti) {
+        mbar_wait(bar + ti % NSTAGE, (uint32_t)((ti / NSTAGE) & 1));
+        if (threadIdx.x == 0) ldgsts_wait_all();   // odd tail elements of the tile (tile_fetch)
+        __syncthreads();
+    }
+};
+constexpr int kRingHeaderDoubles = 2;   // room for up to two mbarriers, keeps the stage buffers 16-byte aligned
+
 // cholesky_band of K = (scaleD * Xd, scaleS * Xs)    block_tri_diag.py:428-440
-template <int D, int T, int L, int MODE>
+// Tiles move by TMA bulk copies through a ring of NSTAGE staging buffers (tma_tile.cuh): the copies of tile t + 1
+// are issued as soon as every thread has left tile t - 1 and land while tile t is scanned and replayed.
+template <int D, int T, int L, int MODE, int NSTAGE = 2>
 __global__ void __launch_bounds__(T)
 k_chol_tiled(const double* __restrict__ Xd, const double* __restrict__ Xs, double scaleD, double scaleS,
              double* __restrict__ Ld, double* __restrict__ Ls, int64_t B, int64_t N, int nseg, int64_t seg_len,
              const Mat<D>* __restrict__ carry_in, Mat<D>* __restrict__ init_out,
              SchurElem<D>* __restrict__ seg_elem, int64_t* status, int first = 1) {
     constexpr int DD = D * D, TL = T * L;
+    constexpr int SD = tile_slots((TL + 1) * DD), SS = tile_slots(TL * DD);
     extern __shared__ __align__(16) double smem[];
-    double* sKd = smem;
-    double* sKs = sKd + (TL + 1) * DD;
-    SchurElem<D>* wtot = reinterpret_cast<SchurElem<D>*>(sKs + TL * DD);
+    double* stage0 = smem + kRingHeaderDoubles;
+    SchurElem<D>* wtot = reinterpret_cast<SchurElem<D>*>(stage0 + NSTAGE * (SD + SS));
+    TileRing<NSTAGE> ring;
+    ring.init(smem);
     const int64_t b = blockIdx.x / nseg;
     const int seg = (int)(blockIdx.x % nseg);
     const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
     const double* xd = Xd + b * (N + 1) * DD;
     const double* xs = Xs + b * N * DD;
+    const int ntiles = (int)((t1 - t0 + TL - 1) / TL);
+    auto issue = [&](int ti) {   // thread 0: start the copies of tile ti
+        const int64_t tk = t0 + (int64_t)ti * TL;
+        const int cnt = (int)min((int64_t)TL, t1 - tk);
+        double* base = stage0 + (ti % NSTAGE) * (SD + SS);
+        uint64_t* bar = ring.bar + ti % NSTAGE;
+        uint32_t bytes = tile_fetch(base, xd + tk * DD, (cnt + 1) * DD, bar);
+        bytes += tile_fetch(base + SD, xs + tk * DD, cnt * DD, bar);
+        mbar_arrive_expect_tx(bar, bytes);
+    };
+    if (threadIdx.x == 0 && ntiles > 0) issue(0);
     Mat<D> S_tile = mat_zero<D>();
     if (MODE == SWEEP_FULL && (seg > 0 || !first)) S_tile = carry_in[b * nseg + seg];
     SchurElem<D> seg_tot = SchurOps<D>::identity();
-    for (int64_t tk = t0; tk < t1; tk += TL) {
+    for (int ti = 0; ti < ntiles; ++ti) {
+        const int64_t tk = t0 + (int64_t)ti * TL;
         const int cnt = (int)min((int64_t)TL, t1 - tk);
-        __syncthreads();
-        stage_in<T>(sKd, xd + tk * DD, (int64_t)(cnt + 1) * DD);
-        stage_in<T>(sKs, xs + tk * DD, (int64_t)cnt * DD);
-        stage_wait();
-        stage_scale<T>(sKd, (int64_t)(cnt + 1) * DD, scaleD);
-        stage_scale<T>(sKs, (int64_t)cnt * DD, scaleS);
-        __syncthreads();
-        if (tk + TL < t1) {
-            const int64_t nxt = min((int64_t)TL, t1 - (tk + TL));
-            prefetch_range<T>(xd + (tk + TL + 1) * DD, nxt * DD);
-            prefetch_range<T>(xs + (tk + TL) * DD, nxt * DD);
+        if (NSTAGE == 1 && ti > 0) {   // single buffer: refill once everybody has left the previous tile
+            __syncthreads();
+            if (threadIdx.x == 0) { bulk_wait_read(); issue(ti); }
         }
+        ring.wait(ti);
+        if (NSTAGE > 1 && threadIdx.x == 0 && ti + 1 < ntiles) {
+            bulk_wait_read();          // the bulk stores of tile ti - 1 have read the buffer tile ti + 1 goes into
+            issue(ti + 1);
+        }
+        double* base = stage0 + (ti % NSTAGE) * (SD + SS);
+        double* sKd = base + tile_off(xd + tk * DD);
+        double* sKs = base + SD + tile_off(xs + tk * DD);
         if (seg == 0 && tk == 0 && first) {
-            S_tile = mat_load<D>(sKd);
+            S_tile = tile_block<D, true>(sKd, scaleD);
             if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = S_tile;
         }
         const int k0 = threadIdx.x * L;
         const int len = min(L, cnt - k0);
-        const SchurElem<D> e = chol_tile_summary<D, L>(sKd, sKs, k0, len);
+        const SchurElem<D> e = chol_tile_summary<D, L, true>(sKd, sKs, k0, len, scaleD, scaleS);
         SchurElem<D> total;
         const SchurElem<D> excl = block_exclusive_scan<SchurOps<D>, T>(e, wtot, total);
         if (MODE != SWEEP_FULL) {
@@ -240,17 +299,30 @@ k_chol_tiled(const double* __restrict__ Xd, const double* __restrict__ Xs, doubl
         const Mat<D> S = SchurOps<D>::apply(excl, S_tile);
         S_tile = SchurOps<D>::apply(total, S_tile);
         const int last_node = (tk + cnt == N) ? cnt : -1;
-        chol_tile_recursion<D, L>(sKd, sKs, k0, len, S, last_node, b * (N + 1) + tk, status);
+        chol_tile_recursion<D, L, true>(sKd, sKs, k0, len, S, last_node, b * (N + 1) + tk, status, scaleD, scaleS);
+        fence_async_smem();
         __syncthreads();
-        stage_out<T>(Ld + (b * (N + 1) + tk) * DD, sKd, (int64_t)(cnt + (last_node >= 0 ? 1 : 0)) * DD);
-        stage_out<T>(Ls + (b * N + tk) * DD, sKs, (int64_t)cnt * DD);
+        double* gd = Ld + (b * (N + 1) + tk) * DD;
+        double* gs = Ls + (b * N + tk) * DD;
+        const int nd = (cnt + (last_node >= 0 ? 1 : 0)) * DD, ns = cnt * DD;
+        const bool bulk_d = tile_off(gd) == tile_off(xd + tk * DD), bulk_s = tile_off(gs) == tile_off(xs + tk * DD);
+        if (threadIdx.x == 0) {
+            if (bulk_d) tile_store_bulk(gd, sKd, nd);
+            if (bulk_s) tile_store_bulk(gs, sKs, ns);
+            bulk_commit();
+        }
+        if (!bulk_d) stage_out<T>(gd, sKd, nd);
+        if (!bulk_s) stage_out<T>(gs, sKs, ns);
     }
     if (MODE != SWEEP_FULL && threadIdx.x == 0) seg_elem[b * nseg + seg] = seg_tot;
+    if (threadIdx.x == 0) bulk_wait_all();
 }
 
-template <int D, int T, int L>
+template <int D, int T, int L, int NSTAGE = 2>
 constexpr size_t chol_tiled_smem() {
-    return ((size_t)(T * L + 1) * D * D + (size_t)T * L * D * D) * sizeof(double) + (T / 32) * sizeof(SchurElem<D>);
+    return ((size_t)kRingHeaderDoubles + (size_t)NSTAGE * (tile_slots((T * L + 1) * D * D) + tile_slots(T * L * D * D))) *
+               sizeof(double) +
+           (T / 32) * sizeof(SchurElem<D>);
 }
 
 

@@ -79,21 +79,21 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
     switch (p.kind) {
     case VDP_SWEEP_CHOL: {
         using Ops = SchurOps<D>;
-        constexpr size_t smem = chol_tiled_smem<D, C::T, C::Lc>();
+        constexpr size_t smem = chol_tiled_smem<D, C::T, C::Lc, kSweepStages>();
         const SegPlan pl = plan_segments(1, N, C::T * C::Lc, true);
         DistBufs<Ops> b;
         if (!dist_take<Ops>(sc, pl.nseg, b)) break;
         if (phase == 0) {
-            if ((rc = allow_smem(k_chol_tiled<D, C::T, C::Lc, SWEEP_SUMMARY>, smem))) return rc;
-            k_chol_tiled<D, C::T, C::Lc, SWEEP_SUMMARY><<<pl.nseg, C::T, smem, st>>>(
+            if ((rc = allow_smem(k_chol_tiled<D, C::T, C::Lc, SWEEP_SUMMARY, kSweepStages>, smem))) return rc;
+            k_chol_tiled<D, C::T, C::Lc, SWEEP_SUMMARY, kSweepStages><<<pl.nseg, C::T, smem, st>>>(
                 p.in[0], p.in[1], p.scaleD, p.scaleS, p.out[0], p.out[1], 1, N, pl.nseg, pl.seg_len, nullptr,
                 (Mat<D>*)init_blob, b.el, p.status, first);
             VDP_CHECK_LAUNCH();
             k_seg_total<Ops><<<1, 32, 0, st>>>(b.el, pl.nseg, 0, (typename Ops::Elem*)total_blob);
         } else {
             if ((rc = dist_carries<Ops>(b, totals, inits, p.rank, p.nranks, 0, pl.nseg, st))) return rc;
-            if ((rc = allow_smem(k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL>, smem))) return rc;
-            k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL><<<pl.nseg, C::T, smem, st>>>(
+            if ((rc = allow_smem(k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL, kSweepStages>, smem))) return rc;
+            k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL, kSweepStages><<<pl.nseg, C::T, smem, st>>>(
                 p.in[0], p.in[1], p.scaleD, p.scaleS, p.out[0], p.out[1], 1, N, pl.nseg, pl.seg_len, b.carry, nullptr,
                 nullptr, p.status, first);
         }

@@ -26,6 +26,12 @@ template <> struct TileCfg<1> { static constexpr int T = VDP_T1, Lc = VDP_LC1, L
 template <> struct TileCfg<2> { static constexpr int T = 64, Lc = 9, Li = 9, Lm = 5, Ln = 5; };
 template <> struct TileCfg<3> { static constexpr int T = 64, Lc = 5, Li = 5, Lm = 3, Ln = 3; };
 
+// staging buffers per sweep kernel: 2 = the copies of the next tile land while the current one is processed
+#ifndef VDP_SWEEP_STAGES
+#define VDP_SWEEP_STAGES 2
+#endif
+constexpr int kSweepStages = VDP_SWEEP_STAGES;
+
 constexpr int64_t kTargetBlocks = 148 * 4;     // CTAs wanted in flight before sequences are split in time
 constexpr int64_t kMaxSegTotal = 4096;         // bound on B * nseg (sizes the segment scratch)
 constexpr size_t kSegScratchBytes = 8u << 20;  // part of every fused-level workspace
@@ -99,13 +105,13 @@ template <int D>
 static int run_chol_tiled(const double* Xd, const double* Xs, double scaleD, double scaleS, double* Ld, double* Ls,
                           int64_t B, int64_t N, int64_t* status, SegScratch sc, cudaStream_t st) {
     using C = TileCfg<D>;
-    constexpr size_t smem = chol_tiled_smem<D, C::T, C::Lc>();
+    constexpr size_t smem = chol_tiled_smem<D, C::T, C::Lc, kSweepStages>();
     const SegPlan pl = plan_segments(B, N, C::T * C::Lc, sc.size > 0);
     const unsigned grid = (unsigned)(B * pl.nseg);
     int rc;
-    if ((rc = allow_smem(k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL>, smem))) return rc;
+    if ((rc = allow_smem(k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL, kSweepStages>, smem))) return rc;
     if (pl.nseg == 1) {
-        k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL><<<grid, C::T, smem, st>>>(Xd, Xs, scaleD, scaleS, Ld, Ls, B, N, 1,
+        k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL, kSweepStages><<<grid, C::T, smem, st>>>(Xd, Xs, scaleD, scaleS, Ld, Ls, B, N, 1,
                                                                            pl.seg_len, nullptr, nullptr, nullptr, status);
         VDP_CHECK_LAUNCH();
         return VDP_OK;
@@ -114,12 +120,12 @@ static int run_chol_tiled(const double* Xd, const double* Xs, double scaleD, dou
     Mat<D>* init = sc.take<Mat<D>>((size_t)B);
     SchurElem<D>* el = sc.take<SchurElem<D>>((size_t)B * pl.nseg);
     if (!el) { set_error("segment scratch too small"); return VDP_E_WORKSPACE; }
-    if ((rc = allow_smem(k_chol_tiled<D, C::T, C::Lc, SWEEP_SUMMARY>, smem))) return rc;
-    k_chol_tiled<D, C::T, C::Lc, SWEEP_SUMMARY><<<grid, C::T, smem, st>>>(Xd, Xs, scaleD, scaleS, Ld, Ls, B, N, pl.nseg,
+    if ((rc = allow_smem(k_chol_tiled<D, C::T, C::Lc, SWEEP_SUMMARY, kSweepStages>, smem))) return rc;
+    k_chol_tiled<D, C::T, C::Lc, SWEEP_SUMMARY, kSweepStages><<<grid, C::T, smem, st>>>(Xd, Xs, scaleD, scaleS, Ld, Ls, B, N, pl.nseg,
                                                                           pl.seg_len, nullptr, init, el, status);
     VDP_CHECK_LAUNCH();
     if ((rc = launch_seg_scan<SchurOps<D>>(el, init, carry, B, pl.nseg, 0, st))) return rc;
-    k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL><<<grid, C::T, smem, st>>>(Xd, Xs, scaleD, scaleS, Ld, Ls, B, N, pl.nseg,
+    k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL, kSweepStages><<<grid, C::T, smem, st>>>(Xd, Xs, scaleD, scaleS, Ld, Ls, B, N, pl.nseg,
                                                                        pl.seg_len, carry, nullptr, nullptr, status);
     VDP_CHECK_LAUNCH();
     return VDP_OK;
