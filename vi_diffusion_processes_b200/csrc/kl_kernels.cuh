@@ -317,8 +317,15 @@ struct KlHandoff { double gm[D]; double gS[D * D]; };
 // variational_cvi_sde.py:286-296 is applied in place instead of writing the gradients:
 //   g1 += lr (scatter(d1) - dKL/deta1),  gd += lr (scatter(d2) - dKL/deta_d),  gs -= lr dKL/deta_s
 // where scatter(d.) has been pre-scattered into sc1/scd by the caller.
+// register budget: the scalar kernel (one thread per grid point, blocks of 128) is bound by the latency of dependent
+// float64 instructions, so resident warps count for more than a few spilled words (measured on B200, C4 shape:
+// 56 registers 0.79 ms, 48: 0.76, 40 + 48 bytes of stack: 0.73)
+#ifndef VDP_KL_MINBLOCKS
+#define VDP_KL_MINBLOCKS 12
+#endif
+template <int G> struct KlBounds { static constexpr int threads = (G == 1) ? 128 : 256, blocks = (G == 1) ? VDP_KL_MINBLOCKS : 1; };
 template <int DRIFT, int D, int H, int G, bool CLOSED = false>
-__global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double dt, double pi_factor,
+__global__ void __launch_bounds__(KlBounds<G>::threads, KlBounds<G>::blocks) k_kl_grad(DriftParams P, Mat<D> q, double dt, double pi_factor,
                           const double* __restrict__ time_grid, Vec<D> x0_mu, Mat<D> x0_cov,
                           const double* __restrict__ Aq, const double* __restrict__ m,
                           const double* __restrict__ Sd, double* __restrict__ terms, double* __restrict__ g1,
@@ -338,7 +345,7 @@ __global__ void __launch_bounds__(256) k_kl_grad(DriftParams P, Mat<D> q, double
     const int64_t i = node0 + (int64_t)blockIdx.x * (groups - 1) + gidx - 1;   // flat node index of this group
     const bool in_range = (i >= 0) && (i < total);
     int64_t b = 0, k = 0;
-    if (in_range) { b = i / n; k = i % n; }
+    if (in_range) split_index(i, n, b, k);
     const bool has_term = in_range && (k < N);
     bool ok = true;
     KlTermOut<D> t;
@@ -519,7 +526,8 @@ __global__ void k_kl_value(DriftParams P, Mat<D> q, double dt, double pi_factor,
     const int64_t n = N + 1;
     if (i >= ((node1 < 0) ? B * n : node1)) return;
     constexpr int DD = D * D;
-    const int64_t b = i / n, k = i % n;
+    int64_t b, k;
+    split_index(i, n, b, k);
     if (k == N) { if (lane == 0) terms[i] = 0.0; return; }
     const int64_t tt = b * N + k;
     bool ok = true;

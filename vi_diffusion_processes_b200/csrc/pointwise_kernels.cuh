@@ -58,7 +58,8 @@ __global__ void k_ssm_to_naturals(const double* __restrict__ A, const double* __
     const int64_t n = N + 1;
     if (i >= B * n) return;
     constexpr int DD = D * D;
-    const int64_t b = i / n, k = i % n;
+    int64_t b, k;
+    split_index(i, n, b, k);
     const Mat<D> ck = (k == 0) ? mat_load<D>(cholP0 + b * DD) : mat_load<D>(cholQ + (b * N + k - 1) * DD);
     const Vec<D> ok = (k == 0) ? vec_load<D>(mu0 + b * D) : vec_load<D>(bo + (b * N + k - 1) * D);
     Mat<D> Ak = mat_zero<D>(), cn = mat_eye<D>(), td, ts;
@@ -189,7 +190,8 @@ __global__ void k_sites_from_naturals(const double* __restrict__ A, const double
     const int64_t n = N + 1;
     if (i >= B * n) return;
     constexpr int DD = D * D;
-    const int64_t b = i / n, k = i % n;
+    int64_t b, k;
+    split_index(i, n, b, k);
     const Mat<D> ck = (k == 0) ? mat_load<D>(cholP0 + b * DD) : mat_load<D>(cholQ + (b * N + k - 1) * DD);
     const Vec<D> ok = (k == 0) ? vec_load<D>(mu0 + b * D) : vec_load<D>(bo + (b * N + k - 1) * D);
     Mat<D> Ak = mat_zero<D>(), cn = mat_eye<D>(), td, ts;
@@ -214,7 +216,8 @@ __global__ void k_ssm_to_expectations(const double* __restrict__ A, const double
     const int64_t n = N + 1;
     if (i >= B * n) return;
     constexpr int DD = D * D;
-    const int64_t b = i / n, k = i % n;
+    int64_t b, k;
+    split_index(i, n, b, k);
     const Vec<D> mk = vec_load<D>(m + i * D);
     const Mat<D> Sk = mat_load<D>(Sd + i * DD);
     vec_store<D>(e1 + i * D, mk);
@@ -373,7 +376,8 @@ __global__ void k_expectations_to_ssm_vjp(const double* __restrict__ e1, const d
     const int64_t n = N + 1;
     if (i >= B * n) return;
     constexpr int DD = D * D;
-    const int64_t b = i / n, k = i % n;
+    int64_t b, k;
+    split_index(i, n, b, k);
     bool ok = true;
     Vec<D> gm = vec_zero<D>();
     Mat<D> gS = mat_zero<D>();

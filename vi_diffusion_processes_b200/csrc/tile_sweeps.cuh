@@ -471,7 +471,7 @@ struct MeanKlArgs {
     int tiles_per_seg = 0;
 };
 
-template <int D, int T, int L, int MODE, int DRIFT = -1>
+template <int D, int T, int L, int MODE, int DRIFT = -1, int NSTAGE = 2>
 __global__ void __launch_bounds__(T)
 k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const double* __restrict__ mu0,
              double* __restrict__ m, int64_t B, int64_t N, int nseg, int64_t seg_len,
@@ -481,38 +481,47 @@ k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
     constexpr bool KL = (DRIFT >= 0) && (MODE == SWEEP_FULL);
     static_assert(DRIFT < 0 || D == 1, "the fused KL terms are scalar");
     using Ops = AffVecOps<D>;
+    constexpr int SM = tile_slots(TL * DD), SV = tile_slots(TL * D), S1 = tile_slots(TL);
+    constexpr int kStage = SM + SV + (KL ? 2 * S1 : 0);                   // A, b, [S, chol Q]
     extern __shared__ __align__(16) double smem[];
-    double* sA = smem;                        // A of transition i               (TL)
-    double* sb = sA + TL * DD;                // offsets -> m_{k+1}              (TL)
-    double* sS = sb + TL * D;                 // S of node i                     (TL, KL only)
-    double* sQ = sS + (KL ? TL : 0);          // chol Q of transition i          (TL, KL only)
-    typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(sQ + (KL ? TL : 0));
+    double* stage0 = smem + kRingHeaderDoubles;
+    typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(stage0 + NSTAGE * kStage);
+    TileRing<NSTAGE> ring;
+    ring.init(smem);
     const int64_t b = blockIdx.x / nseg;
     const int seg = (int)(blockIdx.x % nseg);
     const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
+    const int ntiles = (int)((t1 - t0 + TL - 1) / TL);
+    auto issue = [&](int ti) {   // thread 0: start the copies of tile ti
+        const int64_t tk = t0 + (int64_t)ti * TL;
+        const int cnt = (int)min((int64_t)TL, t1 - tk);
+        double* base = stage0 + (ti % NSTAGE) * kStage;
+        uint64_t* bar = ring.bar + ti % NSTAGE;
+        uint32_t bytes = tile_fetch(base, A + (b * N + tk) * DD, cnt * DD, bar);
+        bytes += tile_fetch(base + SM, bo + (b * N + tk) * D, cnt * D, bar);
+        if (KL) {
+            bytes += tile_fetch(base + SM + SV, kl.Sd + (b * (N + 1) + tk), cnt, bar);
+            bytes += tile_fetch(base + SM + SV + S1, kl.cholQ + (b * N + tk), cnt, bar);
+        }
+        mbar_arrive_expect_tx(bar, bytes);
+    };
+    if (threadIdx.x == 0 && ntiles > 0) issue(0);
     Vec<D> st = vec_zero<D>();
     if (MODE == SWEEP_FULL && seg > 0) st = carry_in[b * nseg + seg];
     typename Ops::Elem seg_tot = Ops::identity();
-    for (int64_t tk = t0; tk < t1; tk += TL) {
+    for (int ti = 0; ti < ntiles; ++ti) {
+        const int64_t tk = t0 + (int64_t)ti * TL;
         const int cnt = (int)min((int64_t)TL, t1 - tk);
-        __syncthreads();
-        stage_in<T>(sA, A + (b * N + tk) * DD, (int64_t)cnt * DD);
-        stage_in<T>(sb, bo + (b * N + tk) * D, (int64_t)cnt * D);
-        if (KL) {
-            stage_in<T>(sS, kl.Sd + (b * (N + 1) + tk), (int64_t)cnt);
-            stage_in<T>(sQ, kl.cholQ + (b * N + tk), (int64_t)cnt);
+        if (NSTAGE == 1 && ti > 0) {
+            __syncthreads();
+            if (threadIdx.x == 0) { bulk_wait_read(); issue(ti); }
         }
-        stage_wait();
-        __syncthreads();
-        if (tk + TL < t1) {   // next tile on its way into L2
-            const int64_t nk = tk + TL, ncnt = min((int64_t)TL, t1 - nk);
-            prefetch_range<T>(A + (b * N + nk) * DD, ncnt * DD);
-            prefetch_range<T>(bo + (b * N + nk) * D, ncnt * D);
-            if (KL) {
-                prefetch_range<T>(kl.Sd + (b * (N + 1) + nk), ncnt);
-                prefetch_range<T>(kl.cholQ + (b * N + nk), ncnt);
-            }
-        }
+        ring.wait(ti);
+        double* base = stage0 + (ti % NSTAGE) * kStage;
+        double* sA = base + tile_off(A + (b * N + tk) * DD);                  // A of transition i
+        double* sb = base + SM + tile_off(bo + (b * N + tk) * D);             // offsets -> m_{k+1}
+        double* sS = base + SM + SV + (KL ? tile_off(kl.Sd + (b * (N + 1) + tk)) : 0);       // S of node i (KL only)
+        double* sQ = base + SM + SV + S1 + (KL ? tile_off(kl.cholQ + (b * N + tk)) : 0);     // chol Q of transition i
         if (seg == 0 && tk == 0) {
             st = vec_load<D>(mu0 + b * D);
             if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = st;
@@ -526,6 +535,10 @@ k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
             s.M = mat_load<D>(sA + (k0 + t) * DD);
             s.v = vec_load<D>(sb + (k0 + t) * D);
             e = Ops::combine(e, s);
+        }
+        if (NSTAGE > 1 && threadIdx.x == 0 && ti + 1 < ntiles) {
+            bulk_wait_read();
+            issue(ti + 1);
         }
         typename Ops::Elem total;
         const typename Ops::Elem excl = block_exclusive_scan<Ops, T>(e, wtot, total);
@@ -551,8 +564,10 @@ k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
             vec_store<D>(sb + (k0 + t) * D, mk);
         }
         if (KL && len > 0) kl_acc -= log(kl_ratio);      // sum of 0.5 (-2 log ratio_t)
+        fence_async_smem();
         __syncthreads();
-        stage_out<T>(m + (b * (N + 1) + tk + 1) * D, sb, (int64_t)cnt * D);
+        tile_store<T>(m + (b * (N + 1) + tk + 1) * D, sb, cnt * D);
+        if (threadIdx.x == 0) bulk_commit();
         if constexpr (KL) {
             if (seg == 0 && tk == 0 && threadIdx.x == 0) {
                 bool ok = true;
@@ -569,12 +584,17 @@ k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
                 kl.partials[((int64_t)b * nseg + seg) * kl.tiles_per_seg + (tk - t0) / TL] = sS[0];
         }
     }
-    if (MODE != SWEEP_FULL && threadIdx.x == 0) seg_elem[b * nseg + seg] = seg_tot;
+    if (threadIdx.x == 0) {
+        if (MODE != SWEEP_FULL) seg_elem[b * nseg + seg] = seg_tot;
+        bulk_wait_all();
+    }
 }
 
-template <int D, int T, int L, bool KL = false>
+template <int D, int T, int L, bool KL = false, int NSTAGE = 2>
 constexpr size_t mean_tiled_smem() {
-    return ((size_t)T * L * D * D + (size_t)T * L * D + (KL ? 2 * (size_t)T * L : 0)) * sizeof(double) +
+    return ((size_t)kRingHeaderDoubles +
+            (size_t)NSTAGE * (tile_slots(T * L * D * D) + tile_slots(T * L * D) + (KL ? 2 * tile_slots(T * L) : 0))) *
+               sizeof(double) +
            (T / 32) * sizeof(AffVecElem<D>);
 }
 
@@ -691,7 +711,7 @@ constexpr size_t invband_tiled_smem() {
 // COV: the diagonal blocks of the inverse band the Sigma recursion walks through are the marginal covariances of the
 // Gaussian the naturals describe; they are staged out as well (Sd [B, N+1, D, D]), which makes a separate
 // inverse-band sweep over the same factor unnecessary in the posterior rebuild.
-template <int D, int T, int L, int MODE, bool FROML = false, bool COV = false>
+template <int D, int T, int L, int MODE, bool FROML = false, bool COV = false, int NSTAGE = 2>
 __global__ void __launch_bounds__(T)
 k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, const double* __restrict__ th1,
                 const double* __restrict__ thd, const double* __restrict__ ths, double* __restrict__ A,
@@ -702,19 +722,37 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
                 AffVecElem<D>* __restrict__ seg_elemY, int64_t* status, int first = 1, int last = 1,
                 double* __restrict__ Sd = nullptr) {
     constexpr int DD = D * D, TL = T * L;
+    constexpr int SM = tile_slots(TL * DD), SV = tile_slots(TL * D);      // slots of a staged matrix / vector array
+    constexpr int kStage = (FROML ? 2 : 4) * SM + SV;                     // Ld, Ls, [thd, ths,] th1
     extern __shared__ __align__(16) double smem[];
-    double* sLd = smem;              // L_kk  -> chol of the conditional covariance of node k
-    double* sLs = sLd + TL * DD;     // L_sub -> A_k
-    double* sTd = sLs + TL * DD;     // theta_diag -> conditional covariance of node k   (not FROML)
-    double* sTs = sTd + TL * DD;     // theta_sub                                         (not FROML)
-    double* sT1 = FROML ? sLs + TL * DD : sTs + TL * DD;     // theta_1 -> offset of node k
-    double* sSd = sT1 + TL * D;      // marginal covariance of node k                     (COV)
-    AffSymElem<D>* wtotS = reinterpret_cast<AffSymElem<D>*>(sSd + (COV ? TL * DD : 0));
+    double* stage0 = smem + kRingHeaderDoubles;
+    double* rawSd = stage0 + NSTAGE * kStage;                              // marginal covariances (COV; output only)
+    AffSymElem<D>* wtotS = reinterpret_cast<AffSymElem<D>*>(rawSd + (COV ? SM : 0));
     AffVecElem<D>* wtotY = reinterpret_cast<AffVecElem<D>*>(wtotS);   // used after the Sigma scan is over
+    TileRing<NSTAGE> ring;
+    ring.init(smem);
     const int64_t b = blockIdx.x / nseg;
     const int seg = (int)(blockIdx.x % nseg);
     const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
     const int64_t n = N + 1;
+    const int ntiles = (int)((t1 - t0 + TL - 1) / TL);
+    auto issue = [&](int ti) {   // thread 0: start the copies of the ti-th tile from the top
+        const int64_t hi = t1 - (int64_t)ti * TL, lo = max(t0, hi - TL);
+        const int cnt = (int)(hi - lo);
+        double* base = stage0 + (ti % NSTAGE) * kStage;
+        uint64_t* bar = ring.bar + ti % NSTAGE;
+        uint32_t bytes = tile_fetch(base, Ld + (b * n + lo) * DD, cnt * DD, bar);
+        bytes += tile_fetch(base + SM, Ls + (b * N + lo) * DD, cnt * DD, bar);
+        if (MODE != SWEEP_SUMMARY) {
+            if (!FROML) {
+                bytes += tile_fetch(base + 2 * SM, thd + (b * n + lo) * DD, cnt * DD, bar);
+                bytes += tile_fetch(base + 3 * SM, ths + (b * N + lo) * DD, cnt * DD, bar);
+            }
+            bytes += tile_fetch(base + (FROML ? 2 : 4) * SM, th1 + (b * n + lo) * D, cnt * D, bar);
+        }
+        mbar_arrive_expect_tx(bar, bytes);
+    };
+    if (threadIdx.x == 0 && ntiles > 0) issue(0);
     Mat<D> S_tile = mat_zero<D>();
     Vec<D> y_tile = vec_zero<D>();
     if (t1 == N && last) {
@@ -745,27 +783,21 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
     }
     AffSymElem<D> seg_totS = AffSymOps<D>::identity();
     AffVecElem<D> seg_totY = AffVecOps<D>::identity();
-    for (int64_t hi = t1; hi > t0; hi -= TL) {
-        const int64_t lo = max(t0, hi - TL);
+    for (int ti = 0; ti < ntiles; ++ti) {
+        const int64_t hi = t1 - (int64_t)ti * TL, lo = max(t0, hi - TL);
         const int cnt = (int)(hi - lo);
-        __syncthreads();
-        stage_in<T>(sLd, Ld + (b * n + lo) * DD, (int64_t)cnt * DD);
-        stage_in<T>(sLs, Ls + (b * N + lo) * DD, (int64_t)cnt * DD);
-        if (MODE != SWEEP_SUMMARY) {
-            if (!FROML) {
-                stage_in<T>(sTd, thd + (b * n + lo) * DD, (int64_t)cnt * DD);
-                stage_in<T>(sTs, ths + (b * N + lo) * DD, (int64_t)cnt * DD);
-            }
-            stage_in<T>(sT1, th1 + (b * n + lo) * D, (int64_t)cnt * D);
+        if (NSTAGE == 1 && ti > 0) {
+            __syncthreads();
+            if (threadIdx.x == 0) { bulk_wait_read(); issue(ti); }
         }
-        stage_wait();
-        __syncthreads();
-        if (lo > t0) {
-            const int64_t nlo = max(t0, lo - TL);
-            prefetch_range<T>(Ld + (b * n + nlo) * DD, (lo - nlo) * DD);
-            prefetch_range<T>(Ls + (b * N + nlo) * DD, (lo - nlo) * DD);
-            if (MODE != SWEEP_SUMMARY) prefetch_range<T>(th1 + (b * n + nlo) * D, (lo - nlo) * D);
-        }
+        ring.wait(ti);
+        double* base = stage0 + (ti % NSTAGE) * kStage;
+        double* sLd = base + tile_off(Ld + (b * n + lo) * DD);                 // L_kk  -> chol of the conditional covariance
+        double* sLs = base + SM + tile_off(Ls + (b * N + lo) * DD);            // L_sub -> A_k
+        double* sTd = base + 2 * SM + tile_off(thd + (b * n + lo) * DD);       // theta_diag -> conditional covariance (not FROML)
+        double* sTs = base + 3 * SM + tile_off(ths + (b * N + lo) * DD);       // theta_sub                         (not FROML)
+        double* sT1 = base + (FROML ? 2 : 4) * SM + tile_off(th1 + (b * n + lo) * D);   // theta_1 -> offset of node k
+        double* sSd = rawSd + (COV ? tile_off(Sd + (b * n + lo) * DD) : 0);    // placed with the parity of its destination
         const BwdChunk ch = bwd_chunk<L>(cnt);
         // FROML: L_{bot,bot-1}, the block below this thread's chunk (the neighbour overwrites it in its recursion)
         Mat<D> Lbelow = mat_zero<D>();
@@ -774,6 +806,14 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
             else if (lo >= 1) Lbelow = mat_load<D>(Ls + (b * N + lo - 1) * DD);
         }
         const AffSymElem<D> eS = invband_tile_summary<D>(sLd, sLs, ch);
+        if (NSTAGE > 1 && threadIdx.x == 0 && ti + 1 < ntiles) {
+            // (here rather than at the top of the tile: the bulk stores of the previous tile, whose buffer the next
+            // tile goes into, have had this thread's summary phase to read their source)
+            bulk_wait_read();
+            issue(ti + 1);
+        } else if (COV && threadIdx.x == 0) {
+            bulk_wait_read();   // sSd is one buffer: its previous store must have read it before the recursion below
+        }
         AffSymElem<D> totalS;
         const AffSymElem<D> exclS = block_exclusive_scan<AffSymOps<D>, T>(eS, wtotS, totalS);
         if (MODE == SWEEP_SUMMARY) {
@@ -826,30 +866,35 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
             else cov = mat_load<D>(sTd + k * DD);
             vec_store<D>(sT1 + k * D, mv(cov, y));
         }
+        fence_async_smem();
         __syncthreads();
-        stage_out<T>(A + (b * N + lo) * DD, sLs, (int64_t)cnt * DD);
-        if (COV) stage_out<T>(Sd + (b * n + lo) * DD, sSd, (int64_t)cnt * DD);
         // (cholQ == NULL: the caller has no use for the process-noise factors, e.g. the rebuild between the data-site
         // and the girsanov-site update, whose consumer reads A, the means and the marginal covariances only)
+        tile_store<T>(A + (b * N + lo) * DD, sLs, cnt * DD);
+        if (COV) tile_store<T>(Sd + (b * n + lo) * DD, sSd, cnt * DD);
         if (lo >= 1 || !first) {   // time-sharded ranks own one slot before index 0 of bo / cholQ
-            stage_out<T>(bo + (b * N + lo - 1) * D, sT1, (int64_t)cnt * D);
-            if (cholQ) stage_out<T>(cholQ + (b * N + lo - 1) * DD, sLd, (int64_t)cnt * DD);
+            tile_store<T>(bo + (b * N + lo - 1) * D, sT1, cnt * D);
+            if (cholQ) tile_store<T>(cholQ + (b * N + lo - 1) * DD, sLd, cnt * DD);
         } else {
             stage_out<T>(mu0 + b * D, sT1, D);
             stage_out<T>(cholP0 + b * DD, sLd, DD);
-            stage_out<T>(bo + b * N * D, sT1 + D, (int64_t)(cnt - 1) * D);
-            if (cholQ) stage_out<T>(cholQ + b * N * DD, sLd + DD, (int64_t)(cnt - 1) * DD);
+            tile_store<T>(bo + b * N * D, sT1 + D, (cnt - 1) * D);
+            if (cholQ) tile_store<T>(cholQ + b * N * DD, sLd + DD, (cnt - 1) * DD);
         }
+        if (threadIdx.x == 0) bulk_commit();
     }
     if (threadIdx.x == 0) {
         if (MODE == SWEEP_SUMMARY) seg_elemS[b * nseg + seg] = seg_totS;
         if (MODE == SWEEP_SUMMARY2) seg_elemY[b * nseg + seg] = seg_totY;
+        bulk_wait_all();
     }
 }
 
-template <int D, int T, int L, bool FROML = false, bool COV = false>
+template <int D, int T, int L, bool FROML = false, bool COV = false, int NSTAGE = 2>
 constexpr size_t nat2ssm_tiled_smem() {
-    return (((FROML ? 2 : 4) + (COV ? 1 : 0)) * (size_t)T * L * D * D + (size_t)T * L * D) * sizeof(double) +
+    return ((size_t)kRingHeaderDoubles +
+            (size_t)NSTAGE * ((FROML ? 2 : 4) * tile_slots(T * L * D * D) + tile_slots(T * L * D)) +
+            (COV ? tile_slots(T * L * D * D) : 0)) * sizeof(double) +
            (T / 32) * (sizeof(AffSymElem<D>) > sizeof(AffVecElem<D>) ? sizeof(AffSymElem<D>) : sizeof(AffVecElem<D>));
 }
 

@@ -106,4 +106,16 @@ __device__ __forceinline__ bool tile_store_bulk(double* g, const double* s, int 
     return true;
 }
 
+// ALL T threads of the block (after fence_async_smem + barrier): store a tile's array, as one bulk store when the parity
+// of shared and global position agree, else with coalesced thread stores.  Thread 0 commits the bulk group afterwards.
+template <int T>
+__device__ __forceinline__ void tile_store(double* __restrict__ g, const double* __restrict__ s, int count) {
+    if (count <= 0) return;
+    if (tile_off(g) == (int)((smem_u32(s) >> 3) & 1u)) {
+        if (threadIdx.x == 0) tile_store_bulk(g, s, count);
+    } else {
+        for (int i = threadIdx.x; i < count; i += T) g[i] = s[i];
+    }
+}
+
 }  // namespace vdp

@@ -24,7 +24,8 @@ __global__ void k_ssm_kl_terms(const double* __restrict__ A1, const double* __re
     const int64_t n = N + 1;
     if (i >= B * n) return;
     constexpr int DD = D * D;
-    const int64_t b = i / n, k = i % n;
+    int64_t b, k;
+    split_index(i, n, b, k);
     const Mat<D> S = mat_load<D>(S1 + i * DD);
     const Mat<D> Pd = -2.0 * mat_load<D>(thd2 + i * DD);
     double trace = 0.0;

@@ -11,7 +11,7 @@ template <int D> struct TileCfg;
 #define VDP_T1 128
 #endif
 #ifndef VDP_LC1
-#define VDP_LC1 17
+#define VDP_LC1 9
 #endif
 #ifndef VDP_LI1
 #define VDP_LI1 17
@@ -30,7 +30,21 @@ template <> struct TileCfg<3> { static constexpr int T = 64, Lc = 5, Li = 5, Lm 
 #ifndef VDP_SWEEP_STAGES
 #define VDP_SWEEP_STAGES 2
 #endif
-constexpr int kSweepStages = VDP_SWEEP_STAGES;
+#ifndef VDP_STAGES_C
+#define VDP_STAGES_C VDP_SWEEP_STAGES
+#endif
+// (measured on B200, C4 shape, T = 128: Cholesky L = 9 with 2 stages 0.228 ms (L = 17: 0.257; 1 stage: 0.232);
+// naturals_to_ssm L = 9 with 1 stage 0.407 ms (2 stages halve the CTAs per SM: 0.538; L = 5 with 2 stages 0.427);
+// means L = 9 with 1 stage 0.216 ms (2 stages 0.226): the ring only pays where it does not cost occupancy)
+#ifndef VDP_STAGES_N
+#define VDP_STAGES_N 1
+#endif
+#ifndef VDP_STAGES_M
+#define VDP_STAGES_M 1
+#endif
+constexpr int kSweepStages = VDP_STAGES_C;   // Cholesky sweep
+constexpr int kStagesN = VDP_STAGES_N;       // naturals_to_ssm backward sweep
+constexpr int kStagesM = VDP_STAGES_M;       // mean sweep
 
 constexpr int64_t kTargetBlocks = 148 * 4;     // CTAs wanted in flight before sequences are split in time
 constexpr int64_t kMaxSegTotal = 4096;         // bound on B * nseg (sizes the segment scratch)
@@ -169,14 +183,14 @@ static int run_nat2ssm_bwd_tiled_impl(const double* Ld, const double* Ls, const 
                                       double* cholP0, int64_t B, int64_t N, int64_t* status, SegScratch sc,
                                       cudaStream_t st, double* Sd) {
     using C = TileCfg<D>;
-    constexpr size_t smem = nat2ssm_tiled_smem<D, C::T, C::Ln, true>();
-    constexpr size_t smem_full = nat2ssm_tiled_smem<D, C::T, C::Ln, true, COV>();
+    constexpr size_t smem = nat2ssm_tiled_smem<D, C::T, C::Ln, true, false, kStagesN>();
+    constexpr size_t smem_full = nat2ssm_tiled_smem<D, C::T, C::Ln, true, COV, kStagesN>();
     const SegPlan pl = plan_segments(B, N, C::T * C::Ln, sc.size > 0);
     const unsigned grid = (unsigned)(B * pl.nseg);
     int rc;
-    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true, COV>, smem_full))) return rc;
+    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true, COV, kStagesN>, smem_full))) return rc;
     if (pl.nseg == 1) {
-        k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true, COV><<<grid, C::T, smem_full, st>>>(
+        k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true, COV, kStagesN><<<grid, C::T, smem_full, st>>>(
             Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, 1, pl.seg_len, nullptr, nullptr, nullptr, nullptr,
             nullptr, nullptr, status, 1, 1, Sd);
         VDP_CHECK_LAUNCH();
@@ -189,19 +203,19 @@ static int run_nat2ssm_bwd_tiled_impl(const double* Ld, const double* Ls, const 
     AffSymElem<D>* elS = sc.take<AffSymElem<D>>((size_t)B * pl.nseg);
     AffVecElem<D>* elY = sc.take<AffVecElem<D>>((size_t)B * pl.nseg);
     if (!elY) { set_error("segment scratch too small"); return VDP_E_WORKSPACE; }
-    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY, true>, smem))) return rc;
-    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2, true>, smem))) return rc;
-    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY, true><<<grid, C::T, smem, st>>>(
+    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY, true, false, kStagesN>, smem))) return rc;
+    if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2, true, false, kStagesN>, smem))) return rc;
+    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY, true, false, kStagesN><<<grid, C::T, smem, st>>>(
         Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, pl.nseg, pl.seg_len, nullptr, nullptr, initS, initY, elS,
         elY, status);
     VDP_CHECK_LAUNCH();
     if ((rc = launch_seg_scan<AffSymOps<D>>(elS, initS, carryS, B, pl.nseg, 1, st))) return rc;
-    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2, true><<<grid, C::T, smem, st>>>(
+    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2, true, false, kStagesN><<<grid, C::T, smem, st>>>(
         Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, pl.nseg, pl.seg_len, carryS, nullptr, initS, initY, elS,
         elY, status);
     VDP_CHECK_LAUNCH();
     if ((rc = launch_seg_scan<AffVecOps<D>>(elY, initY, carryY, B, pl.nseg, 1, st))) return rc;
-    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true, COV><<<grid, C::T, smem_full, st>>>(
+    k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, true, COV, kStagesN><<<grid, C::T, smem_full, st>>>(
         Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, pl.nseg, pl.seg_len, carryS, carryY, nullptr, nullptr,
         nullptr, nullptr, status, 1, 1, Sd);
     VDP_CHECK_LAUNCH();
@@ -265,8 +279,8 @@ static int run_mean_fwd_tiled(const double* A, const double* b, const double* mu
     using Ops = AffVecOps<D>;
     constexpr bool KL = DRIFT >= 0;
     constexpr int L = (D == 1) ? C::Lm : 2 * C::Lm;   // the same tile (and rounding order of the means) with and without KL
-    constexpr size_t smem = mean_tiled_smem<D, C::T, L>();
-    constexpr size_t smem_full = mean_tiled_smem<D, C::T, L, KL>();
+    constexpr size_t smem = mean_tiled_smem<D, C::T, L, false, kStagesM>();
+    constexpr size_t smem_full = mean_tiled_smem<D, C::T, L, KL, kStagesM>();
     const SegPlan pl = plan_segments(B, N, C::T * L, sc.size > 0);
     const unsigned grid = (unsigned)(B * pl.nseg);
     MeanKlArgs ka;
@@ -277,9 +291,9 @@ static int run_mean_fwd_tiled(const double* A, const double* b, const double* mu
         VDP_CHECK_CUDA(cudaMemsetAsync(ka.partials, 0, (size_t)B * *n_partials * sizeof(double), st));
     }
     int rc;
-    if ((rc = allow_smem(k_mean_tiled<D, C::T, L, SWEEP_FULL, DRIFT>, smem_full))) return rc;
+    if ((rc = allow_smem(k_mean_tiled<D, C::T, L, SWEEP_FULL, DRIFT, kStagesM>, smem_full))) return rc;
     if (pl.nseg == 1) {
-        k_mean_tiled<D, C::T, L, SWEEP_FULL, DRIFT><<<grid, C::T, smem_full, st>>>(A, b, mu0, m, B, N, 1, pl.seg_len,
+        k_mean_tiled<D, C::T, L, SWEEP_FULL, DRIFT, kStagesM><<<grid, C::T, smem_full, st>>>(A, b, mu0, m, B, N, 1, pl.seg_len,
                                                                                  nullptr, nullptr, nullptr, ka);
         VDP_CHECK_LAUNCH();
         return VDP_OK;
@@ -288,12 +302,12 @@ static int run_mean_fwd_tiled(const double* A, const double* b, const double* mu
     typename Ops::State* init = sc.take<typename Ops::State>((size_t)B);
     typename Ops::Elem* el = sc.take<typename Ops::Elem>((size_t)B * pl.nseg);
     if (!el) { set_error("segment scratch too small"); return VDP_E_WORKSPACE; }
-    if ((rc = allow_smem(k_mean_tiled<D, C::T, L, SWEEP_SUMMARY>, smem))) return rc;
-    k_mean_tiled<D, C::T, L, SWEEP_SUMMARY><<<grid, C::T, smem, st>>>(A, b, mu0, m, B, N, pl.nseg, pl.seg_len, nullptr,
+    if ((rc = allow_smem(k_mean_tiled<D, C::T, L, SWEEP_SUMMARY, -1, kStagesM>, smem))) return rc;
+    k_mean_tiled<D, C::T, L, SWEEP_SUMMARY, -1, kStagesM><<<grid, C::T, smem, st>>>(A, b, mu0, m, B, N, pl.nseg, pl.seg_len, nullptr,
                                                                     init, el);
     VDP_CHECK_LAUNCH();
     if ((rc = launch_seg_scan<Ops>(el, init, carry, B, pl.nseg, 0, st))) return rc;
-    k_mean_tiled<D, C::T, L, SWEEP_FULL, DRIFT><<<grid, C::T, smem_full, st>>>(A, b, mu0, m, B, N, pl.nseg, pl.seg_len,
+    k_mean_tiled<D, C::T, L, SWEEP_FULL, DRIFT, kStagesM><<<grid, C::T, smem_full, st>>>(A, b, mu0, m, B, N, pl.nseg, pl.seg_len,
                                                                              carry, nullptr, nullptr, ka);
     VDP_CHECK_LAUNCH();
     return VDP_OK;
