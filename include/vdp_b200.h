@@ -290,6 +290,26 @@ int vdp_cvi_materialize_sites(const vdp_cvi_problem* problem_host, void* stream)
  * With the full range [0, B (N+1)) the two phases together equal vdp_cvi_site_update. */
 int vdp_cvi_site_update_sharded(const vdp_cvi_problem* problem_host, int phase, int64_t node_begin,
                                 int64_t node_end, void* stream);
+/* The steps of a site update one at a time, WITHOUT the posterior rebuild between them -- for callers that rebuild
+ * the posterior themselves, e.g. on a time-sharded chain (vdp_dist_sweep_*, BASELINE config 5) where `problem` is a
+ * rank's local stretch of the chain extended by one halo grid point at either end:
+ *   vdp_cvi_update_data_sites            update_data_sites, variational_cvi_sde.py:301-314 (the gradient step only;
+ *                                        reads fx_mus at the observed grid points, writes d1, d2)
+ *   vdp_cvi_full_sites                   full_sites, :161-174: theta = nat(p) + g + scatter(data sites)
+ *                                        -> th1 [B,N+1,D], thd [B,N+1,D,D], ths [B,N,D,D]
+ *   vdp_cvi_update_girsanov_sites_range  update_girsanov_sites, :279-296, on the flat node range [begin, end): reads
+ *                                        qA, fx_mus, fx_covs (valid on the range and one grid point either side),
+ *                                        updates g1, gd on the range and gs on its transitions; KL_0 enters at grid
+ *                                        point 0 of the problem if the range holds it
+ *   vdp_cvi_elbo_terms_range             the terms of classic_elbo, :339-352, from q*, fx_mus, fx_covs as they are:
+ *                                        ve [B] over the problem's observations, kl [B] = the range's partial sum,
+ *                                        elbo = ve - kl */
+int vdp_cvi_update_data_sites(const vdp_cvi_problem* problem_host, void* stream);
+int vdp_cvi_full_sites(const vdp_cvi_problem* problem_host, double* th1, double* thd, double* ths, void* stream);
+int vdp_cvi_update_girsanov_sites_range(const vdp_cvi_problem* problem_host, int64_t node_begin, int64_t node_end,
+                                        void* stream);
+int vdp_cvi_elbo_terms_range(const vdp_cvi_problem* problem_host, int64_t node_begin, int64_t node_end, void* stream);
+
 /* classic_elbo only (no site is modified); fills elbo/ve/kl, q* and fx_* */
 int vdp_cvi_elbo(const vdp_cvi_problem* problem_host, void* stream);
 
@@ -464,6 +484,18 @@ typedef struct vdp_dist_sweep {
     size_t workspace_bytes;
     int64_t* status;
 } vdp_dist_sweep;
+
+/* Exchange between ranks issued from C on the compute stream: a communicator over NCCL (bound at run time with
+ * dlopen("libnccl.so.2"); the library has no link-time dependency on NCCL).  One process per GPU:
+ *     rank 0: vdp_comm_unique_id(id)  ->  the 128 bytes travel to every rank by any out-of-band channel
+ *     every rank, its GPU current:  vdp_comm_create(&comm, id, rank, nranks)
+ *     vdp_comm_all_gather(comm, send, recv, bytes_per_rank, stream): recv [nranks x bytes_per_rank], device memory,
+ *     asynchronous on `stream` (ncclAllGather); this is the all-gather of the sequence above. */
+typedef struct vdp_comm vdp_comm;
+int vdp_comm_unique_id(void* id128_host);
+int vdp_comm_create(vdp_comm** comm, const void* id128_host, int rank, int nranks);
+int vdp_comm_all_gather(vdp_comm* comm, const void* send, void* recv, size_t bytes_per_rank, void* stream);
+int vdp_comm_destroy(vdp_comm* comm);
 
 size_t vdp_dist_workspace(int D);
 int vdp_dist_blob_bytes(int kind, int stage, int D, size_t* total_bytes, size_t* init_bytes);

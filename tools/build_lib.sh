@@ -23,6 +23,6 @@ for tu in $TUS; do cat "$OBJ/tu_$tu.log"; done
 [ $fail -eq 0 ] || { echo "compile failed"; exit 1; }
 objs=""
 for tu in $ALL; do objs="$objs $OBJ/tu_$tu.o"; done
-nvcc -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT.tmp" $objs
+nvcc -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT.tmp" $objs -ldl
 mv "$OUT.tmp" "$OUT"
 echo "built $OUT"

@@ -135,6 +135,10 @@ SIGNATURES = {
     "vdp_cvi_materialize_sites": (C.c_int, [C.POINTER(CviProblem), vp]),
     "vdp_cvi_site_update_sharded": (C.c_int, [C.POINTER(CviProblem), C.c_int, i64, i64, vp]),
     "vdp_cvi_elbo": (C.c_int, [C.POINTER(CviProblem), vp]),
+    "vdp_cvi_update_data_sites": (C.c_int, [C.POINTER(CviProblem), vp]),
+    "vdp_cvi_full_sites": (C.c_int, [C.POINTER(CviProblem), vp, vp, vp, vp]),
+    "vdp_cvi_update_girsanov_sites_range": (C.c_int, [C.POINTER(CviProblem), i64, i64, vp]),
+    "vdp_cvi_elbo_terms_range": (C.c_int, [C.POINTER(CviProblem), i64, i64, vp]),
     "vdp_drift_num_params": (C.c_int, [C.c_int]),
     "vdp_cvi_grad_kl_prior_params": (C.c_int, [C.POINTER(CviProblem), vp, vp]),
     "vdp_cvi_grad_ve_prior_params": (C.c_int, [C.POINTER(CviProblem), vp, vp, C.c_int, C.c_double, C.c_double, vp,
@@ -159,6 +163,10 @@ SIGNATURES = {
     "vdp_vgp_update_initial_statistics": (C.c_int, [C.POINTER(VgpProblem), vp]),
     "vdp_vgp_elbo": (C.c_int, [C.POINTER(VgpProblem), vp]),
     "vdp_vgp_sweep": (C.c_int, [C.POINTER(VgpProblem), vp]),
+    "vdp_comm_unique_id": (C.c_int, [vp]),
+    "vdp_comm_create": (C.c_int, [C.POINTER(vp), vp, C.c_int, C.c_int]),
+    "vdp_comm_all_gather": (C.c_int, [vp, vp, vp, C.c_size_t, vp]),
+    "vdp_comm_destroy": (C.c_int, [vp]),
     "vdp_dist_workspace": (C.c_size_t, [C.c_int]),
     "vdp_dist_blob_bytes": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "vdp_dist_sweep_summary": (C.c_int, [C.POINTER(DistSweep), vp, vp, vp]),

@@ -305,4 +305,5 @@ extern "C" int vdp_euler_maruyama(int drift_id, const double* params_host, const
 #include "vdp_dist.inl"
 #include "vdp_noalloc.inl"
 #include "vdp_ssm_density.inl"
+#include "vdp_comm.inl"
 #endif

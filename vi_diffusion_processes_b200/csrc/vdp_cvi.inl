@@ -330,6 +330,82 @@ int vdp_cvi_materialize_sites(const vdp_cvi_problem* p, void* stream) {
     return VDP_OK;
 }
 
+// ---- the steps of a site update one at a time, without the posterior rebuild between them: what a caller that
+// rebuilds the posterior itself (time-sharded chains, vdp_dist_sweep_*) strings together
+int vdp_cvi_update_data_sites(const vdp_cvi_problem* p, void* stream) {
+    int rc = check_problem(p);
+    if (rc) return rc;
+    if (p->B == 0 || p->n_obs == 0) return VDP_OK;
+    VDP_DISPATCH_D(p->D, (k_data_site_update<kD><<<grid_for(p->B * p->n_obs, kPtBlock), kPtBlock, 0, as_stream(stream)>>>(
+                             p->fx_mus, p->obs_idx, p->obs_y, host_mat<kD>(p->lik_chol), p->lr_data, p->d1, p->d2, p->B,
+                             p->N, p->n_obs)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+int vdp_cvi_full_sites(const vdp_cvi_problem* p, double* th1, double* thd, double* ths, void* stream) {
+    int rc = check_problem(p);
+    if (rc) return rc;
+    VDP_REQUIRE(th1 && thd && ths, "th1, thd, ths");
+    if (p->B == 0) return VDP_OK;
+    cudaStream_t st = as_stream(stream);
+    VDP_DISPATCH_D(p->D, {
+        k_ssm_to_naturals<kD><<<grid_for(p->B * (p->N + 1), kPtBlock), kPtBlock, 0, st>>>(
+            p->pA, p->pb, p->pcholQ, p->pmu0, p->pcholP0, p->g1, p->gd, p->gs, th1, thd, ths, p->B, p->N);
+        if (p->n_obs > 0)
+            k_scatter_data<kD><<<grid_for(p->B * p->n_obs, kPtBlock), kPtBlock, 0, st>>>(p->d1, p->d2, p->obs_idx, th1,
+                                                                                     thd, p->B, p->N, p->n_obs);
+    });
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
+int vdp_cvi_update_girsanov_sites_range(const vdp_cvi_problem* p, int64_t node_begin, int64_t node_end, void* stream) {
+    int rc = check_problem(p);
+    if (rc) return rc;
+    VDP_REQUIRE(node_begin >= 0 && node_end >= node_begin && node_end <= p->B * (p->N + 1), "node range");
+    if (p->B == 0 || node_end == node_begin) return VDP_OK;
+    CviWs w;
+    if (!cvi_ws_take(p->workspace, p->workspace_bytes, p->B, p->N, p->D, w)) {
+        set_error("workspace too small: need %zu bytes", cvi_ws_bytes(p->B, p->N, p->D));
+        return VDP_E_WORKSPACE;
+    }
+    const DriftParams P = make_params(p->drift_params);
+    cudaStream_t st = as_stream(stream);
+    const size_t n = (size_t)p->B * (p->N + 1);
+    VDP_DISPATCH_D(p->D, VDP_DISPATCH_DRIFT(p->drift_id, {
+        VDP_CHECK_CUDA(cudaMemsetAsync(w.sc1, 0, n * kD * sizeof(double), st));
+        VDP_CHECK_CUDA(cudaMemsetAsync(w.scd, 0, n * kD * kD * sizeof(double), st));
+        if (p->n_obs > 0) {
+            k_scatter_data<kD><<<grid_for(p->B * p->n_obs, kPtBlock), kPtBlock, 0, st>>>(p->d1, p->d2, p->obs_idx, w.sc1,
+                                                                                     w.scd, p->B, p->N, p->n_obs);
+            VDP_CHECK_LAUNCH();
+        }
+        rc = launch_kl_grad<kDrift, kD>(P, p->q, p->dt, p->time_grid, p->x0_mu, p->x0_cov, p->qA, p->fx_mus, p->fx_covs,
+                                        nullptr, p->g1, p->gd, p->gs, 1, p->lr_girsanov, w.sc1, w.scd, p->B, p->N,
+                                        p->status, st, node_begin, node_end);
+        if (rc) return rc;
+    }));
+    return VDP_OK;
+}
+
+int vdp_cvi_elbo_terms_range(const vdp_cvi_problem* p, int64_t node_begin, int64_t node_end, void* stream) {
+    int rc = check_problem(p);
+    if (rc) return rc;
+    VDP_REQUIRE(node_begin >= 0 && node_end >= node_begin && node_end <= p->B * (p->N + 1), "node range");
+    if (p->B == 0) return VDP_OK;
+    CviWs w;
+    if (!cvi_ws_take(p->workspace, p->workspace_bytes, p->B, p->N, p->D, w)) {
+        set_error("workspace too small: need %zu bytes", cvi_ws_bytes(p->B, p->N, p->D));
+        return VDP_E_WORKSPACE;
+    }
+    const DriftParams P = make_params(p->drift_params);
+    VDP_DISPATCH_D(p->D, VDP_DISPATCH_DRIFT(p->drift_id, {
+        if ((rc = run_elbo<kDrift, kD>(*p, w, P, as_stream(stream), node_begin, node_end))) return rc;
+    }));
+    return VDP_OK;
+}
+
 int vdp_cvi_site_update_sharded(const vdp_cvi_problem* p, int phase, int64_t node_begin, int64_t node_end,
                                 void* stream) {
     int rc = check_problem(p);

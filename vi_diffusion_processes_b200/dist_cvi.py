@@ -1,0 +1,178 @@
+"""
+CVI-DP site update of ONE long sequence with the chain sharded in TIME over ranks (BASELINE config 5: 10^7 grid steps,
+D = 3, "parallel-in-time scan sharded over 2/4/8 GPUs ... with a small NCCL-over-NVLink exchange of scan carries").
+
+No rank holds the whole chain.  Rank r owns the grid points [n0, n1) and the transitions [s, e) of
+``time_partition`` and keeps, for every array of the model, its own stretch extended by ONE halo grid point at either
+end (the "extended local chain"); on it the pointwise stages of the update run through the same C entry points a single
+GPU uses, restricted to the owned node range:
+
+    update_data_sites     vdp_cvi_update_data_sites             variational_cvi_sde.py:301-314   (own observations)
+    full_sites            vdp_cvi_full_sites                    :161-174
+    dist_q + marginals    TimeShardedChain (vdp_dist_sweep_*)   :176-192, gauss_markov.py:107-117   <- scan carries
+    update_girsanov_sites vdp_cvi_update_girsanov_sites_range   :279-296  (H = 20 quadrature, own grid points)
+    classic_elbo          vdp_cvi_elbo_terms_range              :339-352  (partial sums, added in rank order)
+
+What crosses ranks per update: the scan elements / initial states of the sweeps (two rebuilds x 5 all-gathers of a
+few hundred bytes), one halo blob per rebuild (marginal mean + covariance of a rank's first and last grid point and
+its last transition matrix: (2 D + 3 D^2) doubles) and 2 doubles of ELBO terms.  All of it goes through
+``Comm.all_gather`` -- ``vdp_comm_all_gather`` (NCCL issued from C on the compute stream) in a multi-process run,
+plain lists when the ranks are emulated in one process (tests).  The linearised prior needs no exchange: transition
+k is linearised around grid point k + 1 alone (variational_cvi_sde.py:412), which the extended chain holds.
+
+The state after an update equals the single-GPU state up to the rounding of the scan carries (1e-12 relative,
+tests/test_gpu_dist_cvi.py); the ELBO terms are added in rank order, so a run is reproducible bit for bit.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check
+from .cvi import CviEngine
+from .dist_time import Comm, TimeShardedChain, time_partition
+
+F64 = torch.float64
+
+
+class _RankState:
+    def __init__(self, rank, nranks, N, n0, n1, s, e):
+        self.rank, self.nranks = rank, nranks
+        self.first, self.last = rank == 0, rank == nranks - 1
+        self.n0, self.n1, self.s, self.e = n0, n1, s, e
+        self.x0, self.x1 = max(n0 - 1, 0), min(n1 + 1, N + 1)        # extended chain: grid points [x0, x1)
+        self.lo = n0 - self.x0                                        # owned range in extended-local indices
+        self.hi = self.lo + (n1 - n0)
+        self.nt = e - s                                               # owned transitions, local index lo .. lo + nt
+        self.eng: CviEngine = None
+
+
+class TimeShardedCvi:
+    """
+    ``drift_id, drift_params, q, lik_chol, x0_mu, x0_cov`` as :class:`CviEngine`; ``time_grid`` [N+1],
+    ``obs_idx`` [n_obs] (grid indices, sorted or not) and ``obs_y`` [n_obs, D] describe the WHOLE sequence: every rank
+    slices its own part (synthetic inputs are cheap to regenerate per rank; a loader would read the rank's stretch).
+    """
+
+    def __init__(self, drift_id, drift_params, q, time_grid, obs_idx, obs_y, lik_chol, x0_mu, x0_cov, comm: Comm,
+                 device="cuda", stabilize_ssm=True, clip_state_transitions=(-1.0, 1.0)):
+        tg = np.asarray(time_grid, dtype=np.float64)
+        self.N = N = tg.shape[0] - 1
+        self.D = D = np.atleast_2d(np.asarray(q)).shape[0]
+        self.comm = comm
+        self.device = torch.device(device)
+        self.chain = TimeShardedChain(N, D, comm, device=device)
+        obs_idx = np.asarray(obs_idx, dtype=np.int64).reshape(-1)
+        obs_y = np.asarray(obs_y, dtype=np.float64).reshape(obs_idx.shape[0], D)
+        self.ranks: List[_RankState] = []
+        for r in comm.local_ranks:
+            s, e = self.chain.parts[r]
+            n0, n1 = self.chain.owned_nodes(r)
+            st = _RankState(r, comm.nranks, N, n0, n1, s, e)
+            mine = (obs_idx >= n0) & (obs_idx < n1)
+            st.eng = CviEngine(drift_id, drift_params, q, tg[st.x0:st.x1], (obs_idx[mine] - st.x0)[None],
+                               obs_y[mine][None], lik_chol, x0_mu, x0_cov, device=device, stabilize_ssm=stabilize_ssm,
+                               clip_state_transitions=clip_state_transitions, carry_naturals=False)
+            n_ext = st.x1 - st.x0
+            z = lambda *shape: torch.zeros(shape, dtype=F64, device=self.device)
+            st.th1, st.thd, st.ths = z(1, n_ext, D), z(1, n_ext, D, D), z(1, n_ext - 1, D, D)
+            self.ranks.append(st)
+        self.elbo = None
+
+    # ---- C calls on one rank's extended chain
+    @staticmethod
+    def _call(st: _RankState, name, lr_data=0.0, lr_girsanov=0.0, *args):
+        p = st.eng._problem(lr_data, lr_girsanov)
+        st.eng._run(name, C.byref(p), *args)
+
+    def _own(self, st: _RankState):
+        """views of the owned part of theta on the extended chain"""
+        return (st.th1[0, st.lo:st.hi], st.thd[0, st.lo:st.hi], st.ths[0, st.lo:st.lo + st.nt])
+
+    def _rebuild(self):
+        """dist_q + marginals on the time-sharded chain, results into the engines' extended arrays + halos."""
+        D = self.D
+        for st in self.ranks:
+            self._call(st, "vdp_cvi_full_sites", 0.0, 0.0, C.c_void_p(st.th1.data_ptr()), C.c_void_p(st.thd.data_ptr()),
+                       C.c_void_p(st.ths.data_ptr()))
+        own = [self._own(st) for st in self.ranks]
+        ssm = self.chain.naturals_to_ssm([o[0] for o in own], [o[1] for o in own], [o[2] for o in own])
+        marg = self.chain.ssm_marginals([o["A"] for o in ssm], [o["b"] for o in ssm], [o["cholQ"] for o in ssm],
+                                        [o["mu0"] for o in ssm], [o["cholP0"] for o in ssm])
+        blobs = []
+        for st, o, (m, S) in zip(self.ranks, ssm, marg):
+            e = st.eng
+            e.qA[0, st.lo:st.lo + st.nt] = o["A"]
+            e.qb[0, st.lo:st.lo + st.nt] = o["b"]
+            e.qcholQ[0, st.lo:st.lo + st.nt] = o["cholQ"]
+            if st.first:
+                e.qmu0[0] = o["mu0"]
+                e.qcholP0[0] = o["cholP0"]
+            e.fx_mus[0, st.lo:st.hi] = m
+            e.fx_covs[0, st.lo:st.hi] = S
+            blobs.append(torch.cat([m[0], S[0].reshape(-1), m[-1], S[-1].reshape(-1), o["A"][-1].reshape(-1)]))
+        allb = self.comm.all_gather(blobs)
+        DD = D * D
+        for st in self.ranks:
+            e = st.eng
+            if not st.first:      # front halo: last grid point and last transition of the rank before
+                bl = allb[st.rank - 1]
+                e.fx_mus[0, 0] = bl[D + DD:2 * D + DD]
+                e.fx_covs[0, 0] = bl[2 * D + DD:2 * D + 2 * DD].reshape(D, D)
+                e.qA[0, 0] = bl[2 * D + 2 * DD:].reshape(D, D)
+            if not st.last:       # back halo: first grid point of the rank after
+                bl = allb[st.rank + 1]
+                e.fx_mus[0, -1] = bl[:D]
+                e.fx_covs[0, -1] = bl[D:D + DD].reshape(D, D)
+
+    def site_update(self, lr_data, lr_girsanov):
+        """cvi_dp_trainer.py:71-77 once; returns the ELBO (float), the same on every rank."""
+        for st in self.ranks:
+            self._call(st, "vdp_cvi_update_data_sites", lr_data, lr_girsanov)
+        self._rebuild()
+        for st in self.ranks:
+            self._call(st, "vdp_cvi_update_girsanov_sites_range", lr_data, lr_girsanov, st.lo, st.hi)
+        self._rebuild()
+        return self.classic_elbo(rebuilt=True)
+
+    def classic_elbo(self, rebuilt=False):
+        if not rebuilt:
+            self._rebuild()
+        parts = []
+        for st in self.ranks:
+            self._call(st, "vdp_cvi_elbo_terms_range", 0.0, 0.0, st.lo, st.hi)
+            parts.append(torch.cat([st.eng.ve, st.eng.kl]))
+        allp = self.comm.all_gather(parts)
+        tot = allp[0].clone()
+        for t in allp[1:]:                 # fixed rank order: reproducible bit for bit
+            tot = tot + t.to(tot.device)
+        self.ve, self.kl = tot[0], tot[1]
+        self.elbo = tot[0] - tot[1]
+        return float(self.elbo.item())
+
+    def relinearize(self):
+        """cvi_dp_trainer.py:110-134 on every rank's extended chain (pointwise: no exchange, the halos are there)."""
+        for st in self.ranks:
+            st.eng.relinearize()
+
+    def check_status(self):
+        self.chain.check_status()
+        for st in self.ranks:
+            st.eng.check_status()
+
+    # ---- owned slices, for gathering / comparing
+    def owned(self, name):
+        """list over local ranks of the owned stretch of ``name`` (g1, gd, fx_mus, fx_covs: grid points;
+        gs, qA, qb, qcholQ: transitions)"""
+        out = []
+        for st in self.ranks:
+            t = getattr(st.eng, name)[0]
+            if name in ("gs", "qA", "qb", "qcholQ", "pA", "pb", "pcholQ"):
+                out.append(t[st.lo:st.lo + st.nt])
+            else:
+                out.append(t[st.lo:st.hi])
+        return out
