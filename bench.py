@@ -37,6 +37,10 @@ X0_MU, X0_COV = 1.0, 1e-2
 DW_PARAMS = [4.0, 1.0]
 LR = 0.5
 ALGO_BYTES_PER_STEP_D1 = 80  # 8 * (4D + 6D^2) for D = 1
+# float64 operations per grid step of one D = 3 site update: the KL-gradient quadrature
+# (8000 nodes x ~109 flops: affine map, drift + Jacobian, residual, quadratic form, adjoint accumulators in the nested
+# form of kl_kernels.cuh) + the KL value quadrature of classic_elbo (8000 x ~44) + ~6 kflop of block algebra
+C5_FLOPS_PER_STEP = 8000 * 109 + 8000 * 44 + 6000
 
 
 def make_problem(B, N, seed):
@@ -323,6 +327,15 @@ def run_ours(args):
     ms_e2e_rp = timed(step_e2e, e2e_steps, 1)
     host_eng.close()
 
+    # second workload of BASELINE.json (config 5): ONE sequence of 10^7 grid steps, D = 3, the chain sharded in TIME
+    # over the ranks with the scan carries / halos exchanged over NCCL (strong scaling).  Reported under "c5" of the
+    # same line so that the scaling run records a workload with a collective on its data path.
+    c5 = None
+    if not args.no_c5:
+        del host_eng
+        torch.cuda.empty_cache()
+        c5 = run_c5_leg(args)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -379,6 +392,7 @@ def run_ours(args):
                             "frac": value * ALGO_BYTES_PER_STEP_D1 / world / 1e9 / peak},
         "phases": phases,
         "parity_check": parity,
+        "c5": c5,
         "cpu_baseline": {"value": cpu_val, "unit": "grid-steps/s", "cores": cpu_cores, "kind": "port",
                          "sample": f"C/OpenMP restatement of the oracle (oracle/cvi_d1.c, gcc -O2), {cpu_cores} "
                                    f"threads x 64 sequences x {N} grid steps x 10 site updates, {cpu_s:.1f} s",
@@ -392,6 +406,48 @@ def run_ours(args):
         dist.destroy_process_group()
     if parity is not None and not parity["ok"]:
         raise SystemExit("bench.py: parity check against the CPU oracle failed: %s" % json.dumps(parity))
+
+
+def run_c5_leg(args):
+    """BASELINE config 5 through tools/c5_time_sharded.run (time-sharded chain, dist_cvi.TimeShardedCvi)."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import c5_time_sharded
+    res = c5_time_sharded.run(N=args.c5_grid, n_obs=args.c5_obs, steps=args.c5_steps, warmup=1)
+    if res is not None:
+        peak_fp64 = 37.0e12   # B200 FP64 vector peak (vendor figure; SURVEY 8d) -- the quadrature is FP64-bound
+        flops = C5_FLOPS_PER_STEP * res["value"]
+        res["roofline"] = {"bound": "fp64", "achieved": flops / 1e12 / res["n_gpus"], "peak": peak_fp64 / 1e12,
+                           "unit": "TFLOP/s", "frac": flops / res["n_gpus"] / peak_fp64,
+                           "flops_per_grid_step": C5_FLOPS_PER_STEP,
+                           "peak_source": "vendor FP64 vector figure (no measured FP64 peak in MEASURED_PEAKS.json)"}
+    return res
+
+
+def run_c5(args):
+    """`--workload c5`: the C5 leg alone, as a bench line of its own."""
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    sampler = ClockSampler(local_rank)
+    if int(os.environ.get("RANK", "0")) == 0:
+        sampler.start()
+    res = run_c5_leg(args)
+    if res is not None:
+        line = {"metric": "grid-steps/sec per CVI-DP site update", "value": res["value"], "unit": "grid-steps/s",
+                "n_gpus": world, "steps": res["steps"], "warmup": res["warmup"], "ms_per_step": res["ms_per_step"],
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "config": {"workload": res["workload"], "grid_steps": args.c5_grid,
+                                                "state_dim": 3, "n_obs": args.c5_obs, "quad_H": 20,
+                                                "parallelism": f"time-sharded x{world}: {res['collective']}"},
+                "clocks": sampler.stop(), "roofline": res["roofline"], "c5": res}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def run_vdp(args):
@@ -463,8 +519,13 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cvi", choices=["cvi", "vdp"],
-                    help="cvi = the BASELINE.json metric (default); vdp = the VDP sweep on the same shape (1 GPU)")
+    ap.add_argument("--workload", default="cvi", choices=["cvi", "vdp", "c5"],
+                    help="cvi = the BASELINE.json metric on config 4 with config 5 under the key c5 (default); vdp = the "
+                         "VDP sweep on the config-4 shape (1 GPU); c5 = config 5 alone (time-sharded over the ranks)")
+    ap.add_argument("--c5-grid", type=int, default=10_000_000, help="grid steps of the config-5 sequence")
+    ap.add_argument("--c5-obs", type=int, default=10_000)
+    ap.add_argument("--c5-steps", type=int, default=2)
+    ap.add_argument("--no-c5", action="store_true", help="skip the config-5 leg of the default run")
     ap.add_argument("--seqs", type=int, default=4096, help="sequences per GPU")
     ap.add_argument("--grid", type=int, default=10000, help="grid steps per sequence")
     ap.add_argument("--quick", action="store_true", help="tuning runs: resident timing and phases only")
@@ -476,6 +537,8 @@ def main():
         run_reference(args)
     elif args.workload == "vdp":
         run_vdp(args)
+    elif args.workload == "c5":
+        run_c5(args)
     else:
         run_ours(args)
 

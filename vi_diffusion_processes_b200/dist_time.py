@@ -39,27 +39,60 @@ def time_partition(N: int, nranks: int):
 
 
 class Comm:
-    """All-gather of one small tensor per rank.  ``ranks`` = the ranks driven by this process."""
+    """
+    All-gather of one small tensor per rank.  ``local_ranks`` = the ranks driven by this process.
 
-    def __init__(self, nranks: int, local_ranks: List[int], group=None):
+    Transports: a plain list when all ranks live in this process (``emulated``: tests); ``torch.distributed`` (gloo
+    in the CPU tests of the plumbing); or -- the GPU data path -- ``vdp_comm_all_gather``: NCCL issued from C on the
+    compute stream (``from_process_group(backend="nccl_c")``; torch.distributed then only carries the 128-byte NCCL
+    id to the ranks once).
+    """
+
+    def __init__(self, nranks: int, local_ranks: List[int], group=None, c_comm=None):
         self.nranks, self.local_ranks, self.group = nranks, list(local_ranks), group
         self.distributed = len(self.local_ranks) != nranks
+        self._c_comm = c_comm
+        self.n_gathers = 0            # exchanges issued (reported by the bench)
 
     @classmethod
     def emulated(cls, nranks):
         return cls(nranks, list(range(nranks)))
 
     @classmethod
-    def from_process_group(cls, group=None):
+    def from_process_group(cls, group=None, backend="torch"):
         import torch.distributed as dist
-        return cls(dist.get_world_size(group), [dist.get_rank(group)], group)
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        if backend == "torch" or world == 1:
+            return cls(world, [rank], group)
+        assert backend == "nccl_c", backend
+        lib = _lib.load()
+        ident = (C.c_char * 128)()
+        if rank == 0:
+            check(lib.vdp_comm_unique_id(ident), "vdp_comm_unique_id")
+        box = [bytes(ident)]
+        dist.broadcast_object_list(box, src=0, group=group)
+        handle = C.c_void_p()
+        check(lib.vdp_comm_create(C.byref(handle), box[0], rank, world), "vdp_comm_create")   # current CUDA device
+        return cls(world, [rank], group, c_comm=handle)
+
+    def close(self):
+        if self._c_comm is not None:
+            _lib.load().vdp_comm_destroy(self._c_comm)
+            self._c_comm = None
 
     def all_gather(self, per_local: List[torch.Tensor]) -> List[torch.Tensor]:
         """per_local[i] = the tensor of local rank i -> list over ALL ranks (same for every local rank)."""
+        self.n_gathers += 1
         if not self.distributed:
             return list(per_local)
-        import torch.distributed as dist
         t = per_local[0].contiguous()
+        if self._c_comm is not None:
+            out = torch.empty((self.nranks,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+            stream = C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+            check(_lib.load().vdp_comm_all_gather(self._c_comm, C.c_void_p(t.data_ptr()), C.c_void_p(out.data_ptr()),
+                                                  t.numel() * t.element_size(), stream), "vdp_comm_all_gather")
+            return list(out.unbind(0))
+        import torch.distributed as dist
         out = [torch.empty_like(t) for _ in range(self.nranks)]
         dist.all_gather(out, t, group=self.group)
         return out
