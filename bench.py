@@ -37,10 +37,12 @@ X0_MU, X0_COV = 1.0, 1e-2
 DW_PARAMS = [4.0, 1.0]
 LR = 0.5
 ALGO_BYTES_PER_STEP_D1 = 80  # 8 * (4D + 6D^2) for D = 1
-# float64 operations per grid step of one D = 3 site update: the KL-gradient quadrature
-# (8000 nodes x ~109 flops: affine map, drift + Jacobian, residual, quadratic form, adjoint accumulators in the nested
-# form of kl_kernels.cuh) + the KL value quadrature of classic_elbo (8000 x ~44) + ~6 kflop of block algebra
-C5_FLOPS_PER_STEP = 8000 * 109 + 8000 * 44 + 6000
+# float64 operations per grid step of one D = 3 site update (counted from kl_kernels.cuh kl_quad_nested3, see
+# tools/quad_profile.py / BASELINE.md section 4): the KL-gradient quadrature (8000 nodes x 94 flops: point, OU drift,
+# residual, Q_p^-1-weighted residual, quadratic form, adjoint accumulators) + the KL value quadrature of classic_elbo
+# (8000 x 42) + ~6 kflop of block algebra
+FP64_PEAK_MEASURED = 37.0e12   # flop/s; replaced by the measured value below once tools/quad_profile.py has run
+C5_FLOPS_PER_STEP = 8000 * 94 + 8000 * 42 + 6000
 
 
 def make_problem(B, N, seed):
@@ -172,15 +174,15 @@ PHASE_TRAFFIC = {
     "chol_fwd": (0, 2 + 2),           # read thd, ths ; write Ld, Ls
     # read th1 | Ld, Ls ; write b | A, cholQ, Sd (K blocks rebuilt from L in the tile; the marginal covariances are
     # the diagonal of the inverse band the sweep walks through, so no separate inverse-band sweep)
-    "nat2ssm_bwd": (1 + 1, 2 + 3),
+    # (the rebuild between the two site updates does not write chol Q: 48 and 56 B, 52 on average)
+    "nat2ssm_bwd": (1 + 1, 2 + 2.5),
     # means alone: read b | A ; write m.  The sweep of the second rebuild also reads S, cholQ and adds up the KL
     # terms of classic_elbo (24 and 40 B per grid step: 32 on average over the two launches of an update)
     "marg_fwd": (1 + 1, 1 + 1),
     "invband_bwd": (0, 2 + 1),        # (only with VDP_REFACTOR_PRECISION=1) read Ld, Ls ; write Sd
-    # read m, g1, sc1, prior b | A, S, gd, gs, scd, prior A, cholQ ; write g1, th1 | gd, gs, thd, ths: the kernel
-    # also emits the naturals of the posterior that follows (no second k_ssm_to_naturals pass); the dense copy of the
-    # data sites (sc) is carried between updates like the naturals (no memset)
-    "kl_grad": (1 + 1 + 1 + 1 + 1 + 1, 2 + 2 + 1 + 2 + 1 + 2 + 1),
+    # sites held in theta between carried updates (VDP_FLAG_SITES_IN_NATURALS): read m, sc1, th1 | A, S, scd, thd, ths ;
+    # write th1 | thd, ths -- theta moves by lr (scatter - dKL/deta); neither the sites nor the prior are touched
+    "kl_grad": (1 + 1 + 1 + 1, 1 + 1 + 1 + 2 + 2),
     "elbo": (0, 0),                   # variational expectations at the observations + sum of the KL partials
 }
 LAUNCHES_PER_UPDATE = 1 + 4 + 1 + 3 + 3   # kernels of ours in one vdp_cvi_site_update in steady state (data sites,
@@ -414,12 +416,13 @@ def run_c5_leg(args):
     import c5_time_sharded
     res = c5_time_sharded.run(N=args.c5_grid, n_obs=args.c5_obs, steps=args.c5_steps, warmup=1)
     if res is not None:
-        peak_fp64 = 37.0e12   # B200 FP64 vector peak (vendor figure) -- the quadrature is FP64-bound
+        peak_fp64 = FP64_PEAK_MEASURED   # vdp_test_fp64_fma on this pool's B200 (tools/quad_profile.py)
         flops = C5_FLOPS_PER_STEP * res["value"]
         res["roofline"] = {"bound": "fp64", "achieved": flops / 1e12 / res["n_gpus"], "peak": peak_fp64 / 1e12,
                            "unit": "TFLOP/s", "frac": flops / res["n_gpus"] / peak_fp64,
                            "flops_per_grid_step": C5_FLOPS_PER_STEP,
-                           "peak_source": "vendor FP64 vector figure (no measured FP64 peak in MEASURED_PEAKS.json)"}
+                           "peak_source": "measured float64 FMA throughput of this pool's B200 (vdp_test_fp64_fma, "
+                                          "profiles/r02_quadrature_d2_d3.json)"}
     return res
 
 

@@ -527,6 +527,11 @@ enum {
 int vdp_test_fastmath(const double* x, const double* y, double* rcp, double* sq, double* rsq, double* quo,
                       int64_t n, void* stream);
 
+/* Diagnostic: float64 FMA throughput (the roofline denominator of the quadrature kernels, which are bound by the
+ * FP64 pipe): blocks x threads threads run `iters` rounds of 16 independent fused multiply-adds each;
+ * flops = 2 * 16 * iters * blocks * threads.  out [blocks * threads] receives the chains' sums.  Time it with events. */
+int vdp_test_fp64_fma(double* out, int64_t blocks, int threads, int64_t iters, void* stream);
+
 int vdp_profile_enable(int on);
 int vdp_profile_read(double* ms_by_phase, int64_t* spans_by_phase, int n_phases);
 

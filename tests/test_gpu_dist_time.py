@@ -1,7 +1,7 @@
 """
 Time-segment sharding (BASELINE config 5 path): the posterior rebuild of one long sequence split over R ranks
 must match the oracle's sequential result.  Ranks are emulated in one process on one GPU (same kernels, same
-blobs, all-gather replaced by a list) -- the real multi-process run is tests/dist_time_worker.py under torchrun.
+blobs, all-gather replaced by a list) -- the real multi-process runs are tools/dist_time_run.py and tools/c5_time_sharded.py under torchrun.
 """
 import numpy as np
 import pytest
@@ -87,3 +87,37 @@ def test_time_partition_covers_the_grid():
         assert max(e - s for s, e in parts) - min(e - s for s, e in parts) <= 1
     with pytest.raises(ValueError):
         time_partition(3, 5)
+
+
+def test_time_sharded_rebuild_long_chain_8_ranks_equals_single_rank():
+    """N = 10^6 transitions, D = 3, 8 emulated ranks against the single-rank CUDA result (the NumPy oracle walks the
+    chain block by block in Python and is too slow at this length; the single-rank kernels are pinned to it above)."""
+    from vi_diffusion_processes_b200.dist_time import Comm, TimeShardedChain
+    N, D, R = 1_000_000, 3, 8
+    rng = np.random.default_rng(7)
+    ssm = rand_ssm(rng, N, D)
+    th1, thd, ths = G.ssm_to_naturals(ssm)
+    res = {}
+    for nr in (1, R):
+        chain = TimeShardedChain(N, D, Comm.emulated(nr))
+        l1, ld, ls = [], [], []
+        for r in range(nr):
+            s, e = chain.parts[r]
+            n0, n1 = chain.owned_nodes(r)
+            l1.append(dev(th1[n0:n1]))
+            ld.append(dev(thd[n0:n1]))
+            ls.append(dev(ths[s:e]))
+        out = chain.naturals_to_ssm(l1, ld, ls)
+        marg = chain.ssm_marginals([o["A"] for o in out], [o["b"] for o in out], [o["cholQ"] for o in out],
+                                   [o["mu0"] for o in out], [o["cholP0"] for o in out])
+        chain.check_status()
+        res[nr] = {k: torch.cat([o[k] for o in out]) for k in ("A", "b", "cholQ")}
+        res[nr]["m"] = torch.cat([m for m, _ in marg])
+        res[nr]["S"] = torch.cat([S for _, S in marg])
+    for k in ("A", "b", "cholQ", "m", "S"):
+        a, b = res[R][k], res[1][k]
+        assert a.shape == b.shape
+        assert float((a - b).abs().max()) <= 1e-11 * float(b.abs().max()), k
+    # and the marginal means satisfy the forward recursion of the model they were built from
+    m = res[R]["m"].cpu().numpy()
+    assert np.abs(m[1:] - (np.einsum("nij,nj->ni", ssm.state_transitions, m[:-1]) + ssm.state_offsets)).max() < 1e-9

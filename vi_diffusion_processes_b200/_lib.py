@@ -172,6 +172,7 @@ SIGNATURES = {
     "vdp_dist_sweep_summary": (C.c_int, [C.POINTER(DistSweep), vp, vp, vp]),
     "vdp_dist_sweep_finish": (C.c_int, [C.POINTER(DistSweep), vp, vp, vp]),
     "vdp_test_fastmath": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, vp]),
+    "vdp_test_fp64_fma": (C.c_int, [vp, i64, C.c_int, i64, vp]),
     "vdp_profile_enable": (C.c_int, [C.c_int]),
     "vdp_profile_read": (C.c_int, [c_dp, c_i64p, C.c_int]),
 }

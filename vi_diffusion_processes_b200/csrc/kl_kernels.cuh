@@ -323,7 +323,15 @@ struct KlHandoff { double gm[D]; double gS[D * D]; };
 #ifndef VDP_KL_MINBLOCKS
 #define VDP_KL_MINBLOCKS 12
 #endif
-template <int G> struct KlBounds { static constexpr int threads = (G == 1) ? 128 : 256, blocks = (G == 1) ? VDP_KL_MINBLOCKS : 1; };
+// warp-per-grid-point kernels (D >= 2): 2 blocks of 256 threads per SM = 128 registers (measured on B200: 255
+// registers / 1 block 14.1 ms (D = 2, 4096 x 500) and 9.44 ms (D = 3, 2 x 10^5); 128 / 2 blocks 10.6 and 8.86 ms; 80 / 3
+// blocks spills: 11.9 and 12.5 ms)
+#ifndef VDP_KLG_MINBLOCKS
+#define VDP_KLG_MINBLOCKS 2
+#endif
+template <int G> struct KlBounds {
+    static constexpr int threads = (G == 1) ? 128 : 256, blocks = (G == 1) ? VDP_KL_MINBLOCKS : VDP_KLG_MINBLOCKS;
+};
 template <int DRIFT, int D, int H, int G, bool CLOSED = false>
 __global__ void __launch_bounds__(KlBounds<G>::threads, KlBounds<G>::blocks) k_kl_grad(DriftParams P, Mat<D> q, double dt, double pi_factor,
                           const double* __restrict__ time_grid, Vec<D> x0_mu, Mat<D> x0_cov,

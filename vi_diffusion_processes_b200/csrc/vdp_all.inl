@@ -172,6 +172,29 @@ int vdp_test_fastmath(const double* x, const double* y, double* rcp, double* sq,
     return VDP_OK;
 }
 
+// diagnostic: float64 FMA throughput of the device (the roofline denominator of the quadrature kernels): every thread
+// runs `iters` rounds of 16 independent DFMA chains; 2 * 16 * iters * threads flops in all
+__global__ void k_test_fp64_fma(double* __restrict__ out, int64_t iters, double a, double b) {
+    double x[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) x[j] = (double)(threadIdx.x + j);
+    for (int64_t i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) x[j] = fma(x[j], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) s += x[j];
+    out[blockIdx.x * (int64_t)blockDim.x + threadIdx.x] = s;
+}
+
+int vdp_test_fp64_fma(double* out, int64_t blocks, int threads, int64_t iters, void* stream) {
+    VDP_REQUIRE(out && blocks > 0 && threads > 0 && threads <= 1024 && iters >= 0, "out, blocks, threads, iters");
+    k_test_fp64_fma<<<(unsigned)blocks, threads, 0, as_stream(stream)>>>(out, iters, 0.999999, 1e-9);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // op level
 // ---------------------------------------------------------------------------------------------------
