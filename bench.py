@@ -41,7 +41,7 @@ ALGO_BYTES_PER_STEP_D1 = 80  # 8 * (4D + 6D^2) for D = 1
 # tools/quad_profile.py / BASELINE.md section 4): the KL-gradient quadrature (8000 nodes x 94 flops: point, OU drift,
 # residual, Q_p^-1-weighted residual, quadratic form, adjoint accumulators) + the KL value quadrature of classic_elbo
 # (8000 x 42) + ~6 kflop of block algebra
-FP64_PEAK_MEASURED = 37.0e12   # flop/s; replaced by the measured value below once tools/quad_profile.py has run
+FP64_PEAK_MEASURED = 33.67e12   # flop/s: vdp_test_fp64_fma on this pool's B200 (profiles/r02_quadrature_d2_d3.json)
 C5_FLOPS_PER_STEP = 8000 * 94 + 8000 * 42 + 6000
 
 
@@ -179,7 +179,7 @@ PHASE_TRAFFIC = {
     # means alone: read b | A ; write m.  The sweep of the second rebuild also reads S, cholQ and adds up the KL
     # terms of classic_elbo (24 and 40 B per grid step: 32 on average over the two launches of an update)
     "marg_fwd": (1 + 1, 1 + 1),
-    "invband_bwd": (0, 2 + 1),        # (only with VDP_REFACTOR_PRECISION=1) read Ld, Ls ; write Sd
+    "invband_bwd": (0, 2 + 1),        # (only with VDP_FLAG_REFACTOR_PRECISION) read Ld, Ls ; write Sd
     # sites held in theta between carried updates (VDP_FLAG_SITES_IN_NATURALS): read m, sc1, th1 | A, S, scd, thd, ths ;
     # write th1 | thd, ths -- theta moves by lr (scatter - dKL/deta); neither the sites nor the prior are touched
     "kl_grad": (1 + 1 + 1 + 1, 1 + 1 + 1 + 2 + 2),
@@ -302,11 +302,11 @@ def run_ours(args):
     lib.vdp_profile_enable(0)
     # the same update with the 20-point Gauss-Hermite loops instead of their closed form (polynomial drift), and with
     # the naturals recomputed over the whole grid every update: reported beside the headline, not part of it
-    os.environ["VDP_GH_QUADRATURE"] = "1"
+    eng.route_flags = _lib.FLAG_GH_QUADRATURE          # per-call route flag of vdp_cvi_problem (no environment)
     ms_gh = timed(step_resident, args.steps, 1)
-    os.environ["VDP_NO_CARRIED_NATURALS"] = "1"
+    eng.carry_naturals = False
     ms_gh_full = timed(step_resident, args.steps, 1)
-    del os.environ["VDP_GH_QUADRATURE"], os.environ["VDP_NO_CARRIED_NATURALS"]
+    eng.route_flags, eng.carry_naturals = 0, True
     # nvidia-smi samples every 100 ms: keep the same load running (untimed) until at least ~0.6 s have been sampled
     while time.perf_counter() - t_load < 0.6:
         step_resident()

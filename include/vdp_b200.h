@@ -50,6 +50,13 @@ enum {
 };
 
 int vdp_version(void);
+/* Process-wide tuning switches: "SWEEPS" (0 heuristic, 1 thread per sequence, 2 parallel-in-time tiles), "NSEG" (time
+ * segments per sequence of the tiled sweeps, 0 = heuristic), and the route switches "GH_QUADRATURE",
+ * "REFACTOR_PRECISION", "NO_CARRIED_NATURALS", "NO_FUSED_NATURALS", "SEPARATE_KL_VALUE" (0 / 1; the per-call
+ * VDP_FLAG_* of the same name are the re-entrant way to choose a route).  Their defaults are read from the
+ * environment variables VDP_<KEY> once, when the library is loaded; no entry point reads the environment. */
+int vdp_config_set(const char* key, int value);
+int vdp_config_get(const char* key, int* value);
 const char* vdp_last_error(void);
 /* copies status[2] to the host after synchronising `stream`; returns status[0] */
 int64_t vdp_read_status(const int64_t* status, int64_t* out_host2, void* stream);
@@ -273,6 +280,14 @@ typedef struct vdp_cvi_problem {
                                          onto a new linearised prior (tranform_girsanov_sites, sde_utils.py:550-568:
                                          g + nat(p_old) - nat(p_new)) leaves theta unchanged. */
 
+/* Route switches (same results up to rounding; each held to the default route by a test): */
+#define VDP_FLAG_GH_QUADRATURE 64       /* polynomial scalar drifts: run the 20-node Gauss-Hermite loops of the reference
+                                           instead of their closed form (Gaussian moments) */
+#define VDP_FLAG_REFACTOR_PRECISION 128 /* marginals through a second factorisation of the rebuilt precision, as the
+                                           reference does (four sweeps per rebuild instead of three) */
+#define VDP_FLAG_NO_FUSED_NATURALS 256  /* rebuild the naturals from the sites after the girsanov update */
+#define VDP_FLAG_SEPARATE_KL_VALUE 512  /* KL terms of classic_elbo in their own pass, not inside the mean sweep */
+
 size_t vdp_cvi_workspace(int64_t B, int64_t N, int D, int64_t n_obs);
 int vdp_cvi_site_update(const vdp_cvi_problem* problem_host, void* stream);
 /* g1, gd, gs <- theta - nat(p) - scatter(data sites) from the natural parameters and the dense data-site copy the
@@ -418,6 +433,7 @@ typedef struct vdp_vgp_problem {
 
 #define VDP_VGP_STABILIZE 1    /* stabilize_system=True (clips of vi_sde.py:184-197, 314-323, 393-397) */
 #define VDP_VGP_UPDATE_X0 2    /* vdp_vgp_sweep also runs update_initial_statistics */
+#define VDP_VGP_GH_QUADRATURE 4 /* as VDP_FLAG_GH_QUADRATURE */
 
 /* LinearDrift.to_ssm (markovflow/sde/drift.py:64-116): A_ssm = I + A delta_k, b_ssm = b delta_k,
  * cholQ = chol(q delta_k).  A [B,N,D,D], b [B,N,D] -> same shapes. */

@@ -3,6 +3,8 @@ import os
 import sys
 
 import numpy as np
+
+from vi_diffusion_processes_b200 import _lib  # noqa: E402
 import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -29,9 +31,8 @@ try:
 except Exception as e:   # the oracle's constructor signature may differ: the GPU-vs-GPU comparison still prints
     print("oracle not built:", e)
 for it in range(4):
-    os.environ.pop("VDP_GH_QUADRATURE", None)
-    ea = a.site_update(0.5, 0.5).clone()
-    os.environ["VDP_GH_QUADRATURE"] = "1"
+    ea = a.site_update(0.5, 0.5).clone()                     # closed-form moments (default route)
+    c.route_flags = _lib.FLAG_GH_QUADRATURE                  # the 20-node loops
     ec = c.site_update(0.5, 0.5).clone()
     out = {}
     for name in ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs"):

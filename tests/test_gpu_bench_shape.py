@@ -47,13 +47,12 @@ def _record(name, row):
 
 
 @pytest.mark.parametrize("route", ["default", "gh20_loops", "benes"])
-def test_c4_shape_three_updates_with_relinearisation(route, monkeypatch):
+def test_c4_shape_three_updates_with_relinearisation(route, vdp_cfg):
     import bench
     from vi_diffusion_processes_b200.cvi import CviEngine
-    for k in ("VDP_SWEEPS", "VDP_NSEG", "VDP_GH_QUADRATURE"):
-        monkeypatch.delenv(k, raising=False)
+    vdp_cfg(SWEEPS=None, NSEG=None, GH_QUADRATURE=None)
     if route == "gh20_loops":
-        monkeypatch.setenv("VDP_GH_QUADRATURE", "1")
+        vdp_cfg(GH_QUADRATURE="1")
     drift, params = (S.DRIFT_BENES, [1.0]) if route == "benes" else (S.DRIFT_DW, bench.DW_PARAMS)
     grid, idx, y = bench.make_problem(B, N, seed=4096)          # the generator of the bench workload
     assert grid.shape[0] == N + 1 and idx.shape == (B, bench.N_OBS)

@@ -26,11 +26,11 @@ def _close(a, b, tol, scale=None):
 
 
 @pytest.mark.parametrize("R", [1, 2, 3, 5])
-def test_time_sharded_update_d1_equals_single_gpu_and_oracle(R, monkeypatch):
+def test_time_sharded_update_d1_equals_single_gpu_and_oracle(R, vdp_cfg):
     from vi_diffusion_processes_b200.cvi import CviEngine
     from vi_diffusion_processes_b200.dist_cvi import TimeShardedCvi
     from vi_diffusion_processes_b200.dist_time import Comm
-    monkeypatch.setenv("VDP_SWEEPS", "tiled")
+    vdp_cfg(SWEEPS="tiled")
     rng = np.random.default_rng(31)
     N, n_obs = 2300, 21
     grid = np.round(np.arange(N + 1) * 0.005, 6)

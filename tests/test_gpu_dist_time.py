@@ -37,13 +37,13 @@ def rand_ssm(rng, N, D):
 @pytest.mark.parametrize("nseg", [None, "2"])
 @pytest.mark.parametrize("R", [1, 2, 3, 5])
 @pytest.mark.parametrize("D,N", [(1, 6000), (2, 1500), (3, 901)])
-def test_time_sharded_posterior_rebuild(monkeypatch, D, N, R, nseg):
+def test_time_sharded_posterior_rebuild(vdp_cfg, D, N, R, nseg):
     from vi_diffusion_processes_b200.dist_time import Comm, TimeShardedChain
-    monkeypatch.setenv("VDP_SWEEPS", "tiled")
+    vdp_cfg(SWEEPS="tiled")
     if nseg:
-        monkeypatch.setenv("VDP_NSEG", nseg)
+        vdp_cfg(NSEG=nseg)
     else:
-        monkeypatch.delenv("VDP_NSEG", raising=False)
+        vdp_cfg(NSEG=None)
     rng = np.random.default_rng(61 + D + R)
     ssm = rand_ssm(rng, N, D)
     th1, thd, ths = G.ssm_to_naturals(ssm)

@@ -38,15 +38,15 @@ def ops():
 
 
 @pytest.fixture(params=["seq", "tiled", "tiled-seg3"])
-def sweeps(request, monkeypatch):
+def sweeps(request, vdp_cfg):
     """Run the test once per sweep mapping: thread-per-sequence, parallel-in-time tiles with one segment
     per sequence, and tiles with every sequence split in three time segments (carry exchange path)."""
     mode = request.param
-    monkeypatch.setenv("VDP_SWEEPS", "seq" if mode == "seq" else "tiled")
+    vdp_cfg(SWEEPS="seq" if mode == "seq" else "tiled")
     if mode == "tiled-seg3":
-        monkeypatch.setenv("VDP_NSEG", "3")
+        vdp_cfg(NSEG="3")
     else:
-        monkeypatch.delenv("VDP_NSEG", raising=False)
+        vdp_cfg(NSEG=None)
     return mode
 
 
@@ -438,7 +438,7 @@ def test_euler_maruyama_philox_statistics(ops):
     assert torch.equal(sub, a[:100])
 
 
-def test_fused_naturals_equal_separate_pass(monkeypatch):
+def test_fused_naturals_equal_separate_pass(vdp_cfg):
     """The girsanov-update kernel emits the naturals of the posterior that follows; with VDP_NO_FUSED_NATURALS the
     rebuild makes its own pass over the sites (k_ssm_to_naturals + scatter).  Same statements, same state."""
     from oracle.sde_np import DRIFT_DW
@@ -454,7 +454,7 @@ def test_fused_naturals_equal_separate_pass(monkeypatch):
     a, c = mk(), mk()
     for _ in range(3):
         ea = a.site_update(0.5, 0.5).clone()
-    monkeypatch.setenv("VDP_NO_FUSED_NATURALS", "1")
+    vdp_cfg(NO_FUSED_NATURALS="1")
     for _ in range(3):
         ec = c.site_update(0.5, 0.5).clone()
     for name in ("g1", "gd", "gs", "d1", "d2", "fx_mus", "fx_covs"):
@@ -538,7 +538,7 @@ def test_carried_naturals_repeated_observation_points():
 
 
 @pytest.mark.parametrize("drift,params,noise", [("dw", [4.0, 1.0], 0.1), ("dw", [2.5, 0.7], 1e-3), ("ou", [0.8], 0.05)])
-def test_closed_form_moments_equal_gauss_hermite(monkeypatch, drift, params, noise):
+def test_closed_form_moments_equal_gauss_hermite(vdp_cfg, drift, params, noise):
     """For polynomial scalar drifts the 20-point Gauss-Hermite sums of the KL term and of its gradient are taken in
     closed form (central Gaussian moments; the rule is exact for these integrands).  VDP_GH_QUADRATURE=1 runs the
     quadrature loops: same sites, marginals and ELBO to rounding, also with a small observation noise (posterior
@@ -562,7 +562,7 @@ def test_closed_form_moments_equal_gauss_hermite(monkeypatch, drift, params, noi
         if it == 2:
             a.relinearize()
         ea.append(a.site_update(0.5, 0.5).clone())
-    monkeypatch.setenv("VDP_GH_QUADRATURE", "1")
+    vdp_cfg(GH_QUADRATURE="1")
     for it in range(4):
         if it == 2:
             c.relinearize()
@@ -580,7 +580,7 @@ def test_closed_form_moments_equal_gauss_hermite(monkeypatch, drift, params, noi
 
 
 @pytest.mark.parametrize("drift,params", [("dw", [4.0, 1.0]), ("ou", [0.8])])
-def test_vdp_closed_form_moments_equal_gauss_hermite(monkeypatch, drift, params):
+def test_vdp_closed_form_moments_equal_gauss_hermite(vdp_cfg, drift, params):
     """The same closed forms in the VDP sweep (E_sde and its gradients, 20 points; expected drift and slope of
     update_param, 10 points) against the quadrature loops (VDP_GH_QUADRATURE=1)."""
     from vi_diffusion_processes_b200.markovflow.sde import sde as sde_mod
@@ -599,7 +599,7 @@ def test_vdp_closed_form_moments_equal_gauss_hermite(monkeypatch, drift, params)
         return e, [e.sweep(0.1, update_x0=it > 1).clone() for it in range(4)]
 
     a, ea = run()
-    monkeypatch.setenv("VDP_GH_QUADRATURE", "1")
+    vdp_cfg(GH_QUADRATURE="1")
     c, ec = run()
     for name in ("A", "b", "m", "S", "lambda_lagrange", "psi_lagrange"):
         ref = getattr(c, name)
@@ -610,7 +610,7 @@ def test_vdp_closed_form_moments_equal_gauss_hermite(monkeypatch, drift, params)
 
 @pytest.mark.parametrize("drift,params,D,N,nseg", [("dw", [4.0, 1.0], 1, 3000, 0), ("dw", [4.0, 1.0], 1, 6000, 3),
                                                   ("vdp", [1.0, 1.0], 2, 1500, 0), ("ou", [0.7], 1, 40, 0)])
-def test_marginals_from_first_factor(monkeypatch, drift, params, D, N, nseg):
+def test_marginals_from_first_factor(vdp_cfg, drift, params, D, N, nseg):
     """Posterior rebuild: the marginal covariances come from the Cholesky factor naturals_to_ssm started from (the
     factor of the matrix the reference rebuilds from the state-space model and factorises a second time), the means
     from the forward recursion alone.  VDP_REFACTOR_PRECISION=1 runs the second factorisation: same state to
@@ -619,7 +619,7 @@ def test_marginals_from_first_factor(monkeypatch, drift, params, D, N, nseg):
     from vi_diffusion_processes_b200.cvi import CviEngine
     did = {"dw": sde_mod.DRIFT_DW, "ou": sde_mod.DRIFT_OU, "vdp": sde_mod.DRIFT_VDP}[drift]
     if nseg:
-        monkeypatch.setenv("VDP_NSEG", str(nseg))
+        vdp_cfg(NSEG=str(nseg))
     rng = np.random.default_rng(52)
     B, n_obs = 3, 12
     grid = np.round(np.arange(N + 1) * 0.005, 3)
@@ -628,7 +628,7 @@ def test_marginals_from_first_factor(monkeypatch, drift, params, D, N, nseg):
     mk = lambda: CviEngine(did, params, np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.ones(D), 1e-2 * np.eye(D))
     a, c = mk(), mk()
     ea = [a.site_update(0.5, 0.5).clone() for _ in range(3)]
-    monkeypatch.setenv("VDP_REFACTOR_PRECISION", "1")
+    vdp_cfg(REFACTOR_PRECISION="1")
     ec = [c.site_update(0.5, 0.5).clone() for _ in range(3)]
     a.check_status()
     c.check_status()
@@ -643,7 +643,7 @@ def test_marginals_from_first_factor(monkeypatch, drift, params, D, N, nseg):
 
 @pytest.mark.parametrize("drift,params,N,nseg", [("dw", [4.0, 1.0], 3000, 0), ("dw", [4.0, 1.0], 7000, 3),
                                                 ("ou", [0.7], 2500, 0)])
-def test_kl_terms_summed_in_the_mean_sweep(monkeypatch, drift, params, N, nseg):
+def test_kl_terms_summed_in_the_mean_sweep(vdp_cfg, drift, params, N, nseg):
     """Second rebuild of a site update, D = 1, polynomial drift: the mean sweep adds up the KL terms of classic_elbo on
     its way (per thread, per CTA, per tile; k_reduce_terms adds the tiles).  VDP_SEPARATE_KL_VALUE=1 runs k_kl_value
     over the grid instead: same ELBO and state up to the summation order."""
@@ -651,7 +651,7 @@ def test_kl_terms_summed_in_the_mean_sweep(monkeypatch, drift, params, N, nseg):
     from vi_diffusion_processes_b200.cvi import CviEngine
     did = {"dw": sde_mod.DRIFT_DW, "ou": sde_mod.DRIFT_OU}[drift]
     if nseg:
-        monkeypatch.setenv("VDP_NSEG", str(nseg))
+        vdp_cfg(NSEG=str(nseg))
     rng = np.random.default_rng(61)
     B, n_obs = 3, 12
     grid = np.round(np.arange(N + 1) * 0.005, 3)
@@ -660,7 +660,7 @@ def test_kl_terms_summed_in_the_mean_sweep(monkeypatch, drift, params, N, nseg):
     mk = lambda: CviEngine(did, params, np.ones((1, 1)), grid, idx, y, [[0.1]], [1.0], [[1e-2]])
     a, c = mk(), mk()
     ea = [a.site_update(0.5, 0.5).clone() for _ in range(3)]
-    monkeypatch.setenv("VDP_SEPARATE_KL_VALUE", "1")
+    vdp_cfg(SEPARATE_KL_VALUE="1")
     ec = [c.site_update(0.5, 0.5).clone() for _ in range(3)]
     a.check_status()
     th = c._prior_naturals(c.pA, c.pb)

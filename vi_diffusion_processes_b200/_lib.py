@@ -91,12 +91,16 @@ SWEEP_CHOL, SWEEP_NAT2SSM, SWEEP_MARG, SWEEP_INVBAND = 0, 1, 2, 3
 FLAG_SKIP_DATA_UPDATE, FLAG_SKIP_ELBO, FLAG_SKIP_GIRSANOV, FLAG_POSTERIOR_SSM_ONLY = 1, 2, 4, 8
 FLAG_NATURALS_CARRIED = 16
 FLAG_SITES_IN_NATURALS = 32
+FLAG_GH_QUADRATURE, FLAG_REFACTOR_PRECISION, FLAG_NO_FUSED_NATURALS, FLAG_SEPARATE_KL_VALUE = 64, 128, 256, 512
 VGP_STABILIZE = 1
 VGP_UPDATE_X0 = 2
+VGP_GH_QUADRATURE = 4
 
 # name -> (restype, argtypes); every symbol include/vdp_b200.h declares
 SIGNATURES = {
     "vdp_version": (C.c_int, []),
+    "vdp_config_set": (C.c_int, [C.c_char_p, C.c_int]),
+    "vdp_config_get": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
     "vdp_last_error": (C.c_char_p, []),
     "vdp_read_status": (i64, [vp, c_i64p, vp]),
     "vdp_btd_cholesky": (C.c_int, [vp, vp, vp, vp, i64, i64, C.c_int, vp, vp]),
@@ -197,6 +201,30 @@ def load():
         fn.argtypes = args
     _lib = lib
     return lib
+
+
+CONFIG_KEYS = ("SWEEPS", "NSEG", "GH_QUADRATURE", "REFACTOR_PRECISION", "NO_CARRIED_NATURALS", "NO_FUSED_NATURALS",
+               "SEPARATE_KL_VALUE")
+_SWEEPS = {None: 0, "auto": 0, "seq": 1, "tiled": 2}
+
+
+def configure(**kw):
+    """Process-wide tuning switches of the library (vdp_config_set): ``configure(SWEEPS="tiled", NSEG=3)``; ``None``
+    restores the default (0).  Used by tests and tuning runs; per-call ``FLAG_*`` select numerics routes re-entrantly."""
+    lib = load()
+    for k, v in kw.items():
+        k = k.upper()
+        if k not in CONFIG_KEYS:
+            raise VdpError(f"unknown configuration key {k}")
+        if k == "SWEEPS" and not isinstance(v, int):
+            v = _SWEEPS[v]
+        check(lib.vdp_config_set(k.encode(), int(v or 0)), "vdp_config_set")
+
+
+def config_get(key):
+    out = C.c_int()
+    check(load().vdp_config_get(key.upper().encode(), C.byref(out)), "vdp_config_get")
+    return out.value
 
 
 def check(rc: int, what: str):

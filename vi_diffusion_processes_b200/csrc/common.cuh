@@ -13,6 +13,21 @@ namespace vdp {
 
 void set_error(const char* fmt, ...);
 
+// Process-wide tuning / route switches (vdp_config_set).  Defaults come from the environment ONCE, when the library is
+// loaded (VDP_SWEEPS=seq|tiled, VDP_NSEG, VDP_GH_QUADRATURE, ... -- test and tuning hooks); no entry point reads the
+// environment afterwards.  The numerics routes can also be chosen per call through the problem's flags
+// (VDP_FLAG_GH_QUADRATURE, ...), which is what a caller that needs re-entrancy per stream uses.
+struct Config {
+    int sweeps = 0;                 // 0 = heuristic, 1 = thread per sequence, 2 = parallel-in-time tiles
+    int nseg = 0;                   // > 0: time segments per sequence of the tiled sweeps
+    int gh_quadrature = 0;          // 20-node Gauss-Hermite loops instead of the closed-form moments (cubic drifts)
+    int refactor_precision = 0;     // marginals through a second factorisation, as the reference (four sweeps)
+    int no_carried_naturals = 0;    // ignore VDP_FLAG_NATURALS_CARRIED
+    int no_fused_naturals = 0;      // rebuild the naturals from the sites after the girsanov update
+    int separate_kl_value = 0;      // KL terms of classic_elbo in their own pass instead of inside the mean sweep
+};
+extern Config g_cfg;
+
 #define VDP_CHECK_CUDA(expr)                                                                   \
     do {                                                                                       \
         cudaError_t _e = (expr);                                                               \

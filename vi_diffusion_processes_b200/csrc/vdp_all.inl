@@ -88,6 +88,37 @@ struct Profiler {
 };
 #if VDP_EMIT_CORE
 Profiler g_prof;
+
+static int env_flag(const char* name) {
+    const char* e = getenv(name);
+    return (e && *e) ? atoi(e) : 0;
+}
+static Config config_from_env() {
+    Config c;
+    const char* e = getenv("VDP_SWEEPS");
+    if (e && !strcmp(e, "seq")) c.sweeps = 1;
+    if (e && !strcmp(e, "tiled")) c.sweeps = 2;
+    c.nseg = env_flag("VDP_NSEG");
+    c.gh_quadrature = env_flag("VDP_GH_QUADRATURE");
+    c.refactor_precision = env_flag("VDP_REFACTOR_PRECISION");
+    c.no_carried_naturals = env_flag("VDP_NO_CARRIED_NATURALS");
+    c.no_fused_naturals = env_flag("VDP_NO_FUSED_NATURALS");
+    c.separate_kl_value = env_flag("VDP_SEPARATE_KL_VALUE");
+    return c;
+}
+Config g_cfg = config_from_env();   // the environment is read here, once, at load time
+static int* config_field(const char* key) {
+    if (!key) return nullptr;
+    if (!strncmp(key, "VDP_", 4)) key += 4;
+    if (!strcmp(key, "SWEEPS")) return &g_cfg.sweeps;
+    if (!strcmp(key, "NSEG")) return &g_cfg.nseg;
+    if (!strcmp(key, "GH_QUADRATURE")) return &g_cfg.gh_quadrature;
+    if (!strcmp(key, "REFACTOR_PRECISION")) return &g_cfg.refactor_precision;
+    if (!strcmp(key, "NO_CARRIED_NATURALS")) return &g_cfg.no_carried_naturals;
+    if (!strcmp(key, "NO_FUSED_NATURALS")) return &g_cfg.no_fused_naturals;
+    if (!strcmp(key, "SEPARATE_KL_VALUE")) return &g_cfg.separate_kl_value;
+    return nullptr;
+}
 #else
 extern Profiler g_prof;
 #endif
@@ -114,7 +145,20 @@ using namespace vdp;
 #if VDP_EMIT_CORE
 extern "C" {
 
-int vdp_version(void) { return 100; }
+int vdp_version(void) { return 200; }
+
+int vdp_config_set(const char* key, int value) {
+    int* f = config_field(key);
+    if (!f) { set_error("unknown configuration key %s", key ? key : "(null)"); return VDP_E_BADARG; }
+    *f = value;
+    return VDP_OK;
+}
+int vdp_config_get(const char* key, int* value) {
+    int* f = config_field(key);
+    if (!f || !value) { set_error("unknown configuration key %s", key ? key : "(null)"); return VDP_E_BADARG; }
+    *value = *f;
+    return VDP_OK;
+}
 const char* vdp_last_error(void) { return g_error; }
 
 int64_t vdp_read_status(const int64_t* status, int64_t* out_host2, void* stream) {

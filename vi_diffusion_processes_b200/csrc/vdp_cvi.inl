@@ -15,16 +15,16 @@ static int launch_kl_grad(const DriftParams& P, const double* q_host, double dt,
                           const double* Sd, double* terms, double* g1, double* gd, double* gs, int upd, double lr,
                           const double* sc1, const double* scd, int64_t B, int64_t N, int64_t* status,
                           cudaStream_t st, int64_t node0 = 0, int64_t node1 = -1,
-                          const KlNaturalsOut& nat = KlNaturalsOut()) {
+                          const KlNaturalsOut& nat = KlNaturalsOut(), bool gh_loops = false) {
     using KL = KlLaunch<D>;
     const int64_t total = ((node1 < 0) ? B * (N + 1) : node1) - node0;
     if (total <= 0) return VDP_OK;
     const unsigned grid = (unsigned)((total + KL::groups - 2) / (KL::groups - 1));
     const size_t smem = KL::groups * sizeof(KlHandoff<D>);
     // polynomial scalar drifts: the 20-point Gauss-Hermite sums are taken in closed form (CubicMoments, the same
-    // values up to rounding); VDP_GH_QUADRATURE=1 runs the quadrature loops instead
+    // values up to rounding); VDP_FLAG_GH_QUADRATURE / the GH_QUADRATURE switch run the quadrature loops instead
     if constexpr (D == 1 && KL::G == 1 && DriftStep1<DRIFT>::kCubic) {
-        if (!env_int("VDP_GH_QUADRATURE", 0)) {
+        if (!gh_loops && !g_cfg.gh_quadrature) {
             k_kl_grad<DRIFT, D, 20, KL::G, true><<<grid, KL::threads, smem, st>>>(
                 P, host_mat<D>(q_host), dt, pi_factor(D), time_grid, host_vec<D>(x0_mu), host_mat<D>(x0_cov), Aq, m,
                 Sd, terms, g1, gd, gs, upd, lr, sc1, scd, B, N, status, node0, node1, nat);
@@ -101,7 +101,8 @@ static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t 
     // and the forward sweep that follows computes the means alone.  VDP_REFACTOR_PRECISION=1 keeps the second
     // factorisation + inverse band (equal to rounding, tests/test_gpu_parity.py::test_marginals_from_first_factor).
     const bool ssm_only = (p.flags & VDP_FLAG_POSTERIOR_SSM_ONLY) != 0;
-    const bool lite = use_tiled_sweeps(B, N) && !env_int("VDP_REFACTOR_PRECISION", 0);
+    const bool gh_loops = (p.flags & VDP_FLAG_GH_QUADRATURE) || g_cfg.gh_quadrature;
+    const bool lite = use_tiled_sweeps(B, N) && !(p.flags & VDP_FLAG_REFACTOR_PRECISION) && !g_cfg.refactor_precision;
     int rc = run_nat2ssm<D>(w.th1, w.thd, w.ths, p.qA, p.qb, (skip_cholQ && lite && !ssm_only) ? nullptr : p.qcholQ,
                             p.qmu0, p.qcholP0, w.Ld, w.Ls, B, N, p.status, st, sc,
                             (lite && !ssm_only) ? p.fx_covs : nullptr);
@@ -110,7 +111,7 @@ static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t 
         prof_mark(VDP_PHASE_MARG_FWD, st);
         if constexpr (DRIFT >= 0 && D == 1) {
             if constexpr (DriftStep1<(DRIFT < 0 ? 0 : DRIFT)>::kCubic) {
-                if (kl_partials && !env_int("VDP_GH_QUADRATURE", 0) && !env_int("VDP_SEPARATE_KL_VALUE", 0)) {
+                if (kl_partials && !gh_loops && !(p.flags & VDP_FLAG_SEPARATE_KL_VALUE) && !g_cfg.separate_kl_value) {
                     MeanKlArgs ka;
                     ka.P = make_params(p.drift_params);
                     ka.Qp = p.dt * p.q[0];
@@ -145,7 +146,8 @@ static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams&
         p.fx_mus, p.fx_covs, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.ve, B, N, p.n_obs);
     VDP_CHECK_LAUNCH();
     bool closed = false;
-    if constexpr (D == 1 && G == 1 && DriftStep1<DRIFT>::kCubic) closed = !env_int("VDP_GH_QUADRATURE", 0);
+    if constexpr (D == 1 && G == 1 && DriftStep1<DRIFT>::kCubic)
+        closed = !(p.flags & VDP_FLAG_GH_QUADRATURE) && !g_cfg.gh_quadrature;
     if (kl_partials > 0) {
         // the mean sweep of the rebuild has left kl_partials partial sums per sequence in w.terms
         k_reduce_terms<<<(unsigned)B, 256, 0, st>>>(w.terms, kl_partials, p.kl);
@@ -193,7 +195,7 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     }
     // the naturals written by the previous update's girsanov kernel are still valid away from the observations
     const bool carried = (p.flags & VDP_FLAG_NATURALS_CARRIED) && p.n_obs <= 128 && node1 < 0 &&
-                         !env_int("VDP_NO_CARRIED_NATURALS", 0);
+                         !g_cfg.no_carried_naturals;
     // sites held in theta (VDP_FLAG_SITES_IN_NATURALS, only together with carried naturals): the girsanov update moves
     // theta itself, g1 / gd / gs are neither read nor written (vdp_cvi_materialize_sites forms them on request)
     const bool lazy = carried && (p.flags & VDP_FLAG_SITES_IN_NATURALS) && !stop_after_sites &&
@@ -234,7 +236,8 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     }
     // whole-chain update: the kernel also writes the naturals of the posterior that follows (no second pass over
     // the sites); the sharded quadrature exchanges site ranges first and rebuilds from the sites
-    const bool fuse_nat = lazy || ((node1 < 0) && !stop_after_sites && !env_int("VDP_NO_FUSED_NATURALS", 0));
+    const bool fuse_nat = lazy || ((node1 < 0) && !stop_after_sites && !(p.flags & VDP_FLAG_NO_FUSED_NATURALS) &&
+                                   !g_cfg.no_fused_naturals);
     KlNaturalsOut nat;
     if (fuse_nat) {
         if (!lazy) { nat.pA = p.pA; nat.pb = p.pb; nat.pcholQ = p.pcholQ; nat.pmu0 = p.pmu0; nat.pcholP0 = p.pcholP0; }
@@ -242,7 +245,7 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     }
     if ((rc = launch_kl_grad<DRIFT, D>(P, p.q, p.dt, p.time_grid, p.x0_mu, p.x0_cov, p.qA, p.fx_mus, p.fx_covs,
                                        nullptr, p.g1, p.gd, p.gs, lazy ? 2 : 1, p.lr_girsanov, w.sc1, w.scd, B, N,
-                                       p.status, st, node0, node1, nat)))
+                                       p.status, st, node0, node1, nat, (p.flags & VDP_FLAG_GH_QUADRATURE) != 0)))
         return rc;
     if (stop_after_sites) { prof_mark(VDP_PHASE_END, st); return VDP_OK; }
     const bool want_elbo = !(p.flags & VDP_FLAG_SKIP_ELBO);
@@ -383,7 +386,8 @@ int vdp_cvi_update_girsanov_sites_range(const vdp_cvi_problem* p, int64_t node_b
         }
         rc = launch_kl_grad<kDrift, kD>(P, p->q, p->dt, p->time_grid, p->x0_mu, p->x0_cov, p->qA, p->fx_mus, p->fx_covs,
                                         nullptr, p->g1, p->gd, p->gs, 1, p->lr_girsanov, w.sc1, w.scd, p->B, p->N,
-                                        p->status, st, node_begin, node_end);
+                                        p->status, st, node_begin, node_end, KlNaturalsOut(),
+                                        (p->flags & VDP_FLAG_GH_QUADRATURE) != 0);
         if (rc) return rc;
     }));
     return VDP_OK;

@@ -68,22 +68,16 @@ struct SegPlan {
     int64_t seg_len;
 };
 
-static inline int env_int(const char* name, int dflt) {
-    const char* e = getenv(name);
-    return (e && *e) ? atoi(e) : dflt;
-}
-
-// VDP_SWEEPS = seq | tiled overrides the heuristic (tests run both paths)
+// vdp_config_set("SWEEPS", 1 | 2) overrides the heuristic (tests run both mappings)
 static inline bool use_tiled_sweeps(int64_t B, int64_t N) {
-    const char* e = getenv("VDP_SWEEPS");
-    if (e && !strcmp(e, "seq")) return false;
-    if (e && !strcmp(e, "tiled")) return N >= 1;
+    if (g_cfg.sweeps == 1) return false;
+    if (g_cfg.sweeps == 2) return N >= 1;
     return N >= 512 || (B < 148 * 64 && N >= 32);
 }
 
 static inline SegPlan plan_segments(int64_t B, int64_t N, int tile_steps, bool have_scratch) {
     int64_t want = 1;
-    const int forced = env_int("VDP_NSEG", 0);
+    const int forced = g_cfg.nseg;
     if (forced > 0) {
         want = forced;
     } else if (B < kTargetBlocks) {

@@ -20,10 +20,8 @@ from ._lib import CviProblem, check
 F64 = torch.float64
 
 
-def _env_on(name):
-    import os
-    v = os.environ.get(name, "")
-    return bool(v) and v != "0"
+def _cfg_on(name):
+    return _lib.config_get(name) != 0
 
 
 class CviEngine:
@@ -43,6 +41,7 @@ class CviEngine:
         # consecutive carried updates keep the girsanov sites implicitly in theta (VDP_FLAG_SITES_IN_NATURALS) and
         # form g1 / gd / gs when somebody reads them (the g1 / gd / gs properties below)
         self.lazy_sites = bool(lazy_sites) and self.carry_naturals
+        self.route_flags = 0          # FLAG_GH_QUADRATURE | FLAG_REFACTOR_PRECISION | ...: OR-ed into every call
         self._sites_stale = False
         self._nat_sig = None
         self.drift_id = int(drift_id)
@@ -158,7 +157,7 @@ class CviEngine:
             setattr(p, name, t.data_ptr())
         p.workspace = self._ws.data_ptr()
         p.workspace_bytes = self._ws_bytes
-        p.flags = flags
+        p.flags = flags | self.route_flags
         if not keep_carry:
             self._nat_sig = None      # whatever is called with this problem may rewrite the workspace
         return p
@@ -188,12 +187,14 @@ class CviEngine:
         replaced or modified in place through torch (storage pointer + version counter).
         """
         carry = self.carry_naturals if carry is None else carry
+        flags |= self.route_flags
         lazy = False
         if carry and self._nat_sig is not None and self._nat_sig == self._nat_signature():
             flags |= _lib.FLAG_NATURALS_CARRIED
             # the library honours the lazy sites under these conditions (vdp_cvi.inl run_site_update)
             lazy = (self.lazy_sites and self.n_obs <= 128 and not (flags & _lib.FLAG_SKIP_GIRSANOV)
-                    and not _env_on("VDP_NO_CARRIED_NATURALS") and not _env_on("VDP_NO_FUSED_NATURALS"))
+                    and not _cfg_on("NO_CARRIED_NATURALS") and not _cfg_on("NO_FUSED_NATURALS")
+                    and not (flags & _lib.FLAG_NO_FUSED_NATURALS))
             if lazy:
                 flags |= _lib.FLAG_SITES_IN_NATURALS
         p = self._problem(lr_data, lr_girsanov, flags, keep_carry=lazy)
@@ -217,7 +218,8 @@ class CviEngine:
         the problem has been replaced (re-linearisation, site assignment) or the step sizes / drift parameters change.
         """
         # everything a captured launch sequence holds by value or by address
-        key = (float(lr_data), float(lr_girsanov), int(flags), tuple(self.drift_params), tuple(self.x0_mu.tolist()),
+        key = (float(lr_data), float(lr_girsanov), int(flags | self.route_flags), tuple(self.drift_params),
+               tuple(_lib.config_get(k) for k in _lib.CONFIG_KEYS), tuple(self.x0_mu.tolist()),
                tuple(self.x0_cov.reshape(-1).tolist()), tuple(self.q.reshape(-1).tolist()),
                tuple(self.lik_chol.reshape(-1).tolist()), self.dt, self.clip, self.stabilize_ssm,
                tuple(getattr(self, n).data_ptr() for n in self._PTR_FIELDS))

@@ -52,6 +52,7 @@ class VgpEngine:
         self.x0_mu = np.zeros(D) if x0_mu is None else np.asarray(x0_mu, dtype=np.float64).reshape(D)
         self.x0_cov = self.q * np.eye(D) if x0_cov is None else np.atleast_2d(np.asarray(x0_cov, dtype=np.float64))
         self.stabilize_system = bool(stabilize_system)
+        self.route_flags = 0          # VGP_GH_QUADRATURE: OR-ed into every call
         z = lambda *s: torch.zeros(s, dtype=F64, device=dev)
         eye = torch.eye(D, dtype=F64, device=dev)
         self.A, self.b = z(B, N, D, D), z(B, N, D)
@@ -91,7 +92,8 @@ class VgpEngine:
             setattr(p, field, t.data_ptr())
         p.workspace = self._ws.data_ptr()
         p.workspace_bytes = self._ws_bytes
-        p.flags = (_lib.VGP_STABILIZE if self.stabilize_system else 0) | (_lib.VGP_UPDATE_X0 if update_x0 else 0)
+        p.flags = ((_lib.VGP_STABILIZE if self.stabilize_system else 0) | (_lib.VGP_UPDATE_X0 if update_x0 else 0) |
+                   self.route_flags)
         return p
 
     def _call(self, name, p):
@@ -138,7 +140,8 @@ class VgpEngine:
         ``CviEngine.site_update_graphed``); re-captured when a buffer, a step size or a drift parameter changes."""
         names = ("time_grid", "A", "b", "lambda_lagrange", "psi_lagrange", "q_initial_mean", "q_initial_chol",
                  "obs_idx", "obs_y", "m", "S", "elbo_value", "status")
-        key = (float(lr), bool(update_x0), float(x0_lr), tuple(self.drift_params), tuple(self.x0_mu.tolist()),
+        key = (float(lr), bool(update_x0), float(x0_lr), self.route_flags, tuple(self.drift_params),
+               tuple(_lib.config_get(k) for k in _lib.CONFIG_KEYS), tuple(self.x0_mu.tolist()),
                tuple(self.x0_cov.reshape(-1).tolist()), tuple(self.q.reshape(-1).tolist()),
                tuple(self.lik_chol.reshape(-1).tolist()), self.dt, self.stabilize_system, tuple(getattr(self, n).data_ptr() for n in names))
         cache = getattr(self, "_graphs", None)
