@@ -253,6 +253,12 @@ typedef struct vdp_cvi_problem {
     int64_t* status;           /* device int64[2] or NULL */
     int32_t flags;             /* VDP_FLAG_* */
     int32_t reserved;
+    /* optional per-sequence step sizes in DEVICE memory (all NULL: lr_data / lr_girsanov above apply to every
+     * sequence): sequence b is updated with lr_data_dev[b] / lr_girsanov_dev[b], or left as it is where
+     * active_dev[b] == 0.  This is what lets a trainer loop decay its step sizes and stop sequences without the host
+     * (vdp_cvi_optimize_sites). */
+    const double *lr_data_dev, *lr_girsanov_dev;   /* [B] */
+    const int32_t* active_dev;                     /* [B] */
 } vdp_cvi_problem;
 
 #define VDP_FLAG_DEFAULT 0
@@ -324,6 +330,31 @@ int vdp_cvi_full_sites(const vdp_cvi_problem* problem_host, double* th1, double*
 int vdp_cvi_update_girsanov_sites_range(const vdp_cvi_problem* problem_host, int64_t node_begin, int64_t node_end,
                                         void* stream);
 int vdp_cvi_elbo_terms_range(const vdp_cvi_problem* problem_host, int64_t node_begin, int64_t node_end, void* stream);
+
+/* CVISitesTrainer._optimize_sites_under_stable_prior (docs/diffusion_processes/cvi_dp_trainer.py:63-101) ON THE DEVICE:
+ * up to max_itr site updates (cvi_dp_trainer.py:71-77 each), the ELBO-decrease => step sizes / 10 rule (:84-87) and
+ * the |ELBO change| < optim_tol stop (:89-91) evaluated per sequence by a kernel after each update, the loop itself a
+ * CUDA-graph WHILE node whose condition that kernel sets -- no host synchronisation between updates.  The call
+ * enqueues the whole loop on `stream` and returns; the host reads n_itr / elbo_trace / test_* once afterwards.
+ *   in:     elbo_trace row 0 = the ELBO before the loop (classic_elbo); lr_data, lr_girsanov [B] current step sizes
+ *   in/out: the problem's state as vdp_cvi_site_update; lr_data, lr_girsanov (decayed values persist, as the
+ *           reference keeps them on the trainer object)
+ *   out:    n_itr [B] updates a sequence took, elbo_trace rows 1..n_itr (later rows repeat the last value), and the
+ *           marginals at the test grid points after every update (for NLPD / RMSE, exp_dp_utils.py:189-224)
+ * The first update runs with problem->flags, the following ones with later_flags (typically | NATURALS_CARRIED
+ * | SITES_IN_NATURALS).  A sequence that has stopped keeps its state (its step sizes are taken as 0). */
+typedef struct vdp_cvi_loop {
+    int32_t max_itr, n_test;
+    int32_t later_flags, reserved;
+    double optim_tol;
+    double *lr_data, *lr_girsanov;   /* [B] */
+    int32_t *active, *n_itr;         /* [B] (active: scratch) */
+    double* elbo_trace;              /* [max_itr + 1, B] */
+    const int64_t* test_idx;         /* [B, n_test] or NULL */
+    double *test_mus, *test_covs;    /* [max_itr, B, n_test, D], [max_itr, B, n_test, D, D] or NULL */
+    int32_t* counters;               /* device int32[2] scratch: {updates done, sequences still active} */
+} vdp_cvi_loop;
+int vdp_cvi_optimize_sites(const vdp_cvi_problem* problem_host, const vdp_cvi_loop* loop_host, void* stream);
 
 /* classic_elbo only (no site is modified); fills elbo/ve/kl, q* and fx_* */
 int vdp_cvi_elbo(const vdp_cvi_problem* problem_host, void* stream);

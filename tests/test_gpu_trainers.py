@@ -84,3 +84,54 @@ def test_vi_markov_gp_trainer_matches_oracle_loop():
     for g, w, name in zip(got, want, ("elbo", "nlpd", "rmse")):
         assert len(g) == len(w) == 6, name
         np.testing.assert_allclose(g, w, rtol=1e-9, err_msg=name)
+
+
+def test_device_side_site_loop_equals_host_loop_per_sequence():
+    """vdp_cvi_optimize_sites (CUDA-graph WHILE node, convergence / step-size decay decided by a kernel, per sequence)
+    against the host loop of cvi_dp_trainer.py:63-101 run on one-sequence engines: same number of updates, ELBO
+    traces, decayed step sizes, test-point marginals and final state for every sequence of a batch whose members
+    stop at different iterations."""
+    from oracle.sde_np import DRIFT_DW
+    from vi_diffusion_processes_b200.cvi import CviEngine
+    rng = np.random.default_rng(77)
+    B, N, n_obs, n_test = 3, 500, 9, 5
+    grid = np.round(np.arange(N + 1) * 0.01, 6)
+    idx = np.sort(np.stack([rng.choice(N + 1, n_obs, replace=False) for _ in range(B)]), axis=1)
+    y = rng.normal(size=(B, n_obs, 1)) * np.array([0.05, 0.3, 0.6])[:, None, None] + 1.0
+    tidx = np.sort(np.stack([rng.choice(N + 1, n_test, replace=False) for _ in range(B)]), axis=1)
+    mk = lambda sl: CviEngine(DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx[sl], y[sl], [[0.1]], [1.0], [[1e-2]])
+    max_itr, tol, lr0 = 12, 0.5, 0.7
+    batch = mk(slice(None))
+    res = batch.optimize_sites(max_itr, tol, lr0, lr0, test_idx=tidx)
+    batch.check_status()
+    n_seen = set()
+    for b in range(B):
+        one = mk(slice(b, b + 1))
+        lr = lr0
+        elbo = [one.classic_elbo_keep_marginals().item()]
+        tm = []
+        while len(elbo) - 1 < max_itr:
+            elbo.append(one.site_update(lr, lr).item())
+            tm.append(one.fx_mus[0, tidx[b], 0].cpu().numpy().copy())
+            if len(elbo) > 2 and elbo[-2] > elbo[-1]:
+                lr /= 10
+            if len(elbo) > 2 and abs(elbo[-2] - elbo[-1]) < tol:
+                break
+        n = len(elbo) - 1
+        n_seen.add(n)
+        assert int(res["n_itr"][b]) == n, (b, int(res["n_itr"][b]), n)
+        np.testing.assert_allclose(res["elbo_trace"][:n + 1, b].numpy(), elbo, rtol=1e-10)
+        np.testing.assert_allclose(float(res["lr_data"][b]), lr, rtol=1e-15)
+        np.testing.assert_allclose(res["test_mus"][:n, b, :, 0].numpy(), np.stack(tm), rtol=1e-9, atol=1e-12)
+        for name in ("fx_mus", "fx_covs", "d1", "d2"):
+            a, w = getattr(batch, name)[b], getattr(one, name)[0]
+            assert float((a - w).abs().max()) <= 1e-10 * float(w.abs().max()), (b, name)
+        th = one._prior_naturals(one.pA, one.pb)
+        for name, t in (("g1", th[0]), ("gd", th[1]), ("gs", th[2])):
+            a, w = getattr(batch, name)[b], getattr(one, name)[0]
+            assert float((a - w).abs().max()) <= 1e-10 * float((t[0] + w).abs().max()), (b, name)
+    assert len(n_seen) > 1, "the sequences were meant to stop at different iterations"
+    # a second call on the same engine reuses the captured loop and starts from the decayed step sizes
+    res2 = batch.optimize_sites(max_itr, tol, res["lr_data"].numpy(), res["lr_girsanov"].numpy(), test_idx=tidx)
+    batch.check_status()
+    assert (res2["n_itr"] >= 2).all()

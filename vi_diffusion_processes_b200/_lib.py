@@ -44,6 +44,23 @@ class CviProblem(C.Structure):
         ("workspace", vp), ("workspace_bytes", C.c_size_t),
         ("status", vp),
         ("flags", C.c_int32), ("reserved", C.c_int32),
+        ("lr_data_dev", vp), ("lr_girsanov_dev", vp),
+        ("active_dev", vp),
+    ]
+
+
+class CviLoop(C.Structure):
+    """Mirror of ``struct vdp_cvi_loop`` (include/vdp_b200.h)."""
+    _fields_ = [
+        ("max_itr", C.c_int32), ("n_test", C.c_int32),
+        ("later_flags", C.c_int32), ("reserved", C.c_int32),
+        ("optim_tol", C.c_double),
+        ("lr_data", vp), ("lr_girsanov", vp),
+        ("active", vp), ("n_itr", vp),
+        ("elbo_trace", vp),
+        ("test_idx", vp),
+        ("test_mus", vp), ("test_covs", vp),
+        ("counters", vp),
     ]
 
 
@@ -139,6 +156,7 @@ SIGNATURES = {
     "vdp_cvi_materialize_sites": (C.c_int, [C.POINTER(CviProblem), vp]),
     "vdp_cvi_site_update_sharded": (C.c_int, [C.POINTER(CviProblem), C.c_int, i64, i64, vp]),
     "vdp_cvi_elbo": (C.c_int, [C.POINTER(CviProblem), vp]),
+    "vdp_cvi_optimize_sites": (C.c_int, [C.POINTER(CviProblem), C.POINTER(CviLoop), vp]),
     "vdp_cvi_update_data_sites": (C.c_int, [C.POINTER(CviProblem), vp]),
     "vdp_cvi_full_sites": (C.c_int, [C.POINTER(CviProblem), vp, vp, vp, vp]),
     "vdp_cvi_update_girsanov_sites_range": (C.c_int, [C.POINTER(CviProblem), i64, i64, vp]),

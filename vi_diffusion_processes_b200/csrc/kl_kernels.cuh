@@ -303,6 +303,9 @@ __device__ __forceinline__ void kl_term(const DriftParams& P, const Mat<D>& Qp, 
 struct KlNaturalsOut {
     const double *pA = nullptr, *pb = nullptr, *pcholQ = nullptr, *pmu0 = nullptr, *pcholP0 = nullptr;
     double *th1 = nullptr, *thd = nullptr, *ths = nullptr;
+    // optional per-sequence step sizes held on the device (vdp_cvi_problem.lr_girsanov_dev / active_dev)
+    const double* lr_dev = nullptr;
+    const int32_t* active = nullptr;
 };
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -426,6 +429,7 @@ __global__ void __launch_bounds__(KlBounds<G>::threads, KlBounds<G>::blocks) k_k
     }
     // S = eta_d - m m^T
     gm = gm - 2.0 * mv(gS, mk);
+    if (nat.lr_dev) lr = (!nat.active || nat.active[b]) ? nat.lr_dev[b] : 0.0;
     if (terms) terms[i] = value;
     if (!upd) {
         vec_store<D>(g1 + i * D, gm);

@@ -283,11 +283,13 @@ template <int D>
 __global__ void k_data_site_update(const double* __restrict__ fx_mus, const int64_t* __restrict__ obs_idx,
                                    const double* __restrict__ obs_y, Mat<D> lik_chol, double lr,
                                    double* __restrict__ d1, double* __restrict__ d2, int64_t B, int64_t N,
-                                   int64_t n_obs) {
+                                   int64_t n_obs, const double* __restrict__ lr_dev = nullptr,
+                                   const int32_t* __restrict__ active = nullptr) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= B * n_obs) return;
     constexpr int DD = D * D;
     const int64_t b = i / n_obs;
+    if (lr_dev) lr = (!active || active[b]) ? lr_dev[b] : 0.0;   // per-sequence step size held on the device
     const int64_t k = obs_idx[i];
     const Vec<D> mu = vec_load<D>(fx_mus + (b * (N + 1) + k) * D);
     const Mat<D> inv = chol_inverse(lik_chol);

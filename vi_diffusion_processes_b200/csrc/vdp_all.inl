@@ -364,6 +364,7 @@ extern "C" int vdp_euler_maruyama(int drift_id, const double* params_host, const
 #endif
 #if VDP_EMIT_CVI
 #include "vdp_host.inl"
+#include "vdp_trainer.inl"
 #endif
 #if VDP_EMIT_VGP
 #include "vdp_vgp.inl"

@@ -190,7 +190,8 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     if (!(p.flags & VDP_FLAG_SKIP_DATA_UPDATE) && p.n_obs > 0) {
         prof_mark(VDP_PHASE_DATA_SITES, st);
         k_data_site_update<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
-            p.fx_mus, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.lr_data, p.d1, p.d2, B, N, p.n_obs);
+            p.fx_mus, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.lr_data, p.d1, p.d2, B, N, p.n_obs, p.lr_data_dev,
+            p.active_dev);
         VDP_CHECK_LAUNCH();
     }
     // the naturals written by the previous update's girsanov kernel are still valid away from the observations
@@ -243,6 +244,8 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
         if (!lazy) { nat.pA = p.pA; nat.pb = p.pb; nat.pcholQ = p.pcholQ; nat.pmu0 = p.pmu0; nat.pcholP0 = p.pcholP0; }
         nat.th1 = w.th1; nat.thd = w.thd; nat.ths = w.ths;
     }
+    nat.lr_dev = p.lr_girsanov_dev;
+    nat.active = p.active_dev;
     if ((rc = launch_kl_grad<DRIFT, D>(P, p.q, p.dt, p.time_grid, p.x0_mu, p.x0_cov, p.qA, p.fx_mus, p.fx_covs,
                                        nullptr, p.g1, p.gd, p.gs, lazy ? 2 : 1, p.lr_girsanov, w.sc1, w.scd, B, N,
                                        p.status, st, node0, node1, nat, (p.flags & VDP_FLAG_GH_QUADRATURE) != 0)))
@@ -341,7 +344,7 @@ int vdp_cvi_update_data_sites(const vdp_cvi_problem* p, void* stream) {
     if (p->B == 0 || p->n_obs == 0) return VDP_OK;
     VDP_DISPATCH_D(p->D, (k_data_site_update<kD><<<grid_for(p->B * p->n_obs, kPtBlock), kPtBlock, 0, as_stream(stream)>>>(
                              p->fx_mus, p->obs_idx, p->obs_y, host_mat<kD>(p->lik_chol), p->lr_data, p->d1, p->d2, p->B,
-                             p->N, p->n_obs)));
+                             p->N, p->n_obs, p->lr_data_dev, p->active_dev)));
     VDP_CHECK_LAUNCH();
     return VDP_OK;
 }
@@ -386,7 +389,12 @@ int vdp_cvi_update_girsanov_sites_range(const vdp_cvi_problem* p, int64_t node_b
         }
         rc = launch_kl_grad<kDrift, kD>(P, p->q, p->dt, p->time_grid, p->x0_mu, p->x0_cov, p->qA, p->fx_mus, p->fx_covs,
                                         nullptr, p->g1, p->gd, p->gs, 1, p->lr_girsanov, w.sc1, w.scd, p->B, p->N,
-                                        p->status, st, node_begin, node_end, KlNaturalsOut(),
+                                        p->status, st, node_begin, node_end, [&] {
+                                            KlNaturalsOut nat;
+                                            nat.lr_dev = p->lr_girsanov_dev;
+                                            nat.active = p->active_dev;
+                                            return nat;
+                                        }(),
                                         (p->flags & VDP_FLAG_GH_QUADRATURE) != 0);
         if (rc) return rc;
     }));

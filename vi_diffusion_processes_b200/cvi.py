@@ -207,6 +207,55 @@ class CviEngine:
             self._nat_sig = None
         return self.elbo
 
+    def optimize_sites(self, max_itr, optim_tol, lr_data, lr_girsanov, test_idx=None):
+        """
+        ``CVISitesTrainer._optimize_sites_under_stable_prior`` (cvi_dp_trainer.py:63-101) on the device
+        (``vdp_cvi_optimize_sites``): up to ``max_itr`` site updates with the ELBO-drop => step sizes / 10 rule and the
+        convergence test evaluated per sequence by a kernel, the loop a CUDA-graph WHILE node -- no host
+        synchronisation between updates.  ``lr_data`` / ``lr_girsanov``: scalars or [B]; ``test_idx`` [B, n_test] grid
+        indices whose marginals are recorded after every update (for NLPD / RMSE).
+
+        Returns a dict of CPU tensors: ``n_itr`` [B], ``elbo_trace`` [max_itr + 1, B] (row 0 = ELBO before the loop),
+        ``lr_data`` / ``lr_girsanov`` [B] (decayed), ``test_mus`` [max_itr, B, n_test, D], ``test_covs``.
+        """
+        B, D, dev = self.B, self.D, self.device
+        mk = lambda v: torch.as_tensor(np.broadcast_to(np.asarray(v, dtype=np.float64), (B,)).copy()).to(dev)
+        lrd, lrg = mk(lr_data), mk(lr_girsanov)
+        trace = torch.zeros((max_itr + 1, B), dtype=F64, device=dev)
+        trace[0] = self.classic_elbo_keep_marginals()      # tmp_elbo_vals = [classic_elbo()]   (:67)
+        active = torch.zeros(B, dtype=torch.int32, device=dev)
+        n_itr = torch.zeros(B, dtype=torch.int32, device=dev)
+        counters = torch.zeros(2, dtype=torch.int32, device=dev)
+        lp = _lib.CviLoop()
+        lp.max_itr, lp.optim_tol = int(max_itr), float(optim_tol)
+        n_test = 0
+        tm = tc = ti = None
+        if test_idx is not None:
+            ti = torch.as_tensor(np.asarray(test_idx, dtype=np.int64).reshape(B, -1)).to(dev).contiguous()
+            n_test = ti.shape[1]
+            tm = torch.zeros((max_itr, B, n_test, D), dtype=F64, device=dev)
+            tc = torch.zeros((max_itr, B, n_test, D, D), dtype=F64, device=dev)
+            lp.test_idx, lp.test_mus, lp.test_covs = ti.data_ptr(), tm.data_ptr(), tc.data_ptr()
+        lp.n_test = n_test
+        lp.lr_data, lp.lr_girsanov = lrd.data_ptr(), lrg.data_ptr()
+        lp.active, lp.n_itr, lp.elbo_trace, lp.counters = (active.data_ptr(), n_itr.data_ptr(), trace.data_ptr(),
+                                                           counters.data_ptr())
+        lazy = (self.carry_naturals and self.lazy_sites and self.n_obs <= 128 and max_itr >= 2
+                and not _cfg_on("NO_CARRIED_NATURALS") and not _cfg_on("NO_FUSED_NATURALS")
+                and not (self.route_flags & _lib.FLAG_NO_FUSED_NATURALS))
+        later = self.route_flags
+        if self.carry_naturals:
+            later |= _lib.FLAG_NATURALS_CARRIED | (_lib.FLAG_SITES_IN_NATURALS if lazy else 0)
+        lp.later_flags = later
+        p = self._problem(0.0, 0.0, self.route_flags)      # first update: naturals rebuilt from the sites
+        self._run("vdp_cvi_optimize_sites", C.byref(p), C.byref(lp))
+        self._sites_stale = lazy
+        self._nat_sig = self._nat_signature() if self.carry_naturals else None
+        out = {"n_itr": n_itr.cpu(), "elbo_trace": trace.cpu(), "lr_data": lrd.cpu(), "lr_girsanov": lrg.cpu()}
+        if tm is not None:
+            out["test_mus"], out["test_covs"] = tm.cpu(), tc.cpu()
+        return out
+
     _PTR_FIELDS = ("time_grid", "pA", "pb", "pcholQ", "pmu0", "pcholP0", "_g1", "_gd", "_gs", "d1", "d2", "obs_idx", "obs_y",
                    "fx_mus", "fx_covs", "qA", "qb", "qcholQ", "qmu0", "qcholP0", "elbo", "ve", "kl", "status")
 

@@ -155,6 +155,18 @@ class CVISitesSDE:
         """The three calls above fused in one launch sequence; returns the ELBO."""
         return self._eng.site_update(data_lr, girsanov_lr)[0]
 
+    def optimize_sites(self, max_itr: int, optim_tol: float, data_lr: float, girsanov_lr: float, test_indices=None):
+        """``CVISitesTrainer._optimize_sites_under_stable_prior`` (cvi_dp_trainer.py:63-101) as one device-side
+        loop (``vdp_cvi_optimize_sites``).  Returns (elbo list, test means [n, n_test, D], test covariances, data_lr,
+        girsanov_lr) with n = the updates the loop took."""
+        ti = None if test_indices is None else np.asarray(test_indices, dtype=np.int64)[None]
+        r = self._eng.optimize_sites(max_itr, optim_tol, data_lr, girsanov_lr, test_idx=ti)
+        n = int(r["n_itr"][0])
+        elbo = [float(v) for v in r["elbo_trace"][1:n + 1, 0]]
+        tm = r["test_mus"][:n, 0] if "test_mus" in r else None
+        tc = r["test_covs"][:n, 0] if "test_covs" in r else None
+        return elbo, tm, tc, float(r["lr_data"][0]), float(r["lr_girsanov"][0])
+
     def variational_expectation(self):
         """variational_cvi_sde.py:319-337 (of the current posterior)"""
         self.classic_elbo()

@@ -91,8 +91,11 @@ class CVISitesTrainer:
     def __init__(self, model, test_data, prior_sde=None, max_itr: int = 100, optim_tol: float = 1e-2,
                  max_itr_sites_optim: int = 20, girsanov_sites_lr: float = 0.1, data_sites_lr: float = 0.1,
                  learn_prior_sde: bool = False, prior_sde_lr: float = 1e-2, learning_max_itr: int = 100,
-                 learning_tol: float = 1e-2, **unused):
+                 learning_tol: float = 1e-2, device_loop: bool = True, **unused):
         self.model, self.test_data, self.prior_sde = model, test_data, prior_sde
+        # the inner loop runs on the device (vdp_cvi_optimize_sites: CUDA-graph WHILE node, convergence and step-size
+        # decay decided by a kernel) when the model offers it; device_loop=False keeps the host loop below
+        self.device_loop = bool(device_loop) and hasattr(model, "optimize_sites")
         self.max_itr, self.optim_tol, self.max_itr_sites_optim = max_itr, optim_tol, max_itr_sites_optim
         self.girsanov_sites_lr, self.data_sites_lr = girsanov_sites_lr, data_sites_lr
         self.learn_prior_sde, self.prior_sde_lr = learn_prior_sde, prior_sde_lr
@@ -136,8 +139,29 @@ class CVISitesTrainer:
         m, S = self.model.likelihood.predict_mean_and_var(*self._marginals())
         return calculate_rmse(m, self.model.time_grid, self.test_data)
 
+    def _optimize_sites_on_device(self):
+        """cvi_dp_trainer.py:63-101 with the loop on the device: one call, one read-back."""
+        idx = _test_indices(self.model.time_grid, self.test_data[0])
+        elbo, tm, tc, self.data_sites_lr, self.girsanov_sites_lr = self.model.optimize_sites(
+            self.max_itr_sites_optim, self.optim_tol, self.data_sites_lr, self.girsanov_sites_lr, test_indices=idx)
+        self._check()
+        y = torch.as_tensor(as_np(self.test_data[1]), dtype=tm.dtype).reshape(idx.shape[0], -1)
+        nlpd, rmse = [], []
+        for m, S in zip(tm, tc):       # NLPD / RMSE of every iteration from the recorded test marginals
+            m, S = self.model.likelihood.predict_mean_and_var(m, S)
+            L = torch.linalg.cholesky(S)
+            z = torch.linalg.solve_triangular(L, (y - m)[..., None], upper=False)[..., 0]
+            D = m.shape[-1]
+            logp = (-0.5 * (z * z).sum(-1) - torch.log(torch.diagonal(L, dim1=-2, dim2=-1)).sum(-1)
+                    - 0.5 * D * math.log(2 * math.pi))
+            nlpd.append(float(-logp.mean().item()))
+            rmse.append(float(torch.sqrt(torch.mean((m - y) ** 2)).item()))
+        return elbo, nlpd, rmse
+
     def _optimize_sites_under_stable_prior(self):
         """cvi_dp_trainer.py:63-101"""
+        if self.device_loop:
+            return self._optimize_sites_on_device()
         elbo, nlpd, rmse = [self._elbo()], [], []
         while (len(elbo) - 1) < self.max_itr_sites_optim:
             # update_data_sites; update_girsanov_sites; classic_elbo  == one fused vdp_cvi_site_update
