@@ -465,6 +465,9 @@ typedef struct vdp_vgp_problem {
 #define VDP_VGP_STABILIZE 1    /* stabilize_system=True (clips of vi_sde.py:184-197, 314-323, 393-397) */
 #define VDP_VGP_UPDATE_X0 2    /* vdp_vgp_sweep also runs update_initial_statistics */
 #define VDP_VGP_GH_QUADRATURE 4 /* as VDP_FLAG_GH_QUADRATURE */
+#define VDP_VGP_REFACTOR_PRECISION 8 /* forward_pass: marginal covariances through the rebuilt precision (banded
+                                  Cholesky + inverse band, state_space_model.py:262) as the reference, instead of the
+                                  forward recursion S_{k+1} = A S A^T + Q riding on the mean sweep (equal to rounding) */
 
 /* LinearDrift.to_ssm (markovflow/sde/drift.py:64-116): A_ssm = I + A delta_k, b_ssm = b delta_k,
  * cholQ = chol(q delta_k).  A [B,N,D,D], b [B,N,D] -> same shapes. */

@@ -4,7 +4,7 @@
 BASELINE.md section 5 rows for configs C1-C3 (the golden fixtures made from the reference's shipped data files):
 per config, on cuda:0 -- max relative error of ELBO / marginals / sites against the fixture, device time of one
 CVI-DP site update and of one VDP sweep (CUDA events, sites after the 3 fixture updates), and the NumPy oracle's time
-for the same update on one host core.  Prints one JSON object (kept as profiles/r01_c123_results.json).
+for the same update on one host core.  Prints one JSON object (kept as profiles/r02_c123_results.json).
 """
 import glob
 import json
@@ -61,13 +61,28 @@ for path in sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "*.npz"))):
            "err_elbo": relerr(elbos, g["cvi_elbo"]),
            "err_marginals": max(relerr(eng.fx_mus[0].cpu().numpy(), g["cvi_m"]),
                                 relerr(eng.fx_covs[0].cpu().numpy(), g["cvi_S"])),
-           "err_sites_vs_posterior_naturals": site_err}
+           "err_sites_vs_posterior_naturals": site_err,
+           # UNSCALED: max |cuda - fixture| / max |fixture| per site tensor, beside the float64 floor of the route
+           # itself on this data (float64 vs 80-bit evaluation of the oracle, make_golden.py)
+           "err_sites_unscaled": {k: relerr(t[0].cpu().numpy(), g["cvi_" + k])
+                                  for k, t in (("g1", eng.g1), ("gd", eng.gd), ("gs", eng.gs))},
+           "site_floor_f64_vs_f80": {k: float(v) for k, v in zip(("g1", "gd", "gs"), g["site_floor_f64_vs_f80"])}}
     ms = device_ms(lambda: eng.site_update(0.1 * lr, 0.1 * lr))
     eng.check_status()
     row["cvi_ms_per_update"] = ms
     row["cvi_ms_per_update_cuda_graph"] = device_ms(lambda: eng.site_update_graphed(0.1 * lr, 0.1 * lr))
     eng.check_status()
     row["cvi_grid_steps_per_s"] = N / (ms * 1e-3)
+    # the trainer's inner loop on the device (vdp_cvi_optimize_sites, CUDA-graph WHILE node): 20 updates per call
+    # (tolerance 0: never stops early), wall time per update including the one read-back per call
+    eng.optimize_sites(20, 0.0, 0.1 * lr, 0.1 * lr)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(5):
+        r = eng.optimize_sites(20, 0.0, 0.1 * lr, 0.1 * lr)
+    row["cvi_ms_per_update_device_loop_wall"] = (time.perf_counter() - t0) / (5 * 20) * 1e3
+    assert int(r["n_itr"][0]) == 20
+    eng.check_status()
     vg = VgpEngine(int(g["drift_id"]), g["drift_params"], g["q"], g["time_grid"], g["obs_idx"], g["obs_y"], lik,
                    g["x0_mu"], g["x0_cov"], stabilize_system=bool(g["vgp_stabilize"]))
     vg.A += 2.0 * torch.eye(D, dtype=torch.float64, device="cuda")

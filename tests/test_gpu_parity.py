@@ -709,3 +709,40 @@ def test_cuda_graph_replay_equals_direct_calls():
         assert torch.equal(ec, ed), it
     for name in ("A", "b", "lambda_lagrange", "psi_lagrange", "q_initial_mean", "q_initial_chol", "m", "S"):
         assert torch.equal(getattr(c, name), getattr(d, name)), name
+
+
+@pytest.mark.parametrize("D,N,nseg", [(1, 3000, 0), (1, 6000, 3), (2, 1500, 0), (3, 700, 2)])
+def test_vdp_forward_recursion_equals_rebuilt_precision(vdp_cfg, D, N, nseg):
+    """VariationalMarkovGP.forward_pass on the tiled route takes the marginal covariances from the forward recursion
+    S_{k+1} = A S A^T + Q riding on the mean sweep (one fused kernel); VGP_REFACTOR_PRECISION keeps the reference's
+    route (rebuilt precision, banded Cholesky, inverse band; state_space_model.py:262).  Same marginals to rounding,
+    over sweeps, with and without stabilize_system, with several time segments per sequence."""
+    from vi_diffusion_processes_b200 import _lib
+    from vi_diffusion_processes_b200.markovflow.sde import sde as sde_mod
+    from vi_diffusion_processes_b200.vgp import VgpEngine
+    vdp_cfg(SWEEPS="tiled")
+    if nseg:
+        vdp_cfg(NSEG=nseg)
+    did, params = {1: (sde_mod.DRIFT_DW, [4.0, 1.0]), 2: (sde_mod.DRIFT_VDP, [1.0, 1.0]),
+                   3: (sde_mod.DRIFT_OU_ND, [0.5])}[D]
+    rng = np.random.default_rng(51 + D)
+    n_obs, B = 10, 2
+    grid = np.round(np.arange(N + 1) * 0.005, 6)
+    idx = np.sort(np.stack([rng.choice(np.arange(1, N + 1), n_obs, replace=False) for _ in range(B)]), axis=1)
+    y = rng.normal(size=(B, n_obs, D)) * 0.2 + 1.0
+    for stab in (False, True):
+        def run(flags):
+            e = VgpEngine(did, params, np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.ones(D), 0.01 * np.eye(D),
+                          stabilize_system=stab)
+            e.route_flags = flags
+            e.A += 2.0 * torch.eye(D, dtype=torch.float64, device="cuda")
+            e.b += 2.0
+            return e, [e.sweep(0.05, update_x0=it > 1).clone() for it in range(3)]
+        a, ea = run(0)
+        c, ec = run(_lib.VGP_REFACTOR_PRECISION)
+        a.check_status()
+        for name in ("m", "S", "A", "b", "lambda_lagrange", "psi_lagrange"):
+            ref = getattr(c, name)
+            assert (getattr(a, name) - ref).abs().max() <= 1e-11 * ref.abs().max(), (stab, name)
+        for x, r in zip(ea, ec):
+            assert (x - r).abs().max() <= 1e-11 * r.abs().max()

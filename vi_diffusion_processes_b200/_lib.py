@@ -112,6 +112,7 @@ FLAG_GH_QUADRATURE, FLAG_REFACTOR_PRECISION, FLAG_NO_FUSED_NATURALS, FLAG_SEPARA
 VGP_STABILIZE = 1
 VGP_UPDATE_X0 = 2
 VGP_GH_QUADRATURE = 4
+VGP_REFACTOR_PRECISION = 8
 
 # name -> (restype, argtypes); every symbol include/vdp_b200.h declares
 SIGNATURES = {

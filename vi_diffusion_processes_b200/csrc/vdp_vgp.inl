@@ -50,10 +50,53 @@ static int check_vgp(const vdp_vgp_problem* p, VgpWs& w) {
     return VDP_OK;
 }
 
+// forward_pass as one fused sweep (k_vgp_forward_tiled): to_ssm, means and the covariance recursion
+template <int D>
+static int run_vgp_forward_tiled(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st) {
+    using C = TileCfg<D>;
+    using Ops = FwdOps<D>;
+    constexpr int L = C::Lm;
+    constexpr int NST = 1;
+    constexpr size_t smem = vgp_forward_tiled_smem<D, C::T, L, NST>();
+    const int64_t B = p.B, N = p.N;
+    SegScratch sc(w.seg, kSegScratchBytes);
+    const SegPlan pl = plan_segments(B, N, C::T * L, true);
+    const unsigned grid = (unsigned)(B * pl.nseg);
+    const int stab = (p.flags & VDP_VGP_STABILIZE) ? 1 : 0;
+    int rc;
+    if ((rc = allow_smem(k_vgp_forward_tiled<D, C::T, L, SWEEP_FULL, NST>, smem))) return rc;
+    if (pl.nseg == 1) {
+        k_vgp_forward_tiled<D, C::T, L, SWEEP_FULL, NST><<<grid, C::T, smem, st>>>(
+            p.A, p.b, host_mat<D>(p.q), p.time_grid, stab, p.q_mean, p.q_chol, p.m, p.S, B, N, 1, pl.seg_len, nullptr,
+            nullptr, nullptr, p.status);
+        VDP_CHECK_LAUNCH();
+        return VDP_OK;
+    }
+    typename Ops::State* carry = sc.take<typename Ops::State>((size_t)B * pl.nseg);
+    typename Ops::State* init = sc.take<typename Ops::State>((size_t)B);
+    typename Ops::Elem* el = sc.take<typename Ops::Elem>((size_t)B * pl.nseg);
+    if (!el) { set_error("segment scratch too small"); return VDP_E_WORKSPACE; }
+    if ((rc = allow_smem(k_vgp_forward_tiled<D, C::T, L, SWEEP_SUMMARY, NST>, smem))) return rc;
+    k_vgp_forward_tiled<D, C::T, L, SWEEP_SUMMARY, NST><<<grid, C::T, smem, st>>>(
+        p.A, p.b, host_mat<D>(p.q), p.time_grid, stab, p.q_mean, p.q_chol, p.m, p.S, B, N, pl.nseg, pl.seg_len, nullptr,
+        init, el, p.status);
+    VDP_CHECK_LAUNCH();
+    if ((rc = launch_seg_scan<Ops>(el, init, carry, B, pl.nseg, 0, st))) return rc;
+    k_vgp_forward_tiled<D, C::T, L, SWEEP_FULL, NST><<<grid, C::T, smem, st>>>(
+        p.A, p.b, host_mat<D>(p.q), p.time_grid, stab, p.q_mean, p.q_chol, p.m, p.S, B, N, pl.nseg, pl.seg_len, carry,
+        nullptr, nullptr, p.status);
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
 // vi_sde.py:171-204
 template <int D>
 static int vgp_forward(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st) {
     const int64_t B = p.B, N = p.N;
+    // tiled route: one fused sweep (covariances by the forward recursion); VDP_VGP_REFACTOR_PRECISION / the
+    // REFACTOR_PRECISION switch keep the reference's route through the rebuilt precision
+    if (use_tiled_sweeps(B, N) && !(p.flags & VDP_VGP_REFACTOR_PRECISION) && !g_cfg.refactor_precision)
+        return run_vgp_forward_tiled<D>(p, w, st);
     k_vgp_to_ssm<D><<<grid_for(B * N, kPtBlock), kPtBlock, 0, st>>>(p.A, p.b, -1.0, host_mat<D>(p.q), p.time_grid,
                                                                     (p.flags & VDP_VGP_STABILIZE) ? 1 : 0, w.sA, w.sb,
                                                                     w.scQ, B, N, p.status);

@@ -55,6 +55,136 @@ __global__ void k_vgp_to_ssm(const double* __restrict__ A, const double* __restr
     mat_store<D>(scQ + t * DD, cQ);
 }
 
+// VariationalMarkovGP.forward_pass (vi_sde.py:171-204) in ONE forward sweep: LinearDrift(-A, b).to_ssm (+ the
+// stabilize_system clip, :184-197) evaluated in the staged tile, the marginal means m_{k+1} = A_k m_k + b_k
+// (state_space_model.py:251) and the marginal covariances by the forward recursion
+//     S_{k+1} = A_k S_k A_k^T + Q_k,   S_0 = chol P_0 chol P_0^T,   Q_k = chol(q delta_k) chol(q delta_k)^T,
+// scanned together as PairOps<AffVecOps, AffSymOps> (element of S: C = Q, G = A^T).  The reference takes the
+// covariances from the rebuilt precision (banded Cholesky + inverse band, state_space_model.py:262); the forward
+// recursion is the same quantity by another rounding route (sums of positive semi-definite terms; pinned to the oracle
+// at 1e-9 by the VDP parity tests, and to the reference's route -- VDP_VGP_REFACTOR_PRECISION -- at 1e-11).
+// 32 instead of 112 bytes per grid step (D = 1) and one sweep instead of a pointwise pass + two sweeps.
+template <int D>
+using FwdOps = PairOps<AffVecOps<D>, AffSymOps<D>>;
+
+template <int D, int T, int L, int MODE, int NSTAGE = 1>
+__global__ void __launch_bounds__(T)
+k_vgp_forward_tiled(const double* __restrict__ A, const double* __restrict__ bv, Mat<D> q,
+                    const double* __restrict__ time_grid, int stabilize, const double* __restrict__ mu0,
+                    const double* __restrict__ cholP0, double* __restrict__ m, double* __restrict__ S, int64_t B,
+                    int64_t N, int nseg, int64_t seg_len, const typename FwdOps<D>::State* __restrict__ carry_in,
+                    typename FwdOps<D>::State* __restrict__ init_out, typename FwdOps<D>::Elem* __restrict__ seg_elem,
+                    int64_t* status) {
+    constexpr int DD = D * D, TL = T * L;
+    using Ops = FwdOps<D>;
+    constexpr int SM = tile_slots(TL * DD), SV = tile_slots(TL * D);
+    constexpr int kStage = SM + SV;
+    extern __shared__ __align__(16) double smem[];
+    double* stage0 = smem + kRingHeaderDoubles;
+    typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(stage0 + NSTAGE * kStage);
+    TileRing<NSTAGE> ring;
+    ring.init(smem);
+    const int64_t b = blockIdx.x / nseg;
+    const int seg = (int)(blockIdx.x % nseg);
+    const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
+    const int ntiles = (int)((t1 - t0 + TL - 1) / TL);
+    auto issue = [&](int ti) {
+        const int64_t tk = t0 + (int64_t)ti * TL;
+        const int cnt = (int)min((int64_t)TL, t1 - tk);
+        double* base = stage0 + (ti % NSTAGE) * kStage;
+        uint64_t* bar = ring.bar + ti % NSTAGE;
+        uint32_t bytes = tile_fetch(base, A + (b * N + tk) * DD, cnt * DD, bar);
+        bytes += tile_fetch(base + SM, bv + (b * N + tk) * D, cnt * D, bar);
+        mbar_arrive_expect_tx(bar, bytes);
+    };
+    if (threadIdx.x == 0 && ntiles > 0) issue(0);
+    typename Ops::State st;
+    st.a = vec_zero<D>();
+    st.b = mat_zero<D>();
+    if (MODE == SWEEP_FULL && seg > 0) st = carry_in[b * nseg + seg];
+    typename Ops::Elem seg_tot = Ops::identity();
+    for (int ti = 0; ti < ntiles; ++ti) {
+        const int64_t tk = t0 + (int64_t)ti * TL;
+        const int cnt = (int)min((int64_t)TL, t1 - tk);
+        if (NSTAGE == 1 && ti > 0) {
+            __syncthreads();
+            if (threadIdx.x == 0) { bulk_wait_read(); issue(ti); }
+        }
+        ring.wait(ti);
+        double* base = stage0 + (ti % NSTAGE) * kStage;
+        double* sA = base + tile_off(A + (b * N + tk) * DD);       // drift A -> SSM A_k -> S_{k+1}
+        double* sb = base + SM + tile_off(bv + (b * N + tk) * D);  // drift b -> SSM b_k -> m_{k+1}
+        if (seg == 0 && tk == 0) {
+            st.a = vec_load<D>(mu0 + b * D);
+            const Mat<D> c0 = mat_load<D>(cholP0 + b * DD);
+            st.b = mmT(c0, c0);
+            if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = st;
+            if (MODE == SWEEP_FULL && threadIdx.x == 0) {
+                vec_store<D>(m + b * (N + 1) * D, st.a);
+                mat_store<D>(S + b * (N + 1) * DD, st.b);
+            }
+        }
+        const int k0 = threadIdx.x * L;
+        const int len = min(L, cnt - k0);
+        // LinearDrift(-A, b).to_ssm on this thread's chunk, in place; chunk element on the way
+        typename Ops::Elem e = Ops::identity();
+        bool ok = true;
+        for (int t = 0; t < len; ++t) {
+            const double delta = time_grid[tk + k0 + t + 1] - time_grid[tk + k0 + t];
+            Mat<D> At = delta * (-1.0 * mat_load<D>(sA + (k0 + t) * DD)) + mat_eye<D>();
+            Vec<D> bt = delta * vec_load<D>(sb + (k0 + t) * D);
+            if (stabilize) { At = vgp_fix(At, -1.0, 1.0); bt = vgp_fix(bt, -1.0, 1.0); }
+            mat_store<D>(sA + (k0 + t) * DD, At);
+            vec_store<D>(sb + (k0 + t) * D, bt);
+            const Mat<D> cQ = chol(delta * q, ok);
+            typename Ops::Elem s;
+            s.a.M = At;
+            s.a.v = bt;
+            s.b.C = mmT(cQ, cQ);
+            s.b.G = transpose(At);
+            e = Ops::combine(e, s);
+        }
+        if (!ok) report_not_pd(status, b * (N + 1) + tk + k0);
+        if (NSTAGE > 1 && threadIdx.x == 0 && ti + 1 < ntiles) {
+            bulk_wait_read();
+            issue(ti + 1);
+        }
+        typename Ops::Elem total;
+        const typename Ops::Elem excl = block_exclusive_scan<Ops, T>(e, wtot, total);
+        if (MODE != SWEEP_FULL) {
+            seg_tot = Ops::combine(seg_tot, total);
+            continue;
+        }
+        typename Ops::State cur = Ops::apply(excl, st);
+        st = Ops::apply(total, st);
+        for (int t = 0; t < len; ++t) {
+            const double delta = time_grid[tk + k0 + t + 1] - time_grid[tk + k0 + t];
+            const Mat<D> At = mat_load<D>(sA + (k0 + t) * DD);
+            const Mat<D> cQ = chol(delta * q, ok);
+            cur.a = vec_load<D>(sb + (k0 + t) * D) + mv(At, cur.a);
+            cur.b = mmT(cQ, cQ) + mm(At, mmT(cur.b, At));
+            vec_store<D>(sb + (k0 + t) * D, cur.a);
+            mat_store<D>(sA + (k0 + t) * DD, cur.b);
+        }
+        fence_async_smem();
+        __syncthreads();
+        tile_store<T>(m + (b * (N + 1) + tk + 1) * D, sb, cnt * D);
+        tile_store<T>(S + (b * (N + 1) + tk + 1) * DD, sA, cnt * DD);
+        if (threadIdx.x == 0) bulk_commit();
+    }
+    if (threadIdx.x == 0) {
+        if (MODE != SWEEP_FULL) seg_elem[b * nseg + seg] = seg_tot;
+        bulk_wait_all();
+    }
+}
+
+template <int D, int T, int L, int NSTAGE = 1>
+constexpr size_t vgp_forward_tiled_smem() {
+    return ((size_t)kRingHeaderDoubles + (size_t)NSTAGE * (tile_slots(T * L * D * D) + tile_slots(T * L * D))) *
+               sizeof(double) +
+           (T / 32) * sizeof(typename FwdOps<D>::Elem);
+}
+
 // E_sde terms and (optionally) gradients: one group of G lanes per transition (b, k), marginal of node k.
 //   term_k = 0.5 dt E_{N(m_k,S_k)} || (-A_k) x + b_k - f(x) ||^2_{q^-1}
 //   dEdm = d term / d m_k / dt, dEdS = d term / d S_k / dt       (vi_sde.py:206-225 divides by dt)
