@@ -427,6 +427,29 @@ int vdp_cvi_host_set_prior(vdp_cvi_host_ctx* ctx, int64_t B, const double* pA, c
 int vdp_cvi_host_site_update(vdp_cvi_host_ctx* ctx, const vdp_cvi_problem* problem, int64_t* status_host2);
 int vdp_cvi_host_destroy(vdp_cvi_host_ctx* ctx);
 
+/* Resident-state session of the host-buffer interface: the state of the B sequences (sites, linearised prior,
+ * posterior, marginals, carried naturals) is uploaded ONCE and stays on the device between calls, the way the
+ * reference's model object keeps its tf.Variables between trainer iterations (cvi_dp_trainer.py:71-77); per site
+ * update the host hands over that update's inputs -- the observation values, host memory -- and receives its results
+ * in host memory: ELBO terms [B] and the posterior marginals fx_mus [B,N+1,D], fx_covs [B,N+1,D,D] (each optional =
+ * NULL).  Sequences run in chunks of `chunk` on `streams` rotating streams, so the download of one chunk overlaps the
+ * kernels of the next; consecutive updates carry the naturals and keep the girsanov sites in theta.
+ *   vdp_cvi_session_create          every array pointer of `problem` addresses HOST memory; obs_idx is fixed for the
+ *                                   session (the observation times), obs_y is the initial set of values
+ *   vdp_cvi_session_site_update     obs_y_host [B,n_obs,D] (NULL: unchanged); flags: VDP_FLAG_GH_QUADRATURE,
+ *                                   VDP_FLAG_REFACTOR_PRECISION, VDP_FLAG_SEPARATE_KL_VALUE; returns when the results
+ *                                   are in the host buffers
+ *   vdp_cvi_session_download_state  the whole state back into the host arrays of `problem` (girsanov sites
+ *                                   materialised from theta); NULL pointers are skipped */
+typedef struct vdp_cvi_session vdp_cvi_session;
+int vdp_cvi_session_create(vdp_cvi_session** session, const vdp_cvi_problem* problem_host_arrays, int64_t chunk,
+                           int streams, int device);
+int vdp_cvi_session_site_update(vdp_cvi_session* session, const double* obs_y_host, double lr_data,
+                                double lr_girsanov, int flags, double* elbo_host, double* ve_host, double* kl_host,
+                                double* fx_mus_host, double* fx_covs_host, int64_t* status_host2);
+int vdp_cvi_session_download_state(vdp_cvi_session* session, const vdp_cvi_problem* problem_host_arrays);
+int vdp_cvi_session_destroy(vdp_cvi_session* session);
+
 /* ------------------------------------------------------------------------------------------------
  * VDP: VariationalMarkovGP (markovflow/models/vi_sde.py:63-482), batched over B sequences.
  *   vdp_vgp_forward_pass               forward_pass              vi_sde.py:171-204  -> m, S

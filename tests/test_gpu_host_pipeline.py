@@ -97,3 +97,41 @@ def test_host_errors():
     host.resident_prior = False
     host.site_update(0.1, 0.1)
     host.close()
+
+
+@pytest.mark.parametrize("B,chunk,streams", [(10, 4, 3), (7, 16, 1), (5, 2, 2)])
+def test_resident_session_matches_oracle_and_engine(B, chunk, streams):
+    """vdp_cvi_session_*: state uploaded once, per update observation values up and ELBO terms + marginals down.
+    Against the oracle (1e-9) and the device engine; the observation values change between updates; the state read
+    back at the end (girsanov sites materialised from theta) matches the oracle's."""
+    from vi_diffusion_processes_b200.cvi import CviEngine, CviSession
+    rng = np.random.default_rng(37)
+    N = 700
+    grid, idx, y = _problem(rng, B, N, 12, 0.005)
+    mk = lambda: CviEngine(S.DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y[..., None], [[0.1]], [1.0], [[1e-2]])
+    ses = CviSession(mk(), chunk=chunk, streams=streams)
+    dev_eng = mk()
+    ref = scalar_d1.BatchedCVISitesSDE1D(S.DRIFT_DW, [4.0, 1.0], 1.0, grid, idx, y, 0.1, 1.0, 1e-2)
+    up, down = ses.bytes_per_update()
+    assert up == B * 12 * 8 and down == (3 * B + 2 * B * (N + 1)) * 8
+    for it in range(4):
+        if it == 2:          # new observation values for this update
+            y = y + 0.05 * rng.normal(size=y.shape)
+            ref.obs_y = y.copy()
+            dev_eng.obs_y.copy_(torch.as_tensor(y[..., None]))
+            ses.host["obs_y"].copy_(torch.as_tensor(y[..., None]))
+        e = ses.site_update(0.5, 0.5)
+        d = dev_eng.site_update(0.5, 0.5)
+        r = ref.site_update(0.5, 0.5)
+        assert rel(e, r) < TOL and rel(e, d) < 1e-11
+        assert rel(ses.host["fx_mus"][..., 0], ref.fx_mus) < TOL and rel(ses.host["fx_covs"][..., 0, 0], ref.fx_covs) < TOL
+    h = ses.download_state()
+    th = scalar_d1.ssm_to_naturals(ref.p["A"], ref.p["b"], ref.p["cQ"], ref.p["mu0"], ref.p["cP0"])
+    for got, want, t in ((h["g1"][..., 0], ref.g1, th[0]), (h["gd"][..., 0, 0], ref.gd, th[1]),
+                         (h["gs"][..., 0, 0], ref.gs, th[2])):
+        scale = max(np.abs(want).max(), 1e-3 * np.abs(t + want).max())
+        assert rel(got, want, scale=scale) < TOL
+    assert rel(h["d1"][..., 0], ref.d1) < TOL and rel(h["d2"][..., 0, 0], ref.d2) < TOL
+    for k in ("qA", "qb", "qcholQ"):
+        assert rel(h[k], getattr(dev_eng, k)) < 1e-10, k
+    ses.close()

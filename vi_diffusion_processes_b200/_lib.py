@@ -175,6 +175,10 @@ SIGNATURES = {
     "vdp_cvi_host_set_prior": (C.c_int, [vp, i64, vp, vp, vp, vp, vp]),
     "vdp_cvi_host_site_update": (C.c_int, [vp, C.POINTER(CviProblem), c_i64p]),
     "vdp_cvi_host_destroy": (C.c_int, [vp]),
+    "vdp_cvi_session_create": (C.c_int, [C.POINTER(vp), C.POINTER(CviProblem), i64, C.c_int, C.c_int]),
+    "vdp_cvi_session_site_update": (C.c_int, [vp, vp, C.c_double, C.c_double, C.c_int, vp, vp, vp, vp, vp, c_i64p]),
+    "vdp_cvi_session_download_state": (C.c_int, [vp, C.POINTER(CviProblem)]),
+    "vdp_cvi_session_destroy": (C.c_int, [vp]),
     "vdp_linear_drift_to_ssm": (C.c_int, [vp, vp, c_dp, vp, vp, vp, vp, i64, i64, C.c_int, vp, vp]),
     "vdp_sq_drift_difference_workspace": (C.c_size_t, [i64, i64, C.c_int]),
     "vdp_sq_drift_difference": (C.c_int, [C.c_int, c_dp, c_dp, C.c_double, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t,

@@ -259,3 +259,196 @@ int vdp_cvi_host_site_update(vdp_cvi_host_ctx* c, const vdp_cvi_problem* hp, int
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// Resident-state session: the state of the B sequences (girsanov and data sites, linearised prior, posterior,
+// marginals, carried naturals) stays on the device between calls, as the reference's model object keeps its
+// tf.Variables between trainer iterations; per site update the host supplies that update's inputs -- the observations
+// -- and receives its results: ELBO terms and the posterior marginals (what cvi_dp_trainer.py:75-77 reads every
+// iteration for ELBO / NLPD / RMSE).  Sequences are processed in chunks on rotating streams so that the download of
+// one chunk's marginals overlaps the kernels of the next.
+struct vdp_cvi_session {
+    vdp_cvi_problem dev;          // device-resident problem of all B sequences (pointers into `pool`)
+    int64_t chunk = 0;
+    int device = 0, nstreams = 0, updates = 0;
+    char* pool = nullptr;
+    cudaStream_t st[4] = {nullptr, nullptr, nullptr, nullptr};
+    size_t ws_chunk = 0;          // workspace bytes of one chunk (each chunk keeps its own: carried naturals)
+};
+
+extern "C" {
+
+int vdp_cvi_session_destroy(vdp_cvi_session* s) {
+    if (!s) return VDP_OK;
+    cudaSetDevice(s->device);
+    for (int i = 0; i < s->nstreams; ++i)
+        if (s->st[i]) { cudaStreamSynchronize(s->st[i]); cudaStreamDestroy(s->st[i]); }
+    if (s->pool) cudaFree(s->pool);
+    delete s;
+    return VDP_OK;
+}
+
+int vdp_cvi_session_create(vdp_cvi_session** out, const vdp_cvi_problem* hp, int64_t chunk, int streams, int device) {
+    VDP_REQUIRE(out && hp && chunk >= 1 && streams >= 1 && streams <= 4, "out, problem, chunk, streams (1..4)");
+    VDP_REQUIRE(hp->B >= 1 && hp->N >= 1 && hp->D >= 1 && hp->D <= 3 && hp->n_obs >= 0, "B, N, D, n_obs");
+    VDP_REQUIRE(hp->time_grid && hp->pA && hp->pb && hp->pcholQ && hp->pmu0 && hp->pcholP0 && hp->g1 && hp->gd &&
+                    hp->gs && hp->fx_mus && hp->fx_covs, "host state pointers");
+    VDP_REQUIRE(hp->n_obs == 0 || (hp->d1 && hp->d2 && hp->obs_idx && hp->obs_y), "host data-site pointers");
+    VDP_CHECK_CUDA(cudaSetDevice(device));
+    vdp_cvi_session* s = new vdp_cvi_session();
+    s->device = device;
+    s->chunk = std::min<int64_t>(chunk, hp->B);
+    s->nstreams = streams;
+    s->dev = *hp;
+    const int64_t B = hp->B, N = hp->N, no = hp->n_obs;
+    const size_t d = hp->D, dd = d * d, b = (size_t)B, S = sizeof(double);
+    const int64_t nchunks = (B + s->chunk - 1) / s->chunk;
+    s->ws_chunk = (vdp_cvi_workspace(s->chunk, N, hp->D, no) + 255) & ~size_t(255);
+    const size_t total = padded(N + 1) + 256 + 2 * (2 * padded(b * N * dd) + padded(b * N * d) + padded(b * d) +
+                                                    padded(b * dd))                          // prior, posterior
+                         + padded(b * (N + 1) * d) + padded(b * (N + 1) * dd) + padded(b * N * dd)   // sites
+                         + padded(b * no * d + 1) + padded(b * no * dd + 1) + padded(b * no + 1) + padded(b * no * d + 1)
+                         + padded(b * (N + 1) * d) + padded(b * (N + 1) * dd) + 3 * padded(b) + (size_t)nchunks * s->ws_chunk;
+    if (cudaMalloc((void**)&s->pool, total) != cudaSuccess) {
+        cudaGetLastError();
+        set_error("vdp_cvi_session_create: cannot allocate %zu device bytes", total);
+        delete s;
+        return VDP_E_CUDA;
+    }
+    Arena ar(s->pool, total);
+    vdp_cvi_problem& p = s->dev;
+    double* tg = ar.take(N + 1);
+    p.time_grid = tg;
+    p.status = (int64_t*)ar.take_bytes(256);
+    double *pA = ar.take(b * N * dd), *pb = ar.take(b * N * d), *pQ = ar.take(b * N * dd), *pm = ar.take(b * d),
+           *pP = ar.take(b * dd);
+    p.pA = pA; p.pb = pb; p.pcholQ = pQ; p.pmu0 = pm; p.pcholP0 = pP;
+    p.qA = ar.take(b * N * dd); p.qb = ar.take(b * N * d); p.qcholQ = ar.take(b * N * dd); p.qmu0 = ar.take(b * d);
+    p.qcholP0 = ar.take(b * dd);
+    p.g1 = ar.take(b * (N + 1) * d); p.gd = ar.take(b * (N + 1) * dd); p.gs = ar.take(b * N * dd);
+    p.d1 = ar.take(b * no * d + 1); p.d2 = ar.take(b * no * dd + 1);
+    int64_t* oi = (int64_t*)ar.take(b * no + 1);
+    double* oy = ar.take(b * no * d + 1);
+    p.obs_idx = oi; p.obs_y = oy;
+    p.fx_mus = ar.take(b * (N + 1) * d); p.fx_covs = ar.take(b * (N + 1) * dd);
+    p.elbo = ar.take(b); p.ve = ar.take(b); p.kl = ar.take(b);
+    p.workspace = ar.take_bytes((size_t)nchunks * s->ws_chunk);
+    p.workspace_bytes = s->ws_chunk;
+    p.lr_data_dev = p.lr_girsanov_dev = nullptr;
+    p.active_dev = nullptr;
+    bool ok = p.workspace != nullptr;
+    for (int i = 0; i < streams && ok; ++i) ok = cudaStreamCreateWithFlags(&s->st[i], cudaStreamNonBlocking) == cudaSuccess;
+    if (!ok) { set_error("vdp_cvi_session_create: setup failed"); vdp_cvi_session_destroy(s); return VDP_E_CUDA; }
+    cudaStream_t st = s->st[0];
+    cudaError_t e = cudaMemsetAsync(p.status, 0, 2 * sizeof(int64_t), st);
+    auto up = [&](void* dst, const void* src, size_t bytes) { if (e == cudaSuccess) e = h2d(dst, src, bytes, st); };
+    up(tg, hp->time_grid, (N + 1) * S);
+    up(pA, hp->pA, b * N * dd * S); up(pb, hp->pb, b * N * d * S); up(pQ, hp->pcholQ, b * N * dd * S);
+    up(pm, hp->pmu0, b * d * S); up(pP, hp->pcholP0, b * dd * S);
+    up(p.g1, hp->g1, b * (N + 1) * d * S); up(p.gd, hp->gd, b * (N + 1) * dd * S); up(p.gs, hp->gs, b * N * dd * S);
+    up(p.fx_mus, hp->fx_mus, b * (N + 1) * d * S); up(p.fx_covs, hp->fx_covs, b * (N + 1) * dd * S);
+    if (no > 0) {
+        up(p.d1, hp->d1, b * no * d * S); up(p.d2, hp->d2, b * no * dd * S);
+        up(oi, hp->obs_idx, b * no * sizeof(int64_t)); up(oy, hp->obs_y, b * no * d * S);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+        set_error("vdp_cvi_session_create: upload failed: %s", cudaGetErrorString(e));
+        vdp_cvi_session_destroy(s);
+        return VDP_E_CUDA;
+    }
+    *out = s;
+    return VDP_OK;
+}
+
+// the view of sequences [b0, b0 + nb) of the resident problem
+static vdp_cvi_problem session_chunk(const vdp_cvi_session* s, int64_t b0, int64_t nb, int64_t ci) {
+    vdp_cvi_problem p = s->dev;
+    const size_t N = (size_t)p.N, d = (size_t)p.D, dd = d * d, no = (size_t)p.n_obs, o = (size_t)b0;
+    p.B = nb;
+    p.pA += o * N * dd; p.pb += o * N * d; p.pcholQ += o * N * dd; p.pmu0 += o * d; p.pcholP0 += o * dd;
+    p.qA += o * N * dd; p.qb += o * N * d; p.qcholQ += o * N * dd; p.qmu0 += o * d; p.qcholP0 += o * dd;
+    p.g1 += o * (N + 1) * d; p.gd += o * (N + 1) * dd; p.gs += o * N * dd;
+    p.d1 += o * no * d; p.d2 += o * no * dd; p.obs_idx += o * no; p.obs_y += o * no * d;
+    p.fx_mus += o * (N + 1) * d; p.fx_covs += o * (N + 1) * dd;
+    p.elbo += o; p.ve += o; p.kl += o;
+    p.workspace = (char*)s->dev.workspace + (size_t)ci * s->ws_chunk;
+    p.workspace_bytes = s->ws_chunk;
+    return p;
+}
+
+int vdp_cvi_session_site_update(vdp_cvi_session* s, const double* obs_y_host, double lr_data, double lr_girsanov,
+                                int flags, double* elbo_host, double* ve_host, double* kl_host, double* fx_mus_host,
+                                double* fx_covs_host, int64_t* status_host2) {
+    VDP_REQUIRE(s != nullptr, "session");
+    VDP_CHECK_CUDA(cudaSetDevice(s->device));
+    const int64_t B = s->dev.B, N = s->dev.N, no = s->dev.n_obs;
+    const size_t d = (size_t)s->dev.D, dd = d * d, S = sizeof(double);
+    // from the second update on every chunk's workspace holds the naturals of its previous update: carried, with the
+    // girsanov sites held in theta (vdp_cvi_session_download_state materialises them)
+    int fl = flags & (VDP_FLAG_GH_QUADRATURE | VDP_FLAG_REFACTOR_PRECISION | VDP_FLAG_SEPARATE_KL_VALUE);
+    if (s->updates > 0) fl |= VDP_FLAG_NATURALS_CARRIED | VDP_FLAG_SITES_IN_NATURALS;
+    int rc = VDP_OK;
+    int64_t ci = 0;
+    for (int64_t b0 = 0; b0 < B && rc == VDP_OK; b0 += s->chunk, ++ci) {
+        const int64_t nb = std::min<int64_t>(s->chunk, B - b0);
+        cudaStream_t st = s->st[ci % s->nstreams];
+        vdp_cvi_problem p = session_chunk(s, b0, nb, ci);
+        p.lr_data = lr_data;
+        p.lr_girsanov = lr_girsanov;
+        p.flags = fl;
+        cudaError_t e = cudaSuccess;
+        if (obs_y_host && no > 0)
+            e = h2d((void*)p.obs_y, obs_y_host + (size_t)b0 * no * d, (size_t)nb * no * d * S, st);
+        if (e != cudaSuccess) { set_error("H2D copy: %s", cudaGetErrorString(e)); rc = VDP_E_CUDA; break; }
+        if ((rc = vdp_cvi_site_update(&p, st))) break;
+        const size_t o = (size_t)b0;
+        if (e == cudaSuccess && elbo_host) e = d2h(elbo_host + o, p.elbo, nb * S, st);
+        if (e == cudaSuccess && ve_host) e = d2h(ve_host + o, p.ve, nb * S, st);
+        if (e == cudaSuccess && kl_host) e = d2h(kl_host + o, p.kl, nb * S, st);
+        if (e == cudaSuccess && fx_mus_host) e = d2h(fx_mus_host + o * (N + 1) * d, p.fx_mus, nb * (N + 1) * d * S, st);
+        if (e == cudaSuccess && fx_covs_host) e = d2h(fx_covs_host + o * (N + 1) * dd, p.fx_covs, nb * (N + 1) * dd * S, st);
+        if (e != cudaSuccess) { set_error("D2H copy: %s", cudaGetErrorString(e)); rc = VDP_E_CUDA; }
+    }
+    for (int i = 0; i < s->nstreams; ++i)
+        if (cudaStreamSynchronize(s->st[i]) != cudaSuccess && rc == VDP_OK) {
+            set_error("stream synchronize: %s", cudaGetErrorString(cudaGetLastError()));
+            rc = VDP_E_CUDA;
+        }
+    if (rc == VDP_OK) s->updates += 1;
+    if (rc == VDP_OK && status_host2)
+        VDP_CHECK_CUDA(cudaMemcpy(status_host2, s->dev.status, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost));
+    return rc;
+}
+
+int vdp_cvi_session_download_state(vdp_cvi_session* s, const vdp_cvi_problem* hp) {
+    VDP_REQUIRE(s && hp && hp->B == s->dev.B && hp->N == s->dev.N && hp->D == s->dev.D && hp->n_obs == s->dev.n_obs,
+                "session, problem of the session's shape (host pointers)");
+    VDP_CHECK_CUDA(cudaSetDevice(s->device));
+    const int64_t B = s->dev.B, N = s->dev.N, no = s->dev.n_obs;
+    const size_t d = (size_t)s->dev.D, dd = d * d, b = (size_t)B, S = sizeof(double);
+    cudaStream_t st = s->st[0];
+    int rc = VDP_OK;
+    if (s->updates > 1) {      // the sites live in theta: g = theta - nat(p) - scatter(data sites), chunk by chunk
+        int64_t ci = 0;
+        for (int64_t b0 = 0; b0 < B && rc == VDP_OK; b0 += s->chunk, ++ci) {
+            vdp_cvi_problem p = session_chunk(s, b0, std::min<int64_t>(s->chunk, B - b0), ci);
+            rc = vdp_cvi_materialize_sites(&p, st);
+        }
+        if (rc) return rc;
+    }
+    const vdp_cvi_problem& p = s->dev;
+    cudaError_t e = cudaSuccess;
+    auto down = [&](void* dst, const void* src, size_t bytes) { if (e == cudaSuccess && dst) e = d2h(dst, src, bytes, st); };
+    down(hp->g1, p.g1, b * (N + 1) * d * S); down(hp->gd, p.gd, b * (N + 1) * dd * S); down(hp->gs, p.gs, b * N * dd * S);
+    if (no > 0) { down(hp->d1, p.d1, b * no * d * S); down(hp->d2, p.d2, b * no * dd * S); }
+    down(hp->fx_mus, p.fx_mus, b * (N + 1) * d * S); down(hp->fx_covs, p.fx_covs, b * (N + 1) * dd * S);
+    down(hp->qA, p.qA, b * N * dd * S); down(hp->qb, p.qb, b * N * d * S); down(hp->qcholQ, p.qcholQ, b * N * dd * S);
+    down(hp->qmu0, p.qmu0, b * d * S); down(hp->qcholP0, p.qcholP0, b * dd * S);
+    down(hp->elbo, p.elbo, b * S); down(hp->ve, p.ve, b * S); down(hp->kl, p.kl, b * S);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { set_error("D2H copy: %s", cudaGetErrorString(e)); return VDP_E_CUDA; }
+    return VDP_OK;
+}
+
+}  // extern "C"

@@ -440,3 +440,66 @@ class CviHostEngine:
             self.close()
         except Exception:
             pass
+
+
+class CviSession:
+    """
+    Resident-state session of the host-buffer interface (``vdp_cvi_session_*``): the state is uploaded once from
+    pinned host tensors and stays on the device; every :meth:`site_update` takes that update's observation values from
+    host memory and writes the ELBO terms and the posterior marginals back to host memory.  ``host`` maps the field
+    names of ``vdp_cvi_problem`` to the pinned CPU tensors (``host["fx_mus"]`` etc. receive the results).
+    """
+
+    FIELDS = CviHostEngine.STATE + CviHostEngine.PRIOR + CviHostEngine.CONST + CviHostEngine.OUT
+
+    def __init__(self, eng: CviEngine, chunk=1024, streams=3):
+        self._eng = eng
+        self.B, self.N, self.D, self.n_obs = eng.B, eng.N, eng.D, eng.n_obs
+        self.host = {k: getattr(eng, k).detach().to("cpu").contiguous().pin_memory() for k in self.FIELDS}
+        p = self._host_problem()
+        self._s = C.c_void_p()
+        dev = eng.device.index if eng.device.index is not None else torch.cuda.current_device()
+        check(_lib.load().vdp_cvi_session_create(C.byref(self._s), C.byref(p), int(chunk), int(streams), dev),
+              "vdp_cvi_session_create")
+
+    def _host_problem(self):
+        p = self._eng._problem(0.0, 0.0)
+        for k, t in self.host.items():
+            setattr(p, k, t.data_ptr())
+        p.workspace, p.workspace_bytes, p.status = None, 0, None
+        return p
+
+    def bytes_per_update(self):
+        """(host->device, device->host) bytes one site_update moves: observation values up; ELBO terms and marginals
+        down."""
+        h = self.host
+        nb = lambda names: sum(h[k].numel() * h[k].element_size() for k in names)
+        return nb(["obs_y"]), nb(["elbo", "ve", "kl", "fx_mus", "fx_covs"])
+
+    def site_update(self, lr_data, lr_girsanov, flags=0, obs_y=None):
+        h = self.host
+        y = h["obs_y"] if obs_y is None else obs_y
+        st = (C.c_int64 * 2)()
+        check(_lib.load().vdp_cvi_session_site_update(
+            self._s, C.c_void_p(y.data_ptr()), float(lr_data), float(lr_girsanov), int(flags),
+            C.c_void_p(h["elbo"].data_ptr()), C.c_void_p(h["ve"].data_ptr()), C.c_void_p(h["kl"].data_ptr()),
+            C.c_void_p(h["fx_mus"].data_ptr()), C.c_void_p(h["fx_covs"].data_ptr()), st), "vdp_cvi_session_site_update")
+        if st[0] != 0:
+            raise _lib.VdpError(f"non positive-definite block (code {st[0]}, grid index {st[1]})")
+        return h["elbo"]
+
+    def download_state(self):
+        p = self._host_problem()
+        check(_lib.load().vdp_cvi_session_download_state(self._s, C.byref(p)), "vdp_cvi_session_download_state")
+        return self.host
+
+    def close(self):
+        if self._s:
+            _lib.load().vdp_cvi_session_destroy(self._s)
+            self._s = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
