@@ -12,8 +12,13 @@ path; per-GPU work is fixed (B = 4096 per GPU) so scaling is "weak".  Timing sta
 updates.
 
 value  = grid steps of all ranks / max-over-ranks device time, state resident in HBM.
-e2e    = same metric with the site/posterior/prior state living in pinned HOST memory: every step copies
-         the inputs host->device, runs the update through the C ABI and copies the results back.
+e2e    = same metric through the host-buffer C ABI with the copies inside the timed region: resident-state session
+         (vdp_cvi_session_*): per step the observation values go host->device and the ELBO terms + posterior
+         marginals device->host.  e2e_full_state_roundtrip = every array of the problem both ways every step
+         (vdp_cvi_host_site_update, round 1's e2e).  Both come with the box's measured raw copy ceiling.
+c5     = BASELINE config 5 (one sequence, 10^7 grid steps, D = 3) with the chain sharded in time over the ranks and
+         the scan carries / halos exchanged over NCCL (strong scaling); `--workload c5` prints it as its own line.
+parity_check = first 4 sequences of the timed state against the CPU oracle; the run exits non-zero above 1e-9.
 """
 from __future__ import annotations
 
