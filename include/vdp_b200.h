@@ -52,7 +52,7 @@ enum {
 int vdp_version(void);
 /* Process-wide tuning switches: "SWEEPS" (0 heuristic, 1 thread per sequence, 2 parallel-in-time tiles), "NSEG" (time
  * segments per sequence of the tiled sweeps, 0 = heuristic), and the route switches "GH_QUADRATURE",
- * "REFACTOR_PRECISION", "NO_CARRIED_NATURALS", "NO_FUSED_NATURALS", "SEPARATE_KL_VALUE" (0 / 1; the per-call
+ * "REFACTOR_PRECISION", "NO_CARRIED_NATURALS", "NO_FUSED_NATURALS", "SEPARATE_KL_VALUE", "NO_FUSED_FORWARD" (0 / 1; the per-call
  * VDP_FLAG_* of the same name are the re-entrant way to choose a route).  Their defaults are read from the
  * environment variables VDP_<KEY> once, when the library is loaded; no entry point reads the environment. */
 int vdp_config_set(const char* key, int value);
@@ -293,6 +293,8 @@ typedef struct vdp_cvi_problem {
                                            reference does (four sweeps per rebuild instead of three) */
 #define VDP_FLAG_NO_FUSED_NATURALS 256  /* rebuild the naturals from the sites after the girsanov update */
 #define VDP_FLAG_SEPARATE_KL_VALUE 512  /* KL terms of classic_elbo in their own pass, not inside the mean sweep */
+#define VDP_FLAG_NO_FUSED_FORWARD 1024  /* mean sweep, KL gradient / site update and the factorisation of the next
+                                          * rebuild as three kernels instead of the one forward pass (D = 1) */
 
 size_t vdp_cvi_workspace(int64_t B, int64_t N, int D, int64_t n_obs);
 int vdp_cvi_site_update(const vdp_cvi_problem* problem_host, void* stream);

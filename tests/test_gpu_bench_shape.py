@@ -4,7 +4,8 @@ not parity-tested"): N = 10^4 grid steps, dt = 0.005, 50 observations per sequen
 bench.py generates -- three site updates with a re-linearisation, CUDA (C ABI) against the C/OpenMP restatement of the
 oracle (oracle/cvi_d1.c, pinned to the NumPy oracle by tests/test_oracle_c_port.py).  Run on the default route
 (closed-form Gaussian moments + carried naturals) and on the 20-node Gauss-Hermite loops, and for a drift that is not a
-polynomial (Benes), which always takes the loops.
+polynomial (Benes), which always takes the loops; "fused_forward" forces one time segment per sequence, which is what
+the 4096 sequences of the bench get and what puts the update on the one-kernel forward pass.
 
 Site tensors: the assertion uses the same rule as tests/test_gpu_parity.py::test_site_update_d1 (relative to
 max(|site|, 1e-3 |theta_q|), bar 1e-9 or 3 x the float64 floor of the route); the UNSCALED max-relative errors are
@@ -46,13 +47,15 @@ def _record(name, row):
     json.dump(data, open(path, "w"), indent=1, sort_keys=True)
 
 
-@pytest.mark.parametrize("route", ["default", "gh20_loops", "benes"])
+@pytest.mark.parametrize("route", ["default", "fused_forward", "gh20_loops", "benes"])
 def test_c4_shape_three_updates_with_relinearisation(route, vdp_cfg):
     import bench
     from vi_diffusion_processes_b200.cvi import CviEngine
     vdp_cfg(SWEEPS=None, NSEG=None, GH_QUADRATURE=None)
     if route == "gh20_loops":
         vdp_cfg(GH_QUADRATURE="1")
+    if route == "fused_forward":      # one segment per sequence, as at the bench's 4096 sequences: the one-kernel
+        vdp_cfg(NSEG="1")             # forward pass (csrc/fwd_fused.cuh) takes the second and third update
     drift, params = (S.DRIFT_BENES, [1.0]) if route == "benes" else (S.DRIFT_DW, bench.DW_PARAMS)
     grid, idx, y = bench.make_problem(B, N, seed=4096)          # the generator of the bench workload
     assert grid.shape[0] == N + 1 and idx.shape == (B, bench.N_OBS)

@@ -109,6 +109,7 @@ FLAG_SKIP_DATA_UPDATE, FLAG_SKIP_ELBO, FLAG_SKIP_GIRSANOV, FLAG_POSTERIOR_SSM_ON
 FLAG_NATURALS_CARRIED = 16
 FLAG_SITES_IN_NATURALS = 32
 FLAG_GH_QUADRATURE, FLAG_REFACTOR_PRECISION, FLAG_NO_FUSED_NATURALS, FLAG_SEPARATE_KL_VALUE = 64, 128, 256, 512
+FLAG_NO_FUSED_FORWARD = 1024
 VGP_STABILIZE = 1
 VGP_UPDATE_X0 = 2
 VGP_GH_QUADRATURE = 4
@@ -227,7 +228,7 @@ def load():
 
 
 CONFIG_KEYS = ("SWEEPS", "NSEG", "GH_QUADRATURE", "REFACTOR_PRECISION", "NO_CARRIED_NATURALS", "NO_FUSED_NATURALS",
-               "SEPARATE_KL_VALUE")
+               "SEPARATE_KL_VALUE", "NO_FUSED_FORWARD")
 _SWEEPS = {None: 0, "auto": 0, "seq": 1, "tiled": 2}
 
 

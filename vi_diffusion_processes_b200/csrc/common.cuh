@@ -24,6 +24,7 @@ struct Config {
     int refactor_precision = 0;     // marginals through a second factorisation, as the reference (four sweeps)
     int no_carried_naturals = 0;    // ignore VDP_FLAG_NATURALS_CARRIED
     int no_fused_naturals = 0;      // rebuild the naturals from the sites after the girsanov update
+    int no_fused_forward = 0;       // mean sweep, KL gradient and the next factorisation as three kernels instead of one
     int separate_kl_value = 0;      // KL terms of classic_elbo in their own pass instead of inside the mean sweep
 };
 extern Config g_cfg;

@@ -29,6 +29,39 @@ struct KlTermOut {
     Mat<D> ges;           // d term / d eta_s[k]
 };
 
+// Gradient of one scalar transition term for a polynomial drift (closed-form moments), from the transition A_k, the
+// means and variances of its two grid points and 1 / S_k:  d term / d (m_k, S_k) -> (Lgm, LgS), d term / d (m_{k+1},
+// S_{k+1}) -> (Rgm, RgS), d term / d eta_s[k] -> gC  (the adjoint chain of kl_term_scalar below, same statements).
+template <int DRIFT>
+__device__ __forceinline__ void kl_grad_closed_core(const DriftParams& P, double Qp, double dt, double A, double iSk,
+                                                    double mk, double mn, double Sk, double Sn, double& Lgm,
+                                                    double& LgS, double& Rgm, double& RgS, double& gC, bool& ok) {
+    const double b = mn - A * mk;
+    const double Qc = Sn - A * (Sk * A);
+    if (!(Qc > 0.0) || !(Qp > 0.0)) ok = false;
+    const double iQc = rcp_fast(Qc), Qpinv = rcp_fast(Qp);
+    const typename DriftStep1<DRIFT>::K kst = DriftStep1<DRIFT>::prepare(P, dt, A, b);
+    double c0, c1, c2, c3;
+    DriftStep1<DRIFT>::taylor(kst, mk, c0, c1, c2, c3);
+    CubicMoments cm;
+    cm.template eval<true>(c0, c1, c2, c3, Sk);
+    const double gb = -Qpinv * cm.Ed;
+    double gA = -Qpinv * fma(mk, cm.Ed, cm.Ede);
+    Lgm = Qpinv * cm.Ejd;
+    LgS = 0.5 * ((Qpinv * cm.Ejde) * iSk);             // adjoint of chol(S_k)
+    const double gQc = 0.5 * (Qpinv - iQc);
+    Rgm = gb;                                          // b = m_{k+1} - A m_k
+    gA -= gb * mk;
+    Lgm -= A * gb;
+    gA -= 2.0 * (gQc * (A * Sk));                      // Qc = S_{k+1} - A S_k A
+    LgS -= A * (gQc * A);
+    gC = gA * iSk;                                     // A = C / S_k
+    LgS -= gC * A;
+    Lgm -= gC * mn;                                    // C = eta_s - m_k m_{k+1}
+    Rgm -= gC * mk;
+    RgS = gQc;
+}
+
 // D = 1, one thread per transition: the same term with every block a scalar.  Per-step invariants are
 // hoisted out of the node loop, pi^(-1/2) and sqrt(2) are factored out of the sums, and each of the
 // three divisors (chol S_k, chol Q_c, chol Q_p) is inverted once (3 sqrt + 3 div + 1 log per step
@@ -42,6 +75,24 @@ __device__ __forceinline__ void kl_term_scalar(const DriftParams& P, double Qp, 
     const double Sn = edn - mn * mn;
     const double Cs = esk - mk * mn;
     if (!(Sk > 0.0)) ok = false;
+    if constexpr (CLOSED) {
+        if (!want_value) {
+            // Gradient only, closed-form moments: every divisor enters as a reciprocal of S_k, Q_c or Q_p (the
+            // Cholesky factors only serve the node placement of the quadrature loops and the log-determinants of the
+            // value), so three reciprocals replace the three coupled square-root / reciprocal-square-root
+            // evaluations (~27 float64 instructions per grid point less; same values to rounding).
+            const double iSk = rcp_fast(Sk);
+            double Lgm, LgS, Rgm, gQc, gC;
+            kl_grad_closed_core<DRIFT>(P, Qp, dt, Cs * iSk, iSk, mk, mn, Sk, Sn, Lgm, LgS, Rgm, gQc, gC, ok);
+            out.value = 0.0;
+            out.ges(0, 0) = gC;
+            out.left.gm(0) = Lgm;
+            out.left.gS(0, 0) = LgS;
+            out.right.gm(0) = Rgm;
+            out.right.gS(0, 0) = gQc;
+            return;
+        }
+    }
     double LS, iLS;
     sqrt_rsqrt_fast(Sk, LS, iLS);
     const double A = (Cs * iLS) * iLS;
@@ -335,7 +386,9 @@ struct KlHandoff { double gm[D]; double gS[D * D]; };
 template <int G> struct KlBounds {
     static constexpr int threads = (G == 1) ? 128 : 256, blocks = (G == 1) ? VDP_KL_MINBLOCKS : VDP_KLG_MINBLOCKS;
 };
-template <int DRIFT, int D, int H, int G, bool CLOSED = false>
+// UPDT >= 0: the update mode is a compile-time constant (prunes the other modes' code from the scalar kernel)
+// NOVAL: the caller passes terms == nullptr (gradient only), known at compile time
+template <int DRIFT, int D, int H, int G, bool CLOSED = false, int UPDT = -1, bool NOVAL = false>
 __global__ void __launch_bounds__(KlBounds<G>::threads, KlBounds<G>::blocks) k_kl_grad(DriftParams P, Mat<D> q, double dt, double pi_factor,
                           const double* __restrict__ time_grid, Vec<D> x0_mu, Mat<D> x0_cov,
                           const double* __restrict__ Aq, const double* __restrict__ m,
@@ -343,6 +396,8 @@ __global__ void __launch_bounds__(KlBounds<G>::threads, KlBounds<G>::blocks) k_k
                           double* __restrict__ gd, double* __restrict__ gs, int upd, double lr,
                           const double* __restrict__ sc1, const double* __restrict__ scd, int64_t B, int64_t N,
                           int64_t* status, int64_t node0 = 0, int64_t node1 = -1, KlNaturalsOut nat = KlNaturalsOut()) {
+    if (UPDT >= 0) upd = UPDT;
+    if (NOVAL) terms = nullptr;
     // nodes [node0, node1) of the flat (b, k) index are processed (default: all); a rank of the sharded
     // quadrature passes its own range, the halo group recomputes the term that straddles the range start
     extern __shared__ unsigned char smem_raw[];

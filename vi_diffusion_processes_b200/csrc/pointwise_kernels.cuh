@@ -175,6 +175,30 @@ __global__ void k_patch_naturals_delta(const double* __restrict__ d1, const doub
     mat_store<D>(scd + i * DD, s2);
 }
 
+// The data-site part of the girsanov update when the sites are held in theta: the update g += lr (scatter(data sites)
+// - dKL/d eta) (variational_cvi_sde.py:286-292) moves theta by lr * scatter(data sites) at the observed grid points --
+// applied here, one thread per observation entry (the first of several on one grid point does the work, from the
+// dense copy's summed entry) -- and by -lr * dKL/d eta everywhere, which the forward pass that follows applies.
+template <int D>
+__global__ void k_add_data_step(const int64_t* __restrict__ obs_idx, const double* __restrict__ sc1,
+                                const double* __restrict__ scd, double* __restrict__ th1, double* __restrict__ thd,
+                                double lr, const double* __restrict__ lr_dev, const int32_t* __restrict__ active,
+                                int64_t B, int64_t N, int64_t n_obs) {
+    const int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (o >= B * n_obs) return;
+    constexpr int DD = D * D;
+    const int64_t b = o / n_obs, j = o - b * n_obs;
+    const int64_t k = obs_idx[o];
+    if (k < 0 || k > N) return;
+    const int64_t* row = obs_idx + b * n_obs;
+    for (int64_t jj = 0; jj < j; ++jj)
+        if (row[jj] == k) return;
+    if (lr_dev) lr = (!active || active[b]) ? lr_dev[b] : 0.0;
+    const int64_t i = b * (N + 1) + k;
+    vec_store<D>(th1 + i * D, vec_load<D>(th1 + i * D) + lr * vec_load<D>(sc1 + i * D));
+    mat_store<D>(thd + i * DD, mat_load<D>(thd + i * DD) + lr * mat_load<D>(scd + i * DD));
+}
+
 // girsanov sites from the natural parameters they are part of (variational_cvi_sde.py:161-174 read backwards):
 //   g = theta - nat(p) - scatter(data sites),   sub-diagonal: g_s = theta_s - nat_s(p)
 // sc1 / scd = the dense copy of the data sites (zero away from the observations).

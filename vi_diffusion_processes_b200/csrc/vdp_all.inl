@@ -32,6 +32,7 @@
 #include "prior_grad_kernels.cuh"
 #include "quad_core.cuh"
 #include "tile_sweeps.cuh"
+#include "fwd_fused.cuh"
 #include "vgp_kernels.cuh"
 #include "sim_kernels.cuh"
 
@@ -104,6 +105,7 @@ static Config config_from_env() {
     c.no_carried_naturals = env_flag("VDP_NO_CARRIED_NATURALS");
     c.no_fused_naturals = env_flag("VDP_NO_FUSED_NATURALS");
     c.separate_kl_value = env_flag("VDP_SEPARATE_KL_VALUE");
+    c.no_fused_forward = env_flag("VDP_NO_FUSED_FORWARD");
     return c;
 }
 Config g_cfg = config_from_env();   // the environment is read here, once, at load time
@@ -117,6 +119,7 @@ static int* config_field(const char* key) {
     if (!strcmp(key, "NO_CARRIED_NATURALS")) return &g_cfg.no_carried_naturals;
     if (!strcmp(key, "NO_FUSED_NATURALS")) return &g_cfg.no_fused_naturals;
     if (!strcmp(key, "SEPARATE_KL_VALUE")) return &g_cfg.separate_kl_value;
+    if (!strcmp(key, "NO_FUSED_FORWARD")) return &g_cfg.no_fused_forward;
     return nullptr;
 }
 #else

@@ -25,9 +25,15 @@ static int launch_kl_grad(const DriftParams& P, const double* q_host, double dt,
     // values up to rounding); VDP_FLAG_GH_QUADRATURE / the GH_QUADRATURE switch run the quadrature loops instead
     if constexpr (D == 1 && KL::G == 1 && DriftStep1<DRIFT>::kCubic) {
         if (!gh_loops && !g_cfg.gh_quadrature) {
-            k_kl_grad<DRIFT, D, 20, KL::G, true><<<grid, KL::threads, smem, st>>>(
-                P, host_mat<D>(q_host), dt, pi_factor(D), time_grid, host_vec<D>(x0_mu), host_mat<D>(x0_cov), Aq, m,
-                Sd, terms, g1, gd, gs, upd, lr, sc1, scd, B, N, status, node0, node1, nat);
+#define VDP_KL_CLOSED(U, NV)                                                                                          \
+    k_kl_grad<DRIFT, D, 20, KL::G, true, U, NV><<<grid, KL::threads, smem, st>>>(                                         \
+        P, host_mat<D>(q_host), dt, pi_factor(D), time_grid, host_vec<D>(x0_mu), host_mat<D>(x0_cov), Aq, m, Sd, terms, \
+        g1, gd, gs, upd, lr, sc1, scd, B, N, status, node0, node1, nat)
+            if (upd == 2 && !terms) VDP_KL_CLOSED(2, true);
+            else if (upd == 2) VDP_KL_CLOSED(2, false);
+            else if (upd == 1) VDP_KL_CLOSED(1, false);
+            else VDP_KL_CLOSED(0, false);
+#undef VDP_KL_CLOSED
             VDP_CHECK_LAUNCH();
             return VDP_OK;
         }
@@ -77,9 +83,12 @@ static inline bool cvi_ws_take(void* ws, size_t bytes, int64_t B, int64_t N, int
 // terms on its way (tiled route, D = 1, polynomial drift in closed form) it does, and *kl_partials is the number of
 // partial sums per sequence it left in w.terms (0: run_elbo makes its own pass).
 // skip_cholQ (tiled route only): the caller does not read the process-noise factors of this rebuild
+// stop_before_means (tiled route): q as an SSM and the marginal covariances only (the fused forward pass computes the
+// means itself);  factor_ready (tiled route): w.Ld / w.Ls already hold the factor of the naturals' precision
 template <int D, int DRIFT = -1>
 static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t st, bool naturals_ready = false,
-                         int64_t* kl_partials = nullptr, bool skip_cholQ = false) {
+                         int64_t* kl_partials = nullptr, bool skip_cholQ = false, bool stop_before_means = false,
+                         bool factor_ready = false) {
     const int64_t B = p.B, N = p.N;
     if (kl_partials) *kl_partials = 0;
     if (!naturals_ready) {
@@ -105,8 +114,9 @@ static int run_posterior(const vdp_cvi_problem& p, const CviWs& w, cudaStream_t 
     const bool lite = use_tiled_sweeps(B, N) && !(p.flags & VDP_FLAG_REFACTOR_PRECISION) && !g_cfg.refactor_precision;
     int rc = run_nat2ssm<D>(w.th1, w.thd, w.ths, p.qA, p.qb, (skip_cholQ && lite && !ssm_only) ? nullptr : p.qcholQ,
                             p.qmu0, p.qcholP0, w.Ld, w.Ls, B, N, p.status, st, sc,
-                            (lite && !ssm_only) ? p.fx_covs : nullptr);
+                            (lite && !ssm_only) ? p.fx_covs : nullptr, factor_ready);
     if (rc || ssm_only) return rc;
+    if (stop_before_means && lite) return VDP_OK;
     if (lite) {
         prof_mark(VDP_PHASE_MARG_FWD, st);
         if constexpr (DRIFT >= 0 && D == 1) {
@@ -214,7 +224,46 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     }
     // the rebuild between the two site updates feeds k_kl_grad (A, means, marginal covariances): no chol Q needed
     const bool girsanov_follows = !(p.flags & VDP_FLAG_SKIP_GIRSANOV);
-    if ((rc = run_posterior<D>(p, w, st, carried, nullptr, girsanov_follows))) return rc;
+    // One forward pass for mean sweep -> KL gradient / site update -> factorisation of the next rebuild
+    // (fwd_fused.cuh): scalar chains, polynomial drift in closed form, sites held in theta, one segment per sequence
+    bool fused_fwd = false;
+    if constexpr (D == 1 && DriftStep1<DRIFT>::kCubic) {
+        using FC = TileCfg<1>;
+        fused_fwd = lazy && !(p.flags & (VDP_FLAG_GH_QUADRATURE | VDP_FLAG_REFACTOR_PRECISION | VDP_FLAG_NO_FUSED_FORWARD)) &&
+                    !g_cfg.gh_quadrature && !g_cfg.refactor_precision && !g_cfg.no_fused_forward &&
+                    use_tiled_sweeps(B, N) && plan_segments(B, N, FC::T * FC::Lm, true).nseg == 1;
+    }
+    if ((rc = run_posterior<D>(p, w, st, carried, nullptr, girsanov_follows, fused_fwd))) return rc;
+    if constexpr (D == 1 && DriftStep1<DRIFT>::kCubic) {
+        if (fused_fwd) {
+            using FC = TileCfg<1>;
+            prof_mark(VDP_PHASE_KL_GRAD, st);
+            if (p.n_obs > 0) {
+                k_add_data_step<1><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
+                    p.obs_idx, w.sc1, w.scd, w.th1, w.thd, p.lr_girsanov, p.lr_girsanov_dev, p.active_dev, B, N, p.n_obs);
+                VDP_CHECK_LAUNCH();
+            }
+            FwdFusedArgs fa;
+            fa.P = P;
+            fa.q = p.q[0]; fa.dt = p.dt; fa.lr = p.lr_girsanov;
+            fa.x0_mu = p.x0_mu[0]; fa.x0_cov = p.x0_cov[0];
+            fa.time_grid = p.time_grid;
+            fa.A = p.qA; fa.bo = p.qb; fa.mu0 = p.qmu0; fa.Sd = p.fx_covs;
+            fa.th1 = w.th1; fa.thd = w.thd; fa.ths = w.ths;
+            fa.Ld = w.Ld; fa.Ls = w.Ls;
+            fa.lr_dev = p.lr_girsanov_dev; fa.active = p.active_dev;
+            fa.status = p.status;
+            constexpr size_t smem = fwd_fused_smem<FC::T, FC::Lm>();
+            if ((rc = allow_smem(k_fwd_fused<DRIFT, FC::T, FC::Lm>, smem))) return rc;
+            k_fwd_fused<DRIFT, FC::T, FC::Lm><<<(unsigned)B, FC::T, smem, st>>>(fa, B, N);
+            VDP_CHECK_LAUNCH();
+            const bool want = !(p.flags & VDP_FLAG_SKIP_ELBO);
+            int64_t parts = 0;
+            if ((rc = run_posterior<D, DRIFT>(p, w, st, true, want ? &parts : nullptr, false, false, true))) return rc;
+            if (want) return run_elbo<DRIFT, D>(p, w, P, st, 0, -1, parts);
+            return VDP_OK;
+        }
+    }
     if (p.flags & VDP_FLAG_SKIP_GIRSANOV) {
         if (!(p.flags & VDP_FLAG_SKIP_ELBO)) return run_elbo<DRIFT, D>(p, w, P, st);
         return VDP_OK;

@@ -18,11 +18,15 @@ static int launch_chol_nat(const double* thd, const double* ths, double* Ld, dou
 template <int D>
 static int run_nat2ssm(const double* th1, const double* thd, const double* ths, double* A, double* b, double* cholQ,
                        double* mu0, double* cholP0, double* Ld, double* Ls, int64_t B, int64_t N, int64_t* status,
-                       cudaStream_t st, SegScratch sc = SegScratch(nullptr, 0), double* Sd_tiled = nullptr) {
+                       cudaStream_t st, SegScratch sc = SegScratch(nullptr, 0), double* Sd_tiled = nullptr,
+                       bool factor_ready = false) {
     int rc;
     if (use_tiled_sweeps(B, N)) {
-        prof_mark(VDP_PHASE_CHOL_FWD, st);
-        if ((rc = run_chol_tiled<D>(thd, ths, -2.0, -1.0, Ld, Ls, B, N, status, sc, st))) return rc;
+        // factor_ready: (Ld, Ls) already hold the factor of (-2 thd, -ths) (the fused forward pass of the site update)
+        if (!factor_ready) {
+            prof_mark(VDP_PHASE_CHOL_FWD, st);
+            if ((rc = run_chol_tiled<D>(thd, ths, -2.0, -1.0, Ld, Ls, B, N, status, sc, st))) return rc;
+        }
         prof_mark(VDP_PHASE_NAT2SSM_BWD, st);
         // Sd_tiled (tiled route only): marginal covariances of the Gaussian the naturals describe, written on the way
         return run_nat2ssm_bwd_tiled<D>(Ld, Ls, th1, thd, ths, A, b, cholQ, mu0, cholP0, B, N, status, sc, st, Sd_tiled);

@@ -386,7 +386,8 @@ int vdp_cvi_session_site_update(vdp_cvi_session* s, const double* obs_y_host, do
     const size_t d = (size_t)s->dev.D, dd = d * d, S = sizeof(double);
     // from the second update on every chunk's workspace holds the naturals of its previous update: carried, with the
     // girsanov sites held in theta (vdp_cvi_session_download_state materialises them)
-    int fl = flags & (VDP_FLAG_GH_QUADRATURE | VDP_FLAG_REFACTOR_PRECISION | VDP_FLAG_SEPARATE_KL_VALUE);
+    int fl = flags & (VDP_FLAG_GH_QUADRATURE | VDP_FLAG_REFACTOR_PRECISION | VDP_FLAG_SEPARATE_KL_VALUE |
+                      VDP_FLAG_NO_FUSED_FORWARD);
     if (s->updates > 0) fl |= VDP_FLAG_NATURALS_CARRIED | VDP_FLAG_SITES_IN_NATURALS;
     int rc = VDP_OK;
     int64_t ci = 0;

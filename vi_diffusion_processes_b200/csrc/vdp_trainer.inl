@@ -121,7 +121,7 @@ extern "C" int vdp_cvi_optimize_sites(const vdp_cvi_problem* hp, const vdp_cvi_l
     std::string key(reinterpret_cast<const char*>(&q), sizeof(q));
     key.append(reinterpret_cast<const char*>(lp), sizeof(*lp));
     for (const char* k : {"SWEEPS", "NSEG", "GH_QUADRATURE", "REFACTOR_PRECISION", "NO_CARRIED_NATURALS",
-                          "NO_FUSED_NATURALS", "SEPARATE_KL_VALUE"}) {
+                          "NO_FUSED_NATURALS", "SEPARATE_KL_VALUE", "NO_FUSED_FORWARD"}) {
         int v = 0;
         vdp_config_get(k, &v);
         key.append(reinterpret_cast<const char*>(&v), sizeof(v));
