@@ -25,12 +25,24 @@
 #define VDP_FUSED_MINBLOCKS 4
 #endif
 #ifndef VDP_FUSED_UNROLL
-#define VDP_FUSED_UNROLL 16   /* >= L: the term loop fully unrolled (a partial unroll indexes the per-thread grid times dynamically) */
+#define VDP_FUSED_UNROLL 3   /* unroll of the term loop of a full chunk */
+#endif
+
+#ifndef VDP_FUSED_PREFETCH
+#define VDP_FUSED_PREFETCH 1   /* measured: 0.83 -> 0.75 ms on the C4 shape */
+#endif
+// tile shape of the fused pass (defaults: the shape of the D = 1 mean sweep, so the means round the same way)
+#ifndef VDP_TF1
+#define VDP_TF1 VDP_T1
+#endif
+#ifndef VDP_LF1
+#define VDP_LF1 VDP_LM1
 #endif
 
 namespace vdp {
 
 constexpr int kFusedUnroll = VDP_FUSED_UNROLL;
+constexpr int kFusedT = VDP_TF1, kFusedL = VDP_LF1;
 
 struct FwdFusedArgs {
     DriftParams P;
@@ -45,23 +57,108 @@ struct FwdFusedArgs {
     int64_t* status = nullptr;
 };
 
-constexpr int kFusedHeader = 32;                 // doubles: mbarrier, tile-to-tile carries, scan scratch
+// doubles in front of the staged arrays: mbarrier, tile-to-tile carries, scan scratch (one 32-byte element per warp)
+template <int T>
+__host__ __device__ constexpr int fused_header() { return 8 + (T / 32) * 4; }
 template <int T, int L>
 __host__ __device__ constexpr int fused_region() { return tile_slots(T * L + 1) + 2; }   // 2 margin slots in front
 template <int T, int L>
-constexpr size_t fwd_fused_smem() { return ((size_t)kFusedHeader + 6 * (size_t)fused_region<T, L>()) * sizeof(double); }
+constexpr size_t fwd_fused_smem() {
+    return ((size_t)fused_header<T>() + 6 * (size_t)fused_region<T, L>()) * sizeof(double);
+}
+
+// The KL-gradient terms of one chunk (transitions k0 .. k0 + len - 1 of the staged tile) and the site update of the
+// grid points they finish.  FULL: len == L at compile time (no per-step guards).  m: mean at the chunk's first point
+// on entry, at its last point + 1 on exit;  g0m / g0S: left part of the first term;  prm / prS: right part of the last.
+template <int DRIFT, int L, bool FULL, int UNROLL>
+__device__ __forceinline__ void fused_chunk_terms(const FwdFusedArgs& a, const double* __restrict__ tgp, int len,
+                                                  int k0, const double* sA, const double* sB, const double* sS,
+                                                  double* s1, double* sD, double* sT, double nlr, double& m,
+                                                  double& g0m, double& g0S, double& prm, double& prS, int& bad) {
+    double Sk = sS[k0];
+    double t_lo = __ldg(tgp);
+    bool ok = true;
+    const int cnt = FULL ? L : len;
+#pragma unroll UNROLL
+    for (int t = 0; t < cnt; ++t) {
+        const int j = k0 + t;
+        const double t_hi = __ldg(tgp + t + 1);
+        const double Ak = sA[j];
+        const double mn = sB[j] + Ak * m;
+        const double Sn = sS[j + 1];
+        const double Qp = (t_hi - t_lo) * a.q;
+        if (!(Sk > 0.0)) ok = false;
+        double Lgm, LgS, Rgm, RgS, gC;
+        kl_grad_closed_core<DRIFT>(a.P, Qp, a.dt, Ak, rcp_fast(Sk), m, mn, Sk, Sn, Lgm, LgS, Rgm, RgS, gC, ok);
+        if (!ok) { bad = t + 1; ok = true; }
+        if (t == 0) {
+            g0m = Lgm;
+            g0S = LgS;
+        } else {
+            // point j: left part of term j + right part of term j - 1;  S = eta_d - m m^T
+            const double gSj = LgS + prS;
+            const double gmj = (Lgm + prm) - 2.0 * (gSj * m);
+            s1[j] = fma(nlr, gmj, s1[j]);
+            sD[j] = fma(nlr, gSj, sD[j]);
+        }
+        sT[j] = fma(nlr, gC, sT[j]);
+        prm = Rgm;
+        prS = RgS;
+        m = mn;
+        Sk = Sn;
+        t_lo = t_hi;
+    }
+}
+
+// The lagged Cholesky recursion of one chunk from its incoming Schur complement s: factor entries into oLd / oLs.
+template <int L, bool FULL>
+__device__ __forceinline__ int fused_chunk_chol(const double* cKd, const double* cKs, int k0, int len, double s,
+                                                double* oLd, double* oLs) {
+    int badc = -1;
+    if constexpr (FULL) {
+        double ks[L], kd[L];
+#pragma unroll
+        for (int t = 0; t < L; ++t) {
+            ks[t] = -cKs[k0 + t];
+            kd[t] = (t < L - 1) ? -2.0 * cKd[k0 + t + 1] : 1.0;
+        }
+#pragma unroll
+        for (int t = 0; t < L; ++t) {
+            if (!(s > 0.0) && badc < 0) badc = t;
+            const double r = rcp_fast(s);
+            double Lk, rL;
+            sqrt_rsqrt_fast(s, Lk, rL);
+            oLd[k0 + t] = Lk;
+            oLs[k0 + t] = div_r(ks[t], Lk, rL);
+            if (t < L - 1) s = fma(-(ks[t] * ks[t]), r, kd[t]);
+        }
+    } else {
+#pragma unroll 1
+        for (int t = 0; t < len; ++t) {
+            if (!(s > 0.0) && badc < 0) badc = t;
+            const double ks = -cKs[k0 + t];
+            const double r = rcp_fast(s);
+            double Lk, rL;
+            sqrt_rsqrt_fast(s, Lk, rL);
+            oLd[k0 + t] = Lk;
+            oLs[k0 + t] = div_r(ks, Lk, rL);
+            if (t < len - 1) s = fma(-(ks * ks), r, -2.0 * cKd[k0 + t + 1]);
+        }
+    }
+    return badc;
+}
 
 template <int DRIFT, int T, int L>
 __global__ void __launch_bounds__(T, VDP_FUSED_MINBLOCKS) k_fwd_fused(FwdFusedArgs a, int64_t B, int64_t N) {
     constexpr int TL = T * L, SR = fused_region<T, L>();
-    static_assert(T / 32 * sizeof(SchurElem<1>) <= 16 * sizeof(double), "scan scratch");
+    static_assert(sizeof(SchurElem<1>) <= 4 * sizeof(double) && sizeof(AffVecElem<1>) <= 4 * sizeof(double), "scan scratch");
     extern __shared__ __align__(16) double smem[];
     // header: [0] mbarrier, [2..5] right gradient part handed from tile to tile (two parities), [6..7] theta_s' of
-    // the tile's last transition (two parities), [8..23] scan scratch
+    // the tile's last transition (two parities), [8..) scan scratch
     double* carryR = smem + 2;
     double* carryTs = smem + 6;
     void* wtot = smem + 8;
-    double* rawA = smem + kFusedHeader + 2;       // A_k            -> L_{k+1,k} (lagged)
+    double* rawA = smem + fused_header<T>() + 2;       // A_k            -> L_{k+1,k} (lagged)
     double* rawB = rawA + SR;                     // b_k
     double* rawS = rawB + SR;                     // S_k            -> L_kk (lagged)
     double* raw1 = rawS + SR;                     // theta_1
@@ -107,12 +204,19 @@ __global__ void __launch_bounds__(T, VDP_FUSED_MINBLOCKS) k_fwd_fused(FwdFusedAr
             __syncthreads();
             if (threadIdx.x == 0) { bulk_wait_read(); issue(ti); }
         }
-        // grid spacing of this thread's transitions (L2-resident, shared by every sequence): on their way before the
-        // tile's own arrays have landed
-        double tg[L + 1];
-#pragma unroll
-        for (int t = 0; t <= L; ++t) tg[t] = (t <= len) ? __ldg(a.time_grid + tk + k0 + t) : 0.0;
         ring.wait(ti);
+#if VDP_FUSED_PREFETCH
+        if (threadIdx.x == 0 && ti + 1 < ntiles) {   // the next tile's lines travel to L2 while this one is worked on
+            const int64_t tn = tk + TL;
+            const int cn2 = (int)min((int64_t)TL, N - tn);
+            bulk_prefetch_l2(gA + tn, cn2);
+            bulk_prefetch_l2(gB + tn, cn2);
+            bulk_prefetch_l2(gS + tn + 1, cn2);
+            bulk_prefetch_l2(g1 + tn + 1, cn2);
+            bulk_prefetch_l2(gD + tn + 1, cn2);
+            bulk_prefetch_l2(gT + tn, cn2);
+        }
+#endif
         double* sA = rawA + tile_off(gA + tk);
         double* sB = rawB + tile_off(gB + tk);
         double* sS = rawS + tile_off(gS + tk);
@@ -122,9 +226,17 @@ __global__ void __launch_bounds__(T, VDP_FUSED_MINBLOCKS) k_fwd_fused(FwdFusedAr
         // ---- means: chunk element, block scan, replay (state_space_model.py:251)
         using VOps = AffVecOps<1>;
         VOps::Elem e = VOps::identity();
+        if (len == L) {
 #pragma unroll
-        for (int t = 0; t < L; ++t) {
-            if (t < len) {
+            for (int t = 0; t < L; ++t) {
+                AffVecElem<1> s;
+                s.M.a[0] = sA[k0 + t];
+                s.v.v[0] = sB[k0 + t];
+                e = VOps::combine(e, s);
+            }
+        } else {
+#pragma unroll 1
+            for (int t = 0; t < len; ++t) {
                 AffVecElem<1> s;
                 s.M.a[0] = sA[k0 + t];
                 s.v.v[0] = sB[k0 + t];
@@ -136,40 +248,17 @@ __global__ void __launch_bounds__(T, VDP_FUSED_MINBLOCKS) k_fwd_fused(FwdFusedAr
         const double m0 = VOps::apply(exclV, st).v[0];
         st = VOps::apply(totalV, st);
         // ---- KL gradient per transition, site update of the finished grid points
-        double m = m0, Sk = (len > 0) ? sS[k0] : 1.0;
+        double m = m0;
         double g0m = 0.0, g0S = 0.0;          // left part of the chunk's first term (its point waits for the neighbour)
-        double prm = 0.0, prS = 0.0;          // right part of the previous term
-        bool ok = true;
+        double prm = 0.0, prS = 0.0;          // right part of the chunk's last term
         int bad = 0;
-#pragma unroll kFusedUnroll
-        for (int t = 0; t < L; ++t) {
-            if (t < len) {
-                const int j = k0 + t;
-                const double Ak = sA[j];
-                const double mn = sB[j] + Ak * m;
-                const double Sn = sS[j + 1];
-                const double Qp = (tg[t + 1] - tg[t]) * a.q;
-                if (!(Sk > 0.0)) ok = false;
-                double Lgm, LgS, Rgm, RgS, gC;
-                kl_grad_closed_core<DRIFT>(a.P, Qp, a.dt, Ak, rcp_fast(Sk), m, mn, Sk, Sn, Lgm, LgS, Rgm, RgS, gC, ok);
-                if (!ok) { bad = t + 1; ok = true; }
-                if (t == 0) {
-                    g0m = Lgm;
-                    g0S = LgS;
-                } else {
-                    // point j: left part of term j + right part of term j - 1;  S = eta_d - m m^T
-                    const double gSj = LgS + prS;
-                    const double gmj = (Lgm + prm) - 2.0 * (gSj * m);
-                    s1[j] = fma(nlr, gmj, s1[j]);
-                    sD[j] = fma(nlr, gSj, sD[j]);
-                }
-                sT[j] = fma(nlr, gC, sT[j]);
-                prm = Rgm;
-                prS = RgS;
-                m = mn;
-                Sk = Sn;
-            }
-        }
+        // (the grid times are L2 / L1 resident and shared by every sequence: read per term)
+        if (len == L)
+            fused_chunk_terms<DRIFT, L, true, kFusedUnroll>(a, a.time_grid + tk + k0, L, k0, sA, sB, sS, s1, sD, sT, nlr, m,
+                                                            g0m, g0S, prm, prS, bad);
+        else if (len > 0)
+            fused_chunk_terms<DRIFT, L, false, 1>(a, a.time_grid + tk + k0, len, k0, sA, sB, sS, s1, sD, sT, nlr, m, g0m,
+                                                  g0S, prm, prS, bad);
         if (bad) report_not_pd(a.status, b * n + tk + k0 + bad - 1);
         // hand the right part of the chunk's last term on: through the (consumed) slots of the chunk's last transition
         // to the next thread, or to the next tile; the sequence's last grid point is finished here
@@ -227,25 +316,9 @@ __global__ void __launch_bounds__(T, VDP_FUSED_MINBLOCKS) k_fwd_fused(FwdFusedAr
         double* oLd = rawS + (int)((reinterpret_cast<uintptr_t>(gLd) >> 3) & 1u);
         double* oLs = rawA + (int)((reinterpret_cast<uintptr_t>(gLs) >> 3) & 1u);
         {
-            double ks[L], kd[L];
-#pragma unroll
-            for (int t = 0; t < L; ++t) {
-                ks[t] = (t < len) ? -cKs[k0 + t] : 0.0;
-                kd[t] = (t < len - 1) ? -2.0 * cKd[k0 + t + 1] : 1.0;
-            }
             int badc = -1;
-#pragma unroll
-            for (int t = 0; t < L; ++t) {
-                if (t < len) {
-                    if (!(s > 0.0) && badc < 0) badc = t;
-                    const double r = rcp_fast(s);
-                    double Lk, rL;
-                    sqrt_rsqrt_fast(s, Lk, rL);
-                    oLd[k0 + t] = Lk;
-                    oLs[k0 + t] = div_r(ks[t], Lk, rL);
-                    if (t < len - 1) s = fma(-(ks[t] * ks[t]), r, kd[t]);
-                }
-            }
+            if (len == L) badc = fused_chunk_chol<L, true>(cKd, cKs, k0, L, s, oLd, oLs);
+            else if (len > 0) badc = fused_chunk_chol<L, false>(cKd, cKs, k0, len, s, oLd, oLs);
             if (badc >= 0 && (ti > 0 || k0 + badc > 0)) report_not_pd(a.status, b * n + tk - 1 + k0 + badc);
         }
         fence_async_smem();

@@ -52,6 +52,16 @@ __device__ __forceinline__ Mat<D> transition_from_cov(const Mat<D>& Skk, const M
 // conditional precision -> covariance and its Cholesky factor (chol, cholesky_solve(I), chol)
 template <int D>
 __device__ __forceinline__ void cov_from_precision(const Mat<D>& prec, Mat<D>& cov, Mat<D>& cholcov, bool& ok) {
+    if constexpr (D == 1) {
+        // scalar: chol(1 / p) = p^(-1/2) and 1 / p = (p^(-1/2))^2 from one reciprocal square root
+        const double p = prec.a[0];
+        if (!(p > 0.0)) ok = false;
+        double sp, rs;
+        sqrt_rsqrt_fast(p, sp, rs);
+        cholcov.a[0] = rs;
+        cov.a[0] = rs * rs;
+        return;
+    }
     const Mat<D> c = chol(prec, ok);
     cov = chol_inverse(c);
     cholcov = chol(cov, ok);

@@ -21,6 +21,14 @@
 #include "kl_kernels.cuh"
 #include "tma_tile.cuh"
 
+// L2 prefetch of the next tile in the single-buffer sweeps (naturals_to_ssm, means)
+#ifndef VDP_PREFETCH_N
+#define VDP_PREFETCH_N 0
+#endif
+#ifndef VDP_PREFETCH_M
+#define VDP_PREFETCH_M 1
+#endif
+
 namespace vdp {
 
 enum { SWEEP_FULL = 0, SWEEP_SUMMARY = 1, SWEEP_SUMMARY2 = 2 };
@@ -517,6 +525,16 @@ k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
             if (threadIdx.x == 0) { bulk_wait_read(); issue(ti); }
         }
         ring.wait(ti);
+        if (VDP_PREFETCH_M && NSTAGE == 1 && threadIdx.x == 0 && ti + 1 < ntiles) {
+            const int64_t tn = tk + TL;
+            const int nc = (int)min((int64_t)TL, t1 - tn);
+            bulk_prefetch_l2(A + (b * N + tn) * DD, nc * DD);
+            bulk_prefetch_l2(bo + (b * N + tn) * D, nc * D);
+            if (KL) {
+                bulk_prefetch_l2(kl.Sd + (b * (N + 1) + tn), nc);
+                bulk_prefetch_l2(kl.cholQ + (b * N + tn), nc);
+            }
+        }
         double* base = stage0 + (ti % NSTAGE) * kStage;
         double* sA = base + tile_off(A + (b * N + tk) * DD);                  // A of transition i
         double* sb = base + SM + tile_off(bo + (b * N + tk) * D);             // offsets -> m_{k+1}
@@ -791,6 +809,20 @@ k_nat2ssm_tiled(const double* __restrict__ Ld, const double* __restrict__ Ls, co
             if (threadIdx.x == 0) { bulk_wait_read(); issue(ti); }
         }
         ring.wait(ti);
+        if (VDP_PREFETCH_N && NSTAGE == 1 && threadIdx.x == 0 && ti + 1 < ntiles) {
+            // single buffer: the next tile's lines travel to L2 while this one is worked on
+            const int64_t nhi = lo, nlo = max(t0, nhi - TL);
+            const int nc = (int)(nhi - nlo);
+            bulk_prefetch_l2(Ld + (b * n + nlo) * DD, nc * DD);
+            bulk_prefetch_l2(Ls + (b * N + nlo) * DD, nc * DD);
+            if (MODE != SWEEP_SUMMARY) {
+                if (!FROML) {
+                    bulk_prefetch_l2(thd + (b * n + nlo) * DD, nc * DD);
+                    bulk_prefetch_l2(ths + (b * N + nlo) * DD, nc * DD);
+                }
+                bulk_prefetch_l2(th1 + (b * n + nlo) * D, nc * D);
+            }
+        }
         double* base = stage0 + (ti % NSTAGE) * kStage;
         double* sLd = base + tile_off(Ld + (b * n + lo) * DD);                 // L_kk  -> chol of the conditional covariance
         double* sLs = base + SM + tile_off(Ls + (b * N + lo) * DD);            // L_sub -> A_k

@@ -64,6 +64,15 @@ __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wa
 // generic-proxy writes to shared memory (st.shared) become visible to the asynchronous proxy (bulk stores)
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// start [g, g + count) on its way to L2 (the tile this CTA stages next: its bulk copy then finds the lines there);
+// one thread, one instruction: the range is widened to 16-byte bounds inside the array's allocation
+__device__ __forceinline__ void bulk_prefetch_l2(const double* g, int count) {
+    if (count <= 1) return;
+    const double* g0 = g - ((reinterpret_cast<uintptr_t>(g) >> 3) & 1u);
+    const uint32_t bytes = (uint32_t)(((g + count) - g0) >> 1) << 4;
+    if (bytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(g0), "r"(bytes) : "memory");
+}
+
 __device__ __forceinline__ void ldgsts8(double* s, const double* g) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(smem_u32(s)), "l"(g) : "memory");
 }

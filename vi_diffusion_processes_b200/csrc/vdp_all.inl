@@ -32,7 +32,6 @@
 #include "prior_grad_kernels.cuh"
 #include "quad_core.cuh"
 #include "tile_sweeps.cuh"
-#include "fwd_fused.cuh"
 #include "vgp_kernels.cuh"
 #include "sim_kernels.cuh"
 
@@ -142,6 +141,7 @@ static inline void prof_mark(int phase, cudaStream_t st) {
 }  // namespace vdp
 
 #include "vdp_sweeps.inl"
+#include "fwd_fused.cuh"
 
 using namespace vdp;
 

@@ -228,15 +228,13 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     // (fwd_fused.cuh): scalar chains, polynomial drift in closed form, sites held in theta, one segment per sequence
     bool fused_fwd = false;
     if constexpr (D == 1 && DriftStep1<DRIFT>::kCubic) {
-        using FC = TileCfg<1>;
         fused_fwd = lazy && !(p.flags & (VDP_FLAG_GH_QUADRATURE | VDP_FLAG_REFACTOR_PRECISION | VDP_FLAG_NO_FUSED_FORWARD)) &&
                     !g_cfg.gh_quadrature && !g_cfg.refactor_precision && !g_cfg.no_fused_forward &&
-                    use_tiled_sweeps(B, N) && plan_segments(B, N, FC::T * FC::Lm, true).nseg == 1;
+                    use_tiled_sweeps(B, N) && plan_segments(B, N, kFusedT * kFusedL, true).nseg == 1;
     }
     if ((rc = run_posterior<D>(p, w, st, carried, nullptr, girsanov_follows, fused_fwd))) return rc;
     if constexpr (D == 1 && DriftStep1<DRIFT>::kCubic) {
         if (fused_fwd) {
-            using FC = TileCfg<1>;
             prof_mark(VDP_PHASE_KL_GRAD, st);
             if (p.n_obs > 0) {
                 k_add_data_step<1><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
@@ -253,9 +251,9 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
             fa.Ld = w.Ld; fa.Ls = w.Ls;
             fa.lr_dev = p.lr_girsanov_dev; fa.active = p.active_dev;
             fa.status = p.status;
-            constexpr size_t smem = fwd_fused_smem<FC::T, FC::Lm>();
-            if ((rc = allow_smem(k_fwd_fused<DRIFT, FC::T, FC::Lm>, smem))) return rc;
-            k_fwd_fused<DRIFT, FC::T, FC::Lm><<<(unsigned)B, FC::T, smem, st>>>(fa, B, N);
+            constexpr size_t smem = fwd_fused_smem<kFusedT, kFusedL>();
+            if ((rc = allow_smem(k_fwd_fused<DRIFT, kFusedT, kFusedL>, smem))) return rc;
+            k_fwd_fused<DRIFT, kFusedT, kFusedL><<<(unsigned)B, kFusedT, smem, st>>>(fa, B, N);
             VDP_CHECK_LAUNCH();
             const bool want = !(p.flags & VDP_FLAG_SKIP_ELBO);
             int64_t parts = 0;
