@@ -48,6 +48,9 @@ ALGO_BYTES_PER_STEP_D1 = 80  # 8 * (4D + 6D^2) for D = 1
 # (8000 x 42) + ~6 kflop of block algebra
 FP64_PEAK_MEASURED = 33.67e12   # flop/s: vdp_test_fp64_fma on this pool's B200 (profiles/r02_quadrature_d2_d3.json)
 C5_FLOPS_PER_STEP = 8000 * 94 + 8000 * 42 + 6000
+# D = 3 update, every input and output once: prior A, b, chol Q (21) + sites g1, gd, gs in and out (2 x 21) + q as an
+# SSM A, b, chol Q (21) + marginals m, S (12) + time grid (1) = 97 doubles; the 10^4 observations add < 0.1 %
+C5_BYTES_PER_STEP = 97 * 8
 
 
 def make_problem(B, N, seed):
@@ -482,15 +485,29 @@ def run_c5_leg(args):
     """BASELINE config 5 through tools/c5_time_sharded.run (time-sharded chain, dist_cvi.TimeShardedCvi)."""
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import c5_time_sharded
+    # default route: the drift is linear, so the 2-point rule per dimension is exact (csrc/drifts.cuh DriftPoly) and the
+    # update is bound by the sweeps' HBM traffic; then the same update with the reference's 20 points per dimension
+    # (8000 nodes per transition), which is bound by the float64 pipe
     res = c5_time_sharded.run(N=args.c5_grid, n_obs=args.c5_obs, steps=args.c5_steps, warmup=1)
+    gh = c5_time_sharded.run(N=args.c5_grid, n_obs=args.c5_obs, steps=1, warmup=1, gh20=True)
     if res is not None:
+        peak_hbm, peak_src = measured_peaks()
+        bytes_step = C5_BYTES_PER_STEP
+        gbs = bytes_step * res["value"] / 1e9 / res["n_gpus"]
+        res["roofline"] = {"bound": "hbm", "achieved": gbs, "peak": peak_hbm, "unit": "GB/s", "frac": gbs / peak_hbm,
+                           "algorithmic_bytes_per_grid_step": bytes_step, "peak_source": peak_src,
+                           "note": "inputs and outputs of one update once: prior SSM, sites and data in; sites, q as an "
+                                   "SSM and marginals out (D = 3: 97 doubles per grid step)"}
         peak_fp64 = FP64_PEAK_MEASURED   # vdp_test_fp64_fma on this pool's B200 (tools/quad_profile.py)
-        flops = C5_FLOPS_PER_STEP * res["value"]
-        res["roofline"] = {"bound": "fp64", "achieved": flops / 1e12 / res["n_gpus"], "peak": peak_fp64 / 1e12,
-                           "unit": "TFLOP/s", "frac": flops / res["n_gpus"] / peak_fp64,
-                           "flops_per_grid_step": C5_FLOPS_PER_STEP,
-                           "peak_source": "measured float64 FMA throughput of this pool's B200 (vdp_test_fp64_fma, "
-                                          "profiles/r02_quadrature_d2_d3.json)"}
+        flops = C5_FLOPS_PER_STEP * gh["value"]
+        res["gh20_reference_order"] = {
+            "ms_per_step": gh["ms_per_step"], "value": gh["value"], "unit": "grid-steps/s", "elbo": gh["elbo"],
+            "quadrature_nodes_per_transition": 8000,
+            "roofline": {"bound": "fp64", "achieved": flops / 1e12 / gh["n_gpus"], "peak": peak_fp64 / 1e12,
+                         "unit": "TFLOP/s", "frac": flops / gh["n_gpus"] / peak_fp64,
+                         "flops_per_grid_step": C5_FLOPS_PER_STEP,
+                         "peak_source": "measured float64 FMA throughput of this pool's B200 (vdp_test_fp64_fma, "
+                                        "profiles/r02_quadrature_d2_d3.json)"}}
     return res
 
 
@@ -513,7 +530,9 @@ def run_c5(args):
                 "n_gpus": world, "steps": res["steps"], "warmup": res["warmup"], "ms_per_step": res["ms_per_step"],
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": {"workload": res["workload"], "grid_steps": args.c5_grid,
-                                                "state_dim": 3, "n_obs": args.c5_obs, "quad_H": 20,
+                                                "state_dim": 3, "n_obs": args.c5_obs,
+                                                "quad_H": "2 per dimension (exact for the linear drift); "
+                                                          "gh20_reference_order: 20",
                                                 "parallelism": f"time-sharded x{world}: {res['collective']}"},
                 "clocks": sampler.stop(), "roofline": res["roofline"], "c5": res}
         print(json.dumps(line))

@@ -32,7 +32,7 @@ def make_problem(N, n_obs, seed=7, dt=1e-3, D=3):
     return grid, idx, y
 
 
-def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False):
+def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=False):
     """Returns (result dict on rank 0 else None[, the TimeShardedCvi]).  The process group, if any, must exist."""
     import torch.distributed as dist
     from vi_diffusion_processes_b200.dist_cvi import TimeShardedCvi
@@ -47,6 +47,10 @@ def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False):
     sh = TimeShardedCvi(DRIFT_OU_ND, [0.5], np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.zeros(D), np.eye(D), comm=comm,
                         device=device)
     del grid
+    if gh20:      # the reference's 20 points per dimension instead of the exact 2-point rule of the linear drift
+        from vi_diffusion_processes_b200 import _lib
+        for st in sh.ranks:
+            st.eng.route_flags |= _lib.FLAG_GH_QUADRATURE
     for _ in range(max(1, warmup)):
         elbo = sh.site_update(lr, lr)
     sh.check_status()
@@ -75,7 +79,7 @@ def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False):
                            f"update per step, chain sharded in time over {world} rank(s)",
                "n_gpus": world, "steps": steps, "warmup": max(1, warmup), "ms_per_step": ms_step,
                "value": N / (ms_step * 1e-3), "unit": "grid-steps/s", "scaling": "strong", "elbo": elbo,
-               "quadrature_nodes_per_transition": 8000,
+               "quadrature_nodes_per_transition": 8000 if gh20 else 8,
                "collective": "vdp_comm_all_gather (ncclAllGather issued from C on the compute stream)" if world > 1
                else "none (1 rank)",
                "all_gathers_per_step": (comm.n_gathers - g0) // steps,

@@ -121,6 +121,21 @@ template <> struct Drift<DRIFT_LORENZ63, 3> {
     }
 };
 
+// Polynomial drifts.  degree = p > 0: every component of f is a polynomial of total degree <= p in x.  The integrands
+// of the KL term along the Gaussian path (sde_utils.py:317-354) and of its reverse-mode adjoint are then polynomials
+// of degree <= 2 p in the quadrature variable, which a Gauss-Hermite rule with p + 1 points per dimension integrates
+// exactly -- as does the reference's 20-point rule: the two agree to rounding, for the value and for the gradient
+// (both are the same function of (m, S)).  (p + 1)^D nodes instead of 20^D: 16 instead of 400 for Van der Pol,
+// 27 / 8 instead of 8000 for Lorenz-63 / a linear drift in D = 3.  degree = 0: not a polynomial, the 20-point rule.
+template <int ID> struct DriftPoly { static constexpr int degree = 0; };
+template <> struct DriftPoly<DRIFT_OU> { static constexpr int degree = 1; };
+template <> struct DriftPoly<DRIFT_OU_ND> { static constexpr int degree = 1; };
+template <> struct DriftPoly<DRIFT_DW> { static constexpr int degree = 3; };
+template <> struct DriftPoly<DRIFT_VDP> { static constexpr int degree = 3; };
+template <> struct DriftPoly<DRIFT_LORENZ63> { static constexpr int degree = 2; };
+// points per dimension of the exact rule (20 where there is none)
+template <int ID> struct ExactOrder { static constexpr int H = DriftPoly<ID>::degree > 0 ? DriftPoly<ID>::degree + 1 : 20; };
+
 // D = 1 quadrature loops (kl_kernels.cuh): residual of one Euler step against a linear transition and its slope,
 //   d(x) = x + dt f(x) - (A x + b),     j(x) = d'(x) = 1 + dt f'(x) - A,
 // from per-transition constants prepared once outside the node loop.  The generic form calls the drift functor;

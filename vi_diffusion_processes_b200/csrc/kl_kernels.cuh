@@ -386,10 +386,32 @@ struct KlHandoff { double gm[D]; double gS[D * D]; };
 template <int G> struct KlBounds {
     static constexpr int threads = (G == 1) ? 128 : 256, blocks = (G == 1) ? VDP_KL_MINBLOCKS : VDP_KLG_MINBLOCKS;
 };
+// D >= 2 with the exact low-order rule of a polynomial drift (ExactOrder: 4 .. 64 nodes per grid point): a small group
+// of lanes per grid point -- every lane repeats the pointwise algebra around the quadrature, so a whole warp per
+// grid point would spend its time there -- and a register budget for the D x D blocks each lane holds
+#ifndef VDP_KLX_G2
+#define VDP_KLX_G2 2
+#endif
+#ifndef VDP_KLX_G3
+#define VDP_KLX_G3 4
+#endif
+#ifndef VDP_KLX_MINBLOCKS2
+#define VDP_KLX_MINBLOCKS2 3   /* D = 2: 152 registers */
+#endif
+#ifndef VDP_KLX_MINBLOCKS3
+#define VDP_KLX_MINBLOCKS3 2   /* D = 3: 168 registers spill 120-200 bytes */
+#endif
+template <int D> struct KlExactGroup { static constexpr int value = (D == 2) ? VDP_KLX_G2 : VDP_KLX_G3; };
+// launch shape of k_kl_grad by (D, H, G): threads per block and resident blocks the register budget is cut for
+template <int D, int H, int G> struct KlShape {
+    static constexpr bool exact = (D >= 2 && H <= 4);
+    static constexpr int threads = exact ? 128 : KlBounds<G>::threads;
+    static constexpr int blocks = exact ? (D == 2 ? VDP_KLX_MINBLOCKS2 : VDP_KLX_MINBLOCKS3) : KlBounds<G>::blocks;
+};
 // UPDT >= 0: the update mode is a compile-time constant (prunes the other modes' code from the scalar kernel)
 // NOVAL: the caller passes terms == nullptr (gradient only), known at compile time
 template <int DRIFT, int D, int H, int G, bool CLOSED = false, int UPDT = -1, bool NOVAL = false>
-__global__ void __launch_bounds__(KlBounds<G>::threads, KlBounds<G>::blocks) k_kl_grad(DriftParams P, Mat<D> q, double dt, double pi_factor,
+__global__ void __launch_bounds__(KlShape<D, H, G>::threads, KlShape<D, H, G>::blocks) k_kl_grad(DriftParams P, Mat<D> q, double dt, double pi_factor,
                           const double* __restrict__ time_grid, Vec<D> x0_mu, Mat<D> x0_cov,
                           const double* __restrict__ Aq, const double* __restrict__ m,
                           const double* __restrict__ Sd, double* __restrict__ terms, double* __restrict__ g1,

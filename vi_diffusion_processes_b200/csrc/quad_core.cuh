@@ -16,9 +16,31 @@ static __constant__ double c_gh_x10[10] = VDP_GH_X_10;
 static __constant__ double c_gh_w10[10] = VDP_GH_W_10;
 static __constant__ double c_gh_x20[20] = VDP_GH_X_20;
 static __constant__ double c_gh_w20[20] = VDP_GH_W_20;
+// low-order rules: an H-point rule is exact up to degree 2H - 1, so for a polynomial drift of degree p every
+// integrand of the KL term and of its adjoint (degree <= 2p) gets from the (p + 1)-point rule the value the
+// reference's 20-point rule gives (DriftPoly in drifts.cuh)
+static __constant__ double c_gh_x2[2] = VDP_GH_X_2;
+static __constant__ double c_gh_w2[2] = VDP_GH_W_2;
+static __constant__ double c_gh_x3[3] = VDP_GH_X_3;
+static __constant__ double c_gh_w3[3] = VDP_GH_W_3;
+static __constant__ double c_gh_x4[4] = VDP_GH_X_4;
+static __constant__ double c_gh_w4[4] = VDP_GH_W_4;
 
-template <int H> __device__ __forceinline__ double gh_x(int i) { return H == 10 ? c_gh_x10[i] : c_gh_x20[i]; }
-template <int H> __device__ __forceinline__ double gh_w(int i) { return H == 10 ? c_gh_w10[i] : c_gh_w20[i]; }
+template <int H> __device__ __forceinline__ double gh_x(int i) {
+    static_assert(H == 2 || H == 3 || H == 4 || H == 10 || H == 20, "no Gauss-Hermite table of this order");
+    if constexpr (H == 2) return c_gh_x2[i];
+    else if constexpr (H == 3) return c_gh_x3[i];
+    else if constexpr (H == 4) return c_gh_x4[i];
+    else if constexpr (H == 10) return c_gh_x10[i];
+    else return c_gh_x20[i];
+}
+template <int H> __device__ __forceinline__ double gh_w(int i) {
+    if constexpr (H == 2) return c_gh_w2[i];
+    else if constexpr (H == 3) return c_gh_w3[i];
+    else if constexpr (H == 4) return c_gh_w4[i];
+    else if constexpr (H == 10) return c_gh_w10[i];
+    else return c_gh_w20[i];
+}
 
 // The same tables in global memory for lookups whose index differs from lane to lane (D >= 2: the lanes of a
 // group hold different nodes).  A constant-bank read is serialised once per distinct address in the warp (up
@@ -27,8 +49,14 @@ static __device__ const double d_gh_x10[10] = VDP_GH_X_10;
 static __device__ const double d_gh_w10[10] = VDP_GH_W_10;
 static __device__ const double d_gh_x20[20] = VDP_GH_X_20;
 static __device__ const double d_gh_w20[20] = VDP_GH_W_20;
-template <int H> __device__ __forceinline__ double gh_x_div(int i) { return __ldg(H == 10 ? &d_gh_x10[i] : &d_gh_x20[i]); }
-template <int H> __device__ __forceinline__ double gh_w_div(int i) { return __ldg(H == 10 ? &d_gh_w10[i] : &d_gh_w20[i]); }
+template <int H> __device__ __forceinline__ double gh_x_div(int i) {
+    if constexpr (H <= 4) return gh_x<H>(i);      // (2-4 entries: the constant bank replays are few)
+    else return __ldg(H == 10 ? &d_gh_x10[i] : &d_gh_x20[i]);
+}
+template <int H> __device__ __forceinline__ double gh_w_div(int i) {
+    if constexpr (H <= 4) return gh_w<H>(i);
+    else return __ldg(H == 10 ? &d_gh_w10[i] : &d_gh_w20[i]);
+}
 
 template <int H, int D> struct NodeCount { static constexpr int value = H * NodeCount<H, D - 1>::value; };
 template <int H> struct NodeCount<H, 0> { static constexpr int value = 1; };
@@ -61,10 +89,13 @@ __device__ __forceinline__ Vec<D> gh_point(const Mat<D>& L, const Vec<D>& m, con
     return X;
 }
 
+// (groups narrower than a warp: only the lanes of the group take part -- neighbouring groups of the same warp may
+// be on another branch, e.g. the group of a sequence's last grid point, which has no transition term)
 template <int G> __device__ __forceinline__ double group_sum(double v) {
     if (G > 1) {
+        const unsigned mask = (G >= 32) ? 0xffffffffu : (((1u << (G & 31)) - 1u) << ((threadIdx.x & 31u) & ~(unsigned)(G - 1)));
 #pragma unroll
-        for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o, G);
+        for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o, G);
     }
     return v;
 }

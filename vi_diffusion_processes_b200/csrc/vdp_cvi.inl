@@ -38,6 +38,20 @@ static int launch_kl_grad(const DriftParams& P, const double* q_host, double dt,
             return VDP_OK;
         }
     }
+    // D >= 2, polynomial drift: the exact low-order rule (DriftPoly / ExactOrder in drifts.cuh), a few lanes per grid
+    // point; VDP_FLAG_GH_QUADRATURE / the GH_QUADRATURE switch keep the reference's 20 points per dimension
+    if constexpr (D >= 2 && DriftPoly<DRIFT>::degree > 0) {
+        if (!gh_loops && !g_cfg.gh_quadrature) {
+            constexpr int HX = ExactOrder<DRIFT>::H, GX = KlExactGroup<D>::value;
+            constexpr int threads = KlShape<D, HX, GX>::threads, groups = threads / GX;
+            const unsigned gridx = (unsigned)((total + groups - 2) / (groups - 1));
+            k_kl_grad<DRIFT, D, HX, GX><<<gridx, threads, groups * sizeof(KlHandoff<D>), st>>>(
+                P, host_mat<D>(q_host), dt, pi_factor(D), time_grid, host_vec<D>(x0_mu), host_mat<D>(x0_cov), Aq, m, Sd,
+                terms, g1, gd, gs, upd, lr, sc1, scd, B, N, status, node0, node1, nat);
+            VDP_CHECK_LAUNCH();
+            return VDP_OK;
+        }
+    }
     k_kl_grad<DRIFT, D, 20, KL::G><<<grid, KL::threads, smem, st>>>(
         P, host_mat<D>(q_host), dt, pi_factor(D), time_grid, host_vec<D>(x0_mu), host_mat<D>(x0_cov), Aq, m, Sd,
         terms, g1, gd, gs, upd, lr, sc1, scd, B, N, status, node0, node1, nat);
@@ -174,6 +188,14 @@ static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams&
                 p.qcholP0, p.pmu0, p.pcholP0, w.terms, B, N, p.status, node0, node1);
             VDP_CHECK_LAUNCH();
         }
+    } else if (cnt > 0 && D >= 2 && DriftPoly<DRIFT>::degree > 0 && !(p.flags & VDP_FLAG_GH_QUADRATURE) &&
+               !g_cfg.gh_quadrature) {
+        // exact low-order rule of a polynomial drift, one thread per grid point (value only: little state per thread)
+        constexpr int HX = (D >= 2) ? ExactOrder<DRIFT>::H : 20;
+        k_kl_value<DRIFT, D, HX, 1><<<grid_for(cnt, kPtBlock), kPtBlock, 0, st>>>(
+            P, host_mat<D>(p.q), p.dt, pi_factor(D), p.qA, p.qb, p.qcholQ, p.fx_mus, p.fx_covs, p.qmu0, p.qcholP0,
+            p.pmu0, p.pcholP0, w.terms, B, N, p.status, node0, node1);
+        VDP_CHECK_LAUNCH();
     } else if (cnt > 0) {
         k_kl_value<DRIFT, D, 20, G><<<grid_for(cnt * G, kPtBlock), kPtBlock, 0, st>>>(
             P, host_mat<D>(p.q), p.dt, pi_factor(D), p.qA, p.qb, p.qcholQ, p.fx_mus, p.fx_covs, p.qmu0, p.qcholP0,
