@@ -36,10 +36,15 @@ def test_cvi_checkpoint_round_trip(tmp_path):
     assert set(d.keys()) == set(vio.CVI_MODEL_KEYS)
     assert d["girsanov_sites_nat2_subdiag"].shape == (200, 1, 1) and d["data_sites_nat1"].shape == (10, 1)
     b = vio.load_cvi_model(str(tmp_path / "cvi_model.npz"), mk_cvi())
-    assert float(a.classic_elbo()) == float(b.classic_elbo())
-    assert torch.equal(a.fx_mus, b.fx_mus) and torch.equal(a.fx_covs, b.fx_covs)
-    # training continues identically from the restored sites
-    assert float(a.site_update(0.5, 0.5)) == float(b.site_update(0.5, 0.5))
+    assert float(a.classic_elbo()) == float(b.classic_elbo())       # both rebuilt from the same site tensors
+    # a's stored marginals are those of its last site update, which carried the natural parameters theta along and
+    # held the girsanov sites inside them; b's come from theta rebuilt as nat(p) + g + data sites out of the saved
+    # sites: the same numbers up to the rounding of that sum
+    for x, r in ((a.fx_mus, b.fx_mus), (a.fx_covs, b.fx_covs)):
+        assert float((x - r).abs().max()) <= 1e-12 * float(r.abs().max())
+    # training continues from the restored sites as it does from the live model
+    ea, eb = float(a.site_update(0.5, 0.5)), float(b.site_update(0.5, 0.5))
+    assert abs(ea - eb) <= 1e-11 * abs(eb)
 
 
 def test_vi_gp_checkpoint_round_trip(tmp_path):
