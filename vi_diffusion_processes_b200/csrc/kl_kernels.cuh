@@ -726,4 +726,48 @@ static __global__ void k_reduce_terms(const double* __restrict__ terms, int64_t 
     if (threadIdx.x == 0) out[b] = sh[0];
 }
 
+// Long sequences (one chain of 10^7 grid points is ONE block above): first the sum of every chunk of kReduceChunk terms
+// into the chunk's first slot -- a block reads and writes its own chunk only -- then the strided sum of those.  The
+// order of the additions is fixed by (n, chunk), so the result is reproducible.  `terms` is scratch and is overwritten.
+constexpr int64_t kReduceChunk = 8192;
+static __global__ void k_reduce_chunks(double* __restrict__ terms, int64_t n, int64_t nchunks) {
+    __shared__ double sh[256];
+    const int64_t b = blockIdx.x / nchunks, c = blockIdx.x % nchunks;
+    double* t = terms + b * n + c * kReduceChunk;
+    const int64_t cnt = min(kReduceChunk, n - c * kReduceChunk);
+    double acc = 0.0;
+    for (int64_t k = threadIdx.x; k < cnt; k += blockDim.x) acc += t[k];
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = blockDim.x / 2; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) t[0] = sh[0];
+}
+static __global__ void k_reduce_strided(const double* __restrict__ terms, int64_t n, int64_t nchunks,
+                                        double* __restrict__ out) {
+    __shared__ double sh[256];
+    const int64_t b = blockIdx.x;
+    double acc = 0.0;
+    for (int64_t c = threadIdx.x; c < nchunks; c += blockDim.x) acc += terms[b * n + c * kReduceChunk];
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = blockDim.x / 2; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[b] = sh[0];
+}
+// out[b] = sum_k terms[b, k]; terms may be overwritten
+static inline void launch_reduce_terms(double* terms, int64_t n, double* out, int64_t B, cudaStream_t st) {
+    if (n >= 8 * kReduceChunk && B <= 1024) {
+        const int64_t nchunks = (n + kReduceChunk - 1) / kReduceChunk;
+        k_reduce_chunks<<<(unsigned)(B * nchunks), 256, 0, st>>>(terms, n, nchunks);
+        k_reduce_strided<<<(unsigned)B, 256, 0, st>>>(terms, n, nchunks, out);
+    } else {
+        k_reduce_terms<<<(unsigned)B, 256, 0, st>>>(terms, n, out);
+    }
+}
+
 }  // namespace vdp

@@ -105,6 +105,36 @@ __global__ void k_seg_scan(const typename Ops::Elem* __restrict__ elems, const t
     }
 }
 
+// The same carries for FEW sequences with MANY segments (one long chain split in time): one block per sequence, one
+// thread per segment, block-wide scan of the segment elements -- log depth instead of nseg sequential compositions
+// (592 segments of a D = 3 chain: 1 ms -> 0.03 ms per scan).  nseg <= T.
+template <class Ops, int T>
+__global__ void __launch_bounds__(T) k_seg_scan_par(const typename Ops::Elem* __restrict__ elems,
+                                                    const typename Ops::State* __restrict__ init,
+                                                    typename Ops::State* __restrict__ carry, int nseg, int reverse) {
+    __shared__ typename Ops::Elem wtot[T / 32];
+    const int64_t b = blockIdx.x;
+    const int i = threadIdx.x;                       // position in sweep order
+    const int s = reverse ? nseg - 1 - i : i;
+    typename Ops::Elem e = Ops::identity();
+    if (i < nseg) e = elems[b * nseg + s];
+    typename Ops::Elem total;
+    const typename Ops::Elem excl = block_exclusive_scan<Ops, T>(e, wtot, total);
+    if (i < nseg) carry[b * nseg + s] = Ops::apply(excl, init[b]);
+}
+// composition of all segment elements of one sequence (the rank total of the time-sharded sweeps)
+template <class Ops, int T>
+__global__ void __launch_bounds__(T) k_seg_total_par(const typename Ops::Elem* __restrict__ elems, int nseg, int reverse,
+                                                     typename Ops::Elem* __restrict__ total_out) {
+    __shared__ typename Ops::Elem wtot[T / 32];
+    const int i = threadIdx.x;
+    typename Ops::Elem e = Ops::identity();
+    if (i < nseg) e = elems[reverse ? nseg - 1 - i : i];
+    typename Ops::Elem total;
+    block_exclusive_scan<Ops, T>(e, wtot, total);
+    if (i == 0) *total_out = total;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // forward Cholesky over one staged tile: sKd holds X_kk for nodes [0, cnt] of the tile (in: X, out: L_kk),
 // sKs holds X_{k+1,k} for transitions [0, cnt) (in: X, out: L_{k+1,k}); the factorised matrix is

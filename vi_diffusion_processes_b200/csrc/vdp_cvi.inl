@@ -202,7 +202,7 @@ static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams&
             p.pmu0, p.pcholP0, w.terms, B, N, p.status, node0, node1);
         VDP_CHECK_LAUNCH();
     }
-    k_reduce_terms<<<(unsigned)B, 256, 0, st>>>(w.terms, N + 1, p.kl);
+    launch_reduce_terms(w.terms, N + 1, p.kl, B, st);
     VDP_CHECK_LAUNCH();
     k_elbo_combine<<<grid_for(B, kPtBlock), kPtBlock, 0, st>>>(p.ve, p.kl, p.elbo, B);
     VDP_CHECK_LAUNCH();
@@ -365,7 +365,7 @@ int vdp_cvi_kl_and_grad(int drift_id, const double* params_host, const double* q
                                             gd, gs, 0, 0.0, nullptr, nullptr, B, N, status, st);
         if (rc) return rc;
     }));
-    k_reduce_terms<<<(unsigned)B, 256, 0, st>>>(terms, N + 1, kl);
+    launch_reduce_terms(terms, N + 1, kl, B, st);
     VDP_CHECK_LAUNCH();
     return VDP_OK;
 }

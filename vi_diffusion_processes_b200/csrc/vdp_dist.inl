@@ -15,6 +15,13 @@
 
 namespace vdp {
 
+// staging buffers of the time-sharded naturals_to_ssm sweep (its D = 3 tile is 60 KB: a second buffer leaves one CTA
+// of 64 threads per SM)
+#ifndef VDP_DIST_STAGES_N
+#define VDP_DIST_STAGES_N 1
+#endif
+constexpr int kDistStagesN = VDP_DIST_STAGES_N;
+
 template <class Ops>
 __global__ void k_seg_total(const typename Ops::Elem* __restrict__ el, int nseg, int reverse,
                             typename Ops::Elem* __restrict__ total) {
@@ -22,6 +29,16 @@ __global__ void k_seg_total(const typename Ops::Elem* __restrict__ el, int nseg,
     typename Ops::Elem t = Ops::identity();
     for (int i = 0; i < nseg; ++i) t = Ops::combine(t, el[reverse ? nseg - 1 - i : i]);
     *total = t;
+}
+
+// composition of all nseg segment elements of the rank's stretch (block-wide scan when there are many)
+template <class Ops>
+static inline void launch_seg_total(const typename Ops::Elem* el, int nseg, int reverse, typename Ops::Elem* total,
+                                    cudaStream_t st) {
+    if (nseg >= 16 && nseg <= 128) k_seg_total_par<Ops, 128><<<1, 128, 0, st>>>(el, nseg, reverse, total);
+    else if (nseg > 128 && nseg <= 512) k_seg_total_par<Ops, 512><<<1, 512, 0, st>>>(el, nseg, reverse, total);
+    else if (nseg > 512 && nseg <= 1024) k_seg_total_par<Ops, 1024><<<1, 1024, 0, st>>>(el, nseg, reverse, total);
+    else k_seg_total<Ops><<<1, 32, 0, st>>>(el, nseg, reverse, total);
 }
 
 // incoming carry of `rank`: the natural initial state (held by rank 0 forward / rank G-1 backward) pushed
@@ -89,7 +106,7 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
                 p.in[0], p.in[1], p.scaleD, p.scaleS, p.out[0], p.out[1], 1, N, pl.nseg, pl.seg_len, nullptr,
                 (Mat<D>*)init_blob, b.el, p.status, first);
             VDP_CHECK_LAUNCH();
-            k_seg_total<Ops><<<1, 32, 0, st>>>(b.el, pl.nseg, 0, (typename Ops::Elem*)total_blob);
+            launch_seg_total<Ops>(b.el, pl.nseg, 0, (typename Ops::Elem*)total_blob, st);
         } else {
             if ((rc = dist_carries<Ops>(b, totals, inits, p.rank, p.nranks, 0, pl.nseg, st))) return rc;
             if ((rc = allow_smem(k_chol_tiled<D, C::T, C::Lc, SWEEP_FULL, kSweepStages>, smem))) return rc;
@@ -112,7 +129,7 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
                 p.in[0], p.in[1], p.in[2], p.in[3], p.in[4], p.out[0], p.out[1], p.out[2], 1, N, pl.nseg, pl.seg_len,
                 nullptr, (typename Ops::State*)init_blob, b.el, p.status, first, last);
             VDP_CHECK_LAUNCH();
-            k_seg_total<Ops><<<1, 32, 0, st>>>(b.el, pl.nseg, 0, (typename Ops::Elem*)total_blob);
+            launch_seg_total<Ops>(b.el, pl.nseg, 0, (typename Ops::Elem*)total_blob, st);
         } else {
             if ((rc = dist_carries<Ops>(b, totals, inits, p.rank, p.nranks, 0, pl.nseg, st))) return rc;
             if ((rc = allow_smem(k_marg_tiled<D, C::T, C::Lm, SWEEP_FULL>, smem))) return rc;
@@ -135,7 +152,7 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
                 p.in[0], p.in[1], p.out[0], p.out[1], 1, N, pl.nseg, pl.seg_len, nullptr, (Mat<D>*)init_blob, b.el,
                 last);
             VDP_CHECK_LAUNCH();
-            k_seg_total<Ops><<<1, 32, 0, st>>>(b.el, pl.nseg, 1, (typename Ops::Elem*)total_blob);
+            launch_seg_total<Ops>(b.el, pl.nseg, 1, (typename Ops::Elem*)total_blob, st);
         } else {
             if ((rc = dist_carries<Ops>(b, totals, inits, p.rank, p.nranks, 1, pl.nseg, st))) return rc;
             if ((rc = allow_smem(k_invband_tiled<D, C::T, C::Li, SWEEP_FULL>, smem))) return rc;
@@ -148,30 +165,30 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
     case VDP_SWEEP_NAT2SSM: {
         using OpsS = AffSymOps<D>;
         using OpsY = AffVecOps<D>;
-        constexpr size_t smem = nat2ssm_tiled_smem<D, C::T, C::Ln>();
+        constexpr size_t smem = nat2ssm_tiled_smem<D, C::T, C::Ln, false, false, kDistStagesN>();
         const SegPlan pl = plan_segments(1, N, C::T * C::Ln, true);
         DistBufs<OpsS> bs;
         DistBufs<OpsY> by;
         if (!dist_take<OpsS>(sc, pl.nseg, bs) || !dist_take<OpsY>(sc, pl.nseg, by)) break;
 #define VDP_N2S_ARGS(MODE_)                                                                                        \
-    k_nat2ssm_tiled<D, C::T, C::Ln, MODE_><<<pl.nseg, C::T, smem, st>>>(                                             \
+    k_nat2ssm_tiled<D, C::T, C::Ln, MODE_, false, false, kDistStagesN><<<pl.nseg, C::T, smem, st>>>(                                             \
         p.in[0], p.in[1], p.in[2], p.in[3], p.in[4], p.out[0], p.out[1], p.out[2], p.out[3], p.out[4], 1, N, pl.nseg,  \
         pl.seg_len, bs.carry, by.carry, (Mat<D>*)init_blob, (Vec<D>*)init_blob, bs.el, by.el, p.status, first, last)
         if (phase == 0 && p.stage == 0) {
-            if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY>, smem))) return rc;
+            if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY, false, false, kDistStagesN>, smem))) return rc;
             VDP_N2S_ARGS(SWEEP_SUMMARY);
             VDP_CHECK_LAUNCH();
-            k_seg_total<OpsS><<<1, 32, 0, st>>>(bs.el, pl.nseg, 1, (typename OpsS::Elem*)total_blob);
+            launch_seg_total<OpsS>(bs.el, pl.nseg, 1, (typename OpsS::Elem*)total_blob, st);
         } else if (phase == 0) {
             if ((rc = dist_carries<OpsS>(bs, p.prev_totals, p.prev_inits, p.rank, p.nranks, 1, pl.nseg, st))) return rc;
-            if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2>, smem))) return rc;
+            if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_SUMMARY2, false, false, kDistStagesN>, smem))) return rc;
             VDP_N2S_ARGS(SWEEP_SUMMARY2);
             VDP_CHECK_LAUNCH();
-            k_seg_total<OpsY><<<1, 32, 0, st>>>(by.el, pl.nseg, 1, (typename OpsY::Elem*)total_blob);
+            launch_seg_total<OpsY>(by.el, pl.nseg, 1, (typename OpsY::Elem*)total_blob, st);
         } else {
             // the Sigma carries were left in the workspace by the stage-1 summary
             if ((rc = dist_carries<OpsY>(by, totals, inits, p.rank, p.nranks, 1, pl.nseg, st))) return rc;
-            if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL>, smem))) return rc;
+            if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, false, false, kDistStagesN>, smem))) return rc;
             VDP_N2S_ARGS(SWEEP_FULL);
         }
 #undef VDP_N2S_ARGS

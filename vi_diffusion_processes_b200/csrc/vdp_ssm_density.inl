@@ -167,7 +167,7 @@ int vdp_ssm_kl_divergence(const double* A1, const double* b1, const double* chol
             A1, m1, S1, cholP01, cholQ1, m2, thd, ths, Ld, Ls, cholP02, cholQ2, terms, B, N);
         VDP_CHECK_LAUNCH();
     });
-    k_reduce_terms<<<(unsigned)B, 256, 0, st>>>(terms, N + 1, kl);
+    launch_reduce_terms(terms, N + 1, kl, B, st);
     VDP_CHECK_LAUNCH();
     return VDP_OK;
 }
