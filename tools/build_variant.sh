@@ -8,8 +8,12 @@ NAME="$1"; FLAGS="$2"
 OBJ=/tmp/vdp_b200_obj
 VOBJ=/tmp/vdp_b200_var_$NAME
 mkdir -p "$VOBJ" "$HERE/variants"
-cp $OBJ/tu_core.o $OBJ/tu_prior.o $OBJ/tu_vgp.o $OBJ/tu_dist.o "$VOBJ/"
-nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -diag-suppress 177 $FLAGS \
-     -c -o "$VOBJ/tu_cvi.o" "$HERE/vi_diffusion_processes_b200/csrc/tu_cvi.cu"
+cp $OBJ/tu_core.o $OBJ/tu_prior.o $OBJ/tu_vgp.o $OBJ/tu_dist.o $OBJ/tu_cvi.o "$VOBJ/"
+# VDP_VARIANT_TUS="cvi dist": the units rebuilt with the extra flags (default: cvi)
+for tu in ${VDP_VARIANT_TUS:-cvi}; do
+  nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -diag-suppress 177 $FLAGS \
+       -c -o "$VOBJ/tu_$tu.o" "$HERE/vi_diffusion_processes_b200/csrc/tu_$tu.cu" &
+done
+wait
 nvcc -gencode arch=compute_100a,code=sm_100a -shared -o "$HERE/variants/libvdp_$NAME.so" "$VOBJ"/tu_*.o
 echo "built variants/libvdp_$NAME.so"

@@ -386,20 +386,21 @@ struct KlHandoff { double gm[D]; double gS[D * D]; };
 template <int G> struct KlBounds {
     static constexpr int threads = (G == 1) ? 128 : 256, blocks = (G == 1) ? VDP_KL_MINBLOCKS : VDP_KLG_MINBLOCKS;
 };
-// D >= 2 with the exact low-order rule of a polynomial drift (ExactOrder: 4 .. 64 nodes per grid point): a small group
-// of lanes per grid point -- every lane repeats the pointwise algebra around the quadrature, so a whole warp per
-// grid point would spend its time there -- and a register budget for the D x D blocks each lane holds
+// D >= 2 with the exact low-order rule of a polynomial drift (ExactOrder: 4 .. 64 nodes per grid point): every lane of
+// a group repeats the pointwise algebra around the quadrature, which now outweighs the node loop, so one thread per
+// grid point does best (measured on B200, kl_grad phase: D = 2 VdP 4096 x 500: 1 lane 0.26 ms, 2: 0.45, 4: 0.79;
+// D = 3 OU 2 x 10^5: 1 lane 0.088 ms, 2: 0.118, 4: 0.194, 8: 0.365); the register budget is for the D x D blocks
 #ifndef VDP_KLX_G2
-#define VDP_KLX_G2 2
+#define VDP_KLX_G2 1
 #endif
 #ifndef VDP_KLX_G3
-#define VDP_KLX_G3 4
+#define VDP_KLX_G3 1
 #endif
 #ifndef VDP_KLX_MINBLOCKS2
-#define VDP_KLX_MINBLOCKS2 3   /* D = 2: 152 registers */
+#define VDP_KLX_MINBLOCKS2 4
 #endif
 #ifndef VDP_KLX_MINBLOCKS3
-#define VDP_KLX_MINBLOCKS3 2   /* D = 3: 168 registers spill 120-200 bytes */
+#define VDP_KLX_MINBLOCKS3 2
 #endif
 template <int D> struct KlExactGroup { static constexpr int value = (D == 2) ? VDP_KLX_G2 : VDP_KLX_G3; };
 // launch shape of k_kl_grad by (D, H, G): threads per block and resident blocks the register budget is cut for
