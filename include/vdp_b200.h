@@ -542,8 +542,14 @@ int vdp_vgp_sweep(const vdp_vgp_problem* problem_host, void* stream);
  *                      N_local = halo as for A), in[3] mu0, in[4] cholP0 (rank 0 only);
  *                      out[0] m [N_local+1, D], out[1] Ld [N_local+1], out[2] Ls [N_local]
  *   VDP_SWEEP_INVBAND  in[0] Ld, in[1] Ls; out[0] Sd [N_local (+1 on the last rank)], out[1] Ss or NULL
+ *   VDP_SWEEP_MEAN     in[0] A [N_local], in[1] b [N_local], in[2] mu0 (rank 0 only); out[0] m [N_local+1, D]
+ *                      (marginal means alone, state_space_model.py:251)
+ * VDP_SWEEP_NAT2SSM with out[5] = Sd [N_local (+1 on the last rank), D, D] != NULL also writes the marginal
+ * covariances of the Gaussian the naturals describe (the diagonal of the inverse band the sweep walks through);
+ * together with VDP_SWEEP_MEAN that is the rebuild's marginals without VDP_SWEEP_MARG + VDP_SWEEP_INVBAND (a second
+ * factorisation of the same precision).
  * ---------------------------------------------------------------------------------------------- */
-enum { VDP_SWEEP_CHOL = 0, VDP_SWEEP_NAT2SSM = 1, VDP_SWEEP_MARG = 2, VDP_SWEEP_INVBAND = 3 };
+enum { VDP_SWEEP_CHOL = 0, VDP_SWEEP_NAT2SSM = 1, VDP_SWEEP_MARG = 2, VDP_SWEEP_INVBAND = 3, VDP_SWEEP_MEAN = 4 };
 
 typedef struct vdp_dist_sweep {
     int32_t kind, stage;

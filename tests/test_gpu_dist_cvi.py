@@ -89,3 +89,35 @@ def test_time_sharded_update_3d():
             # (OU prior with zero offsets: nat_1(p) and the exact g1 are 0, theta_1 is made of the data sites)
             scale = max(float((t[0] + want).abs().max()), float(single.d1.abs().max()) if k == "g1" else 0.0)
             assert _close(_gather(sh, k), want, 1e-11, scale=scale), k
+
+
+@pytest.mark.parametrize("D,R,N", [(1, 3, 3100), (2, 3, 1500), (3, 4, 900)])
+def test_time_sharded_marginals_from_first_factor(D, R, N, vdp_cfg):
+    """The time-sharded rebuild takes the marginal covariances from the backward sweep of naturals_to_ssm and the means
+    from a mean-only forward sweep (VDP_SWEEP_MEAN, VDP_SWEEP_NAT2SSM out[5]); ``refactor_precision=True`` keeps the
+    reference's route (precision rebuilt from the SSM, second factorisation, inverse band: gauss_markov.py:107-117).
+    Same update to rounding, several segments per rank."""
+    from vi_diffusion_processes_b200.dist_cvi import TimeShardedCvi
+    from vi_diffusion_processes_b200.dist_time import Comm
+    from vi_diffusion_processes_b200.markovflow.sde import sde as sde_mod
+    vdp_cfg(SWEEPS="tiled", NSEG=3)
+    did, params = {1: (sde_mod.DRIFT_DW, [4.0, 1.0]), 2: (sde_mod.DRIFT_VDP, [1.0, 1.0]),
+                   3: (sde_mod.DRIFT_OU_ND, [0.5])}[D]
+    rng = np.random.default_rng(40 + D)
+    n_obs = 17
+    grid = np.round(np.arange(N + 1) * 0.005, 6)
+    idx = np.sort(rng.choice(N + 1, n_obs, replace=False))
+    y = rng.normal(size=(n_obs, D)) * 0.3 + 1.0
+    args = (did, params, np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.ones(D), 0.05 * np.eye(D))
+    a = TimeShardedCvi(*args, comm=Comm.emulated(R))
+    c = TimeShardedCvi(*args, comm=Comm.emulated(R), refactor_precision=True)
+    for it in range(3):
+        ea, ec = a.site_update(0.5, 0.5), c.site_update(0.5, 0.5)
+        a.check_status()
+        c.check_status()
+        assert abs(ea - ec) <= 1e-11 * abs(ec), (it, ea, ec)
+        for k in ("fx_mus", "fx_covs", "qA", "qb", "qcholQ"):
+            assert _close(_gather(a, k), _gather(c, k), 1e-10), (it, k)
+        if it == 0:
+            a.relinearize()
+            c.relinearize()

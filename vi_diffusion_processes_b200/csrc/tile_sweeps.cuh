@@ -514,7 +514,7 @@ __global__ void __launch_bounds__(T)
 k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const double* __restrict__ mu0,
              double* __restrict__ m, int64_t B, int64_t N, int nseg, int64_t seg_len,
              const Vec<D>* __restrict__ carry_in, Vec<D>* __restrict__ init_out,
-             AffVecElem<D>* __restrict__ seg_elem, MeanKlArgs kl = MeanKlArgs()) {
+             AffVecElem<D>* __restrict__ seg_elem, MeanKlArgs kl = MeanKlArgs(), int first = 1) {
     constexpr int DD = D * D, TL = T * L;
     constexpr bool KL = (DRIFT >= 0) && (MODE == SWEEP_FULL);
     static_assert(DRIFT < 0 || D == 1, "the fused KL terms are scalar");
@@ -544,8 +544,9 @@ k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
         mbar_arrive_expect_tx(bar, bytes);
     };
     if (threadIdx.x == 0 && ntiles > 0) issue(0);
+    // first = 0 (time-sharded ranks after the first): the chain starts from the carry of the ranks before it
     Vec<D> st = vec_zero<D>();
-    if (MODE == SWEEP_FULL && seg > 0) st = carry_in[b * nseg + seg];
+    if (MODE == SWEEP_FULL && (seg > 0 || !first)) st = carry_in[b * nseg + seg];
     typename Ops::Elem seg_tot = Ops::identity();
     for (int ti = 0; ti < ntiles; ++ti) {
         const int64_t tk = t0 + (int64_t)ti * TL;
@@ -571,8 +572,10 @@ k_mean_tiled(const double* __restrict__ A, const double* __restrict__ bo, const 
         double* sS = base + SM + SV + (KL ? tile_off(kl.Sd + (b * (N + 1) + tk)) : 0);       // S of node i (KL only)
         double* sQ = base + SM + SV + S1 + (KL ? tile_off(kl.cholQ + (b * N + tk)) : 0);     // chol Q of transition i
         if (seg == 0 && tk == 0) {
-            st = vec_load<D>(mu0 + b * D);
-            if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = st;
+            if (first) {
+                st = vec_load<D>(mu0 + b * D);
+                if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = st;
+            }
             if (MODE == SWEEP_FULL && threadIdx.x == 0) vec_store<D>(m + b * (N + 1) * D, st);
         }
         const int k0 = threadIdx.x * L;

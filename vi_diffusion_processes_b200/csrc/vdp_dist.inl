@@ -188,10 +188,45 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
         } else {
             // the Sigma carries were left in the workspace by the stage-1 summary
             if ((rc = dist_carries<OpsY>(by, totals, inits, p.rank, p.nranks, 1, pl.nseg, st))) return rc;
-            if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, false, false, kDistStagesN>, smem))) return rc;
-            VDP_N2S_ARGS(SWEEP_FULL);
+            if (p.out[5]) {   // marginal covariances on the way
+                constexpr size_t smem_cov = nat2ssm_tiled_smem<D, C::T, C::Ln, false, true, kDistStagesN>();
+                if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, false, true, kDistStagesN>, smem_cov)))
+                    return rc;
+                k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, false, true, kDistStagesN><<<pl.nseg, C::T, smem_cov, st>>>(
+                    p.in[0], p.in[1], p.in[2], p.in[3], p.in[4], p.out[0], p.out[1], p.out[2], p.out[3], p.out[4], 1, N,
+                    pl.nseg, pl.seg_len, bs.carry, by.carry, (Mat<D>*)init_blob, (Vec<D>*)init_blob, bs.el, by.el,
+                    p.status, first, last, p.out[5]);
+            } else {
+                if ((rc = allow_smem(k_nat2ssm_tiled<D, C::T, C::Ln, SWEEP_FULL, false, false, kDistStagesN>, smem)))
+                    return rc;
+                VDP_N2S_ARGS(SWEEP_FULL);
+            }
         }
 #undef VDP_N2S_ARGS
+        VDP_CHECK_LAUNCH();
+        return VDP_OK;
+    }
+    case VDP_SWEEP_MEAN: {
+        using Ops = AffVecOps<D>;
+        constexpr int L = (D == 1) ? C::Lm : 2 * C::Lm;
+        constexpr size_t smem = mean_tiled_smem<D, C::T, L, false, kStagesM>();
+        const SegPlan pl = plan_segments(1, N, C::T * L, true);
+        DistBufs<Ops> b;
+        if (!dist_take<Ops>(sc, pl.nseg, b)) break;
+        if (phase == 0) {
+            if ((rc = allow_smem(k_mean_tiled<D, C::T, L, SWEEP_SUMMARY, -1, kStagesM>, smem))) return rc;
+            k_mean_tiled<D, C::T, L, SWEEP_SUMMARY, -1, kStagesM><<<pl.nseg, C::T, smem, st>>>(
+                p.in[0], p.in[1], p.in[2], p.out[0], 1, N, pl.nseg, pl.seg_len, nullptr, (Vec<D>*)init_blob, b.el,
+                MeanKlArgs(), first);
+            VDP_CHECK_LAUNCH();
+            launch_seg_total<Ops>(b.el, pl.nseg, 0, (typename Ops::Elem*)total_blob, st);
+        } else {
+            if ((rc = dist_carries<Ops>(b, totals, inits, p.rank, p.nranks, 0, pl.nseg, st))) return rc;
+            if ((rc = allow_smem(k_mean_tiled<D, C::T, L, SWEEP_FULL, -1, kStagesM>, smem))) return rc;
+            k_mean_tiled<D, C::T, L, SWEEP_FULL, -1, kStagesM><<<pl.nseg, C::T, smem, st>>>(
+                p.in[0], p.in[1], p.in[2], p.out[0], 1, N, pl.nseg, pl.seg_len, b.carry, nullptr, nullptr, MeanKlArgs(),
+                first);
+        }
         VDP_CHECK_LAUNCH();
         return VDP_OK;
     }
@@ -224,6 +259,7 @@ int vdp_dist_blob_bytes(int kind, int stage, int D, size_t* total_bytes, size_t*
         case VDP_SWEEP_CHOL: *total_bytes = sizeof(SchurElem<kD>); *init_bytes = sizeof(Mat<kD>); break;
         case VDP_SWEEP_MARG: *total_bytes = sizeof(typename MargOps<kD>::Elem); *init_bytes = sizeof(typename MargOps<kD>::State); break;
         case VDP_SWEEP_INVBAND: *total_bytes = sizeof(AffSymElem<kD>); *init_bytes = sizeof(Mat<kD>); break;
+        case VDP_SWEEP_MEAN: *total_bytes = sizeof(AffVecElem<kD>); *init_bytes = sizeof(Vec<kD>); break;
         case VDP_SWEEP_NAT2SSM:
             if (stage == 0) { *total_bytes = sizeof(AffSymElem<kD>); *init_bytes = sizeof(Mat<kD>); }
             else { *total_bytes = sizeof(AffVecElem<kD>); *init_bytes = sizeof(Vec<kD>); }

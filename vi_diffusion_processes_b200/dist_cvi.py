@@ -59,11 +59,12 @@ class TimeShardedCvi:
     """
 
     def __init__(self, drift_id, drift_params, q, time_grid, obs_idx, obs_y, lik_chol, x0_mu, x0_cov, comm: Comm,
-                 device="cuda", stabilize_ssm=True, clip_state_transitions=(-1.0, 1.0)):
+                 device="cuda", stabilize_ssm=True, clip_state_transitions=(-1.0, 1.0), refactor_precision=False):
         tg = np.asarray(time_grid, dtype=np.float64)
         self.N = N = tg.shape[0] - 1
         self.D = D = np.atleast_2d(np.asarray(q)).shape[0]
         self.comm = comm
+        self.refactor_precision = bool(refactor_precision)
         self.device = torch.device(device)
         self.chain = TimeShardedChain(N, D, comm, device=device)
         obs_idx = np.asarray(obs_idx, dtype=np.int64).reshape(-1)
@@ -100,9 +101,19 @@ class TimeShardedCvi:
             self._call(st, "vdp_cvi_full_sites", 0.0, 0.0, C.c_void_p(st.th1.data_ptr()), C.c_void_p(st.thd.data_ptr()),
                        C.c_void_p(st.ths.data_ptr()))
         own = [self._own(st) for st in self.ranks]
-        ssm = self.chain.naturals_to_ssm([o[0] for o in own], [o[1] for o in own], [o[2] for o in own])
-        marg = self.chain.ssm_marginals([o["A"] for o in ssm], [o["b"] for o in ssm], [o["cholQ"] for o in ssm],
-                                        [o["mu0"] for o in ssm], [o["cholP0"] for o in ssm])
+        if self.refactor_precision:
+            # the reference's route (gauss_markov.py:107-117): precision rebuilt from the SSM, factorised again,
+            # diagonal of its inverse band
+            ssm = self.chain.naturals_to_ssm([o[0] for o in own], [o[1] for o in own], [o[2] for o in own])
+            marg = self.chain.ssm_marginals([o["A"] for o in ssm], [o["b"] for o in ssm], [o["cholQ"] for o in ssm],
+                                            [o["mu0"] for o in ssm], [o["cholP0"] for o in ssm])
+        else:
+            # the same matrix is the one naturals_to_ssm started from: its backward sweep writes the marginal
+            # covariances on the way, a mean-only forward sweep follows (as the single-GPU rebuild does)
+            ssm = self.chain.naturals_to_ssm([o[0] for o in own], [o[1] for o in own], [o[2] for o in own],
+                                             want_cov=True)
+            means = self.chain.ssm_means([o["A"] for o in ssm], [o["b"] for o in ssm], [o["mu0"] for o in ssm])
+            marg = [(m, o["S"]) for m, o in zip(means, ssm)]
         blobs = []
         for st, o, (m, S) in zip(self.ranks, ssm, marg):
             e = st.eng

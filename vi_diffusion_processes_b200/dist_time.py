@@ -204,10 +204,13 @@ class TimeShardedChain:
     def _from_prev(self, lasts: List[torch.Tensor]):
         return halo_from_prev(self.comm, lasts)
 
-    def naturals_to_ssm(self, th1: List[torch.Tensor], thd: List[torch.Tensor], ths: List[torch.Tensor]):
+    def naturals_to_ssm(self, th1: List[torch.Tensor], thd: List[torch.Tensor], ths: List[torch.Tensor],
+                        want_cov: bool = False):
         """naturals_to_ssm_params (ssm_gaussian_transformations.py:333-511), time-sharded.
         Returns per local rank a dict: A [n,D,D], b [n,D], cholQ [n,D,D] for its transitions (n = e - s), the
-        node-s factor ``cholQ_prev`` (cholQ of transition s-1; None on rank 0) and mu0 / cholP0 on rank 0."""
+        node-s factor ``cholQ_prev`` (cholQ of transition s-1; None on rank 0) and mu0 / cholP0 on rank 0.
+        ``want_cov``: also ``S`` [n_own, D, D], the marginal covariances of the owned grid points (the diagonal of
+        the inverse band the backward sweep walks through -- no second factorisation needed for them)."""
         D, dev = self.D, self.ranks[0].device
         halo = self._from_next([t[:1].contiguous() for t in thd])
         Kd, Ld, Ls = [], [], []
@@ -229,11 +232,13 @@ class TimeShardedChain:
             qbuf.append(torch.zeros((n + 1, D, D), dtype=F64, device=dev))
             mu0.append(torch.zeros(D, dtype=F64, device=dev))
             cP0.append(torch.zeros((D, D), dtype=F64, device=dev))
+        Sd = [torch.empty((rk.N_local + (1 if rk.last else 0), D, D), dtype=F64, device=dev) if want_cov else None
+              for rk in self.ranks]
 
         def n2s(rk, stage, prev):
             i = idx[id(rk)]
             return rk.sweep(_lib.SWEEP_NAT2SSM, stage, [Ld[i], Ls[i], th1[i], thd[i], ths[i]],
-                            [A[i], bbuf[i][1:], qbuf[i][1:], mu0[i], cP0[i]], prev=prev)
+                            [A[i], bbuf[i][1:], qbuf[i][1:], mu0[i], cP0[i], Sd[i]], prev=prev)
         _run_sweep(self.comm, self.ranks, _lib.SWEEP_NAT2SSM, n2s, D)
         # transition e-1 (output of node e) lives in slot 0 of the next rank
         nb = self._from_next([t[:1].contiguous() for t in bbuf])
@@ -244,8 +249,22 @@ class TimeShardedChain:
                 bbuf[i][-1:] = nb[i]
                 qbuf[i][-1:] = nq[i]
             out.append(dict(A=A[i], b=bbuf[i][1:], cholQ=qbuf[i][1:], cholQ_prev=None if rk.first else qbuf[i][:1],
-                            mu0=mu0[i] if rk.first else None, cholP0=cP0[i] if rk.first else None))
+                            mu0=mu0[i] if rk.first else None, cholP0=cP0[i] if rk.first else None, S=Sd[i]))
         return out
+
+    def ssm_means(self, A: List[torch.Tensor], b: List[torch.Tensor], mu0: List[Optional[torch.Tensor]]):
+        """StateSpaceModel.marginal_means (state_space_model.py:251), time-sharded: per local rank m [n_own, D]."""
+        D, dev = self.D, self.ranks[0].device
+        m = [torch.empty((rk.N_local + 1, D), dtype=F64, device=dev) for rk in self.ranks]
+        idx = {id(rk): i for i, rk in enumerate(self.ranks)}
+        dummy_v = torch.zeros(D, dtype=F64, device=dev)
+
+        def mean(rk, stage, prev):
+            i = idx[id(rk)]
+            return rk.sweep(_lib.SWEEP_MEAN, 0, [A[i].contiguous(), b[i].contiguous(),
+                                                 mu0[i] if rk.first else dummy_v], [m[i]])
+        _run_sweep(self.comm, self.ranks, _lib.SWEEP_MEAN, mean, D)
+        return [m[i][:rk.N_local + (1 if rk.last else 0)] for i, rk in enumerate(self.ranks)]
 
     def ssm_marginals(self, A: List[torch.Tensor], b: List[torch.Tensor], cholQ: List[torch.Tensor],
                       mu0: List[Optional[torch.Tensor]], cholP0: List[Optional[torch.Tensor]]):
