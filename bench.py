@@ -179,22 +179,27 @@ PHASE_TRAFFIC = {
     # consecutive updates carry the naturals of the previous update in the workspace and rewrite them at the observed
     # grid points only (VDP_FLAG_NATURALS_CARRIED): O(n_obs) per sequence instead of a pass over the grid
     "sites_to_nat": (0, 0),
-    "chol_fwd": (0, 2 + 2),           # read thd, ths ; write Ld, Ls
+    # read thd, ths ; write Ld, Ls.  Once per update: the factor of the second rebuild comes out of the fused forward
+    # pass (phase kl_grad)
+    "chol_fwd": (0, 2 + 2),
     # read th1 | Ld, Ls ; write b | A, cholQ, Sd (K blocks rebuilt from L in the tile; the marginal covariances are
     # the diagonal of the inverse band the sweep walks through, so no separate inverse-band sweep)
     # (the rebuild between the two site updates does not write chol Q: 48 and 56 B, 52 on average)
     "nat2ssm_bwd": (1 + 1, 2 + 2.5),
-    # means alone: read b | A ; write m.  The sweep of the second rebuild also reads S, cholQ and adds up the KL
-    # terms of classic_elbo (24 and 40 B per grid step: 32 on average over the two launches of an update)
-    "marg_fwd": (1 + 1, 1 + 1),
+    # mean sweep of the second rebuild: read b | A, S, cholQ ; write m -- it adds up the KL terms of classic_elbo on
+    # its way.  (The means of the first rebuild never leave the fused forward pass.)
+    "marg_fwd": (1 + 1, 1 + 1 + 1),
     "invband_bwd": (0, 2 + 1),        # (only with VDP_FLAG_REFACTOR_PRECISION) read Ld, Ls ; write Sd
-    # sites held in theta between carried updates (VDP_FLAG_SITES_IN_NATURALS): read m, sc1, th1 | A, S, scd, thd, ths ;
-    # write th1 | thd, ths -- theta moves by lr (scatter - dKL/deta); neither the sites nor the prior are touched
-    "kl_grad": (1 + 1 + 1 + 1, 1 + 1 + 1 + 2 + 2),
+    # fused forward pass (csrc/fwd_fused.cuh: means of the first rebuild -> KL gradient -> girsanov update of theta ->
+    # Cholesky factor of the second rebuild): read b, th1 | A, S, thd, ths ; write th1 | thd, ths, Ld, Ls.  The sites
+    # are held in theta between carried updates (VDP_FLAG_SITES_IN_NATURALS); the data-site part of the step is added
+    # at the observed grid points by a per-observation kernel
+    "kl_grad": (1 + 1 + 1, 1 + 1 + 2 + 2 + 2),
     "elbo": (0, 0),                   # variational expectations at the observations + sum of the KL partials
 }
-LAUNCHES_PER_UPDATE = 1 + 4 + 1 + 3 + 3   # kernels of ours in one vdp_cvi_site_update in steady state (data sites,
-#                                           patch + 3 sweeps, kl_grad, 3 sweeps, VE + reduce + combine)
+LAUNCHES_PER_UPDATE = 1 + 3 + 2 + 2 + 3   # kernels of ours in one vdp_cvi_site_update in steady state (data sites;
+#                                           patch + Cholesky + naturals_to_ssm; data step + fused forward pass;
+#                                           naturals_to_ssm + means; VE + reduce + combine)
 
 
 def phase_bytes_per_step(name, D):
@@ -347,6 +352,21 @@ def run_ours(args):
     eng.carry_naturals = False
     ms_gh_full = timed(step_resident, args.steps, 1)
     eng.route_flags, eng.carry_naturals = 0, True
+    # a drift that is not a polynomial (Benes, f = theta tanh(x)): no closed form and no fused forward pass, the
+    # 20-point loops and the three-kernel route are all there is -- what 4 of the reference's 7 drifts get
+    ms_benes = None
+    if not args.quick:
+        from vi_diffusion_processes_b200.markovflow.sde.sde import DRIFT_BENES
+        eng_b = CviEngine(DRIFT_BENES, [1.0], np.ones((1, 1)), grid, idx, y[..., None], [[NOISE_STD]], [X0_MU],
+                          [[X0_COV]], device=device)
+        ms_benes = timed(lambda: eng_b.site_update(0.1, 0.1), args.steps, 2)   # (same kernels at any step size; the
+        try:                                                                   # bench data come from a double well)
+            eng_b.check_status()
+            benes_ok = True
+        except _lib.VdpError:
+            benes_ok = False
+        del eng_b
+        torch.cuda.empty_cache()
     # nvidia-smi samples every 100 ms: keep the same load running (untimed) until at least ~0.6 s have been sampled
     while time.perf_counter() - t_load < 0.6:
         step_resident()
@@ -432,6 +452,11 @@ def run_ours(args):
         "clocks": clocks,
         "variants": {"gh20_loops": {"ms_per_step": ms_gh / args.steps,
                                     "value": steps_total * args.steps / (ms_gh * 1e-3)},
+                     "benes_drift_gh20_loops": {"ms_per_step": ms_benes / args.steps,
+                                                "value": steps_total * args.steps / (ms_benes * 1e-3),
+                                                "status_ok": benes_ok, "step_sizes": 0.1,
+                                                "note": "f = tanh(x): not a polynomial, so neither the closed-form "
+                                                        "moments nor the fused forward pass apply"},
                      "gh20_loops_naturals_recomputed_every_update": {
                          "ms_per_step": ms_gh_full / args.steps,
                          "value": steps_total * args.steps / (ms_gh_full * 1e-3)}},

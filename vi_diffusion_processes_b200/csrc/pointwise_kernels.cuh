@@ -358,6 +358,39 @@ __global__ void k_variational_expectation(const double* __restrict__ fx_mus, con
 }
 
 
+// The same sum for few sequences with many observations (one long chain): one block per sequence, the threads stride
+// over the observations, fixed tree over the block.
+template <int D>
+__global__ void __launch_bounds__(256) k_variational_expectation_block(
+    const double* __restrict__ fx_mus, const double* __restrict__ fx_covs, const int64_t* __restrict__ obs_idx,
+    const double* __restrict__ obs_y, Mat<D> lik_chol, double* __restrict__ ve, int64_t B, int64_t N, int64_t n_obs) {
+    __shared__ double sh[256];
+    const int64_t b = blockIdx.x;
+    constexpr int DD = D * D;
+    const Mat<D> inv = chol_inverse(lik_chol);
+    double logdet = 0.0;
+#pragma unroll
+    for (int e = 0; e < D; ++e) logdet += log(fabs(lik_chol(e, e)));
+    double acc = 0.0;
+    for (int64_t j = threadIdx.x; j < n_obs; j += 256) {
+        const int64_t i = b * n_obs + j;
+        const int64_t node = b * (N + 1) + obs_idx[i];
+        const Vec<D> z = trsv(lik_chol, vec_load<D>(obs_y + i * D) - vec_load<D>(fx_mus + node * D));
+        const Mat<D> S = mat_load<D>(fx_covs + node * DD);
+        double tr = 0.0;
+#pragma unroll
+        for (int e = 0; e < DD; ++e) tr += inv.a[e] * S.a[e];
+        acc += -0.5 * tr + (-0.5 * dot(z, z) - logdet - 0.5 * D * 1.8378770664093453);
+    }
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) ve[b] = sh[0];
+}
+
 // Vector-Jacobian product of expectations_to_ssm_params (what tape.gradient(ssm_params, etas,
 // output_gradients=dL_dssm) returns in ssm_natgrad.py:168), pointwise in time.  Transition k touches nodes k
 // and k+1; thread i = (b, k) recomputes the two transitions next to its node and keeps the parts that land

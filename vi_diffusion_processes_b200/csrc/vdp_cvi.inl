@@ -166,8 +166,12 @@ static int run_elbo(const vdp_cvi_problem& p, const CviWs& w, const DriftParams&
     const bool ranged = node1 >= 0;
     const int64_t cnt = (ranged ? node1 : B * (N + 1)) - node0;
     if (ranged) VDP_CHECK_CUDA(cudaMemsetAsync(w.terms, 0, (size_t)B * (N + 1) * sizeof(double), st));
-    k_variational_expectation<D><<<grid_for(B * 32, kPtBlock), kPtBlock, 0, st>>>(
-        p.fx_mus, p.fx_covs, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.ve, B, N, p.n_obs);
+    if (B <= 64 && p.n_obs >= 1024)
+        k_variational_expectation_block<D><<<(unsigned)B, 256, 0, st>>>(
+            p.fx_mus, p.fx_covs, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.ve, B, N, p.n_obs);
+    else
+        k_variational_expectation<D><<<grid_for(B * 32, kPtBlock), kPtBlock, 0, st>>>(
+            p.fx_mus, p.fx_covs, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.ve, B, N, p.n_obs);
     VDP_CHECK_LAUNCH();
     bool closed = false;
     if constexpr (D == 1 && G == 1 && DriftStep1<DRIFT>::kCubic)
