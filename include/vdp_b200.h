@@ -75,6 +75,15 @@ int vdp_btd_cholesky(const double* Kd, const double* Ks, double* Ld, double* Ls,
 int vdp_btd_inverse_band(const double* Ld, const double* Ls, double* Sd, double* Ss,
                          int64_t B, int64_t n, int D, void* stream);
 
+/* Directional derivative of the inverse band: for K = L L^T and a symmetric block-tridiagonal direction
+ * dK = (dKd [B,n,D,D] read through its lower triangle, dKs [B,n-1,D,D] = dK_{k+1,k}) the blocks dSd = d(Sigma_kk),
+ * dSs = d(Sigma_{k+1,k}) of d(K^-1) = -K^-1 dK K^-1 (forward-mode differentiation of cholesky_band and
+ * inverse_from_cholesky_band, block_tri_diag.py:428-440, :318-337).  n >= 2.  Serves the Fisher-norm term of
+ * SSMNaturalGradient(momentum=True): tape.gradient(naturals_to_ssm_params(theta), theta, output_gradients=dL_dssm)
+ * contracted with dL/d eta (ssm_natgrad.py:163-190) is a directional derivative of theta -> eta. */
+int vdp_btd_inverse_band_jvp(const double* Ld, const double* Ls, const double* dKd, const double* dKs,
+                             double* dSd, double* dSs, int64_t B, int64_t n, int D, void* stream);
+
 /* solve_triang_mat  (block_tri_diag.py:339-351 LowerTriangularBlockTriDiagonal.solve)
  * x = L^-1 rhs (transpose = 0) or L^-T rhs (transpose = 1); rhs, x: [B,n,D]; Ls may be NULL */
 int vdp_btd_solve(const double* Ld, const double* Ls, const double* rhs, double* x, int transpose,

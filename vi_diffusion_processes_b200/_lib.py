@@ -124,6 +124,7 @@ SIGNATURES = {
     "vdp_read_status": (i64, [vp, c_i64p, vp]),
     "vdp_btd_cholesky": (C.c_int, [vp, vp, vp, vp, i64, i64, C.c_int, vp, vp]),
     "vdp_btd_inverse_band": (C.c_int, [vp, vp, vp, vp, i64, i64, C.c_int, vp]),
+    "vdp_btd_inverse_band_jvp": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i64, C.c_int, vp]),
     "vdp_btd_solve": (C.c_int, [vp, vp, vp, vp, C.c_int, i64, i64, C.c_int, vp]),
     "vdp_btd_matvec": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_int, i64, i64, C.c_int, vp]),
     "vdp_btd_logdet": (C.c_int, [vp, vp, i64, i64, C.c_int, vp]),

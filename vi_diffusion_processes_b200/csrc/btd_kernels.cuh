@@ -66,6 +66,80 @@ __global__ void k_invband_bwd(const double* __restrict__ Ld, const double* __res
     }
 }
 
+// Directional derivative of (Cholesky factor ->) inverse band with respect to the factorised matrix: for K = L L^T
+// block tridiagonal and a symmetric block-tridiagonal direction dK = (dKd, dKs), the diagonal and sub-diagonal blocks of
+// d(K^-1) = -K^-1 dK K^-1.  Forward-mode differentiation of the two recursions the layer runs (cholesky_band,
+// block_tri_diag.py:428-440; inverse_from_cholesky_band, :318-337):
+//   forward   dS_k = dKd_k - dLs_{k-1} Ls_{k-1}^T - Ls_{k-1} dLs_{k-1}^T,   dL_kk = L_kk Phi(L_kk^-1 dS_k L_kk^-T),
+//             dLs_k = (dKs_k - Ls_k dL_kk^T) L_kk^-T            (Phi: lower triangle, diagonal halved)
+//   backward  U = L_kk^-1, dU = -U dL_kk U, G = Ls_k U, dG = dLs_k U + Ls_k dU,
+//             dSig_{k+1,k} = -dSig_{k+1,k+1} G - Sig_{k+1,k+1} dG,
+//             dSig_kk = dU^T U + U^T dU - dSig_{k+1,k}^T G - Sig_{k+1,k}^T dG.
+// The output arrays hold dL between the two passes.  One thread per sequence (O(n) blocks each): this serves the
+// Fisher-norm term of SSMNaturalGradient(momentum=True) (ssm_natgrad.py:163-190), not a hot path.
+template <int D>
+__global__ void k_invband_jvp(const double* __restrict__ Ld, const double* __restrict__ Ls,
+                              const double* __restrict__ dKd, const double* __restrict__ dKs,
+                              double* __restrict__ dSd, double* __restrict__ dSs, int64_t B, int64_t n) {
+    const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    constexpr int DD = D * D;
+    const double* ld = Ld + b * n * DD;
+    const double* ls = Ls + b * (n - 1) * DD;
+    const double* kd = dKd + b * n * DD;
+    const double* ks = dKs + b * (n - 1) * DD;
+    double* od = dSd + b * n * DD;
+    double* os = dSs + b * (n - 1) * DD;
+    // ---- forward: tangent of the factor
+    Mat<D> dLs_prev = mat_zero<D>(), Ls_prev = mat_zero<D>();
+    for (int64_t k = 0; k < n; ++k) {
+        const Mat<D> Lkk = mat_load<D>(ld + k * DD);
+        Mat<D> dS = mirror_lower(mat_load<D>(kd + k * DD));
+        if (k > 0) dS = dS - mmT(dLs_prev, Ls_prev) - mmT(Ls_prev, dLs_prev);
+        // Phi(L^-1 dS L^-T)
+        Mat<D> X = trsm(Lkk, transpose(trsm(Lkk, dS)));      // L^-1 (L^-1 dS)^T = L^-1 dS^T L^-T, dS symmetric
+        Mat<D> P = mat_zero<D>();
+#pragma unroll
+        for (int i = 0; i < D; ++i)
+#pragma unroll
+            for (int j = 0; j <= i; ++j) P(i, j) = (i == j) ? 0.5 * X(i, j) : X(i, j);
+        const Mat<D> dLkk = mm(Lkk, P);
+        mat_store<D>(od + k * DD, dLkk);
+        if (k < n - 1) {
+            const Mat<D> Lsk = mat_load<D>(ls + k * DD);
+            const Mat<D> R = mat_load<D>(ks + k * DD) - mmT(Lsk, dLkk);     // dKs_k - Ls_k dL_kk^T
+            const Mat<D> dLsk = transpose(trsm(Lkk, transpose(R)));         // R L_kk^-T
+            mat_store<D>(os + k * DD, dLsk);
+            dLs_prev = dLsk;
+            Ls_prev = Lsk;
+        }
+    }
+    // ---- backward: tangent of the inverse band
+    Mat<D> S, dS;
+    {
+        const Mat<D> U = trsm(mat_load<D>(ld + (n - 1) * DD), mat_eye<D>());
+        const Mat<D> dU = -1.0 * mm(U, mm(mat_load<D>(od + (n - 1) * DD), U));
+        S = Tmm(U, U);
+        dS = Tmm(dU, U) + Tmm(U, dU);
+        mat_store<D>(od + (n - 1) * DD, dS);
+    }
+    for (int64_t k = n - 2; k >= 0; --k) {
+        const Mat<D> U = trsm(mat_load<D>(ld + k * DD), mat_eye<D>());
+        const Mat<D> dU = -1.0 * mm(U, mm(mat_load<D>(od + k * DD), U));
+        const Mat<D> Lsk = mat_load<D>(ls + k * DD);
+        const Mat<D> G = mm(Lsk, U);
+        const Mat<D> dG = mm(mat_load<D>(os + k * DD), U) + mm(Lsk, dU);
+        const Mat<D> Ssub = -1.0 * mm(S, G);
+        const Mat<D> dSsub = -1.0 * (mm(dS, G) + mm(S, dG));
+        const Mat<D> Skk = Tmm(U, U) - Tmm(Ssub, G);
+        const Mat<D> dSkk = (Tmm(dU, U) + Tmm(U, dU)) - (Tmm(dSsub, G) + Tmm(Ssub, dG));
+        mat_store<D>(os + k * DD, dSsub);
+        mat_store<D>(od + k * DD, dSkk);
+        S = mirror_lower(Skk);
+        dS = sym(dSkk);
+    }
+}
+
 // naturals_to_ssm_params, backward half (ssm_gaussian_transformations.py:443-504) fused in one sweep:
 // inverse band -> A_k -> conditional precision -> covariance, chol -> (A^-T)-solve of theta1 -> offsets.
 template <int D>

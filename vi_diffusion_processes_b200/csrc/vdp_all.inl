@@ -277,6 +277,16 @@ int vdp_btd_inverse_band(const double* Ld, const double* Ls, double* Sd, double*
     return VDP_OK;
 }
 
+int vdp_btd_inverse_band_jvp(const double* Ld, const double* Ls, const double* dKd, const double* dKs, double* dSd,
+                             double* dSs, int64_t B, int64_t n, int D, void* stream) {
+    VDP_REQUIRE(Ld && Ls && dKd && dKs && dSd && dSs && B >= 0 && n >= 2, "pointers, B, n >= 2");
+    if (B == 0) return VDP_OK;
+    VDP_DISPATCH_D(D, (k_invband_jvp<kD><<<grid_for(B, kSeqBlock), kSeqBlock, 0, as_stream(stream)>>>(
+                          Ld, Ls, dKd, dKs, dSd, dSs, B, n)));
+    VDP_CHECK_LAUNCH();
+    return VDP_OK;
+}
+
 int vdp_btd_solve(const double* Ld, const double* Ls, const double* rhs, double* x, int transpose, int64_t B,
                   int64_t n, int D, void* stream) {
     VDP_REQUIRE(Ld && rhs && x && B >= 0 && n >= 1, "Ld, rhs, x, B, n");

@@ -92,6 +92,17 @@ def btd_inverse_band(Ld, Ls=None, want_sub=True):
     return Sd, Ss
 
 
+def btd_inverse_band_jvp(Ld, Ls, dKd, dKs):
+    """d(Sigma_kk), d(Sigma_{k+1,k}) of d(K^-1) = -K^-1 dK K^-1 for K = L L^T and a symmetric block-tridiagonal
+    direction dK (lower triangle of the diagonal blocks read)."""
+    _req(Ld, Ls, dKd, dKs)
+    B, n, D = _bnd(Ld)
+    dSd, dSs = torch.empty_like(Ld), torch.empty_like(Ls)
+    check(_lib.load().vdp_btd_inverse_band_jvp(_p(Ld), _p(Ls), _p(dKd), _p(dKs), _p(dSd), _p(dSs), B, n, D, _stream()),
+          "vdp_btd_inverse_band_jvp")
+    return dSd, dSs
+
+
 def btd_solve(Ld, Ls, rhs, transpose=False):
     _req(Ld, Ls, rhs)
     B, n, D = _bnd(Ld)
