@@ -96,3 +96,51 @@ def test_kl_gradient_entry_point_low_order_equals_twenty_points(vdp_cfg):
     assert (kl_a - kl_c).abs().max() <= 1e-11 * kl_c.abs().max()
     for x, r in zip(g_a, g_c):
         assert (x - r).abs().max() <= 1e-10 * r.abs().max()
+
+
+@pytest.mark.parametrize("name", ["vdp", "lorenz", "ou3"])
+def test_linearisation_low_order_equals_ten_points(name, vdp_cfg):
+    """E f and E J of the linearised prior (sde.py:109-128, H = 10 in the reference) through the low-order rule"""
+    from vi_diffusion_processes_b200 import ops
+    did, params, D, N, dt = _case(name)
+    rng = np.random.default_rng(11 + D)
+    B = 2
+    grid = torch.as_tensor(np.arange(N + 1) * dt, device="cuda")
+    m = torch.as_tensor(1.0 + 0.3 * rng.normal(size=(B, N, D)), device="cuda")
+    L = np.tril(0.1 * rng.normal(size=(B, N, D, D))) + 0.4 * np.eye(D)
+    S = torch.as_tensor(L @ np.swapaxes(L, -1, -2), device="cuda")
+    a = ops.linearize_to_ssm(did, params, np.eye(D), grid, m, S, clip=(-1.0, 1.0), want_unclipped=True)
+    vdp_cfg(GH_QUADRATURE=1)
+    c = ops.linearize_to_ssm(did, params, np.eye(D), grid, m, S, clip=(-1.0, 1.0), want_unclipped=True)
+    for x, r in zip(a, c):
+        assert float((x - r).abs().max()) <= 1e-12 * max(float(r.abs().max()), 1.0)
+
+
+@pytest.mark.parametrize("name", ["vdp", "lorenz"])
+def test_vdp_sweeps_low_order_equal_reference_order(name):
+    """VariationalMarkovGP sweeps (vi_sde.py:171-414): E_sde with its gradients (H = 20) and the parameter update
+    (H = 10) through the low-order rule against VDP_VGP_GH_QUADRATURE"""
+    from vi_diffusion_processes_b200 import _lib
+    from vi_diffusion_processes_b200.vgp import VgpEngine
+    did, params, D, N, dt = _case(name)
+    N = 200 if D == 2 else 100
+    rng = np.random.default_rng(21 + D)
+    B, n_obs = 2, 8
+    grid = np.round(np.arange(N + 1) * dt, 6)
+    idx = np.sort(np.stack([rng.choice(np.arange(1, N + 1), n_obs, replace=False) for _ in range(B)]), axis=1)
+    y = 1.0 + 0.2 * rng.normal(size=(B, n_obs, D))
+
+    def make(flags):
+        eng = VgpEngine(did, params, np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.ones(D), 0.01 * np.eye(D))
+        eng.route_flags = flags
+        return eng
+
+    a, c = make(0), make(_lib.VGP_GH_QUADRATURE)
+    for it in range(3):
+        a.sweep(0.05)
+        c.sweep(0.05)
+        for nm in ("A", "b", "m", "S"):
+            ref = getattr(c, nm)
+            assert float((getattr(a, nm) - ref).abs().max()) <= 1e-11 * max(float(ref.abs().max()), 1.0), (it, nm)
+    ea, ec = a.elbo(), c.elbo()
+    assert float((ea - ec).abs().max()) <= 1e-11 * float(ec.abs().max())

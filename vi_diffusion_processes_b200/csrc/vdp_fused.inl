@@ -99,9 +99,22 @@ int vdp_linearize_to_ssm(int drift_id, const double* params_host, const double* 
     const int fj = drift_full_jacobian(drift_id) ? 1 : 0;
     VDP_DISPATCH_D(D, VDP_DISPATCH_DRIFT(drift_id, {
         constexpr int G = QuadGroup<kD>::value;
-        k_linearize<kDrift, kD, 10, G><<<grid_for(B * N * G, kPtBlock), kPtBlock, 0, as_stream(stream)>>>(
-            P, host_mat<kD>(q_host), time_grid, m, S, pi_factor(kD), fj, A, b, cholQ, A_lin, b_lin, clip, clip_lo,
-            clip_hi, B, N, status);
+        bool done = false;
+        // polynomial drift in D >= 2: E f and E J through the exact low-order rule (DriftPoly / ExactOrder in
+        // drifts.cuh), one thread per grid point; the GH_QUADRATURE switch keeps the reference's 10 points
+        if constexpr (kD >= 2 && DriftPoly<kDrift>::degree > 0) {
+            if (!g_cfg.gh_quadrature) {
+                k_linearize<kDrift, kD, ExactOrder<kDrift>::H, 1><<<grid_for(B * N, kPtBlock), kPtBlock, 0,
+                                                                   as_stream(stream)>>>(
+                    P, host_mat<kD>(q_host), time_grid, m, S, pi_factor(kD), fj, A, b, cholQ, A_lin, b_lin, clip,
+                    clip_lo, clip_hi, B, N, status);
+                done = true;
+            }
+        }
+        if (!done)
+            k_linearize<kDrift, kD, 10, G><<<grid_for(B * N * G, kPtBlock), kPtBlock, 0, as_stream(stream)>>>(
+                P, host_mat<kD>(q_host), time_grid, m, S, pi_factor(kD), fj, A, b, cholQ, A_lin, b_lin, clip, clip_lo,
+                clip_hi, B, N, status);
     }));
     VDP_CHECK_LAUNCH();
     return VDP_OK;

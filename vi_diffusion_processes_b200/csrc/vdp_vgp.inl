@@ -118,6 +118,16 @@ static int vgp_esde(const vdp_vgp_problem& p, const VgpWs& w, bool grads, cudaSt
             return VDP_OK;
         }
     }
+    // polynomial drift in D >= 2: the exact low-order rule, one thread per grid point (drifts.cuh DriftPoly)
+    if constexpr (D >= 2 && DriftPoly<DRIFT>::degree > 0) {
+        if (!(p.flags & VDP_VGP_GH_QUADRATURE) && !g_cfg.gh_quadrature) {
+            k_vgp_esde<DRIFT, D, ExactOrder<DRIFT>::H, 1><<<grid_for(p.B * p.N, kPtBlock), kPtBlock, 0, st>>>(
+                P, host_mat<D>(p.q), p.dt, pi_factor(D), p.A, p.b, p.m, p.S, w.terms, grads ? w.dEdm : nullptr,
+                grads ? w.dEdS : nullptr, p.B, p.N, p.status);
+            VDP_CHECK_LAUNCH();
+            return VDP_OK;
+        }
+    }
     k_vgp_esde<DRIFT, D, 20, G><<<grid_for(p.B * p.N * G, kPtBlock), kPtBlock, 0, st>>>(
         P, host_mat<D>(p.q), p.dt, pi_factor(D), p.A, p.b, p.m, p.S, w.terms, grads ? w.dEdm : nullptr,
         grads ? w.dEdS : nullptr, p.B, p.N, p.status);
@@ -182,6 +192,15 @@ static int vgp_update_param(const vdp_vgp_problem& p, cudaStream_t st) {
     if constexpr (D == 1 && G == 1 && DriftStep1<DRIFT>::kCubic) {
         if (!(p.flags & VDP_VGP_GH_QUADRATURE) && !g_cfg.gh_quadrature) {
             k_vgp_update_param<DRIFT, D, 10, G, true><<<grid_for(p.B * p.N * G, kPtBlock), kPtBlock, 0, st>>>(
+                P, host_mat<D>(p.q), pi_factor(D), (p.flags & VDP_VGP_STABILIZE) ? 1 : 0, p.lr, p.m, p.S, p.lam, p.psi,
+                p.A, p.b, p.B, p.N, p.status);
+            VDP_CHECK_LAUNCH();
+            return VDP_OK;
+        }
+    }
+    if constexpr (D >= 2 && DriftPoly<DRIFT>::degree > 0) {
+        if (!(p.flags & VDP_VGP_GH_QUADRATURE) && !g_cfg.gh_quadrature) {
+            k_vgp_update_param<DRIFT, D, ExactOrder<DRIFT>::H, 1><<<grid_for(p.B * p.N, kPtBlock), kPtBlock, 0, st>>>(
                 P, host_mat<D>(p.q), pi_factor(D), (p.flags & VDP_VGP_STABILIZE) ? 1 : 0, p.lr, p.m, p.S, p.lam, p.psi,
                 p.A, p.b, p.B, p.N, p.status);
             VDP_CHECK_LAUNCH();
