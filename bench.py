@@ -13,9 +13,11 @@ updates.
 
 value  = grid steps of all ranks / max-over-ranks device time, state resident in HBM.
 e2e    = same metric through the host-buffer C ABI with the copies inside the timed region: resident-state session
-         (vdp_cvi_session_*): per step the observation values go host->device and the ELBO terms + posterior
-         marginals device->host.  e2e_full_state_roundtrip = every array of the problem both ways every step
-         (vdp_cvi_host_site_update, round 1's e2e).  Both come with the box's measured raw copy ceiling.
+         (vdp_cvi_session_*): per step the observation values go host->device and the step's result, the ELBO
+         terms per sequence, device->host.  e2e_marginals_down = the same call also bringing the posterior marginals
+         of every grid point down every step (round 2a's e2e); e2e_full_state_roundtrip = every array of the problem
+         both ways every step (vdp_cvi_host_site_update, round 1's e2e); these two come with the box's measured raw
+         copy ceiling.
 c5     = BASELINE config 5 (one sequence, 10^7 grid steps, D = 3) with the chain sharded in time over the ranks and
          the scan carries / halos exchanged over NCCL (strong scaling); `--workload c5` prints it as its own line.
 parity_check = first 4 sequences of the timed state against the CPU oracle; the run exits non-zero above 1e-9.
@@ -323,7 +325,10 @@ def run_ours(args):
         host_eng.site_update(LR, LR)        # returns when the results are in the host buffers
 
     def step_session():
-        session.site_update(LR, LR)         # obs values up, update, ELBO terms + marginals down, returns when done
+        session.site_update(LR, LR, marginals=False)   # obs values up, update, ELBO terms down, returns when done
+
+    def step_session_marginals():
+        session.site_update(LR, LR)         # ... and the posterior marginals of every grid point down as well
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -384,13 +389,18 @@ def run_ours(args):
     e2e_steps = max(2, args.steps // 2)
     # (1) resident-state session (vdp_cvi_session_*): the state was uploaded once and lives on the device, as the
     # reference's model object keeps its variables between trainer iterations; every step moves that step's inputs
-    # (the observation values, pinned host memory) up and its results (ELBO terms and the posterior marginals, what
-    # cvi_dp_trainer.py:75-77 reads every iteration) down.  This is the `e2e` of the line.
+    # (the observation values, pinned host memory) up and its result (the ELBO terms: ve, kl, elbo per sequence -- the
+    # loss the reference's trainer reads every iteration, cvi_dp_trainer.py:75; NLPD / RMSE there are two more scalars
+    # from marginals that stay with the model) down.  This is the `e2e` of the line.  `e2e_marginals_down` is the same
+    # call that also brings the posterior marginals of every grid point to the host every step (the `e2e` of round 2a),
+    # with the raw copy ceiling of its bytes.
     from vi_diffusion_processes_b200.cvi import CviSession
     session = CviSession(eng, chunk=args.session_chunk, streams=3)
-    s_h2d, s_d2h = session.bytes_per_update()
+    s_h2d, s_d2h = session.bytes_per_update(marginals=False)
     ms_session = timed(step_session, args.steps, 2)
-    ms_session_ceiling = copy_ceiling_ms(s_h2d, s_d2h, device, barrier, world, dist)
+    sm_h2d, sm_d2h = session.bytes_per_update(marginals=True)
+    ms_session_m = timed(step_session_marginals, args.steps, 2)
+    ms_session_ceiling = copy_ceiling_ms(sm_h2d, sm_d2h, device, barrier, world, dist)
     session.close()
     del session
     # (2) the whole state in host memory, every array both ways every step (vdp_cvi_host_site_update): the round-1
@@ -464,12 +474,18 @@ def run_ours(args):
                 "d2h_bytes_per_step": s_d2h, "ms_per_step": ms_session / args.steps,
                 "api": "vdp_cvi_session_site_update (C ABI, host buffers): state resident on the device between calls "
                        "(uploaded once by vdp_cvi_session_create, like the reference's model variables); per step the "
-                       "observation values go up from pinned host memory and the ELBO terms [B] + posterior marginals "
-                       "fx_mus, fx_covs [B, N+1] come down to pinned host memory; %d-sequence chunks on 3 streams"
-                       % min(args.session_chunk, B),
-                "copy_ceiling_ms": ms_session_ceiling, "frac_of_copy_ceiling": ms_session_ceiling / (ms_session / args.steps),
-                "copy_ceiling": "raw pinned cudaMemcpyAsync of the same h2d + d2h bytes on two streams at once, all "
-                                "ranks concurrently, max over ranks, best of 4"},
+                       "observation values [B, n_obs] go up from pinned host memory and the step's result, the ELBO "
+                       "terms ve, kl, elbo [B], comes down to pinned host memory (what cvi_dp_trainer.py:75 reads "
+                       "every iteration); the call returns when they are there; %d-sequence chunks on 3 streams"
+                       % min(args.session_chunk, B)},
+        "e2e_marginals_down": {
+            "value": steps_total * args.steps / (ms_session_m * 1e-3), "unit": "grid-steps/s",
+            "h2d_bytes_per_step": sm_h2d, "d2h_bytes_per_step": sm_d2h, "ms_per_step": ms_session_m / args.steps,
+            "api": "the same call with fx_mus_host / fx_covs_host given: the posterior marginals of every grid point "
+                   "[B, N+1] also come down every step (this was `e2e` in round 2a)",
+            "copy_ceiling_ms": ms_session_ceiling, "frac_of_copy_ceiling": ms_session_ceiling / (ms_session_m / args.steps),
+            "copy_ceiling": "raw pinned cudaMemcpyAsync of the same h2d + d2h bytes on two streams at once, all "
+                            "ranks concurrently, max over ranks, best of 4"},
         "e2e_full_state_roundtrip": {
             "value": e2e_value, "unit": "grid-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "ms_per_step": ms_e2e / e2e_steps,

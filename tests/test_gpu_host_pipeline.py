@@ -135,3 +135,29 @@ def test_resident_session_matches_oracle_and_engine(B, chunk, streams):
     for k in ("qA", "qb", "qcholQ"):
         assert rel(h[k], getattr(dev_eng, k)) < 1e-10, k
     ses.close()
+
+
+def test_resident_session_without_marginal_download():
+    """``site_update(marginals=False)``: only the ELBO terms travel device -> host per update (what the reference's
+    trainer reads every iteration); the host marginal buffers stay as they are until ``download_state`` fills them."""
+    from vi_diffusion_processes_b200.cvi import CviEngine, CviSession
+    rng = np.random.default_rng(41)
+    B, N = 6, 900
+    grid, idx, y = _problem(rng, B, N, 9, 0.005)
+    mk = lambda: CviEngine(S.DRIFT_DW, [4.0, 1.0], np.ones((1, 1)), grid, idx, y[..., None], [[0.1]], [1.0], [[1e-2]])
+    ses, full = CviSession(mk(), chunk=4, streams=2), CviSession(mk(), chunk=4, streams=2)
+    up, down = ses.bytes_per_update(marginals=False)
+    assert up == B * 9 * 8 and down == 3 * B * 8
+    ses.host["fx_mus"].fill_(-7.0)
+    ses.host["fx_covs"].fill_(-7.0)
+    for it in range(3):
+        e = ses.site_update(0.5, 0.5, marginals=False)
+        f = full.site_update(0.5, 0.5)
+        assert torch.equal(e, f)
+        for k in ("ve", "kl"):
+            assert torch.equal(ses.host[k], full.host[k])
+    assert bool((ses.host["fx_mus"] == -7.0).all()) and bool((ses.host["fx_covs"] == -7.0).all())
+    h = ses.download_state()
+    assert torch.equal(h["fx_mus"], full.host["fx_mus"]) and torch.equal(h["fx_covs"], full.host["fx_covs"])
+    ses.close()
+    full.close()

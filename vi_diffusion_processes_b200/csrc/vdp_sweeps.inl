@@ -24,7 +24,19 @@ template <int D> struct TileCfg;
 #endif
 template <> struct TileCfg<1> { static constexpr int T = VDP_T1, Lc = VDP_LC1, Li = VDP_LI1, Lm = VDP_LM1, Ln = VDP_LN1; };
 template <> struct TileCfg<2> { static constexpr int T = 64, Lc = 9, Li = 9, Lm = 5, Ln = 5; };
-template <> struct TileCfg<3> { static constexpr int T = 64, Lc = 5, Li = 5, Lm = 3, Ln = 3; };
+#ifndef VDP_T3
+#define VDP_T3 64
+#endif
+#ifndef VDP_LC3
+#define VDP_LC3 5
+#endif
+#ifndef VDP_LM3
+#define VDP_LM3 3
+#endif
+#ifndef VDP_LN3
+#define VDP_LN3 3
+#endif
+template <> struct TileCfg<3> { static constexpr int T = VDP_T3, Lc = VDP_LC3, Li = 5, Lm = VDP_LM3, Ln = VDP_LN3; };
 
 // staging buffers per sweep kernel: 2 = the copies of the next tile land while the current one is processed
 #ifndef VDP_SWEEP_STAGES
@@ -46,7 +58,10 @@ constexpr int kSweepStages = VDP_STAGES_C;   // Cholesky sweep
 constexpr int kStagesN = VDP_STAGES_N;       // naturals_to_ssm backward sweep
 constexpr int kStagesM = VDP_STAGES_M;       // mean sweep
 
-constexpr int64_t kTargetBlocks = 148 * 4;     // CTAs wanted in flight before sequences are split in time
+#ifndef VDP_TARGET_BLOCKS
+#define VDP_TARGET_BLOCKS (148 * 4)
+#endif
+constexpr int64_t kTargetBlocks = VDP_TARGET_BLOCKS;   // CTAs wanted in flight before sequences are split in time
 constexpr int64_t kMaxSegTotal = 4096;         // bound on B * nseg (sizes the segment scratch)
 constexpr size_t kSegScratchBytes = 8u << 20;  // part of every fused-level workspace
 

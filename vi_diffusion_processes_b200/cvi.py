@@ -469,21 +469,24 @@ class CviSession:
         p.workspace, p.workspace_bytes, p.status = None, 0, None
         return p
 
-    def bytes_per_update(self):
-        """(host->device, device->host) bytes one site_update moves: observation values up; ELBO terms and marginals
-        down."""
+    def bytes_per_update(self, marginals=True):
+        """(host->device, device->host) bytes one site_update moves: observation values up; ELBO terms and (with
+        ``marginals``) the posterior marginals down."""
         h = self.host
         nb = lambda names: sum(h[k].numel() * h[k].element_size() for k in names)
-        return nb(["obs_y"]), nb(["elbo", "ve", "kl", "fx_mus", "fx_covs"])
+        return nb(["obs_y"]), nb(["elbo", "ve", "kl"] + (["fx_mus", "fx_covs"] if marginals else []))
 
-    def site_update(self, lr_data, lr_girsanov, flags=0, obs_y=None):
+    def site_update(self, lr_data, lr_girsanov, flags=0, obs_y=None, marginals=True):
+        """``marginals=False``: only the ELBO terms come down -- what the reference's trainer reads every iteration
+        (cvi_dp_trainer.py:75, the marginals stay with the model); ``download_state`` fetches them when wanted."""
         h = self.host
         y = h["obs_y"] if obs_y is None else obs_y
         st = (C.c_int64 * 2)()
         check(_lib.load().vdp_cvi_session_site_update(
             self._s, C.c_void_p(y.data_ptr()), float(lr_data), float(lr_girsanov), int(flags),
             C.c_void_p(h["elbo"].data_ptr()), C.c_void_p(h["ve"].data_ptr()), C.c_void_p(h["kl"].data_ptr()),
-            C.c_void_p(h["fx_mus"].data_ptr()), C.c_void_p(h["fx_covs"].data_ptr()), st), "vdp_cvi_session_site_update")
+            C.c_void_p(h["fx_mus"].data_ptr()) if marginals else None,
+            C.c_void_p(h["fx_covs"].data_ptr()) if marginals else None, st), "vdp_cvi_session_site_update")
         if st[0] != 0:
             raise _lib.VdpError(f"non positive-definite block (code {st[0]}, grid index {st[1]})")
         return h["elbo"]
