@@ -502,6 +502,14 @@ typedef struct vdp_vgp_problem {
 #define VDP_VGP_REFACTOR_PRECISION 8 /* forward_pass: marginal covariances through the rebuilt precision (banded
                                   Cholesky + inverse band, state_space_model.py:262) as the reference, instead of the
                                   forward recursion S_{k+1} = A S A^T + Q riding on the mean sweep (equal to rounding) */
+#define VDP_VGP_STATE_CARRIED 16 /* vdp_vgp_sweep only.  The caller's promise: the previous call on this problem was a
+                                  vdp_vgp_sweep and nothing it read or wrote (A, b, the initial statistics, m, S, the
+                                  observations, the workspace) has changed since.  The sweep ends with the forward pass
+                                  and the E_sde quadrature of the parameters it has just written -- for its ELBO -- and
+                                  the next sweep would begin by computing exactly those again (vi_markov_gp_trainer.py:
+                                  62-73 calls update_param, which starts from forward_pass, then elbo, which runs it
+                                  again): with the flag it starts from the marginals and dE_sde/dm, dE_sde/dS the
+                                  workspace still holds.  Same results bit for bit. */
 
 /* LinearDrift.to_ssm (markovflow/sde/drift.py:64-116): A_ssm = I + A delta_k, b_ssm = b delta_k,
  * cholQ = chol(q delta_k).  A [B,N,D,D], b [B,N,D] -> same shapes. */

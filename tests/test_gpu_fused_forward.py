@@ -146,3 +146,41 @@ def test_fused_forward_in_the_device_loop(vdp_cfg):
     assert int(ra["n_itr"].max()) >= 3 and int(ra["n_itr"].min()) < 8      # some converge early, some do not
     assert torch.allclose(ra["elbo_trace"], rb["elbo_trace"], rtol=1e-10, atol=0)
     assert float((a.fx_mus - b.fx_mus).abs().max()) < 1e-10
+
+
+@pytest.mark.parametrize("D,stab", [(1, False), (1, True), (2, False)])
+def test_vdp_sweep_carried_state_is_bitwise_the_plain_sweep(D, stab):
+    """VDP_VGP_STATE_CARRIED: a sweep starts from the forward pass and the E_sde quadrature the previous sweep ended
+    with (vi_markov_gp_trainer.py:62-73 computes both twice).  Bitwise the same parameters, multipliers, marginals and
+    ELBO; an in-place change of A between sweeps (torch version counter) or another call on the engine drops the
+    carry."""
+    from vi_diffusion_processes_b200.vgp import VgpEngine
+    from vi_diffusion_processes_b200.markovflow.sde import sde as sde_mod
+    did, params = (sde_mod.DRIFT_DW, [4.0, 1.0]) if D == 1 else (sde_mod.DRIFT_VDP, [1.0, 1.0])
+    rng = np.random.default_rng(60 + D)
+    B, N, n_obs = 3, 1500 if D == 1 else 300, 9
+    grid = np.round(np.arange(N + 1) * 0.005, 6)
+    idx = np.sort(np.stack([rng.choice(np.arange(1, N + 1), n_obs, replace=False) for _ in range(B)]), axis=1)
+    y = 1.0 + 0.2 * rng.normal(size=(B, n_obs, D))
+    mk = lambda: VgpEngine(did, params, np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.ones(D), 0.01 * np.eye(D),
+                           stabilize_system=stab)
+    a, c = mk(), mk()
+    for e in (a, c):
+        e.A += 1.5
+        e.b += 1.5
+    carried = []
+    for it in range(6):
+        if it == 3:                       # in-place edit: the carry must notice
+            a.A.mul_(0.99)
+            c.A.mul_(0.99)
+        if it == 4:                       # another entry point in between
+            a.elbo()
+        sig_ok = a._carry_sig is not None and a._carry_sig == a._carry_signature()
+        carried.append(sig_ok)
+        ea = a.sweep(0.1, update_x0=(it % 2 == 1)).clone()
+        ec = c.sweep(0.1, update_x0=(it % 2 == 1), carry=False).clone()
+        assert torch.equal(ea, ec), it
+        for nm in ("A", "b", "m", "S", "lambda_lagrange", "psi_lagrange", "q_initial_mean", "q_initial_chol"):
+            assert torch.equal(getattr(a, nm), getattr(c, nm)), (it, nm)
+    assert carried == [False, True, True, False, False, True]
+    a.check_status()

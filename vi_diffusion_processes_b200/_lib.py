@@ -112,6 +112,7 @@ FLAG_GH_QUADRATURE, FLAG_REFACTOR_PRECISION, FLAG_NO_FUSED_NATURALS, FLAG_SEPARA
 FLAG_NO_FUSED_FORWARD = 1024
 VGP_STABILIZE = 1
 VGP_UPDATE_X0 = 2
+VGP_STATE_CARRIED = 16
 VGP_GH_QUADRATURE = 4
 VGP_REFACTOR_PRECISION = 8
 

@@ -136,14 +136,15 @@ static int vgp_esde(const vdp_vgp_problem& p, const VgpWs& w, bool grads, cudaSt
 }
 
 // vi_sde.py:289-347
+// have_grads: w.dEdm / w.dEdS already hold dE_sde/dm, dE_sde/dS of the current (A, b, m, S)
 template <int DRIFT, int D>
-static int vgp_lagrange(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st) {
+static int vgp_lagrange(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st, bool have_grads = false) {
     using C = LagrangeCfg<D>;
     using Ops = LagrangeOps<D>;
     const int64_t B = p.B, N = p.N;
     const int stab = (p.flags & VDP_VGP_STABILIZE) ? 1 : 0;
     int rc;
-    if ((rc = vgp_esde<DRIFT, D>(p, w, true, st))) return rc;
+    if (!have_grads && (rc = vgp_esde<DRIFT, D>(p, w, true, st))) return rc;
     const size_t n = (size_t)B * (N + 1);
     VDP_CHECK_CUDA(cudaMemsetAsync(w.dobs_m, 0, n * D * sizeof(double), st));
     VDP_CHECK_CUDA(cudaMemsetAsync(w.dobs_S, 0, n * D * D * sizeof(double), st));
@@ -225,10 +226,11 @@ static int vgp_update_initial(const vdp_vgp_problem& p, cudaStream_t st) {
 }
 
 // vi_sde.py:436-455 (m, S of the problem must be the current forward pass)
+// with_grads: the E_sde pass also leaves dE_sde/dm, dE_sde/dS in the workspace (for the sweep that follows)
 template <int DRIFT, int D>
-static int vgp_elbo(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st) {
+static int vgp_elbo(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st, bool with_grads = false) {
     int rc;
-    if ((rc = vgp_esde<DRIFT, D>(p, w, false, st))) return rc;
+    if ((rc = vgp_esde<DRIFT, D>(p, w, with_grads, st))) return rc;
     k_reduce_terms<<<(unsigned)p.B, 256, 0, st>>>(w.terms, p.N, w.esde);
     VDP_CHECK_LAUNCH();
     if (p.n_obs > 0) {
@@ -305,13 +307,16 @@ VDP_VGP_ENTRY(vdp_vgp_update_param, { if ((rc = vgp_update_param<kDrift, kD>(*p,
 VDP_VGP_ENTRY(vdp_vgp_update_initial_statistics, { if ((rc = vgp_update_initial<kD>(*p, st))) return rc; })
 VDP_VGP_ENTRY(vdp_vgp_elbo, { if ((rc = vgp_elbo<kDrift, kD>(*p, w, st))) return rc; })
 // one iteration of VIMarkovGPTrainer.perform_inference (vi_markov_gp_trainer.py:62-73)
+// (the tail -- forward pass + E_sde quadrature with its gradients -- is what the next sweep starts from:
+// VDP_VGP_STATE_CARRIED skips the head)
 VDP_VGP_ENTRY(vdp_vgp_sweep, {
-    if ((rc = vgp_forward<kD>(*p, w, st))) return rc;
-    if ((rc = vgp_lagrange<kDrift, kD>(*p, w, st))) return rc;
+    const bool carried = (p->flags & VDP_VGP_STATE_CARRIED) != 0;
+    if (!carried) { if ((rc = vgp_forward<kD>(*p, w, st))) return rc; }
+    if ((rc = vgp_lagrange<kDrift, kD>(*p, w, st, carried))) return rc;
     if ((rc = vgp_update_param<kDrift, kD>(*p, st))) return rc;
     if (p->flags & VDP_VGP_UPDATE_X0) { if ((rc = vgp_update_initial<kD>(*p, st))) return rc; }
     if ((rc = vgp_forward<kD>(*p, w, st))) return rc;
-    if ((rc = vgp_elbo<kDrift, kD>(*p, w, st))) return rc;
+    if ((rc = vgp_elbo<kDrift, kD>(*p, w, st, true))) return rc;
 })
 
 }  // extern "C"

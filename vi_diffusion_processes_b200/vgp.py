@@ -53,6 +53,8 @@ class VgpEngine:
         self.x0_cov = self.q * np.eye(D) if x0_cov is None else np.atleast_2d(np.asarray(x0_cov, dtype=np.float64))
         self.stabilize_system = bool(stabilize_system)
         self.route_flags = 0          # VGP_GH_QUADRATURE: OR-ed into every call
+        self.carry_state = True       # consecutive sweeps start from the previous sweep's forward pass (see sweep)
+        self._carry_sig = None
         z = lambda *s: torch.zeros(s, dtype=F64, device=dev)
         eye = torch.eye(D, dtype=F64, device=dev)
         self.A, self.b = z(B, N, D, D), z(B, N, D)
@@ -97,6 +99,7 @@ class VgpEngine:
         return p
 
     def _call(self, name, p):
+        self._carry_sig = None                 # any call may touch the workspace / the state a sweep would carry
         with torch.cuda.device(self.device):   # the launches go to the current device
             stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
             check(getattr(_lib.load(), name)(C.byref(p), stream), name)
@@ -124,8 +127,27 @@ class VgpEngine:
         return self.elbo_value
 
     # vi_markov_gp_trainer.py:62-73
-    def sweep(self, lr, update_x0=False, x0_lr=0.1):
-        self._call("vdp_vgp_sweep", self._problem(lr=lr, x0_lr=x0_lr, update_x0=update_x0))
+    _CARRY_FIELDS = ("A", "b", "q_initial_mean", "q_initial_chol", "m", "S", "obs_idx", "obs_y", "time_grid", "_ws")
+
+    def _carry_signature(self):
+        """everything the head of a sweep (forward pass + E_sde quadrature) is a function of: storage and torch version
+        counter of the tensors, the scalar parameters, the route"""
+        return (tuple((t.data_ptr(), t._version) for t in (getattr(self, n) for n in self._CARRY_FIELDS)),
+                tuple(self.drift_params), tuple(self.q.reshape(-1).tolist()), self.dt, self.stabilize_system,
+                self.route_flags, tuple(_lib.config_get(k) for k in _lib.CONFIG_KEYS))
+
+    def sweep(self, lr, update_x0=False, x0_lr=0.1, carry=None):
+        """One iteration of VIMarkovGPTrainer.perform_inference.  A sweep ends with the forward pass and the E_sde
+        quadrature of the parameters it has just written (for its ELBO); the next sweep would begin with the same two
+        computations.  If nothing they depend on has changed in between -- checked here: no other call on this engine,
+        no tensor replaced or modified through torch -- ``VDP_VGP_STATE_CARRIED`` lets it start from what the
+        workspace still holds (bitwise the same results)."""
+        carry = self.carry_state if carry is None else carry
+        p = self._problem(lr=lr, x0_lr=x0_lr, update_x0=update_x0)
+        if carry and self._carry_sig is not None and self._carry_sig == self._carry_signature():
+            p.flags |= _lib.VGP_STATE_CARRIED
+        self._call("vdp_vgp_sweep", p)
+        self._carry_sig = self._carry_signature() if carry else None
         return self.elbo_value
 
     # vi_sde.py:457-470
@@ -153,13 +175,14 @@ class VgpEngine:
                 cache.clear()
             keep = ("A", "b", "lambda_lagrange", "psi_lagrange", "q_initial_mean", "q_initial_chol", "m", "S")
             state = [getattr(self, n).clone() for n in keep]
-            self.sweep(lr, update_x0=update_x0, x0_lr=x0_lr)      # warm-up outside the capture, undone below
+            self.sweep(lr, update_x0=update_x0, x0_lr=x0_lr, carry=False)   # warm-up outside the capture, undone below
             g = torch.cuda.CUDAGraph()
             with torch.cuda.device(self.device), torch.cuda.graph(g):
-                self.sweep(lr, update_x0=update_x0, x0_lr=x0_lr)
+                self.sweep(lr, update_x0=update_x0, x0_lr=x0_lr, carry=False)
             for n, t in zip(keep, state):
                 getattr(self, n).copy_(t)
             cache[key] = g
+        self._carry_sig = None
         g.replay()
         return self.elbo_value
 
