@@ -161,17 +161,18 @@ def _run_sweep(comm: Comm, ranks: List[_Rank], kind, problems_stage, D):
     gathered = None
     for stage in range(stages):
         tb, ib = _blob_bytes(kind, stage, D)
-        totals, inits = [], []
+        # one blob per rank = [scan element of the rank's stretch | its natural initial state]: one all-gather per stage
+        tbp = (tb + 15) // 16 * 16
+        blobs = []
         for i, rk in enumerate(ranks):
-            tot = torch.zeros(tb, dtype=torch.uint8, device=rk.device)
-            ini = torch.zeros(ib, dtype=torch.uint8, device=rk.device)
+            blob = torch.zeros(tbp + ib, dtype=torch.uint8, device=rk.device)
             p = problems_stage(rk, stage, prev[i])
-            check(lib.vdp_dist_sweep_summary(C.byref(p), tot.data_ptr(), ini.data_ptr(), _stream()),
+            check(lib.vdp_dist_sweep_summary(C.byref(p), blob.data_ptr(), blob.data_ptr() + tbp, _stream()),
                   "vdp_dist_sweep_summary")
-            totals.append(tot)
-            inits.append(ini)
-        all_t = torch.cat(comm.all_gather(totals)).contiguous()
-        all_i = torch.cat(comm.all_gather(inits)).contiguous()
+            blobs.append(blob)
+        allb = comm.all_gather(blobs)
+        all_t = torch.cat([x[:tb] for x in allb]).contiguous()
+        all_i = torch.cat([x[tbp:] for x in allb]).contiguous()
         gathered = (all_t, all_i)
         prev = [gathered] * len(ranks)
     for i, rk in enumerate(ranks):
@@ -240,14 +241,13 @@ class TimeShardedChain:
             return rk.sweep(_lib.SWEEP_NAT2SSM, stage, [Ld[i], Ls[i], th1[i], thd[i], ths[i]],
                             [A[i], bbuf[i][1:], qbuf[i][1:], mu0[i], cP0[i], Sd[i]], prev=prev)
         _run_sweep(self.comm, self.ranks, _lib.SWEEP_NAT2SSM, n2s, D)
-        # transition e-1 (output of node e) lives in slot 0 of the next rank
-        nb = self._from_next([t[:1].contiguous() for t in bbuf])
-        nq = self._from_next([t[:1].contiguous() for t in qbuf])
+        # transition e-1 (output of node e) lives in slot 0 of the next rank (offset and factor in one exchange)
+        nbq = self._from_next([torch.cat([tb_[0].reshape(-1), tq_[0].reshape(-1)]) for tb_, tq_ in zip(bbuf, qbuf)])
         out = []
         for i, rk in enumerate(self.ranks):
             if not rk.last:
-                bbuf[i][-1:] = nb[i]
-                qbuf[i][-1:] = nq[i]
+                bbuf[i][-1] = nbq[i][:D]
+                qbuf[i][-1] = nbq[i][D:].reshape(D, D)
             out.append(dict(A=A[i], b=bbuf[i][1:], cholQ=qbuf[i][1:], cholQ_prev=None if rk.first else qbuf[i][:1],
                             mu0=mu0[i] if rk.first else None, cholP0=cP0[i] if rk.first else None, S=Sd[i]))
         return out
