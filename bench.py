@@ -395,9 +395,14 @@ def run_ours(args):
     # call that also brings the posterior marginals of every grid point to the host every step (the `e2e` of round 2a),
     # with the raw copy ceiling of its bytes.
     from vi_diffusion_processes_b200.cvi import CviSession
-    session = CviSession(eng, chunk=args.session_chunk, streams=3)
+    # (with only the ELBO terms coming down there is no download to overlap with the next chunk's kernels: one chunk
+    # of all sequences keeps the launches full; the marginal download is pipelined over chunks of --session-chunk)
+    session = CviSession(eng, chunk=B, streams=1)
     s_h2d, s_d2h = session.bytes_per_update(marginals=False)
     ms_session = timed(step_session, args.steps, 2)
+    session.close()
+    del session
+    session = CviSession(eng, chunk=args.session_chunk, streams=3)
     sm_h2d, sm_d2h = session.bytes_per_update(marginals=True)
     ms_session_m = timed(step_session_marginals, args.steps, 2)
     ms_session_ceiling = copy_ceiling_ms(sm_h2d, sm_d2h, device, barrier, world, dist)
@@ -476,13 +481,13 @@ def run_ours(args):
                        "(uploaded once by vdp_cvi_session_create, like the reference's model variables); per step the "
                        "observation values [B, n_obs] go up from pinned host memory and the step's result, the ELBO "
                        "terms ve, kl, elbo [B], comes down to pinned host memory (what cvi_dp_trainer.py:75 reads "
-                       "every iteration); the call returns when they are there; %d-sequence chunks on 3 streams"
-                       % min(args.session_chunk, B)},
+                       "every iteration); the call returns when they are there; one chunk of all %d sequences" % B},
         "e2e_marginals_down": {
             "value": steps_total * args.steps / (ms_session_m * 1e-3), "unit": "grid-steps/s",
             "h2d_bytes_per_step": sm_h2d, "d2h_bytes_per_step": sm_d2h, "ms_per_step": ms_session_m / args.steps,
             "api": "the same call with fx_mus_host / fx_covs_host given: the posterior marginals of every grid point "
-                   "[B, N+1] also come down every step (this was `e2e` in round 2a)",
+                   "[B, N+1] also come down every step (this was `e2e` in round 2a); %d-sequence chunks on 3 streams"
+                   % min(args.session_chunk, B),
             "copy_ceiling_ms": ms_session_ceiling, "frac_of_copy_ceiling": ms_session_ceiling / (ms_session_m / args.steps),
             "copy_ceiling": "raw pinned cudaMemcpyAsync of the same h2d + d2h bytes on two streams at once, all "
                             "ranks concurrently, max over ranks, best of 4"},
