@@ -199,8 +199,8 @@ PHASE_TRAFFIC = {
     "kl_grad": (1 + 1 + 1, 1 + 1 + 2 + 2 + 2),
     "elbo": (0, 0),                   # variational expectations at the observations + sum of the KL partials
 }
-LAUNCHES_PER_UPDATE = 1 + 3 + 2 + 2 + 3   # kernels of ours in one vdp_cvi_site_update in steady state (data sites;
-#                                           patch + Cholesky + naturals_to_ssm; data step + fused forward pass;
+LAUNCHES_PER_UPDATE = 3 + 2 + 2 + 3       # kernels of ours in one vdp_cvi_site_update in steady state (data sites +
+#                                           patch, Cholesky, naturals_to_ssm; data step + fused forward pass;
 #                                           naturals_to_ssm + means; VE + reduce + combine)
 
 

@@ -145,60 +145,6 @@ __global__ void k_patch_naturals(const double* __restrict__ A, const double* __r
     mat_store<D>(scd + i * DD, s2);
 }
 
-// The same patch when the girsanov sites are held implicitly in theta (VDP_FLAG_SITES_IN_NATURALS: theta is the
-// state, g = theta - nat(p) - scatter(data sites) is formed on request): theta changes by the change of the data
-// sites at the observed grid points, whose previous sum is the dense copy's current entry.
-template <int D>
-__global__ void k_patch_naturals_delta(const double* __restrict__ d1, const double* __restrict__ d2,
-                                       const int64_t* __restrict__ obs_idx, double* __restrict__ th1,
-                                       double* __restrict__ thd, double* __restrict__ sc1, double* __restrict__ scd,
-                                       int64_t B, int64_t N, int64_t n_obs) {
-    const int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (o >= B * n_obs) return;
-    constexpr int DD = D * D;
-    const int64_t b = o / n_obs, j = o - b * n_obs;
-    const int64_t k = obs_idx[o];
-    if (k < 0 || k > N) return;
-    const int64_t* row = obs_idx + b * n_obs;
-    Vec<D> s1 = vec_zero<D>();
-    Mat<D> s2 = mat_zero<D>();
-    for (int64_t jj = 0; jj < n_obs; ++jj) {
-        if (row[jj] != k) continue;
-        if (jj < j) return;
-        s1 = s1 + vec_load<D>(d1 + (b * n_obs + jj) * D);
-        s2 = s2 + mat_load<D>(d2 + (b * n_obs + jj) * DD);
-    }
-    const int64_t i = b * (N + 1) + k;
-    vec_store<D>(th1 + i * D, vec_load<D>(th1 + i * D) + (s1 - vec_load<D>(sc1 + i * D)));
-    mat_store<D>(thd + i * DD, mat_load<D>(thd + i * DD) + (s2 - mat_load<D>(scd + i * DD)));
-    vec_store<D>(sc1 + i * D, s1);
-    mat_store<D>(scd + i * DD, s2);
-}
-
-// The data-site part of the girsanov update when the sites are held in theta: the update g += lr (scatter(data sites)
-// - dKL/d eta) (variational_cvi_sde.py:286-292) moves theta by lr * scatter(data sites) at the observed grid points --
-// applied here, one thread per observation entry (the first of several on one grid point does the work, from the
-// dense copy's summed entry) -- and by -lr * dKL/d eta everywhere, which the forward pass that follows applies.
-template <int D>
-__global__ void k_add_data_step(const int64_t* __restrict__ obs_idx, const double* __restrict__ sc1,
-                                const double* __restrict__ scd, double* __restrict__ th1, double* __restrict__ thd,
-                                double lr, const double* __restrict__ lr_dev, const int32_t* __restrict__ active,
-                                int64_t B, int64_t N, int64_t n_obs) {
-    const int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (o >= B * n_obs) return;
-    constexpr int DD = D * D;
-    const int64_t b = o / n_obs, j = o - b * n_obs;
-    const int64_t k = obs_idx[o];
-    if (k < 0 || k > N) return;
-    const int64_t* row = obs_idx + b * n_obs;
-    for (int64_t jj = 0; jj < j; ++jj)
-        if (row[jj] == k) return;
-    if (lr_dev) lr = (!active || active[b]) ? lr_dev[b] : 0.0;
-    const int64_t i = b * (N + 1) + k;
-    vec_store<D>(th1 + i * D, vec_load<D>(th1 + i * D) + lr * vec_load<D>(sc1 + i * D));
-    mat_store<D>(thd + i * DD, mat_load<D>(thd + i * DD) + lr * mat_load<D>(scd + i * DD));
-}
-
 // girsanov sites from the natural parameters they are part of (variational_cvi_sde.py:161-174 read backwards):
 //   g = theta - nat(p) - scatter(data sites),   sub-diagonal: g_s = theta_s - nat_s(p)
 // sc1 / scd = the dense copy of the data sites (zero away from the observations).
@@ -324,6 +270,89 @@ __global__ void k_data_site_update(const double* __restrict__ fx_mus, const int6
     const Mat<D> o2 = mat_load<D>(d2 + i * DD);
     vec_store<D>(d1 + i * D, (1.0 - lr) * o1 + lr * g1);
     mat_store<D>(d2 + i * DD, (1.0 - lr) * o2 + lr * gS);
+}
+
+// Steady state of the carried route with the girsanov sites held implicitly in theta (VDP_FLAG_SITES_IN_NATURALS:
+// theta is the state, g = theta - nat(p) - scatter(data sites) is formed on request): update_data_sites
+// (variational_cvi_sde.py:301-314, the statements of k_data_site_update) and the patch of theta in ONE launch with one
+// block per sequence.  theta changes by the change of the data sites at the observed grid points, whose previous sum
+// is the dense copy's (sc1 / scd) current entry; of several entries on one grid point the first does the work.  The
+// sequence's grid indices sit in shared memory for that duplicate scan, and the data sites of all its observations
+// are updated before any of them is summed.  n_obs <= kObsMaxShared.
+constexpr int kObsBlock = 64;
+constexpr int kObsMaxShared = 128;
+template <int D>
+__global__ void __launch_bounds__(kObsBlock) k_obs_update_patch(
+    const double* __restrict__ fx_mus, const int64_t* __restrict__ obs_idx, const double* __restrict__ obs_y,
+    Mat<D> lik_chol, double lr, const double* __restrict__ lr_dev, const int32_t* __restrict__ active,
+    int skip_data_update, double* __restrict__ d1, double* __restrict__ d2, double* __restrict__ th1,
+    double* __restrict__ thd, double* __restrict__ sc1, double* __restrict__ scd, int64_t N, int64_t n_obs) {
+    __shared__ int64_t row[kObsMaxShared];
+    constexpr int DD = D * D;
+    const int64_t b = blockIdx.x;
+    if (lr_dev) lr = (!active || active[b]) ? lr_dev[b] : 0.0;
+    for (int64_t j = threadIdx.x; j < n_obs; j += kObsBlock) {
+        const int64_t i = b * n_obs + j;
+        const int64_t k = obs_idx[i];
+        row[j] = k;
+        if (skip_data_update) continue;
+        const Vec<D> mu = vec_load<D>(fx_mus + (b * (N + 1) + k) * D);
+        const Mat<D> inv = chol_inverse(lik_chol);
+        const Vec<D> gmu = mv(sym(inv), vec_load<D>(obs_y + i * D) - mu);
+        const Mat<D> gS = -0.5 * inv;
+        const Vec<D> g1 = gmu - 2.0 * mv(gS, mu);
+        const Vec<D> o1 = vec_load<D>(d1 + i * D);
+        const Mat<D> o2 = mat_load<D>(d2 + i * DD);
+        vec_store<D>(d1 + i * D, (1.0 - lr) * o1 + lr * g1);
+        mat_store<D>(d2 + i * DD, (1.0 - lr) * o2 + lr * gS);
+    }
+    __syncthreads();
+    for (int64_t j = threadIdx.x; j < n_obs; j += kObsBlock) {
+        const int64_t k = row[j];
+        if (k < 0 || k > N) continue;
+        Vec<D> s1 = vec_zero<D>();
+        Mat<D> s2 = mat_zero<D>();
+        bool mine = true;
+        for (int64_t jj = 0; jj < n_obs; ++jj) {
+            if (row[jj] != k) continue;
+            if (jj < j) { mine = false; break; }
+            s1 = s1 + vec_load<D>(d1 + (b * n_obs + jj) * D);
+            s2 = s2 + mat_load<D>(d2 + (b * n_obs + jj) * DD);
+        }
+        if (!mine) continue;
+        const int64_t i = b * (N + 1) + k;
+        vec_store<D>(th1 + i * D, vec_load<D>(th1 + i * D) + (s1 - vec_load<D>(sc1 + i * D)));
+        mat_store<D>(thd + i * DD, mat_load<D>(thd + i * DD) + (s2 - mat_load<D>(scd + i * DD)));
+        vec_store<D>(sc1 + i * D, s1);
+        mat_store<D>(scd + i * DD, s2);
+    }
+}
+// The data-site part of the girsanov update when the sites are held in theta: the update g += lr (scatter(data sites)
+// - dKL/d eta) (variational_cvi_sde.py:286-292) moves theta by lr * scatter(data sites) at the observed grid points --
+// applied here, one block per sequence (the first of several entries on one grid point does the work, from the dense
+// copy's summed entry) -- and by -lr * dKL/d eta everywhere, which the forward pass that follows applies.
+template <int D>
+__global__ void __launch_bounds__(kObsBlock) k_add_data_step_seq(
+    const int64_t* __restrict__ obs_idx, const double* __restrict__ sc1, const double* __restrict__ scd,
+    double* __restrict__ th1, double* __restrict__ thd, double lr, const double* __restrict__ lr_dev,
+    const int32_t* __restrict__ active, int64_t N, int64_t n_obs) {
+    __shared__ int64_t row[kObsMaxShared];
+    constexpr int DD = D * D;
+    const int64_t b = blockIdx.x;
+    for (int64_t j = threadIdx.x; j < n_obs; j += kObsBlock) row[j] = obs_idx[b * n_obs + j];
+    if (lr_dev) lr = (!active || active[b]) ? lr_dev[b] : 0.0;
+    __syncthreads();
+    for (int64_t j = threadIdx.x; j < n_obs; j += kObsBlock) {
+        const int64_t k = row[j];
+        if (k < 0 || k > N) continue;
+        bool mine = true;
+        for (int64_t jj = 0; jj < j; ++jj)
+            if (row[jj] == k) { mine = false; break; }
+        if (!mine) continue;
+        const int64_t i = b * (N + 1) + k;
+        vec_store<D>(th1 + i * D, vec_load<D>(th1 + i * D) + lr * vec_load<D>(sc1 + i * D));
+        mat_store<D>(thd + i * DD, mat_load<D>(thd + i * DD) + lr * mat_load<D>(scd + i * DD));
+    }
 }
 
 // variational_expectation (variational_cvi_sde.py:319-337): one warp per sequence, the lanes stride over the

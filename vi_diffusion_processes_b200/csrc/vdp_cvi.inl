@@ -222,14 +222,6 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     const int64_t B = p.B, N = p.N;
     const DriftParams P = make_params(p.drift_params);
     int rc;
-    // (A) update_data_sites  variational_cvi_sde.py:301-317
-    if (!(p.flags & VDP_FLAG_SKIP_DATA_UPDATE) && p.n_obs > 0) {
-        prof_mark(VDP_PHASE_DATA_SITES, st);
-        k_data_site_update<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
-            p.fx_mus, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.lr_data, p.d1, p.d2, B, N, p.n_obs, p.lr_data_dev,
-            p.active_dev);
-        VDP_CHECK_LAUNCH();
-    }
     // the naturals written by the previous update's girsanov kernel are still valid away from the observations
     const bool carried = (p.flags & VDP_FLAG_NATURALS_CARRIED) && p.n_obs <= 128 && node1 < 0 &&
                          !g_cfg.no_carried_naturals;
@@ -237,16 +229,29 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
     // theta itself, g1 / gd / gs are neither read nor written (vdp_cvi_materialize_sites forms them on request)
     const bool lazy = carried && (p.flags & VDP_FLAG_SITES_IN_NATURALS) && !stop_after_sites &&
                       !(p.flags & VDP_FLAG_SKIP_GIRSANOV);
-    if (carried && p.n_obs > 0) {
+    // (A) update_data_sites  variational_cvi_sde.py:301-317
+    if (lazy && p.n_obs > 0) {
+        // ... and the patch of theta at the observed grid points in the same launch (one block per sequence)
         prof_mark(VDP_PHASE_SITES_TO_NAT, st);
-        if (lazy)
-            k_patch_naturals_delta<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
-                p.d1, p.d2, p.obs_idx, w.th1, w.thd, w.sc1, w.scd, B, N, p.n_obs);
-        else
+        k_obs_update_patch<D><<<(unsigned)B, kObsBlock, 0, st>>>(
+            p.fx_mus, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.lr_data, p.lr_data_dev, p.active_dev,
+            (p.flags & VDP_FLAG_SKIP_DATA_UPDATE) ? 1 : 0, p.d1, p.d2, w.th1, w.thd, w.sc1, w.scd, N, p.n_obs);
+        VDP_CHECK_LAUNCH();
+    } else {
+        if (!(p.flags & VDP_FLAG_SKIP_DATA_UPDATE) && p.n_obs > 0) {
+            prof_mark(VDP_PHASE_DATA_SITES, st);
+            k_data_site_update<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
+                p.fx_mus, p.obs_idx, p.obs_y, host_mat<D>(p.lik_chol), p.lr_data, p.d1, p.d2, B, N, p.n_obs,
+                p.lr_data_dev, p.active_dev);
+            VDP_CHECK_LAUNCH();
+        }
+        if (carried && p.n_obs > 0) {
+            prof_mark(VDP_PHASE_SITES_TO_NAT, st);
             k_patch_naturals<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
                 p.pA, p.pb, p.pcholQ, p.pmu0, p.pcholP0, p.g1, p.gd, p.d1, p.d2, p.obs_idx, w.th1, w.thd, w.sc1, w.scd,
                 B, N, p.n_obs);
-        VDP_CHECK_LAUNCH();
+            VDP_CHECK_LAUNCH();
+        }
     }
     // the rebuild between the two site updates feeds k_kl_grad (A, means, marginal covariances): no chol Q needed
     const bool girsanov_follows = !(p.flags & VDP_FLAG_SKIP_GIRSANOV);
@@ -263,8 +268,8 @@ static int run_site_update(const vdp_cvi_problem& p, const CviWs& w, cudaStream_
         if (fused_fwd) {
             prof_mark(VDP_PHASE_KL_GRAD, st);
             if (p.n_obs > 0) {
-                k_add_data_step<1><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(
-                    p.obs_idx, w.sc1, w.scd, w.th1, w.thd, p.lr_girsanov, p.lr_girsanov_dev, p.active_dev, B, N, p.n_obs);
+                k_add_data_step_seq<1><<<(unsigned)B, kObsBlock, 0, st>>>(
+                    p.obs_idx, w.sc1, w.scd, w.th1, w.thd, p.lr_girsanov, p.lr_girsanov_dev, p.active_dev, N, p.n_obs);
                 VDP_CHECK_LAUNCH();
             }
             FwdFusedArgs fa;
