@@ -51,24 +51,37 @@ static int check_vgp(const vdp_vgp_problem* p, VgpWs& w) {
 }
 
 // forward_pass as one fused sweep (k_vgp_forward_tiled): to_ssm, means and the covariance recursion
-template <int D>
-static int run_vgp_forward_tiled(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st) {
+// DRIFT >= 0 (D = 1, polynomial drift) with esde_parts != NULL: the FULL pass also evaluates the E_sde terms and their
+// gradients (w.dEdm, w.dEdS) and leaves *esde_parts partial sums of the terms per sequence in w.terms.
+template <int D, int DRIFT = -1>
+static int run_vgp_forward_tiled(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st,
+                                 int64_t* esde_parts = nullptr) {
     using C = TileCfg<D>;
     using Ops = FwdOps<D>;
     constexpr int L = C::Lm;
     constexpr int NST = 1;
+    constexpr bool ES = DRIFT >= 0;
     constexpr size_t smem = vgp_forward_tiled_smem<D, C::T, L, NST>();
+    constexpr size_t smem_full = vgp_forward_tiled_smem<D, C::T, L, NST, ES>();
     const int64_t B = p.B, N = p.N;
     SegScratch sc(w.seg, kSegScratchBytes);
     const SegPlan pl = plan_segments(B, N, C::T * L, true);
     const unsigned grid = (unsigned)(B * pl.nseg);
     const int stab = (p.flags & VDP_VGP_STABILIZE) ? 1 : 0;
+    VgpEsdeArgs es;
+    if (ES) {
+        es.P = make_params(p.drift_params);
+        es.q = p.q[0]; es.dt = p.dt;
+        es.dEdm = w.dEdm; es.dEdS = w.dEdS; es.partials = w.terms;
+        es.tiles_per_seg = (int)((pl.seg_len + C::T * L - 1) / (C::T * L));
+        *esde_parts = (int64_t)pl.nseg * es.tiles_per_seg;
+    }
     int rc;
-    if ((rc = allow_smem(k_vgp_forward_tiled<D, C::T, L, SWEEP_FULL, NST>, smem))) return rc;
+    if ((rc = allow_smem(k_vgp_forward_tiled<D, C::T, L, SWEEP_FULL, NST, DRIFT>, smem_full))) return rc;
     if (pl.nseg == 1) {
-        k_vgp_forward_tiled<D, C::T, L, SWEEP_FULL, NST><<<grid, C::T, smem, st>>>(
+        k_vgp_forward_tiled<D, C::T, L, SWEEP_FULL, NST, DRIFT><<<grid, C::T, smem_full, st>>>(
             p.A, p.b, host_mat<D>(p.q), p.time_grid, stab, p.q_mean, p.q_chol, p.m, p.S, B, N, 1, pl.seg_len, nullptr,
-            nullptr, nullptr, p.status);
+            nullptr, nullptr, p.status, es);
         VDP_CHECK_LAUNCH();
         return VDP_OK;
     }
@@ -82,9 +95,9 @@ static int run_vgp_forward_tiled(const vdp_vgp_problem& p, const VgpWs& w, cudaS
         init, el, p.status);
     VDP_CHECK_LAUNCH();
     if ((rc = launch_seg_scan<Ops>(el, init, carry, B, pl.nseg, 0, st))) return rc;
-    k_vgp_forward_tiled<D, C::T, L, SWEEP_FULL, NST><<<grid, C::T, smem, st>>>(
+    k_vgp_forward_tiled<D, C::T, L, SWEEP_FULL, NST, DRIFT><<<grid, C::T, smem_full, st>>>(
         p.A, p.b, host_mat<D>(p.q), p.time_grid, stab, p.q_mean, p.q_chol, p.m, p.S, B, N, pl.nseg, pl.seg_len, carry,
-        nullptr, nullptr, p.status);
+        nullptr, nullptr, p.status, es);
     VDP_CHECK_LAUNCH();
     return VDP_OK;
 }
@@ -136,6 +149,21 @@ static int vgp_esde(const vdp_vgp_problem& p, const VgpWs& w, bool grads, cudaSt
 }
 
 // vi_sde.py:289-347
+// forward pass + E_sde terms and gradients.  *parts > 0: the forward sweep did both (partial sums of the terms in
+// w.terms); *parts = 0: the two separate passes ran and w.terms holds one term per transition.
+template <int DRIFT, int D>
+static int vgp_forward_esde(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st, int64_t* parts) {
+    *parts = 0;
+    int rc;
+    if constexpr (D == 1 && DriftStep1<DRIFT>::kCubic) {
+        if (use_tiled_sweeps(p.B, p.N) && !(p.flags & (VDP_VGP_REFACTOR_PRECISION | VDP_VGP_GH_QUADRATURE)) &&
+            !g_cfg.refactor_precision && !g_cfg.gh_quadrature && !g_cfg.no_fused_forward)
+            return run_vgp_forward_tiled<D, DRIFT>(p, w, st, parts);
+    }
+    if ((rc = vgp_forward<D>(p, w, st))) return rc;
+    return vgp_esde<DRIFT, D>(p, w, true, st);
+}
+
 // have_grads: w.dEdm / w.dEdS already hold dE_sde/dm, dE_sde/dS of the current (A, b, m, S)
 template <int DRIFT, int D>
 static int vgp_lagrange(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st, bool have_grads = false) {
@@ -226,12 +254,13 @@ static int vgp_update_initial(const vdp_vgp_problem& p, cudaStream_t st) {
 }
 
 // vi_sde.py:436-455 (m, S of the problem must be the current forward pass)
-// with_grads: the E_sde pass also leaves dE_sde/dm, dE_sde/dS in the workspace (for the sweep that follows)
 template <int DRIFT, int D>
-static int vgp_elbo(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st, bool with_grads = false) {
+// terms_ready >= 0: w.terms already holds the E_sde terms (terms_ready = 0: one per transition; > 0: that many partial
+// sums per sequence, from the fused forward sweep)
+static int vgp_elbo(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st, int64_t terms_ready = -1) {
     int rc;
-    if ((rc = vgp_esde<DRIFT, D>(p, w, with_grads, st))) return rc;
-    k_reduce_terms<<<(unsigned)p.B, 256, 0, st>>>(w.terms, p.N, w.esde);
+    if (terms_ready < 0 && (rc = vgp_esde<DRIFT, D>(p, w, false, st))) return rc;
+    k_reduce_terms<<<(unsigned)p.B, 256, 0, st>>>(w.terms, terms_ready > 0 ? terms_ready : p.N, w.esde);
     VDP_CHECK_LAUNCH();
     if (p.n_obs > 0) {
         k_variational_expectation<D><<<grid_for(p.B * 32, kPtBlock), kPtBlock, 0, st>>>(
@@ -311,12 +340,13 @@ VDP_VGP_ENTRY(vdp_vgp_elbo, { if ((rc = vgp_elbo<kDrift, kD>(*p, w, st))) return
 // VDP_VGP_STATE_CARRIED skips the head)
 VDP_VGP_ENTRY(vdp_vgp_sweep, {
     const bool carried = (p->flags & VDP_VGP_STATE_CARRIED) != 0;
-    if (!carried) { if ((rc = vgp_forward<kD>(*p, w, st))) return rc; }
-    if ((rc = vgp_lagrange<kDrift, kD>(*p, w, st, carried))) return rc;
+    int64_t parts = 0;
+    if (!carried) { if ((rc = vgp_forward_esde<kDrift, kD>(*p, w, st, &parts))) return rc; }
+    if ((rc = vgp_lagrange<kDrift, kD>(*p, w, st, true))) return rc;
     if ((rc = vgp_update_param<kDrift, kD>(*p, st))) return rc;
     if (p->flags & VDP_VGP_UPDATE_X0) { if ((rc = vgp_update_initial<kD>(*p, st))) return rc; }
-    if ((rc = vgp_forward<kD>(*p, w, st))) return rc;
-    if ((rc = vgp_elbo<kDrift, kD>(*p, w, st, true))) return rc;
+    if ((rc = vgp_forward_esde<kDrift, kD>(*p, w, st, &parts))) return rc;
+    if ((rc = vgp_elbo<kDrift, kD>(*p, w, st, parts))) return rc;
 })
 
 }  // extern "C"

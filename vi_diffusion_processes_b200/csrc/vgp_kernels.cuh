@@ -67,21 +67,71 @@ __global__ void k_vgp_to_ssm(const double* __restrict__ A, const double* __restr
 template <int D>
 using FwdOps = PairOps<AffVecOps<D>, AffSymOps<D>>;
 
-template <int D, int T, int L, int MODE, int NSTAGE = 1>
+// process noise of one step as the state-space model holds it, chol(delta q) chol(delta q)^T (drift.py:64-116 keeps the
+// factor); a scalar needs no round trip through the square root
+template <int D>
+__device__ __forceinline__ Mat<D> step_noise(double delta, const Mat<D>& q, bool& ok) {
+    if constexpr (D == 1) {
+        Mat<1> r;
+        r.a[0] = delta * q.a[0];
+        if (!(r.a[0] > 0.0)) ok = false;
+        return r;
+    } else {
+        const Mat<D> cQ = chol(delta * q, ok);
+        return mmT(cQ, cQ);
+    }
+}
+
+// E_sde term of one transition and its gradients for a polynomial scalar drift in closed form (the quantities of
+// k_vgp_esde<.., CLOSED> below: term = 0.5 dt E || (-A) x + b - f(x) ||^2 / q at the marginal N(m, S) of the
+// transition's first grid point; dEdm, dEdS divided by dt as vi_sde.py:206-225 does).  Scalar algebra: the adjoint
+// of chol(S) collapses to a division by S, so no square root is needed (sinv = 1 / q, hoisted by the caller).
+template <int DRIFT>
+__device__ __forceinline__ void vgp_esde_closed1(const DriftParams& P, double sinv, double dt, double A0, double b0,
+                                                 double m1, double Sk, double& term, double& dm, double& dS, bool& ok) {
+    if (!(Sk > 0.0)) ok = false;
+    const double a1 = -A0;
+    const typename DriftStep1<DRIFT>::K kst = DriftStep1<DRIFT>::prepare(P, -1.0, 1.0 - a1, -b0);
+    double c0, c1, c2, c3;
+    DriftStep1<DRIFT>::taylor(kst, m1, c0, c1, c2, c3);
+    CubicMoments cm;
+    cm.template eval<true>(c0, c1, c2, c3, Sk);
+    term = (0.5 * dt) * (sinv * cm.Ed2);
+    dm = sinv * cm.Ejd;
+    dS = (0.5 * sinv) * (cm.Ejde * rcp_fast(Sk));
+}
+
+// DRIFT >= 0 (D = 1, polynomial drift, FULL mode): the sweep also evaluates the E_sde terms and their gradients of
+// every transition from the marginals it has just computed -- per-tile partial sums of the terms and dEdm / dEdS leave
+// with the tile -- so the separate pass over A, b, m, S (k_vgp_esde, 56 bytes per grid step) is not needed.
+struct VgpEsdeArgs {
+    DriftParams P;
+    double q = 1.0, dt = 0.0;
+    double *dEdm = nullptr, *dEdS = nullptr;   // [B, N]
+    double* partials = nullptr;                // [B, nseg * tiles_per_seg]
+    int tiles_per_seg = 0;
+};
+
+template <int D, int T, int L, int MODE, int NSTAGE = 1, int DRIFT = -1>
 __global__ void __launch_bounds__(T)
 k_vgp_forward_tiled(const double* __restrict__ A, const double* __restrict__ bv, Mat<D> q,
                     const double* __restrict__ time_grid, int stabilize, const double* __restrict__ mu0,
                     const double* __restrict__ cholP0, double* __restrict__ m, double* __restrict__ S, int64_t B,
                     int64_t N, int nseg, int64_t seg_len, const typename FwdOps<D>::State* __restrict__ carry_in,
                     typename FwdOps<D>::State* __restrict__ init_out, typename FwdOps<D>::Elem* __restrict__ seg_elem,
-                    int64_t* status) {
+                    int64_t* status, VgpEsdeArgs es = VgpEsdeArgs()) {
     constexpr int DD = D * D, TL = T * L;
+    constexpr bool ESDE = (DRIFT >= 0) && (MODE == SWEEP_FULL);
+    static_assert(DRIFT < 0 || (D == 1 && NSTAGE == 1), "the fused E_sde terms are scalar, single staging buffer");
     using Ops = FwdOps<D>;
     constexpr int SM = tile_slots(TL * DD), SV = tile_slots(TL * D);
     constexpr int kStage = SM + SV;
     extern __shared__ __align__(16) double smem[];
     double* stage0 = smem + kRingHeaderDoubles;
-    typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(stage0 + NSTAGE * kStage);
+    double* rawGm = stage0 + NSTAGE * kStage;                 // ESDE: dEdm / dEdS of the tile, then the reduction
+    double* rawGS = rawGm + (ESDE ? SM : 0);
+    double* xcarry = rawGS + (ESDE ? SM : 0);                 // ESDE: stored marginal of the tile's last grid point
+    typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(xcarry + (ESDE ? 4 : 0));
     TileRing<NSTAGE> ring;
     ring.init(smem);
     const int64_t b = blockIdx.x / nseg;
@@ -103,6 +153,7 @@ k_vgp_forward_tiled(const double* __restrict__ A, const double* __restrict__ bv,
     st.b = mat_zero<D>();
     if (MODE == SWEEP_FULL && seg > 0) st = carry_in[b * nseg + seg];
     typename Ops::Elem seg_tot = Ops::identity();
+    const double es_sinv = ESDE ? 1.0 / es.q : 0.0;
     for (int ti = 0; ti < ntiles; ++ti) {
         const int64_t tk = t0 + (int64_t)ti * TL;
         const int cnt = (int)min((int64_t)TL, t1 - tk);
@@ -134,13 +185,14 @@ k_vgp_forward_tiled(const double* __restrict__ A, const double* __restrict__ bv,
             Mat<D> At = delta * (-1.0 * mat_load<D>(sA + (k0 + t) * DD)) + mat_eye<D>();
             Vec<D> bt = delta * vec_load<D>(sb + (k0 + t) * D);
             if (stabilize) { At = vgp_fix(At, -1.0, 1.0); bt = vgp_fix(bt, -1.0, 1.0); }
-            mat_store<D>(sA + (k0 + t) * DD, At);
-            vec_store<D>(sb + (k0 + t) * D, bt);
-            const Mat<D> cQ = chol(delta * q, ok);
+            if (!ESDE) {   // (ESDE keeps the drift's own A, b staged: the replay needs them for the E_sde terms)
+                mat_store<D>(sA + (k0 + t) * DD, At);
+                vec_store<D>(sb + (k0 + t) * D, bt);
+            }
             typename Ops::Elem s;
             s.a.M = At;
             s.a.v = bt;
-            s.b.C = mmT(cQ, cQ);
+            s.b.C = step_noise<D>(delta, q, ok);
             s.b.G = transpose(At);
             e = Ops::combine(e, s);
         }
@@ -156,21 +208,86 @@ k_vgp_forward_tiled(const double* __restrict__ A, const double* __restrict__ bv,
             continue;
         }
         typename Ops::State cur = Ops::apply(excl, st);
+        const typename Ops::State tile_in = st;
         st = Ops::apply(total, st);
+        double* sGm = rawGm;
+        double* sGS = rawGS;
+        double keepA = 0.0, keepb = 0.0, acc = 0.0;
+        if constexpr (ESDE) {   // outputs placed with the parity of their destination (bulk stores)
+            sGm += tile_off(es.dEdm + (b * N + tk));
+            sGS += tile_off(es.dEdS + (b * N + tk));
+        }
         for (int t = 0; t < len; ++t) {
             const double delta = time_grid[tk + k0 + t + 1] - time_grid[tk + k0 + t];
-            const Mat<D> At = mat_load<D>(sA + (k0 + t) * DD);
-            const Mat<D> cQ = chol(delta * q, ok);
-            cur.a = vec_load<D>(sb + (k0 + t) * D) + mv(At, cur.a);
-            cur.b = mmT(cQ, cQ) + mm(At, mmT(cur.b, At));
+            Mat<D> At;
+            Vec<D> bt;
+            if constexpr (ESDE) {
+                const Mat<D> A0 = mat_load<D>(sA + (k0 + t) * DD);
+                const Vec<D> b0 = vec_load<D>(sb + (k0 + t) * D);
+                if (t == 0) {
+                    keepA = A0.a[0];       // the marginal of the chunk's first grid point is the neighbour's to store
+                    keepb = b0.v[0];
+                } else {
+                    double term, dm, dS;
+                    vgp_esde_closed1<(DRIFT < 0 ? 0 : DRIFT)>(es.P, es_sinv, es.dt, A0.a[0], b0.v[0], cur.a.v[0],
+                                                              cur.b.a[0], term, dm, dS, ok);
+                    acc += term;
+                    sGm[k0 + t] = dm;
+                    sGS[k0 + t] = dS;
+                }
+                At = delta * (-1.0 * A0) + mat_eye<D>();
+                bt = delta * b0;
+                if (stabilize) { At = vgp_fix(At, -1.0, 1.0); bt = vgp_fix(bt, -1.0, 1.0); }
+            } else {
+                At = mat_load<D>(sA + (k0 + t) * DD);
+                bt = vec_load<D>(sb + (k0 + t) * D);
+            }
+            cur.a = bt + mv(At, cur.a);
+            cur.b = step_noise<D>(delta, q, ok) + mm(At, mmT(cur.b, At));
             vec_store<D>(sb + (k0 + t) * D, cur.a);
             mat_store<D>(sA + (k0 + t) * DD, cur.b);
+        }
+        if constexpr (ESDE) {
+            if (len > 0 && k0 + len == cnt) {   // the tile's last stored marginal, for the next tile's first transition
+                xcarry[2 * (ti & 1)] = cur.a.v[0];
+                xcarry[2 * (ti & 1) + 1] = cur.b.a[0];
+            }
+            __syncthreads();
+            if (len > 0) {
+                double m1, S1;
+                if (threadIdx.x > 0) { m1 = sb[k0 - 1]; S1 = sA[k0 - 1]; }
+                else if (ti > 0) { m1 = xcarry[2 * ((ti - 1) & 1)]; S1 = xcarry[2 * ((ti - 1) & 1) + 1]; }
+                else { m1 = tile_in.a.v[0]; S1 = tile_in.b.a[0]; }   // sequence start (or the segment's incoming carry)
+                double term, dm, dS;
+                vgp_esde_closed1<(DRIFT < 0 ? 0 : DRIFT)>(es.P, es_sinv, es.dt, keepA, keepb, m1, S1, term, dm, dS, ok);
+                acc += term;
+                sGm[k0] = dm;
+                sGS[k0] = dS;
+            }
+            if (!ok) report_not_pd(status, b * (N + 1) + tk + k0);
         }
         fence_async_smem();
         __syncthreads();
         tile_store<T>(m + (b * (N + 1) + tk + 1) * D, sb, cnt * D);
         tile_store<T>(S + (b * (N + 1) + tk + 1) * DD, sA, cnt * DD);
+        if constexpr (ESDE) {
+            tile_store<T>(es.dEdm + (b * N + tk), sGm, cnt);
+            tile_store<T>(es.dEdS + (b * N + tk), sGS, cnt);
+        }
         if (threadIdx.x == 0) bulk_commit();
+        if constexpr (ESDE) {
+            // sum of the tile's terms: fixed tree over the block (scratch behind the carry slots' scan area is busy:
+            // the staged b array has been handed to the bulk store, so the reduction uses its own slots)
+            double* red = reinterpret_cast<double*>(wtot + T / 32);
+            red[threadIdx.x] = acc;
+            __syncthreads();
+            for (int s2 = T / 2; s2 > 0; s2 >>= 1) {
+                if ((int)threadIdx.x < s2) red[threadIdx.x] += red[threadIdx.x + s2];
+                __syncthreads();
+            }
+            if (threadIdx.x == 0)
+                es.partials[((int64_t)b * nseg + seg) * es.tiles_per_seg + ti] = red[0];
+        }
     }
     if (threadIdx.x == 0) {
         if (MODE != SWEEP_FULL) seg_elem[b * nseg + seg] = seg_tot;
@@ -178,10 +295,10 @@ k_vgp_forward_tiled(const double* __restrict__ A, const double* __restrict__ bv,
     }
 }
 
-template <int D, int T, int L, int NSTAGE = 1>
+template <int D, int T, int L, int NSTAGE = 1, bool ESDE = false>
 constexpr size_t vgp_forward_tiled_smem() {
-    return ((size_t)kRingHeaderDoubles + (size_t)NSTAGE * (tile_slots(T * L * D * D) + tile_slots(T * L * D))) *
-               sizeof(double) +
+    return ((size_t)kRingHeaderDoubles + (size_t)NSTAGE * (tile_slots(T * L * D * D) + tile_slots(T * L * D)) +
+            (ESDE ? 2 * (size_t)tile_slots(T * L * D * D) + 4 + T : 0)) * sizeof(double) +
            (T / 32) * sizeof(typename FwdOps<D>::Elem);
 }
 
