@@ -166,7 +166,9 @@ static int vgp_forward_esde(const vdp_vgp_problem& p, const VgpWs& w, cudaStream
 
 // have_grads: w.dEdm / w.dEdS already hold dE_sde/dm, dE_sde/dS of the current (A, b, m, S)
 template <int DRIFT, int D>
-static int vgp_lagrange(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st, bool have_grads = false) {
+// jumps_sparse: the jump buffers are zero away from the observed grid points (left so by the previous sweep)
+static int vgp_lagrange(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t st, bool have_grads = false,
+                        bool jumps_sparse = false) {
     using C = LagrangeCfg<D>;
     using Ops = LagrangeOps<D>;
     const int64_t B = p.B, N = p.N;
@@ -174,8 +176,14 @@ static int vgp_lagrange(const vdp_vgp_problem& p, const VgpWs& w, cudaStream_t s
     int rc;
     if (!have_grads && (rc = vgp_esde<DRIFT, D>(p, w, true, st))) return rc;
     const size_t n = (size_t)B * (N + 1);
-    VDP_CHECK_CUDA(cudaMemsetAsync(w.dobs_m, 0, n * D * sizeof(double), st));
-    VDP_CHECK_CUDA(cudaMemsetAsync(w.dobs_S, 0, n * D * D * sizeof(double), st));
+    if (!jumps_sparse) {
+        VDP_CHECK_CUDA(cudaMemsetAsync(w.dobs_m, 0, n * D * sizeof(double), st));
+        VDP_CHECK_CUDA(cudaMemsetAsync(w.dobs_S, 0, n * D * D * sizeof(double), st));
+    } else if (p.n_obs > 0) {
+        k_vgp_jump_clear<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(p.obs_idx, w.dobs_m, w.dobs_S, B, N,
+                                                                                  p.n_obs);
+        VDP_CHECK_LAUNCH();
+    }
     if (p.n_obs > 0) {
         k_vgp_jump<D><<<grid_for(B * p.n_obs, kPtBlock), kPtBlock, 0, st>>>(p.m, p.obs_idx, p.obs_y,
                                                                             host_mat<D>(p.lik_chol), w.dobs_m,
@@ -342,7 +350,7 @@ VDP_VGP_ENTRY(vdp_vgp_sweep, {
     const bool carried = (p->flags & VDP_VGP_STATE_CARRIED) != 0;
     int64_t parts = 0;
     if (!carried) { if ((rc = vgp_forward_esde<kDrift, kD>(*p, w, st, &parts))) return rc; }
-    if ((rc = vgp_lagrange<kDrift, kD>(*p, w, st, true))) return rc;
+    if ((rc = vgp_lagrange<kDrift, kD>(*p, w, st, true, carried))) return rc;
     if ((rc = vgp_update_param<kDrift, kD>(*p, st))) return rc;
     if (p->flags & VDP_VGP_UPDATE_X0) { if ((rc = vgp_update_initial<kD>(*p, st))) return rc; }
     if ((rc = vgp_forward_esde<kDrift, kD>(*p, w, st, &parts))) return rc;

@@ -439,6 +439,23 @@ __global__ void k_vgp_jump(const double* __restrict__ m, const int64_t* __restri
     for (int e = 0; e < DD; ++e) atomicAdd(dobs_S + node * DD + e, gS.a[e]);
 }
 
+// the entries k_vgp_jump is about to accumulate into, set to zero (consecutive sweeps: the rest of the two buffers
+// is still zero from the sweep before, so the dense memsets are not repeated)
+template <int D>
+__global__ void k_vgp_jump_clear(const int64_t* __restrict__ obs_idx, double* __restrict__ dobs_m,
+                                 double* __restrict__ dobs_S, int64_t B, int64_t N, int64_t n_obs) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= B * n_obs) return;
+    constexpr int DD = D * D;
+    const int64_t k = obs_idx[i];
+    if (k < 0 || k > N) return;
+    const int64_t node = (i / n_obs) * (N + 1) + k;
+#pragma unroll
+    for (int e = 0; e < D; ++e) dobs_m[node * D + e] = 0.0;
+#pragma unroll
+    for (int e = 0; e < DD; ++e) dobs_S[node * DD + e] = 0.0;
+}
+
 // update_param: one group per transition (b, k), marginal of node k, H = 10
 template <int DRIFT, int D, int H, int G, bool CLOSED = false>
 __global__ void k_vgp_update_param(DriftParams P, Mat<D> q, double pi_factor, int stabilize, double lr,
