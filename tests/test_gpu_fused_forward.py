@@ -54,11 +54,11 @@ def _theta_scale(eng):
 
 
 @pytest.mark.parametrize("drift,params", [(S.DRIFT_DW, [1.0, 1.0]), (S.DRIFT_OU, [0.8])])
-@pytest.mark.parametrize("N", [100, TILE - 1, TILE, TILE + 1, 2 * TILE, 2 * TILE + 1, 5000])
+@pytest.mark.parametrize("N", [2, 3, 10, 100, TILE - 1, TILE, TILE + 1, 2 * TILE, 2 * TILE + 1, 5000])
 def test_fused_forward_equals_three_kernel_route(drift, params, N, vdp_cfg):
     from vi_diffusion_processes_b200 import _lib
     vdp_cfg(SWEEPS="tiled", NSEG=1)
-    B, n_obs = 5, 12
+    B, n_obs = 5, (12 if N >= 100 else 2)
     grid, idx, y = _problem(B, N, n_obs, seed=N, dup=True, ends=(N % 2 == 0))
     fused = _engine(drift, params, grid, idx, y)
     plain = _engine(drift, params, grid, idx, y, flags=_lib.FLAG_NO_FUSED_FORWARD)
