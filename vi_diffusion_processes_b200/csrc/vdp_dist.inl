@@ -21,6 +21,11 @@ namespace vdp {
 #define VDP_DIST_STAGES_N 1
 #endif
 constexpr int kDistStagesN = VDP_DIST_STAGES_N;
+// segments a rank's stretch is split into.  The D = 3 tiles are large (Cholesky 92 KB, naturals_to_ssm 60-74 KB of shared
+// memory per CTA: 2 and 3 resident CTAs per SM), so 4 CTAs per SM worth of segments run as 1.3-2 waves; 6 per SM is a
+// whole number of waves for both (measured on the 10^7-step chain: 592 segments 20.3 ms, 444: 19.5, 888: 19.3)
+template <int D>
+constexpr int64_t kDistTarget = (D == 3) ? 148 * 6 : kTargetBlocks;
 
 template <class Ops>
 __global__ void k_seg_total(const typename Ops::Elem* __restrict__ el, int nseg, int reverse,
@@ -97,7 +102,7 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
     case VDP_SWEEP_CHOL: {
         using Ops = SchurOps<D>;
         constexpr size_t smem = chol_tiled_smem<D, C::T, C::Lc, kSweepStages>();
-        const SegPlan pl = plan_segments(1, N, C::T * C::Lc, true);
+        const SegPlan pl = plan_segments(1, N, C::T * C::Lc, true, kDistTarget<D>);
         DistBufs<Ops> b;
         if (!dist_take<Ops>(sc, pl.nseg, b)) break;
         if (phase == 0) {
@@ -120,7 +125,7 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
     case VDP_SWEEP_MARG: {
         using Ops = MargOps<D>;
         constexpr size_t smem = marg_tiled_smem<D, C::T, C::Lm>();
-        const SegPlan pl = plan_segments(1, N, C::T * C::Lm, true);
+        const SegPlan pl = plan_segments(1, N, C::T * C::Lm, true, kDistTarget<D>);
         DistBufs<Ops> b;
         if (!dist_take<Ops>(sc, pl.nseg, b)) break;
         if (phase == 0) {
@@ -143,7 +148,7 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
     case VDP_SWEEP_INVBAND: {
         using Ops = AffSymOps<D>;
         constexpr size_t smem = invband_tiled_smem<D, C::T, C::Li>();
-        const SegPlan pl = plan_segments(1, N, C::T * C::Li, true);
+        const SegPlan pl = plan_segments(1, N, C::T * C::Li, true, kDistTarget<D>);
         DistBufs<Ops> b;
         if (!dist_take<Ops>(sc, pl.nseg, b)) break;
         if (phase == 0) {
@@ -166,7 +171,7 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
         using OpsS = AffSymOps<D>;
         using OpsY = AffVecOps<D>;
         constexpr size_t smem = nat2ssm_tiled_smem<D, C::T, C::Ln, false, false, kDistStagesN>();
-        const SegPlan pl = plan_segments(1, N, C::T * C::Ln, true);
+        const SegPlan pl = plan_segments(1, N, C::T * C::Ln, true, kDistTarget<D>);
         DistBufs<OpsS> bs;
         DistBufs<OpsY> by;
         if (!dist_take<OpsS>(sc, pl.nseg, bs) || !dist_take<OpsY>(sc, pl.nseg, by)) break;
@@ -210,7 +215,7 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
         using Ops = AffVecOps<D>;
         constexpr int L = (D == 1) ? C::Lm : 2 * C::Lm;
         constexpr size_t smem = mean_tiled_smem<D, C::T, L, false, kStagesM>();
-        const SegPlan pl = plan_segments(1, N, C::T * L, true);
+        const SegPlan pl = plan_segments(1, N, C::T * L, true, kDistTarget<D>);
         DistBufs<Ops> b;
         if (!dist_take<Ops>(sc, pl.nseg, b)) break;
         if (phase == 0) {

@@ -90,13 +90,14 @@ static inline bool use_tiled_sweeps(int64_t B, int64_t N) {
     return N >= 512 || (B < 148 * 64 && N >= 32);
 }
 
-static inline SegPlan plan_segments(int64_t B, int64_t N, int tile_steps, bool have_scratch) {
+static inline SegPlan plan_segments(int64_t B, int64_t N, int tile_steps, bool have_scratch,
+                                    int64_t target_blocks = kTargetBlocks) {
     int64_t want = 1;
     const int forced = g_cfg.nseg;
     if (forced > 0) {
         want = forced;
-    } else if (B < kTargetBlocks) {
-        want = (kTargetBlocks + B - 1) / B;
+    } else if (B < target_blocks) {
+        want = (target_blocks + B - 1) / B;
         want = std::min<int64_t>(want, std::max<int64_t>(1, N / tile_steps));   // >= one full tile per segment
     }
     want = std::min<int64_t>(want, std::max<int64_t>(1, kMaxSegTotal / std::max<int64_t>(B, 1)));
