@@ -105,34 +105,46 @@ __global__ void k_seg_scan(const typename Ops::Elem* __restrict__ elems, const t
     }
 }
 
-// The same carries for FEW sequences with MANY segments (one long chain split in time): one block per sequence, one
-// thread per segment, block-wide scan of the segment elements -- log depth instead of nseg sequential compositions
-// (592 segments of a D = 3 chain: 1 ms -> 0.03 ms per scan).  nseg <= T.
-template <class Ops, int T>
-__global__ void __launch_bounds__(T) k_seg_scan_par(const typename Ops::Elem* __restrict__ elems,
-                                                    const typename Ops::State* __restrict__ init,
-                                                    typename Ops::State* __restrict__ carry, int nseg, int reverse) {
+// The same carries for FEW sequences with MANY segments (one long chain split in time): one block per sequence, every
+// thread takes a run of consecutive segments (in sweep order), composes them, the block scans the run totals -- log
+// depth instead of nseg sequential compositions -- and each thread then replays its run from its incoming state with
+// `apply`, which is cheaper than `combine`.  256 threads keep the D = 3 elements (up to 40 doubles) in registers.
+// (592 segments of a D = 3 chain: 1 ms -> 0.03 ms per scan.)
+constexpr int kSegScanThreads = 256;
+template <class Ops>
+__global__ void __launch_bounds__(kSegScanThreads) k_seg_scan_par(const typename Ops::Elem* __restrict__ elems,
+                                                                 const typename Ops::State* __restrict__ init,
+                                                                 typename Ops::State* __restrict__ carry, int nseg,
+                                                                 int reverse) {
+    constexpr int T = kSegScanThreads;
     __shared__ typename Ops::Elem wtot[T / 32];
     const int64_t b = blockIdx.x;
-    const int i = threadIdx.x;                       // position in sweep order
-    const int s = reverse ? nseg - 1 - i : i;
+    const int per = (nseg + T - 1) / T;
+    const int i0 = threadIdx.x * per, i1 = min(nseg, i0 + per);      // positions in sweep order
     typename Ops::Elem e = Ops::identity();
-    if (i < nseg) e = elems[b * nseg + s];
+    for (int i = i0; i < i1; ++i) e = Ops::combine(e, elems[b * nseg + (reverse ? nseg - 1 - i : i)]);
     typename Ops::Elem total;
     const typename Ops::Elem excl = block_exclusive_scan<Ops, T>(e, wtot, total);
-    if (i < nseg) carry[b * nseg + s] = Ops::apply(excl, init[b]);
+    typename Ops::State st = Ops::apply(excl, init[b]);
+    for (int i = i0; i < i1; ++i) {
+        const int s = reverse ? nseg - 1 - i : i;
+        carry[b * nseg + s] = st;
+        st = Ops::apply(elems[b * nseg + s], st);
+    }
 }
 // composition of all segment elements of one sequence (the rank total of the time-sharded sweeps)
-template <class Ops, int T>
-__global__ void __launch_bounds__(T) k_seg_total_par(const typename Ops::Elem* __restrict__ elems, int nseg, int reverse,
-                                                     typename Ops::Elem* __restrict__ total_out) {
+template <class Ops>
+__global__ void __launch_bounds__(kSegScanThreads) k_seg_total_par(const typename Ops::Elem* __restrict__ elems, int nseg,
+                                                                  int reverse, typename Ops::Elem* __restrict__ total_out) {
+    constexpr int T = kSegScanThreads;
     __shared__ typename Ops::Elem wtot[T / 32];
-    const int i = threadIdx.x;
+    const int per = (nseg + T - 1) / T;
+    const int i0 = threadIdx.x * per, i1 = min(nseg, i0 + per);
     typename Ops::Elem e = Ops::identity();
-    if (i < nseg) e = elems[reverse ? nseg - 1 - i : i];
+    for (int i = i0; i < i1; ++i) e = Ops::combine(e, elems[reverse ? nseg - 1 - i : i]);
     typename Ops::Elem total;
     block_exclusive_scan<Ops, T>(e, wtot, total);
-    if (i == 0) *total_out = total;
+    if (threadIdx.x == 0) *total_out = total;
 }
 
 // ---------------------------------------------------------------------------------------------------

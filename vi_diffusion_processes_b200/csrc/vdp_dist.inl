@@ -40,9 +40,7 @@ __global__ void k_seg_total(const typename Ops::Elem* __restrict__ el, int nseg,
 template <class Ops>
 static inline void launch_seg_total(const typename Ops::Elem* el, int nseg, int reverse, typename Ops::Elem* total,
                                     cudaStream_t st) {
-    if (nseg >= 16 && nseg <= 128) k_seg_total_par<Ops, 128><<<1, 128, 0, st>>>(el, nseg, reverse, total);
-    else if (nseg > 128 && nseg <= 512) k_seg_total_par<Ops, 512><<<1, 512, 0, st>>>(el, nseg, reverse, total);
-    else if (nseg > 512 && nseg <= 1024) k_seg_total_par<Ops, 1024><<<1, 1024, 0, st>>>(el, nseg, reverse, total);
+    if (nseg >= 16) k_seg_total_par<Ops><<<1, kSegScanThreads, 0, st>>>(el, nseg, reverse, total);
     else k_seg_total<Ops><<<1, 32, 0, st>>>(el, nseg, reverse, total);
 }
 

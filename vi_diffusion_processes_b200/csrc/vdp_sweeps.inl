@@ -120,10 +120,8 @@ template <class Ops>
 static inline int launch_seg_scan(const typename Ops::Elem* el, const typename Ops::State* init,
                                   typename Ops::State* carry, int64_t B, int nseg, int reverse, cudaStream_t st) {
     // few sequences, many segments: scan the segments of a sequence in parallel
-    if (B <= 16 && nseg >= 16 && nseg <= 1024) {
-        if (nseg <= 128) k_seg_scan_par<Ops, 128><<<(unsigned)B, 128, 0, st>>>(el, init, carry, nseg, reverse);
-        else if (nseg <= 512) k_seg_scan_par<Ops, 512><<<(unsigned)B, 512, 0, st>>>(el, init, carry, nseg, reverse);
-        else k_seg_scan_par<Ops, 1024><<<(unsigned)B, 1024, 0, st>>>(el, init, carry, nseg, reverse);
+    if (B <= 16 && nseg >= 16) {
+        k_seg_scan_par<Ops><<<(unsigned)B, kSegScanThreads, 0, st>>>(el, init, carry, nseg, reverse);
     } else {
         k_seg_scan<Ops><<<grid_for(B, 32), 32, 0, st>>>(el, init, carry, B, nseg, reverse);
     }
