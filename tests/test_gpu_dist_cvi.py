@@ -121,3 +121,36 @@ def test_time_sharded_marginals_from_first_factor(D, R, N, vdp_cfg):
         if it == 0:
             a.relinearize()
             c.relinearize()
+
+
+@pytest.mark.parametrize("D,R,N", [(1, 3, 2300), (3, 2, 700)])
+def test_time_sharded_update_replayed_from_a_graph(D, R, N):
+    """TimeShardedCvi.site_update_graphed: the first call runs eagerly and captures, the others replay -- the same
+    launches on the same buffers, so ELBO and state equal the plain updates bit for bit"""
+    from vi_diffusion_processes_b200.dist_cvi import TimeShardedCvi
+    from vi_diffusion_processes_b200.dist_time import Comm
+    rng = np.random.default_rng(33 + D)
+    n_obs = 17
+    grid = np.round(np.arange(N + 1) * 0.005, 6)
+    idx = np.sort(rng.choice(N + 1, n_obs, replace=False))
+    y = rng.normal(size=(n_obs, D)) * 0.3 + 1.0
+    if D == 1:
+        args = (S.DRIFT_DW, [4.0, 1.0], np.eye(1), grid, idx, y, 0.1 * np.eye(1), np.ones(1), 1e-2 * np.eye(1))
+    else:
+        args = (S.DRIFT_OU_ND, [0.5], np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.zeros(D), 0.5 * np.eye(D))
+    plain = TimeShardedCvi(*args, comm=Comm.emulated(R))
+    graphed = TimeShardedCvi(*args, comm=Comm.emulated(R))
+    for it in range(4):
+        a = plain.site_update(0.4, 0.4)
+        b = graphed.site_update_graphed(0.4, 0.4)
+        plain.check_status()
+        graphed.check_status()
+        assert a == b, (it, a, b)
+        for k in ("g1", "gd", "gs", "fx_mus", "fx_covs", "qA", "qb", "qcholQ"):
+            assert torch.equal(_gather(plain, k), _gather(graphed, k)), (it, k)
+    assert len(graphed._graphs) == 1
+    graphed.relinearize()                   # new prior buffers: the next call re-captures
+    plain.relinearize()
+    for it in range(2):
+        assert plain.site_update(0.4, 0.4) == graphed.site_update_graphed(0.4, 0.4)
+    assert len(graphed._graphs) == 1

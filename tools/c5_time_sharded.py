@@ -32,7 +32,7 @@ def make_problem(N, n_obs, seed=7, dt=1e-3, D=3):
     return grid, idx, y
 
 
-def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=False):
+def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=False, graphed=False):
     """Returns (result dict on rank 0 else None[, the TimeShardedCvi]).  The process group, if any, must exist."""
     import torch.distributed as dist
     from vi_diffusion_processes_b200.dist_cvi import TimeShardedCvi
@@ -51,8 +51,9 @@ def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=
         from vi_diffusion_processes_b200 import _lib
         for st in sh.ranks:
             st.eng.route_flags |= _lib.FLAG_GH_QUADRATURE
-    for _ in range(max(1, warmup)):
-        elbo = sh.site_update(lr, lr)
+    update = sh.site_update_graphed if graphed else sh.site_update      # graphed: first call eager + capture
+    for _ in range(max(1, warmup) + (1 if graphed else 0)):
+        elbo = update(lr, lr)
     sh.check_status()
     t_build = time.perf_counter() - t_build
 
@@ -65,7 +66,7 @@ def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(steps):
-        elbo = sh.site_update(lr, lr)
+        elbo = update(lr, lr)
     e1.record()
     barrier()
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
@@ -80,6 +81,7 @@ def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=
                "n_gpus": world, "steps": steps, "warmup": max(1, warmup), "ms_per_step": ms_step,
                "value": N / (ms_step * 1e-3), "unit": "grid-steps/s", "scaling": "strong", "elbo": elbo,
                "quadrature_nodes_per_transition": 8000 if gh20 else 8,
+               "launch": "CUDA graph replay (launches and ncclAllGather captured once)" if graphed else "eager",
                "collective": "vdp_comm_all_gather (ncclAllGather issued from C on the compute stream)" if world > 1
                else "none (1 rank)",
                "all_gathers_per_step": (comm.n_gathers - g0) // steps,
@@ -98,6 +100,8 @@ def main():
     ap.add_argument("--obs", type=int, default=10_000)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=1)
+    ap.add_argument("--graphed", action="store_true", help="replay the update from a CUDA graph")
+    ap.add_argument("--gh20", action="store_true", help="the reference's 20 points per dimension")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -105,7 +109,7 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    res = run(a.grid, a.obs, a.steps, a.warmup)
+    res = run(a.grid, a.obs, a.steps, a.warmup, gh20=a.gh20, graphed=a.graphed)
     if res is not None:
         print(json.dumps(res))
     if world > 1:

@@ -24,8 +24,11 @@ constexpr int kDistStagesN = VDP_DIST_STAGES_N;
 // segments a rank's stretch is split into.  The D = 3 tiles are large (Cholesky 92 KB, naturals_to_ssm 60-74 KB of shared
 // memory per CTA: 2 and 3 resident CTAs per SM), so 4 CTAs per SM worth of segments run as 1.3-2 waves; 6 per SM is a
 // whole number of waves for both (measured on the 10^7-step chain: 592 segments 20.3 ms, 444: 19.5, 888: 19.3)
+#ifndef VDP_DIST_TARGET3
+#define VDP_DIST_TARGET3 (148 * 6)
+#endif
 template <int D>
-constexpr int64_t kDistTarget = (D == 3) ? 148 * 6 : kTargetBlocks;
+constexpr int64_t kDistTarget = (D == 3) ? VDP_DIST_TARGET3 : kTargetBlocks;
 
 template <class Ops>
 __global__ void k_seg_total(const typename Ops::Elem* __restrict__ el, int nseg, int reverse,

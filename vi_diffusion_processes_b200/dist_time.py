@@ -206,17 +206,31 @@ class TimeShardedChain:
         return halo_from_prev(self.comm, lasts)
 
     def naturals_to_ssm(self, th1: List[torch.Tensor], thd: List[torch.Tensor], ths: List[torch.Tensor],
-                        want_cov: bool = False):
+                        want_cov: bool = False, out: Optional[List[dict]] = None):
         """naturals_to_ssm_params (ssm_gaussian_transformations.py:333-511), time-sharded.
         Returns per local rank a dict: A [n,D,D], b [n,D], cholQ [n,D,D] for its transitions (n = e - s), the
         node-s factor ``cholQ_prev`` (cholQ of transition s-1; None on rank 0) and mu0 / cholP0 on rank 0.
         ``want_cov``: also ``S`` [n_own, D, D], the marginal covariances of the owned grid points (the diagonal of
-        the inverse band the backward sweep walks through -- no second factorisation needed for them)."""
+        the inverse band the backward sweep walks through -- no second factorisation needed for them).
+
+        ``out`` (optional, per local rank): the caller's own arrays for the sweeps to write into instead of fresh
+        ones (a chain of 10^7 steps moves 0.7 GB per copy): ``A`` [n,D,D], ``b`` [n,D], ``cholQ`` [n,D,D], ``S``
+        [n_own,D,D]; ``b_prev`` [1,D] / ``cholQ_prev`` [1,D,D] = the slots right BEFORE ``b`` / ``cholQ`` in memory
+        on every rank but the first (a rank's first node produces offset and factor of the transition into it);
+        ``thd_ext`` = ``thd`` with one more row behind it, which receives the next rank's first block (unused on
+        the last rank)."""
         D, dev = self.D, self.ranks[0].device
         halo = self._from_next([t[:1].contiguous() for t in thd])
         Kd, Ld, Ls = [], [], []
-        for rk, d_own, h in zip(self.ranks, thd, halo):
-            kd = d_own if rk.last else torch.cat([d_own, h])
+        for i, (rk, d_own, h) in enumerate(zip(self.ranks, thd, halo)):
+            if rk.last:
+                kd = d_own
+            elif out is not None and out[i].get("thd_ext") is not None:
+                kd = out[i]["thd_ext"]
+                assert kd.data_ptr() == d_own.data_ptr() and kd.is_contiguous()
+                kd[-1] = h[0]
+            else:
+                kd = torch.cat([d_own, h])
             assert kd.shape[0] == rk.N_local + 1
             Kd.append(kd.contiguous())
             Ld.append(torch.empty_like(Kd[-1]))
@@ -225,37 +239,61 @@ class TimeShardedChain:
         _run_sweep(self.comm, self.ranks, _lib.SWEEP_CHOL,
                    lambda rk, st, prev: rk.sweep(_lib.SWEEP_CHOL, 0, [Kd[idx[id(rk)]], ths[idx[id(rk)]]],
                                                  [Ld[idx[id(rk)]], Ls[idx[id(rk)]]], -2.0, -1.0), D)
-        A, bbuf, qbuf, mu0, cP0 = [], [], [], [], []
-        for rk in self.ranks:
-            n = rk.N_local
-            A.append(torch.empty((n, D, D), dtype=F64, device=dev))
-            bbuf.append(torch.zeros((n + 1, D), dtype=F64, device=dev))       # slot j <-> transition s - 1 + j
-            qbuf.append(torch.zeros((n + 1, D, D), dtype=F64, device=dev))
+        A, bo, qo, bprev, qprev, mu0, cP0, Sd = [], [], [], [], [], [], [], []
+        for i, rk in enumerate(self.ranks):
+            n, n_own = rk.N_local, rk.N_local + (1 if rk.last else 0)
+            o = out[i] if out is not None else {}
+            A.append(o["A"] if "A" in o else torch.empty((n, D, D), dtype=F64, device=dev))
+            if "b" in o:
+                bo.append(o["b"])
+                qo.append(o["cholQ"])
+                bprev.append(None if rk.first else o["b_prev"])
+                qprev.append(None if rk.first else o["cholQ_prev"])
+                if not rk.first:       # slot j - 1 <-> transition s - 1 + j: one slot before the owned ones
+                    assert bprev[-1].data_ptr() + D * 8 == bo[-1].data_ptr()
+                    assert qprev[-1].data_ptr() + D * D * 8 == qo[-1].data_ptr()
+            else:
+                bb = torch.empty((n + 1, D), dtype=F64, device=dev)
+                qb = torch.empty((n + 1, D, D), dtype=F64, device=dev)
+                bo.append(bb[1:])
+                qo.append(qb[1:])
+                bprev.append(None if rk.first else bb[:1])
+                qprev.append(None if rk.first else qb[:1])
             mu0.append(torch.zeros(D, dtype=F64, device=dev))
             cP0.append(torch.zeros((D, D), dtype=F64, device=dev))
-        Sd = [torch.empty((rk.N_local + (1 if rk.last else 0), D, D), dtype=F64, device=dev) if want_cov else None
-              for rk in self.ranks]
+            Sd.append((o["S"] if "S" in o else torch.empty((n_own, D, D), dtype=F64, device=dev)) if want_cov else None)
+            for t, shape in ((A[-1], (n, D, D)), (bo[-1], (n, D)), (qo[-1], (n, D, D))):
+                assert tuple(t.shape) == shape and t.is_contiguous(), (tuple(t.shape), shape)
+            assert Sd[-1] is None or (tuple(Sd[-1].shape) == (n_own, D, D) and Sd[-1].is_contiguous())
 
         def n2s(rk, stage, prev):
             i = idx[id(rk)]
             return rk.sweep(_lib.SWEEP_NAT2SSM, stage, [Ld[i], Ls[i], th1[i], thd[i], ths[i]],
-                            [A[i], bbuf[i][1:], qbuf[i][1:], mu0[i], cP0[i], Sd[i]], prev=prev)
+                            [A[i], bo[i], qo[i], mu0[i], cP0[i], Sd[i]], prev=prev)
         _run_sweep(self.comm, self.ranks, _lib.SWEEP_NAT2SSM, n2s, D)
-        # transition e-1 (output of node e) lives in slot 0 of the next rank (offset and factor in one exchange)
-        nbq = self._from_next([torch.cat([tb_[0].reshape(-1), tq_[0].reshape(-1)]) for tb_, tq_ in zip(bbuf, qbuf)])
-        out = []
+        # transition e-1 (output of node e) lives in the slot before the next rank's own (offset and factor in one
+        # exchange; the first rank has no such slot and offers zeros nobody reads)
+        zero = torch.zeros(D + D * D, dtype=F64, device=dev)
+        nbq = self._from_next([zero if bp is None else torch.cat([bp.reshape(-1), qp.reshape(-1)])
+                               for bp, qp in zip(bprev, qprev)])
+        res = []
         for i, rk in enumerate(self.ranks):
             if not rk.last:
-                bbuf[i][-1] = nbq[i][:D]
-                qbuf[i][-1] = nbq[i][D:].reshape(D, D)
-            out.append(dict(A=A[i], b=bbuf[i][1:], cholQ=qbuf[i][1:], cholQ_prev=None if rk.first else qbuf[i][:1],
+                bo[i][-1] = nbq[i][:D]
+                qo[i][-1] = nbq[i][D:].reshape(D, D)
+            res.append(dict(A=A[i], b=bo[i], cholQ=qo[i], cholQ_prev=qprev[i],
                             mu0=mu0[i] if rk.first else None, cholP0=cP0[i] if rk.first else None, S=Sd[i]))
-        return out
+        return res
 
-    def ssm_means(self, A: List[torch.Tensor], b: List[torch.Tensor], mu0: List[Optional[torch.Tensor]]):
-        """StateSpaceModel.marginal_means (state_space_model.py:251), time-sharded: per local rank m [n_own, D]."""
+    def ssm_means(self, A: List[torch.Tensor], b: List[torch.Tensor], mu0: List[Optional[torch.Tensor]],
+                  out: Optional[List[torch.Tensor]] = None):
+        """StateSpaceModel.marginal_means (state_space_model.py:251), time-sharded: per local rank m [n_own, D].
+        ``out`` (optional): per local rank an array [n + 1, D] to write into -- the sweep of a rank also produces the
+        mean of the next rank's first grid point, in the last row."""
         D, dev = self.D, self.ranks[0].device
-        m = [torch.empty((rk.N_local + 1, D), dtype=F64, device=dev) for rk in self.ranks]
+        m = [torch.empty((rk.N_local + 1, D), dtype=F64, device=dev) for rk in self.ranks] if out is None else out
+        for rk, t in zip(self.ranks, m):
+            assert tuple(t.shape) == (rk.N_local + 1, D) and t.is_contiguous()
         idx = {id(rk): i for i, rk in enumerate(self.ranks)}
         dummy_v = torch.zeros(D, dtype=F64, device=dev)
 
