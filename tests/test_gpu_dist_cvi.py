@@ -154,3 +154,43 @@ def test_time_sharded_update_replayed_from_a_graph(D, R, N):
     for it in range(2):
         assert plain.site_update(0.4, 0.4) == graphed.site_update_graphed(0.4, 0.4)
     assert len(graphed._graphs) == 1
+
+
+@pytest.mark.parametrize("D,R", [(1, 3), (3, 2)])
+def test_time_sharded_naturals_carried_between_updates(D, R):
+    """carry_naturals (default): the first rebuild of an update corrects theta at the observed grid points instead of
+    rebuilding it from the prior everywhere -- same state as the full rebuild to rounding; a torch-side write to the
+    sites or a re-linearisation in between falls back to the full rebuild"""
+    from vi_diffusion_processes_b200.dist_cvi import TimeShardedCvi
+    from vi_diffusion_processes_b200.dist_time import Comm
+    rng = np.random.default_rng(43 + D)
+    N, n_obs = 900, 15
+    grid = np.round(np.arange(N + 1) * 0.005, 6)
+    idx = np.sort(rng.choice(N + 1, n_obs, replace=False))
+    idx[0], idx[-1] = 0, N
+    y = rng.normal(size=(n_obs, D)) * 0.3 + 1.0
+    if D == 1:
+        args = (S.DRIFT_DW, [4.0, 1.0], np.eye(1), grid, idx, y, 0.1 * np.eye(1), np.ones(1), 1e-2 * np.eye(1))
+    else:
+        args = (S.DRIFT_OU_ND, [0.5], np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.zeros(D), 0.5 * np.eye(D))
+    full = TimeShardedCvi(*args, comm=Comm.emulated(R), carry_naturals=False)
+    lazy = TimeShardedCvi(*args, comm=Comm.emulated(R))
+    for it in range(6):
+        a, b = full.site_update(0.4, 0.4), lazy.site_update(0.4, 0.4)
+        lazy.check_status()
+        assert abs(a - b) <= 1e-11 * abs(a), (it, a, b)
+        for k in ("g1", "gd", "gs", "fx_mus", "fx_covs", "qA", "qb", "qcholQ"):
+            # the sites are small differences of naturals of size 1 / (q dt) (zero up to rounding for a linear
+            # drift): measured against theta, as the other tests of this file do
+            scale = float(max(st.thd.abs().max() for st in full.ranks)) if k[0] == "g" else None
+            assert _close(_gather(lazy, k), _gather(full, k), 1e-11, scale=scale), (it, k)
+        assert lazy._th_sig == lazy._th_signature()
+        if it == 1:
+            full.relinearize()
+            lazy.relinearize()
+            assert lazy._th_sig is None
+        if it == 3:                         # data sites rewritten behind the engine's back
+            for eng in (full, lazy):
+                for st in eng.ranks:
+                    st.eng.d1.mul_(0.5)
+            assert lazy._th_sig != lazy._th_signature()

@@ -32,7 +32,7 @@ def make_problem(N, n_obs, seed=7, dt=1e-3, D=3):
     return grid, idx, y
 
 
-def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=False, graphed=False):
+def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=False, graphed=False, carry=True):
     """Returns (result dict on rank 0 else None[, the TimeShardedCvi]).  The process group, if any, must exist."""
     import torch.distributed as dist
     from vi_diffusion_processes_b200.dist_cvi import TimeShardedCvi
@@ -45,14 +45,16 @@ def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=
     comm = Comm.from_process_group(backend="nccl_c") if world > 1 else Comm.emulated(1)
     t_build = time.perf_counter()
     sh = TimeShardedCvi(DRIFT_OU_ND, [0.5], np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.zeros(D), np.eye(D), comm=comm,
-                        device=device)
+                        device=device, carry_naturals=carry)
     del grid
     if gh20:      # the reference's 20 points per dimension instead of the exact 2-point rule of the linear drift
         from vi_diffusion_processes_b200 import _lib
         for st in sh.ranks:
             st.eng.route_flags |= _lib.FLAG_GH_QUADRATURE
     update = sh.site_update_graphed if graphed else sh.site_update      # graphed: first call eager + capture
-    for _ in range(max(1, warmup) + (1 if graphed else 0)):
+    # two updates at least: the second is the first one on the carried route (theta corrected at the observations)
+    warmup = max(2, warmup)
+    for _ in range(warmup + (1 if graphed else 0)):
         elbo = update(lr, lr)
     sh.check_status()
     t_build = time.perf_counter() - t_build
@@ -78,7 +80,7 @@ def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=
         ms_step = float(ms.item()) / steps
         res = {"workload": f"C5: 1 sequence x {N} grid steps, D=3 OU prior, {n_obs} observations, one CVI-DP site "
                            f"update per step, chain sharded in time over {world} rank(s)",
-               "n_gpus": world, "steps": steps, "warmup": max(1, warmup), "ms_per_step": ms_step,
+               "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms_step,
                "value": N / (ms_step * 1e-3), "unit": "grid-steps/s", "scaling": "strong", "elbo": elbo,
                "quadrature_nodes_per_transition": 8000 if gh20 else 8,
                "launch": "CUDA graph replay (launches and ncclAllGather captured once)" if graphed else "eager",
@@ -101,6 +103,7 @@ def main():
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=1)
     ap.add_argument("--graphed", action="store_true", help="replay the update from a CUDA graph")
+    ap.add_argument("--no-carry", action="store_true", help="rebuild theta from the prior in both rebuilds")
     ap.add_argument("--gh20", action="store_true", help="the reference's 20 points per dimension")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -109,7 +112,7 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    res = run(a.grid, a.obs, a.steps, a.warmup, gh20=a.gh20, graphed=a.graphed)
+    res = run(a.grid, a.obs, a.steps, a.warmup, gh20=a.gh20, graphed=a.graphed, carry=not a.no_carry)
     if res is not None:
         print(json.dumps(res))
     if world > 1:

@@ -59,12 +59,14 @@ class TimeShardedCvi:
     """
 
     def __init__(self, drift_id, drift_params, q, time_grid, obs_idx, obs_y, lik_chol, x0_mu, x0_cov, comm: Comm,
-                 device="cuda", stabilize_ssm=True, clip_state_transitions=(-1.0, 1.0), refactor_precision=False):
+                 device="cuda", stabilize_ssm=True, clip_state_transitions=(-1.0, 1.0), refactor_precision=False,
+                 carry_naturals=True):
         tg = np.asarray(time_grid, dtype=np.float64)
         self.N = N = tg.shape[0] - 1
         self.D = D = np.atleast_2d(np.asarray(q)).shape[0]
         self.comm = comm
         self.refactor_precision = bool(refactor_precision)
+        self.carry_naturals, self._th_sig = bool(carry_naturals), None
         self.device = torch.device(device)
         self.chain = TimeShardedChain(N, D, comm, device=device)
         obs_idx = np.asarray(obs_idx, dtype=np.int64).reshape(-1)
@@ -94,10 +96,28 @@ class TimeShardedCvi:
         """views of the owned part of theta on the extended chain"""
         return (st.th1[0, st.lo:st.hi], st.thd[0, st.lo:st.hi], st.ths[0, st.lo:st.lo + st.nt])
 
-    def _rebuild(self):
-        """dist_q + marginals on the time-sharded chain, results into the engines' extended arrays + halos."""
+    _TH_FIELDS = ("pA", "pb", "pcholQ", "pmu0", "pcholP0", "_g1", "_gd", "_gs", "d1", "d2", "obs_idx")
+
+    def _th_signature(self):
+        """what the full naturals held in ``st.th1 / thd / ths`` were computed from (torch-side writes bump _version;
+        the C calls of this class that write them are followed by a rebuild or reset ``_th_sig``)"""
+        return tuple((t.data_ptr(), t._version) for st in self.ranks
+                     for t in [getattr(st.eng, n) for n in self._TH_FIELDS] + [st.th1, st.thd, st.ths])
+
+    def _rebuild(self, data_sites_before=None):
+        """dist_q + marginals on the time-sharded chain, results into the engines' extended arrays + halos.
+        ``data_sites_before``: per local rank the (d1, d2) the naturals in ``st.th*`` were built with, when nothing
+        but the data sites has changed since -- theta is then corrected at the observed grid points only instead of
+        being rebuilt from the prior at every grid point (0.5 GB read + written per 10^6 steps in D = 3)."""
         D = self.D
-        for st in self.ranks:
+        for i, st in enumerate(self.ranks):
+            if data_sites_before is not None:
+                e = st.eng
+                if e.obs_idx.numel():
+                    old1, old2 = data_sites_before[i]
+                    st.th1[0].index_add_(0, e.obs_idx[0], (e.d1 - old1)[0])
+                    st.thd[0].index_add_(0, e.obs_idx[0], (e.d2 - old2)[0])
+                continue
             self._call(st, "vdp_cvi_full_sites", 0.0, 0.0, C.c_void_p(st.th1.data_ptr()), C.c_void_p(st.thd.data_ptr()),
                        C.c_void_p(st.ths.data_ptr()))
         own = [self._own(st) for st in self.ranks]
@@ -156,12 +176,16 @@ class TimeShardedCvi:
 
     def _site_update_device(self, lr_data, lr_girsanov):
         """one update as a stream-ordered sequence of launches and exchanges (no host read): capturable"""
+        carried = self.carry_naturals and self._th_sig is not None and self._th_sig == self._th_signature()
+        before = [(st.eng.d1.clone(), st.eng.d2.clone()) for st in self.ranks] if carried else None
+        self._th_sig = None
         for st in self.ranks:
             self._call(st, "vdp_cvi_update_data_sites", lr_data, lr_girsanov)
-        self._rebuild()
+        self._rebuild(before)
         for st in self.ranks:
             self._call(st, "vdp_cvi_update_girsanov_sites_range", lr_data, lr_girsanov, st.lo, st.hi)
         self._rebuild()
+        self._th_sig = self._th_signature()       # theta of (prior, both kinds of sites) as they stand now
         self._elbo_device()
 
     def site_update(self, lr_data, lr_girsanov):
@@ -200,7 +224,9 @@ class TimeShardedCvi:
         cache = getattr(self, "_graphs", None)
         if cache is None:
             cache = self._graphs = {}
-        ent = cache.get(key)
+        # the captured sequence is the one of a carried update (theta corrected at the observations only)
+        fresh = self._th_sig is not None and self._th_sig == self._th_signature()
+        ent = cache.get(key) if (fresh or not self.carry_naturals) else None
         if ent is None:
             out = self.site_update(lr_data, lr_girsanov)
             cache.clear()                      # a graph keeps its temporaries: hold one
@@ -234,6 +260,7 @@ class TimeShardedCvi:
 
     def relinearize(self):
         """cvi_dp_trainer.py:110-134 on every rank's extended chain (pointwise: no exchange, the halos are there)."""
+        self._th_sig = None
         for st in self.ranks:
             st.eng.relinearize()
 
