@@ -200,7 +200,10 @@ class TimeShardedCvi:
             e = st.eng
             ptrs += [t.data_ptr() for t in (st.th1, st.thd, st.ths)]
             ptrs += [getattr(e, n).data_ptr() for n in e._PTR_FIELDS]
-            ptrs += [int(e.route_flags)] + [float(x) for x in e.drift_params]
+            # ... and by value (as CviEngine.site_update_graphed keys them)
+            ptrs += [int(e.route_flags), e.dt, e.clip, e.stabilize_ssm] + [float(x) for x in e.drift_params]
+            ptrs += e.x0_mu.tolist() + e.x0_cov.reshape(-1).tolist() + e.q.reshape(-1).tolist() \
+                + e.lik_chol.reshape(-1).tolist()
         return (float(lr_data), float(lr_girsanov), self.refactor_precision,
                 tuple(_lib.config_get(k) for k in _lib.CONFIG_KEYS), tuple(ptrs))
 
