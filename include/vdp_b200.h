@@ -565,8 +565,20 @@ int vdp_vgp_sweep(const vdp_vgp_problem* problem_host, void* stream);
  * covariances of the Gaussian the naturals describe (the diagonal of the inverse band the sweep walks through);
  * together with VDP_SWEEP_MEAN that is the rebuild's marginals without VDP_SWEEP_MARG + VDP_SWEEP_INVBAND (a second
  * factorisation of the same precision).
+ *
+ * The rebuild in two sweeps instead of three (no factor stored; equal to the route above in exact arithmetic):
+ *   VDP_SWEEP_INFO     naturals_to_ssm_params as ONE backward sweep in information form (the Schur complements of
+ *                      the precision taken from the bottom, the linear term riding along):
+ *                      in[0] th1 [N_local (+1 on the last rank), D], in[1] thd, in[2] ths [N_local];
+ *                      out[0] A, out[1] b, out[2] cholQ [N_local] (each at the index of its transition, no halo
+ *                      slots), out[3] mu0, out[4] cholP0 (rank 0 only)
+ *   VDP_SWEEP_MOMENTS  marginal means and covariances by the moment recursion m' = A m + b, S' = A S A^T + Q:
+ *                      in[0] A, in[1] b, in[2] cholQ [N_local], in[3] mu0, in[4] cholP0 (rank 0 only);
+ *                      out[0] m [N_local+1, D], out[1] Sd [N_local+1, D, D] (last row = the first grid point of the
+ *                      next rank)
  * ---------------------------------------------------------------------------------------------- */
-enum { VDP_SWEEP_CHOL = 0, VDP_SWEEP_NAT2SSM = 1, VDP_SWEEP_MARG = 2, VDP_SWEEP_INVBAND = 3, VDP_SWEEP_MEAN = 4 };
+enum { VDP_SWEEP_CHOL = 0, VDP_SWEEP_NAT2SSM = 1, VDP_SWEEP_MARG = 2, VDP_SWEEP_INVBAND = 3, VDP_SWEEP_MEAN = 4,
+       VDP_SWEEP_INFO = 5, VDP_SWEEP_MOMENTS = 6 };
 
 typedef struct vdp_dist_sweep {
     int32_t kind, stage;

@@ -194,3 +194,64 @@ def test_time_sharded_naturals_carried_between_updates(D, R):
                 for st in eng.ranks:
                     st.eng.d1.mul_(0.5)
             assert lazy._th_sig != lazy._th_signature()
+
+
+@pytest.mark.parametrize("D,R,N", [(1, 1, 700), (1, 3, 3100), (2, 3, 1500), (3, 1, 500), (3, 4, 900), (3, 5, 2100)])
+def test_time_sharded_rebuild_in_information_form(D, R, N, vdp_cfg):
+    """``info_rebuild=True``: dist_q as ONE backward sweep in information form (VDP_SWEEP_INFO: the Schur complements of
+    the precision from the bottom, transitions straight from them) and the marginals by the moment recursion
+    (VDP_SWEEP_MOMENTS) -- against the default rebuild (Cholesky sweep, inverse band, means): the same Gaussian, so the
+    same update to rounding; several segments per rank, first / last grid point observed."""
+    from vi_diffusion_processes_b200.dist_cvi import TimeShardedCvi
+    from vi_diffusion_processes_b200.dist_time import Comm
+    from vi_diffusion_processes_b200.markovflow.sde import sde as sde_mod
+    vdp_cfg(SWEEPS="tiled", NSEG=3)
+    did, params = {1: (sde_mod.DRIFT_DW, [4.0, 1.0]), 2: (sde_mod.DRIFT_VDP, [1.0, 1.0]),
+                   3: (sde_mod.DRIFT_OU_ND, [0.5])}[D]
+    rng = np.random.default_rng(50 + D)
+    n_obs = 17
+    grid = np.round(np.arange(N + 1) * 0.005, 6)
+    idx = np.sort(rng.choice(N + 1, n_obs, replace=False))
+    idx[0], idx[-1] = 0, N
+    y = rng.normal(size=(n_obs, D)) * 0.3 + 1.0
+    args = (did, params, np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.ones(D), 0.05 * np.eye(D))
+    a = TimeShardedCvi(*args, comm=Comm.emulated(R), info_rebuild=True)
+    c = TimeShardedCvi(*args, comm=Comm.emulated(R))
+    for it in range(4):
+        ea, ec = a.site_update(0.5, 0.5), c.site_update(0.5, 0.5)
+        a.check_status()
+        c.check_status()
+        assert abs(ea - ec) <= 1e-11 * abs(ec), (it, ea, ec)
+        for k in ("fx_mus", "fx_covs", "qA", "qb", "qcholQ"):
+            assert _close(_gather(a, k), _gather(c, k), 1e-10), (it, k)
+        scale = float(max(st.thd.abs().max() for st in c.ranks))
+        for k in ("g1", "gd", "gs"):
+            assert _close(_gather(a, k), _gather(c, k), 1e-11, scale=scale), (it, k)
+        for x, r in zip((a.ranks[0].eng.qmu0, a.ranks[0].eng.qcholP0), (c.ranks[0].eng.qmu0, c.ranks[0].eng.qcholP0)):
+            assert _close(x, r, 1e-10)
+        if it == 1:
+            a.relinearize()
+            c.relinearize()
+
+
+def test_information_form_rebuild_against_the_oracle_3d():
+    """the two-sweep rebuild against the NumPy restatement of the reference (D = 3, N small enough for the oracle)"""
+    from vi_diffusion_processes_b200.dist_cvi import TimeShardedCvi
+    from vi_diffusion_processes_b200.dist_time import Comm
+    rng = np.random.default_rng(61)
+    N, n_obs = 41, 7
+    grid = np.round(np.arange(N + 1) * 0.01, 2)
+    idx = np.sort(rng.choice(N + 1, n_obs, replace=False))
+    y = rng.normal(size=(n_obs, 3)) * 0.5
+    sde = S.OUNdSDE(0.5, np.eye(3))
+    x0 = S.Gaussian(np.zeros(3), 0.5 * np.eye(3))
+    ref = M.CVISitesSDE(sde, grid, (grid[idx], y), M.MultivariateGaussian(0.1 * np.eye(3)), prior_initial_state=x0)
+    args = (sde.drift_id, sde.params, sde.q, grid, idx, y, 0.1 * np.eye(3), x0.mu, x0.cov)
+    sh = TimeShardedCvi(*args, comm=Comm.emulated(3), info_rebuild=True)
+    for it in range(2):
+        e = sh.site_update(0.3, 0.3)
+        r = ref.site_update(0.3, 0.3)
+        sh.check_status()
+        assert abs(e - r) <= 1e-9 * abs(r), (it, e, r)
+        assert _close(_gather(sh, "fx_mus").cpu(), torch.as_tensor(np.asarray(ref.fx_mus).reshape(N + 1, 3)), 1e-9)
+        assert _close(_gather(sh, "fx_covs").cpu(), torch.as_tensor(np.asarray(ref.fx_covs).reshape(N + 1, 3, 3)), 1e-9)

@@ -32,7 +32,7 @@ def make_problem(N, n_obs, seed=7, dt=1e-3, D=3):
     return grid, idx, y
 
 
-def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=False, graphed=False, carry=True):
+def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=False, graphed=False, carry=True, info=None):
     """Returns (result dict on rank 0 else None[, the TimeShardedCvi]).  The process group, if any, must exist."""
     import torch.distributed as dist
     from vi_diffusion_processes_b200.dist_cvi import TimeShardedCvi
@@ -45,7 +45,8 @@ def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=
     comm = Comm.from_process_group(backend="nccl_c") if world > 1 else Comm.emulated(1)
     t_build = time.perf_counter()
     sh = TimeShardedCvi(DRIFT_OU_ND, [0.5], np.eye(D), grid, idx, y, 0.1 * np.eye(D), np.zeros(D), np.eye(D), comm=comm,
-                        device=device, carry_naturals=carry)
+                        device=device, carry_naturals=carry,
+                        **({} if info is None else {"info_rebuild": bool(info)}))
     del grid
     if gh20:      # the reference's 20 points per dimension instead of the exact 2-point rule of the linear drift
         from vi_diffusion_processes_b200 import _lib
@@ -83,6 +84,7 @@ def run(N=10_000_000, n_obs=10_000, steps=2, warmup=1, lr=0.5, keep=False, gh20=
                "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms_step,
                "value": N / (ms_step * 1e-3), "unit": "grid-steps/s", "scaling": "strong", "elbo": elbo,
                "quadrature_nodes_per_transition": 8000 if gh20 else 8,
+               "rebuild": "information form + moments (2 sweeps)" if sh.info_rebuild else "Cholesky + inverse band + means (3 sweeps)",
                "launch": "CUDA graph replay (launches and ncclAllGather captured once)" if graphed else "eager",
                "collective": "vdp_comm_all_gather (ncclAllGather issued from C on the compute stream)" if world > 1
                else "none (1 rank)",
@@ -104,6 +106,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=1)
     ap.add_argument("--graphed", action="store_true", help="replay the update from a CUDA graph")
     ap.add_argument("--no-carry", action="store_true", help="rebuild theta from the prior in both rebuilds")
+    ap.add_argument("--info", type=int, default=None, help="1 / 0: the two-sweep rebuild in information form on / off")
     ap.add_argument("--gh20", action="store_true", help="the reference's 20 points per dimension")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -112,7 +115,7 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    res = run(a.grid, a.obs, a.steps, a.warmup, gh20=a.gh20, graphed=a.graphed, carry=not a.no_carry)
+    res = run(a.grid, a.obs, a.steps, a.warmup, gh20=a.gh20, graphed=a.graphed, carry=not a.no_carry, info=a.info)
     if res is not None:
         print(json.dumps(res))
     if world > 1:

@@ -104,7 +104,7 @@ class DistSweep(C.Structure):
     ]
 
 
-SWEEP_CHOL, SWEEP_NAT2SSM, SWEEP_MARG, SWEEP_INVBAND, SWEEP_MEAN = 0, 1, 2, 3, 4
+SWEEP_CHOL, SWEEP_NAT2SSM, SWEEP_MARG, SWEEP_INVBAND, SWEEP_MEAN, SWEEP_INFO, SWEEP_MOMENTS = 0, 1, 2, 3, 4, 5, 6
 FLAG_SKIP_DATA_UPDATE, FLAG_SKIP_ELBO, FLAG_SKIP_GIRSANOV, FLAG_POSTERIOR_SSM_ONLY = 1, 2, 4, 8
 FLAG_NATURALS_CARRIED = 16
 FLAG_SITES_IN_NATURALS = 32

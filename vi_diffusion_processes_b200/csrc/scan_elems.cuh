@@ -12,6 +12,8 @@
 //               Schur complement on positive-definite blocks (the pairwise-potential elements of the
 //               parallel smoother of Sarkka & Garcia-Fernandez), i.e. it is a block Cholesky of the same
 //               precision in nested-dissection order, backward stable like the sequential order.
+//   InfoElem    the same Schur complements taken from the bottom with the linear term riding along: the forward
+//               transitions of the Gaussian straight from its naturals (see InfoOps below).
 //   AffSymElem  backward inverse band (inverse_from_cholesky_band, block_tri_diag.py:318-337):
 //               S_out = C + G^T S_in G, all terms positive semi-definite.
 //   AffVecElem  affine vector recursions (solve_triang_mat on the A^-1 block, state_space_model.py:251,
@@ -126,6 +128,96 @@ struct SchurOps<1> {
         State o;
         o.a[0] = e.Lb.a[0] - div_fast(e.Lab.a[0], S.a[0] + e.La.a[0]) * e.Lab.a[0];
         return o;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------------
+// Information-form backward sweep: the precision K = (-2 theta_d, -theta_s) with its linear term theta_1 taken apart
+// from the BOTTOM.  State at node k+1 = (J, h), the precision and linear term of x_{k+1} given x_k = 0 with everything
+// after k+1 integrated out; one step down
+//     J_k = Kd_k - Ts_k^T J_{k+1}^-1 Ts_k,     h_k = t1_k + Ts_k^T J_{k+1}^-1 h_{k+1}        (Ts_k = theta_s[k] = -K_{k+1,k})
+// and on the way  A_k = J_{k+1}^-1 Ts_k,  b_k = J_{k+1}^-1 h_{k+1},  Q_k = J_{k+1}^-1: the forward transitions of the
+// Gaussian the naturals describe (what naturals_to_ssm_params, ssm_gaussian_transformations.py:333-511, returns), without
+// a Cholesky sweep from the top and without the inverse band.  Elements:
+//     J' = Lb - Lab^T (J + La)^-1 Lab,     h' = vb + Lab^T (J + La)^-1 (h + va)
+// closed under composition (the matrix part is SchurElem; the vector part rides on the same Schur complement).
+template <int D>
+struct InfoElem {
+    Mat<D> La, Lab, Lb;
+    Vec<D> va, vb;
+    int id;   // 1 = identity map
+};
+template <int D>
+struct InfoState {
+    Mat<D> J;
+    Vec<D> h;
+};
+
+template <int D>
+struct InfoOps {
+    using Elem = InfoElem<D>;
+    using State = InfoState<D>;
+    VDP_HD static Elem identity() {
+        Elem e;
+        e.La = mat_zero<D>();
+        e.Lab = mat_zero<D>();
+        e.Lb = mat_zero<D>();
+        e.va = vec_zero<D>();
+        e.vb = vec_zero<D>();
+        e.id = 1;
+        return e;
+    }
+    VDP_HD static Elem step(const Mat<D>& Ts, const Mat<D>& Kd, const Vec<D>& t1) {
+        Elem e;
+        e.La = mat_zero<D>();
+        e.Lab = Ts;
+        e.Lb = Kd;
+        e.va = vec_zero<D>();
+        e.vb = t1;
+        e.id = 0;
+        return e;
+    }
+    // e1 first (the upper stretch of the chain), then e2
+    VDP_HD static Elem combine(const Elem& e1, const Elem& e2) {
+        if (e1.id) return e2;
+        if (e2.id) return e1;
+        bool ok = true;
+        const Mat<D> Lm = chol(e1.Lb + e2.La, ok);
+        const Mat<D> WU = trsm(Lm, transpose(e1.Lab));
+        const Mat<D> WV = trsm(Lm, e2.Lab);
+        const Vec<D> wg = trsv(Lm, e1.vb + e2.va);
+        Elem r;
+        r.La = e1.La - Tmm(WU, WU);
+        r.Lab = Tmm(WU, WV);
+        r.Lb = e2.Lb - Tmm(WV, WV);
+        r.va = e1.va + Tmv(WU, wg);
+        r.vb = e2.vb + Tmv(WV, wg);
+        r.id = 0;
+        return r;
+    }
+    // e followed by one step (La = 0, va = 0 of the step folded in)
+    VDP_HD static void push(Elem& e, const Mat<D>& Ts, const Mat<D>& Kd, const Vec<D>& t1) {
+        if (e.id) { e = step(Ts, Kd, t1); return; }
+        bool ok = true;
+        const Mat<D> Lm = chol(e.Lb, ok);
+        const Mat<D> WU = trsm(Lm, transpose(e.Lab));
+        const Mat<D> WV = trsm(Lm, Ts);
+        const Vec<D> wg = trsv(Lm, e.vb);
+        e.La = e.La - Tmm(WU, WU);
+        e.Lab = Tmm(WU, WV);
+        e.Lb = Kd - Tmm(WV, WV);
+        e.va = e.va + Tmv(WU, wg);
+        e.vb = t1 + Tmv(WV, wg);
+    }
+    VDP_HD static State apply(const Elem& e, const State& s) {
+        if (e.id) return s;
+        bool ok = true;
+        const Mat<D> Lx = chol(s.J + e.La, ok);
+        const Mat<D> W = trsm(Lx, e.Lab);
+        State r;
+        r.J = e.Lb - Tmm(W, W);
+        r.h = e.vb + Tmv(W, trsv(Lx, s.h + e.va));
+        return r;
     }
 };
 

@@ -975,4 +975,252 @@ constexpr size_t nat2ssm_tiled_smem() {
            (T / 32) * (sizeof(AffSymElem<D>) > sizeof(AffVecElem<D>) ? sizeof(AffSymElem<D>) : sizeof(AffVecElem<D>));
 }
 
+// ---------------------------------------------------------------------------------------------------
+// naturals_to_ssm_params (ssm_gaussian_transformations.py:333-511) as ONE backward sweep in information form
+// (InfoOps, scan_elems.cuh): no Cholesky sweep from the top, no inverse band, one recursion instead of two dependent
+// ones.  Transition k is produced from the state (J, h) at node k+1:
+//     A_k = J^-1 theta_s[k],  b_k = J^-1 h,  chol Q_k = chol(J^-1);   node 0 of the chain: mu0 = J_0^-1 h_0, chol P0.
+// Same values as the reference route in exact arithmetic (A from the conditional precision instead of from the
+// covariances of the inverse band); a route of its own, held to the oracle like the others.
+// in: th1 [B,N+1,D], thd [B,N+1,D,D], ths [B,N,D,D];  out: A, bo, cholQ [B,N,...] (all at the index of their transition),
+// mu0, cholP0.  Time-sharded: `last` = the stretch ends with the chain's final node (its naturals are the start state);
+// otherwise the top segment starts from carry_in; `first` = node 0 of the stretch is node 0 of the chain.
+template <int D, int T, int L, int MODE, int NSTAGE = 1>
+__global__ void __launch_bounds__(T)
+k_info_tiled(const double* __restrict__ th1, const double* __restrict__ thd, const double* __restrict__ ths,
+             double* __restrict__ A, double* __restrict__ bo, double* __restrict__ cholQ, double* __restrict__ mu0,
+             double* __restrict__ cholP0, int64_t B, int64_t N, int nseg, int64_t seg_len,
+             const InfoState<D>* __restrict__ carry_in, InfoState<D>* __restrict__ init_out,
+             InfoElem<D>* __restrict__ seg_elem, int64_t* status, int first = 1, int last = 1) {
+    constexpr int DD = D * D, TL = T * L;
+    using Ops = InfoOps<D>;
+    constexpr int SM = tile_slots(TL * DD), SV = tile_slots(TL * D);
+    constexpr int kStage = 2 * SM + SV;                                    // thd, ths, th1
+    extern __shared__ __align__(16) double smem[];
+    double* stage0 = smem + kRingHeaderDoubles;
+    InfoElem<D>* wtot = reinterpret_cast<InfoElem<D>*>(stage0 + NSTAGE * kStage);
+    TileRing<NSTAGE> ring;
+    ring.init(smem);
+    const int64_t b = blockIdx.x / nseg;
+    const int seg = (int)(blockIdx.x % nseg);
+    const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
+    const int64_t n = N + 1;
+    const int ntiles = (int)((t1 - t0 + TL - 1) / TL);
+    auto issue = [&](int ti) {   // thread 0: start the copies of the ti-th tile from the top
+        const int64_t hi = t1 - (int64_t)ti * TL, lo = max(t0, hi - TL);
+        const int cnt = (int)(hi - lo);
+        double* base = stage0 + (ti % NSTAGE) * kStage;
+        uint64_t* bar = ring.bar + ti % NSTAGE;
+        uint32_t bytes = tile_fetch(base, thd + (b * n + lo) * DD, cnt * DD, bar);
+        bytes += tile_fetch(base + SM, ths + (b * N + lo) * DD, cnt * DD, bar);
+        bytes += tile_fetch(base + 2 * SM, th1 + (b * n + lo) * D, cnt * D, bar);
+        mbar_arrive_expect_tx(bar, bytes);
+    };
+    if (threadIdx.x == 0 && ntiles > 0) issue(0);
+    InfoState<D> st;
+    st.J = mat_eye<D>();
+    st.h = vec_zero<D>();
+    if (t1 == N && last) {
+        st.J = mirror_lower(-2.0 * mat_load<D>(thd + (b * n + N) * DD));
+        st.h = vec_load<D>(th1 + (b * n + N) * D);
+        if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = st;
+    } else if (MODE == SWEEP_FULL) {
+        st = carry_in[b * nseg + seg];
+    }
+    InfoElem<D> seg_tot = Ops::identity();
+    for (int ti = 0; ti < ntiles; ++ti) {
+        const int64_t hi = t1 - (int64_t)ti * TL, lo = max(t0, hi - TL);
+        const int cnt = (int)(hi - lo);
+        if (NSTAGE == 1 && ti > 0) {
+            __syncthreads();
+            if (threadIdx.x == 0) { bulk_wait_read(); issue(ti); }
+        }
+        ring.wait(ti);
+        double* base = stage0 + (ti % NSTAGE) * kStage;
+        double* sTd = base + tile_off(thd + (b * n + lo) * DD);               // theta_d[k] -> chol Q_k
+        double* sTs = base + SM + tile_off(ths + (b * N + lo) * DD);          // theta_s[k] -> A_k
+        double* sT1 = base + 2 * SM + tile_off(th1 + (b * n + lo) * D);       // theta_1[k] -> b_k
+        const BwdChunk ch = bwd_chunk<L>(cnt);
+        InfoElem<D> e = Ops::identity();
+        for (int k = ch.top - 1; k >= ch.bot; --k)
+            Ops::push(e, mat_load<D>(sTs + k * DD), mirror_lower(-2.0 * mat_load<D>(sTd + k * DD)),
+                      vec_load<D>(sT1 + k * D));
+        if (NSTAGE > 1 && threadIdx.x == 0 && ti + 1 < ntiles) {
+            bulk_wait_read();
+            issue(ti + 1);
+        }
+        InfoElem<D> total;
+        const InfoElem<D> excl = block_exclusive_scan<Ops, T>(e, wtot, total);
+        if (MODE != SWEEP_FULL) {
+            seg_tot = Ops::combine(seg_tot, total);
+            continue;
+        }
+        InfoState<D> s = Ops::apply(excl, st);
+        st = Ops::apply(total, st);
+        bool ok = true;
+        for (int k = ch.top - 1; k >= ch.bot; --k) {
+            const Mat<D> Ts = mat_load<D>(sTs + k * DD);
+            const Mat<D> Kd = -2.0 * mat_load<D>(sTd + k * DD);
+            const Vec<D> t1k = vec_load<D>(sT1 + k * D);
+            Mat<D> cov, cc;
+            cov_from_precision(s.J, cov, cc, ok);
+            if (!ok) { report_not_pd(status, b * n + lo + k + 1); ok = true; }
+            const Mat<D> Ak = mm(cov, Ts);
+            const Vec<D> bk = mv(cov, s.h);
+            mat_store<D>(sTs + k * DD, Ak);
+            mat_store<D>(sTd + k * DD, cc);
+            vec_store<D>(sT1 + k * D, bk);
+            s.J = mirror_lower(Kd - Tmm(Ts, Ak));
+            s.h = t1k + Tmv(Ts, bk);
+        }
+        if (first && lo == 0 && ch.len > 0 && ch.bot == 0) {   // node 0 of the chain: the initial state
+            Mat<D> cov, cc;
+            cov_from_precision(s.J, cov, cc, ok);
+            if (!ok) report_not_pd(status, b * n);
+            vec_store<D>(mu0 + b * D, mv(cov, s.h));
+            mat_store<D>(cholP0 + b * DD, cc);
+        }
+        fence_async_smem();
+        __syncthreads();
+        tile_store<T>(A + (b * N + lo) * DD, sTs, cnt * DD);
+        tile_store<T>(cholQ + (b * N + lo) * DD, sTd, cnt * DD);
+        tile_store<T>(bo + (b * N + lo) * D, sT1, cnt * D);
+        if (threadIdx.x == 0) bulk_commit();
+    }
+    if (threadIdx.x == 0) {
+        if (MODE != SWEEP_FULL) seg_elem[b * nseg + seg] = seg_tot;
+        bulk_wait_all();
+    }
+}
+
+template <int D, int T, int L, int NSTAGE = 1>
+constexpr size_t info_tiled_smem() {
+    return ((size_t)kRingHeaderDoubles + (size_t)NSTAGE * (2 * tile_slots(T * L * D * D) + tile_slots(T * L * D))) *
+               sizeof(double) +
+           (T / 32) * sizeof(InfoElem<D>);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Marginal means and covariances of a state-space model by the moment recursion
+//     m_{k+1} = A_k m_k + b_k,     S_{k+1} = A_k S_k A_k^T + Q_k,     Q_k = chol Q_k chol Q_k^T
+// (what StateSpaceModel.marginals, state_space_model.py:231-262, returns; the reference goes through the precision and
+// its inverse band).  Forward sweep; the two recursions share A and are scanned together.
+// out: m [B,N+1,D], Sd [B,N+1,D,D].  Time-sharded: `first` = the stretch starts at node 0 of the chain (state from
+// mu0 / cholP0), otherwise from carry_in; the last row written is the state of the node after the stretch.
+template <int D>
+using MomOps = PairOps<AffSymOps<D>, AffVecOps<D>>;
+
+template <int D, int T, int L, int MODE, int NSTAGE = 1>
+__global__ void __launch_bounds__(T)
+k_moments_tiled(const double* __restrict__ A, const double* __restrict__ bo, const double* __restrict__ cholQ,
+                const double* __restrict__ mu0, const double* __restrict__ cholP0, double* __restrict__ m,
+                double* __restrict__ Sd, int64_t B, int64_t N, int nseg, int64_t seg_len,
+                const typename MomOps<D>::State* __restrict__ carry_in,
+                typename MomOps<D>::State* __restrict__ init_out, typename MomOps<D>::Elem* __restrict__ seg_elem,
+                int first = 1) {
+    constexpr int DD = D * D, TL = T * L;
+    using Ops = MomOps<D>;
+    constexpr int SM = tile_slots(TL * DD), SV = tile_slots(TL * D);
+    constexpr int kStage = 2 * SM + SV;                                    // A, chol Q, b
+    extern __shared__ __align__(16) double smem[];
+    double* stage0 = smem + kRingHeaderDoubles;
+    typename Ops::Elem* wtot = reinterpret_cast<typename Ops::Elem*>(stage0 + NSTAGE * kStage);
+    TileRing<NSTAGE> ring;
+    ring.init(smem);
+    const int64_t b = blockIdx.x / nseg;
+    const int seg = (int)(blockIdx.x % nseg);
+    const int64_t t0 = seg * seg_len, t1 = min(N, t0 + seg_len);
+    const int64_t n = N + 1;
+    const int ntiles = (int)((t1 - t0 + TL - 1) / TL);
+    auto issue = [&](int ti) {
+        const int64_t tk = t0 + (int64_t)ti * TL;
+        const int cnt = (int)min((int64_t)TL, t1 - tk);
+        double* base = stage0 + (ti % NSTAGE) * kStage;
+        uint64_t* bar = ring.bar + ti % NSTAGE;
+        uint32_t bytes = tile_fetch(base, A + (b * N + tk) * DD, cnt * DD, bar);
+        bytes += tile_fetch(base + SM, cholQ + (b * N + tk) * DD, cnt * DD, bar);
+        bytes += tile_fetch(base + 2 * SM, bo + (b * N + tk) * D, cnt * D, bar);
+        mbar_arrive_expect_tx(bar, bytes);
+    };
+    if (threadIdx.x == 0 && ntiles > 0) issue(0);
+    typename Ops::State st;
+    st.a = mat_zero<D>();
+    st.b = vec_zero<D>();
+    if (MODE == SWEEP_FULL && (seg > 0 || !first)) st = carry_in[b * nseg + seg];
+    typename Ops::Elem seg_tot = Ops::identity();
+    for (int ti = 0; ti < ntiles; ++ti) {
+        const int64_t tk = t0 + (int64_t)ti * TL;
+        const int cnt = (int)min((int64_t)TL, t1 - tk);
+        if (NSTAGE == 1 && ti > 0) {
+            __syncthreads();
+            if (threadIdx.x == 0) { bulk_wait_read(); issue(ti); }
+        }
+        ring.wait(ti);
+        double* base = stage0 + (ti % NSTAGE) * kStage;
+        double* sA = base + tile_off(A + (b * N + tk) * DD);                  // A of transition i
+        double* sQ = base + SM + tile_off(cholQ + (b * N + tk) * DD);         // chol Q of transition i -> S of node i + 1
+        double* sb = base + 2 * SM + tile_off(bo + (b * N + tk) * D);         // offset of transition i -> m of node i + 1
+        if (seg == 0 && tk == 0) {
+            if (first) {
+                const Mat<D> c0 = mat_load<D>(cholP0 + b * DD);
+                st.a = mmT(c0, c0);
+                st.b = vec_load<D>(mu0 + b * D);
+                if (MODE != SWEEP_FULL && threadIdx.x == 0) init_out[b] = st;
+            }
+            if (MODE == SWEEP_FULL && threadIdx.x == 0) {
+                vec_store<D>(m + b * n * D, st.b);
+                mat_store<D>(Sd + b * n * DD, st.a);
+            }
+        }
+        const int k0 = threadIdx.x * L;
+        const int len = min(L, cnt - k0);
+        typename Ops::Elem e = Ops::identity();
+        for (int t = 0; t < len; ++t) {
+            typename Ops::Elem s;
+            const Mat<D> Ak = mat_load<D>(sA + (k0 + t) * DD), cc = mat_load<D>(sQ + (k0 + t) * DD);
+            s.a.G = transpose(Ak);
+            s.a.C = mmT(cc, cc);
+            s.b.M = Ak;
+            s.b.v = vec_load<D>(sb + (k0 + t) * D);
+            e = Ops::combine(e, s);
+        }
+        if (NSTAGE > 1 && threadIdx.x == 0 && ti + 1 < ntiles) {
+            bulk_wait_read();
+            issue(ti + 1);
+        }
+        typename Ops::Elem total;
+        const typename Ops::Elem excl = block_exclusive_scan<Ops, T>(e, wtot, total);
+        if (MODE != SWEEP_FULL) {
+            seg_tot = Ops::combine(seg_tot, total);
+            continue;
+        }
+        typename Ops::State s = Ops::apply(excl, st);
+        st = Ops::apply(total, st);
+        for (int t = 0; t < len; ++t) {
+            const Mat<D> Ak = mat_load<D>(sA + (k0 + t) * DD), cc = mat_load<D>(sQ + (k0 + t) * DD);
+            s.b = vec_load<D>(sb + (k0 + t) * D) + mv(Ak, s.b);
+            s.a = sym(mmT(cc, cc) + mmT(mm(Ak, s.a), Ak));
+            vec_store<D>(sb + (k0 + t) * D, s.b);
+            mat_store<D>(sQ + (k0 + t) * DD, s.a);
+        }
+        fence_async_smem();
+        __syncthreads();
+        tile_store<T>(m + (b * n + tk + 1) * D, sb, cnt * D);
+        tile_store<T>(Sd + (b * n + tk + 1) * DD, sQ, cnt * DD);
+        if (threadIdx.x == 0) bulk_commit();
+    }
+    if (threadIdx.x == 0) {
+        if (MODE != SWEEP_FULL) seg_elem[b * nseg + seg] = seg_tot;
+        bulk_wait_all();
+    }
+}
+
+template <int D, int T, int L, int NSTAGE = 1>
+constexpr size_t moments_tiled_smem() {
+    return ((size_t)kRingHeaderDoubles + (size_t)NSTAGE * (2 * tile_slots(T * L * D * D) + tile_slots(T * L * D))) *
+               sizeof(double) +
+           (T / 32) * sizeof(typename MomOps<D>::Elem);
+}
+
+
 }  // namespace vdp

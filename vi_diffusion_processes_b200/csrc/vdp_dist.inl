@@ -29,6 +29,18 @@ constexpr int kDistStagesN = VDP_DIST_STAGES_N;
 #endif
 template <int D>
 constexpr int64_t kDistTarget = (D == 3) ? VDP_DIST_TARGET3 : kTargetBlocks;
+// grid steps per thread of the information-form sweep and of the moment sweep (three staged arrays each: 32 KB per
+// CTA of 64 threads in D = 3 at 3 steps per thread)
+#ifndef VDP_LINFO3
+#define VDP_LINFO3 3
+#endif
+#ifndef VDP_LMOM3
+#define VDP_LMOM3 3
+#endif
+template <int D>
+constexpr int kInfoL = (D == 3) ? VDP_LINFO3 : TileCfg<D>::Ln;
+template <int D>
+constexpr int kMomentsL = (D == 3) ? VDP_LMOM3 : TileCfg<D>::Lm;
 
 template <class Ops>
 __global__ void k_seg_total(const typename Ops::Elem* __restrict__ el, int nseg, int reverse,
@@ -236,6 +248,54 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
         VDP_CHECK_LAUNCH();
         return VDP_OK;
     }
+    case VDP_SWEEP_INFO: {
+        using Ops = InfoOps<D>;
+        constexpr int L = kInfoL<D>;
+        constexpr size_t smem = info_tiled_smem<D, C::T, L, 1>();
+        const SegPlan pl = plan_segments(1, N, C::T * L, true, kDistTarget<D>);
+        DistBufs<Ops> b;
+        if (!dist_take<Ops>(sc, pl.nseg, b)) break;
+        if (phase == 0) {
+            if ((rc = allow_smem(k_info_tiled<D, C::T, L, SWEEP_SUMMARY, 1>, smem))) return rc;
+            k_info_tiled<D, C::T, L, SWEEP_SUMMARY, 1><<<pl.nseg, C::T, smem, st>>>(
+                p.in[0], p.in[1], p.in[2], p.out[0], p.out[1], p.out[2], p.out[3], p.out[4], 1, N, pl.nseg, pl.seg_len,
+                nullptr, (typename Ops::State*)init_blob, b.el, p.status, first, last);
+            VDP_CHECK_LAUNCH();
+            launch_seg_total<Ops>(b.el, pl.nseg, 1, (typename Ops::Elem*)total_blob, st);
+        } else {
+            if ((rc = dist_carries<Ops>(b, totals, inits, p.rank, p.nranks, 1, pl.nseg, st))) return rc;
+            if ((rc = allow_smem(k_info_tiled<D, C::T, L, SWEEP_FULL, 1>, smem))) return rc;
+            k_info_tiled<D, C::T, L, SWEEP_FULL, 1><<<pl.nseg, C::T, smem, st>>>(
+                p.in[0], p.in[1], p.in[2], p.out[0], p.out[1], p.out[2], p.out[3], p.out[4], 1, N, pl.nseg, pl.seg_len,
+                b.carry, nullptr, nullptr, p.status, first, last);
+        }
+        VDP_CHECK_LAUNCH();
+        return VDP_OK;
+    }
+    case VDP_SWEEP_MOMENTS: {
+        using Ops = MomOps<D>;
+        constexpr int L = kMomentsL<D>;
+        constexpr size_t smem = moments_tiled_smem<D, C::T, L, 1>();
+        const SegPlan pl = plan_segments(1, N, C::T * L, true, kDistTarget<D>);
+        DistBufs<Ops> b;
+        if (!dist_take<Ops>(sc, pl.nseg, b)) break;
+        if (phase == 0) {
+            if ((rc = allow_smem(k_moments_tiled<D, C::T, L, SWEEP_SUMMARY, 1>, smem))) return rc;
+            k_moments_tiled<D, C::T, L, SWEEP_SUMMARY, 1><<<pl.nseg, C::T, smem, st>>>(
+                p.in[0], p.in[1], p.in[2], p.in[3], p.in[4], p.out[0], p.out[1], 1, N, pl.nseg, pl.seg_len, nullptr,
+                (typename Ops::State*)init_blob, b.el, first);
+            VDP_CHECK_LAUNCH();
+            launch_seg_total<Ops>(b.el, pl.nseg, 0, (typename Ops::Elem*)total_blob, st);
+        } else {
+            if ((rc = dist_carries<Ops>(b, totals, inits, p.rank, p.nranks, 0, pl.nseg, st))) return rc;
+            if ((rc = allow_smem(k_moments_tiled<D, C::T, L, SWEEP_FULL, 1>, smem))) return rc;
+            k_moments_tiled<D, C::T, L, SWEEP_FULL, 1><<<pl.nseg, C::T, smem, st>>>(
+                p.in[0], p.in[1], p.in[2], p.in[3], p.in[4], p.out[0], p.out[1], 1, N, pl.nseg, pl.seg_len, b.carry,
+                nullptr, nullptr, first);
+        }
+        VDP_CHECK_LAUNCH();
+        return VDP_OK;
+    }
     default:
         set_error("unknown sweep kind %d", p.kind);
         return VDP_E_BADARG;
@@ -266,6 +326,8 @@ int vdp_dist_blob_bytes(int kind, int stage, int D, size_t* total_bytes, size_t*
         case VDP_SWEEP_MARG: *total_bytes = sizeof(typename MargOps<kD>::Elem); *init_bytes = sizeof(typename MargOps<kD>::State); break;
         case VDP_SWEEP_INVBAND: *total_bytes = sizeof(AffSymElem<kD>); *init_bytes = sizeof(Mat<kD>); break;
         case VDP_SWEEP_MEAN: *total_bytes = sizeof(AffVecElem<kD>); *init_bytes = sizeof(Vec<kD>); break;
+        case VDP_SWEEP_INFO: *total_bytes = sizeof(InfoElem<kD>); *init_bytes = sizeof(InfoState<kD>); break;
+        case VDP_SWEEP_MOMENTS: *total_bytes = sizeof(typename MomOps<kD>::Elem); *init_bytes = sizeof(typename MomOps<kD>::State); break;
         case VDP_SWEEP_NAT2SSM:
             if (stage == 0) { *total_bytes = sizeof(AffSymElem<kD>); *init_bytes = sizeof(Mat<kD>); }
             else { *total_bytes = sizeof(AffVecElem<kD>); *init_bytes = sizeof(Vec<kD>); }

@@ -60,13 +60,14 @@ class TimeShardedCvi:
 
     def __init__(self, drift_id, drift_params, q, time_grid, obs_idx, obs_y, lik_chol, x0_mu, x0_cov, comm: Comm,
                  device="cuda", stabilize_ssm=True, clip_state_transitions=(-1.0, 1.0), refactor_precision=False,
-                 carry_naturals=True):
+                 carry_naturals=True, info_rebuild=False):
         tg = np.asarray(time_grid, dtype=np.float64)
         self.N = N = tg.shape[0] - 1
         self.D = D = np.atleast_2d(np.asarray(q)).shape[0]
         self.comm = comm
         self.refactor_precision = bool(refactor_precision)
         self.carry_naturals, self._th_sig = bool(carry_naturals), None
+        self.info_rebuild = bool(info_rebuild)
         self.device = torch.device(device)
         self.chain = TimeShardedChain(N, D, comm, device=device)
         obs_idx = np.asarray(obs_idx, dtype=np.int64).reshape(-1)
@@ -121,7 +122,19 @@ class TimeShardedCvi:
             self._call(st, "vdp_cvi_full_sites", 0.0, 0.0, C.c_void_p(st.th1.data_ptr()), C.c_void_p(st.thd.data_ptr()),
                        C.c_void_p(st.ths.data_ptr()))
         own = [self._own(st) for st in self.ranks]
-        if self.refactor_precision:
+        if self.info_rebuild:
+            # two sweeps: information form from the bottom (transitions straight from the naturals, no factor, no
+            # inverse band), moments from the top; straight into the engines' arrays
+            outs, mouts = [], []
+            for st in self.ranks:
+                e, lo, nt = st.eng, st.lo, st.nt
+                outs.append(dict(A=e.qA[0, lo:lo + nt], b=e.qb[0, lo:lo + nt], cholQ=e.qcholQ[0, lo:lo + nt]))
+                mouts.append((e.fx_mus[0, lo:lo + nt + 1], e.fx_covs[0, lo:lo + nt + 1]))
+            ssm = self.chain.naturals_to_ssm_info([o[0] for o in own], [o[1] for o in own], [o[2] for o in own],
+                                                  out=outs)
+            marg = self.chain.ssm_moments([o["A"] for o in ssm], [o["b"] for o in ssm], [o["cholQ"] for o in ssm],
+                                          [o["mu0"] for o in ssm], [o["cholP0"] for o in ssm], out=mouts)
+        elif self.refactor_precision:
             # the reference's route (gauss_markov.py:107-117): precision rebuilt from the SSM, factorised again,
             # diagonal of its inverse band
             ssm = self.chain.naturals_to_ssm([o[0] for o in own], [o[1] for o in own], [o[2] for o in own])
@@ -204,7 +217,7 @@ class TimeShardedCvi:
             ptrs += [int(e.route_flags), e.dt, e.clip, e.stabilize_ssm] + [float(x) for x in e.drift_params]
             ptrs += e.x0_mu.tolist() + e.x0_cov.reshape(-1).tolist() + e.q.reshape(-1).tolist() \
                 + e.lik_chol.reshape(-1).tolist()
-        return (float(lr_data), float(lr_girsanov), self.refactor_precision,
+        return (float(lr_data), float(lr_girsanov), self.refactor_precision, self.info_rebuild,
                 tuple(_lib.config_get(k) for k in _lib.CONFIG_KEYS), tuple(ptrs))
 
     def site_update_graphed(self, lr_data, lr_girsanov):

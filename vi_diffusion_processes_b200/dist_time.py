@@ -304,6 +304,69 @@ class TimeShardedChain:
         _run_sweep(self.comm, self.ranks, _lib.SWEEP_MEAN, mean, D)
         return [m[i][:rk.N_local + (1 if rk.last else 0)] for i, rk in enumerate(self.ranks)]
 
+    # ---- the rebuild in two sweeps: information form from the bottom, moments from the top
+    def naturals_to_ssm_info(self, th1: List[torch.Tensor], thd: List[torch.Tensor], ths: List[torch.Tensor],
+                             out: Optional[List[dict]] = None):
+        """naturals_to_ssm_params as ONE backward sweep in information form (``VDP_SWEEP_INFO``: the Schur complements
+        of the precision taken from the bottom with the linear term riding along; csrc/scan_elems.cuh InfoOps).  No
+        factor is stored, no halo of the inputs is exchanged, every output lands at the index of its transition.
+        Returns per local rank a dict A [n,D,D], b [n,D], cholQ [n,D,D], mu0 / cholP0 (rank 0, else None).
+        ``out`` (optional, per local rank): ``A``, ``b``, ``cholQ`` arrays to write into."""
+        D, dev = self.D, self.ranks[0].device
+        A, bo, qo, mu0, cP0 = [], [], [], [], []
+        for i, rk in enumerate(self.ranks):
+            n = rk.N_local
+            o = out[i] if out is not None else {}
+            A.append(o["A"] if "A" in o else torch.empty((n, D, D), dtype=F64, device=dev))
+            bo.append(o["b"] if "b" in o else torch.empty((n, D), dtype=F64, device=dev))
+            qo.append(o["cholQ"] if "cholQ" in o else torch.empty((n, D, D), dtype=F64, device=dev))
+            mu0.append(torch.zeros(D, dtype=F64, device=dev))
+            cP0.append(torch.zeros((D, D), dtype=F64, device=dev))
+            for t, shape in ((A[-1], (n, D, D)), (bo[-1], (n, D)), (qo[-1], (n, D, D))):
+                assert tuple(t.shape) == shape and t.is_contiguous(), (tuple(t.shape), shape)
+            n_own = n + (1 if rk.last else 0)
+            assert th1[i].shape[0] == n_own and thd[i].shape[0] == n_own and ths[i].shape[0] == n
+        idx = {id(rk): i for i, rk in enumerate(self.ranks)}
+
+        def info(rk, stage, prev):
+            i = idx[id(rk)]
+            return rk.sweep(_lib.SWEEP_INFO, 0, [th1[i].contiguous(), thd[i].contiguous(), ths[i].contiguous()],
+                            [A[i], bo[i], qo[i], mu0[i], cP0[i]])
+        _run_sweep(self.comm, self.ranks, _lib.SWEEP_INFO, info, D)
+        return [dict(A=A[i], b=bo[i], cholQ=qo[i], mu0=mu0[i] if rk.first else None,
+                     cholP0=cP0[i] if rk.first else None) for i, rk in enumerate(self.ranks)]
+
+    def ssm_moments(self, A: List[torch.Tensor], b: List[torch.Tensor], cholQ: List[torch.Tensor],
+                    mu0: List[Optional[torch.Tensor]], cholP0: List[Optional[torch.Tensor]],
+                    out: Optional[List[tuple]] = None):
+        """StateSpaceModel.marginals (state_space_model.py:231-262) by the moment recursion m' = A m + b,
+        S' = A S A^T + Q (``VDP_SWEEP_MOMENTS``), time-sharded.  Returns per local rank (m [n_own, D], S [n_own, D, D]).
+        ``out`` (optional): per local rank (m [n + 1, D], S [n + 1, D, D]) to write into -- the sweep of a rank also
+        produces the moments of the next rank's first grid point, in the last row."""
+        D, dev = self.D, self.ranks[0].device
+        if out is None:
+            out = [(torch.empty((rk.N_local + 1, D), dtype=F64, device=dev),
+                    torch.empty((rk.N_local + 1, D, D), dtype=F64, device=dev)) for rk in self.ranks]
+        for rk, (m, S) in zip(self.ranks, out):
+            assert tuple(m.shape) == (rk.N_local + 1, D) and m.is_contiguous()
+            assert tuple(S.shape) == (rk.N_local + 1, D, D) and S.is_contiguous()
+        idx = {id(rk): i for i, rk in enumerate(self.ranks)}
+        dummy_v = torch.zeros(D, dtype=F64, device=dev)
+        dummy_m = torch.zeros((D, D), dtype=F64, device=dev)
+
+        def mom(rk, stage, prev):
+            i = idx[id(rk)]
+            return rk.sweep(_lib.SWEEP_MOMENTS, 0,
+                            [A[i].contiguous(), b[i].contiguous(), cholQ[i].contiguous(),
+                             mu0[i] if rk.first else dummy_v, cholP0[i] if rk.first else dummy_m],
+                            [out[i][0], out[i][1]])
+        _run_sweep(self.comm, self.ranks, _lib.SWEEP_MOMENTS, mom, D)
+        res = []
+        for rk, (m, S) in zip(self.ranks, out):
+            k = rk.N_local + (1 if rk.last else 0)
+            res.append((m[:k], S[:k]))
+        return res
+
     def ssm_marginals(self, A: List[torch.Tensor], b: List[torch.Tensor], cholQ: List[torch.Tensor],
                       mu0: List[Optional[torch.Tensor]], cholP0: List[Optional[torch.Tensor]]):
         """StateSpaceModel.marginals (state_space_model.py:231-262), time-sharded.  Returns per local rank
