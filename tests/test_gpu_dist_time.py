@@ -121,3 +121,39 @@ def test_time_sharded_rebuild_long_chain_8_ranks_equals_single_rank():
     # and the marginal means satisfy the forward recursion of the model they were built from
     m = res[R]["m"].cpu().numpy()
     assert np.abs(m[1:] - (np.einsum("nij,nj->ni", ssm.state_transitions, m[:-1]) + ssm.state_offsets)).max() < 1e-9
+
+
+@pytest.mark.parametrize("N,D,R", [(1_000_000, 3, 8), (30_000, 2, 3), (50_000, 1, 5), (7, 3, 2)])
+def test_information_form_rebuild_recovers_the_model_the_naturals_came_from(N, D, R):
+    """naturals of a random state-space model -> VDP_SWEEP_INFO -> the same A, b, chol Q, mu0, chol P0 back (the
+    information-form sweep inverts ssm_to_naturals exactly), and VDP_SWEEP_MOMENTS on them -> the marginals of the
+    three-sweep route; 10^6 transitions over 8 emulated ranks down to stretches shorter than a tile."""
+    from vi_diffusion_processes_b200.dist_time import Comm, TimeShardedChain
+    rng = np.random.default_rng(11 + D)
+    ssm = rand_ssm(rng, N, D)
+    th1, thd, ths = G.ssm_to_naturals(ssm)
+    chain = TimeShardedChain(N, D, Comm.emulated(R))
+    l1, ld, ls = [], [], []
+    for r in range(R):
+        s, e = chain.parts[r]
+        n0, n1 = chain.owned_nodes(r)
+        l1.append(dev(th1[n0:n1]))
+        ld.append(dev(thd[n0:n1]))
+        ls.append(dev(ths[s:e]))
+    out = chain.naturals_to_ssm_info(l1, ld, ls)
+    marg = chain.ssm_moments([o["A"] for o in out], [o["b"] for o in out], [o["cholQ"] for o in out],
+                             [o["mu0"] for o in out], [o["cholP0"] for o in out])
+    ref = chain.naturals_to_ssm(l1, ld, ls, want_cov=True)
+    ref_m = chain.ssm_means([o["A"] for o in ref], [o["b"] for o in ref], [o["mu0"] for o in ref])
+    chain.check_status()
+    got = {k: torch.cat([o[k] for o in out]).cpu().numpy() for k in ("A", "b", "cholQ")}
+    want = {"A": ssm.state_transitions, "b": ssm.state_offsets, "cholQ": ssm.cholesky_process_covariances}
+    for k in got:
+        assert np.abs(got[k] - want[k]).max() <= 1e-10 * np.abs(want[k]).max(), k
+    assert np.abs(out[0]["mu0"].cpu().numpy() - ssm.initial_mean).max() <= 1e-11
+    assert np.abs(out[0]["cholP0"].cpu().numpy() - ssm.cholesky_initial_covariance).max() <= 1e-11
+    m, S = torch.cat([x for x, _ in marg]), torch.cat([x for _, x in marg])
+    rm, rS = torch.cat(ref_m), torch.cat([o["S"] for o in ref])
+    assert m.shape == rm.shape and S.shape == rS.shape
+    assert float((m - rm).abs().max()) <= 1e-10 * max(float(rm.abs().max()), 1.0)
+    assert float((S - rS).abs().max()) <= 1e-10 * float(rS.abs().max())

@@ -29,18 +29,34 @@ constexpr int kDistStagesN = VDP_DIST_STAGES_N;
 #endif
 template <int D>
 constexpr int64_t kDistTarget = (D == 3) ? VDP_DIST_TARGET3 : kTargetBlocks;
-// grid steps per thread of the information-form sweep and of the moment sweep (three staged arrays each: 32 KB per
-// CTA of 64 threads in D = 3 at 3 steps per thread)
+// grid steps per thread of the information-form sweep and of the moment sweep (three staged arrays each: 27 KB per
+// CTA of 32 threads in D = 3 at 5 steps per thread).  Measured on the 10^7-step chain, ms per update (64 threads, 888
+// segments unless noted): L = 3 / 3: 12.6; 5 / 3: 11.4; 3 / 5: 12.1; 5 / 5 with 592 segments: 9.9; 32 threads, 1184
+// segments, 5 / 5: 9.5 (3 / 3: 10.7; 7 / 7: 10.8; 5 / 9: 9.7; 888 segments: 10.7; 1776: 10.4; 2368: 9.7)
+// (profiles/r02b_tune_c5_tile_shapes.log)
 #ifndef VDP_LINFO3
-#define VDP_LINFO3 3
+#define VDP_LINFO3 5
 #endif
 #ifndef VDP_LMOM3
-#define VDP_LMOM3 3
+#define VDP_LMOM3 5
+#endif
+#ifndef VDP_TINFO3
+#define VDP_TINFO3 32
 #endif
 template <int D>
 constexpr int kInfoL = (D == 3) ? VDP_LINFO3 : TileCfg<D>::Ln;
 template <int D>
 constexpr int kMomentsL = (D == 3) ? VDP_LMOM3 : TileCfg<D>::Lm;
+// threads per CTA of the two sweeps: one warp in D = 3 (the block scan is then a warp scan with no barrier and no
+// shared-memory round; 240 registers per thread leave 8 such CTAs per SM)
+template <int D>
+constexpr int kInfoT = (D == 3) ? VDP_TINFO3 : TileCfg<D>::T;
+// ... and the segments their stretch is split into: 8 per SM
+#ifndef VDP_INFO_TARGET3
+#define VDP_INFO_TARGET3 (148 * 8)
+#endif
+template <int D>
+constexpr int64_t kInfoTarget = (D == 3) ? VDP_INFO_TARGET3 : kTargetBlocks;
 
 template <class Ops>
 __global__ void k_seg_total(const typename Ops::Elem* __restrict__ el, int nseg, int reverse,
@@ -250,22 +266,23 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
     }
     case VDP_SWEEP_INFO: {
         using Ops = InfoOps<D>;
+        constexpr int TI = kInfoT<D>;
         constexpr int L = kInfoL<D>;
-        constexpr size_t smem = info_tiled_smem<D, C::T, L, 1>();
-        const SegPlan pl = plan_segments(1, N, C::T * L, true, kDistTarget<D>);
+        constexpr size_t smem = info_tiled_smem<D, TI, L, 1>();
+        const SegPlan pl = plan_segments(1, N, TI * L, true, kInfoTarget<D>);
         DistBufs<Ops> b;
         if (!dist_take<Ops>(sc, pl.nseg, b)) break;
         if (phase == 0) {
-            if ((rc = allow_smem(k_info_tiled<D, C::T, L, SWEEP_SUMMARY, 1>, smem))) return rc;
-            k_info_tiled<D, C::T, L, SWEEP_SUMMARY, 1><<<pl.nseg, C::T, smem, st>>>(
+            if ((rc = allow_smem(k_info_tiled<D, TI, L, SWEEP_SUMMARY, 1>, smem))) return rc;
+            k_info_tiled<D, TI, L, SWEEP_SUMMARY, 1><<<pl.nseg, TI, smem, st>>>(
                 p.in[0], p.in[1], p.in[2], p.out[0], p.out[1], p.out[2], p.out[3], p.out[4], 1, N, pl.nseg, pl.seg_len,
                 nullptr, (typename Ops::State*)init_blob, b.el, p.status, first, last);
             VDP_CHECK_LAUNCH();
             launch_seg_total<Ops>(b.el, pl.nseg, 1, (typename Ops::Elem*)total_blob, st);
         } else {
             if ((rc = dist_carries<Ops>(b, totals, inits, p.rank, p.nranks, 1, pl.nseg, st))) return rc;
-            if ((rc = allow_smem(k_info_tiled<D, C::T, L, SWEEP_FULL, 1>, smem))) return rc;
-            k_info_tiled<D, C::T, L, SWEEP_FULL, 1><<<pl.nseg, C::T, smem, st>>>(
+            if ((rc = allow_smem(k_info_tiled<D, TI, L, SWEEP_FULL, 1>, smem))) return rc;
+            k_info_tiled<D, TI, L, SWEEP_FULL, 1><<<pl.nseg, TI, smem, st>>>(
                 p.in[0], p.in[1], p.in[2], p.out[0], p.out[1], p.out[2], p.out[3], p.out[4], 1, N, pl.nseg, pl.seg_len,
                 b.carry, nullptr, nullptr, p.status, first, last);
         }
@@ -274,22 +291,23 @@ static int dist_run(const vdp_dist_sweep& p, int phase, void* total_blob, void* 
     }
     case VDP_SWEEP_MOMENTS: {
         using Ops = MomOps<D>;
+        constexpr int TI = kInfoT<D>;
         constexpr int L = kMomentsL<D>;
-        constexpr size_t smem = moments_tiled_smem<D, C::T, L, 1>();
-        const SegPlan pl = plan_segments(1, N, C::T * L, true, kDistTarget<D>);
+        constexpr size_t smem = moments_tiled_smem<D, TI, L, 1>();
+        const SegPlan pl = plan_segments(1, N, TI * L, true, kInfoTarget<D>);
         DistBufs<Ops> b;
         if (!dist_take<Ops>(sc, pl.nseg, b)) break;
         if (phase == 0) {
-            if ((rc = allow_smem(k_moments_tiled<D, C::T, L, SWEEP_SUMMARY, 1>, smem))) return rc;
-            k_moments_tiled<D, C::T, L, SWEEP_SUMMARY, 1><<<pl.nseg, C::T, smem, st>>>(
+            if ((rc = allow_smem(k_moments_tiled<D, TI, L, SWEEP_SUMMARY, 1>, smem))) return rc;
+            k_moments_tiled<D, TI, L, SWEEP_SUMMARY, 1><<<pl.nseg, TI, smem, st>>>(
                 p.in[0], p.in[1], p.in[2], p.in[3], p.in[4], p.out[0], p.out[1], 1, N, pl.nseg, pl.seg_len, nullptr,
                 (typename Ops::State*)init_blob, b.el, first);
             VDP_CHECK_LAUNCH();
             launch_seg_total<Ops>(b.el, pl.nseg, 0, (typename Ops::Elem*)total_blob, st);
         } else {
             if ((rc = dist_carries<Ops>(b, totals, inits, p.rank, p.nranks, 0, pl.nseg, st))) return rc;
-            if ((rc = allow_smem(k_moments_tiled<D, C::T, L, SWEEP_FULL, 1>, smem))) return rc;
-            k_moments_tiled<D, C::T, L, SWEEP_FULL, 1><<<pl.nseg, C::T, smem, st>>>(
+            if ((rc = allow_smem(k_moments_tiled<D, TI, L, SWEEP_FULL, 1>, smem))) return rc;
+            k_moments_tiled<D, TI, L, SWEEP_FULL, 1><<<pl.nseg, TI, smem, st>>>(
                 p.in[0], p.in[1], p.in[2], p.in[3], p.in[4], p.out[0], p.out[1], 1, N, pl.nseg, pl.seg_len, b.carry,
                 nullptr, nullptr, first);
         }

@@ -60,14 +60,14 @@ class TimeShardedCvi:
 
     def __init__(self, drift_id, drift_params, q, time_grid, obs_idx, obs_y, lik_chol, x0_mu, x0_cov, comm: Comm,
                  device="cuda", stabilize_ssm=True, clip_state_transitions=(-1.0, 1.0), refactor_precision=False,
-                 carry_naturals=True, info_rebuild=False):
+                 carry_naturals=True, info_rebuild=True):
         tg = np.asarray(time_grid, dtype=np.float64)
         self.N = N = tg.shape[0] - 1
         self.D = D = np.atleast_2d(np.asarray(q)).shape[0]
         self.comm = comm
         self.refactor_precision = bool(refactor_precision)
         self.carry_naturals, self._th_sig = bool(carry_naturals), None
-        self.info_rebuild = bool(info_rebuild)
+        self.info_rebuild = bool(info_rebuild) and not self.refactor_precision   # (the reference's route wins)
         self.device = torch.device(device)
         self.chain = TimeShardedChain(N, D, comm, device=device)
         obs_idx = np.asarray(obs_idx, dtype=np.int64).reshape(-1)
