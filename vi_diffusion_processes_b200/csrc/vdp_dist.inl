@@ -48,7 +48,7 @@ constexpr int kInfoL = (D == 3) ? VDP_LINFO3 : TileCfg<D>::Ln;
 template <int D>
 constexpr int kMomentsL = (D == 3) ? VDP_LMOM3 : TileCfg<D>::Lm;
 // threads per CTA of the two sweeps: one warp in D = 3 (the block scan is then a warp scan with no barrier and no
-// shared-memory round; 240 registers per thread leave 8 such CTAs per SM)
+// shared-memory round; 27 KB of shared memory per CTA leave 8 of them per SM)
 template <int D>
 constexpr int kInfoT = (D == 3) ? VDP_TINFO3 : TileCfg<D>::T;
 // ... and the segments their stretch is split into: 8 per SM
