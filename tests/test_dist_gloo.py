@@ -163,3 +163,98 @@ def test_sharded_quadrature_exchange_world_size_2():
         assert calls == [(0, n0, n1), (1, n0, n1)]
         assert g1 == [0.0] * e0 + [1.0] * (e1 + 1 - s1)       # every rank holds every rank's site range
         assert gs == [0.0] * e0 + [1.0] * (e1 - s1)
+
+
+def _pack(e):
+    return torch.as_tensor(np.concatenate([e[k].reshape(-1) for k in ("La", "Lab", "Lb", "va", "vb")]))
+
+
+def _unpack(t, D):
+    a = t.numpy()
+    DD = D * D
+    return dict(La=a[:DD].reshape(D, D), Lab=a[DD:2 * DD].reshape(D, D), Lb=a[2 * DD:3 * DD].reshape(D, D),
+                va=a[3 * DD:3 * DD + D], vb=a[3 * DD + D:])
+
+
+def _worker_info(rank, world, port, q):
+    """The two-sweep rebuild of a time-sharded chain with the ranks in separate processes, the kernels replaced by the
+    oracle's NumPy elements (oracle/info_form_np.py): SUMMARY (the element of the rank's stretch) -> all-gather ->
+    incoming carry from the ranks AFTER this one (backward sweep) / BEFORE it (forward sweep) -> recursion over the
+    own stretch.  What the CUDA path does per rank in vdp_dist_sweep_summary / finish (VDP_SWEEP_INFO, VDP_SWEEP_MOMENTS)."""
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import gauss_markov_np as G
+        from oracle import info_form_np as I
+        from vi_diffusion_processes_b200.dist_time import Comm, time_partition
+        comm = Comm.from_process_group()
+        D, N = 2, 13
+        rng = np.random.default_rng(5)                       # the same chain on every rank; each uses its stretch
+        A = 0.6 * np.eye(D) + 0.1 * rng.normal(size=(N, D, D))
+        b = rng.normal(size=(N, D))
+        R = rng.normal(size=(N, D, D))
+        cQ = np.linalg.cholesky(0.05 * np.eye(D) + 0.02 * R @ G.mT(R))
+        ssm = G.StateSpaceModel(rng.normal(size=D), np.linalg.cholesky(0.5 * np.eye(D)), A, b, cQ)
+        t1, td, ts = G.ssm_to_naturals(ssm)
+        Kd = G.symmetrise_from_lower(-2.0 * td)
+        s, e = time_partition(N, world)[rank]
+        last = rank == world - 1
+        # ---- backward sweep in information form
+        el = None
+        for k in range(e - 1, s - 1, -1):
+            st = I.info_step(ts[k], Kd[k], t1[k])
+            el = st if el is None else I.info_combine(el, st)
+        tot = comm.all_gather([_pack(el)])
+        init = comm.all_gather([torch.as_tensor(np.concatenate([Kd[N].reshape(-1), t1[N]]) if last
+                                                else np.full(D * D + D, np.nan))])
+        J, h = init[world - 1][:D * D].numpy().reshape(D, D), init[world - 1][D * D:].numpy()
+        for r in range(world - 1, rank, -1):
+            J, h = I.info_apply(_unpack(tot[r], D), J, h)
+        As, bs, Qs = np.empty((e - s, D, D)), np.empty((e - s, D)), np.empty((e - s, D, D))
+        for k in range(e - 1, s - 1, -1):
+            Q = np.linalg.inv(J)
+            As[k - s], bs[k - s], Qs[k - s] = Q @ ts[k], Q @ h, Q
+            J, h = Kd[k] - ts[k].T @ As[k - s], t1[k] + ts[k].T @ bs[k - s]
+        # ---- forward sweep of the moments: element (M, v, C) of m' = M m + v, S' = M S M^T + C
+        M, v, Cc = np.eye(D), np.zeros(D), np.zeros((D, D))
+        for k in range(e - s):
+            M, v, Cc = As[k] @ M, As[k] @ v + bs[k], As[k] @ Cc @ As[k].T + Qs[k]
+        tot = comm.all_gather([torch.as_tensor(np.concatenate([M.reshape(-1), v, Cc.reshape(-1)]))])
+        P0 = np.linalg.inv(J) if rank == 0 else np.full((D, D), np.nan)
+        mu0 = P0 @ h if rank == 0 else np.full(D, np.nan)
+        init = comm.all_gather([torch.as_tensor(np.concatenate([mu0, P0.reshape(-1)]))])
+        m, S = init[0][:D].numpy(), init[0][D:].numpy().reshape(D, D)
+        for r in range(rank):
+            t = tot[r].numpy()
+            Mr, vr, Cr = t[:D * D].reshape(D, D), t[D * D:D * D + D], t[D * D + D:].reshape(D, D)
+            m, S = Mr @ m + vr, Mr @ S @ Mr.T + Cr
+        ms, Ss = [m], [S]
+        for k in range(e - s):
+            ms.append(As[k] @ ms[-1] + bs[k])
+            Ss.append(As[k] @ Ss[-1] @ As[k].T + Qs[k])
+        n_own = e - s + (1 if last else 0)
+        wm, wS = ssm.marginals
+        n0 = s
+        err = max(np.abs(As - A[s:e]).max(), np.abs(bs - b[s:e]).max(),
+                  np.abs(Qs - cQ[s:e] @ G.mT(cQ[s:e])).max(),
+                  np.abs(np.stack(ms[:n_own]) - wm[n0:n0 + n_own]).max(),
+                  np.abs(np.stack(Ss[:n_own]) - wS[n0:n0 + n_own]).max())
+        q.put((rank, float(err)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_two_sweep_rebuild_across_processes(world):
+    port = _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_info, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert [r for r, _ in res] == list(range(world))
+    assert max(err for _, err in res) <= 1e-11, res
