@@ -101,7 +101,9 @@ class TimeShardedCvi:
 
     def _th_signature(self):
         """what the full naturals held in ``st.th1 / thd / ths`` were computed from (torch-side writes bump _version;
-        the C calls of this class that write them are followed by a rebuild or reset ``_th_sig``)"""
+        the C calls of this class that write them are followed by a rebuild or reset ``_th_sig``).  Re-linearise through
+        :meth:`relinearize`, not through the engines directly: a replaced prior tensor can land on the address of the
+        old one with the same version count, which this signature cannot tell apart."""
         return tuple((t.data_ptr(), t._version) for st in self.ranks
                      for t in [getattr(st.eng, n) for n in self._TH_FIELDS] + [st.th1, st.thd, st.ths])
 
